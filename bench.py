@@ -1,0 +1,261 @@
+#!/usr/bin/env python
+"""bench.py -- 3D Poisson FAS V-cycle throughput (GDOF/s) on B200, with the roofline of the dominant kernel,
+an end-to-end number through the C ABI with host buffers, and the CPU oracle timed beside it.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--n 512] [--box 16]
+
+A step is one standalone V(2,2) GSRB cycle (mg_fas_vcycle, src/m_multigrid.f90:150-243) of the
+tests/test_performance.f90 problem (rhs = 1, phi0 = 0, homogeneous Dirichlet), max_res requested.
+N = 1: BASELINE.json configs[1] (512^3, box 16).  N > 1: weak scaling, 512^3 per GPU along the reference's
+Morton partition (N = 8 is configs[4], 1024^3).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+BYTES_PER_DOF_VCYCLE = 155.4 + 18.3     # Laplacian V(2,2) + max_res request
+SMOOTH_BYTES_PER_CELL = 12.0            # one colour half-sweep launched on its own
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    def __init__(self, index=0):
+        self.rows, self.index, self.proc = [], index, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index),
+                 "--query-gpu=clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+                 "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_power_cap", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def domain_for(n, world):
+    """weak scaling: n^3 per GPU; the Morton-contiguous partition of mg_load_balance gives each rank one cube"""
+    dims = [n, n, n]
+    w, d = world, 0
+    while w > 1:
+        dims[d % 3] *= 2
+        w //= 2
+        d += 1
+    return dims
+
+
+def cpu_reference_line(args, sample_n=None):
+    """the CPU arm: the oracle (C++ restatement of the reference; the Fortran/MPI reference cannot be built in
+    this image) on all host cores, one OpenMP thread per emulated MPI rank, on a bounded sample."""
+    import problems as P
+    from oracle import oracle as O
+    cores = os.cpu_count() or 1
+    ranks = 1
+    while ranks * 2 <= cores:
+        ranks *= 2
+    n = sample_n or min(args.n, 256)
+    O.lib().orc_set_omp_threads(ranks)
+    mg = P.performance_problem(O.OracleMg, n, args.box, n_cpu=ranks)
+    dof = n ** 3
+    for _ in range(max(args.warmup, 0) and 1):
+        mg.mg_fas_vcycle(want_res=True)
+    k = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(k):
+        mg.mg_fas_vcycle(want_res=True)
+    dt = time.perf_counter() - t0
+    val = dof * k / dt / 1e9
+    return {"value": val, "unit": "GDOF/s", "cores": ranks, "kind": "port",
+            "sample": "%d^3 box %d, %d V(2,2) GSRB cycles with max_res, oracle/omg_oracle.cpp, %d OpenMP threads = emulated MPI ranks"
+                      % (n, args.box, k, ranks), "ms_per_step": dt / k * 1e3}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--n", type=int, default=512)
+    ap.add_argument("--box", type=int, default=16)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dims = domain_for(args.n, world)
+    config = {"workload": "test_performance %s box %d: 7-point Laplacian, rhs=1, Dirichlet 0, standalone V(2,2) GSRB cycles with max_res"
+                          % ("x".join(map(str, dims)), args.box),
+              "n_cycle_down": 2, "n_cycle_up": 2, "smoother": "gsrb", "box_size": args.box, "domain": dims,
+              "partition": "mg_load_balance (Morton-contiguous), %d rank(s)" % world,
+              "l2": "inputs larger than L2 (4 x %.2f GB per GPU vs 126 MB)" % (args.n ** 3 * 8 / 1e9)}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cb = cpu_reference_line(args)
+        line = {"impl": "reference", "metric": "3D Poisson FAS V-cycle throughput", "value": cb["value"], "unit": "GDOF/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": config, "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": cb["value"], "unit": "GDOF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "reference MPI Fortran build unavailable on this box (no Fortran compiler / MPI); CPU arm = oracle port"}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import octree_mg_b200 as om
+    import problems as P
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    # tests/test_performance.f90:51-66 without host cc arrays (the run is device-resident)
+    mg = om.Mg(P.mg_laplacian, P.mg_smoother_gsrb, n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
+    mg.set_int("host_cc", 0)
+    for nb in range(1, 7):
+        mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
+    mg.mg_set_methods()
+    mg.mg_build_rectangle(dims, args.box, [1.0 / dims[0]] * 3, [0.0] * 3, [False] * 3)
+    mg.mg_load_balance()
+    mg.mg_load_balance_parents()
+    mg.mg_allocate_storage()
+    if world > 1:
+        uid = C.create_string_buffer(128)
+        if rank == 0:
+            mg.G.omg_nccl_unique_id(uid)
+        t = torch.frombuffer(bytearray(uid.raw), dtype=torch.uint8).cuda()
+        dist.broadcast(t, 0)
+        uid = C.create_string_buffer(bytes(t.cpu().numpy().tobytes()), 128)
+        mg._gck(mg.G.omg_comm_init(mg.gpu, uid, rank, world))
+    dof = dims[0] * dims[1] * dims[2]
+    G, gpu = mg.G, mg.gpu
+    # device-resident initial state: rhs = 1 on the interior of every level, phi = 0 (no host transfer needed)
+    mg._gck(G.omg_set_var_const(gpu, P.mg_irhs, -20, 20, 1.0, 1))
+    mg._gck(G.omg_set_var_const(gpu, P.mg_iphi, -20, 20, 0.0, 0))
+    mg.mg_fas_vcycle(want_res=True)                       # uploads parameters; first cycle also builds the graph
+    for _ in range(max(args.warmup - 1, 0)):
+        mg.fas_vcycles(1)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    res, ms = mg.fas_vcycles(args.steps)                  # CUDA events on the handle's stream bracket the K cycles
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        tms = torch.tensor([ms], device="cuda")
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    launches_per_step = None
+    l0 = mg.stat("launches")
+    mg.fas_vcycles(1)
+    launches_per_step = mg.stat("launches") - l0
+
+    # --- roofline of the dominant kernel (finest-level GSRB colour half-sweep), timed live with CUDA events
+    mg.set_option("profile", 1)
+    mg.fas_vcycles(2)
+    sm_ms = float(G.omg_last_ms(gpu, b"smooth"))
+    n_sm = int(G.omg_last_ms(gpu, b"n_smooth"))
+    prof = {k: float(G.omg_last_ms(gpu, k.encode())) for k in ("smooth", "resid_restrict", "corr_prolong", "resid")}
+    mg.set_option("profile", 0)
+    peak, peak_src = peaks()
+    cells_per_rank = dof / world
+    achieved = SMOOTH_BYTES_PER_CELL * cells_per_rank / (sm_ms * 1e-3) / 1e9 if sm_ms > 0 else None
+    roofline = {"bound": "hbm", "kernel": "gsrb colour half-sweep, finest level (%d launches timed)" % n_sm,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
+                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": SMOOTH_BYTES_PER_CELL * cells_per_rank,
+                "ms_per_launch": sm_ms, "finest_level_ms": prof}
+    value = dof * args.steps / (ms * 1e-3) / 1e9
+    cycle_frac = BYTES_PER_DOF_VCYCLE * value / peak / world
+
+    # --- end to end through the C ABI with host buffers: push phi + rhs (pinned), cycle, pull phi
+    e2e = None
+    if not args.no_e2e:
+        nd = int(G.omg_packed_size(gpu, -20, 20))
+        hphi = torch.zeros(nd, dtype=torch.float64).pin_memory()
+        hrhs = torch.ones(nd, dtype=torch.float64).pin_memory()
+        r = C.c_double(0.0)
+        k2 = max(1, min(args.steps, 3))
+
+        def step():
+            mg._gck(G.omg_push_var_packed(gpu, P.mg_iphi, -20, 20, C.c_void_p(hphi.data_ptr()), nd))
+            mg._gck(G.omg_push_var_packed(gpu, P.mg_irhs, -20, 20, C.c_void_p(hrhs.data_ptr()), nd))
+            mg._gck(G.omg_fas_vcycle(gpu, 0, 0, 1, 1, C.byref(r)))
+            mg._gck(G.omg_pull_var_packed(gpu, P.mg_iphi, -20, 20, C.c_void_p(hphi.data_ptr()), nd, 1))
+        step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k2):
+            step()
+        barrier()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            tt = torch.tensor([dt], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt.item())
+        e2e = {"value": dof * k2 / dt / 1e9, "unit": "GDOF/s", "h2d_bytes_per_step": 2 * nd * 8 * world,
+               "d2h_bytes_per_step": nd * 8 * world + 8, "steps": k2, "ms_per_step": dt / k2 * 1e3,
+               "what": "omg_push_var_packed(phi, rhs) from pinned host slabs (ghost shells included) + omg_fas_vcycle + omg_pull_var_packed(phi)"}
+
+    if rank != 0:
+        return
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        cb = cpu_reference_line(args)
+        cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    line = {"metric": "3D Poisson FAS V-cycle throughput", "value": value, "unit": "GDOF/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+            "roofline": roofline, "cycle_hbm_frac": cycle_frac, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": launches_per_step * args.steps if launches_per_step else None,
+            "launches_per_step": launches_per_step, "clocks": clocks, "residuals": res,
+            "ref_style_unknowns_per_us": None}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,138 @@
+/* include/omg_gpu.h -- C ABI of libomg_b200.so
+ *
+ * Drop-in boundary for octree-mg's multigrid-cycle hot path on NVIDIA B200
+ * (sm_100a).  A host (the Fortran shim in octree-mg_b200/fortran/, the C++ host
+ * mirror in octree-mg_b200/host/, or any FFI) keeps the reference's data model
+ * (mg_t, tree construction, load balancing, storage) and
+ * calls these entry points instead of the bodies of src/m_multigrid.f90 and the
+ * level-wide routines of src/m_ghost_cells.f90 / m_restrict.f90 / m_prolong.f90.
+ *
+ * Conventions
+ *  - plain C, no torch / C++ types; every function returns 0 on success and a
+ *    non-zero code on failure, omg_last_error() gives the message (the
+ *    reference `error stop`s; the shim converts codes back to error stop).
+ *  - box ids, variable indices (iv) and neighbour indices (nb) are 1-based
+ *    exactly as in the reference (mg_iphi=1, mg_irhs=2, mg_iold=3, mg_ires=4,
+ *    mg_iveps=5..; nb 1..6 = -x,+x,-y,+y,-z,+z).
+ *  - a host box variable is the reference's contiguous cc(0:nc+1,0:nc+1,0:nc+1,iv)
+ *    slice: (nc+2)^3 doubles, i fastest (src/m_data_structures.f90:206).
+ *  - there is no CPU fallback: without a CUDA device every call fails loudly.
+ */
+#ifndef OMG_GPU_H
+#define OMG_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OMG_LVL_LO (-20)   /* mg_lvl_lo, src/m_data_structures.f90:62 */
+#define OMG_LVL_HI 20      /* mg_lvl_hi, :64 */
+#define OMG_NLVL 41
+#define OMG_MAX_VARS 10    /* mg_max_num_vars, :36 */
+
+typedef struct omg_handle omg_handle;
+
+/* Flattened view of type(mg_t) tree metadata (src/m_data_structures.f90:250-342,
+ * per-box fields :194-207, level lists :181-191).  All arrays are read during the
+ * call only.  Per-box arrays are indexed [id-1]. */
+typedef struct omg_tree_desc {
+  int32_t n_boxes;              /* mg%n_boxes */
+  int32_t box_size;             /* mg%box_size */
+  int32_t lowest_lvl, highest_lvl, first_normal_lvl;
+  int32_t my_rank, n_cpu;       /* mg%my_rank, mg%n_cpu */
+  int32_t n_extra_vars;         /* mg%n_extra_vars */
+  int32_t periodic[3];          /* mg%periodic */
+  const int32_t* box_size_lvl;  /* [OMG_NLVL], index lvl - OMG_LVL_LO */
+  const double*  dr;            /* [OMG_NLVL][3] */
+  const int32_t* box_rank;      /* [n_boxes]    boxes(id)%rank */
+  const int32_t* box_lvl;       /* [n_boxes]    boxes(id)%lvl */
+  const int32_t* box_ix;        /* [n_boxes][3] boxes(id)%ix */
+  const int32_t* box_parent;    /* [n_boxes]    boxes(id)%parent */
+  const int32_t* box_children;  /* [n_boxes][8] boxes(id)%children */
+  const int32_t* box_neighbors; /* [n_boxes][6] boxes(id)%neighbors (>0 id, 0 refinement bnd, <0 physical) */
+  const int32_t* lvl_ptr;       /* [OMG_NLVL+1] CSR offsets into lvl_ids, index lvl - OMG_LVL_LO */
+  const int32_t* lvl_ids;       /* mg%lvls(lvl)%ids in the reference's order */
+} omg_tree_desc;
+
+/* Cycle parameters read by mg_set_methods / mg_fas_* (src/m_data_structures.f90:300-327,
+ * lambda: src/m_helmholtz.f90:11, m_vhelmholtz.f90:12, m_ahelmholtz.f90:12). */
+typedef struct omg_params {
+  int32_t operator_type;        /* mg_laplacian=1 .. mg_ahelmholtz=5 */
+  int32_t smoother_type;        /* mg_smoother_gs=1, mg_smoother_gsrb=2 */
+  int32_t geometry_type;        /* mg_cartesian=1 only */
+  int32_t n_cycle_down, n_cycle_up, max_coarse_cycles;
+  int32_t subtract_mean;        /* mg%subtract_mean after mg_set_methods / mg_build_rectangle */
+  double  residual_coarse_abs, residual_coarse_rel;
+  double  lambda;               /* helmholtz_lambda / vhelmholtz_lambda / ahelmholtz_lambda */
+} omg_params;
+
+/* ---- lifetime ------------------------------------------------------------ */
+int omg_create(int device, omg_handle** out);             /* one handle per mg_t, bound to one GPU */
+int omg_destroy(omg_handle* h);                           /* mg_deallocate_storage, src/m_allocate_storage.f90:14-47 */
+const char* omg_last_error(const omg_handle* h);          /* message of the last failing call */
+const char* omg_version(void);
+
+/* ---- setup (replaces what mg_allocate_storage sizes, src/m_allocate_storage.f90:51-99) */
+int omg_set_tree(omg_handle* h, const omg_tree_desc* t);  /* device mirrors, all variables zero-filled (:72-76) */
+int omg_set_params(omg_handle* h, const omg_params* p);   /* mg_set_methods, src/m_multigrid.f90:27-60 */
+
+/* Physical boundary conditions of variable iv (mg%bc(nb, iv), src/m_data_structures.f90:232-242).
+ * omg_set_bc_const: bc_type/bc_value constants.  omg_set_bc_plane: the plane a
+ * boundary_cond callback (or mg_phi_bc_store, src/m_ghost_cells.f90:66-117) yields for one
+ * boundary face of one box: nc*nc doubles, first tangential index fastest, plus its bc_type. */
+int omg_set_bc_const(omg_handle* h, int iv, int nb, int bc_type, double bc_value);
+int omg_set_bc_plane(omg_handle* h, int box_id, int nb, int bc_type, const double* plane);
+
+/* ---- host <-> device coherence (hosts read/write mg%boxes(id)%cc directly) */
+/* ptrs[i] -> cc(:,:,:,iv) of box ids[i] ((nc+2)^3 doubles).  push reads interior cells (and,
+ * for iv >= 5, the six ghost faces, which hold user data such as eps); pull writes interior
+ * cells and, when with_ghosts != 0, the six ghost faces as the reference would hold them. */
+int omg_push_var(omg_handle* h, int iv, int n, const int32_t* ids, const double* const* ptrs);
+int omg_pull_var(omg_handle* h, int iv, int n, const int32_t* ids, double* const* ptrs, int with_ghosts);
+/* Same, for all owned boxes of levels lvl_lo..lvl_hi from/to one packed host buffer (boxes in
+ * my_ids order, each (nc+2)^3 doubles); intended for pinned staging buffers. */
+int omg_push_var_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const double* buf, int64_t n_doubles);
+int omg_pull_var_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, double* buf, int64_t n_doubles, int with_ghosts);
+int64_t omg_packed_size(omg_handle* h, int lvl_lo, int lvl_hi);  /* doubles needed by the packed calls */
+int omg_set_var_const(omg_handle* h, int iv, int lvl_lo, int lvl_hi, double value, int interior_only);
+
+/* ---- the hot path -------------------------------------------------------- */
+/* mg_fas_vcycle(mg, highest_lvl, max_res, standalone), src/m_multigrid.f90:150-243.
+ * Optional Fortran arguments become explicit flags. */
+int omg_fas_vcycle(omg_handle* h, int has_highest_lvl, int highest_lvl, int standalone,
+                   int want_res, double* max_res);
+/* mg_fas_fmg(mg, have_guess, max_res), src/m_multigrid.f90:84-147 */
+int omg_fas_fmg(omg_handle* h, int have_guess, int want_res, double* max_res);
+/* mg_fill_ghost_cells_lvl, src/m_ghost_cells.f90:131-175 (refreshes device ghost state of iv) */
+int omg_fill_ghost_cells_lvl(omg_handle* h, int lvl, int iv);
+/* mg_restrict_lvl, src/m_restrict.f90:83-114 */
+int omg_restrict_lvl(omg_handle* h, int iv, int lvl);
+/* mg_prolong with the default mg_prolong_sparse, src/m_prolong.f90:51-85,159-240 */
+int omg_prolong(omg_handle* h, int lvl, int iv, int iv_to, int add);
+/* mg_apply_op with the built-in operator, src/m_multigrid.f90:439-456 */
+int omg_apply_op(omg_handle* h, int i_out);
+/* repeat n V-cycles back to back without host round trips (benchmark loop of
+ * tests/test_performance.f90:68-76); residuals[n] receives max_res per cycle when non-null */
+int omg_fas_vcycles(omg_handle* h, int n, double* residuals);
+
+/* ---- multi-GPU (replaces mg_comm_init + sort_and_transfer_buffers, src/m_communication.f90) */
+int omg_nccl_unique_id(char out[128]);
+int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks);
+/* Emulated ranks inside one process / one GPU (tests): handles exchange through device copies. */
+int omg_comm_init_local(omg_handle* const* handles, int nranks);
+
+/* ---- diagnostics ----------------------------------------------------------- */
+int omg_sync(omg_handle* h);                                          /* cudaStreamSynchronize */
+int omg_timers(omg_handle* h, int* n, const char** names, double* seconds);  /* mg_timers_show */
+int64_t omg_stat(omg_handle* h, const char* key);                     /* "launches", "bytes_h2d", ... */
+int omg_set_option(omg_handle* h, const char* key, int value);        /* "use_graph", "fast_kernels", ... */
+/* CUDA-event timing of the last omg_fas_vcycles call (ms), and of one kernel class inside it */
+double omg_last_ms(omg_handle* h, const char* what);
+void* omg_stream(omg_handle* h);                                       /* cudaStream_t used by the handle */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OMG_GPU_H */

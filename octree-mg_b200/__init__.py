@@ -1,0 +1,401 @@
+"""octree-mg_b200: B200-native (sm_100a) implementation of octree-mg's multigrid-cycle hot path.
+
+Python is harness plumbing only: this module loads the native libraries and exposes the C++ host
+mirror of the reference's Fortran API (`Mg`, same routine names as src/m_octree_mg.f90) for the
+tests and the benchmark.  The product is libomg_b200.so (CUDA kernels behind include/omg_gpu.h);
+nothing here computes on the CPU and nothing here imports the oracle.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+# constants of src/m_data_structures.f90:8-87
+mg_laplacian, mg_vlaplacian, mg_helmholtz, mg_vhelmholtz, mg_ahelmholtz = 1, 2, 3, 4, 5
+mg_smoother_gs, mg_smoother_gsrb = 1, 2
+mg_iphi, mg_irhs, mg_iold, mg_ires, mg_iveps = 1, 2, 3, 4, 5
+mg_num_vars = 4
+mg_bc_dirichlet, mg_bc_neumann, mg_bc_continuous = -10, -11, -12
+mg_num_neighbors = 6
+
+BC_CALLBACK = C.CFUNCTYPE(None, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int,
+                          C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_void_p)
+
+_libs = None
+
+
+class MgError(RuntimeError):
+    pass
+
+
+class omg_tree_desc(C.Structure):
+    _fields_ = [("n_boxes", C.c_int32), ("box_size", C.c_int32), ("lowest_lvl", C.c_int32), ("highest_lvl", C.c_int32),
+                ("first_normal_lvl", C.c_int32), ("my_rank", C.c_int32), ("n_cpu", C.c_int32),
+                ("n_extra_vars", C.c_int32), ("periodic", C.c_int32 * 3),
+                ("box_size_lvl", C.POINTER(C.c_int32)), ("dr", C.POINTER(C.c_double)),
+                ("box_rank", C.POINTER(C.c_int32)), ("box_lvl", C.POINTER(C.c_int32)), ("box_ix", C.POINTER(C.c_int32)),
+                ("box_parent", C.POINTER(C.c_int32)), ("box_children", C.POINTER(C.c_int32)),
+                ("box_neighbors", C.POINTER(C.c_int32)), ("lvl_ptr", C.POINTER(C.c_int32)),
+                ("lvl_ids", C.POINTER(C.c_int32))]
+
+
+class omg_params(C.Structure):
+    _fields_ = [("operator_type", C.c_int32), ("smoother_type", C.c_int32), ("geometry_type", C.c_int32),
+                ("n_cycle_down", C.c_int32), ("n_cycle_up", C.c_int32), ("max_coarse_cycles", C.c_int32),
+                ("subtract_mean", C.c_int32), ("residual_coarse_abs", C.c_double), ("residual_coarse_rel", C.c_double),
+                ("lambda_", C.c_double)]
+
+
+def build(force=False):
+    """Compile libomg_b200.so / libomg_host.so in-tree (nvcc, sm_100a)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_omg_build", os.path.join(HERE, "build.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.build(force=force)
+
+
+def libs():
+    """(libomg_b200, libomg_host) ctypes handles.  Fails loudly if the native code is not built."""
+    global _libs
+    if _libs is None:
+        p_cuda = os.path.join(HERE, "libomg_b200.so")
+        p_host = os.path.join(HERE, "libomg_host.so")
+        if not (os.path.exists(p_cuda) and os.path.exists(p_host)):
+            raise MgError("native libraries missing: run `python octree-mg_b200/build.py` (there is no CPU fallback)")
+        G = C.CDLL(p_cuda, mode=C.RTLD_GLOBAL)
+        Hh = C.CDLL(p_host)
+        _declare(G, Hh)
+        _libs = (G, Hh)
+    return _libs
+
+
+def _declare(G, H):
+    vp, ci, cd = C.c_void_p, C.c_int, C.c_double
+    G.omg_create.argtypes = [ci, C.POINTER(vp)]
+    G.omg_destroy.argtypes = [vp]
+    G.omg_last_error.restype = C.c_char_p
+    G.omg_last_error.argtypes = [vp]
+    G.omg_version.restype = C.c_char_p
+    G.omg_set_tree.argtypes = [vp, C.POINTER(omg_tree_desc)]
+    G.omg_set_params.argtypes = [vp, C.POINTER(omg_params)]
+    G.omg_set_bc_const.argtypes = [vp, ci, ci, ci, cd]
+    G.omg_set_bc_plane.argtypes = [vp, ci, ci, ci, C.POINTER(cd)]
+    G.omg_push_var.argtypes = [vp, ci, ci, C.POINTER(C.c_int32), C.POINTER(C.POINTER(cd))]
+    G.omg_pull_var.argtypes = [vp, ci, ci, C.POINTER(C.c_int32), C.POINTER(C.POINTER(cd)), ci]
+    G.omg_push_var_packed.argtypes = [vp, ci, ci, ci, vp, C.c_int64]
+    G.omg_pull_var_packed.argtypes = [vp, ci, ci, ci, vp, C.c_int64, ci]
+    G.omg_packed_size.restype = C.c_int64
+    G.omg_packed_size.argtypes = [vp, ci, ci]
+    G.omg_set_var_const.argtypes = [vp, ci, ci, ci, cd, ci]
+    G.omg_fas_vcycle.argtypes = [vp, ci, ci, ci, ci, C.POINTER(cd)]
+    G.omg_fas_fmg.argtypes = [vp, ci, ci, C.POINTER(cd)]
+    G.omg_fas_vcycles.argtypes = [vp, ci, C.POINTER(cd)]
+    G.omg_fill_ghost_cells_lvl.argtypes = [vp, ci, ci]
+    G.omg_restrict_lvl.argtypes = [vp, ci, ci]
+    G.omg_prolong.argtypes = [vp, ci, ci, ci, ci]
+    G.omg_apply_op.argtypes = [vp, ci]
+    G.omg_nccl_unique_id.argtypes = [C.c_char_p]
+    G.omg_comm_init.argtypes = [vp, C.c_char_p, ci, ci]
+    G.omg_comm_init_local.argtypes = [C.POINTER(vp), ci]
+    G.omg_sync.argtypes = [vp]
+    G.omg_stat.restype = C.c_int64
+    G.omg_stat.argtypes = [vp, C.c_char_p]
+    G.omg_set_option.argtypes = [vp, C.c_char_p, ci]
+    G.omg_last_ms.restype = cd
+    G.omg_last_ms.argtypes = [vp, C.c_char_p]
+    G.omg_stream.restype = vp
+    G.omg_stream.argtypes = [vp]
+    G.omg_timers.argtypes = [vp, C.POINTER(ci), C.POINTER(C.c_char_p), C.POINTER(cd)]
+
+    H.omgh_create.restype = vp
+    H.omgh_create.argtypes = [ci]
+    H.omgh_destroy.argtypes = [vp]
+    H.omgh_last_error.restype = C.c_char_p
+    H.omgh_last_error.argtypes = [vp]
+    H.omgh_gpu_handle.restype = vp
+    H.omgh_gpu_handle.argtypes = [vp]
+    H.omgh_set_int.argtypes = [vp, C.c_char_p, ci]
+    H.omgh_get_int.argtypes = [vp, C.c_char_p]
+    H.omgh_set_real.argtypes = [vp, C.c_char_p, cd]
+    H.omgh_number_of_unknowns.restype = C.c_longlong
+    H.omgh_number_of_unknowns.argtypes = [vp]
+    H.omgh_box_size_lvl.argtypes = [vp, ci]
+    H.omgh_dr_lvl.argtypes = [vp, ci, C.POINTER(cd)]
+    H.omgh_set_bc.argtypes = [vp, ci, ci, ci, cd]
+    H.omgh_set_bc_callback.argtypes = [vp, ci, ci, BC_CALLBACK, vp]
+    H.omgh_comm_init.argtypes = [vp, ci, ci]
+    H.omgh_build_rectangle.argtypes = [vp, C.POINTER(ci), ci, C.POINTER(cd), C.POINTER(cd), C.POINTER(ci), ci]
+    for n in ("omgh_set_methods", "omgh_allocate_storage", "omgh_deallocate_storage", "omgh_phi_bc_store",
+              "omgh_gpu_push_bc"):
+        getattr(H, n).argtypes = [vp]
+    for n in ("omgh_add_children", "omgh_set_leaves_parents", "omgh_set_next_level_ids", "omgh_set_neighbors_lvl",
+              "omgh_set_refinement_boundaries", "omgh_load_balance", "omgh_apply_op", "omgh_fill_ghost_cells",
+              "omgh_restrict", "omgh_gpu_push"):
+        getattr(H, n).argtypes = [vp, ci]
+    for n in ("omgh_fill_ghost_cells_lvl", "omgh_restrict_lvl", "omgh_set_box_rank", "omgh_gpu_pull"):
+        getattr(H, n).argtypes = [vp, ci, ci]
+    H.omgh_prolong.argtypes = [vp, ci, ci, ci, ci]
+    H.omgh_lvl_list.argtypes = [vp, ci, ci, C.POINTER(ci)]
+    H.omgh_tree_export.argtypes = [vp, C.POINTER(ci)]
+    H.omgh_box_rmin.argtypes = [vp, ci, C.POINTER(cd)]
+    H.omgh_box_cc.restype = C.POINTER(cd)
+    H.omgh_box_cc.argtypes = [vp, ci]
+    H.omgh_fas_vcycle.argtypes = [vp, ci, ci, ci, C.POINTER(cd), ci]
+    H.omgh_fas_fmg.argtypes = [vp, ci, ci, C.POINTER(cd)]
+
+
+def _arr(vals, ctype):
+    return (ctype * len(vals))(*vals)
+
+
+class Mg:
+    """mg_t of the reference, backed by the C++ host mirror and the GPU library.
+
+    gpu_resident=False (default) is the strict drop-in mode: every mg_fas_* call pushes phi/rhs and
+    pulls phi/rhs/old/res, so `cc()` views behave like mg%boxes(id)%cc in the reference.  With
+    gpu_resident=True the caller brackets its own cc accesses with mg_gpu_push / mg_gpu_pull.
+    """
+
+    def __init__(self, operator_type=mg_laplacian, smoother_type=mg_smoother_gsrb, n_extra_vars=0, n_cpu=1, my_rank=0,
+                 device=0, gpu_resident=False):
+        self.G, self.H = libs()
+        self.h = C.c_void_p(self.H.omgh_create(device))
+        self._keep = []
+        self._tree = None
+        self.set_int("operator_type", operator_type)
+        self.set_int("smoother_type", smoother_type)
+        self.set_int("n_extra_vars", n_extra_vars)
+        self.set_int("gpu_resident", int(gpu_resident))
+        self.H.omgh_comm_init(self.h, my_rank, n_cpu)
+
+    def __del__(self):
+        try:
+            self.H.omgh_destroy(self.h)
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise MgError(self.H.omgh_last_error(self.h).decode())
+
+    @property
+    def gpu(self):
+        """omg_handle* of the C ABI (None before mg_allocate_storage)."""
+        p = self.H.omgh_gpu_handle(self.h)
+        return C.c_void_p(p) if p else None
+
+    # -- parameters -----------------------------------------------------------------------------
+    def set_int(self, key, v):
+        self._ck(self.H.omgh_set_int(self.h, key.encode(), int(v)))
+
+    def get_int(self, key):
+        return self.H.omgh_get_int(self.h, key.encode())
+
+    def set_real(self, key, v):
+        self._ck(self.H.omgh_set_real(self.h, key.encode(), float(v)))
+
+    def set_lambda(self, lam):
+        self.set_real("lambda", lam)
+
+    def set_bc(self, nb, iv, bc_type, bc_value=0.0):
+        self._ck(self.H.omgh_set_bc(self.h, nb, iv, bc_type, bc_value))
+
+    def set_bc_callback(self, nb, iv, fn):
+        """fn(r_min[3], dr[3], lvl, nc, iv, nb) -> (bc_type, bc[nc, nc] indexed [t2, t1])."""
+        def tramp(r_min, dr, lvl, nc, iv_, nb_, bc_type, bc, user):
+            t, plane = fn(np.array(r_min[0:3]), np.array(dr[0:3]), lvl, nc, iv_, nb_)
+            bc_type[0] = t
+            np.ctypeslib.as_array(bc, shape=(nc, nc))[...] = plane
+        cb = BC_CALLBACK(tramp)
+        self._keep.append(cb)
+        self._ck(self.H.omgh_set_bc_callback(self.h, nb, iv, cb, None))
+
+    # -- tree / setup -----------------------------------------------------------------------------
+    def mg_set_methods(self):
+        self._ck(self.H.omgh_set_methods(self.h))
+
+    def mg_build_rectangle(self, domain_size, box_size, dx, r_min, periodic, n_finer=0):
+        self._ck(self.H.omgh_build_rectangle(self.h, _arr(list(domain_size), C.c_int), box_size,
+                                             _arr(list(dx), C.c_double), _arr(list(r_min), C.c_double),
+                                             _arr([int(bool(p)) for p in periodic], C.c_int), n_finer))
+        self._tree = None
+
+    def mg_add_children(self, id_):
+        self._ck(self.H.omgh_add_children(self.h, id_))
+        self._tree = None
+
+    def mg_set_leaves_parents(self, lvl):
+        self._ck(self.H.omgh_set_leaves_parents(self.h, lvl))
+
+    def mg_set_next_level_ids(self, lvl):
+        self._ck(self.H.omgh_set_next_level_ids(self.h, lvl))
+
+    def mg_set_neighbors_lvl(self, lvl):
+        self._ck(self.H.omgh_set_neighbors_lvl(self.h, lvl))
+        self._tree = None
+
+    def mg_set_refinement_boundaries(self, lvl):
+        self._ck(self.H.omgh_set_refinement_boundaries(self.h, lvl))
+
+    def mg_load_balance_simple(self):
+        self._ck(self.H.omgh_load_balance(self.h, 0))
+        self._tree = None
+
+    def mg_load_balance(self):
+        self._ck(self.H.omgh_load_balance(self.h, 1))
+        self._tree = None
+
+    def mg_load_balance_parents(self):
+        self._ck(self.H.omgh_load_balance(self.h, 2))
+        self._tree = None
+
+    def mg_allocate_storage(self):
+        self._ck(self.H.omgh_allocate_storage(self.h))
+
+    def mg_deallocate_storage(self):
+        self._ck(self.H.omgh_deallocate_storage(self.h))
+
+    # -- introspection ------------------------------------------------------------------------------
+    lowest_lvl = property(lambda self: self.get_int("lowest_lvl"))
+    first_normal_lvl = property(lambda self: self.get_int("first_normal_lvl"))
+    n_boxes = property(lambda self: self.get_int("n_boxes"))
+    box_size = property(lambda self: self.get_int("box_size"))
+    n_extra_vars = property(lambda self: self.get_int("n_extra_vars"))
+
+    @property
+    def highest_lvl(self):
+        return self.get_int("highest_lvl")
+
+    @highest_lvl.setter
+    def highest_lvl(self, v):
+        self.set_int("highest_lvl", v)
+
+    def mg_number_of_unknowns(self):
+        return int(self.H.omgh_number_of_unknowns(self.h))
+
+    def box_size_lvl(self, lvl):
+        return self.H.omgh_box_size_lvl(self.h, lvl)
+
+    def dr(self, lvl):
+        out = (C.c_double * 3)()
+        self.H.omgh_dr_lvl(self.h, lvl, out)
+        return np.array(out[:])
+
+    def _lst(self, lvl, which):
+        n = self.H.omgh_lvl_list(self.h, lvl, which, None)
+        out = (C.c_int * max(n, 1))()
+        self.H.omgh_lvl_list(self.h, lvl, which, out)
+        return list(out[:n])
+
+    def ids(self, lvl):
+        return self._lst(lvl, 0)
+
+    def leaves(self, lvl):
+        return self._lst(lvl, 1)
+
+    def parents(self, lvl):
+        return self._lst(lvl, 2)
+
+    def ref_bnds(self, lvl):
+        return self._lst(lvl, 3)
+
+    def my_ids(self, lvl):
+        return self._lst(lvl, 4)
+
+    def my_leaves(self, lvl):
+        return self._lst(lvl, 5)
+
+    def tree_export(self):
+        """(n_boxes, 20) int32: rank, lvl, ix(3), parent, children(8), neighbors(6) for ids 1..n_boxes."""
+        out = np.zeros((self.n_boxes, 20), dtype=np.int32)
+        self.H.omgh_tree_export(self.h, out.ctypes.data_as(C.POINTER(C.c_int)))
+        return out
+
+    def box_info(self, id_):
+        if self._tree is None:
+            self._tree = self.tree_export()
+        o = [int(x) for x in self._tree[id_ - 1]]
+        rmin = (C.c_double * 3)()
+        self.H.omgh_box_rmin(self.h, id_, rmin)
+        return dict(rank=o[0], lvl=o[1], ix=o[2:5], parent=o[5], children=o[6:14], neighbors=o[14:20],
+                    r_min=np.array(rmin[:]))
+
+    def set_box_rank(self, id_, rank):
+        self.H.omgh_set_box_rank(self.h, id_, rank)
+        self._tree = None
+
+    def cc(self, id_, nc=None):
+        """numpy view [v, k, j, i] of the host copy boxes(id)%cc (ghost cells included)."""
+        if nc is None:
+            nc = self.box_size_lvl(self.box_info(id_)["lvl"])
+        nv = mg_num_vars + self.n_extra_vars
+        p = self.H.omgh_box_cc(self.h, id_)
+        if not p:
+            raise MgError("box %d is not owned by this rank" % id_)
+        return np.ctypeslib.as_array(p, shape=(nv, nc + 2, nc + 2, nc + 2))
+
+    # -- hot path (device) ----------------------------------------------------------------------------
+    def mg_fill_ghost_cells_lvl(self, lvl, iv):
+        self._ck(self.H.omgh_fill_ghost_cells_lvl(self.h, lvl, iv))
+
+    def mg_fill_ghost_cells(self, iv):
+        self._ck(self.H.omgh_fill_ghost_cells(self.h, iv))
+
+    def mg_restrict_lvl(self, iv, lvl):
+        self._ck(self.H.omgh_restrict_lvl(self.h, iv, lvl))
+
+    def mg_restrict(self, iv):
+        self._ck(self.H.omgh_restrict(self.h, iv))
+
+    def mg_prolong(self, lvl, iv, iv_to, add):
+        self._ck(self.H.omgh_prolong(self.h, lvl, iv, iv_to, int(bool(add))))
+
+    def mg_apply_op(self, i_out):
+        self._ck(self.H.omgh_apply_op(self.h, i_out))
+
+    def mg_phi_bc_store(self):
+        self._ck(self.H.omgh_phi_bc_store(self.h))
+
+    def mg_fas_vcycle(self, highest_lvl=None, want_res=True, standalone=True):
+        r = C.c_double(0.0)
+        has = highest_lvl is not None
+        self._ck(self.H.omgh_fas_vcycle(self.h, int(has), highest_lvl if has else 0, int(want_res), C.byref(r),
+                                        int(standalone)))
+        return r.value if want_res else None
+
+    def mg_fas_fmg(self, have_guess, want_res=True):
+        r = C.c_double(0.0)
+        self._ck(self.H.omgh_fas_fmg(self.h, int(bool(have_guess)), int(want_res), C.byref(r)))
+        return r.value if want_res else None
+
+    def mg_gpu_push(self, iv):
+        self._ck(self.H.omgh_gpu_push(self.h, iv))
+
+    def mg_gpu_pull(self, iv, with_ghosts=True):
+        self._ck(self.H.omgh_gpu_pull(self.h, iv, int(with_ghosts)))
+
+    def mg_gpu_push_bc(self):
+        self._ck(self.H.omgh_gpu_push_bc(self.h))
+
+    # -- C ABI conveniences ------------------------------------------------------------------------------
+    def _gck(self, rc):
+        if rc != 0:
+            raise MgError(self.G.omg_last_error(self.gpu).decode())
+
+    def stat(self, key):
+        return int(self.G.omg_stat(self.gpu, key.encode()))
+
+    def set_option(self, key, value):
+        self._gck(self.G.omg_set_option(self.gpu, key.encode(), int(value)))
+
+    def fas_vcycles(self, n, want_res=True):
+        """n back-to-back device-resident V-cycles (omg_fas_vcycles); returns (residuals, elapsed_ms)."""
+        res = (C.c_double * max(n, 1))()
+        self._gck(self.G.omg_fas_vcycles(self.gpu, n, res if want_res else None))
+        return (list(res[:n]) if want_res else None), float(self.G.omg_last_ms(self.gpu, b"cycles"))
+
+    def sync(self):
+        self._gck(self.G.omg_sync(self.gpu))

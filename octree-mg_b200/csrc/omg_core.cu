@@ -1,0 +1,993 @@
+// omg_core.cu -- handle, tree ingestion, cycle programs and the C ABI (include/omg_gpu.h).
+//
+// The cycle (mg_fas_vcycle / mg_fas_fmg, src/m_multigrid.f90:84-243) is compiled once per call
+// signature into a "program": a flat list of level operations.  Operations
+// on the small coarse levels are grouped into op lists run by the single-CTA tail interpreter
+// (one launch for the whole coarse end of the V, including the data-dependent coarse solve);
+// operations on big levels become one batched kernel launch over all boxes of the level.  A
+// program is replayed through a CUDA graph.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/omg_gpu.h"
+#include "omg_comm.h"
+#include "omg_fast.h"
+#include "omg_kernels.h"
+
+namespace {
+
+constexpr int IPHI = 0, IRHS = 1, IOLD = 2, IRES = 3;
+
+struct OmgError { std::string msg; };
+[[noreturn]] void fail(const std::string& m) { throw OmgError{m}; }
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) fail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+template <class T> struct DevBuf {
+  T* p = nullptr; size_t n = 0;
+  void alloc(size_t count) { free(); n = count; if (count) CK(cudaMalloc(&p, count * sizeof(T))); }
+  void upload(const std::vector<T>& h, cudaStream_t s) {
+    if (h.size() != n || (!p && n)) alloc(h.size());
+    if (n) CK(cudaMemcpyAsync(p, h.data(), n * sizeof(T), cudaMemcpyHostToDevice, s));
+  }
+  void free() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+enum StepKind : int {
+  S_SMOOTH, S_RESID, S_RESTRICT, S_CRHS, S_OLDPL, S_CORR_PROLONG, S_RB_FILL, S_COPY_OLD, S_COARSE_SOLVE,
+  S_TAIL, S_ZERO_PHI, S_SUBMEAN, S_CLEAR_SLOT, S_COPY_SLOT, S_HALO, S_XRESTRICT, S_XPROLONG, S_ALLREDUCE_MAX,
+  S_RESID_RESTRICT
+};
+struct Step { int kind, l, a, b, c; };
+
+struct LevelHost {
+  int lvl = 0, nc = 0, nb = 0;
+  bool tail = false;
+  std::vector<int> ids;                 // owned boxes (global ids) in lvls(lvl)%my_ids order
+  std::vector<int> h_fkind, h_farg, h_ftype, h_fkind_old, h_farg_old, h_parent, h_coff, h_parents, h_leaves,
+      h_rb, h_oldpl;
+  std::vector<double> h_bcpl;
+  int n_gpl = 0, n_gpl_old = 0, n_bcpl = 0;
+  bool meta_dirty = true;
+  DevBuf<int> d_fkind, d_farg, d_ftype, d_fkind_old, d_farg_old, d_parent, d_coff, d_parents, d_leaves, d_rb, d_oldpl;
+  DevBuf<double> d_gpl, d_gpl_old, d_bcpl;
+  DevBuf<double> d_var[OMG_MAXV], d_faces[OMG_MAXV];
+  LevelDev dev;
+  bool all_fast = false;                // every face of every box is FK_SAME or FK_PHYS (fast kernels apply)
+};
+
+struct Program { std::vector<Step> steps; std::vector<TailOp> ops; DevBuf<TailOp> d_ops; cudaGraphExec_t graph = nullptr; int64_t launches_per_run = 0; };
+
+}  // namespace
+
+struct omg_handle {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  // tree
+  bool have_tree = false;
+  int n_boxes = 0, box_size = 0, lowest = 0, highest = 0, first_normal = 0, my_rank = 0, n_cpu = 1, n_extra = 0;
+  int periodic[3] = {0, 0, 0};
+  int nvar = 4;
+  std::vector<int> rank, blvl, ix, parent, children, neighbors, loc;
+  std::vector<std::vector<int>> lvl_ids;
+  std::vector<LevelHost> levels;
+  DevBuf<LevelDev> d_levels;
+  // parameters
+  omg_params params{};
+  bool have_params = false, params_dirty = true;
+  int bc_type[OMG_MAXV][6];
+  double bc_value[OMG_MAXV][6];
+  ParamsDev pdev{};
+  DevBuf<double> d_scal;
+  DevBuf<double> d_partial;
+  // programs
+  std::map<std::string, Program> programs;
+  bool gz[OMG_NLVL];
+  // options
+  int use_graph = 1, fast_kernels = 1, tail_cells = 32768;
+  // staging
+  double* h_stage[2] = {nullptr, nullptr};
+  double* d_stage[2] = {nullptr, nullptr};
+  int* d_boxidx[2] = {nullptr, nullptr};
+  int* h_boxidx[2] = {nullptr, nullptr};
+  size_t stage_doubles = 0; int stage_boxes = 0;
+  cudaEvent_t stage_ev[2] = {nullptr, nullptr};
+  // stats / timers
+  int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double last_ms = 0.0;
+  omg_comm* comm = nullptr;
+  // per-step CUDA-event profile of the finest level (option "profile"): kind -> (events, count)
+  int profile = 0;
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_events;
+  std::map<int, std::pair<double, int64_t>> prof_acc;   // step kind -> (ms, launches)
+
+  LevelHost& L(int lvl) { return levels[lvl - lowest]; }
+};
+
+namespace {
+
+void invalidate_programs(omg_handle* h) {
+  for (auto& kv : h->programs) { if (kv.second.graph) cudaGraphExecDestroy(kv.second.graph); kv.second.d_ops.free(); }
+  h->programs.clear();
+}
+
+void free_levels(omg_handle* h) {
+  for (LevelHost& L : h->levels) {
+    L.d_fkind.free(); L.d_farg.free(); L.d_ftype.free(); L.d_fkind_old.free(); L.d_farg_old.free();
+    L.d_parent.free(); L.d_coff.free(); L.d_parents.free(); L.d_leaves.free(); L.d_rb.free(); L.d_oldpl.free();
+    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free();
+    for (int v = 0; v < OMG_MAXV; ++v) { L.d_var[v].free(); L.d_faces[v].free(); }
+  }
+  h->levels.clear();
+  h->d_levels.free();
+  invalidate_programs(h);
+}
+
+inline bool has_children(const omg_handle* h, int id) { return h->children[(size_t)(id - 1) * 8] != 0; }
+
+// ---- tree ingestion ------------------------------------------------------------------------
+void set_tree(omg_handle* h, const omg_tree_desc* t) {
+  CK(cudaSetDevice(h->device));
+  free_levels(h);
+  h->n_boxes = t->n_boxes; h->box_size = t->box_size; h->lowest = t->lowest_lvl; h->highest = t->highest_lvl;
+  h->first_normal = t->first_normal_lvl; h->my_rank = t->my_rank; h->n_cpu = t->n_cpu; h->n_extra = t->n_extra_vars;
+  for (int d = 0; d < 3; ++d) h->periodic[d] = t->periodic[d];
+  h->nvar = 4 + h->n_extra;
+  if (h->nvar > OMG_MAXV) fail("omg_set_tree: too many variables");
+  if (h->lowest < OMG_LVL_LO || h->highest > OMG_LVL_HI || h->lowest > h->highest) fail("omg_set_tree: bad level range");
+  const size_t n = (size_t)t->n_boxes;
+  h->rank.assign(t->box_rank, t->box_rank + n);
+  h->blvl.assign(t->box_lvl, t->box_lvl + n);
+  h->ix.assign(t->box_ix, t->box_ix + 3 * n);
+  h->parent.assign(t->box_parent, t->box_parent + n);
+  h->children.assign(t->box_children, t->box_children + 8 * n);
+  h->neighbors.assign(t->box_neighbors, t->box_neighbors + 6 * n);
+  h->loc.assign(n + 1, -1);
+  const int nl = h->highest - h->lowest + 1;
+  h->levels.assign(nl, LevelHost());
+  h->lvl_ids.assign(nl, std::vector<int>());
+  const int me = h->my_rank;
+
+  for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
+    LevelHost& L = h->L(lvl);
+    L.lvl = lvl; L.nc = t->box_size_lvl[lvl - OMG_LVL_LO];
+    if (L.nc < 1 || L.nc > 1023) fail("omg_set_tree: unsupported box size");
+    const int a = t->lvl_ptr[lvl - OMG_LVL_LO], b = t->lvl_ptr[lvl - OMG_LVL_LO + 1];
+    h->lvl_ids[lvl - h->lowest].assign(t->lvl_ids + a, t->lvl_ids + b);
+    for (int q = a; q < b; ++q) {
+      const int id = t->lvl_ids[q];
+      if (id < 1 || id > t->n_boxes) fail("omg_set_tree: box id out of range");
+      if (h->rank[id - 1] == me) { h->loc[id] = (int)L.ids.size(); L.ids.push_back(id); }
+    }
+    L.nb = (int)L.ids.size();
+  }
+
+  // tail group: the coarsest levels, while they are small and live on one rank (the reference keeps
+  // everything below first_normal_lvl on one rank, src/m_load_balance.f90:79-81)
+  {
+    bool still = true; int owner = -1;
+    for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
+      LevelHost& L = h->L(lvl);
+      const std::vector<int>& ids = h->lvl_ids[lvl - h->lowest];
+      bool one_rank = true;
+      for (int id : ids) { if (owner < 0) owner = h->rank[id - 1]; if (h->rank[id - 1] != owner) one_rank = false; }
+      const long cells = (long)ids.size() * L.nc * L.nc * L.nc;
+      if (lvl == h->lowest) {
+        if (!one_rank) fail("Multiple CPUs for coarse grid (not implemented yet)");   // m_multigrid.f90:197-200
+        L.tail = true;
+      } else {
+        still = still && one_rank && cells <= h->tail_cells && lvl < h->highest;
+        L.tail = still;
+      }
+    }
+  }
+
+  for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
+    LevelHost& L = h->L(lvl);
+    const int nb = L.nb, nc = L.nc;
+    L.h_fkind.assign((size_t)nb * 6, FK_NONE); L.h_farg.assign((size_t)nb * 6, -1); L.h_ftype.assign((size_t)nb * 6, 0);
+    L.h_fkind_old.assign((size_t)nb * 6, FK_NONE); L.h_farg_old.assign((size_t)nb * 6, -1);
+    L.h_parent.assign(nb, -1); L.h_coff.assign(nb, 0);
+    L.all_fast = true;
+    for (int b = 0; b < nb; ++b) {
+      const int id = L.ids[b];
+      const bool is_parent = has_children(h, id);
+      (is_parent ? L.h_parents : L.h_leaves).push_back(b);
+      const int p = h->parent[id - 1];
+      if (p > 0 && h->rank[p - 1] == me) L.h_parent[b] = h->loc[p];
+      if (lvl > h->first_normal) {
+        int off[3];
+        for (int d = 0; d < 3; ++d) off[d] = ((h->ix[(size_t)(id - 1) * 3 + d] - 1) & 1) * (h->box_size >> 1);
+        L.h_coff[b] = off[0] | (off[1] << 10) | (off[2] << 20);
+      }
+      for (int f = 0; f < 6; ++f) {
+        const int nbid = h->neighbors[(size_t)(id - 1) * 6 + f];
+        const size_t q = (size_t)b * 6 + f;
+        if (nbid > 0) {
+          if (h->rank[nbid - 1] == me) {
+            L.h_fkind[q] = FK_SAME; L.h_farg[q] = h->loc[nbid];
+            if (!is_parent || has_children(h, nbid)) { L.h_fkind_old[q] = FK_SAME; L.h_farg_old[q] = h->loc[nbid]; }
+            else { L.h_fkind_old[q] = FK_PLANE; L.h_farg_old[q] = L.n_gpl_old;
+                   L.h_oldpl.push_back(b); L.h_oldpl.push_back(f); L.h_oldpl.push_back(L.n_gpl_old++); }
+          } else {
+            L.h_fkind[q] = FK_PLANE; L.h_farg[q] = L.n_gpl++;   // remote face: filled by the halo exchange
+            L.all_fast = false;
+            if (is_parent) { L.h_fkind_old[q] = FK_PLANE; L.h_farg_old[q] = L.n_gpl_old;
+                             L.h_oldpl.push_back(b); L.h_oldpl.push_back(f); L.h_oldpl.push_back(L.n_gpl_old++); }
+          }
+        } else if (nbid == 0) {
+          if (p <= 0) fail("omg_set_tree: refinement boundary on a box without parent");
+          const int cnb = h->neighbors[(size_t)(p - 1) * 6 + f];
+          if (cnb <= 0) fail("omg_set_tree: refinement boundary without coarse neighbour (tree not 2:1 balanced)");
+          const int cb = (h->rank[cnb - 1] == me) ? h->loc[cnb] : -1;
+          L.h_fkind[q] = FK_PLANE; L.h_farg[q] = L.n_gpl;
+          L.h_rb.push_back(b); L.h_rb.push_back(f); L.h_rb.push_back(cb); L.h_rb.push_back(L.n_gpl++);
+          L.all_fast = false;
+        } else {
+          L.h_fkind[q] = FK_PHYS; L.h_farg[q] = -1; L.h_ftype[q] = (nbid == -1) ? 0 : nbid;
+          L.h_fkind_old[q] = FK_PHYS; L.h_farg_old[q] = -1;
+        }
+      }
+    }
+    // storage: mg_allocate_storage zero-fills every variable (src/m_allocate_storage.f90:72-76)
+    const int hx = (nc + 1) / 2;
+    const size_t bs = (size_t)2 * nc * nc * hx;
+    for (int v = 0; v < h->nvar; ++v) {
+      L.d_var[v].alloc((size_t)nb * bs);
+      if (nb) CK(cudaMemsetAsync(L.d_var[v].p, 0, (size_t)nb * bs * sizeof(double), h->stream));
+      if (v >= 4) {
+        L.d_faces[v].alloc((size_t)nb * 6 * nc * nc);
+        if (nb) CK(cudaMemsetAsync(L.d_faces[v].p, 0, (size_t)nb * 6 * nc * nc * sizeof(double), h->stream));
+      }
+    }
+    L.d_gpl.alloc((size_t)L.n_gpl * nc * nc);
+    if (L.n_gpl) CK(cudaMemsetAsync(L.d_gpl.p, 0, L.d_gpl.n * sizeof(double), h->stream));
+    L.d_gpl_old.alloc((size_t)L.n_gpl_old * nc * nc);
+    if (L.n_gpl_old) CK(cudaMemsetAsync(L.d_gpl_old.p, 0, L.d_gpl_old.n * sizeof(double), h->stream));
+    L.meta_dirty = true;
+
+    LevelDev& D = L.dev;
+    std::memset(&D, 0, sizeof(D));
+    D.lvl = lvl; D.nc = nc; D.hx = hx; D.nb = nb; D.cs = nc * nc * hx; D.bs = 2 * D.cs;
+    for (int d = 0; d < 3; ++d) {
+      const double dr = t->dr[(size_t)(lvl - OMG_LVL_LO) * 3 + d];
+      D.dr[d] = dr; D.idr2[d] = 1 / (dr * dr);
+    }
+  }
+  for (int l = 0; l < OMG_NLVL; ++l) h->gz[l] = false;
+  h->have_tree = true;
+  h->params_dirty = true;
+  size_t maxleaves = 1;
+  for (LevelHost& L : h->levels) maxleaves = std::max(maxleaves, L.h_leaves.size());
+  h->d_partial.alloc(maxleaves);
+}
+
+// upload metadata that changed (face tables, bc planes, parameters) and refresh the LevelDev copies
+void sync_meta(omg_handle* h) {
+  if (!h->have_tree) fail("no tree: call omg_set_tree first");
+  if (!h->have_params) fail("no parameters: call omg_set_params first");
+  bool any = h->params_dirty;
+  for (LevelHost& L : h->levels) any = any || L.meta_dirty;
+  if (!any) return;
+  cudaStream_t s = h->stream;
+  for (LevelHost& L : h->levels) {
+    LevelDev& D = L.dev;
+    if (L.meta_dirty) {
+      L.d_fkind.upload(L.h_fkind, s); L.d_farg.upload(L.h_farg, s); L.d_ftype.upload(L.h_ftype, s);
+      L.d_fkind_old.upload(L.h_fkind_old, s); L.d_farg_old.upload(L.h_farg_old, s);
+      L.d_parent.upload(L.h_parent, s); L.d_coff.upload(L.h_coff, s);
+      L.d_parents.upload(L.h_parents, s); L.d_leaves.upload(L.h_leaves, s);
+      L.d_rb.upload(L.h_rb, s); L.d_oldpl.upload(L.h_oldpl, s);
+      L.d_bcpl.upload(L.h_bcpl, s);
+      L.meta_dirty = false;
+    }
+    for (int v = 0; v < OMG_MAXV; ++v) { D.var[v] = L.d_var[v].p; D.faces[v] = L.d_faces[v].p; }
+    D.fkind = L.d_fkind.p; D.farg = L.d_farg.p; D.ftype = L.d_ftype.p;
+    D.fkind_old = L.d_fkind_old.p; D.farg_old = L.d_farg_old.p;
+    D.gpl = L.d_gpl.p; D.gpl_old = L.d_gpl_old.p; D.bcpl = L.d_bcpl.p;
+    D.parent = L.d_parent.p; D.coff = L.d_coff.p;
+    D.parents_list = L.d_parents.p; D.n_parents = (int)L.h_parents.size();
+    D.leaves_list = L.d_leaves.p; D.n_leaves = (int)L.h_leaves.size();
+    D.rb_list = L.d_rb.p; D.n_rb = (int)L.h_rb.size() / 4;
+    D.oldpl_list = L.d_oldpl.p; D.n_oldpl = (int)L.h_oldpl.size() / 3;
+    const double sum = D.idr2[0] + D.idr2[1] + D.idr2[2];
+    D.fac = (h->params.operator_type == OP_HELMH) ? 1.0 / (2 * sum + h->params.lambda) : 0.5 / sum;
+  }
+  std::vector<LevelDev> devs;
+  for (LevelHost& L : h->levels) devs.push_back(L.dev);
+  h->d_levels.upload(devs, s);
+  h->pdev.op = h->params.operator_type; h->pdev.smoother = h->params.smoother_type; h->pdev.lambda = h->params.lambda;
+  for (int f = 0; f < 6; ++f) { h->pdev.bc_type[f] = h->bc_type[IPHI][f]; h->pdev.bc_value[f] = h->bc_value[IPHI][f]; }
+  if (!h->d_scal.p) { h->d_scal.alloc(SCAL_COUNT); CK(cudaMemsetAsync(h->d_scal.p, 0, SCAL_COUNT * sizeof(double), s)); }
+  const double ra[2] = {h->params.residual_coarse_rel, h->params.residual_coarse_abs};
+  CK(cudaMemcpyAsync(h->d_scal.p + SCAL_COARSE_REL, ra, sizeof(ra), cudaMemcpyHostToDevice, s));
+  CK(cudaStreamSynchronize(s));   // host vectors / stack values above must outlive the copies
+  h->params_dirty = false;
+  invalidate_programs(h);
+}
+
+// ---- program builder: the reference's control flow, flattened ---------------------------------
+struct Builder {
+  omg_handle* h; Program& P; std::vector<TailOp> pend;
+  bool multi() const { return h->n_cpu > 1; }
+  int li(int lvl) const { return lvl - h->lowest; }
+  void flush() {
+    if (pend.empty()) return;
+    P.steps.push_back({S_TAIL, 0, (int)P.ops.size(), (int)pend.size(), 0});
+    P.ops.insert(P.ops.end(), pend.begin(), pend.end());
+    pend.clear();
+  }
+  void emit(int lvl, int tail_type, int step_kind, int a = 0, int b = 0) {
+    if (h->L(lvl).tail) pend.push_back({tail_type, li(lvl), a, b});
+    else { flush(); P.steps.push_back({step_kind, lvl, a, b, 0}); }
+  }
+  void step(int kind, int lvl, int a = 0, int b = 0, int c = 0) { flush(); P.steps.push_back({kind, lvl, a, b, c}); }
+
+  // mg_fill_ghost_cells_lvl(lvl, mg_iphi): only ghost values with remote inputs are materialised
+  void gf(int lvl) {
+    if (multi() && lvl >= h->first_normal) step(S_HALO, lvl);
+    if (!h->L(lvl).h_rb.empty()) emit(lvl, TOP_RB_FILL, S_RB_FILL, h->gz[lvl - 1 - OMG_LVL_LO] ? 1 : 0);
+    h->gz[lvl - OMG_LVL_LO] = false;
+  }
+  // smooth_boxes src/m_multigrid.f90:404-424
+  void smooth_boxes(int lvl, int n_cycle) {
+    const int sub = (h->params.smoother_type == 2) ? 2 : 1;
+    for (int n = 1; n <= n_cycle * sub; ++n) { emit(lvl, TOP_SMOOTH, S_SMOOTH, (n - 1) & 1); gf(lvl); }
+  }
+  // update_coarse :347-384
+  void update_coarse(int lvl) {
+    const bool fuse = !h->L(lvl).tail && !multi();
+    if (fuse) step(S_RESID_RESTRICT, lvl);
+    else {
+      emit(lvl, TOP_RESID, S_RESID, -1);
+      emit(lvl, TOP_RESTRICT, S_RESTRICT, IPHI, IRES);
+    }
+    if (multi() && lvl >= h->first_normal) step(S_XRESTRICT, lvl);
+    gf(lvl - 1);
+    emit(lvl - 1, TOP_CRHS, S_CRHS);
+    if (!h->L(lvl - 1).h_oldpl.empty()) emit(lvl - 1, TOP_OLDPL, S_OLDPL);
+  }
+  // correct_children(lvl-1) :387-402, prolonging onto lvl
+  void correct_children_onto(int lvl) {
+    if (multi() && lvl - 1 >= h->first_normal - 1) step(S_XPROLONG, lvl);
+    emit(lvl, TOP_CORR_PROLONG, S_CORR_PROLONG);
+  }
+  void subtract_mean(int iv, int with_ghosts) { step(S_SUBMEAN, 0, iv, with_ghosts); }
+
+  // mg_fas_vcycle :150-243
+  void vcycle(bool has_highest, int highest_lvl, bool standalone, bool want_res, int res_slot) {
+    if (h->params.subtract_mean && !has_highest) subtract_mean(IRHS, 0);
+    const int min_lvl = h->lowest, max_lvl = has_highest ? highest_lvl : h->highest;
+    if (standalone) gf(max_lvl);
+    for (int lvl = max_lvl; lvl >= min_lvl + 1; --lvl) { smooth_boxes(lvl, h->params.n_cycle_down); update_coarse(lvl); }
+    const int sub = (h->params.smoother_type == 2) ? 2 : 1;
+    if (h->L(min_lvl).nb > 0 || !multi())
+      pend.push_back({TOP_COARSE_SOLVE, li(min_lvl), (h->params.n_cycle_up + h->params.n_cycle_down) * sub,
+                      h->params.max_coarse_cycles});
+    for (int lvl = min_lvl + 1; lvl <= max_lvl; ++lvl) {
+      correct_children_onto(lvl); gf(lvl); smooth_boxes(lvl, h->params.n_cycle_up);
+    }
+    if (want_res) {
+      step(S_CLEAR_SLOT, 0, SCAL_MAXRES);
+      for (int lvl = min_lvl; lvl <= max_lvl; ++lvl) emit(lvl, TOP_RESID, S_RESID, SCAL_MAXRES);
+      if (multi()) step(S_ALLREDUCE_MAX, 0, SCAL_MAXRES);
+      if (res_slot != SCAL_MAXRES) step(S_COPY_SLOT, 0, res_slot, SCAL_MAXRES);
+    }
+    if (h->params.subtract_mean) subtract_mean(IPHI, 1);
+  }
+  // mg_fas_fmg :84-147
+  void fmg(bool have_guess, bool want_res) {
+    if (!have_guess) {
+      for (int lvl = h->highest; lvl >= h->lowest; --lvl) { step(S_ZERO_PHI, lvl); h->gz[lvl - OMG_LVL_LO] = true; }
+    }
+    gf(h->highest);
+    for (int lvl = h->highest; lvl >= h->lowest + 1; --lvl) update_coarse(lvl);
+    if (h->params.subtract_mean) subtract_mean(IRHS, 0);
+    for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
+      emit(lvl, TOP_COPY_OLD, S_COPY_OLD);
+      if (!h->L(lvl).h_oldpl.empty()) emit(lvl, TOP_OLDPL, S_OLDPL);
+      if (lvl > h->lowest) { correct_children_onto(lvl); gf(lvl); }
+      vcycle(true, lvl, false, want_res && lvl == h->highest, SCAL_MAXRES);
+    }
+  }
+};
+
+// ---- executor ------------------------------------------------------------------------------------
+void run_submean(omg_handle* h, int iv, int with_ghosts) {
+  // subtract_mean + get_sum, src/m_multigrid.f90:245-294
+  cudaStream_t s = h->stream;
+  double* acc = h->d_scal.p + SCAL_MEAN;
+  omgk::fill(acc, 1, 0.0, s); h->launches++;
+  for (int lvl = std::max(1, h->lowest); lvl <= h->highest; ++lvl) {
+    LevelHost& L = h->L(lvl);
+    if (L.h_leaves.empty()) continue;
+    const double w = L.dev.dr[0] * L.dev.dr[1] * L.dev.dr[2];
+    omgk::box_sums(L.dev, iv, w, h->d_partial.p, s);
+    omgk::final_sum(h->d_partial.p, (int)L.h_leaves.size(), acc, s);
+    h->launches += 2;
+  }
+  if (h->n_cpu > 1) omg_comm_allreduce_sum(h->comm, acc, s);
+  if (1 >= h->lowest && 1 <= h->highest) {
+    LevelHost& L1 = h->L(1);
+    const double nc = (double)(h->box_size * h->box_size * h->box_size);
+    const double volume = nc * (L1.dev.dr[0] * L1.dev.dr[1] * L1.dev.dr[2]) * (double)h->lvl_ids[1 - h->lowest].size();
+    omgk::div_scalar(acc, volume, s); h->launches++;
+  }
+  for (LevelHost& L : h->levels) {
+    omgk::sub_scalar(L.d_var[iv].p, L.d_var[iv].n, acc, s); h->launches++;
+    if (with_ghosts && iv == IPHI && L.d_gpl.n) { omgk::sub_scalar(L.d_gpl.p, L.d_gpl.n, acc, s); h->launches++; }
+  }
+}
+
+void exec_steps(omg_handle* h, Program& P) {
+  cudaStream_t s = h->stream;
+  const ParamsDev& PD = h->pdev;
+  for (const Step& st : P.steps) {
+    const bool prof = h->profile && st.l == h->highest && st.kind != S_TAIL && st.kind != S_SUBMEAN &&
+                      st.kind != S_CLEAR_SLOT && st.kind != S_COPY_SLOT && st.kind != S_ZERO_PHI;
+    cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+    if (prof) { CK(cudaEventCreate(&pe0)); CK(cudaEventCreate(&pe1)); CK(cudaEventRecord(pe0, s)); }
+    switch (st.kind) {
+      case S_SMOOTH: {
+        LevelHost& L = h->L(st.l);
+        if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, s))) omgk::smooth(L.dev, PD, st.a, s);
+        h->launches++;
+      } break;
+      case S_RESID: omgk::resid(h->L(st.l).dev, PD, st.a >= 0 ? h->d_scal.p + st.a : nullptr, s); h->launches++; break;
+      case S_RESTRICT: omgk::restrict2(h->L(st.l).dev, h->L(st.l - 1).dev, st.a, st.b, s); h->launches++; break;
+      case S_RESID_RESTRICT: {
+        LevelHost& L = h->L(st.l);
+        if (!(h->fast_kernels && omgf::resid_restrict(L.dev, h->L(st.l - 1).dev, PD, L.all_fast, s))) {
+          omgk::resid(L.dev, PD, nullptr, s); omgk::restrict2(L.dev, h->L(st.l - 1).dev, IPHI, IRES, s); h->launches++;
+        }
+        h->launches++;
+      } break;
+      case S_CRHS: omgk::crhs(h->L(st.l).dev, PD, s); h->launches++; break;
+      case S_OLDPL: omgk::oldpl(h->L(st.l).dev, PD, s); h->launches++; break;
+      case S_CORR_PROLONG: {
+        LevelHost& L = h->L(st.l);
+        if (!(h->fast_kernels && omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, s)))
+          omgk::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, s);
+        h->launches++;
+      } break;
+      case S_RB_FILL: omgk::rb_fill(h->L(st.l).dev, h->L(st.l - 1).dev, PD, 0, st.a, s); h->launches++; break;
+      case S_COPY_OLD: { LevelHost& L = h->L(st.l); omgk::copy(L.d_var[IOLD].p, L.d_var[IPHI].p, L.d_var[IPHI].n, s); h->launches++; } break;
+      case S_TAIL: omgk::tail(h->d_levels.p, PD, P.d_ops.p + st.a, st.b, h->d_scal.p, s); h->launches++; break;
+      case S_ZERO_PHI: {
+        LevelHost& L = h->L(st.l);
+        if (L.d_var[IPHI].n) CK(cudaMemsetAsync(L.d_var[IPHI].p, 0, L.d_var[IPHI].n * sizeof(double), s));
+        if (L.d_gpl.n) CK(cudaMemsetAsync(L.d_gpl.p, 0, L.d_gpl.n * sizeof(double), s));
+      } break;
+      case S_SUBMEAN: run_submean(h, st.a, st.b); break;
+      case S_CLEAR_SLOT: CK(cudaMemsetAsync(h->d_scal.p + st.a, 0, sizeof(double), s)); break;
+      case S_COPY_SLOT: CK(cudaMemcpyAsync(h->d_scal.p + st.a, h->d_scal.p + st.b, sizeof(double), cudaMemcpyDeviceToDevice, s)); break;
+      case S_HALO: omg_comm_halo(h->comm, st.l, s); break;
+      case S_XRESTRICT: omg_comm_restrict(h->comm, st.l, s); break;
+      case S_XPROLONG: omg_comm_prolong(h->comm, st.l, s); break;
+      case S_ALLREDUCE_MAX: omg_comm_allreduce_max(h->comm, h->d_scal.p + st.a, s); break;
+      default: fail("exec_steps: unknown step");
+    }
+    if (prof) { CK(cudaEventRecord(pe1, s)); h->prof_events.push_back({st.kind, {pe0, pe1}}); }
+  }
+  CK(cudaGetLastError());
+}
+
+void run_program(omg_handle* h, Program& P) {
+  if (P.d_ops.n != P.ops.size() || (!P.d_ops.p && !P.ops.empty())) {
+    P.d_ops.upload(P.ops, h->stream);
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  const bool graph_ok = h->use_graph && !h->profile && (h->n_cpu == 1 || omg_comm_graph_safe(h->comm));
+  if (!graph_ok) { exec_steps(h, P); return; }
+  if (!P.graph) {
+    cudaGraph_t g = nullptr;
+    const int64_t l0 = h->launches;
+    CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    try { exec_steps(h, P); } catch (...) { cudaStreamEndCapture(h->stream, &g); if (g) cudaGraphDestroy(g); throw; }
+    CK(cudaStreamEndCapture(h->stream, &g));
+    CK(cudaGraphInstantiate(&P.graph, g, 0));
+    CK(cudaGraphDestroy(g));
+    P.launches_per_run = h->launches - l0;
+    h->launches = l0;
+  }
+  CK(cudaGraphLaunch(P.graph, h->stream));
+  h->launches += P.launches_per_run;
+  h->graph_launches++;
+}
+
+Program& get_program(omg_handle* h, const std::string& key, bool& fresh) {
+  auto it = h->programs.find(key);
+  fresh = (it == h->programs.end());
+  return h->programs[key];
+}
+
+void check_supported(omg_handle* h) {
+  const omg_params& p = h->params;
+  if (p.operator_type < 1 || p.operator_type > 5) fail("mg_set_methods: unknown operator");
+  if (p.geometry_type != 1) fail("set_methods: unsupported geometry");
+  if (p.smoother_type != 2) {
+    if (p.smoother_type == 1) fail("mg_smoother_gs is not available on the device path; use mg_smoother_gsrb");
+    fail("set_methods: unsupported smoother type");
+  }
+  if ((p.operator_type == OP_VLPL || p.operator_type == OP_VHELMH) && h->n_extra < 1) fail("set_methods: mg%n_extra_vars == 0");
+  if (p.operator_type == OP_AHELMH && h->n_extra < 3) fail("ahelmholtz_set_methods: mg%n_extra_vars < 3");
+}
+
+void fas_vcycle(omg_handle* h, int has_highest, int highest_lvl, int standalone, int want_res, double* max_res) {
+  CK(cudaSetDevice(h->device));
+  sync_meta(h);
+  check_supported(h);
+  if (has_highest && (highest_lvl < h->lowest || highest_lvl > h->highest)) fail("mg_fas_vcycle: highest_lvl out of range");
+  char key[64];
+  std::snprintf(key, sizeof key, "v:%d:%d:%d:%d", has_highest, has_highest ? highest_lvl : 0, standalone, want_res);
+  bool fresh;
+  Program& P = get_program(h, key, fresh);
+  if (fresh) {
+    for (int l = 0; l < OMG_NLVL; ++l) h->gz[l] = false;
+    Builder B{h, P, {}};
+    B.vcycle(has_highest != 0, highest_lvl, standalone != 0, want_res != 0, SCAL_MAXRES);
+    B.flush();
+  }
+  run_program(h, P);
+  if (want_res && max_res) {
+    CK(cudaMemcpyAsync(max_res, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+}
+
+void fas_fmg(omg_handle* h, int have_guess, int want_res, double* max_res) {
+  CK(cudaSetDevice(h->device));
+  sync_meta(h);
+  check_supported(h);
+  char key[64];
+  std::snprintf(key, sizeof key, "f:%d:%d", have_guess, want_res);
+  bool fresh;
+  Program& P = get_program(h, key, fresh);
+  if (fresh) {
+    for (int l = 0; l < OMG_NLVL; ++l) h->gz[l] = false;
+    Builder B{h, P, {}};
+    B.fmg(have_guess != 0, want_res != 0);
+    B.flush();
+  }
+  run_program(h, P);
+  if (want_res && max_res) {
+    CK(cudaMemcpyAsync(max_res, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+}
+
+// ---- staging for push / pull -----------------------------------------------------------------------
+void ensure_stage(omg_handle* h, size_t slab) {
+  const size_t want_boxes = std::max<size_t>(1, std::min<size_t>(4096, ((size_t)48 << 20) / (slab * sizeof(double))));
+  const size_t need = want_boxes * slab;
+  if (h->stage_doubles < need) {
+    for (int q = 0; q < 2; ++q) {
+      if (h->h_stage[q]) cudaFreeHost(h->h_stage[q]);
+      if (h->d_stage[q]) cudaFree(h->d_stage[q]);
+      CK(cudaMallocHost(&h->h_stage[q], need * sizeof(double)));
+      CK(cudaMalloc(&h->d_stage[q], need * sizeof(double)));
+      if (!h->d_boxidx[q]) CK(cudaMalloc(&h->d_boxidx[q], 4096 * sizeof(int)));
+      if (!h->h_boxidx[q]) CK(cudaMallocHost(&h->h_boxidx[q], 4096 * sizeof(int)));
+      if (!h->stage_ev[q]) CK(cudaEventCreateWithFlags(&h->stage_ev[q], cudaEventDisableTiming));
+    }
+    h->stage_doubles = need;
+  }
+  h->stage_boxes = (int)std::min<size_t>(4096, h->stage_doubles / slab);
+}
+
+void collect_profile(omg_handle* h) {
+  if (h->prof_events.empty()) return;
+  CK(cudaStreamSynchronize(h->stream));
+  for (auto& e : h->prof_events) {
+    float ms = 0; CK(cudaEventElapsedTime(&ms, e.second.first, e.second.second));
+    auto& acc = h->prof_acc[e.first]; acc.first += ms; acc.second += 1;
+    cudaEventDestroy(e.second.first); cudaEventDestroy(e.second.second);
+  }
+  h->prof_events.clear();
+}
+
+int ghost_mode_for(int v) { return v == IPHI ? (int)GM_PHI : v == IOLD ? (int)GM_OLD : v >= 4 ? (int)GM_STORED : -1; }
+
+// copy interior (+ six faces) between a slab and a user cc(:,:,:,iv) array
+void scatter_slab(double* dst, const double* src, int nc, bool faces) {
+  const int n2 = nc + 2;
+  for (int k = 1; k <= nc; ++k) for (int j = 1; j <= nc; ++j)
+    std::memcpy(dst + ((size_t)k * n2 + j) * n2 + 1, src + ((size_t)k * n2 + j) * n2 + 1, sizeof(double) * nc);
+  if (!faces) return;
+  for (int k = 1; k <= nc; ++k) for (int j = 1; j <= nc; ++j) {
+    const size_t r = ((size_t)k * n2 + j) * n2;
+    dst[r] = src[r]; dst[r + nc + 1] = src[r + nc + 1];
+  }
+  for (int k = 1; k <= nc; ++k) {
+    std::memcpy(dst + ((size_t)k * n2 + 0) * n2 + 1, src + ((size_t)k * n2 + 0) * n2 + 1, sizeof(double) * nc);
+    std::memcpy(dst + ((size_t)k * n2 + nc + 1) * n2 + 1, src + ((size_t)k * n2 + nc + 1) * n2 + 1, sizeof(double) * nc);
+  }
+  for (int j = 1; j <= nc; ++j) {
+    std::memcpy(dst + ((size_t)0 * n2 + j) * n2 + 1, src + ((size_t)0 * n2 + j) * n2 + 1, sizeof(double) * nc);
+    std::memcpy(dst + ((size_t)(nc + 1) * n2 + j) * n2 + 1, src + ((size_t)(nc + 1) * n2 + j) * n2 + 1, sizeof(double) * nc);
+  }
+}
+
+// transfer a list of (local box, host pointer) pairs of one level; packed: host slabs are contiguous from base
+void push_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxes, const double* const* ptrs, const double* packed) {
+  const size_t slab = (size_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2);
+  ensure_stage(h, slab);
+  const int chunk = h->stage_boxes;
+  int q = 0;
+  for (size_t c0 = 0; c0 < boxes.size(); c0 += chunk, q ^= 1) {
+    const int n = (int)std::min<size_t>(chunk, boxes.size() - c0);
+    CK(cudaEventSynchronize(h->stage_ev[q]));
+    const double* src;
+    if (packed) src = packed + c0 * slab;
+    else {
+      for (int m = 0; m < n; ++m) std::memcpy(h->h_stage[q] + (size_t)m * slab, ptrs[c0 + m], slab * sizeof(double));
+      src = h->h_stage[q];
+    }
+    std::memcpy(h->h_boxidx[q], boxes.data() + c0, n * sizeof(int));
+    CK(cudaMemcpyAsync(h->d_stage[q], src, (size_t)n * slab * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->d_boxidx[q], h->h_boxidx[q], n * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    omgk::unpack(L.dev, v, h->d_boxidx[q], n, h->d_stage[q], v >= 4, h->stream);
+    CK(cudaEventRecord(h->stage_ev[q], h->stream));
+    h->launches++; h->bytes_h2d += (int64_t)n * slab * sizeof(double);
+  }
+  CK(cudaStreamSynchronize(h->stream));
+}
+
+void pull_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxes, double* const* ptrs, double* packed, int with_ghosts) {
+  const size_t slab = (size_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2);
+  ensure_stage(h, slab);
+  const int chunk = h->stage_boxes;
+  const int gm = with_ghosts ? ghost_mode_for(v) : -1;
+  struct Pending { size_t c0; int n, q; };
+  Pending prev{0, 0, -1};
+  auto drain = [&](const Pending& p) {
+    if (p.q < 0) return;
+    CK(cudaEventSynchronize(h->stage_ev[p.q]));
+    if (!packed) for (int m = 0; m < p.n; ++m) scatter_slab(ptrs[p.c0 + m], h->h_stage[p.q] + (size_t)m * slab, L.nc, gm >= 0);
+  };
+  int q = 0;
+  for (size_t c0 = 0; c0 < boxes.size(); c0 += chunk, q ^= 1) {
+    const int n = (int)std::min<size_t>(chunk, boxes.size() - c0);
+    std::memcpy(h->h_boxidx[q], boxes.data() + c0, n * sizeof(int));
+    CK(cudaMemcpyAsync(h->d_boxidx[q], h->h_boxidx[q], n * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    omgk::pack(L.dev, h->pdev, v, h->d_boxidx[q], n, h->d_stage[q], gm, h->stream);
+    double* dst = packed ? packed + c0 * slab : h->h_stage[q];
+    CK(cudaMemcpyAsync(dst, h->d_stage[q], (size_t)n * slab * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaEventRecord(h->stage_ev[q], h->stream));
+    h->launches++; h->bytes_d2h += (int64_t)n * slab * sizeof(double);
+    drain(prev);
+    prev = {c0, n, q};
+  }
+  drain(prev);
+  CK(cudaStreamSynchronize(h->stream));
+}
+
+int check_iv(omg_handle* h, int iv) {
+  if (iv < 1 || iv > h->nvar) fail("variable index out of range");
+  return iv - 1;
+}
+
+void push_pull_ids(omg_handle* h, int iv, int n, const int32_t* ids, const double* const* cptrs, double* const* ptrs, int with_ghosts, bool push) {
+  CK(cudaSetDevice(h->device));
+  sync_meta(h);
+  const int v = check_iv(h, iv);
+  // group by level, preserving order
+  std::map<int, std::pair<std::vector<int>, std::vector<size_t>>> by_lvl;
+  for (int m = 0; m < n; ++m) {
+    const int id = ids[m];
+    if (id < 1 || id > h->n_boxes || h->loc[id] < 0) fail("push/pull: box not owned by this rank");
+    auto& e = by_lvl[h->blvl[id - 1]];
+    e.first.push_back(h->loc[id]); e.second.push_back(m);
+  }
+  for (auto& kv : by_lvl) {
+    LevelHost& L = h->L(kv.first);
+    if (push) {
+      std::vector<const double*> p; for (size_t m : kv.second.second) p.push_back(cptrs[m]);
+      push_level(h, L, v, kv.second.first, p.data(), nullptr);
+    } else {
+      std::vector<double*> p; for (size_t m : kv.second.second) p.push_back(ptrs[m]);
+      pull_level(h, L, v, kv.second.first, p.data(), nullptr, with_ghosts);
+    }
+  }
+}
+
+void push_pull_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const double* cbuf, double* buf, int64_t n_doubles, int with_ghosts, bool push) {
+  CK(cudaSetDevice(h->device));
+  sync_meta(h);
+  const int v = check_iv(h, iv);
+  if (lvl_lo < h->lowest || lvl_hi > h->highest || lvl_lo > lvl_hi) fail("packed transfer: level range out of bounds");
+  int64_t off = 0;
+  for (int lvl = lvl_lo; lvl <= lvl_hi; ++lvl) {
+    LevelHost& L = h->L(lvl);
+    const int64_t slab = (int64_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2);
+    if (off + slab * L.nb > n_doubles) fail("packed transfer: buffer too small");
+    std::vector<int> boxes(L.nb); for (int b = 0; b < L.nb; ++b) boxes[b] = b;
+    if (push) push_level(h, L, v, boxes, nullptr, cbuf + off);
+    else pull_level(h, L, v, boxes, nullptr, buf + off, with_ghosts);
+    off += slab * L.nb;
+  }
+}
+
+}  // namespace
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+#define OMG_TRY(h, ...)                                                    \
+  try { __VA_ARGS__; return 0; }                                           \
+  catch (const OmgError& e) { if (h) (h)->err = e.msg; return 1; }         \
+  catch (const std::exception& e) { if (h) (h)->err = e.what(); return 2; }
+
+extern "C" {
+
+const char* omg_version(void) { return "octree-mg_b200 0.1 (sm_100a)"; }
+
+int omg_create(int device, omg_handle** out) {
+  if (!out) return 1;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0 || device < 0 || device >= ndev) return 3;   // no CPU fallback
+  omg_handle* h = new omg_handle();
+  h->device = device;
+  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return 3; }
+  cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
+  for (int v = 0; v < OMG_MAXV; ++v) for (int f = 0; f < 6; ++f) { h->bc_type[v][f] = -10; h->bc_value[v][f] = 0.0; }
+  *out = h;
+  return 0;
+}
+
+int omg_destroy(omg_handle* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  if (h->comm) omg_comm_destroy(h->comm);
+  try { free_levels(h); } catch (...) {}
+  h->d_scal.free(); h->d_partial.free();
+  for (int q = 0; q < 2; ++q) {
+    if (h->h_stage[q]) cudaFreeHost(h->h_stage[q]);
+    if (h->d_stage[q]) cudaFree(h->d_stage[q]);
+    if (h->d_boxidx[q]) cudaFree(h->d_boxidx[q]);
+    if (h->h_boxidx[q]) cudaFreeHost(h->h_boxidx[q]);
+    if (h->stage_ev[q]) cudaEventDestroy(h->stage_ev[q]);
+  }
+  cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+  cudaStreamDestroy(h->stream);
+  delete h;
+  return 0;
+}
+
+const char* omg_last_error(const omg_handle* h) { return h ? h->err.c_str() : "invalid handle (no CUDA device?)"; }
+
+int omg_set_tree(omg_handle* h, const omg_tree_desc* t) { OMG_TRY(h, set_tree(h, t)); }
+
+int omg_set_params(omg_handle* h, const omg_params* p) {
+  OMG_TRY(h, {
+    if (p->lambda < 0) fail("set_lambda: lambda < 0 not allowed");
+    if (h->have_params && std::memcmp(&h->params, p, sizeof(omg_params)) == 0) return 0;   // unchanged: keep cached programs
+    std::memset(&h->params, 0, sizeof(omg_params));
+    h->params.operator_type = p->operator_type; h->params.smoother_type = p->smoother_type; h->params.geometry_type = p->geometry_type;
+    h->params.n_cycle_down = p->n_cycle_down; h->params.n_cycle_up = p->n_cycle_up; h->params.max_coarse_cycles = p->max_coarse_cycles;
+    h->params.subtract_mean = p->subtract_mean; h->params.residual_coarse_abs = p->residual_coarse_abs;
+    h->params.residual_coarse_rel = p->residual_coarse_rel; h->params.lambda = p->lambda;
+    h->have_params = true; h->params_dirty = true;
+  });
+}
+
+int omg_set_bc_const(omg_handle* h, int iv, int nb, int bc_type, double bc_value) {
+  OMG_TRY(h, {
+    if (iv < 1 || iv > OMG_MAXV || nb < 1 || nb > 6) fail("omg_set_bc_const: index out of range");
+    if (bc_type != -10 && bc_type != -11 && bc_type != -12) fail("bc_to_gc: unknown boundary condition");
+    if (h->bc_type[iv - 1][nb - 1] == bc_type && h->bc_value[iv - 1][nb - 1] == bc_value) return 0;
+    h->bc_type[iv - 1][nb - 1] = bc_type; h->bc_value[iv - 1][nb - 1] = bc_value; h->params_dirty = true;
+  });
+}
+
+int omg_set_bc_plane(omg_handle* h, int box_id, int nb, int bc_type, const double* plane) {
+  OMG_TRY(h, {
+    if (!h->have_tree) fail("no tree");
+    if (box_id < 1 || box_id > h->n_boxes || h->loc[box_id] < 0) fail("omg_set_bc_plane: box not owned by this rank");
+    if (nb < 1 || nb > 6) fail("omg_set_bc_plane: nb out of range");
+    if (bc_type != -10 && bc_type != -11 && bc_type != -12) fail("bc_to_gc: unknown boundary condition");
+    LevelHost& L = h->L(h->blvl[box_id - 1]);
+    const size_t q = (size_t)h->loc[box_id] * 6 + (nb - 1);
+    if (L.h_fkind[q] != FK_PHYS) fail("omg_set_bc_plane: not a physical boundary face");
+    const size_t n2 = (size_t)L.nc * L.nc;
+    if (L.h_farg[q] < 0) { L.h_farg[q] = L.n_bcpl++; L.h_farg_old[q] = L.h_farg[q]; L.h_bcpl.resize((size_t)L.n_bcpl * n2); }
+    std::memcpy(&L.h_bcpl[(size_t)L.h_farg[q] * n2], plane, n2 * sizeof(double));
+    L.h_ftype[q] = bc_type;
+    L.meta_dirty = true;
+  });
+}
+
+int omg_push_var(omg_handle* h, int iv, int n, const int32_t* ids, const double* const* ptrs) {
+  OMG_TRY(h, push_pull_ids(h, iv, n, ids, ptrs, nullptr, 0, true));
+}
+int omg_pull_var(omg_handle* h, int iv, int n, const int32_t* ids, double* const* ptrs, int with_ghosts) {
+  OMG_TRY(h, push_pull_ids(h, iv, n, ids, nullptr, ptrs, with_ghosts, false));
+}
+int omg_push_var_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const double* buf, int64_t n_doubles) {
+  OMG_TRY(h, push_pull_packed(h, iv, lvl_lo, lvl_hi, buf, nullptr, n_doubles, 0, true));
+}
+int omg_pull_var_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, double* buf, int64_t n_doubles, int with_ghosts) {
+  OMG_TRY(h, push_pull_packed(h, iv, lvl_lo, lvl_hi, nullptr, buf, n_doubles, with_ghosts, false));
+}
+int64_t omg_packed_size(omg_handle* h, int lvl_lo, int lvl_hi) {
+  if (!h || !h->have_tree) return -1;
+  int64_t n = 0;
+  for (int lvl = std::max(lvl_lo, h->lowest); lvl <= std::min(lvl_hi, h->highest); ++lvl) {
+    LevelHost& L = h->L(lvl);
+    n += (int64_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2) * L.nb;
+  }
+  return n;
+}
+int omg_set_var_const(omg_handle* h, int iv, int lvl_lo, int lvl_hi, double value, int interior_only) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    sync_meta(h);
+    const int v = check_iv(h, iv);
+    for (int lvl = std::max(lvl_lo, h->lowest); lvl <= std::min(lvl_hi, h->highest); ++lvl) {
+      LevelHost& L = h->L(lvl);
+      omgk::fill(L.d_var[v].p, L.d_var[v].n, value, h->stream);
+      if (!interior_only && L.d_faces[v].n) omgk::fill(L.d_faces[v].p, L.d_faces[v].n, value, h->stream);
+      if (!interior_only && v == IPHI && L.d_gpl.n) omgk::fill(L.d_gpl.p, L.d_gpl.n, value, h->stream);
+    }
+  });
+}
+
+int omg_fas_vcycle(omg_handle* h, int has_highest_lvl, int highest_lvl, int standalone, int want_res, double* max_res) {
+  OMG_TRY(h, fas_vcycle(h, has_highest_lvl, highest_lvl, standalone, want_res, max_res));
+}
+int omg_fas_fmg(omg_handle* h, int have_guess, int want_res, double* max_res) {
+  OMG_TRY(h, fas_fmg(h, have_guess, want_res, max_res));
+}
+
+int omg_fas_vcycles(omg_handle* h, int n, double* residuals) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    if (n < 0 || n > 256) fail("omg_fas_vcycles: n out of range (0..256)");
+    sync_meta(h);
+    check_supported(h);
+    const int want = residuals ? 1 : 0;
+    char key[64];
+    std::snprintf(key, sizeof key, "v:%d:%d:%d:%d", 0, 0, 1, want);
+    bool fresh;
+    Program& P = get_program(h, key, fresh);
+    if (fresh) { Builder B{h, P, {}}; B.vcycle(false, 0, true, want != 0, SCAL_MAXRES); B.flush(); }
+    CK(cudaEventRecord(h->ev0, h->stream));
+    for (int c = 0; c < n; ++c) {
+      run_program(h, P);
+      if (want) CK(cudaMemcpyAsync(h->d_scal.p + SCAL_RESHIST + c, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    }
+    CK(cudaEventRecord(h->ev1, h->stream));
+    if (want && n) CK(cudaMemcpyAsync(residuals, h->d_scal.p + SCAL_RESHIST, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1)); h->last_ms = ms;
+  });
+}
+
+int omg_fill_ghost_cells_lvl(omg_handle* h, int lvl, int iv) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    sync_meta(h);
+    const int v = check_iv(h, iv);
+    if (lvl < h->lowest) fail("fill_ghost_cells_lvl: lvl < lowest_lvl");
+    if (lvl > h->highest) fail("fill_ghost_cells_lvl: lvl > highest_lvl");
+    LevelHost& L = h->L(lvl);
+    if (v == IPHI) {
+      if (h->n_cpu > 1 && lvl >= h->first_normal) omg_comm_halo(h->comm, lvl, h->stream);
+      if (!L.h_rb.empty()) omgk::rb_fill(L.dev, h->L(lvl - 1).dev, h->pdev, 0, 0, h->stream);
+    } else if (v >= 4) {
+      if (h->n_cpu > 1) fail("fill_ghost_cells_lvl: extra variables on several ranks not supported yet");
+      omgk::fill_stored(L.dev, h->pdev, v, h->bc_type[v], h->bc_value[v], h->stream);
+      if (!L.h_rb.empty()) omgk::rb_fill(L.dev, h->L(lvl - 1).dev, h->pdev, v, 0, h->stream);
+    } else fail("fill_ghost_cells_lvl: ghost cells of rhs/old/res are not tracked on the device");
+    h->launches++;
+  });
+}
+
+int omg_restrict_lvl(omg_handle* h, int iv, int lvl) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    sync_meta(h);
+    const int v = check_iv(h, iv);
+    if (lvl <= h->lowest || lvl > h->highest) fail("cannot restrict lvl <= lowest_lvl");
+    if (h->n_cpu > 1) fail("omg_restrict_lvl: several ranks not supported for standalone restriction yet");
+    omgk::restrict2(h->L(lvl).dev, h->L(lvl - 1).dev, v, -1, h->stream);
+    h->launches++;
+  });
+}
+
+int omg_prolong(omg_handle* h, int lvl, int iv, int iv_to, int add) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    sync_meta(h);
+    const int v = check_iv(h, iv); const int vt = check_iv(h, iv_to);
+    if (lvl == h->highest) fail("cannot prolong highest level");
+    if (lvl < h->lowest) fail("cannot prolong below lowest level");
+    if (!(v == IPHI || v >= 4)) fail("omg_prolong: source must be phi or an extra variable (ghost cells of rhs/old/res are not tracked)");
+    if (h->n_cpu > 1) fail("omg_prolong: several ranks not supported for standalone prolongation yet");
+    omgk::prolong_var(h->L(lvl + 1).dev, h->L(lvl).dev, h->pdev, v, vt, add, h->stream);
+    h->launches++;
+  });
+}
+
+int omg_apply_op(omg_handle* h, int i_out) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    sync_meta(h);
+    check_supported(h);
+    const int v = check_iv(h, i_out);
+    for (LevelHost& L : h->levels) { omgk::apply_op(L.dev, h->pdev, v, h->stream); h->launches++; }
+  });
+}
+
+int omg_nccl_unique_id(char out[128]) { return omg_comm_unique_id(out); }
+int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks) {
+  OMG_TRY(h, { (void)uid; (void)rank; (void)nranks; fail("omg_comm_init: not built yet"); });
+}
+int omg_comm_init_local(omg_handle* const* handles, int nranks) { (void)handles; (void)nranks; return 1; }
+
+int omg_sync(omg_handle* h) { OMG_TRY(h, { CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream)); }); }
+
+int omg_timers(omg_handle* h, int* n, const char** names, double* seconds) {
+  (void)h; (void)names; (void)seconds; if (n) *n = 0; return 0;
+}
+
+int64_t omg_stat(omg_handle* h, const char* key) {
+  if (!h) return -1;
+  const std::string k(key);
+  if (k == "launches") return h->launches;
+  if (k == "graph_launches") return h->graph_launches;
+  if (k == "bytes_h2d") return h->bytes_h2d;
+  if (k == "bytes_d2h") return h->bytes_d2h;
+  if (k == "coarse_iters") {
+    double v = 0; cudaSetDevice(h->device); cudaStreamSynchronize(h->stream);
+    if (h->d_scal.p) cudaMemcpy(&v, h->d_scal.p + SCAL_COARSE_ITERS, sizeof(double), cudaMemcpyDeviceToHost);
+    return (int64_t)v;
+  }
+  if (k == "n_tail_levels") { int64_t c = 0; for (LevelHost& L : h->levels) c += L.tail; return c; }
+  if (k == "device_bytes") { int64_t c = 0; for (LevelHost& L : h->levels) for (int v = 0; v < OMG_MAXV; ++v) c += (int64_t)(L.d_var[v].n + L.d_faces[v].n) * 8; return c; }
+  return -1;
+}
+
+int omg_set_option(omg_handle* h, const char* key, int value) {
+  OMG_TRY(h, {
+    const std::string k(key);
+    if (k == "use_graph") h->use_graph = value;
+    else if (k == "fast_kernels") h->fast_kernels = value;
+    else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
+    else if (k == "tail_cells") { if (h->have_tree) fail("tail_cells must be set before omg_set_tree"); h->tail_cells = value; }
+    else fail("unknown option " + k);
+    invalidate_programs(h);
+  });
+}
+
+// "cycles": elapsed ms of the last omg_fas_vcycles call.  With option "profile" set, per finest-level
+// kernel class: "smooth", "resid_restrict", "corr_prolong", "resid" -> average ms per launch, and
+// "n_<class>" -> number of launches measured.
+double omg_last_ms(omg_handle* h, const char* what) {
+  if (!h) return -1.0;
+  const std::string k(what);
+  if (k == "cycles") return h->last_ms;
+  try { collect_profile(h); } catch (...) { return -1.0; }
+  std::string name = k; bool count = false;
+  if (k.rfind("n_", 0) == 0) { name = k.substr(2); count = true; }
+  int kind = -1;
+  if (name == "smooth") kind = S_SMOOTH; else if (name == "resid_restrict") kind = S_RESID_RESTRICT;
+  else if (name == "corr_prolong") kind = S_CORR_PROLONG; else if (name == "resid") kind = S_RESID;
+  else if (name == "restrict") kind = S_RESTRICT;
+  auto it = h->prof_acc.find(kind);
+  if (it == h->prof_acc.end() || it->second.second == 0) return count ? 0.0 : -1.0;
+  return count ? (double)it->second.second : it->second.first / (double)it->second.second;
+}
+void* omg_stream(omg_handle* h) { return h ? (void*)h->stream : nullptr; }
+
+}  // extern "C"

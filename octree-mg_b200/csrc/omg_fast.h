@@ -1,0 +1,12 @@
+// omg_fast.h -- tuned sm_100a kernels for big uniform levels (box size 16 / 32, every ghost face
+// FK_SAME or FK_PHYS).  Each launcher returns false when it does not apply; the caller then uses
+// the general path of omg_kernels.cu.  Results are bitwise identical between the two paths.
+#pragma once
+#include <cuda_runtime.h>
+#include "omg_device.cuh"
+
+namespace omgf {
+bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, cudaStream_t s);
+bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s);
+bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool coarse_all_fast, cudaStream_t s);
+}  // namespace omgf

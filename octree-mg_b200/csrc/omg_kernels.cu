@@ -1,0 +1,333 @@
+// omg_kernels.cu -- general-path kernels (one CTA per box, any box size / face kind), the
+// single-CTA "tail" interpreter that runs the coarse end of the cycle in one launch, and the
+// host<->device layout conversion kernels.  Tuned sm_100a kernels live in omg_fast.cu.
+#include "omg_kernels.h"
+#include "omg_ops.cuh"
+
+#define OMG_SWITCH_OP(op, CALL)                      \
+  switch (op) {                                      \
+    case OP_LPL: { constexpr int OP = OP_LPL; CALL; } break;       \
+    case OP_VLPL: { constexpr int OP = OP_VLPL; CALL; } break;     \
+    case OP_HELMH: { constexpr int OP = OP_HELMH; CALL; } break;   \
+    case OP_VHELMH: { constexpr int OP = OP_VHELMH; CALL; } break; \
+    default: { constexpr int OP = OP_AHELMH; CALL; } break;        \
+  }
+
+namespace {
+constexpr int kThreads = 256;
+
+// ------------------------------------------------------------------ batched kernels ----------
+template <int OP>
+__global__ void __launch_bounds__(kThreads) k_smooth(const __grid_constant__ LevelDev L,
+                                                     const __grid_constant__ ParamsDev P, int colour) {
+  do_smooth<OP>(L, P, blockIdx.x, colour, threadIdx.x, blockDim.x);
+}
+
+template <int OP>
+__global__ void __launch_bounds__(kThreads) k_resid(const __grid_constant__ LevelDev L,
+                                                    const __grid_constant__ ParamsDev P, double* maxslot) {
+  __shared__ double red[32];
+  double m = do_resid<OP>(L, P, blockIdx.x, threadIdx.x, blockDim.x);
+  if (maxslot) {
+    m = block_max(m, red);
+    if (threadIdx.x == 0) atomic_max_nonneg(maxslot, m);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) k_restrict(const __grid_constant__ LevelDev Lf,
+                                                       const __grid_constant__ LevelDev Lc, int iv0, int iv1) {
+  do_restrict(Lf, Lc, iv0, blockIdx.x, threadIdx.x, blockDim.x);
+  if (iv1 >= 0) do_restrict(Lf, Lc, iv1, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+template <int OP>
+__global__ void __launch_bounds__(kThreads) k_crhs(const __grid_constant__ LevelDev L,
+                                                   const __grid_constant__ ParamsDev P) {
+  do_crhs<OP>(L, P, L.parents_list[blockIdx.x], threadIdx.x, blockDim.x);
+}
+
+__global__ void __launch_bounds__(kThreads) k_oldpl(const __grid_constant__ LevelDev L,
+                                                    const __grid_constant__ ParamsDev P) {
+  do_oldpl(L, P, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+__global__ void __launch_bounds__(kThreads) k_corr_prolong(const __grid_constant__ LevelDev Lf,
+                                                           const __grid_constant__ LevelDev Lc,
+                                                           const __grid_constant__ ParamsDev P) {
+  do_corr_prolong(Lf, Lc, P, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+__global__ void __launch_bounds__(kThreads) k_prolong_var(const __grid_constant__ LevelDev Lf,
+                                                          const __grid_constant__ LevelDev Lc,
+                                                          const __grid_constant__ ParamsDev P, int iv, int iv_to,
+                                                          int add) {
+  if (iv == 0) do_prolong_var<GM_PHI>(Lf, Lc, P, iv, iv_to, add, blockIdx.x, threadIdx.x, blockDim.x);
+  else do_prolong_var<GM_STORED>(Lf, Lc, P, iv, iv_to, add, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+__global__ void __launch_bounds__(kThreads) k_rb_fill(const __grid_constant__ LevelDev Lf,
+                                                      const __grid_constant__ LevelDev Lc,
+                                                      const __grid_constant__ ParamsDev P, int iv, int gz) {
+  if (gz) do_rb_fill<GM_PHI_GZ>(Lf, Lc, P, iv, blockIdx.x, threadIdx.x, blockDim.x);
+  else do_rb_fill<GM_PHI>(Lf, Lc, P, iv, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+template <int OP>
+__global__ void __launch_bounds__(kThreads) k_apply_op(const __grid_constant__ LevelDev L,
+                                                       const __grid_constant__ ParamsDev P, int i_out) {
+  do_apply_op<OP>(L, P, i_out, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+struct BcVar { int type[6]; double value[6]; };
+__global__ void __launch_bounds__(kThreads) k_fill_stored(const __grid_constant__ LevelDev L,
+                                                          const __grid_constant__ ParamsDev P, int iv,
+                                                          const __grid_constant__ BcVar bc) {
+  do_fill_stored(L, P, iv, bc.type, bc.value, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
+// elementwise helpers over whole-level arrays
+__global__ void k_fill(double* p, size_t n, double v) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+__global__ void k_copy(double* __restrict__ dst, const double* __restrict__ src, size_t n) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+// x[i] -= *mean  (subtract_mean src/m_multigrid.f90:261-275)
+__global__ void k_sub_scalar(double* p, size_t n, const double* mean) {
+  const double m = *mean;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = p[i] - m;
+}
+__global__ void k_sub_scalar_planes(double* p, size_t n, const double* mean) {
+  const double m = *mean;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = p[i] - m;
+}
+
+// get_sum (src/m_multigrid.f90:278-294): deterministic two-stage sum.  Stage 1: one partial per leaf
+// box (fixed in-block tree order); stage 2: one thread adds the partials in box order.
+__global__ void __launch_bounds__(kThreads) k_box_sums(const __grid_constant__ LevelDev L, int iv, double w, double* partial) {
+  __shared__ double sm[kThreads];
+  const int b = L.leaves_list[blockIdx.x];
+  const double* v = L.var[iv] + (size_t)b * L.bs;
+  double s = 0.0;
+  for (int idx = threadIdx.x; idx < L.bs; idx += blockDim.x) {
+    const int colour = idx / L.cs;
+    int i, j, k;
+    if (decode_colour(L, colour, idx - colour * L.cs, i, j, k)) s += v[idx];
+  }
+  sm[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = kThreads / 2; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = w * sm[0];
+}
+__global__ void k_final_sum(const double* partial, int n, double* acc) {
+  __shared__ double sm[1024];
+  // fixed-shape reduction: thread t sums elements t, t+1024, ...; then tree
+  double s = 0.0;
+  for (int i = threadIdx.x; i < n; i += 1024) s += partial[i];
+  sm[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *acc = *acc + sm[0];
+}
+__global__ void k_scale_scalar(double* acc, double inv_volume) { *acc = *acc / inv_volume; }
+
+// ------------------------------------------------------------------ tail interpreter ---------
+template <int OP>
+__device__ void tail_run(const LevelDev* __restrict__ levels, const ParamsDev& P, const TailOp* __restrict__ ops, int n_ops,
+                         double* scal, double* red) {
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  for (int o = 0; o < n_ops; ++o) {
+    const TailOp op = ops[o];
+    const LevelDev& L = levels[op.l];
+    switch (op.type) {
+      case TOP_SMOOTH:
+        for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, op.a, tid, nthr);
+        break;
+      case TOP_RESID: {
+        double m = 0.0;
+        for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
+        if (op.a >= 0) { m = block_max(m, red); if (tid == 0) atomic_max_nonneg(&scal[op.a], m); }
+      } break;
+      case TOP_RESTRICT: {
+        const LevelDev& Lc = levels[op.l - 1];
+        for (int b = 0; b < L.nb; ++b) { do_restrict(L, Lc, op.a, b, tid, nthr); if (op.b >= 0) do_restrict(L, Lc, op.b, b, tid, nthr); }
+      } break;
+      case TOP_CRHS:
+        for (int q = 0; q < L.n_parents; ++q) do_crhs<OP>(L, P, L.parents_list[q], tid, nthr);
+        break;
+      case TOP_OLDPL:
+        for (int e = 0; e < L.n_oldpl; ++e) do_oldpl(L, P, e, tid, nthr);
+        break;
+      case TOP_CORR_PROLONG: {
+        const LevelDev& Lc = levels[op.l - 1];
+        for (int b = 0; b < L.nb; ++b) do_corr_prolong(L, Lc, P, b, tid, nthr);
+      } break;
+      case TOP_RB_FILL: {
+        const LevelDev& Lc = levels[op.l - 1];
+        for (int e = 0; e < L.n_rb; ++e) {
+          if (op.a) do_rb_fill<GM_PHI_GZ>(L, Lc, P, 0, e, tid, nthr); else do_rb_fill<GM_PHI>(L, Lc, P, 0, e, tid, nthr);
+        }
+      } break;
+      case TOP_COPY_OLD:
+        for (size_t i = tid; i < (size_t)L.nb * L.bs; i += nthr) L.var[2][i] = L.var[0][i];
+        break;
+      case TOP_COARSE_SOLVE: {
+        // coarse loop of mg_fas_vcycle, src/m_multigrid.f90:202-208
+        double m = 0.0;
+        for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
+        const double init_res = block_max(m, red);
+        int it = 0;
+        for (int i = 1; i <= op.b; ++i) {
+          for (int n = 1; n <= op.a; ++n) {
+            for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, (n - 1) & 1, tid, nthr);
+            __syncthreads();
+          }
+          m = 0.0;
+          for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
+          const double res = block_max(m, red);
+          it = i;
+          if (res < scal[SCAL_COARSE_REL] * init_res || res < scal[SCAL_COARSE_ABS]) break;
+        }
+        if (tid == 0) scal[SCAL_COARSE_ITERS] = (double)it;
+      } break;
+      default: break;
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ levels, const __grid_constant__ ParamsDev P,
+                                               const TailOp* __restrict__ ops, int n_ops, double* scal) {
+  __shared__ double red[32];
+  OMG_SWITCH_OP(P.op, tail_run<OP>(levels, P, ops, n_ops, scal, red));
+}
+
+// ------------------------------------------------------------------ host <-> device layout ----
+// staging slab per box: (nc+2)^3 doubles, reference order cc(i, j, k) i fastest, ghost shell included.
+__global__ void __launch_bounds__(kThreads) k_unpack(const __grid_constant__ LevelDev L, int iv, const int* __restrict__ boxes,
+                                                     const double* __restrict__ stage, int with_faces) {
+  const int b = boxes[blockIdx.x];
+  const int nc = L.nc, n2 = nc + 2;
+  const double* s = stage + (size_t)blockIdx.x * n2 * n2 * n2;
+  double* v = L.var[iv] + (size_t)b * L.bs;
+  for (int idx = threadIdx.x; idx < L.bs; idx += blockDim.x) {
+    const int colour = idx / L.cs;
+    int i, j, k;
+    if (!decode_colour(L, colour, idx - colour * L.cs, i, j, k)) continue;
+    v[idx] = s[((size_t)(k + 1) * n2 + (j + 1)) * n2 + (i + 1)];
+  }
+  if (with_faces && L.faces[iv]) {
+    double* fc = L.faces[iv] + (size_t)b * 6 * nc * nc;
+    for (int idx = threadIdx.x; idx < 6 * nc * nc; idx += blockDim.x) {
+      const int f = idx / (nc * nc), r = idx - f * nc * nc, t1 = r % nc, t2 = r / nc;
+      const int g = (f & 1) ? nc + 1 : 0;
+      int i, j, k;
+      if (f < 2) { i = g; j = t1 + 1; k = t2 + 1; } else if (f < 4) { i = t1 + 1; j = g; k = t2 + 1; } else { i = t1 + 1; j = t2 + 1; k = g; }
+      fc[idx] = s[((size_t)k * n2 + j) * n2 + i];
+    }
+  }
+}
+
+// ghost_mode: -1 none, else GhostMode for the six faces
+__global__ void __launch_bounds__(kThreads) k_pack(const __grid_constant__ LevelDev L, const __grid_constant__ ParamsDev P, int iv,
+                                                   const int* __restrict__ boxes, double* __restrict__ stage, int ghost_mode) {
+  const int b = boxes[blockIdx.x];
+  const int nc = L.nc, n2 = nc + 2;
+  double* s = stage + (size_t)blockIdx.x * n2 * n2 * n2;
+  const double* v = L.var[iv] + (size_t)b * L.bs;
+  for (int idx = threadIdx.x; idx < n2 * n2 * n2; idx += blockDim.x) s[idx] = 0.0;
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < L.bs; idx += blockDim.x) {
+    const int colour = idx / L.cs;
+    int i, j, k;
+    if (!decode_colour(L, colour, idx - colour * L.cs, i, j, k)) continue;
+    s[((size_t)(k + 1) * n2 + (j + 1)) * n2 + (i + 1)] = v[idx];
+  }
+  if (ghost_mode >= 0) {
+    for (int idx = threadIdx.x; idx < 6 * nc * nc; idx += blockDim.x) {
+      const int f = idx / (nc * nc), r = idx - f * nc * nc, t1 = r % nc, t2 = r / nc;
+      const int g = (f & 1) ? nc : -1;
+      int i, j, k;
+      if (f < 2) { i = g; j = t1; k = t2; } else if (f < 4) { i = t1; j = g; k = t2; } else { i = t1; j = t2; k = g; }
+      double val;
+      if (ghost_mode == GM_PHI) val = cell_at<GM_PHI>(L, P, L.var[iv], nullptr, b, i, j, k);
+      else if (ghost_mode == GM_OLD) val = cell_at<GM_OLD>(L, P, L.var[iv], nullptr, b, i, j, k);
+      else val = cell_at<GM_STORED>(L, P, L.var[iv], L.faces[iv], b, i, j, k);
+      s[((size_t)(k + 1) * n2 + (j + 1)) * n2 + (i + 1)] = val;
+    }
+  }
+}
+
+inline int grid_for(size_t n) { size_t g = (n + 255) / 256; return (int)(g > 148 * 16 ? 148 * 16 : (g == 0 ? 1 : g)); }
+}  // namespace
+
+// ------------------------------------------------------------------ launch wrappers -----------
+namespace omgk {
+
+void smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s) {
+  if (L.nb == 0) return;
+  OMG_SWITCH_OP(P.op, (k_smooth<OP><<<L.nb, kThreads, 0, s>>>(L, P, colour)));
+}
+void resid(const LevelDev& L, const ParamsDev& P, double* maxslot, cudaStream_t s) {
+  if (L.nb == 0) return;
+  OMG_SWITCH_OP(P.op, (k_resid<OP><<<L.nb, kThreads, 0, s>>>(L, P, maxslot)));
+}
+void restrict2(const LevelDev& Lf, const LevelDev& Lc, int iv0, int iv1, cudaStream_t s) {
+  if (Lf.nb == 0) return;
+  k_restrict<<<Lf.nb, kThreads, 0, s>>>(Lf, Lc, iv0, iv1);
+}
+void crhs(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
+  if (L.n_parents == 0) return;
+  OMG_SWITCH_OP(P.op, (k_crhs<OP><<<L.n_parents, kThreads, 0, s>>>(L, P)));
+}
+void oldpl(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
+  if (L.n_oldpl == 0) return;
+  k_oldpl<<<L.n_oldpl, kThreads, 0, s>>>(L, P);
+}
+void corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s) {
+  if (Lf.nb == 0) return;
+  k_corr_prolong<<<Lf.nb, kThreads, 0, s>>>(Lf, Lc, P);
+}
+void prolong_var(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int iv_to, int add, cudaStream_t s) {
+  if (Lf.nb == 0) return;
+  k_prolong_var<<<Lf.nb, kThreads, 0, s>>>(Lf, Lc, P, iv, iv_to, add);
+}
+void rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int gz, cudaStream_t s) {
+  if (Lf.n_rb == 0) return;
+  k_rb_fill<<<Lf.n_rb, kThreads, 0, s>>>(Lf, Lc, P, iv, gz);
+}
+void apply_op(const LevelDev& L, const ParamsDev& P, int i_out, cudaStream_t s) {
+  if (L.nb == 0) return;
+  OMG_SWITCH_OP(P.op, (k_apply_op<OP><<<L.nb, kThreads, 0, s>>>(L, P, i_out)));
+}
+void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv, cudaStream_t s) {
+  if (L.nb == 0) return;
+  BcVar bc;
+  for (int f = 0; f < 6; ++f) { bc.type[f] = bct[f]; bc.value[f] = bcv[f]; }
+  k_fill_stored<<<L.nb, kThreads, 0, s>>>(L, P, iv, bc);
+}
+void fill(double* p, size_t n, double v, cudaStream_t s) { if (n) k_fill<<<grid_for(n), 256, 0, s>>>(p, n, v); }
+void copy(double* dst, const double* src, size_t n, cudaStream_t s) { if (n) k_copy<<<grid_for(n), 256, 0, s>>>(dst, src, n); }
+void sub_scalar(double* p, size_t n, const double* mean, cudaStream_t s) { if (n) k_sub_scalar<<<grid_for(n), 256, 0, s>>>(p, n, mean); }
+void box_sums(const LevelDev& L, int iv, double w, double* partial, cudaStream_t s) {
+  if (L.n_leaves) k_box_sums<<<L.n_leaves, kThreads, 0, s>>>(L, iv, w, partial);
+}
+void final_sum(const double* partial, int n, double* acc, cudaStream_t s) { if (n) k_final_sum<<<1, 1024, 0, s>>>(partial, n, acc); }
+void div_scalar(double* acc, double denom, cudaStream_t s) { k_scale_scalar<<<1, 1, 0, s>>>(acc, denom); }
+void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, cudaStream_t s) {
+  if (n_ops) k_tail<<<1, 1024, 0, s>>>(levels, P, ops, n_ops, scal);
+}
+void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, cudaStream_t s) {
+  if (n) k_unpack<<<n, kThreads, 0, s>>>(L, iv, boxes, stage, with_faces);
+}
+void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, cudaStream_t s) {
+  if (n) k_pack<<<n, kThreads, 0, s>>>(L, P, iv, boxes, stage, ghost_mode);
+}
+
+}  // namespace omgk

@@ -1,0 +1,40 @@
+// omg_kernels.h -- host-callable launchers of the device kernels.
+#pragma once
+#include <cstddef>
+#include <cuda_runtime.h>
+#include "omg_device.cuh"
+
+enum TailOpType : int {
+  TOP_SMOOTH = 0, TOP_RESID, TOP_RESTRICT, TOP_CRHS, TOP_OLDPL, TOP_CORR_PROLONG, TOP_RB_FILL,
+  TOP_COPY_OLD, TOP_COARSE_SOLVE
+};
+struct TailOp { int type, l, a, b; };   // l: index into the device level array (lvl - lowest_lvl)
+
+// slots of the device scalar array
+enum ScalSlot : int {
+  SCAL_COARSE_REL = 0, SCAL_COARSE_ABS = 1, SCAL_COARSE_ITERS = 2, SCAL_MEAN = 3, SCAL_MAXRES = 4,
+  SCAL_RESHIST = 8,            // SCAL_RESHIST + n: max_res of cycle n inside omg_fas_vcycles
+  SCAL_COUNT = 8 + 256
+};
+
+namespace omgk {
+void smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s);
+void resid(const LevelDev& L, const ParamsDev& P, double* maxslot, cudaStream_t s);
+void restrict2(const LevelDev& Lf, const LevelDev& Lc, int iv0, int iv1, cudaStream_t s);
+void crhs(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
+void oldpl(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
+void corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s);
+void prolong_var(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int iv_to, int add, cudaStream_t s);
+void rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int gz, cudaStream_t s);
+void apply_op(const LevelDev& L, const ParamsDev& P, int i_out, cudaStream_t s);
+void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv, cudaStream_t s);
+void fill(double* p, size_t n, double v, cudaStream_t s);
+void copy(double* dst, const double* src, size_t n, cudaStream_t s);
+void sub_scalar(double* p, size_t n, const double* mean, cudaStream_t s);
+void box_sums(const LevelDev& L, int iv, double w, double* partial, cudaStream_t s);
+void final_sum(const double* partial, int n, double* acc, cudaStream_t s);
+void div_scalar(double* acc, double denom, cudaStream_t s);
+void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, cudaStream_t s);
+void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, cudaStream_t s);
+void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, cudaStream_t s);
+}  // namespace omgk

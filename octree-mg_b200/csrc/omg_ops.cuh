@@ -1,0 +1,244 @@
+// omg_ops.cuh -- level operations as device functions over one box, written for an arbitrary
+// thread partition (tid of nthr).  The batched kernels run one CTA per box; the tail interpreter
+// runs them for every box of a small level inside a single CTA.  These are the general path
+// (any box size, any face kind); omg_fast.cuh holds the tuned sm_100a kernels for big levels.
+#pragma once
+#include "omg_device.cuh"
+
+// smooth_boxes inner loop, one colour half-sweep: src/m_multigrid.f90:412-418 -> box_gs_*
+template <int OP>
+__device__ void do_smooth(const LevelDev& L, const ParamsDev& P, int b, int colour, int tid, int nthr) {
+  double* phi = L.var[0];
+  for (int idx = tid; idx < L.cs; idx += nthr) {
+    int i, j, k;
+    if (!decode_colour(L, colour, idx, i, j, k)) continue;
+    phi[(size_t)b * L.bs + colour * L.cs + idx] = gs_at<OP>(L, P, b, i, j, k);
+  }
+}
+
+// residual_box src/m_multigrid.f90:426-436; returns the thread-local max |res|
+template <int OP>
+__device__ double do_resid(const LevelDev& L, const ParamsDev& P, int b, int tid, int nthr) {
+  double m = 0.0;
+  for (int idx = tid; idx < L.bs; idx += nthr) {
+    const int colour = idx / L.cs;
+    int i, j, k;
+    if (!decode_colour(L, colour, idx - colour * L.cs, i, j, k)) continue;
+    const double r = L.var[1][(size_t)b * L.bs + idx] - op_at<OP>(L, P, b, i, j, k);
+    L.var[3][(size_t)b * L.bs + idx] = r;
+    m = fmax(m, fabs(r));
+  }
+  return m;
+}
+
+// restrict_onto src/m_restrict.f90:165-214 seen from the child: child box b of Lf writes its
+// parent's octant.  0.125 * sum(2x2x2) in Fortran array-element order (i fastest).
+__device__ void do_restrict(const LevelDev& Lf, const LevelDev& Lc, int iv, int b, int tid, int nthr) {
+  const int p = Lf.parent[b];
+  if (p < 0) return;   // parent on another rank: handled by the restrict exchange
+  const int off = Lf.coff[b];
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  const int h = Lf.nc >> 1;
+  const double* src = Lf.var[iv] + (size_t)b * Lf.bs;
+  double* dst = Lc.var[iv] + (size_t)p * Lc.bs;
+  for (int idx = tid; idx < h * h * h; idx += nthr) {
+    const int I = idx % h, J = (idx / h) % h, K = idx / (h * h);
+    double s = 0.0;
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+        for (int ii = 0; ii < 2; ++ii) s = s + src[cidx(Lf, 2 * I + ii, 2 * J + jj, 2 * K + kk)];
+    dst[cidx(Lc, ox + I, oy + J, oz + K)] = 0.125 * s;
+  }
+}
+
+// tail of update_coarse src/m_multigrid.f90:369-383 on one parent box: rhs = L(phi) + res; old = phi
+template <int OP>
+__device__ void do_crhs(const LevelDev& L, const ParamsDev& P, int b, int tid, int nthr) {
+  for (int idx = tid; idx < L.bs; idx += nthr) {
+    const int colour = idx / L.cs;
+    int i, j, k;
+    if (!decode_colour(L, colour, idx - colour * L.cs, i, j, k)) continue;
+    const size_t g = (size_t)b * L.bs + idx;
+    L.var[1][g] = op_at<OP>(L, P, b, i, j, k) + L.var[3][g];
+    L.var[2][g] = L.var[0][g];
+  }
+}
+
+// "old ghost" snapshots: the ghost values that `old(:) = phi(:)` copies along
+// (src/m_multigrid.f90:381-382, :121-126) where they cannot be re-derived from old's interior.
+__device__ void do_oldpl(const LevelDev& L, const ParamsDev& P, int e, int tid, int nthr) {
+  const int b = L.oldpl_list[3 * e], f = L.oldpl_list[3 * e + 1], pl = L.oldpl_list[3 * e + 2];
+  const int nc = L.nc;
+  for (int idx = tid; idx < nc * nc; idx += nthr) {
+    const int t1 = idx % nc, t2 = idx / nc;
+    int i, j, k;
+    const int g = (f & 1) ? nc : -1;
+    if (f < 2) { i = g; j = t1; k = t2; } else if (f < 4) { i = t1; j = g; k = t2; } else { i = t1; j = t2; k = g; }
+    L.gpl_old[(size_t)pl * nc * nc + idx] = cell_at<GM_PHI>(L, P, L.var[0], nullptr, b, i, j, k);
+  }
+}
+
+// correct_children src/m_multigrid.f90:387-402 fused with mg_prolong / prolong_onto / mg_prolong_sparse
+// (src/m_prolong.f90:124-156, :159-240) seen from the child box b of Lf:
+//   phi_f += P(phi_c - old_c), and the parent's octant of res_c = phi_c - old_c is stored.
+__device__ __forceinline__ double corr_at(const LevelDev& Lc, const ParamsDev& P, int p, int i, int j, int k) {
+  return cell_at<GM_PHI>(Lc, P, Lc.var[0], nullptr, p, i, j, k) - cell_at<GM_OLD>(Lc, P, Lc.var[2], nullptr, p, i, j, k);
+}
+__device__ void do_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int b, int tid, int nthr) {
+  const int p = Lf.parent[b];
+  if (p < 0) return;
+  const int off = Lf.coff[b];
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  const int h = Lf.nc >> 1;
+  double* phi = Lf.var[0] + (size_t)b * Lf.bs;
+  for (int idx = tid; idx < h * h * h; idx += nthr) {
+    const int I = idx % h, J = (idx / h) % h, K = idx / (h * h);
+    const int ic = ox + I, jc = oy + J, kc = oz + K;
+    const double c = corr_at(Lc, P, p, ic, jc, kc);
+    Lc.var[3][(size_t)p * Lc.bs + cidx(Lc, ic, jc, kc)] = c;
+    const double f0 = 0.25 * c;
+    const double flx = 0.25 * corr_at(Lc, P, p, ic - 1, jc, kc), fhx = 0.25 * corr_at(Lc, P, p, ic + 1, jc, kc);
+    const double fly = 0.25 * corr_at(Lc, P, p, ic, jc - 1, kc), fhy = 0.25 * corr_at(Lc, P, p, ic, jc + 1, kc);
+    const double flz = 0.25 * corr_at(Lc, P, p, ic, jc, kc - 1), fhz = 0.25 * corr_at(Lc, P, p, ic, jc, kc + 1);
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+        for (int ii = 0; ii < 2; ++ii) {
+          const double fine = f0 + (ii ? fhx : flx) + (jj ? fhy : fly) + (kk ? fhz : flz);
+          const int q = cidx(Lf, 2 * I + ii, 2 * J + jj, 2 * K + kk);
+          phi[q] = phi[q] + fine;
+        }
+  }
+}
+
+// generic mg_prolong (src/m_prolong.f90:51-85) of variable iv (ghost mode GMV) into iv_to
+template <int GMV>
+__device__ void do_prolong_var(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int iv_to, int add,
+                               int b, int tid, int nthr) {
+  const int p = Lf.parent[b];
+  if (p < 0) return;
+  const int off = Lf.coff[b];
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  const int h = Lf.nc >> 1;
+  const double* cv = Lc.var[iv]; const double* cf = Lc.faces[iv];
+  double* dst = Lf.var[iv_to] + (size_t)b * Lf.bs;
+  for (int idx = tid; idx < h * h * h; idx += nthr) {
+    const int I = idx % h, J = (idx / h) % h, K = idx / (h * h);
+    const int ic = ox + I, jc = oy + J, kc = oz + K;
+    const double f0 = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc, kc);
+    const double flx = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic - 1, jc, kc), fhx = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic + 1, jc, kc);
+    const double fly = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc - 1, kc), fhy = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc + 1, kc);
+    const double flz = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc, kc - 1), fhz = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc, kc + 1);
+    for (int kk = 0; kk < 2; ++kk) for (int jj = 0; jj < 2; ++jj) for (int ii = 0; ii < 2; ++ii) {
+      const double fine = f0 + (ii ? fhx : flx) + (jj ? fhy : fly) + (kk ? fhz : flz);
+      const int q = cidx(Lf, 2 * I + ii, 2 * J + jj, 2 * K + kk);
+      dst[q] = add ? dst[q] + fine : fine;
+    }
+  }
+}
+
+// fill_refinement_bnd + box_gc_for_fine_neighbor + sides_rb (src/m_ghost_cells.f90:287-328, :500-577,
+// :769-861) for refinement-boundary entry e of the fine level: materialises the ghost plane.
+// GMC = GM_PHI normally, GM_PHI_GZ while the coarse ghosts are the zeros written by mg_fas_fmg.
+// GMV selects the variable class (phi: GM_PHI/GM_PHI_GZ with plane pool; stored: faces pool).
+template <int GMC>
+__device__ void do_rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int e, int tid, int nthr) {
+  const int b = Lf.rb_list[4 * e], f = Lf.rb_list[4 * e + 1], cb = Lf.rb_list[4 * e + 2], pl = Lf.rb_list[4 * e + 3];
+  if (cb < 0) return;   // coarse neighbour on another rank: plane arrives through the halo exchange
+  const int nc = Lf.nc, h = nc >> 1;
+  const int off = Lf.coff[b];
+  const int di[3] = {off & 1023, (off >> 10) & 1023, (off >> 20) & 1023};
+  const int d = f >> 1, ta = (d == 0) ? 1 : 0, tb = (d == 2) ? 1 : 2;
+  const int cfix = (f & 1) ? 0 : nc - 1;          // coarse interior layer adjacent to the fine box
+  const double* cv = Lc.var[iv]; const double* cf = Lc.faces[iv];
+  const double* fv = Lf.var[iv] + (size_t)b * Lf.bs;
+  const int ix = (f & 1) ? nc - 1 : 0, dix = (f & 1) ? -1 : 1;
+  double* out = (iv == 0) ? Lf.gpl + (size_t)pl * nc * nc : Lf.faces[iv] + ((size_t)b * 6 + f) * nc * nc;
+  for (int idx = tid; idx < nc * nc; idx += nthr) {
+    const int A = idx % nc, B = idx / nc;          // 0-based fine tangential indices
+    const int ia = (A >> 1), jb = (B >> 1);        // coarse patch indices (0-based interior of the patch)
+    int c[3];
+    auto T = [&](int da, int db) {
+      c[d] = cfix; c[ta] = di[ta] + ia + da; c[tb] = di[tb] + jb + db;
+      return (iv == 0) ? cell_at<GMC>(Lc, P, cv, nullptr, cb, c[0], c[1], c[2])
+                       : cell_at<GM_STORED>(Lc, P, cv, cf, cb, c[0], c[1], c[2]);
+    };
+    const double t0 = T(0, 0);
+    const double g1 = 0.125 * (T(1, 0) - T(-1, 0));
+    const double g2 = 0.125 * (T(0, 1) - T(0, -1));
+    double gc = (A & 1) ? t0 + g1 : t0 - g1;
+    gc = (B & 1) ? gc + g2 : gc - g2;
+    int q[3], r[3];
+    q[d] = ix; r[d] = ix + dix; q[ta] = r[ta] = A; q[tb] = r[tb] = B;
+    out[idx] = 0.5 * gc + 0.75 * fv[cidx(Lf, q[0], q[1], q[2])] - 0.25 * fv[cidx(Lf, r[0], r[1], r[2])];
+  }
+}
+
+// box_op into an arbitrary variable (mg_apply_op, src/m_multigrid.f90:439-456)
+template <int OP>
+__device__ void do_apply_op(const LevelDev& L, const ParamsDev& P, int i_out, int b, int tid, int nthr) {
+  for (int idx = tid; idx < L.bs; idx += nthr) {
+    const int colour = idx / L.cs;
+    int i, j, k;
+    if (!decode_colour(L, colour, idx - colour * L.cs, i, j, k)) continue;
+    L.var[i_out][(size_t)b * L.bs + idx] = op_at<OP>(L, P, b, i, j, k);
+  }
+}
+
+// materialise the ghost faces of a stored-face variable (mg_fill_ghost_cells_lvl for iv >= 5):
+// same-level copy and physical boundary (constant bc of that variable); refinement boundaries are
+// handled by do_rb_fill.  bc_type / bc_value are the variable's constants for face f.
+__device__ void do_fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv,
+                               int b, int tid, int nthr) {
+  const int nc = L.nc;
+  const double* v = L.var[iv];
+  for (int idx = tid; idx < 6 * nc * nc; idx += nthr) {
+    const int f = idx / (nc * nc), r = idx - f * nc * nc, t1 = r % nc, t2 = r / nc;
+    const int kind = L.fkind[b * 6 + f], arg = L.farg[b * 6 + f];
+    double* out = L.faces[iv] + ((size_t)b * 6 + f) * nc * nc + r;
+    int i1, j1, k1, i2, j2, k2;
+    const int n1 = (f & 1) ? nc - 1 : 0, n2 = (f & 1) ? nc - 2 : 1;
+    if (f < 2) { i1 = n1; i2 = n2; j1 = j2 = t1; k1 = k2 = t2; }
+    else if (f < 4) { j1 = n1; j2 = n2; i1 = i2 = t1; k1 = k2 = t2; }
+    else { k1 = n1; k2 = n2; i1 = i2 = t1; j1 = j2 = t2; }
+    if (kind == FK_SAME) {
+      // neighbour's interior layer facing me
+      int ii = i1, jj = j1, kk = k1;
+      const int m = (f & 1) ? 0 : nc - 1;
+      if (f < 2) ii = m; else if (f < 4) jj = m; else kk = m;
+      *out = v[(size_t)arg * L.bs + cidx(L, ii, jj, kk)];
+    } else if (kind == FK_PHYS) {
+      const int type = bct[f];
+      double c0, c1, c2;
+      if (type == -10) { c0 = 2; c1 = -1; c2 = 0; }
+      else if (type == -11) { c0 = L.dr[f >> 1] * ((f & 1) ? 1.0 : -1.0); c1 = 1; c2 = 0; }
+      else { c0 = 0; c1 = 2; c2 = -1; }
+      const double x1 = v[(size_t)b * L.bs + cidx(L, i1, j1, k1)];
+      const double x2 = nc > 1 ? v[(size_t)b * L.bs + cidx(L, i2, j2, k2)] : 0.0;
+      *out = c0 * bcv[f] + c1 * x1 + c2 * x2;
+    }
+  }
+}
+
+// block-wide max of non-negative doubles; result valid in thread 0 (and broadcast through smem)
+__device__ double block_max(double v, double* smem /* >= 32 doubles */) {
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) smem[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    v = (int)threadIdx.x < nw ? smem[threadIdx.x] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (threadIdx.x == 0) smem[0] = v;
+  }
+  __syncthreads();
+  v = smem[0];
+  __syncthreads();
+  return v;
+}

@@ -1,0 +1,172 @@
+"""GPU parity: the CUDA path (through the C ABI and the host mirror) against the CPU oracle on the same
+inputs.  The product is compiled with -fmad=false and uses the reference's expression order, so for GSRB
+every number must agree BITWISE with the oracle (-ffp-contract=off); the north-star tolerances (1e-10
+relative on per-cycle residuals, 1e-12 * |phi| on the solution) are asserted as well for the record."""
+import numpy as np
+import pytest
+
+import problems as P
+from compare import assert_state_equal, state_diff
+
+pytestmark = pytest.mark.gpu
+
+RES_RTOL = 1e-10     # north-star: per-cycle residual norms within 1e-10 relative
+SOL_RTOL = 1e-12     # north-star: final solution max-abs difference within 1e-12 * solution norm
+
+
+def check_histories(h_o, h_g):
+    assert len(h_o) == len(h_g)
+    for a, b in zip(h_o, h_g):
+        assert abs(a - b) <= RES_RTOL * abs(a), (h_o, h_g)
+    assert h_o == h_g, "residual histories differ in the last bits: %r vs %r" % (h_o, h_g)
+
+
+def check_tolerance(orc, mg):
+    d = state_diff(orc, mg, variables=(1,))["phi"]
+    assert d[0] <= SOL_RTOL * d[1]
+
+
+@pytest.mark.parametrize("fmg", [False, True])
+@pytest.mark.parametrize("n,box", [(32, 8), (64, 16)])
+def test_uniform_grid_laplacian(oracle, product, n, box, fmg):
+    """config 1 (tests/test_uniform_grid.f90), GSRB, Dirichlet planes from the exact solution."""
+    orc, i_sol = P.uniform_problem(oracle.OracleMg, n, box)
+    mg, _ = P.uniform_problem(product.Mg, n, box)
+    h_o = P.run_cycles(orc, 5, fmg)
+    h_g = P.run_cycles(mg, 5, fmg)
+    check_histories(h_o, h_g)
+    check_tolerance(orc, mg)
+    assert_state_equal(orc, mg)
+    # the reference test's own pass criterion: the error against the manufactured solution collapses
+    assert P.max_error(mg, i_sol) < (1e-6 if fmg else 1e-4)
+
+
+def test_performance_problem(oracle, product):
+    """config 2 semantics at a size the oracle finishes quickly: rhs = 1, homogeneous Dirichlet."""
+    orc = P.performance_problem(oracle.OracleMg, 64, 16)
+    mg = P.performance_problem(product.Mg, 64, 16)
+    check_histories(P.run_cycles(orc, 4, False), P.run_cycles(mg, 4, False))
+    assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("op,bc,lam", [
+    (P.mg_helmholtz, "neumann0", 1.0),
+    (P.mg_helmholtz, "callback", 2.5),
+    (P.mg_vlaplacian, "mixed", 0.0),
+    (P.mg_vlaplacian, "callback", 0.0),
+    (P.mg_vhelmholtz, "neumann0", 1.0),
+    (P.mg_ahelmholtz, "mixed", 0.5),
+    (P.mg_laplacian, "mixed", 0.0),
+    (P.mg_laplacian, "continuous_x", 0.0),
+])
+@pytest.mark.parametrize("fmg", [False, True])
+def test_operators_and_boundary_conditions(oracle, product, op, bc, lam, fmg):
+    """config 4 semantics (variable-coefficient / Helmholtz operators, Neumann / mixed / continuous BC)."""
+    orc, _ = P.uniform_problem(oracle.OracleMg, 32, 8, operator_type=op, bc=bc, lam=lam)
+    mg, _ = P.uniform_problem(product.Mg, 32, 8, operator_type=op, bc=bc, lam=lam)
+    check_histories(P.run_cycles(orc, 3, fmg), P.run_cycles(mg, 3, fmg))
+    assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("n,box", [((64, 32, 32), 8), ((48, 48, 48), 8), (32, 4), (64, 32), ((32, 64, 96), 16)])
+def test_shapes_and_box_sizes(oracle, product, n, box):
+    """non-cubic domains, several coarse boxes, box sizes 4 / 32, odd box counts."""
+    orc, _ = P.uniform_problem(oracle.OracleMg, n, box)
+    mg, _ = P.uniform_problem(product.Mg, n, box)
+    check_histories(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("fmg", [False, True])
+def test_refinement(oracle, product, fmg):
+    """config 3 (tests/test_refinement.f90): octree AMR, refinement-boundary ghost interpolation."""
+    orc, i_sol = P.refinement_problem(oracle.OracleMg, 3, 8, 32)
+    mg, _ = P.refinement_problem(product.Mg, 3, 8, 32)
+    # inputs built through the library's own restrict / ghost fill / operator must already agree
+    assert_state_equal(orc, mg, variables=(2, i_sol), ghosts_of=(i_sol,))
+    check_histories(P.run_cycles(orc, 4, fmg), P.run_cycles(mg, 4, fmg))
+    assert_state_equal(orc, mg)
+    assert P.max_error(mg, i_sol, leaves_only=True) < 1e-3
+
+
+def test_refinement_nonzero_bc(oracle, product):
+    """AMR with a non-zero Dirichlet value: exercises the zeroed-ghost state after mg_fas_fmg(have_guess=F)."""
+    def build(cls):
+        mg = cls(P.mg_laplacian, P.mg_smoother_gsrb)
+        for nb in range(1, 7):
+            mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.75)
+        mg.mg_set_methods()
+        # refine a corner region so that refinement boundaries touch the physical boundary
+        P.build_amr_tree(mg, 3, [32] * 3, 8, [1.0 / 32] * 3,
+                         refine=lambda lvl, c, L: bool(np.all(c <= 0.5 ** lvl * L)))
+        for lvl, id_ in P.all_ids(mg):
+            mg.cc(id_)[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1] = 1.0 + 0.1 * lvl
+        return mg
+    orc, mg = build(oracle.OracleMg), build(product.Mg)
+    check_histories(P.run_cycles(orc, 3, True), P.run_cycles(mg, 3, True))
+    check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
+
+
+def test_periodic_subtract_mean(oracle, product):
+    """fully periodic Laplacian: subtract_mean is active (src/m_multigrid.f90:245-294).  The mean is a
+    global sum whose association differs between a sequential CPU loop and a parallel reduction, so this
+    case is held to the north-star tolerances instead of bitwise equality."""
+    def build(cls):
+        mg = cls(P.mg_laplacian, P.mg_smoother_gsrb)
+        mg.mg_set_methods()
+        mg.mg_build_rectangle([32] * 3, 8, [1.0 / 32] * 3, [0.0] * 3, [True] * 3)
+        mg.mg_load_balance()
+        mg.mg_allocate_storage()
+        for lvl, id_ in P.all_ids(mg):
+            X, Y, Z = P.cell_coords(mg, id_, lvl)
+            mg.cc(id_)[P.mg_irhs - 1] = np.sin(2 * np.pi * X) * np.cos(4 * np.pi * Y) + 0.3 * np.sin(2 * np.pi * Z) + 0.05
+        return mg
+    orc, mg = build(oracle.OracleMg), build(product.Mg)
+    assert orc.get_int("subtract_mean") == 1 and mg.get_int("subtract_mean") == 1
+    for fmg in (True, False):
+        h_o, h_g = P.run_cycles(orc, 3, fmg), P.run_cycles(mg, 3, fmg)
+        for a, b in zip(h_o, h_g):
+            assert abs(a - b) <= RES_RTOL * max(abs(a), h_o[0])
+    d = state_diff(orc, mg, variables=(1,), ghosts_of=())["phi"]
+    assert d[0] <= 1e-12 * d[1]
+
+
+def test_phi_bc_store(oracle, product):
+    """mg_phi_bc_store (src/m_ghost_cells.f90:66-117): planes kept in the rhs ghost cells."""
+    orc, _ = P.uniform_problem(oracle.OracleMg, 32, 8)
+    mg, _ = P.uniform_problem(product.Mg, 32, 8)
+    orc.mg_phi_bc_store()
+    mg.mg_phi_bc_store()
+    check_histories(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    assert_state_equal(orc, mg)
+
+
+def test_resident_mode_and_graph_replay(oracle, product):
+    """device-resident cycles (omg_fas_vcycles, CUDA-graph replay) give the same numbers as call-by-call."""
+    orc = P.performance_problem(oracle.OracleMg, 64, 16)
+    mg = P.performance_problem(product.Mg, 64, 16, gpu_resident=True)
+    mg.mg_gpu_push(P.mg_iphi)
+    mg.mg_gpu_push(P.mg_irhs)
+    mg.mg_fas_vcycle(want_res=False)          # uploads parameters / boundary data
+    h_o = P.run_cycles(orc, 5, False)
+    h_g, ms = mg.fas_vcycles(4)
+    assert h_g == h_o[1:]
+    assert mg.stat("graph_launches") >= 4
+    for iv in (1, 2, 3, 4):
+        mg.mg_gpu_pull(iv)
+    assert_state_equal(orc, mg)
+
+
+def test_no_cpu_fallback_errors(product):
+    """error behaviour of the boundary (the reference error-stops; the C ABI returns codes + messages)."""
+    mg = product.Mg(P.mg_laplacian, P.mg_smoother_gs)
+    mg.mg_set_methods()
+    mg.mg_build_rectangle([32] * 3, 8, [1.0 / 32] * 3, [0.0] * 3, [False] * 3)
+    mg.mg_load_balance()
+    mg.mg_allocate_storage()
+    with pytest.raises(product.MgError, match="mg_smoother_gs"):
+        mg.mg_fas_vcycle()
+    with pytest.raises(product.MgError, match="lvl > highest_lvl"):
+        mg.mg_fill_ghost_cells_lvl(5, P.mg_iphi)

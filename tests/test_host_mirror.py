@@ -1,0 +1,110 @@
+"""CPU tests of the host side: the C++ mirror of the reference's setup modules (tree, load balance)
+against the oracle's independent restatement, and the C-ABI library surface.  No GPU needed: nothing
+here launches a kernel (mg_allocate_storage must fail loudly without a device)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import problems as P
+from compare import assert_trees_equal
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def build_uniform(cls, n, box, n_cpu=1, periodic=(False,) * 3, lb="default", smoother=P.mg_smoother_gsrb, **kw):
+    mg = cls(P.mg_laplacian, smoother, n_cpu=n_cpu, **kw)
+    mg.mg_set_methods()
+    n3 = [n] * 3 if np.isscalar(n) else list(n)
+    mg.mg_build_rectangle(n3, box, [1.0 / n3[0]] * 3, [0.0] * 3, list(periodic))
+    if lb == "simple":
+        mg.mg_load_balance_simple()
+    else:
+        mg.mg_load_balance()
+        if lb == "parents":
+            mg.mg_load_balance_parents()
+    return mg
+
+
+@pytest.mark.parametrize("n,box", [(64, 16), (128, 16), (64, 32), ((64, 32, 32), 8), ((48, 48, 48), 8), ((32, 64, 96), 16), (16, 2)])
+@pytest.mark.parametrize("n_cpu", [1, 2, 5, 8])
+def test_rectangle_tree_and_partition_match_oracle(oracle, product, n, box, n_cpu):
+    for lb in ("default", "simple", "parents"):
+        a = build_uniform(oracle.OracleMg, n, box, n_cpu=n_cpu, lb=lb)
+        b = build_uniform(product.Mg, n, box, n_cpu=n_cpu, lb=lb)
+        assert_trees_equal(a, b)
+
+
+def test_periodic_and_gs_trees(oracle, product):
+    for per in [(True, True, True), (True, False, True)]:
+        assert_trees_equal(build_uniform(oracle.OracleMg, 32, 8, periodic=per), build_uniform(product.Mg, 32, 8, periodic=per))
+    a = build_uniform(oracle.OracleMg, 64, 16, smoother=P.mg_smoother_gs)
+    b = build_uniform(product.Mg, 64, 16, smoother=P.mg_smoother_gs)
+    assert_trees_equal(a, b)
+    assert a.box_size_lvl(a.lowest_lvl) == 2
+
+
+@pytest.mark.parametrize("n_cpu", [1, 3, 8])
+def test_amr_tree_matches_oracle(oracle, product, n_cpu):
+    def amr(cls, **kw):
+        mg = cls(P.mg_laplacian, P.mg_smoother_gsrb, n_cpu=n_cpu, **kw)
+        mg.mg_set_methods()
+        mg.mg_allocate_storage = lambda: None         # tree only (no device in this test)
+        P.build_amr_tree(mg, 3, [64] * 3, 16, [1.0 / 64] * 3)
+        return mg
+    a, b = amr(oracle.OracleMg), amr(product.Mg)
+    assert_trees_equal(a, b)
+    assert [len(b.ids(l)) for l in (1, 2, 3)] == [64, 64, 64]
+    assert len(b.ref_bnds(1)) > 0 and len(b.ref_bnds(2)) > 0
+
+
+def test_partition_is_morton_contiguous(product):
+    """north-star: boxes partitioned in Morton order as in m_load_balance -- 8 ranks = 8 octants"""
+    mg = build_uniform(product.Mg, 128, 16, n_cpu=8)
+    t = mg.tree_export()
+    ids = mg.ids(1)
+    ranks = [t[i - 1, 0] for i in ids]
+    assert ranks == sorted(ranks)                                     # contiguous chunks of the ids list
+    for i in ids:
+        ix = t[i - 1, 2:5]
+        octant = (ix[0] - 1) // 4 + 2 * ((ix[1] - 1) // 4) + 4 * ((ix[2] - 1) // 4)
+        assert t[i - 1, 0] == octant
+    assert mg.mg_number_of_unknowns() == 128 ** 3
+
+
+def test_no_device_fails_loudly(product):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    mg = build_uniform(product.Mg, 32, 8)
+    with pytest.raises(product.MgError, match="no CUDA device"):
+        mg.mg_allocate_storage()
+
+
+def test_c_abi_exports_every_declared_symbol(product):
+    """every function declared in include/omg_gpu.h is exported by libomg_b200.so"""
+    hdr = open(os.path.join(ROOT, "include", "omg_gpu.h")).read()
+    names = sorted(set(re.findall(r"\b(omg_[a-z_0-9]+)\s*\(", hdr)))
+    assert len(names) >= 25
+    G, _ = product.libs()
+    for n in names:
+        assert hasattr(G, n), n
+    assert b"sm_100a" in G.omg_version()
+    h = ctypes.c_void_p()
+    import torch
+    if not torch.cuda.is_available():
+        assert G.omg_create(0, ctypes.byref(h)) != 0 and not h.value    # no CPU fallback
+
+
+def test_product_does_not_reference_the_oracle():
+    """the product tree must not import / link / mention the oracle"""
+    pkg = os.path.join(ROOT, "octree-mg_b200")
+    for dirpath, _, files in os.walk(pkg):
+        if os.path.basename(dirpath) == "build":
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp", ".f90")):
+                src = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "liboracle" not in src and "import oracle" not in src and "from oracle" not in src, f

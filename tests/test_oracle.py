@@ -1,0 +1,173 @@
+"""CPU tests of the oracle itself.  The reference ships no golden vectors and cannot be compiled here
+(SURVEY.md F2, F3), so the oracle is pinned by (i) the reference tests' own pass criterion and the
+surveyor's convergence anchors, (ii) rank-count invariance, (iii) GSRB box-size invariance, (iv) bitwise
+agreement with an independent global-array restatement, (v) committed golden fixtures (regression)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import problems as P
+from compare import assert_state_equal
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def global_phi(mg, lvl=None, iv=P.mg_iphi):
+    """assemble the finest uniform level into one [z, y, x] array"""
+    lvl = mg.highest_lvl if lvl is None else lvl
+    nc = mg.box_size_lvl(lvl)
+    ids = mg.ids(lvl)
+    ix = np.array([mg.box_info(i)["ix"] for i in ids])
+    nb = ix.max(axis=0)
+    out = np.zeros((nb[2] * nc, nb[1] * nc, nb[0] * nc))
+    for id_, (bx, by, bz) in zip(ids, ix):
+        out[(bz - 1) * nc:bz * nc, (by - 1) * nc:by * nc, (bx - 1) * nc:bx * nc] = mg.cc(id_, nc)[iv - 1, 1:-1, 1:-1, 1:-1]
+    return out
+
+
+# max error per iteration, 64^3, GSRB, Dirichlet callback
+ANCHOR_V = [9.5e-2, 8.1e-3, 6.8e-4, 5.8e-5, 4.9e-6, 4.2e-7]
+ANCHOR_FMG = [2.6e-2, 4.6e-4, 8.8e-6, 2.2e-7, 4.8e-9, 9.8e-11]
+
+
+@pytest.mark.parametrize("fmg,anchor", [(False, ANCHOR_V), (True, ANCHOR_FMG)])
+def test_convergence_anchors(oracle, fmg, anchor):
+    mg, i_sol = P.uniform_problem(oracle.OracleMg, 64, 16)
+    for it, ref in enumerate(anchor, 1):
+        mg.mg_fas_fmg(it > 1) if fmg else mg.mg_fas_vcycle()
+        err = P.max_error(mg, i_sol)
+        assert abs(err - ref) <= 0.03 * ref, (it, err, ref)
+
+
+def test_manufactured_solution_reaches_rounding(oracle):
+    """tests/test_uniform_grid.f90's criterion: rhs is the discrete operator of the exact field, so the
+    error must fall to rounding level, not O(h^2)."""
+    mg, i_sol = P.uniform_problem(oracle.OracleMg, 32, 8)
+    hist = P.run_cycles(mg, 9, True)
+    assert P.max_error(mg, i_sol) < 5e-13
+    assert hist[-1] < 1e-9 * hist[0]
+
+
+@pytest.mark.parametrize("n_cpu", [2, 3, 8])
+def test_rank_count_invariance_uniform(oracle, n_cpu):
+    """results are bitwise independent of the number of MPI ranks."""
+    a, _ = P.uniform_problem(oracle.OracleMg, 32, 8)
+    b, _ = P.uniform_problem(oracle.OracleMg, 32, 8, n_cpu=n_cpu)
+    assert P.run_cycles(a, 2, True) == P.run_cycles(b, 2, True)
+    assert P.run_cycles(a, 2, False) == P.run_cycles(b, 2, False)
+    assert_state_equal(a, b)
+    ranks = {a_["rank"] for a_ in (b.box_info(i) for i in b.ids(1))}
+    assert len(ranks) == n_cpu
+
+
+@pytest.mark.parametrize("n_cpu", [2, 5])
+def test_rank_count_invariance_amr(oracle, n_cpu):
+    a, _ = P.refinement_problem(oracle.OracleMg, 3, 8, 32)
+    b, _ = P.refinement_problem(oracle.OracleMg, 3, 8, 32, n_cpu=n_cpu)
+    assert P.run_cycles(a, 2, True) == P.run_cycles(b, 2, True)
+    assert P.run_cycles(a, 2, False) == P.run_cycles(b, 2, False)
+    assert_state_equal(a, b)
+
+
+def test_gsrb_box_size_invariance(oracle):
+    """with GSRB on a uniform grid the result does not depend on the box size."""
+    ref = None
+    for box in (4, 8, 16, 32):
+        mg, _ = P.uniform_problem(oracle.OracleMg, 32, box)
+        hist = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False)
+        g = global_phi(mg)
+        if ref is None:
+            ref = (hist, g)
+        else:
+            assert hist == ref[0]
+            assert np.array_equal(g, ref[1])
+
+
+@pytest.mark.parametrize("helm", [False, True])
+def test_global_array_restatement_agrees_bitwise(oracle, helm):
+    """independent numpy multigrid on one global array per level == box-structured oracle, bit for bit"""
+    from oracle.global_array_mg import GlobalMG
+    n, box, lam = 32, 8, (1.5 if helm else 0.0)
+    op = P.mg_helmholtz if helm else P.mg_laplacian
+    mg, _ = P.uniform_problem(oracle.OracleMg, n, box, operator_type=op, lam=lam)
+
+    def bc_fn(l, nb, n_l, dr_l):
+        return P.mg_bc_dirichlet, P.face_plane(P.solution, np.zeros(3), np.full(3, dr_l), n_l, nb)
+    G = GlobalMG(n, 1.0 / n, bc_fn, lam=lam, helmholtz=helm)
+    G.rhs[0][1:-1, 1:-1, 1:-1] = global_phi(mg, iv=P.mg_irhs)
+    h_box = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False)
+    h_glob = [G.fmg(False), G.fmg(True), G.vcycle(), G.vcycle()]
+    assert h_box == h_glob
+    assert np.array_equal(global_phi(mg), G.phi[0][1:-1, 1:-1, 1:-1])
+
+
+def test_global_array_neumann_constants(oracle):
+    from oracle.global_array_mg import GlobalMG
+    n, box = 32, 16
+    mg, _ = P.uniform_problem(oracle.OracleMg, n, box, operator_type=P.mg_helmholtz, lam=1.0, bc="mixed")
+    G = GlobalMG(n, 1.0 / n, lambda l, nb, n_l, dr_l: (P.mg_bc_dirichlet, 0.25) if nb == 1 else (P.mg_bc_neumann, 0.5),
+                 lam=1.0, helmholtz=True)
+    G.rhs[0][1:-1, 1:-1, 1:-1] = global_phi(mg, iv=P.mg_irhs)
+    assert P.run_cycles(mg, 3, True) == [G.fmg(False), G.fmg(True), G.fmg(True)]
+    assert np.array_equal(global_phi(mg), G.phi[0][1:-1, 1:-1, 1:-1])
+
+
+@pytest.mark.parametrize("op,bc,lam", [(P.mg_vlaplacian, "mixed", 0.0), (P.mg_vhelmholtz, "neumann0", 1.0),
+                                       (P.mg_ahelmholtz, "mixed", 0.5), (P.mg_helmholtz, "neumann0", 1.0)])
+def test_operators_converge(oracle, op, bc, lam):
+    mg, _ = P.uniform_problem(oracle.OracleMg, 32, 8, operator_type=op, bc=bc, lam=lam)
+    hist = P.run_cycles(mg, 6, True)
+    assert hist[-1] < 1e-4 * hist[0]
+    assert all(b < a for a, b in zip(hist, hist[1:]))
+
+
+def test_gs_smoother_converges(oracle):
+    """the reference default mg_smoother_gs (used by its test programs)"""
+    mg, i_sol = P.uniform_problem(oracle.OracleMg, 32, 8, smoother=P.mg_smoother_gs)
+    P.run_cycles(mg, 6, True)
+    assert P.max_error(mg, i_sol) < 1e-6
+
+
+def test_refinement_converges(oracle):
+    mg, i_sol = P.refinement_problem(oracle.OracleMg, 3, 8, 32)
+    assert [len(mg.ids(l)) for l in (1, 2, 3)] == [64, 64, 64]
+    e0 = P.max_error(mg, i_sol, leaves_only=True)
+    P.run_cycles(mg, 8, True)
+    assert P.max_error(mg, i_sol, leaves_only=True) < 1e-10 * e0
+
+
+def test_level_structure_matches_survey_appendix_b(oracle):
+    """SURVEY.md appendix B (restated from src/m_build_tree.f90:51-72)"""
+    expect = {(64, 16): (-4, -1, 76), (128, 16): (-5, -2, 588), (128, 32): (-5, -1, 77)}
+    for (n, box), (lo, fn, nb) in expect.items():
+        mg = oracle.OracleMg()
+        mg.mg_set_methods()
+        mg.mg_build_rectangle([n] * 3, box, [1.0 / n] * 3, [0.0] * 3, [False] * 3)
+        assert (mg.lowest_lvl, mg.first_normal_lvl, mg.n_boxes) == (lo, fn, nb)
+
+
+def test_error_conditions(oracle):
+    mg = oracle.OracleMg()
+    with pytest.raises(oracle.OracleError, match="box_size should be even"):
+        mg.mg_build_rectangle([30] * 3, 5, [1.0] * 3, [0.0] * 3, [False] * 3)
+    with pytest.raises(oracle.OracleError, match="does not divide"):
+        mg.mg_build_rectangle([30] * 3, 8, [1.0] * 3, [0.0] * 3, [False] * 3)
+    mg2, _ = P.uniform_problem(oracle.OracleMg, 16, 8)
+    with pytest.raises(oracle.OracleError, match="lvl > highest_lvl"):
+        mg2.mg_fill_ghost_cells_lvl(3, P.mg_iphi)
+    with pytest.raises(oracle.OracleError, match="cannot prolong highest"):
+        mg2.mg_prolong(1, P.mg_iphi, P.mg_iphi, False)
+
+
+def test_golden_fixtures(oracle):
+    """regression fixtures generated by tests/golden/make_golden.py from the oracle"""
+    path = os.path.join(HERE, "golden", "golden.json")
+    with open(path) as f:
+        gold = json.load(f)
+    import golden.make_golden as mk
+    for case in gold["cases"]:
+        got = mk.run_case(oracle.OracleMg, case["name"])
+        assert got["residuals"] == case["residuals"], case["name"]
+        assert got["phi_checksum"] == case["phi_checksum"], case["name"]
