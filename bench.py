@@ -43,7 +43,7 @@ class ClockSampler:
                 ["nvidia-smi", "-i", str(self.index),
                  "--query-gpu=clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
                  "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-                 "clocks_event_reasons.sw_power_cap", "--format=csv,noheader,nounits", "-lms", "100"],
+                 "clocks_event_reasons.sw_power_cap", "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -56,7 +56,14 @@ class ClockSampler:
     def stop(self):
         if self.proc:
             self.proc.terminate()
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        loaded = [r for r in self.rows if len(r) > 2 and r[0].isdigit()]
+        try:   # under load = power draw in the upper half of the observed range
+            pw = [float(r[2]) for r in loaded]
+            cut = 0.5 * (min(pw) + max(pw))
+            loaded = [r for r, w in zip(loaded, pw) if w >= cut] or loaded
+        except Exception:
+            pass
+        sm = sorted(int(r[0]) for r in loaded)
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
@@ -111,6 +118,8 @@ def main():
     ap.add_argument("--box", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
+    ap.add_argument("--no-fast", action="store_true", help="general-path kernels only")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -169,6 +178,13 @@ def main():
     # device-resident initial state: rhs = 1 on the interior of every level, phi = 0 (no host transfer needed)
     mg._gck(G.omg_set_var_const(gpu, P.mg_irhs, -20, 20, 1.0, 1))
     mg._gck(G.omg_set_var_const(gpu, P.mg_iphi, -20, 20, 0.0, 0))
+    if args.no_graph:
+        mg.set_option("use_graph", 0)
+    if args.no_fast:
+        mg.set_option("fast_kernels", 0)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     mg.mg_fas_vcycle(want_res=True)                       # uploads parameters; first cycle also builds the graph
     for _ in range(max(args.warmup - 1, 0)):
         mg.fas_vcycles(1)
@@ -179,9 +195,6 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     barrier()
     res, ms = mg.fas_vcycles(args.steps)                  # CUDA events on the handle's stream bracket the K cycles
     barrier()

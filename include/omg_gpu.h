@@ -117,6 +117,12 @@ int omg_apply_op(omg_handle* h, int i_out);
  * tests/test_performance.f90:68-76); residuals[n] receives max_res per cycle when non-null */
 int omg_fas_vcycles(omg_handle* h, int n, double* residuals);
 
+/* One building block of the cycle on its own, for per-kernel parity tests: what = "smooth_boxes" (lvl,
+ * arg = n_cycle; src/m_multigrid.f90:404-424), "update_coarse" (lvl; :347-384), "correct_children" (lvl;
+ * :387-402 plus the ghost fill that follows), "coarse_solve" (:202-208), "max_residual_lvl" (lvl; :296-311,
+ * result in *out). */
+int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* out);
+
 /* ---- multi-GPU (replaces mg_comm_init + sort_and_transfer_buffers, src/m_communication.f90) */
 int omg_nccl_unique_id(char out[128]);
 int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks);

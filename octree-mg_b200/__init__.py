@@ -94,6 +94,7 @@ def _declare(G, H):
     G.omg_fas_fmg.argtypes = [vp, ci, ci, C.POINTER(cd)]
     G.omg_fas_vcycles.argtypes = [vp, ci, C.POINTER(cd)]
     G.omg_fill_ghost_cells_lvl.argtypes = [vp, ci, ci]
+    G.omg_debug_step.argtypes = [vp, C.c_char_p, ci, ci, C.POINTER(cd)]
     G.omg_restrict_lvl.argtypes = [vp, ci, ci]
     G.omg_prolong.argtypes = [vp, ci, ci, ci, ci]
     G.omg_apply_op.argtypes = [vp, ci]
@@ -129,7 +130,7 @@ def _declare(G, H):
     H.omgh_comm_init.argtypes = [vp, ci, ci]
     H.omgh_build_rectangle.argtypes = [vp, C.POINTER(ci), ci, C.POINTER(cd), C.POINTER(cd), C.POINTER(ci), ci]
     for n in ("omgh_set_methods", "omgh_allocate_storage", "omgh_deallocate_storage", "omgh_phi_bc_store",
-              "omgh_gpu_push_bc"):
+              "omgh_gpu_push_bc", "omgh_gpu_push_params"):
         getattr(H, n).argtypes = [vp]
     for n in ("omgh_add_children", "omgh_set_leaves_parents", "omgh_set_next_level_ids", "omgh_set_neighbors_lvl",
               "omgh_set_refinement_boundaries", "omgh_load_balance", "omgh_apply_op", "omgh_fill_ghost_cells",
@@ -377,6 +378,9 @@ class Mg:
     def mg_gpu_pull(self, iv, with_ghosts=True):
         self._ck(self.H.omgh_gpu_pull(self.h, iv, int(with_ghosts)))
 
+    def mg_gpu_push_params(self):
+        self._ck(self.H.omgh_gpu_push_params(self.h))
+
     def mg_gpu_push_bc(self):
         self._ck(self.H.omgh_gpu_push_bc(self.h))
 
@@ -399,3 +403,30 @@ class Mg:
 
     def sync(self):
         self._gck(self.G.omg_sync(self.gpu))
+
+    # -- building blocks of the cycle (private in the reference; exposed for per-kernel parity tests) -------
+    def _step(self, what, lvl, arg=0):
+        """device-resident single step; in drop-in mode the four variables are pushed before and pulled after"""
+        resident = bool(self.get_int("gpu_resident"))
+        self._ck(self.H.omgh_gpu_push_params(self.h))
+        if not resident:
+            for iv in range(1, mg_num_vars + self.n_extra_vars + 1):
+                self.mg_gpu_push(iv)
+        out = C.c_double(0.0)
+        self._gck(self.G.omg_debug_step(self.gpu, what.encode(), lvl, arg, C.byref(out)))
+        if not resident:
+            for iv in (1, 2, 3, 4):
+                self.mg_gpu_pull(iv, True)
+        return out.value
+
+    def smooth_boxes(self, lvl, n_cycle):
+        self._step("smooth_boxes", lvl, n_cycle)
+
+    def update_coarse(self, lvl):
+        self._step("update_coarse", lvl)
+
+    def correct_children(self, lvl):
+        self._step("correct_children", lvl)
+
+    def max_residual_lvl(self, lvl):
+        return self._step("max_residual_lvl", lvl)

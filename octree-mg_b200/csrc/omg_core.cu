@@ -440,7 +440,12 @@ void exec_steps(omg_handle* h, Program& P) {
         if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, s))) omgk::smooth(L.dev, PD, st.a, s);
         h->launches++;
       } break;
-      case S_RESID: omgk::resid(h->L(st.l).dev, PD, st.a >= 0 ? h->d_scal.p + st.a : nullptr, s); h->launches++; break;
+      case S_RESID: {
+        LevelHost& L = h->L(st.l);
+        double* slot = st.a >= 0 ? h->d_scal.p + st.a : nullptr;
+        if (!(h->fast_kernels && omgf::resid_max(L.dev, PD, L.all_fast, slot, s))) omgk::resid(L.dev, PD, slot, s);
+        h->launches++;
+      } break;
       case S_RESTRICT: omgk::restrict2(h->L(st.l).dev, h->L(st.l - 1).dev, st.a, st.b, s); h->launches++; break;
       case S_RESID_RESTRICT: {
         LevelHost& L = h->L(st.l);
@@ -449,7 +454,11 @@ void exec_steps(omg_handle* h, Program& P) {
         }
         h->launches++;
       } break;
-      case S_CRHS: omgk::crhs(h->L(st.l).dev, PD, s); h->launches++; break;
+      case S_CRHS: {
+        LevelHost& L = h->L(st.l);
+        if (!(h->fast_kernels && omgf::crhs(L.dev, PD, L.all_fast, s))) omgk::crhs(L.dev, PD, s);
+        h->launches++;
+      } break;
       case S_OLDPL: omgk::oldpl(h->L(st.l).dev, PD, s); h->launches++; break;
       case S_CORR_PROLONG: {
         LevelHost& L = h->L(st.l);
@@ -702,7 +711,8 @@ void push_pull_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const doubl
   CK(cudaSetDevice(h->device));
   sync_meta(h);
   const int v = check_iv(h, iv);
-  if (lvl_lo < h->lowest || lvl_hi > h->highest || lvl_lo > lvl_hi) fail("packed transfer: level range out of bounds");
+  lvl_lo = std::max(lvl_lo, h->lowest); lvl_hi = std::min(lvl_hi, h->highest);
+  if (lvl_lo > lvl_hi) fail("packed transfer: empty level range");
   int64_t off = 0;
   for (int lvl = lvl_lo; lvl <= lvl_hi; ++lvl) {
     LevelHost& L = h->L(lvl);
@@ -740,6 +750,11 @@ int omg_create(int device, omg_handle** out) {
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return 3; }
   cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
   for (int v = 0; v < OMG_MAXV; ++v) for (int f = 0; f < 6; ++f) { h->bc_type[v][f] = -10; h->bc_value[v][f] = 0.0; }
+  // defaults of type(mg_t), src/m_data_structures.f90:300-327
+  h->params.operator_type = 1; h->params.smoother_type = 1; h->params.geometry_type = 1;
+  h->params.n_cycle_down = 2; h->params.n_cycle_up = 2; h->params.max_coarse_cycles = 1000;
+  h->params.residual_coarse_abs = 1e-8; h->params.residual_coarse_rel = 1e-8;
+  h->have_params = true;
   *out = h;
   return 0;
 }
@@ -831,7 +846,7 @@ int64_t omg_packed_size(omg_handle* h, int lvl_lo, int lvl_hi) {
 int omg_set_var_const(omg_handle* h, int iv, int lvl_lo, int lvl_hi, double value, int interior_only) {
   OMG_TRY(h, {
     CK(cudaSetDevice(h->device));
-    sync_meta(h);
+    if (!h->have_tree) fail("no tree: call omg_set_tree first");
     const int v = check_iv(h, iv);
     for (int lvl = std::max(lvl_lo, h->lowest); lvl <= std::min(lvl_hi, h->highest); ++lvl) {
       LevelHost& L = h->L(lvl);
@@ -870,6 +885,38 @@ int omg_fas_vcycles(omg_handle* h, int n, double* residuals) {
     if (want && n) CK(cudaMemcpyAsync(residuals, h->d_scal.p + SCAL_RESHIST, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1)); h->last_ms = ms;
+  });
+}
+
+// Run one building block of the cycle on its own (parity tests compare each against the oracle):
+// "smooth_boxes" (lvl, n_cycle)  src/m_multigrid.f90:404-424     "update_coarse" (lvl)  :347-384
+// "correct_children" (lvl)  :387-402 (+ the ghost fill that follows it)   "coarse_solve"  :202-208
+// "max_residual_lvl" (lvl) -> *out  :296-311
+int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* out) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    sync_meta(h);
+    check_supported(h);
+    const std::string w(what);
+    if (lvl < h->lowest || lvl > h->highest) fail("omg_debug_step: level out of range");
+    Program P;
+    for (int l = 0; l < OMG_NLVL; ++l) h->gz[l] = false;
+    Builder B{h, P, {}};
+    if (w == "smooth_boxes") B.smooth_boxes(lvl, arg);
+    else if (w == "update_coarse") { if (lvl <= h->lowest) fail("update_coarse: lvl <= lowest_lvl"); B.update_coarse(lvl); }
+    else if (w == "correct_children") { if (lvl >= h->highest) fail("correct_children: lvl >= highest_lvl"); B.correct_children_onto(lvl + 1); B.gf(lvl + 1); }
+    else if (w == "coarse_solve") {
+      const int sub = (h->params.smoother_type == 2) ? 2 : 1;
+      B.pend.push_back({TOP_COARSE_SOLVE, B.li(h->lowest), (h->params.n_cycle_up + h->params.n_cycle_down) * sub, h->params.max_coarse_cycles});
+    } else if (w == "max_residual_lvl") { B.step(S_CLEAR_SLOT, 0, SCAL_MAXRES); B.emit(lvl, TOP_RESID, S_RESID, SCAL_MAXRES); }
+    else fail("omg_debug_step: unknown step " + w);
+    B.flush();
+    const int ug = h->use_graph; h->use_graph = 0;
+    try { run_program(h, P); } catch (...) { h->use_graph = ug; P.d_ops.free(); throw; }
+    h->use_graph = ug;
+    CK(cudaStreamSynchronize(h->stream));
+    P.d_ops.free();
+    if (out) CK(cudaMemcpy(out, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost));
   });
 }
 

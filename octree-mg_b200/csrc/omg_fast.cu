@@ -1,7 +1,531 @@
-// omg_fast.cu -- tuned kernels (placeholder: general path is used until these land)
+// omg_fast.cu -- tuned sm_100a kernels for big uniform levels (box size 16 or 32, every ghost face of
+// every box FK_SAME or FK_PHYS).  One CTA per tile = (box, slab of KT k-planes).  The tile and its ghost
+// layer are staged in shared memory with TMA bulk copies (cp.async.bulk, completion on an mbarrier):
+// thanks to the colour-split layout a colour half-sweep needs exactly the OTHER colour of the box, which
+// is one contiguous 16 KiB block, plus 1 KiB (z) / 16 x 64 B (y) face slices of the neighbours' blocks.
+// The arithmetic is the same expression, in the same order, as the general path (omg_ops.cuh), so both
+// paths agree bitwise with each other and with the oracle.
 #include "omg_fast.h"
+
+#include <cstdint>
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// ---- mbarrier / TMA bulk-copy PTX ---------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+// global -> shared bulk copy (TMA, SASS UBLKCP); 16-byte aligned, size a multiple of 16
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void bc_coeffs(int type, double dr, int f, double& c0, double& c1, double& c2) {
+  // bc_to_gc, src/m_ghost_cells.f90:682-698
+  if (type == -10) { c0 = 2; c1 = -1; c2 = 0; }
+  else if (type == -11) { c0 = dr * ((f & 1) ? 1.0 : -1.0); c1 = 1; c2 = 0; }
+  else { c0 = 0; c1 = 2; c2 = -1; }
+}
+
+// =================================================================================================
+// GSRB colour half-sweep, Laplacian / Helmholtz (box_gs_lpl src/m_laplacian.f90:52-114, box_gs_helmh
+// src/m_helmholtz.f90:49-108) over all boxes of a level.
+//   reads : other colour of the tile (+ ghost layer), rhs of this colour      writes: this colour
+//   algorithmic bytes: 12 B per cell of the level per launch
+// Shared memory per CTA (NC=16, KT=16): 16 KiB tile + 6 KiB ghost layer.
+// =================================================================================================
+template <int NC, int KT>
+struct SmoothSmem {
+  static constexpr int HX = NC / 2;
+  double B[KT][NC][HX];     // other colour, dense as in global memory
+  double zlo[NC][HX], zhi[NC][HX];
+  double ylo[KT][HX], yhi[KT][HX];
+  double xg[KT][NC];        // the single x ghost each row needs (low side if the row's updated cells start at i=0, else high side)
+  uint64_t bar;
+};
+
+template <int NC, int KT>
+__global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
+                                                              const __grid_constant__ ParamsDev P, int colour) {
+  constexpr int HX = NC / 2;
+  constexpr int TILES = NC / KT;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SmoothSmem<NC, KT>& S = *reinterpret_cast<SmoothSmem<NC, KT>*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int b = blockIdx.x / TILES;
+  const int k0 = (blockIdx.x % TILES) * KT;
+  const int oc = colour ^ 1;
+  const double* __restrict__ phi = L.var[0];
+  const size_t boxoff = (size_t)b * L.bs;
+  const double* __restrict__ Bg = phi + boxoff + (size_t)oc * L.cs;     // other colour of this box
+  double* __restrict__ Ag = L.var[0] + boxoff + (size_t)colour * L.cs;  // colour being updated
+  const double* __restrict__ Rg = L.var[1] + boxoff + (size_t)colour * L.cs;
+
+  int kind[6], arg[6];
+#pragma unroll
+  for (int f = 0; f < 6; ++f) { kind[f] = L.fkind[b * 6 + f]; arg[f] = L.farg[b * 6 + f]; }
+  // z faces of an interior slab come from the box itself
+  const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
+
+  if (tid == 0) mbar_init(&S.bar, 1);
+  __syncthreads();
+
+  if (tid < 32) {
+    // ---- warp 0: all TMA bulk copies of this tile ----
+    if (tid == 0) {
+      uint32_t bytes = KT * NC * HX * 8;
+      if (zlo_in || kind[4] == FK_SAME) bytes += NC * HX * 8;
+      if (zhi_in || kind[5] == FK_SAME) bytes += NC * HX * 8;
+      if (kind[2] == FK_SAME) bytes += KT * HX * 8;
+      if (kind[3] == FK_SAME) bytes += KT * HX * 8;
+      mbar_arrive_expect_tx(&S.bar, bytes);
+      bulk_g2s(&S.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+    }
+    __syncwarp();
+    if (tid == 1) {
+      if (zlo_in) bulk_g2s(&S.zlo[0][0], Bg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
+      else if (kind[4] == FK_SAME) bulk_g2s(&S.zlo[0][0], phi + (size_t)arg[4] * L.bs + (size_t)oc * L.cs + (size_t)(NC - 1) * NC * HX, NC * HX * 8, &S.bar);
+    }
+    if (tid == 2) {
+      if (zhi_in) bulk_g2s(&S.zhi[0][0], Bg + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
+      else if (kind[5] == FK_SAME) bulk_g2s(&S.zhi[0][0], phi + (size_t)arg[5] * L.bs + (size_t)oc * L.cs, NC * HX * 8, &S.bar);
+    }
+    // y faces: one 8*HX-byte row per k-plane from the neighbour's row j = NC-1 (low) / j = 0 (high)
+    for (int q = tid; q < 2 * KT; q += 32) {
+      const int hi = q / KT, kk = q % KT;
+      if (kind[2 + hi] == FK_SAME) {
+        const double* src = phi + (size_t)arg[2 + hi] * L.bs + (size_t)oc * L.cs + ((size_t)(k0 + kk) * NC + (hi ? 0 : NC - 1)) * HX;
+        bulk_g2s(hi ? &S.yhi[kk][0] : &S.ylo[kk][0], src, HX * 8, &S.bar);
+      }
+    }
+  } else {
+    // ---- other warps: the x ghosts (one 8-byte value per row, strided in the neighbour) ----
+    for (int r = tid - 32; r < KT * NC; r += kThreads - 32) {
+      const int kk = r / NC, j = r % NC;
+      const int sA = colour ^ ((j + k0 + kk) & 1);     // 0: this row's updated cells are i = 0, 2, ..: needs i = -1
+      const int f = sA ? 1 : 0;
+      if (kind[f] == FK_SAME)
+        S.xg[kk][j] = phi[(size_t)arg[f] * L.bs + (size_t)oc * L.cs + ((size_t)(k0 + kk) * NC + j) * HX + (sA ? 0 : HX - 1)];
+    }
+  }
+
+  // rhs of this thread's cells (issued before the wait so that the loads overlap the bulk copies)
+  constexpr int PER = KT * NC * HX / kThreads;
+  double rhs[PER];
+#pragma unroll
+  for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)k0 * NC * HX + q * kThreads + tid];
+
+  mbar_wait(&S.bar, 0);
+  __syncthreads();
+
+  // ---- physical boundaries: ghost = c0*b + c1*phi(1) + c2*phi(2), evaluated like bc_to_gc ----
+  bool any_phys = false;
+#pragma unroll
+  for (int f = 0; f < 6; ++f) any_phys = any_phys || (kind[f] == FK_PHYS);
+  if (any_phys) {
+    for (int f = 0; f < 6; ++f) {
+      if (kind[f] != FK_PHYS) continue;
+      if (f == 4 && zlo_in) continue;
+      if (f == 5 && zhi_in) continue;
+      int type = L.ftype[b * 6 + f];
+      if (type == 0) type = P.bc_type[f];
+      double c0, c1, c2;
+      bc_coeffs(type, L.dr[f >> 1], f, c0, c1, c2);
+      const double* pl = arg[f] >= 0 ? L.bcpl + (size_t)arg[f] * NC * NC : nullptr;
+      const double bconst = P.bc_value[f];
+      if (f < 2) {
+        for (int r = tid; r < KT * NC; r += kThreads) {
+          const int kk = r / NC, j = r % NC, k = k0 + kk;
+          const int sA = colour ^ ((j + k) & 1);
+          if (sA != f) continue;                       // this row needs the other side
+          const int m = f ? HX - 1 : 0;
+          const double bv = pl ? pl[k * NC + j] : bconst;
+          S.xg[kk][j] = c0 * bv + c1 * Ag[((size_t)k * NC + j) * HX + m] + c2 * S.B[kk][j][m];
+        }
+      } else if (f < 4) {
+        const int j1 = (f & 1) ? NC - 1 : 0, j2 = (f & 1) ? NC - 2 : 1;
+        for (int r = tid; r < KT * HX; r += kThreads) {
+          const int kk = r / HX, m = r % HX, k = k0 + kk;
+          const int i = 2 * m + (colour ^ ((j1 + k) & 1));
+          const double bv = pl ? pl[k * NC + i] : bconst;
+          const double g = c0 * bv + c1 * Ag[((size_t)k * NC + j1) * HX + m] + c2 * S.B[kk][j2][m];
+          if (f & 1) S.yhi[kk][m] = g; else S.ylo[kk][m] = g;
+        }
+      } else {
+        const int k1 = (f & 1) ? NC - 1 : 0, kk1 = k1 - k0, kk2 = (f & 1) ? kk1 - 1 : kk1 + 1;
+        for (int r = tid; r < NC * HX; r += kThreads) {
+          const int j = r / HX, m = r % HX;
+          const int i = 2 * m + (colour ^ ((j + k1) & 1));
+          const double bv = pl ? pl[j * NC + i] : bconst;
+          const double g = c0 * bv + c1 * Ag[((size_t)k1 * NC + j) * HX + m] + c2 * S.B[kk2][j][m];
+          if (f & 1) S.zhi[j][m] = g; else S.zlo[j][m] = g;
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- update this colour ----
+  const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], fac = L.fac;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    const int idx = q * kThreads + tid;
+    const int m = idx % HX, j = (idx / HX) % NC, kk = idx / (HX * NC);
+    const int sA = colour ^ ((j + k0 + kk) & 1);
+    const int ml = m - 1 + sA, mh = m + sA;
+    const double xlo = ml >= 0 ? S.B[kk][j][ml] : S.xg[kk][j];
+    const double xhi = mh < HX ? S.B[kk][j][mh] : S.xg[kk][j];
+    const double ylo = j > 0 ? S.B[kk][j - 1][m] : S.ylo[kk][m];
+    const double yhi = j < NC - 1 ? S.B[kk][j + 1][m] : S.yhi[kk][m];
+    const double zlo = kk > 0 ? S.B[kk - 1][j][m] : S.zlo[j][m];
+    const double zhi = kk < KT - 1 ? S.B[kk + 1][j][m] : S.zhi[j][m];
+    Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - rhs[q]);
+  }
+}
+
+template <int NC, int KT>
+bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s) {
+  static bool configured = false;
+  const size_t smem = sizeof(SmoothSmem<NC, KT>);
+  if (!configured) {
+    if (cudaFuncSetAttribute(k_smooth_lpl_fast<NC, KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    configured = true;
+  }
+  k_smooth_lpl_fast<NC, KT><<<L.nb * (NC / KT), kThreads, smem, s>>>(L, P, colour);
+  return true;
+}
+
+
+// =================================================================================================
+// Both-colour staged stencil kernel, Laplacian / Helmholtz.  One thread per coarse cell = 2x2x2 fine cells
+// (so the restriction sum needs no exchange and uses the reference's element order).
+//   MODE_RESID_RESTRICT  residual_box + 2 x mg_restrict_lvl of update_coarse (src/m_multigrid.f90:355-363,
+//                        m_restrict.f90:165-214): res = rhs - L(phi) stored, phi and res restricted onto the
+//                        parent's octant.  26 B per fine cell (18 B + the stored fine residual).
+//   MODE_RESID_MAX       max_residual_lvl (:296-311): res stored, max |res| -> atomic max.  24 B per cell.
+//   MODE_CRHS            tail of update_coarse (:369-383) on parents: rhs = L(phi) + res, old = phi.  32 B.
+// =================================================================================================
+enum { MODE_RESID_RESTRICT = 0, MODE_RESID_MAX = 1, MODE_CRHS = 2 };
+
+template <int NC, int KT>
+struct StencilSmem {
+  static constexpr int HX = NC / 2;
+  double Ph[2][KT][NC][HX];
+  double zlo[2][NC][HX], zhi[2][NC][HX];
+  double ylo[2][KT][HX], yhi[2][KT][HX];
+  double xlo[KT][NC], xhi[KT][NC];
+  double red[32];
+  uint64_t bar;
+};
+
+template <int NC, int KT, int MODE, bool HELM>
+__global__ void __launch_bounds__(kThreads) k_stencil_fast(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
+                                                           const __grid_constant__ ParamsDev P, double* maxslot) {
+  constexpr int HX = NC / 2;
+  constexpr int TILES = NC / KT;
+  using SM = StencilSmem<NC, KT>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SM& S = *reinterpret_cast<SM*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int bq = blockIdx.x / TILES;
+  const int b = (MODE == MODE_CRHS) ? L.parents_list[bq] : bq;
+  const int k0 = (blockIdx.x % TILES) * KT;
+  const double* __restrict__ phi = L.var[0];
+  const size_t boxoff = (size_t)b * L.bs;
+
+  int kind[6], arg[6];
+#pragma unroll
+  for (int f = 0; f < 6; ++f) { kind[f] = L.fkind[b * 6 + f]; arg[f] = L.farg[b * 6 + f]; }
+  const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
+
+  if (tid == 0) mbar_init(&S.bar, 1);
+  __syncthreads();
+
+  if (tid == 0) {
+    uint32_t bytes = 2 * KT * NC * HX * 8;
+    if (zlo_in || kind[4] == FK_SAME) bytes += 2 * NC * HX * 8;
+    if (zhi_in || kind[5] == FK_SAME) bytes += 2 * NC * HX * 8;
+    mbar_arrive_expect_tx(&S.bar, bytes);
+    if (TILES == 1) bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff, 2 * KT * NC * HX * 8, &S.bar);   // whole box: one 32 KiB copy
+    else {
+      bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+      bulk_g2s(&S.Ph[1][0][0][0], phi + boxoff + L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+    }
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      if (zlo_in) bulk_g2s(&S.zlo[c][0][0], phi + boxoff + (size_t)c * L.cs + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
+      else if (kind[4] == FK_SAME) bulk_g2s(&S.zlo[c][0][0], phi + (size_t)arg[4] * L.bs + (size_t)c * L.cs + (size_t)(NC - 1) * NC * HX, NC * HX * 8, &S.bar);
+      if (zhi_in) bulk_g2s(&S.zhi[c][0][0], phi + boxoff + (size_t)c * L.cs + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
+      else if (kind[5] == FK_SAME) bulk_g2s(&S.zhi[c][0][0], phi + (size_t)arg[5] * L.bs + (size_t)c * L.cs, NC * HX * 8, &S.bar);
+    }
+  }
+  // y faces (rows j = NC-1 / 0 of the neighbours, both colours) and x faces (cells i = NC-1 / 0) by plain loads
+  for (int r = tid; r < 2 * 2 * KT * HX; r += kThreads) {
+    const int m = r % HX, kk = (r / HX) % KT, c = (r / (HX * KT)) & 1, hi = r / (2 * HX * KT);
+    if (kind[2 + hi] == FK_SAME) {
+      const double v = phi[(size_t)arg[2 + hi] * L.bs + (size_t)c * L.cs + ((size_t)(k0 + kk) * NC + (hi ? 0 : NC - 1)) * HX + m];
+      if (hi) S.yhi[c][kk][m] = v; else S.ylo[c][kk][m] = v;
+    }
+  }
+  for (int r = tid; r < 2 * KT * NC; r += kThreads) {
+    const int j = r % NC, kk = (r / NC) % KT, hi = r / (NC * KT);
+    if (kind[hi] == FK_SAME) {
+      const int k = k0 + kk, i = hi ? 0 : NC - 1;
+      const double v = phi[(size_t)arg[hi] * L.bs + (size_t)((i + j + k) & 1) * L.cs + ((size_t)k * NC + j) * HX + (i >> 1)];
+      if (hi) S.xhi[kk][j] = v; else S.xlo[kk][j] = v;
+    }
+  }
+  mbar_wait(&S.bar, 0);
+  __syncthreads();
+
+  auto inner = [&](int i, int j, int kk) -> double { return S.Ph[(i + j + k0 + kk) & 1][kk][j][i >> 1]; };
+
+  bool any_phys = false;
+#pragma unroll
+  for (int f = 0; f < 6; ++f) any_phys = any_phys || (kind[f] == FK_PHYS);
+  if (any_phys) {
+    for (int f = 0; f < 6; ++f) {
+      if (kind[f] != FK_PHYS) continue;
+      if (f == 4 && zlo_in) continue;
+      if (f == 5 && zhi_in) continue;
+      int type = L.ftype[b * 6 + f];
+      if (type == 0) type = P.bc_type[f];
+      double c0, c1, c2;
+      bc_coeffs(type, L.dr[f >> 1], f, c0, c1, c2);
+      const double* pl = arg[f] >= 0 ? L.bcpl + (size_t)arg[f] * NC * NC : nullptr;
+      const double bconst = P.bc_value[f];
+      const int n1 = (f & 1) ? NC - 1 : 0, n2 = (f & 1) ? NC - 2 : 1;
+      if (f < 2) {
+        for (int r = tid; r < KT * NC; r += kThreads) {
+          const int kk = r / NC, j = r % NC;
+          const double bv = pl ? pl[(k0 + kk) * NC + j] : bconst;
+          const double g = c0 * bv + c1 * inner(n1, j, kk) + c2 * inner(n2, j, kk);
+          if (f & 1) S.xhi[kk][j] = g; else S.xlo[kk][j] = g;
+        }
+      } else if (f < 4) {
+        for (int r = tid; r < KT * NC; r += kThreads) {
+          const int kk = r / NC, i = r % NC;
+          const double bv = pl ? pl[(k0 + kk) * NC + i] : bconst;
+          const double g = c0 * bv + c1 * inner(i, n1, kk) + c2 * inner(i, n2, kk);
+          const int c = (i + (f & 1 ? NC : -1) + k0 + kk) & 1;
+          if (f & 1) S.yhi[c][kk][i >> 1] = g; else S.ylo[c][kk][i >> 1] = g;
+        }
+      } else {
+        const int kk1 = n1 - k0, kk2 = n2 - k0;
+        for (int r = tid; r < NC * NC; r += kThreads) {
+          const int j = r / NC, i = r % NC;
+          const double bv = pl ? pl[j * NC + i] : bconst;
+          const double g = c0 * bv + c1 * inner(i, j, kk1) + c2 * inner(i, j, kk2);
+          const int c = (i + j + (f & 1 ? NC : -1)) & 1;
+          if (f & 1) S.zhi[c][j][i >> 1] = g; else S.zlo[c][j][i >> 1] = g;
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  // value at ghosted tile coordinates (one coordinate may leave the tile)
+  auto at = [&](int i, int j, int kk) -> double {
+    const int c = (i + j + k0 + kk) & 1;
+    if (i < 0) return S.xlo[kk][j];
+    if (i >= NC) return S.xhi[kk][j];
+    if (j < 0) return S.ylo[c][kk][i >> 1];
+    if (j >= NC) return S.yhi[c][kk][i >> 1];
+    if (kk < 0) return S.zlo[c][j][i >> 1];
+    if (kk >= KT) return S.zhi[c][j][i >> 1];
+    return S.Ph[c][kk][j][i >> 1];
+  };
+
+  const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], lambda = P.lambda;
+  const double* __restrict__ in1 = (MODE == MODE_CRHS ? L.var[3] : L.var[1]) + boxoff;   // res (crhs) or rhs
+  double* __restrict__ out1 = (MODE == MODE_CRHS ? L.var[1] : L.var[3]) + boxoff;        // rhs (crhs) or res
+  double* __restrict__ out2 = L.var[2] + boxoff;                                         // old (crhs)
+  double vmax = 0.0;
+  int p = -1, ox = 0, oy = 0, oz = 0;
+  if (MODE == MODE_RESID_RESTRICT) {
+    p = L.parent[b];
+    const int off = L.coff[b];
+    ox = off & 1023; oy = (off >> 10) & 1023; oz = (off >> 20) & 1023;
+  }
+  constexpr int HC = NC / 2, NCOARSE = (KT / 2) * HC * HC;
+#pragma unroll 1
+  for (int cidx_ = tid; cidx_ < NCOARSE; cidx_ += kThreads) {
+    const int I = cidx_ % HC, J = (cidx_ / HC) % HC, Kc = cidx_ / (HC * HC);
+    double sphi = 0.0, sres = 0.0;
+#pragma unroll
+    for (int dk = 0; dk < 2; ++dk)
+#pragma unroll
+      for (int dj = 0; dj < 2; ++dj)
+#pragma unroll
+        for (int di = 0; di < 2; ++di) {
+          const int i = 2 * I + di, j = 2 * J + dj, kk = 2 * Kc + dk;
+          const double u0 = at(i, j, kk);
+          double lap = idx2 * (at(i - 1, j, kk) + at(i + 1, j, kk) - 2 * u0) + idy2 * (at(i, j - 1, kk) + at(i, j + 1, kk) - 2 * u0) +
+                       idz2 * (at(i, j, kk - 1) + at(i, j, kk + 1) - 2 * u0);
+          if (HELM) lap = lap - lambda * u0;
+          const size_t g = (size_t)((di + dj + dk) & 1) * L.cs + ((size_t)(k0 + kk) * NC + j) * HX + I;
+          if (MODE == MODE_CRHS) {
+            out1[g] = lap + in1[g];
+            out2[g] = u0;
+          } else {
+            const double r = in1[g] - lap;
+            out1[g] = r;
+            if (MODE == MODE_RESID_MAX) vmax = fmax(vmax, fabs(r));
+            else { sphi = sphi + u0; sres = sres + r; }
+          }
+        }
+    if (MODE == MODE_RESID_RESTRICT && p >= 0) {
+      const int ic = ox + I, jc = oy + J, kc = oz + (k0 >> 1) + Kc;
+      const size_t gc = (size_t)p * Lc.bs + (size_t)((ic + jc + kc) & 1) * Lc.cs + ((size_t)kc * NC + jc) * HX + (ic >> 1);
+      Lc.var[0][gc] = 0.125 * sphi;
+      Lc.var[3][gc] = 0.125 * sres;
+    }
+  }
+  if (MODE == MODE_RESID_MAX) {
+    for (int o = 16; o > 0; o >>= 1) vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    if ((tid & 31) == 0) S.red[tid >> 5] = vmax;
+    __syncthreads();
+    if (tid < 32) {
+      vmax = tid < kThreads / 32 ? S.red[tid] : 0.0;
+      for (int o = 16; o > 0; o >>= 1) vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+      if (tid == 0) atomicMax(reinterpret_cast<unsigned long long*>(maxslot), (unsigned long long)__double_as_longlong(vmax));
+    }
+  }
+}
+
+template <int NC, int KT, int MODE, bool HELM>
+bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+  static bool configured = false;
+  const size_t smem = sizeof(StencilSmem<NC, KT>);
+  if (!configured) {
+    if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    configured = true;
+  }
+  k_stencil_fast<NC, KT, MODE, HELM><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot);
+  return true;
+}
+
+template <int MODE>
+bool dispatch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+  const bool helm = (P.op == OP_HELMH);
+  if (L.nc == 16) return helm ? launch_stencil<16, 16, MODE, true>(L, Lc, P, nboxes, maxslot, s) : launch_stencil<16, 16, MODE, false>(L, Lc, P, nboxes, maxslot, s);
+  if (L.nc == 32) return helm ? launch_stencil<32, 8, MODE, true>(L, Lc, P, nboxes, maxslot, s) : launch_stencil<32, 8, MODE, false>(L, Lc, P, nboxes, maxslot, s);
+  return false;
+}
+
+
+// =================================================================================================
+// correct_children fused with mg_prolong / mg_prolong_sparse (src/m_multigrid.f90:387-402,
+// src/m_prolong.f90:124-156, :159-240), seen from the fine box: the (NC/2+2)^3 patch of the correction
+// phi_c - old_c around the child's octant is staged in shared memory (ghost values through cell_at, so any
+// face kind works), then every thread prolongs coarse cells onto 2x2x2 fine cells and adds them to phi.
+//   18 B per fine cell (read + write phi_f, 1/8 of phi_c and old_c) + 1 B for the stored coarse res.
+// =================================================================================================
+template <int NC>
+__global__ void __launch_bounds__(kThreads) k_corr_prolong_fast(const __grid_constant__ LevelDev Lf, const __grid_constant__ LevelDev Lc,
+                                                                const __grid_constant__ ParamsDev P) {
+  constexpr int HC = NC / 2, HX = NC / 2, PW = HC + 2;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* corr = reinterpret_cast<double*>(smem_raw);       // [PW][PW][PW]
+  const int tid = threadIdx.x, b = blockIdx.x;
+  const int p = Lf.parent[b];
+  if (p < 0) return;
+  const int off = Lf.coff[b];
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  for (int r = tid; r < PW * PW * PW; r += kThreads) {
+    const int a = r % PW, bb = (r / PW) % PW, c = r / (PW * PW);
+    const int nedge = (a == 0 || a == PW - 1) + (bb == 0 || bb == PW - 1) + (c == 0 || c == PW - 1);
+    if (nedge > 1) continue;                                   // never read by the 7-point prolongation
+    const int ic = ox + a - 1, jc = oy + bb - 1, kc = oz + c - 1;
+    const double v = cell_at<GM_PHI>(Lc, P, Lc.var[0], nullptr, p, ic, jc, kc) - cell_at<GM_OLD>(Lc, P, Lc.var[2], nullptr, p, ic, jc, kc);
+    corr[r] = v;
+    if (nedge == 0) Lc.var[3][(size_t)p * Lc.bs + cidx(Lc, ic, jc, kc)] = v;   // res_c = phi_c - old_c on the parent (:396-398)
+  }
+  __syncthreads();
+  double* __restrict__ phi = Lf.var[0] + (size_t)b * Lf.bs;
+#pragma unroll 1
+  for (int r = tid; r < HC * HC * HC; r += kThreads) {
+    const int I = r % HC, J = (r / HC) % HC, K = r / (HC * HC);
+    const int q = ((K + 1) * PW + (J + 1)) * PW + (I + 1);
+    const double f0 = 0.25 * corr[q];
+    const double flx = 0.25 * corr[q - 1], fhx = 0.25 * corr[q + 1];
+    const double fly = 0.25 * corr[q - PW], fhy = 0.25 * corr[q + PW];
+    const double flz = 0.25 * corr[q - PW * PW], fhz = 0.25 * corr[q + PW * PW];
+#pragma unroll
+    for (int dk = 0; dk < 2; ++dk)
+#pragma unroll
+      for (int dj = 0; dj < 2; ++dj)
+#pragma unroll
+        for (int di = 0; di < 2; ++di) {
+          const double fine = f0 + (di ? fhx : flx) + (dj ? fhy : fly) + (dk ? fhz : flz);
+          const size_t g = (size_t)((di + dj + dk) & 1) * Lf.cs + ((size_t)(2 * K + dk) * NC + (2 * J + dj)) * HX + I;
+          phi[g] = phi[g] + fine;
+        }
+  }
+}
+
+template <int NC>
+bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s) {
+  static bool configured = false;
+  const size_t smem = sizeof(double) * (NC / 2 + 2) * (NC / 2 + 2) * (NC / 2 + 2);
+  if (!configured) {
+    if (cudaFuncSetAttribute(k_corr_prolong_fast<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    configured = true;
+  }
+  k_corr_prolong_fast<NC><<<Lf.nb, kThreads, smem, s>>>(Lf, Lc, P);
+  return true;
+}
+
+}  // namespace
+
 namespace omgf {
-bool smooth(const LevelDev&, const ParamsDev&, int, bool, cudaStream_t) { return false; }
-bool resid_restrict(const LevelDev&, const LevelDev&, const ParamsDev&, bool, cudaStream_t) { return false; }
-bool corr_prolong(const LevelDev&, const LevelDev&, const ParamsDev&, bool, cudaStream_t) { return false; }
+
+bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, cudaStream_t s) {
+  if (!all_fast || L.nb == 0) return false;
+  if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  if (L.nc == 16) return launch_smooth<16, 16>(L, P, colour, s);
+  if (L.nc == 32) return launch_smooth<32, 8>(L, P, colour, s);
+  return false;
+}
+bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s) {
+  if (!all_fast || Lf.nb == 0 || Lc.nc != Lf.nc) return false;
+  if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  return dispatch_stencil<MODE_RESID_RESTRICT>(Lf, Lc, P, Lf.nb, nullptr, s);
+}
+bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s) {
+  if (!all_fast || L.nb == 0 || !maxslot) return false;
+  if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  return dispatch_stencil<MODE_RESID_MAX>(L, L, P, L.nb, maxslot, s);
+}
+bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s) {
+  if (!all_fast || L.n_parents == 0) return false;
+  if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  return dispatch_stencil<MODE_CRHS>(L, L, P, L.n_parents, nullptr, s);
+}
+bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool, cudaStream_t s) {
+  if (Lf.nb == 0 || Lc.nc != Lf.nc) return false;
+  if (Lf.nc == 16) return launch_corr_prolong<16>(Lf, Lc, P, s);
+  if (Lf.nc == 32) return launch_corr_prolong<32>(Lf, Lc, P, s);
+  return false;
+}
+
 }  // namespace omgf

@@ -8,5 +8,7 @@
 namespace omgf {
 bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, cudaStream_t s);
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s);
+bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s);
+bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s);
 bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool coarse_all_fast, cudaStream_t s);
 }  // namespace omgf

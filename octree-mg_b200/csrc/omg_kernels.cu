@@ -139,6 +139,17 @@ __global__ void k_scale_scalar(double* acc, double inv_volume) { *acc = *acc / i
 
 // ------------------------------------------------------------------ tail interpreter ---------
 template <int OP>
+__device__ void tail_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
+  if (L.nc & 1) {   // odd box size: Jacobi between boxes, see do_smooth_staged
+    for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 0, tid, nthr);
+    __syncthreads();
+    for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 1, tid, nthr);
+  } else {
+    for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, colour, tid, nthr);
+  }
+}
+
+template <int OP>
 __device__ void tail_run(const LevelDev* __restrict__ levels, const ParamsDev& P, const TailOp* __restrict__ ops, int n_ops,
                          double* scal, double* red) {
   const int tid = threadIdx.x, nthr = blockDim.x;
@@ -147,7 +158,7 @@ __device__ void tail_run(const LevelDev* __restrict__ levels, const ParamsDev& P
     const LevelDev& L = levels[op.l];
     switch (op.type) {
       case TOP_SMOOTH:
-        for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, op.a, tid, nthr);
+        tail_smooth<OP>(L, P, op.a, tid, nthr);
         break;
       case TOP_RESID: {
         double m = 0.0;
@@ -185,7 +196,7 @@ __device__ void tail_run(const LevelDev* __restrict__ levels, const ParamsDev& P
         int it = 0;
         for (int i = 1; i <= op.b; ++i) {
           for (int n = 1; n <= op.a; ++n) {
-            for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, (n - 1) & 1, tid, nthr);
+            tail_smooth<OP>(L, P, (n - 1) & 1, tid, nthr);
             __syncthreads();
           }
           m = 0.0;

@@ -16,6 +16,23 @@ __device__ void do_smooth(const LevelDev& L, const ParamsDev& P, int b, int colo
   }
 }
 
+// Odd box sizes (only possible on the coarsest level, e.g. 1^3 boxes): the local red-black colouring no
+// longer matches across boxes, so a half-sweep reads neighbour cells of the colour being updated.  The
+// reference reads them from ghost cells filled BEFORE the half-sweep (Jacobi between boxes), so the new
+// values are staged in the res variable (scratch at this point of the coarse solve) and committed after
+// a barrier.  phase 0: compute into res; phase 1: commit.
+template <int OP>
+__device__ void do_smooth_staged(const LevelDev& L, const ParamsDev& P, int b, int colour, int phase, int tid, int nthr) {
+  double* phi = L.var[0];
+  double* tmp = L.var[3];
+  for (int idx = tid; idx < L.cs; idx += nthr) {
+    int i, j, k;
+    if (!decode_colour(L, colour, idx, i, j, k)) continue;
+    const size_t g = (size_t)b * L.bs + colour * L.cs + idx;
+    if (phase == 0) tmp[g] = gs_at<OP>(L, P, b, i, j, k); else phi[g] = tmp[g];
+  }
+}
+
 // residual_box src/m_multigrid.f90:426-436; returns the thread-local max |res|
 template <int OP>
 __device__ double do_resid(const LevelDev& L, const ParamsDev& P, int b, int tid, int nthr) {

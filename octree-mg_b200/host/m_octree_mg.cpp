@@ -510,6 +510,8 @@ static void transfer(mg_t& mg, int iv, bool push, bool with_ghosts, int lvl_lo, 
 void mg_gpu_push(mg_t& mg, int iv) { transfer(mg, iv, true, false, mg_lvl_lo, mg_lvl_hi); }
 void mg_gpu_pull(mg_t& mg, int iv, bool with_ghosts) { transfer(mg, iv, false, with_ghosts, mg_lvl_lo, mg_lvl_hi); }
 
+void mg_gpu_push_params(mg_t& mg) { push_params(mg); }
+
 static int n_eps_vars(const mg_t& mg) {
   return (mg.operator_type == mg_vlaplacian || mg.operator_type == mg_vhelmholtz) ? 1 : (mg.operator_type == mg_ahelmholtz ? 3 : 0);
 }
@@ -621,6 +623,7 @@ int omgh_get_int(void* h, const char* key) {
   if (k == "n_extra_vars") return mg.n_extra_vars; if (k == "n_cpu") return mg.n_cpu; if (k == "my_rank") return mg.my_rank;
   if (k == "subtract_mean") return mg.subtract_mean; if (k == "n_smoother_substeps") return mg.n_smoother_substeps;
   if (k == "phi_bc_data_stored") return mg.phi_bc_data_stored;
+  if (k == "gpu_resident") return mg.gpu_resident;
   return -999999;
 }
 int omgh_set_real(void* h, const char* key, double v) {
@@ -697,5 +700,6 @@ int omgh_restrict(void* h, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_restr
 int omgh_prolong(void* h, int lvl, int iv, int iv_to, int add) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_prolong(w->mg, lvl, iv, iv_to, add != 0)); }
 int omgh_gpu_push(void* h, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_gpu_push(w->mg, iv)); }
 int omgh_gpu_pull(void* h, int iv, int with_ghosts) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_gpu_pull(w->mg, iv, with_ghosts != 0)); }
+int omgh_gpu_push_params(void* h) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_gpu_push_params(w->mg)); }
 int omgh_gpu_push_bc(void* h) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_gpu_push_bc(w->mg)); }
 }  // extern "C"

@@ -140,6 +140,7 @@ void mg_prolong(mg_t& mg, int lvl, int iv, int iv_to, bool add);
 // ---- host <-> device coherence ------------------------------------------------------
 void mg_gpu_push(mg_t& mg, int iv);                       // all levels, owned boxes
 void mg_gpu_pull(mg_t& mg, int iv, bool with_ghosts = true);
+void mg_gpu_push_params(mg_t& mg);                        // mg_t scalars, bc constants (+ planes when dirty)
 void mg_gpu_push_bc(mg_t& mg);                            // evaluate boundary_cond callbacks -> device planes
 
 }  // namespace omg

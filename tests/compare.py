@@ -10,6 +10,13 @@ def face_slices(nc):
     return [(s, s, 0), (s, s, nc + 1), (s, 0, s), (s, nc + 1, s), (0, s, s), (nc + 1, s, s)]
 
 
+def _maxdiff(a, b):
+    """max |a - b|; any NaN / inf on either side counts as an infinite difference"""
+    if not (np.isfinite(a).all() and np.isfinite(b).all()):
+        return float("inf")
+    return float(np.abs(a - b).max())
+
+
 def assert_trees_equal(a, b):
     assert a.lowest_lvl == b.lowest_lvl and a.highest_lvl == b.highest_lvl
     assert a.first_normal_lvl == b.first_normal_lvl and a.n_boxes == b.n_boxes
@@ -36,11 +43,11 @@ def state_diff(orc, mg, variables=(1, 2, 3, 4), ghosts_of=(1,), levels=None, ids
             for id_ in (ids_of(lvl) if ids_of else orc.ids(lvl)):
                 a = orc.cc(id_, nc)[iv - 1]
                 b = mg.cc(id_, nc)[iv - 1]
-                d = max(d, float(np.abs(a[1:-1, 1:-1, 1:-1] - b[1:-1, 1:-1, 1:-1]).max()))
+                d = max(d, _maxdiff(a[1:-1, 1:-1, 1:-1], b[1:-1, 1:-1, 1:-1]))
                 m = max(m, float(np.abs(a[1:-1, 1:-1, 1:-1]).max()))
                 if iv in ghosts_of:
                     for sl in face_slices(nc):
-                        d = max(d, float(np.abs(a[sl] - b[sl]).max()))
+                        d = max(d, _maxdiff(a[sl], b[sl]))
         out[VAR_NAMES.get(iv, "var%d" % iv)] = (d, m)
     return out
 

@@ -125,10 +125,13 @@ def test_periodic_subtract_mean(oracle, product):
         return mg
     orc, mg = build(oracle.OracleMg), build(product.Mg)
     assert orc.get_int("subtract_mean") == 1 and mg.get_int("subtract_mean") == 1
+    rhs_norm = max(float(np.abs(orc.cc(i)[P.mg_irhs - 1]).max()) for i in orc.ids(orc.highest_lvl))
     for fmg in (True, False):
         h_o, h_g = P.run_cycles(orc, 3, fmg), P.run_cycles(mg, 3, fmg)
         for a, b in zip(h_o, h_g):
-            assert abs(a - b) <= RES_RTOL * max(abs(a), h_o[0])
+            # a mean that differs in the last bit moves every residual by ~eps * |phi| / h^2: below that floor
+            # the relative test is meaningless (SURVEY.md 8d "parity procedure")
+            assert abs(a - b) <= max(RES_RTOL * abs(a), 1e-12 * rhs_norm)
     d = state_diff(orc, mg, variables=(1,), ghosts_of=())["phi"]
     assert d[0] <= 1e-12 * d[1]
 

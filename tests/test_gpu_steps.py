@@ -1,0 +1,78 @@
+"""Per-kernel GPU parity: every building block of the cycle (smooth_boxes, update_coarse = residual +
+restriction + coarse rhs, correct_children = correction + prolongation, max_residual_lvl) run on its own on
+seeded random states and compared bitwise with the oracle, level by level."""
+import numpy as np
+import pytest
+
+import problems as P
+from compare import assert_state_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def randomize(mg, seed, variables=(1, 2, 3, 4)):
+    rng = np.random.default_rng(seed)
+    for lvl, id_ in P.all_ids(mg):
+        cc = mg.cc(id_)
+        for iv in variables:
+            cc[iv - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal(cc[0, 1:-1, 1:-1, 1:-1].shape)
+
+
+def prepare(oracle, product, n, box, op=P.mg_laplacian, bc="callback", lam=0.0, seed=7):
+    orc, _ = P.uniform_problem(oracle.OracleMg, n, box, operator_type=op, bc=bc, lam=lam)
+    mg, _ = P.uniform_problem(product.Mg, n, box, operator_type=op, bc=bc, lam=lam)
+    for m in (orc, mg):
+        randomize(m, seed)
+    # make the oracle's stored ghost cells consistent with the interiors: old(:) = phi(:) of a first random
+    # field (ghosts included), then a second random field in phi
+    orc.mg_fill_ghost_cells(P.mg_iphi)
+    for lvl, id_ in P.all_ids(orc):
+        c_o, c_g = orc.cc(id_), mg.cc(id_)
+        c_o[P.mg_iold - 1] = c_o[P.mg_iphi - 1]
+        c_g[P.mg_iold - 1] = c_g[P.mg_iphi - 1]
+    randomize(orc, seed + 1, variables=(1,))
+    randomize(mg, seed + 1, variables=(1,))
+    orc.mg_fill_ghost_cells(P.mg_iphi)
+    return orc, mg
+
+
+CASES = [(32, 8, P.mg_laplacian, "callback", 0.0), ((48, 48, 48), 8, P.mg_laplacian, "callback", 0.0),
+         ((32, 64, 96), 16, P.mg_helmholtz, "mixed", 1.0), (32, 8, P.mg_vlaplacian, "mixed", 0.0)]
+
+
+@pytest.mark.parametrize("n,box,op,bc,lam", CASES)
+def test_smooth_boxes_every_level(oracle, product, n, box, op, bc, lam):
+    orc, mg = prepare(oracle, product, n, box, op, bc, lam)
+    for lvl in range(orc.highest_lvl, orc.lowest_lvl - 1, -1):
+        orc.smooth_boxes(lvl, 2)
+        mg.smooth_boxes(lvl, 2)
+        assert_state_equal(orc, mg, variables=(1,), levels=[lvl])
+
+
+@pytest.mark.parametrize("n,box,op,bc,lam", CASES)
+def test_update_coarse_every_level(oracle, product, n, box, op, bc, lam):
+    orc, mg = prepare(oracle, product, n, box, op, bc, lam)
+    for lvl in range(orc.highest_lvl, orc.lowest_lvl, -1):
+        orc.update_coarse(lvl)
+        mg.update_coarse(lvl)
+        assert_state_equal(orc, mg, variables=(4,), ghosts_of=(), levels=[lvl])           # fine residual
+        assert_state_equal(orc, mg, variables=(1, 2, 3, 4), ghosts_of=(1, 3), levels=[lvl - 1])
+
+
+@pytest.mark.parametrize("n,box,op,bc,lam", CASES)
+def test_correct_children_every_level(oracle, product, n, box, op, bc, lam):
+    orc, mg = prepare(oracle, product, n, box, op, bc, lam)
+    for lvl in range(orc.lowest_lvl, orc.highest_lvl):
+        orc.correct_children(lvl)
+        orc.mg_fill_ghost_cells_lvl(lvl + 1, P.mg_iphi)
+        mg.correct_children(lvl)
+        assert_state_equal(orc, mg, variables=(1,), levels=[lvl + 1])
+        assert_state_equal(orc, mg, variables=(4,), ghosts_of=(), levels=[lvl])          # res = phi - old on parents
+
+
+@pytest.mark.parametrize("n,box,op,bc,lam", CASES)
+def test_max_residual_every_level(oracle, product, n, box, op, bc, lam):
+    orc, mg = prepare(oracle, product, n, box, op, bc, lam)
+    for lvl in range(orc.lowest_lvl, orc.highest_lvl + 1):
+        assert orc.max_residual_lvl(lvl) == mg.max_residual_lvl(lvl)
+        assert_state_equal(orc, mg, variables=(4,), ghosts_of=(), levels=[lvl])
