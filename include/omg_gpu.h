@@ -126,8 +126,15 @@ int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* ou
 /* ---- multi-GPU (replaces mg_comm_init + sort_and_transfer_buffers, src/m_communication.f90) */
 int omg_nccl_unique_id(char out[128]);
 int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks);
-/* Emulated ranks inside one process / one GPU (tests): handles exchange through device copies. */
+/* Emulated ranks inside one process (one host thread per rank; parity tests on a single GPU): the handles
+ * exchange through device copies ordered by CUDA events.  handles[r] must hold the tree of rank r. */
 int omg_comm_init_local(omg_handle* const* handles, int nranks);
+/* The static exchange plan, computable without a device: keys (2 * key + kind) of the items rank `me` sends to /
+ * receives from `peer` in phase 0 (ghost cells, key 6*id + face, src/m_ghost_cells.f90:374-379), 1 (restriction,
+ * key 8*parent + child, src/m_restrict.f90:158-160) or 2 (prolongation, key child id, src/m_prolong.f90:116-118)
+ * on level lvl, in message order.  At most cap keys are written; the counts are always returned. */
+int omg_exchange_plan(const omg_tree_desc* t, int me, int phase, int lvl, int peer, int64_t* send_keys,
+                      int64_t* recv_keys, int cap, int* n_send, int* n_recv);
 
 /* ---- diagnostics ----------------------------------------------------------- */
 int omg_sync(omg_handle* h);                                          /* cudaStreamSynchronize */

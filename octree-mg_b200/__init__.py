@@ -65,6 +65,10 @@ def libs():
         p_host = os.path.join(HERE, "libomg_host.so")
         if not (os.path.exists(p_cuda) and os.path.exists(p_host)):
             raise MgError("native libraries missing: run `python octree-mg_b200/build.py` (there is no CPU fallback)")
+        # one NCCL per process: bind the copy PyTorch ships (if any) so that both can live together
+        nccl = os.path.join(os.path.dirname(os.path.dirname(np.__file__)), "nvidia", "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(nccl):
+            os.environ.setdefault("OMG_NCCL_LIB", nccl)
         G = C.CDLL(p_cuda, mode=C.RTLD_GLOBAL)
         Hh = C.CDLL(p_host)
         _declare(G, Hh)
@@ -101,6 +105,8 @@ def _declare(G, H):
     G.omg_nccl_unique_id.argtypes = [C.c_char_p]
     G.omg_comm_init.argtypes = [vp, C.c_char_p, ci, ci]
     G.omg_comm_init_local.argtypes = [C.POINTER(vp), ci]
+    G.omg_exchange_plan.argtypes = [C.POINTER(omg_tree_desc), ci, ci, ci, ci, C.POINTER(C.c_int64), C.POINTER(C.c_int64), ci,
+                                    C.POINTER(ci), C.POINTER(ci)]
     G.omg_sync.argtypes = [vp]
     G.omg_stat.restype = C.c_int64
     G.omg_stat.argtypes = [vp, C.c_char_p]
@@ -315,6 +321,39 @@ class Mg:
         self.H.omgh_tree_export(self.h, out.ctypes.data_as(C.POINTER(C.c_int)))
         return out
 
+    def tree_desc(self):
+        """(omg_tree_desc, keepalive): the flattened tree mg_allocate_storage hands to omg_set_tree; needs no device."""
+        t = np.ascontiguousarray(self.tree_export())
+        n = t.shape[0]
+        cols = dict(rank=t[:, 0], lvl=t[:, 1], ix=t[:, 2:5], parent=t[:, 5], children=t[:, 6:14], neighbors=t[:, 14:20])
+        keep = {k: np.ascontiguousarray(v, dtype=np.int32) for k, v in cols.items()}
+        ptr, ids = [0] * 42, []
+        for lvl in range(-20, 21):
+            if self.lowest_lvl <= lvl <= self.highest_lvl:
+                ids += self.ids(lvl)
+            ptr[lvl + 20 + 1] = len(ids)
+        keep["lvl_ptr"] = np.array(ptr, dtype=np.int32)
+        keep["lvl_ids"] = np.array(ids, dtype=np.int32)
+        keep["bsl"] = np.array([self.box_size_lvl(l) for l in range(-20, 21)], dtype=np.int32)
+        keep["dr"] = np.array([self.dr(l) for l in range(-20, 21)], dtype=np.float64)
+        p32 = lambda a: a.ctypes.data_as(C.POINTER(C.c_int32))
+        d = omg_tree_desc(n, self.box_size, self.lowest_lvl, self.highest_lvl, self.first_normal_lvl,
+                          self.get_int("my_rank"), self.get_int("n_cpu"), self.n_extra_vars, (C.c_int32 * 3)(0, 0, 0),
+                          p32(keep["bsl"]), keep["dr"].ctypes.data_as(C.POINTER(C.c_double)), p32(keep["rank"]),
+                          p32(keep["lvl"]), p32(keep["ix"]), p32(keep["parent"]), p32(keep["children"]),
+                          p32(keep["neighbors"]), p32(keep["lvl_ptr"]), p32(keep["lvl_ids"]))
+        return d, keep
+
+    def exchange_plan(self, phase, lvl, peer, me=None):
+        """(send_keys, recv_keys) of the static exchange plan (omg_exchange_plan); phase 0 ghost, 1 restrict, 2 prolong."""
+        d, keep = self.tree_desc()
+        me = self.get_int("my_rank") if me is None else me
+        ns, nr = C.c_int(0), C.c_int(0)
+        self.G.omg_exchange_plan(C.byref(d), me, phase, lvl, peer, None, None, 0, C.byref(ns), C.byref(nr))
+        sk, rk = (C.c_int64 * max(ns.value, 1))(), (C.c_int64 * max(nr.value, 1))()
+        self.G.omg_exchange_plan(C.byref(d), me, phase, lvl, peer, sk, rk, max(ns.value, nr.value, 1), C.byref(ns), C.byref(nr))
+        return list(sk[:ns.value]), list(rk[:nr.value])
+
     def box_info(self, id_):
         if self._tree is None:
             self._tree = self.tree_export()
@@ -430,3 +469,87 @@ class Mg:
 
     def max_residual_lvl(self, lvl):
         return self._step("max_residual_lvl", lvl)
+
+
+class MgGroup:
+    """n emulated ranks inside one process, for the parity tests on a single GPU (omg_comm_init_local).
+
+    Every method call is forwarded to the Mg of every rank, one host thread per rank (the cycle's exchange
+    steps meet at a host barrier); results must agree on all ranks.  `cc(id)` / `ids(lvl)` give the global
+    view the oracle has, so that the same comparison helpers work."""
+
+    def __init__(self, n_cpu, operator_type=mg_laplacian, smoother_type=mg_smoother_gsrb, n_extra_vars=0, device=0, **kw):
+        self.n = n_cpu
+        self.ranks = [Mg(operator_type, smoother_type, n_extra_vars=n_extra_vars, n_cpu=n_cpu, my_rank=r, device=device, **kw)
+                      for r in range(n_cpu)]
+        self._owner = None
+
+    def _all(self, fn):
+        import threading
+        out, err = [None] * self.n, [None] * self.n
+
+        def run(r):
+            try:
+                out[r] = fn(self.ranks[r])
+            except BaseException as e:      # noqa: BLE001 - re-raised below
+                err[r] = e
+        ts = [threading.Thread(target=run, args=(r,)) for r in range(self.n)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        for e in err:
+            if e is not None:
+                raise e
+        return out
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+        attr = getattr(type(self.ranks[0]), name, None)
+        if isinstance(attr, property):
+            return getattr(self.ranks[0], name)
+
+        def call(*a, **k):
+            res = self._all(lambda m: getattr(m, name)(*a, **k))
+            if isinstance(res[0], (int, float, str, list, tuple, type(None))):
+                assert all(r == res[0] for r in res), "ranks disagree on %s: %r" % (name, res)
+            return res[0]
+        return call
+
+    @property
+    def highest_lvl(self):
+        return self.ranks[0].highest_lvl
+
+    @highest_lvl.setter
+    def highest_lvl(self, v):
+        for m in self.ranks:
+            m.highest_lvl = v
+
+    def mg_allocate_storage(self):
+        for m in self.ranks:
+            m.mg_allocate_storage()
+        hs = (C.c_void_p * self.n)(*[m.gpu for m in self.ranks])
+        if self.ranks[0].G.omg_comm_init_local(hs, self.n) != 0:
+            raise MgError(self.ranks[0].G.omg_last_error(self.ranks[0].gpu).decode())
+        self._owner = None
+
+    def owner(self, id_):
+        if self._owner is None:
+            self._owner = self.ranks[0].tree_export()[:, 0]
+        return self.ranks[int(self._owner[id_ - 1])]
+
+    def cc(self, id_, nc=None):
+        return self.owner(id_).cc(id_, nc)
+
+    def my_ids(self, lvl):
+        return self.ranks[0].ids(lvl)
+
+    def ids(self, lvl):
+        return self.ranks[0].ids(lvl)
+
+    def leaves(self, lvl):
+        return self.ranks[0].leaves(lvl)
+
+    def stat(self, key):
+        return sum(m.stat(key) for m in self.ranks)

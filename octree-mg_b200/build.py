@@ -18,7 +18,7 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-ccbin", "/usr/bin/g++"]
-CU_SOURCES = ["omg_core.cu", "omg_kernels.cu", "omg_fast.cu", "omg_comm.cu"]
+CU_SOURCES = ["omg_core.cu", "omg_kernels.cu", "omg_fast.cu", "omg_comm.cu", "omg_plan.cpp"]
 LIB_CUDA = os.path.join(HERE, "libomg_b200.so")
 LIB_HOST = os.path.join(HERE, "libomg_host.so")
 
@@ -52,7 +52,7 @@ def build(force=False, verbose=False):
     objs = []
     for src in CU_SOURCES:
         s = os.path.join(CSRC, src)
-        o = os.path.join(BUILD, src.replace(".cu", ".o"))
+        o = os.path.join(BUILD, os.path.splitext(src)[0] + ".o")
         objs.append(o)
         if force or _newer(o, [s] + hdrs):
             jobs.append([NVCC] + NVCC_FLAGS + ["-c", s, "-o", o] + (["-Xptxas", "-v"] if verbose else []))
@@ -62,7 +62,7 @@ def build(force=False, verbose=False):
         for o in outs:
             print(o)
     if force or jobs or _newer(LIB_CUDA, objs):
-        _run([NVCC, "-shared", "-o", LIB_CUDA] + objs + ["-L/usr/lib/x86_64-linux-gnu", "-lnccl", "-lcudart"])
+        _run([NVCC, "-shared", "-o", LIB_CUDA] + objs + ["-lcudart", "-ldl"])
     host_src = os.path.join(HOST, "m_octree_mg.cpp")
     if force or _newer(LIB_HOST, [host_src, os.path.join(HOST, "m_octree_mg.hpp"), LIB_CUDA] + hdrs):
         _run(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", LIB_HOST, host_src,

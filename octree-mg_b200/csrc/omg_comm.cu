@@ -1,11 +1,223 @@
-// omg_comm.cu -- placeholder until the NCCL exchange lands (single-rank builds never call these)
+// omg_comm.cu -- transport back ends (see omg_comm.h): NCCL send/recv groups over NVLink, and an
+// in-process emulation of several ranks for single-GPU parity tests.
 #include "omg_comm.h"
-struct omg_comm { int dummy; };
-int omg_comm_unique_id(char out[128]) { for (int i = 0; i < 128; ++i) out[i] = 0; return 1; }
-void omg_comm_destroy(omg_comm*) {}
-bool omg_comm_graph_safe(omg_comm*) { return false; }
-void omg_comm_halo(omg_comm*, int, cudaStream_t) {}
-void omg_comm_restrict(omg_comm*, int, cudaStream_t) {}
-void omg_comm_prolong(omg_comm*, int, cudaStream_t) {}
-void omg_comm_allreduce_max(omg_comm*, double*, cudaStream_t) {}
-void omg_comm_allreduce_sum(omg_comm*, double*, cudaStream_t) {}
+
+#include <chrono>
+#include <condition_variable>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include <dlfcn.h>
+#include <nccl.h>   // types only: the library is loaded at run time (see nccl_api)
+
+namespace {
+[[noreturn]] void cfail(const std::string& m) { throw std::runtime_error(m); }
+
+// NCCL is bound with dlopen when the first communicator is made, not at link time: a process that also uses
+// PyTorch must end up with ONE libnccl.so.2 (torch ships its own, newer than the system one, and fails to
+// import if an older copy is already mapped).  OMG_NCCL_LIB names the file; default: the soname, which
+// resolves to a copy that is already loaded, else to the system library.
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+const NcclApi& nccl_api() {
+  static NcclApi api;
+  static std::once_flag once;
+  static std::string err;
+  std::call_once(once, [] {
+    const char* path = getenv("OMG_NCCL_LIB");
+    void* lib = dlopen(path && *path ? path : "libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!lib) { err = std::string("cannot load NCCL: ") + dlerror(); return; }
+    auto sym = [&](const char* n) { void* p = dlsym(lib, n); if (!p && err.empty()) err = std::string("NCCL symbol missing: ") + n; return p; };
+    api.GetUniqueId = (decltype(api.GetUniqueId))sym("ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))sym("ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
+    api.GroupStart = (decltype(api.GroupStart))sym("ncclGroupStart");
+    api.GroupEnd = (decltype(api.GroupEnd))sym("ncclGroupEnd");
+    api.Send = (decltype(api.Send))sym("ncclSend");
+    api.Recv = (decltype(api.Recv))sym("ncclRecv");
+    api.AllReduce = (decltype(api.AllReduce))sym("ncclAllReduce");
+    api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
+  });
+  if (!err.empty()) cfail(err);
+  return api;
+}
+#define CCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) cfail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+#define NCK(call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) cfail(std::string(#call) + ": " + nccl_api().GetErrorString(r_)); } while (0)
+
+__global__ void k_reduce_slots(const double* __restrict__ slots, int n, int op, double* out) {
+  // fixed rank order: every rank computes the same bits
+  double v = slots[0];
+  for (int r = 1; r < n; ++r) v = (op == OMG_RED_MAX) ? fmax(v, slots[r]) : v + slots[r];
+  *out = v;
+}
+}  // namespace
+
+struct omg_local_group {
+  int n = 0, refs = 0;
+  std::mutex m;
+  std::condition_variable cv;
+  int count = 0;
+  unsigned long gen = 0;
+  bool broken = false;
+  std::vector<omg_comm*> comms;
+
+  // all emulated ranks meet here; a rank that failed (or never arrives) breaks the group instead of hanging it
+  void barrier() {
+    std::unique_lock<std::mutex> lk(m);
+    if (broken) cfail("local rank group is broken (another emulated rank failed)");
+    const unsigned long my = gen;
+    if (++count == n) { count = 0; ++gen; cv.notify_all(); return; }
+    if (!cv.wait_for(lk, std::chrono::seconds(120), [&] { return gen != my || broken; })) {
+      broken = true; cv.notify_all();
+      cfail("local rank group: barrier timed out (ranks must call the same operations)");
+    }
+    if (broken && gen == my) cfail("local rank group is broken (another emulated rank failed)");
+  }
+  void abort_group() { std::lock_guard<std::mutex> lk(m); broken = true; cv.notify_all(); }
+};
+
+struct omg_comm {
+  int rank = 0, n = 1, device = 0;
+  ncclComm_t nccl = nullptr;
+  omg_local_group* g = nullptr;
+  // local back end
+  std::vector<OmgXfer> pub;                 // segments of the exchange in flight, visible to the peers
+  cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
+  double* d_stage = nullptr;                // my contribution to an allreduce
+  double* d_gather = nullptr;               // [n] contributions of all ranks
+};
+
+int omg_comm_unique_id(char out[128]) {
+  static_assert(sizeof(ncclUniqueId) <= 128, "ncclUniqueId larger than the ABI buffer");
+  ncclUniqueId id;
+  try { if (nccl_api().GetUniqueId(&id) != ncclSuccess) return 1; } catch (...) { return 2; }
+  std::memset(out, 0, 128);
+  std::memcpy(out, &id, sizeof(id));
+  return 0;
+}
+
+omg_comm* omg_comm_create_nccl(const char uid[128], int rank, int nranks, int device) {
+  CCK(cudaSetDevice(device));
+  ncclUniqueId id;
+  std::memcpy(&id, uid, sizeof(id));
+  omg_comm* c = new omg_comm();
+  c->rank = rank; c->n = nranks; c->device = device;
+  ncclResult_t r;
+  try { r = nccl_api().CommInitRank(&c->nccl, nranks, id, rank); } catch (...) { delete c; throw; }
+  if (r != ncclSuccess) { delete c; cfail(std::string("ncclCommInitRank: ") + nccl_api().GetErrorString(r)); }
+  return c;
+}
+
+omg_local_group* omg_local_group_create(int nranks) {
+  omg_local_group* g = new omg_local_group();
+  g->n = nranks; g->comms.assign(nranks, nullptr);
+  return g;
+}
+
+omg_comm* omg_comm_create_local(omg_local_group* g, int rank, int device) {
+  CCK(cudaSetDevice(device));
+  omg_comm* c = new omg_comm();
+  c->rank = rank; c->n = g->n; c->device = device; c->g = g;
+  CCK(cudaEventCreateWithFlags(&c->ev_ready, cudaEventDisableTiming));
+  CCK(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
+  CCK(cudaMalloc(&c->d_stage, sizeof(double)));
+  CCK(cudaMalloc(&c->d_gather, sizeof(double) * g->n));
+  std::lock_guard<std::mutex> lk(g->m);
+  g->comms[rank] = c; g->refs++;
+  return c;
+}
+
+void omg_comm_destroy(omg_comm* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->nccl) nccl_api().CommDestroy(c->nccl);
+  if (c->g) {
+    c->g->abort_group();                    // a group cannot continue without one of its ranks
+    if (c->ev_ready) cudaEventDestroy(c->ev_ready);
+    if (c->ev_done) cudaEventDestroy(c->ev_done);
+    if (c->d_stage) cudaFree(c->d_stage);
+    if (c->d_gather) cudaFree(c->d_gather);
+    bool last;
+    { std::lock_guard<std::mutex> lk(c->g->m); c->g->comms[c->rank] = nullptr; last = (--c->g->refs == 0); }
+    if (last) delete c->g;
+  }
+  delete c;
+}
+
+int omg_comm_rank(const omg_comm* c) { return c->rank; }
+int omg_comm_size(const omg_comm* c) { return c->n; }
+bool omg_comm_graph_safe(const omg_comm* c) { return c->nccl != nullptr; }
+
+void omg_comm_exchange(omg_comm* c, const OmgXfer* segs, int nsegs, cudaStream_t s) {
+  if (c->nccl) {
+    // sort_and_transfer_buffers: Isend + Irecv per peer, then Waitall (src/m_communication.f90:48-64);
+    // here one fused group on the stream, completion is stream order
+    const NcclApi& N = nccl_api();
+    if (nsegs == 0) return;
+    NCK(N.GroupStart());
+    for (int i = 0; i < nsegs; ++i) {
+      if (segs[i].send_n) NCK(N.Send(segs[i].send, segs[i].send_n, ncclDouble, segs[i].peer, c->nccl, s));
+      if (segs[i].recv_n) NCK(N.Recv(segs[i].recv, segs[i].recv_n, ncclDouble, segs[i].peer, c->nccl, s));
+    }
+    NCK(N.GroupEnd());
+    return;
+  }
+  omg_local_group* g = c->g;
+  try {
+    c->pub.assign(segs, segs + nsegs);
+    CCK(cudaEventRecord(c->ev_ready, s));                    // my send buffers are packed once this fires
+    g->barrier();
+    for (int i = 0; i < nsegs; ++i) {
+      if (!segs[i].recv_n) continue;
+      omg_comm* p = g->comms[segs[i].peer];
+      if (!p) cfail("local exchange: peer rank is gone");
+      const OmgXfer* src = nullptr;
+      for (const OmgXfer& x : p->pub) if (x.peer == c->rank) src = &x;
+      if (!src || src->send_n != segs[i].recv_n) cfail("local exchange: send/recv plans of two ranks do not match");
+      CCK(cudaStreamWaitEvent(s, p->ev_ready, 0));
+      CCK(cudaMemcpyAsync(segs[i].recv, src->send, segs[i].recv_n * sizeof(double), cudaMemcpyDefault, s));
+    }
+    CCK(cudaEventRecord(c->ev_done, s));                     // I have read my peers' send buffers
+    g->barrier();
+    for (int i = 0; i < nsegs; ++i)
+      if (segs[i].send_n && g->comms[segs[i].peer]) CCK(cudaStreamWaitEvent(s, g->comms[segs[i].peer]->ev_done, 0));
+    g->barrier();                                            // events may be re-recorded only after everyone waited on them
+  } catch (...) { g->abort_group(); throw; }
+}
+
+void omg_comm_allreduce(omg_comm* c, double* d_val, int op, cudaStream_t s) {
+  if (c->nccl) {
+    NCK(nccl_api().AllReduce(d_val, d_val, 1, ncclDouble, op == OMG_RED_MAX ? ncclMax : ncclSum, c->nccl, s));
+    return;
+  }
+  omg_local_group* g = c->g;
+  try {
+    CCK(cudaMemcpyAsync(c->d_stage, d_val, sizeof(double), cudaMemcpyDeviceToDevice, s));
+    CCK(cudaEventRecord(c->ev_ready, s));
+    g->barrier();
+    for (int r = 0; r < c->n; ++r) {
+      omg_comm* p = g->comms[r];
+      if (!p) cfail("local allreduce: peer rank is gone");
+      CCK(cudaStreamWaitEvent(s, p->ev_ready, 0));
+      CCK(cudaMemcpyAsync(c->d_gather + r, p->d_stage, sizeof(double), cudaMemcpyDefault, s));
+    }
+    k_reduce_slots<<<1, 1, 0, s>>>(c->d_gather, c->n, op, d_val);
+    CCK(cudaEventRecord(c->ev_done, s));
+    g->barrier();
+    for (int r = 0; r < c->n; ++r) if (g->comms[r]) CCK(cudaStreamWaitEvent(s, g->comms[r]->ev_done, 0));
+    g->barrier();
+  } catch (...) { g->abort_group(); throw; }
+}

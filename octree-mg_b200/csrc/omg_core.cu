@@ -19,6 +19,7 @@
 #include "omg_comm.h"
 #include "omg_fast.h"
 #include "omg_kernels.h"
+#include "omg_plan.h"
 
 namespace {
 
@@ -45,8 +46,21 @@ enum StepKind : int {
 };
 struct Step { int kind, l, a, b, c; };
 
+// One communication phase of one level: per-peer segments (in items) and the pack / unpack descriptor lists
+struct PhasePlan {
+  struct Seg { int peer, send_off, send_n, recv_off, recv_n; };
+  std::vector<Seg> seg;
+  int n_send = 0, n_recv = 0;
+  bool any = false;                     // some rank has traffic in this phase on this level (same on all ranks)
+  std::vector<int> h_sdesc, h_rdesc;
+  DevBuf<int> d_sdesc, d_rdesc;
+  DevBuf<double> d_send, d_recv;
+  void free() { d_sdesc.free(); d_rdesc.free(); d_send.free(); d_recv.free(); }
+};
+
 struct LevelHost {
   int lvl = 0, nc = 0, nb = 0;
+  PhasePlan xg, xr, xp;                 // ghost (onto this level), restrict (from this level), prolong (onto this level)
   bool tail = false;
   std::vector<int> ids;                 // owned boxes (global ids) in lvls(lvl)%my_ids order
   std::vector<int> h_fkind, h_farg, h_ftype, h_fkind_old, h_farg_old, h_parent, h_coff, h_parents, h_leaves,
@@ -90,7 +104,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 32768;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 32768, graph_multi = 1;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -99,7 +113,7 @@ struct omg_handle {
   size_t stage_doubles = 0; int stage_boxes = 0;
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
   // stats / timers
-  int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0;
+  int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0, exchanges = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_ms = 0.0;
   omg_comm* comm = nullptr;
@@ -124,6 +138,7 @@ void free_levels(omg_handle* h) {
     L.d_parent.free(); L.d_coff.free(); L.d_parents.free(); L.d_leaves.free(); L.d_rb.free(); L.d_oldpl.free();
     L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free();
     for (int v = 0; v < OMG_MAXV; ++v) { L.d_var[v].free(); L.d_faces[v].free(); }
+    L.xg.free(); L.xr.free(); L.xp.free();
   }
   h->levels.clear();
   h->d_levels.free();
@@ -189,9 +204,53 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
     }
   }
 
+  // which (phase, level) pairs carry traffic on ANY rank: decided from the replicated tree, so every rank
+  // emits the same exchange steps
+  if (h->n_cpu > 1) {
+    for (int id = 1; id <= h->n_boxes; ++id) {
+      const int lvl = h->blvl[id - 1];
+      if (lvl < h->lowest || lvl > h->highest) continue;
+      LevelHost& L = h->L(lvl);
+      const int r = h->rank[id - 1], p = h->parent[id - 1];
+      if (p > 0 && h->rank[p - 1] != r) { L.xr.any = true; L.xp.any = true; }
+      for (int f = 0; f < 6; ++f) {
+        const int nbid = h->neighbors[(size_t)(id - 1) * 6 + f];
+        if (nbid > 0) { if (h->rank[nbid - 1] != r) L.xg.any = true; }
+        else if (nbid == 0 && p > 0) {
+          const int cnb = h->neighbors[(size_t)(p - 1) * 6 + f];
+          if (cnb > 0 && h->rank[cnb - 1] != r) L.xg.any = true;
+        }
+      }
+    }
+  }
+  auto coff_of = [&](int id, int lvl) {
+    if (lvl <= h->first_normal) return 0;
+    int off[3];
+    for (int d = 0; d < 3; ++d) off[d] = ((h->ix[(size_t)(id - 1) * 3 + d] - 1) & 1) * (h->box_size >> 1);
+    return off[0] | (off[1] << 10) | (off[2] << 20);
+  };
+
   for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
     LevelHost& L = h->L(lvl);
     const int nb = L.nb, nc = L.nc;
+    // ghost-phase plan: planes received from peer ranks go straight into the plane pool, one contiguous
+    // run per peer (same-level faces first, then interpolated coarse faces), see omg_plan.h
+    std::map<std::pair<int, int>, int> remote_plane;
+    if (L.xg.any) {
+      omgp::LevelPlan pl = omgp::build_plan(*t, me, omgp::PH_GHOST, lvl);
+      int soff = 0, roff = 0;
+      for (const omgp::PeerPlan& pp : pl.peers) {
+        L.xg.seg.push_back({pp.peer, soff, (int)pp.send.size(), roff, (int)pp.recv.size()});
+        for (const omgp::Item& it : pp.recv) remote_plane[{it.box, it.face}] = roff++;
+        for (const omgp::Item& it : pp.send) {
+          L.xg.h_sdesc.push_back(it.kind); L.xg.h_sdesc.push_back(h->loc[it.src]); L.xg.h_sdesc.push_back(it.face);
+          L.xg.h_sdesc.push_back(it.kind == omgp::IT_RB ? coff_of(it.box, lvl) : 0);
+          ++soff;
+        }
+      }
+      L.xg.n_send = soff; L.xg.n_recv = roff;
+      L.n_gpl = roff;
+    }
     L.h_fkind.assign((size_t)nb * 6, FK_NONE); L.h_farg.assign((size_t)nb * 6, -1); L.h_ftype.assign((size_t)nb * 6, 0);
     L.h_fkind_old.assign((size_t)nb * 6, FK_NONE); L.h_farg_old.assign((size_t)nb * 6, -1);
     L.h_parent.assign(nb, -1); L.h_coff.assign(nb, 0);
@@ -202,11 +261,7 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
       (is_parent ? L.h_parents : L.h_leaves).push_back(b);
       const int p = h->parent[id - 1];
       if (p > 0 && h->rank[p - 1] == me) L.h_parent[b] = h->loc[p];
-      if (lvl > h->first_normal) {
-        int off[3];
-        for (int d = 0; d < 3; ++d) off[d] = ((h->ix[(size_t)(id - 1) * 3 + d] - 1) & 1) * (h->box_size >> 1);
-        L.h_coff[b] = off[0] | (off[1] << 10) | (off[2] << 20);
-      }
+      L.h_coff[b] = coff_of(id, lvl);
       for (int f = 0; f < 6; ++f) {
         const int nbid = h->neighbors[(size_t)(id - 1) * 6 + f];
         const size_t q = (size_t)b * 6 + f;
@@ -217,8 +272,7 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
             else { L.h_fkind_old[q] = FK_PLANE; L.h_farg_old[q] = L.n_gpl_old;
                    L.h_oldpl.push_back(b); L.h_oldpl.push_back(f); L.h_oldpl.push_back(L.n_gpl_old++); }
           } else {
-            L.h_fkind[q] = FK_PLANE; L.h_farg[q] = L.n_gpl++;   // remote face: filled by the halo exchange
-            L.all_fast = false;
+            L.h_fkind[q] = FK_PLANE; L.h_farg[q] = remote_plane.at({id, f});   // filled by the halo exchange
             if (is_parent) { L.h_fkind_old[q] = FK_PLANE; L.h_farg_old[q] = L.n_gpl_old;
                              L.h_oldpl.push_back(b); L.h_oldpl.push_back(f); L.h_oldpl.push_back(L.n_gpl_old++); }
           }
@@ -226,16 +280,41 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
           if (p <= 0) fail("omg_set_tree: refinement boundary on a box without parent");
           const int cnb = h->neighbors[(size_t)(p - 1) * 6 + f];
           if (cnb <= 0) fail("omg_set_tree: refinement boundary without coarse neighbour (tree not 2:1 balanced)");
-          const int cb = (h->rank[cnb - 1] == me) ? h->loc[cnb] : -1;
+          const int cb = (h->rank[cnb - 1] == me) ? h->loc[cnb] : -(2 + remote_plane.at({id, f}));
           L.h_fkind[q] = FK_PLANE; L.h_farg[q] = L.n_gpl;
           L.h_rb.push_back(b); L.h_rb.push_back(f); L.h_rb.push_back(cb); L.h_rb.push_back(L.n_gpl++);
-          L.all_fast = false;
         } else {
           L.h_fkind[q] = FK_PHYS; L.h_farg[q] = -1; L.h_ftype[q] = (nbid == -1) ? 0 : nbid;
           L.h_fkind_old[q] = FK_PHYS; L.h_farg_old[q] = -1;
         }
       }
     }
+    // restrict (children on this level -> parents on lvl-1) and prolong (parents on lvl-1 -> children here)
+    if (L.xr.any) {
+      omgp::LevelPlan pl = omgp::build_plan(*t, me, omgp::PH_RESTRICT, lvl);
+      int soff = 0, roff = 0;
+      for (const omgp::PeerPlan& pp : pl.peers) {
+        L.xr.seg.push_back({pp.peer, soff, (int)pp.send.size(), roff, (int)pp.recv.size()});
+        for (const omgp::Item& it : pp.send) { L.xr.h_sdesc.push_back(h->loc[it.src]); ++soff; }
+        for (const omgp::Item& it : pp.recv) { L.xr.h_rdesc.push_back(h->loc[it.box]); L.xr.h_rdesc.push_back(coff_of(it.src, lvl)); ++roff; }
+      }
+      L.xr.n_send = soff; L.xr.n_recv = roff;
+      const size_t item = (size_t)2 * (nc / 2) * (nc / 2) * (nc / 2);
+      L.xr.d_send.alloc(soff * item); L.xr.d_recv.alloc(roff * item);
+    }
+    if (L.xp.any) {
+      omgp::LevelPlan pl = omgp::build_plan(*t, me, omgp::PH_PROLONG, lvl);
+      int soff = 0, roff = 0;
+      for (const omgp::PeerPlan& pp : pl.peers) {
+        L.xp.seg.push_back({pp.peer, soff, (int)pp.send.size(), roff, (int)pp.recv.size()});
+        for (const omgp::Item& it : pp.send) { L.xp.h_sdesc.push_back(h->loc[it.src]); L.xp.h_sdesc.push_back(coff_of(it.box, lvl)); ++soff; }
+        for (const omgp::Item& it : pp.recv) L.h_parent[h->loc[it.box]] = -(2 + roff++);
+      }
+      L.xp.n_send = soff; L.xp.n_recv = roff;
+      const size_t item = (size_t)(nc / 2 + 2) * (nc / 2 + 2) * (nc / 2 + 2);
+      L.xp.d_send.alloc(soff * item); L.xp.d_recv.alloc(roff * item);
+    }
+    if (L.xg.any) L.xg.d_send.alloc((size_t)L.xg.n_send * nc * nc);
     // storage: mg_allocate_storage zero-fills every variable (src/m_allocate_storage.f90:72-76)
     const int hx = (nc + 1) / 2;
     const size_t bs = (size_t)2 * nc * nc * hx;
@@ -286,13 +365,15 @@ void sync_meta(omg_handle* h) {
       L.d_parents.upload(L.h_parents, s); L.d_leaves.upload(L.h_leaves, s);
       L.d_rb.upload(L.h_rb, s); L.d_oldpl.upload(L.h_oldpl, s);
       L.d_bcpl.upload(L.h_bcpl, s);
+      for (PhasePlan* X : {&L.xg, &L.xr, &L.xp}) { X->d_sdesc.upload(X->h_sdesc, s); X->d_rdesc.upload(X->h_rdesc, s); }
+      if (L.xp.d_recv.n) CK(cudaMemsetAsync(L.xp.d_recv.p, 0, L.xp.d_recv.n * sizeof(double), s));
       L.meta_dirty = false;
     }
     for (int v = 0; v < OMG_MAXV; ++v) { D.var[v] = L.d_var[v].p; D.faces[v] = L.d_faces[v].p; }
     D.fkind = L.d_fkind.p; D.farg = L.d_farg.p; D.ftype = L.d_ftype.p;
     D.fkind_old = L.d_fkind_old.p; D.farg_old = L.d_farg_old.p;
     D.gpl = L.d_gpl.p; D.gpl_old = L.d_gpl_old.p; D.bcpl = L.d_bcpl.p;
-    D.parent = L.d_parent.p; D.coff = L.d_coff.p;
+    D.parent = L.d_parent.p; D.coff = L.d_coff.p; D.ppatch = L.xp.d_recv.p;
     D.parents_list = L.d_parents.p; D.n_parents = (int)L.h_parents.size();
     D.leaves_list = L.d_leaves.p; D.n_leaves = (int)L.h_leaves.size();
     D.rb_list = L.d_rb.p; D.n_rb = (int)L.h_rb.size() / 4;
@@ -332,7 +413,7 @@ struct Builder {
 
   // mg_fill_ghost_cells_lvl(lvl, mg_iphi): only ghost values with remote inputs are materialised
   void gf(int lvl) {
-    if (multi() && lvl >= h->first_normal) step(S_HALO, lvl);
+    if (h->L(lvl).xg.any) step(S_HALO, lvl, (lvl > h->lowest && h->gz[lvl - 1 - OMG_LVL_LO]) ? 1 : 0);
     if (!h->L(lvl).h_rb.empty()) emit(lvl, TOP_RB_FILL, S_RB_FILL, h->gz[lvl - 1 - OMG_LVL_LO] ? 1 : 0);
     h->gz[lvl - OMG_LVL_LO] = false;
   }
@@ -343,20 +424,20 @@ struct Builder {
   }
   // update_coarse :347-384
   void update_coarse(int lvl) {
-    const bool fuse = !h->L(lvl).tail && !multi();
+    const bool fuse = !h->L(lvl).tail;
     if (fuse) step(S_RESID_RESTRICT, lvl);
     else {
       emit(lvl, TOP_RESID, S_RESID, -1);
       emit(lvl, TOP_RESTRICT, S_RESTRICT, IPHI, IRES);
     }
-    if (multi() && lvl >= h->first_normal) step(S_XRESTRICT, lvl);
+    if (h->L(lvl).xr.any) step(S_XRESTRICT, lvl, IPHI, IRES);
     gf(lvl - 1);
     emit(lvl - 1, TOP_CRHS, S_CRHS);
     if (!h->L(lvl - 1).h_oldpl.empty()) emit(lvl - 1, TOP_OLDPL, S_OLDPL);
   }
   // correct_children(lvl-1) :387-402, prolonging onto lvl
   void correct_children_onto(int lvl) {
-    if (multi() && lvl - 1 >= h->first_normal - 1) step(S_XPROLONG, lvl);
+    if (h->L(lvl).xp.any) step(S_XPROLONG, lvl);
     emit(lvl, TOP_CORR_PROLONG, S_CORR_PROLONG);
   }
   void subtract_mean(int iv, int with_ghosts) { step(S_SUBMEAN, 0, iv, with_ghosts); }
@@ -400,6 +481,46 @@ struct Builder {
 };
 
 // ---- executor ------------------------------------------------------------------------------------
+void need_comm(omg_handle* h) {
+  if (!h->comm) fail("several ranks but no communicator: call omg_comm_init (mg_comm_init) after omg_set_tree");
+  if (omg_comm_size(h->comm) != h->n_cpu || omg_comm_rank(h->comm) != h->my_rank) fail("communicator rank/size differ from mg%my_rank / mg%n_cpu");
+}
+
+void run_exchange(omg_handle* h, const PhasePlan& X, const double* send, double* recv, size_t item, cudaStream_t s) {
+  need_comm(h);
+  std::vector<OmgXfer> segs;
+  for (const PhasePlan::Seg& g : X.seg)
+    segs.push_back({g.peer, send + (size_t)g.send_off * item, (size_t)g.send_n * item, recv + (size_t)g.recv_off * item, (size_t)g.recv_n * item});
+  try { omg_comm_exchange(h->comm, segs.data(), (int)segs.size(), s); }
+  catch (const std::exception& e) { fail(e.what()); }
+  h->exchanges++;
+}
+
+// mg_fill_ghost_cells_lvl, communication part (src/m_ghost_cells.f90:142-168): faces owned by other ranks
+// arrive directly in this level's plane pool
+void exchange_ghost(omg_handle* h, int lvl, int gz, cudaStream_t s) {
+  LevelHost& L = h->L(lvl);
+  const LevelDev& Lc = lvl > h->lowest ? h->L(lvl - 1).dev : L.dev;
+  if (L.xg.n_send) { omgk::pack_ghost(L.dev, Lc, h->pdev, L.xg.d_sdesc.p, L.xg.n_send, L.xg.d_send.p, gz, s); h->launches++; }
+  run_exchange(h, L.xg, L.xg.d_send.p, L.d_gpl.p, (size_t)L.nc * L.nc, s);
+}
+// mg_restrict_lvl, communication part (src/m_restrict.f90:94-108); both variables of update_coarse in one message
+void exchange_restrict(omg_handle* h, int lvl, int iv0, int iv1, cudaStream_t s) {
+  LevelHost& L = h->L(lvl);
+  const int hn = L.nc / 2;
+  const size_t item = (size_t)(iv1 >= 0 ? 2 : 1) * hn * hn * hn;
+  if (L.xr.n_send) { omgk::pack_restrict(L.dev, L.xr.d_sdesc.p, L.xr.n_send, L.xr.d_send.p, iv0, iv1, s); h->launches++; }
+  run_exchange(h, L.xr, L.xr.d_send.p, L.xr.d_recv.p, item, s);
+  if (L.xr.n_recv) { omgk::unpack_restrict(h->L(lvl - 1).dev, L.xr.d_rdesc.p, L.xr.n_recv, L.xr.d_recv.p, hn, iv0, iv1, s); h->launches++; }
+}
+// mg_prolong, communication part (src/m_prolong.f90:65-78): coarse correction patches instead of fine blocks
+void exchange_prolong(omg_handle* h, int lvl, cudaStream_t s) {
+  LevelHost& L = h->L(lvl);
+  const int pw = L.nc / 2 + 2;
+  if (L.xp.n_send) { omgk::pack_prolong(h->L(lvl - 1).dev, h->pdev, L.xp.d_sdesc.p, L.xp.n_send, L.xp.d_send.p, L.nc, s); h->launches++; }
+  run_exchange(h, L.xp, L.xp.d_send.p, L.xp.d_recv.p, (size_t)pw * pw * pw, s);
+}
+
 void run_submean(omg_handle* h, int iv, int with_ghosts) {
   // subtract_mean + get_sum, src/m_multigrid.f90:245-294
   cudaStream_t s = h->stream;
@@ -413,7 +534,7 @@ void run_submean(omg_handle* h, int iv, int with_ghosts) {
     omgk::final_sum(h->d_partial.p, (int)L.h_leaves.size(), acc, s);
     h->launches += 2;
   }
-  if (h->n_cpu > 1) omg_comm_allreduce_sum(h->comm, acc, s);
+  if (h->n_cpu > 1) { need_comm(h); omg_comm_allreduce(h->comm, acc, OMG_RED_SUM, s); }
   if (1 >= h->lowest && 1 <= h->highest) {
     LevelHost& L1 = h->L(1);
     const double nc = (double)(h->box_size * h->box_size * h->box_size);
@@ -477,10 +598,10 @@ void exec_steps(omg_handle* h, Program& P) {
       case S_SUBMEAN: run_submean(h, st.a, st.b); break;
       case S_CLEAR_SLOT: CK(cudaMemsetAsync(h->d_scal.p + st.a, 0, sizeof(double), s)); break;
       case S_COPY_SLOT: CK(cudaMemcpyAsync(h->d_scal.p + st.a, h->d_scal.p + st.b, sizeof(double), cudaMemcpyDeviceToDevice, s)); break;
-      case S_HALO: omg_comm_halo(h->comm, st.l, s); break;
-      case S_XRESTRICT: omg_comm_restrict(h->comm, st.l, s); break;
-      case S_XPROLONG: omg_comm_prolong(h->comm, st.l, s); break;
-      case S_ALLREDUCE_MAX: omg_comm_allreduce_max(h->comm, h->d_scal.p + st.a, s); break;
+      case S_HALO: exchange_ghost(h, st.l, st.a, s); break;
+      case S_XRESTRICT: exchange_restrict(h, st.l, st.a, st.b, s); break;
+      case S_XPROLONG: exchange_prolong(h, st.l, s); break;
+      case S_ALLREDUCE_MAX: need_comm(h); omg_comm_allreduce(h->comm, h->d_scal.p + st.a, OMG_RED_MAX, s); break;
       default: fail("exec_steps: unknown step");
     }
     if (prof) { CK(cudaEventRecord(pe1, s)); h->prof_events.push_back({st.kind, {pe0, pe1}}); }
@@ -493,7 +614,7 @@ void run_program(omg_handle* h, Program& P) {
     P.d_ops.upload(P.ops, h->stream);
     CK(cudaStreamSynchronize(h->stream));
   }
-  const bool graph_ok = h->use_graph && !h->profile && (h->n_cpu == 1 || omg_comm_graph_safe(h->comm));
+  const bool graph_ok = h->use_graph && !h->profile && (h->n_cpu == 1 || (h->comm && h->graph_multi && omg_comm_graph_safe(h->comm)));
   if (!graph_ok) { exec_steps(h, P); return; }
   if (!P.graph) {
     cudaGraph_t g = nullptr;
@@ -908,7 +1029,10 @@ int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* ou
     else if (w == "coarse_solve") {
       const int sub = (h->params.smoother_type == 2) ? 2 : 1;
       B.pend.push_back({TOP_COARSE_SOLVE, B.li(h->lowest), (h->params.n_cycle_up + h->params.n_cycle_down) * sub, h->params.max_coarse_cycles});
-    } else if (w == "max_residual_lvl") { B.step(S_CLEAR_SLOT, 0, SCAL_MAXRES); B.emit(lvl, TOP_RESID, S_RESID, SCAL_MAXRES); }
+    } else if (w == "max_residual_lvl") {
+      B.step(S_CLEAR_SLOT, 0, SCAL_MAXRES); B.emit(lvl, TOP_RESID, S_RESID, SCAL_MAXRES);
+      if (B.multi()) B.step(S_ALLREDUCE_MAX, 0, SCAL_MAXRES);
+    }
     else fail("omg_debug_step: unknown step " + w);
     B.flush();
     const int ug = h->use_graph; h->use_graph = 0;
@@ -929,7 +1053,7 @@ int omg_fill_ghost_cells_lvl(omg_handle* h, int lvl, int iv) {
     if (lvl > h->highest) fail("fill_ghost_cells_lvl: lvl > highest_lvl");
     LevelHost& L = h->L(lvl);
     if (v == IPHI) {
-      if (h->n_cpu > 1 && lvl >= h->first_normal) omg_comm_halo(h->comm, lvl, h->stream);
+      if (L.xg.any) exchange_ghost(h, lvl, 0, h->stream);
       if (!L.h_rb.empty()) omgk::rb_fill(L.dev, h->L(lvl - 1).dev, h->pdev, 0, 0, h->stream);
     } else if (v >= 4) {
       if (h->n_cpu > 1) fail("fill_ghost_cells_lvl: extra variables on several ranks not supported yet");
@@ -946,8 +1070,8 @@ int omg_restrict_lvl(omg_handle* h, int iv, int lvl) {
     sync_meta(h);
     const int v = check_iv(h, iv);
     if (lvl <= h->lowest || lvl > h->highest) fail("cannot restrict lvl <= lowest_lvl");
-    if (h->n_cpu > 1) fail("omg_restrict_lvl: several ranks not supported for standalone restriction yet");
     omgk::restrict2(h->L(lvl).dev, h->L(lvl - 1).dev, v, -1, h->stream);
+    if (h->L(lvl).xr.any) exchange_restrict(h, lvl, v, -1, h->stream);
     h->launches++;
   });
 }
@@ -960,7 +1084,7 @@ int omg_prolong(omg_handle* h, int lvl, int iv, int iv_to, int add) {
     if (lvl == h->highest) fail("cannot prolong highest level");
     if (lvl < h->lowest) fail("cannot prolong below lowest level");
     if (!(v == IPHI || v >= 4)) fail("omg_prolong: source must be phi or an extra variable (ghost cells of rhs/old/res are not tracked)");
-    if (h->n_cpu > 1) fail("omg_prolong: several ranks not supported for standalone prolongation yet");
+    if (h->L(lvl + 1).xp.any) fail("omg_prolong: standalone prolongation across ranks is not supported (the cycle's fused correction is)");
     omgk::prolong_var(h->L(lvl + 1).dev, h->L(lvl).dev, h->pdev, v, vt, add, h->stream);
     h->launches++;
   });
@@ -978,9 +1102,41 @@ int omg_apply_op(omg_handle* h, int i_out) {
 
 int omg_nccl_unique_id(char out[128]) { return omg_comm_unique_id(out); }
 int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks) {
-  OMG_TRY(h, { (void)uid; (void)rank; (void)nranks; fail("omg_comm_init: not built yet"); });
+  OMG_TRY(h, {
+    if (h->comm) { omg_comm_destroy(h->comm); h->comm = nullptr; }
+    try { h->comm = omg_comm_create_nccl(uid, rank, nranks, h->device); } catch (const std::exception& e) { fail(e.what()); }
+    invalidate_programs(h);
+  });
 }
-int omg_comm_init_local(omg_handle* const* handles, int nranks) { (void)handles; (void)nranks; return 1; }
+int omg_comm_init_local(omg_handle* const* handles, int nranks) {
+  if (!handles || nranks < 1) return 1;
+  omg_handle* h0 = handles[0];
+  OMG_TRY(h0, {
+    omg_local_group* g = omg_local_group_create(nranks);
+    for (int r = 0; r < nranks; ++r) {
+      omg_handle* h = handles[r];
+      if (h->comm) { omg_comm_destroy(h->comm); h->comm = nullptr; }
+      try { h->comm = omg_comm_create_local(g, r, h->device); } catch (const std::exception& e) { fail(e.what()); }
+      invalidate_programs(h);
+    }
+  });
+}
+/* CPU-only view of the static exchange plan (no device needed): keys of the items rank `me` sends to / receives
+ * from `peer` in phase (0 ghost, 1 restrict, 2 prolong) on level lvl, in message order. */
+int omg_exchange_plan(const omg_tree_desc* t, int me, int phase, int lvl, int peer, int64_t* send_keys, int64_t* recv_keys,
+                      int cap, int* n_send, int* n_recv) {
+  if (!t || phase < 0 || phase > 2) return 1;
+  omgp::LevelPlan pl = omgp::build_plan(*t, me, phase, lvl);
+  int ns = 0, nr = 0;
+  for (const omgp::PeerPlan& pp : pl.peers) {
+    if (pp.peer != peer) continue;
+    for (const omgp::Item& it : pp.send) { if (send_keys && ns < cap) send_keys[ns] = it.key * 2 + it.kind; ++ns; }
+    for (const omgp::Item& it : pp.recv) { if (recv_keys && nr < cap) recv_keys[nr] = it.key * 2 + it.kind; ++nr; }
+  }
+  if (n_send) *n_send = ns;
+  if (n_recv) *n_recv = nr;
+  return 0;
+}
 
 int omg_sync(omg_handle* h) { OMG_TRY(h, { CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream)); }); }
 
@@ -995,6 +1151,7 @@ int64_t omg_stat(omg_handle* h, const char* key) {
   if (k == "graph_launches") return h->graph_launches;
   if (k == "bytes_h2d") return h->bytes_h2d;
   if (k == "bytes_d2h") return h->bytes_d2h;
+  if (k == "exchanges") return h->exchanges;
   if (k == "coarse_iters") {
     double v = 0; cudaSetDevice(h->device); cudaStreamSynchronize(h->stream);
     if (h->d_scal.p) cudaMemcpy(&v, h->d_scal.p + SCAL_COARSE_ITERS, sizeof(double), cudaMemcpyDeviceToHost);
@@ -1010,6 +1167,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     const std::string k(key);
     if (k == "use_graph") h->use_graph = value;
     else if (k == "fast_kernels") h->fast_kernels = value;
+    else if (k == "graph_multi") h->graph_multi = value;
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
     else if (k == "tail_cells") { if (h->have_tree) fail("tail_cells must be set before omg_set_tree"); h->tail_cells = value; }
     else fail("unknown option " + k);

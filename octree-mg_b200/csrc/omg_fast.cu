@@ -128,6 +128,29 @@ __global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_const
     }
   }
 
+  // ---- ghost planes materialised elsewhere (refinement boundaries, faces owned by another rank): plain loads
+  // of the other-colour entries of the nc x nc plane ----
+  bool any_plane = false;
+#pragma unroll
+  for (int f = 0; f < 6; ++f) any_plane = any_plane || (kind[f] == FK_PLANE);
+  if (any_plane) {
+    const double* __restrict__ gpl = L.gpl;
+    if (!zlo_in && kind[4] == FK_PLANE)
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.zlo[j][m] = gpl[(size_t)arg[4] * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)]; }
+    if (!zhi_in && kind[5] == FK_PLANE)
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.zhi[j][m] = gpl[(size_t)arg[5] * NC * NC + j * NC + 2 * m + ((oc ^ j) & 1)]; }
+    if (kind[2] == FK_PLANE)
+      for (int r = tid; r < KT * HX; r += kThreads) { const int kk = r / HX, m = r % HX, k = k0 + kk; S.ylo[kk][m] = gpl[(size_t)arg[2] * NC * NC + k * NC + 2 * m + ((oc ^ (k + 1)) & 1)]; }
+    if (kind[3] == FK_PLANE)
+      for (int r = tid; r < KT * HX; r += kThreads) { const int kk = r / HX, m = r % HX, k = k0 + kk; S.yhi[kk][m] = gpl[(size_t)arg[3] * NC * NC + k * NC + 2 * m + ((oc ^ k) & 1)]; }
+    if (kind[0] == FK_PLANE || kind[1] == FK_PLANE)
+      for (int r = tid; r < KT * NC; r += kThreads) {
+        const int kk = r / NC, j = r % NC, k = k0 + kk;
+        const int f = (colour ^ ((j + k) & 1)) ? 1 : 0;
+        if (kind[f] == FK_PLANE) S.xg[kk][j] = gpl[(size_t)arg[f] * NC * NC + k * NC + j];
+      }
+  }
+
   // rhs of this thread's cells (issued before the wait so that the loads overlap the bulk copies)
   constexpr int PER = KT * NC * HX / kThreads;
   double rhs[PER];
@@ -294,6 +317,22 @@ __global__ void __launch_bounds__(kThreads) k_stencil_fast(const __grid_constant
       if (hi) S.xhi[kk][j] = v; else S.xlo[kk][j] = v;
     }
   }
+  {
+    // ghost planes materialised elsewhere (refinement boundaries, faces owned by another rank)
+    const double* __restrict__ gpl = L.gpl;
+    if (!zlo_in && kind[4] == FK_PLANE)
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.zlo[(i + j + 1) & 1][j][i >> 1] = gpl[(size_t)arg[4] * NC * NC + r]; }
+    if (!zhi_in && kind[5] == FK_PLANE)
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.zhi[(i + j) & 1][j][i >> 1] = gpl[(size_t)arg[5] * NC * NC + r]; }
+    if (kind[2] == FK_PLANE)
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, i = r % NC, k = k0 + kk; S.ylo[(i + k + 1) & 1][kk][i >> 1] = gpl[(size_t)arg[2] * NC * NC + k * NC + i]; }
+    if (kind[3] == FK_PLANE)
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, i = r % NC, k = k0 + kk; S.yhi[(i + k) & 1][kk][i >> 1] = gpl[(size_t)arg[3] * NC * NC + k * NC + i]; }
+    if (kind[0] == FK_PLANE)
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xlo[kk][j] = gpl[(size_t)arg[0] * NC * NC + (k0 + kk) * NC + j]; }
+    if (kind[1] == FK_PLANE)
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xhi[kk][j] = gpl[(size_t)arg[1] * NC * NC + (k0 + kk) * NC + j]; }
+  }
   mbar_wait(&S.bar, 0);
   __syncthreads();
 
@@ -448,9 +487,13 @@ __global__ void __launch_bounds__(kThreads) k_corr_prolong_fast(const __grid_con
   double* corr = reinterpret_cast<double*>(smem_raw);       // [PW][PW][PW]
   const int tid = threadIdx.x, b = blockIdx.x;
   const int p = Lf.parent[b];
-  if (p < 0) return;
+  if (p == -1) return;
   const int off = Lf.coff[b];
   const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  if (p <= -2) {   // parent on another rank: the patch arrived with the prolong exchange
+    const double* __restrict__ patch = Lf.ppatch + (size_t)(-(p + 2)) * PW * PW * PW;
+    for (int r = tid; r < PW * PW * PW; r += kThreads) corr[r] = patch[r];
+  } else
   for (int r = tid; r < PW * PW * PW; r += kThreads) {
     const int a = r % PW, bb = (r / PW) % PW, c = r / (PW * PW);
     const int nedge = (a == 0 || a == PW - 1) + (bb == 0 || bb == PW - 1) + (c == 0 || c == PW - 1);

@@ -85,6 +85,42 @@ __global__ void __launch_bounds__(kThreads) k_fill_stored(const __grid_constant_
   do_fill_stored(L, P, iv, bc.type, bc.value, blockIdx.x, threadIdx.x, blockDim.x);
 }
 
+// ---- exchange pack / unpack (multi-rank; one CTA per message item) ---------------------------------
+// ghost phase: desc[4*e] = {kind (0 same-level, 1 coarse->fine), sender's local box, receiver's face, fine child offset}
+__global__ void __launch_bounds__(kThreads) k_pack_ghost(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
+                                                         const __grid_constant__ ParamsDev P, const int* __restrict__ desc,
+                                                         double* __restrict__ out, int gz) {
+  const int e = blockIdx.x;
+  const int kind = desc[4 * e], sb = desc[4 * e + 1], f = desc[4 * e + 2], off = desc[4 * e + 3];
+  double* o = out + (size_t)e * L.nc * L.nc;
+  if (kind == 0) do_pack_face(L, sb, f, o, threadIdx.x, blockDim.x);
+  else if (gz) do_pack_rb_face<GM_PHI_GZ>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
+  else do_pack_rb_face<GM_PHI>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
+}
+// restrict phase: desc[e] = child's local box; item = nvar blocks of (nc/2)^3
+__global__ void __launch_bounds__(kThreads) k_pack_restrict(const __grid_constant__ LevelDev Lf, const int* __restrict__ desc,
+                                                            double* __restrict__ out, int iv0, int iv1) {
+  const int h = Lf.nc >> 1, blk = h * h * h, nv = iv1 >= 0 ? 2 : 1;
+  double* o = out + (size_t)blockIdx.x * blk * nv;
+  do_pack_restrict(Lf, iv0, desc[blockIdx.x], o, threadIdx.x, blockDim.x);
+  if (iv1 >= 0) do_pack_restrict(Lf, iv1, desc[blockIdx.x], o + blk, threadIdx.x, blockDim.x);
+}
+// desc[2*e] = {parent's local box, octant offset}
+__global__ void __launch_bounds__(kThreads) k_unpack_restrict(const __grid_constant__ LevelDev Lc, const int* __restrict__ desc,
+                                                              const double* __restrict__ in, int h, int iv0, int iv1) {
+  const int blk = h * h * h, nv = iv1 >= 0 ? 2 : 1;
+  const double* q = in + (size_t)blockIdx.x * blk * nv;
+  do_unpack_restrict(Lc, iv0, desc[2 * blockIdx.x], desc[2 * blockIdx.x + 1], q, h, threadIdx.x, blockDim.x);
+  if (iv1 >= 0) do_unpack_restrict(Lc, iv1, desc[2 * blockIdx.x], desc[2 * blockIdx.x + 1], q + blk, h, threadIdx.x, blockDim.x);
+}
+// prolong phase: desc[2*e] = {parent's local box, child's octant offset}; item = (nc/2+2)^3 correction patch
+__global__ void __launch_bounds__(kThreads) k_pack_prolong(const __grid_constant__ LevelDev Lc, const __grid_constant__ ParamsDev P,
+                                                           const int* __restrict__ desc, double* __restrict__ out, int nc_f) {
+  const int pw = (nc_f >> 1) + 2;
+  do_pack_prolong(Lc, P, desc[2 * blockIdx.x], desc[2 * blockIdx.x + 1], out + (size_t)blockIdx.x * pw * pw * pw, nc_f,
+                  threadIdx.x, blockDim.x);
+}
+
 // elementwise helpers over whole-level arrays
 __global__ void k_fill(double* p, size_t n, double v) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
@@ -322,6 +358,18 @@ void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, 
   BcVar bc;
   for (int f = 0; f < 6; ++f) { bc.type[f] = bct[f]; bc.value[f] = bcv[f]; }
   k_fill_stored<<<L.nb, kThreads, 0, s>>>(L, P, iv, bc);
+}
+void pack_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int gz, cudaStream_t s) {
+  if (n) k_pack_ghost<<<n, kThreads, 0, s>>>(L, Lc, P, desc, out, gz);
+}
+void pack_restrict(const LevelDev& Lf, const int* desc, int n, double* out, int iv0, int iv1, cudaStream_t s) {
+  if (n) k_pack_restrict<<<n, kThreads, 0, s>>>(Lf, desc, out, iv0, iv1);
+}
+void unpack_restrict(const LevelDev& Lc, const int* desc, int n, const double* in, int h, int iv0, int iv1, cudaStream_t s) {
+  if (n) k_unpack_restrict<<<n, kThreads, 0, s>>>(Lc, desc, in, h, iv0, iv1);
+}
+void pack_prolong(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, cudaStream_t s) {
+  if (n) k_pack_prolong<<<n, kThreads, 0, s>>>(Lc, P, desc, out, nc_f);
 }
 void fill(double* p, size_t n, double v, cudaStream_t s) { if (n) k_fill<<<grid_for(n), 256, 0, s>>>(p, n, v); }
 void copy(double* dst, const double* src, size_t n, cudaStream_t s) { if (n) k_copy<<<grid_for(n), 256, 0, s>>>(dst, src, n); }

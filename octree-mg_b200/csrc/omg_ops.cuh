@@ -106,20 +106,25 @@ __device__ __forceinline__ double corr_at(const LevelDev& Lc, const ParamsDev& P
 }
 __device__ void do_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int b, int tid, int nthr) {
   const int p = Lf.parent[b];
-  if (p < 0) return;
+  if (p == -1) return;
   const int off = Lf.coff[b];
   const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
-  const int h = Lf.nc >> 1;
+  const int h = Lf.nc >> 1, pw = h + 2;
+  // parent on another rank: its rank sent the (h+2)^3 patch of phi_c - old_c around my octant
+  const double* patch = p <= -2 ? Lf.ppatch + (size_t)(-(p + 2)) * pw * pw * pw : nullptr;
+  auto corr = [&](int I, int J, int K) -> double {   // octant coordinates, -1 .. h
+    if (patch) return patch[((K + 1) * pw + (J + 1)) * pw + (I + 1)];
+    return corr_at(Lc, P, p, ox + I, oy + J, oz + K);
+  };
   double* phi = Lf.var[0] + (size_t)b * Lf.bs;
   for (int idx = tid; idx < h * h * h; idx += nthr) {
     const int I = idx % h, J = (idx / h) % h, K = idx / (h * h);
-    const int ic = ox + I, jc = oy + J, kc = oz + K;
-    const double c = corr_at(Lc, P, p, ic, jc, kc);
-    Lc.var[3][(size_t)p * Lc.bs + cidx(Lc, ic, jc, kc)] = c;
+    const double c = corr(I, J, K);
+    if (!patch) Lc.var[3][(size_t)p * Lc.bs + cidx(Lc, ox + I, oy + J, oz + K)] = c;
     const double f0 = 0.25 * c;
-    const double flx = 0.25 * corr_at(Lc, P, p, ic - 1, jc, kc), fhx = 0.25 * corr_at(Lc, P, p, ic + 1, jc, kc);
-    const double fly = 0.25 * corr_at(Lc, P, p, ic, jc - 1, kc), fhy = 0.25 * corr_at(Lc, P, p, ic, jc + 1, kc);
-    const double flz = 0.25 * corr_at(Lc, P, p, ic, jc, kc - 1), fhz = 0.25 * corr_at(Lc, P, p, ic, jc, kc + 1);
+    const double flx = 0.25 * corr(I - 1, J, K), fhx = 0.25 * corr(I + 1, J, K);
+    const double fly = 0.25 * corr(I, J - 1, K), fhy = 0.25 * corr(I, J + 1, K);
+    const double flz = 0.25 * corr(I, J, K - 1), fhz = 0.25 * corr(I, J, K + 1);
 #pragma unroll
     for (int kk = 0; kk < 2; ++kk)
 #pragma unroll
@@ -130,6 +135,68 @@ __device__ void do_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const Pa
           const int q = cidx(Lf, 2 * I + ii, 2 * J + jj, 2 * K + kk);
           phi[q] = phi[q] + fine;
         }
+  }
+}
+
+// prolong_set_buffer (src/m_prolong.f90:91-121) seen from the parent's rank: instead of the prolonged
+// fine block (nc^3 values) the (nc/2+2)^3 patch of the correction phi_c - old_c around the child's octant
+// is sent; the child's rank applies mg_prolong_sparse itself (same values, 4x fewer bytes).  Also stores
+// res_c = phi_c - old_c on the octant (correct_children, src/m_multigrid.f90:396-398).
+__device__ void do_pack_prolong(const LevelDev& Lc, const ParamsDev& P, int p, int off, double* __restrict__ out, int nc_f,
+                                int tid, int nthr) {
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  const int h = nc_f >> 1, pw = h + 2;
+  for (int r = tid; r < pw * pw * pw; r += nthr) {
+    const int a = r % pw, bb = (r / pw) % pw, c = r / (pw * pw);
+    const int nedge = (a == 0 || a == pw - 1) + (bb == 0 || bb == pw - 1) + (c == 0 || c == pw - 1);
+    double v = 0.0;
+    if (nedge <= 1) {
+      const int ic = ox + a - 1, jc = oy + bb - 1, kc = oz + c - 1;
+      v = corr_at(Lc, P, p, ic, jc, kc);
+      if (nedge == 0) Lc.var[3][(size_t)p * Lc.bs + cidx(Lc, ic, jc, kc)] = v;
+    }
+    out[r] = v;
+  }
+}
+
+// restrict_set_buffer (src/m_restrict.f90:116-163): restricted block of child b for a parent on another rank
+__device__ void do_pack_restrict(const LevelDev& Lf, int iv, int b, double* __restrict__ out, int tid, int nthr) {
+  const int h = Lf.nc >> 1;
+  const double* src = Lf.var[iv] + (size_t)b * Lf.bs;
+  for (int idx = tid; idx < h * h * h; idx += nthr) {
+    const int I = idx % h, J = (idx / h) % h, K = idx / (h * h);
+    double s = 0.0;
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+        for (int ii = 0; ii < 2; ++ii) s = s + src[cidx(Lf, 2 * I + ii, 2 * J + jj, 2 * K + kk)];
+    out[idx] = 0.125 * s;
+  }
+}
+// restrict_onto for a child on another rank (src/m_restrict.f90:195-212): received block -> parent's octant
+__device__ void do_unpack_restrict(const LevelDev& Lc, int iv, int p, int off, const double* __restrict__ in, int h,
+                                   int tid, int nthr) {
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  double* dst = Lc.var[iv] + (size_t)p * Lc.bs;
+  for (int idx = tid; idx < h * h * h; idx += nthr) {
+    const int I = idx % h, J = (idx / h) % h, K = idx / (h * h);
+    dst[cidx(Lc, ox + I, oy + J, oz + K)] = in[idx];
+  }
+}
+
+// buffer_for_nb (src/m_ghost_cells.f90:348-383): the interior layer of box sb that a same-level
+// neighbour on another rank needs as its ghost face f (f = face of the RECEIVER)
+__device__ void do_pack_face(const LevelDev& L, int sb, int f, double* __restrict__ out, int tid, int nthr) {
+  const int nc = L.nc;
+  const int layer = (f & 1) ? 0 : nc - 1;
+  const double* v = L.var[0] + (size_t)sb * L.bs;
+  for (int idx = tid; idx < nc * nc; idx += nthr) {
+    const int t1 = idx % nc, t2 = idx / nc;
+    int i, j, k;
+    if (f < 2) { i = layer; j = t1; k = t2; } else if (f < 4) { i = t1; j = layer; k = t2; } else { i = t1; j = t2; k = layer; }
+    out[idx] = v[cidx(L, i, j, k)];
   }
 }
 
@@ -163,33 +230,59 @@ __device__ void do_prolong_var(const LevelDev& Lf, const LevelDev& Lc, const Par
 // :769-861) for refinement-boundary entry e of the fine level: materialises the ghost plane.
 // GMC = GM_PHI normally, GM_PHI_GZ while the coarse ghosts are the zeros written by mg_fas_fmg.
 // GMV selects the variable class (phi: GM_PHI/GM_PHI_GZ with plane pool; stored: faces pool).
+// box_gc_for_fine_neighbor (src/m_ghost_cells.f90:500-577): interpolated coarse value for fine ghost cell
+// (A, B) (0-based tangential indices) of face f of a fine box with child offset di, from coarse box cb
 template <int GMC>
-__device__ void do_rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int e, int tid, int nthr) {
-  const int b = Lf.rb_list[4 * e], f = Lf.rb_list[4 * e + 1], cb = Lf.rb_list[4 * e + 2], pl = Lf.rb_list[4 * e + 3];
-  if (cb < 0) return;   // coarse neighbour on another rank: plane arrives through the halo exchange
-  const int nc = Lf.nc, h = nc >> 1;
-  const int off = Lf.coff[b];
-  const int di[3] = {off & 1023, (off >> 10) & 1023, (off >> 20) & 1023};
+__device__ __forceinline__ double rb_gc_value(const LevelDev& Lc, const ParamsDev& P, int iv, int cb, const int* di, int f,
+                                              int A, int B) {
+  const int nc = Lc.nc;
   const int d = f >> 1, ta = (d == 0) ? 1 : 0, tb = (d == 2) ? 1 : 2;
   const int cfix = (f & 1) ? 0 : nc - 1;          // coarse interior layer adjacent to the fine box
   const double* cv = Lc.var[iv]; const double* cf = Lc.faces[iv];
+  const int ia = (A >> 1), jb = (B >> 1);
+  int c[3];
+  auto T = [&](int da, int db) {
+    c[d] = cfix; c[ta] = di[ta] + ia + da; c[tb] = di[tb] + jb + db;
+    return (iv == 0) ? cell_at<GMC>(Lc, P, cv, nullptr, cb, c[0], c[1], c[2])
+                     : cell_at<GM_STORED>(Lc, P, cv, cf, cb, c[0], c[1], c[2]);
+  };
+  const double t0 = T(0, 0);
+  const double g1 = 0.125 * (T(1, 0) - T(-1, 0));
+  const double g2 = 0.125 * (T(0, 1) - T(0, -1));
+  double gc = (A & 1) ? t0 + g1 : t0 - g1;
+  gc = (B & 1) ? gc + g2 : gc - g2;
+  return gc;
+}
+
+// buffer_for_fine_nb (src/m_ghost_cells.f90:385-422): the coarse owner interpolates the face for a fine
+// box on another rank (fine child offset `off`, receiver face f) from its coarse box cb
+template <int GMC>
+__device__ void do_pack_rb_face(const LevelDev& Lc, const ParamsDev& P, int cb, int off, int f, double* __restrict__ out,
+                                int tid, int nthr) {
+  const int nc = Lc.nc;
+  const int di[3] = {off & 1023, (off >> 10) & 1023, (off >> 20) & 1023};
+  for (int idx = tid; idx < nc * nc; idx += nthr) out[idx] = rb_gc_value<GMC>(Lc, P, 0, cb, di, f, idx % nc, idx / nc);
+}
+
+// fill_refinement_bnd + box_gc_for_fine_neighbor + sides_rb (src/m_ghost_cells.f90:287-328, :500-577,
+// :769-861) for refinement-boundary entry e of the fine level: materialises the ghost plane.
+// GMC = GM_PHI normally, GM_PHI_GZ while the coarse ghosts are the zeros written by mg_fas_fmg.
+template <int GMC>
+__device__ void do_rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int e, int tid, int nthr) {
+  const int b = Lf.rb_list[4 * e], f = Lf.rb_list[4 * e + 1], cb = Lf.rb_list[4 * e + 2], pl = Lf.rb_list[4 * e + 3];
+  if (cb == -1) return;
+  const int nc = Lf.nc;
+  const int off = Lf.coff[b];
+  const int di[3] = {off & 1023, (off >> 10) & 1023, (off >> 20) & 1023};
+  const int d = f >> 1, ta = (d == 0) ? 1 : 0, tb = (d == 2) ? 1 : 2;
   const double* fv = Lf.var[iv] + (size_t)b * Lf.bs;
   const int ix = (f & 1) ? nc - 1 : 0, dix = (f & 1) ? -1 : 1;
+  // coarse neighbour on another rank: the interpolated coarse values arrived with the halo exchange
+  const double* gcpl = cb <= -2 ? Lf.gpl + (size_t)(-(cb + 2)) * nc * nc : nullptr;
   double* out = (iv == 0) ? Lf.gpl + (size_t)pl * nc * nc : Lf.faces[iv] + ((size_t)b * 6 + f) * nc * nc;
   for (int idx = tid; idx < nc * nc; idx += nthr) {
     const int A = idx % nc, B = idx / nc;          // 0-based fine tangential indices
-    const int ia = (A >> 1), jb = (B >> 1);        // coarse patch indices (0-based interior of the patch)
-    int c[3];
-    auto T = [&](int da, int db) {
-      c[d] = cfix; c[ta] = di[ta] + ia + da; c[tb] = di[tb] + jb + db;
-      return (iv == 0) ? cell_at<GMC>(Lc, P, cv, nullptr, cb, c[0], c[1], c[2])
-                       : cell_at<GM_STORED>(Lc, P, cv, cf, cb, c[0], c[1], c[2]);
-    };
-    const double t0 = T(0, 0);
-    const double g1 = 0.125 * (T(1, 0) - T(-1, 0));
-    const double g2 = 0.125 * (T(0, 1) - T(0, -1));
-    double gc = (A & 1) ? t0 + g1 : t0 - g1;
-    gc = (B & 1) ? gc + g2 : gc - g2;
+    const double gc = gcpl ? gcpl[idx] : rb_gc_value<GMC>(Lc, P, iv, cb, di, f, A, B);
     int q[3], r[3];
     q[d] = ix; r[d] = ix + dix; q[ta] = r[ta] = A; q[tb] = r[tb] = B;
     out[idx] = 0.5 * gc + 0.75 * fv[cidx(Lf, q[0], q[1], q[2])] - 0.25 * fv[cidx(Lf, r[0], r[1], r[2])];

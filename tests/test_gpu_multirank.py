@@ -1,0 +1,109 @@
+"""Multi-rank GPU parity on ONE device: n emulated ranks (one handle + one host thread each, omg_comm_init_local)
+run the reference's Morton partition (mg_load_balance) with the static exchange plans of omg_plan.cpp -- ghost
+faces, restriction blocks, coarse correction patches, scalar all-reduce -- and must reproduce the oracle
+bitwise (results are independent of the number of ranks).  The NCCL transport carries the very
+same buffers; it is exercised by bench.py --gpus N."""
+import functools
+
+import pytest
+
+import problems as P
+from compare import assert_state_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def group_cls(product, n_cpu):
+    return functools.partial(product.MgGroup, n_cpu)
+
+
+def check(h_o, h_g):
+    assert h_o == h_g, "residual histories differ: %r vs %r" % (h_o, h_g)
+
+
+@pytest.mark.parametrize("n_cpu", [2, 3, 8])
+@pytest.mark.parametrize("fmg", [False, True])
+def test_uniform_ranks(oracle, product, n_cpu, fmg):
+    orc, _ = P.uniform_problem(oracle.OracleMg, 32, 8, n_cpu=n_cpu)
+    mg, _ = P.uniform_problem(group_cls(product, n_cpu), 32, 8)
+    check(P.run_cycles(orc, 3, fmg), P.run_cycles(mg, 3, fmg))
+    assert_state_equal(orc, mg)
+    assert mg.stat("exchanges") > 0
+
+
+@pytest.mark.parametrize("lb", ["default", "simple", "parents"])
+def test_fast_kernels_with_remote_faces(oracle, product, lb):
+    """box 16: the TMA-staged kernels run on levels whose partition faces arrive through the plane pool"""
+    orc, _ = P.uniform_problem(oracle.OracleMg, (64, 32, 32), 16, n_cpu=4, load_balance=lb)
+    mg, _ = P.uniform_problem(group_cls(product, 4), (64, 32, 32), 16, load_balance=lb)
+    check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    check(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("op,bc,lam", [(P.mg_helmholtz, "neumann0", 1.0), (P.mg_vlaplacian, "mixed", 0.0)])
+def test_operators_ranks(oracle, product, op, bc, lam):
+    orc, _ = P.uniform_problem(oracle.OracleMg, 32, 8, operator_type=op, bc=bc, lam=lam, n_cpu=2)
+    mg, _ = P.uniform_problem(group_cls(product, 2), 32, 8, operator_type=op, bc=bc, lam=lam)
+    check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("n_cpu", [2, 5])
+def test_refinement_ranks(oracle, product, n_cpu):
+    """AMR: refinement-boundary faces whose coarse neighbour lives on another rank are interpolated by the
+    coarse owner and sent (buffer_for_fine_nb, src/m_ghost_cells.f90:385-422)."""
+    def build(cls, **kw):
+        mg = cls(P.mg_laplacian, P.mg_smoother_gsrb, **kw)
+        for nb in range(1, 7):
+            mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.25)
+        mg.mg_set_methods()
+        P.build_amr_tree(mg, 3, [32] * 3, 8, [1.0 / 32] * 3)
+        for lvl, id_ in P.all_ids(mg):
+            mg.cc(id_)[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1] = 1.0 + 0.1 * lvl
+        return mg
+    orc, mg = build(oracle.OracleMg, n_cpu=n_cpu), build(group_cls(product, n_cpu))
+    check(P.run_cycles(orc, 3, True), P.run_cycles(mg, 3, True))
+    check(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
+
+
+def test_periodic_ranks(oracle, product):
+    """periodic neighbours across ranks + subtract_mean (all-reduce SUM); tolerance as in the single-rank test"""
+    import numpy as np
+
+    def build(cls, **kw):
+        mg = cls(P.mg_laplacian, P.mg_smoother_gsrb, **kw)
+        mg.mg_set_methods()
+        mg.mg_build_rectangle([32] * 3, 8, [1.0 / 32] * 3, [0.0] * 3, [True] * 3)
+        mg.mg_load_balance()
+        mg.mg_allocate_storage()
+        for lvl, id_ in P.all_ids(mg):
+            X, Y, Z = P.cell_coords(mg, id_, lvl)
+            mg.cc(id_)[P.mg_irhs - 1] = np.sin(2 * np.pi * X) * np.cos(4 * np.pi * Y) + 0.3 * np.sin(2 * np.pi * Z) + 0.05
+        return mg
+    orc, mg = build(oracle.OracleMg, n_cpu=4), build(group_cls(product, 4))
+    rhs_norm = 1.4
+    for fmg in (True, False):
+        for a, b in zip(P.run_cycles(orc, 3, fmg), P.run_cycles(mg, 3, fmg)):
+            assert abs(a - b) <= max(1e-10 * abs(a), 1e-12 * rhs_norm)
+
+
+def test_steps_ranks(oracle, product):
+    """building blocks on their own across 4 ranks"""
+    orc, _ = P.uniform_problem(oracle.OracleMg, 32, 8, n_cpu=4)
+    mg, _ = P.uniform_problem(group_cls(product, 4), 32, 8)
+    orc.mg_fill_ghost_cells(P.mg_iphi)     # the device derives phi's ghost cells; make the oracle's stored ones consistent
+    for lvl in range(orc.highest_lvl, orc.lowest_lvl, -1):
+        orc.smooth_boxes(lvl, 1)
+        mg.smooth_boxes(lvl, 1)
+        orc.update_coarse(lvl)
+        mg.update_coarse(lvl)
+    assert_state_equal(orc, mg, ghosts_of=(1, 3))
+    for lvl in range(orc.lowest_lvl, orc.highest_lvl):
+        orc.correct_children(lvl)
+        orc.mg_fill_ghost_cells_lvl(lvl + 1, P.mg_iphi)
+        mg.correct_children(lvl)
+    assert_state_equal(orc, mg, variables=(1, 4), ghosts_of=(1,))
+    for lvl in range(orc.lowest_lvl, orc.highest_lvl + 1):
+        assert orc.max_residual_lvl(lvl) == mg.max_residual_lvl(lvl)
