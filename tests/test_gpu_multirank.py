@@ -99,7 +99,7 @@ def test_steps_ranks(oracle, product):
         mg.smooth_boxes(lvl, 1)
         orc.update_coarse(lvl)
         mg.update_coarse(lvl)
-    assert_state_equal(orc, mg, ghosts_of=(1, 3))
+    assert_state_equal(orc, mg, ghosts_of=(1,))
     for lvl in range(orc.lowest_lvl, orc.highest_lvl):
         orc.correct_children(lvl)
         orc.mg_fill_ghost_cells_lvl(lvl + 1, P.mg_iphi)
