@@ -5,7 +5,8 @@ an end-to-end number through the C ABI with host buffers, and the CPU oracle tim
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--n 512] [--box 16]
 
 A step is one standalone V(2,2) GSRB cycle (mg_fas_vcycle, src/m_multigrid.f90:150-243) of the
-tests/test_performance.f90 problem (rhs = 1, phi0 = 0, homogeneous Dirichlet), max_res requested.
+tests/test_performance.f90 problem (rhs = 1, phi0 = 0, homogeneous Dirichlet), called as in that program's timed
+loop (:68-76: `call mg_fas_vcycle(mg)`, no max_res; --max-res adds the all-level residual pass).
 N = 1: BASELINE.json configs[1] (512^3, box 16).  N > 1: weak scaling, 512^3 per GPU along the reference's
 Morton partition (N = 8 is configs[4], 1024^3).
 """
@@ -22,7 +23,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-BYTES_PER_DOF_VCYCLE = 155.4 + 18.3     # Laplacian V(2,2) + max_res request
+BYTES_PER_DOF_VCYCLE = 155.4            # Laplacian V(2,2); + 18.3 when max_res is requested
+BYTES_PER_DOF_MAXRES = 18.3
 SMOOTH_BYTES_PER_CELL = 12.0            # one colour half-sweep launched on its own
 
 
@@ -96,16 +98,16 @@ def cpu_reference_line(args, sample_n=None):
     mg = P.performance_problem(O.OracleMg, n, args.box, n_cpu=ranks)
     dof = n ** 3
     for _ in range(max(args.warmup, 0) and 1):
-        mg.mg_fas_vcycle(want_res=True)
+        mg.mg_fas_vcycle(want_res=args.max_res)
     k = max(1, min(args.steps, 3))
     t0 = time.perf_counter()
     for _ in range(k):
-        mg.mg_fas_vcycle(want_res=True)
+        mg.mg_fas_vcycle(want_res=args.max_res)
     dt = time.perf_counter() - t0
     val = dof * k / dt / 1e9
     return {"value": val, "unit": "GDOF/s", "cores": ranks, "kind": "port",
-            "sample": "%d^3 box %d, %d V(2,2) GSRB cycles with max_res, oracle/omg_oracle.cpp, %d OpenMP threads = emulated MPI ranks"
-                      % (n, args.box, k, ranks), "ms_per_step": dt / k * 1e3}
+            "sample": "%d^3 box %d, %d V(2,2) GSRB cycles%s, oracle/omg_oracle.cpp, %d OpenMP threads = emulated MPI ranks"
+                      % (n, args.box, k, " with max_res" if args.max_res else "", ranks), "ms_per_step": dt / k * 1e3}
 
 
 def main():
@@ -116,6 +118,8 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--n", type=int, default=512)
     ap.add_argument("--box", type=int, default=16)
+    ap.add_argument("--max-res", action="store_true", help="request max_res in every timed cycle (extra residual pass over all levels)")
+    ap.add_argument("--collapse", type=int, default=-1, help="coarse levels with fewer boxes per rank than this live on one GPU (N > 1; -1: default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
@@ -125,8 +129,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dims = domain_for(args.n, world)
-    config = {"workload": "test_performance %s box %d: 7-point Laplacian, rhs=1, Dirichlet 0, standalone V(2,2) GSRB cycles with max_res"
-                          % ("x".join(map(str, dims)), args.box),
+    config = {"workload": "test_performance %s box %d: 7-point Laplacian, rhs=1, Dirichlet 0, standalone V(2,2) GSRB cycles%s"
+                          % ("x".join(map(str, dims)), args.box, " with max_res" if args.max_res else " (mg_fas_vcycle(mg) as in test_performance.f90:68-76)"),
               "n_cycle_down": 2, "n_cycle_up": 2, "smoother": "gsrb", "box_size": args.box, "domain": dims,
               "partition": "mg_load_balance (Morton-contiguous), %d rank(s)" % world,
               "l2": "inputs larger than L2 (4 x %.2f GB per GPU vs 126 MB)" % (args.n ** 3 * 8 / 1e9)}
@@ -158,6 +162,10 @@ def main():
     # tests/test_performance.f90:51-66 without host cc arrays (the run is device-resident)
     mg = om.Mg(P.mg_laplacian, P.mg_smoother_gsrb, n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
     mg.set_int("host_cc", 0)
+    collapse = args.collapse if args.collapse >= 0 else 128
+    if world > 1:
+        mg.set_int("coarse_collapse_boxes", collapse)
+        config["coarse_collapse_boxes_per_rank"] = collapse
     for nb in range(1, 7):
         mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
     mg.mg_set_methods()
@@ -185,9 +193,9 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    mg.mg_fas_vcycle(want_res=True)                       # uploads parameters; first cycle also builds the graph
+    mg.mg_fas_vcycle(want_res=args.max_res)               # uploads parameters; first cycle also builds the graph
     for _ in range(max(args.warmup - 1, 0)):
-        mg.fas_vcycles(1)
+        mg.fas_vcycles(1, want_res=args.max_res)
 
     def barrier():
         torch.cuda.synchronize()
@@ -196,7 +204,7 @@ def main():
         torch.cuda.synchronize()
 
     barrier()
-    res, ms = mg.fas_vcycles(args.steps)                  # CUDA events on the handle's stream bracket the K cycles
+    res, ms = mg.fas_vcycles(args.steps, want_res=args.max_res)   # CUDA events on the handle's stream bracket the K cycles
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     if dist is not None:
@@ -205,8 +213,9 @@ def main():
         ms = float(tms.item())
     launches_per_step = None
     l0 = mg.stat("launches")
-    mg.fas_vcycles(1)
+    mg.fas_vcycles(1, want_res=args.max_res)
     launches_per_step = mg.stat("launches") - l0
+    res_after, _ = mg.fas_vcycles(1, want_res=True)      # untimed: residual after warm-up + timed + 2 cycles
 
     # --- roofline of the dominant kernel (finest-level GSRB colour half-sweep), timed live with CUDA events
     mg.set_option("profile", 1)
@@ -223,7 +232,7 @@ def main():
                 "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": SMOOTH_BYTES_PER_CELL * cells_per_rank,
                 "ms_per_launch": sm_ms, "finest_level_ms": prof}
     value = dof * args.steps / (ms * 1e-3) / 1e9
-    cycle_frac = BYTES_PER_DOF_VCYCLE * value / peak / world
+    cycle_frac = (BYTES_PER_DOF_VCYCLE + (BYTES_PER_DOF_MAXRES if args.max_res else 0.0)) * value / peak / world
 
     # --- end to end through the C ABI with host buffers: push phi + rhs (pinned), cycle, pull phi
     e2e = None
@@ -237,7 +246,7 @@ def main():
         def step():
             mg._gck(G.omg_push_var_packed(gpu, P.mg_iphi, -20, 20, C.c_void_p(hphi.data_ptr()), nd))
             mg._gck(G.omg_push_var_packed(gpu, P.mg_irhs, -20, 20, C.c_void_p(hrhs.data_ptr()), nd))
-            mg._gck(G.omg_fas_vcycle(gpu, 0, 0, 1, 1, C.byref(r)))
+            mg._gck(G.omg_fas_vcycle(gpu, 0, 0, 1, int(args.max_res), C.byref(r)))
             mg._gck(G.omg_pull_var_packed(gpu, P.mg_iphi, -20, 20, C.c_void_p(hphi.data_ptr()), nd, 1))
         step()
         barrier()
@@ -265,7 +274,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
             "roofline": roofline, "cycle_hbm_frac": cycle_frac, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": launches_per_step * args.steps if launches_per_step else None,
-            "launches_per_step": launches_per_step, "clocks": clocks, "residuals": res,
+            "launches_per_step": launches_per_step, "clocks": clocks, "residuals": res, "max_res_after": res_after,
             "ref_style_unknowns_per_us": None}
     print(json.dumps(line))
 

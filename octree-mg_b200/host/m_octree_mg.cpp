@@ -274,6 +274,14 @@ static void assign_coarse_rank(mg_t& mg, int single_cpu_lvl, const std::vector<i
   }
   for (int lvl = mg.lowest_lvl; lvl <= single_cpu_lvl; ++lvl)
     for (int id : mg.L(lvl).ids) mg.boxes[id].rank = coarse_rank;
+  // B200 extension (off by default = the reference's partition): coarse levels that no longer fill the
+  // GPUs collapse onto the coarse rank -- the levels above single_cpu_lvl, bottom up, while they hold fewer
+  // than coarse_collapse_boxes boxes per rank.  Results do not depend on the partition.
+  if (mg.coarse_collapse_boxes > 0 && mg.n_cpu > 1)
+    for (int lvl = single_cpu_lvl + 1; lvl < mg.highest_lvl; ++lvl) {
+      if ((long)mg.L(lvl).ids.size() >= (long)mg.coarse_collapse_boxes * mg.n_cpu) break;
+      for (int id : mg.L(lvl).ids) mg.boxes[id].rank = coarse_rank;
+    }
 }
 
 void mg_load_balance_simple(mg_t& mg) {                                           // :22-63
@@ -613,6 +621,7 @@ int omgh_set_int(void* h, const char* key, int v) {
     else if (k == "subtract_mean") mg.subtract_mean = v != 0;
     else if (k == "bc_dirty") mg.bc_dirty = v != 0;
     else if (k == "host_cc") mg.host_cc = v != 0;
+    else if (k == "coarse_collapse_boxes") mg.coarse_collapse_boxes = v;
     else throw mg_error("unknown int key " + k);
   });
 }

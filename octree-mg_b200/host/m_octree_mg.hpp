@@ -83,6 +83,7 @@ struct mg_t {
   // true: device-resident; the host calls mg_gpu_push / mg_gpu_pull around its own cc accesses.
   bool gpu_resident = false;
   bool bc_dirty = true, eps_dirty = true;
+  int coarse_collapse_boxes = 0;   // > 0: coarse levels with fewer boxes per rank than this live on one GPU (see m_load_balance part)
   bool host_cc = true;   // false: device-resident runs that never touch host cc skip the host allocation
 
   mg_lvl_t& L(int lvl) { return lvls[lvl - mg_lvl_lo]; }

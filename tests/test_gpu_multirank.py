@@ -107,3 +107,18 @@ def test_steps_ranks(oracle, product):
     assert_state_equal(orc, mg, variables=(1, 4), ghosts_of=(1,))
     for lvl in range(orc.lowest_lvl, orc.highest_lvl + 1):
         assert orc.max_residual_lvl(lvl) == mg.max_residual_lvl(lvl)
+
+
+def test_coarse_level_collapse(oracle, product):
+    """coarse levels gathered onto one rank (host-mirror option coarse_collapse_boxes): same numbers"""
+    def make(*a, **k):
+        g = product.MgGroup(4, *a, **k)
+        g.set_int("coarse_collapse_boxes", 16)
+        return g
+    orc = P.performance_problem(oracle.OracleMg, 64, 8, n_cpu=4)
+    mg = P.performance_problem(make, 64, 8)
+    owners = {lvl: sorted({mg.box_info(i)["rank"] for i in mg.ids(lvl)}) for lvl in range(mg.lowest_lvl, mg.highest_lvl + 1)}
+    assert len(owners[mg.highest_lvl]) == 4 and len(owners[mg.highest_lvl - 2]) == 1, owners
+    check(P.run_cycles(orc, 3, False), P.run_cycles(mg, 3, False))
+    check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    assert_state_equal(orc, mg)
