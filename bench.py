@@ -120,6 +120,7 @@ def main():
     ap.add_argument("--box", type=int, default=16)
     ap.add_argument("--max-res", action="store_true", help="request max_res in every timed cycle (extra residual pass over all levels)")
     ap.add_argument("--collapse", type=int, default=-1, help="coarse levels with fewer boxes per rank than this live on one GPU (N > 1; -1: default)")
+    ap.add_argument("--tail-cells", type=int, default=-1, help="levels up to this many cells run inside the single-launch coarse tail")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
@@ -186,6 +187,8 @@ def main():
     # device-resident initial state: rhs = 1 on the interior of every level, phi = 0 (no host transfer needed)
     mg._gck(G.omg_set_var_const(gpu, P.mg_irhs, -20, 20, 1.0, 1))
     mg._gck(G.omg_set_var_const(gpu, P.mg_iphi, -20, 20, 0.0, 0))
+    if args.tail_cells >= 0:
+        mg.set_option("tail_cells", args.tail_cells)
     if args.no_graph:
         mg.set_option("use_graph", 0)
     if args.no_fast:

@@ -104,7 +104,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 32768, graph_multi = 1;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -147,6 +147,26 @@ void free_levels(omg_handle* h) {
 
 inline bool has_children(const omg_handle* h, int id) { return h->children[(size_t)(id - 1) * 8] != 0; }
 
+// tail group: the coarsest levels, while they are small and live on one rank (the reference keeps
+// everything below first_normal_lvl on one rank, src/m_load_balance.f90:79-81)
+void compute_tail(omg_handle* h) {
+  bool still = true; int owner = -1;
+  for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
+    LevelHost& L = h->L(lvl);
+    const std::vector<int>& ids = h->lvl_ids[lvl - h->lowest];
+    bool one_rank = true;
+    for (int id : ids) { if (owner < 0) owner = h->rank[id - 1]; if (h->rank[id - 1] != owner) one_rank = false; }
+    const long cells = (long)ids.size() * L.nc * L.nc * L.nc;
+    if (lvl == h->lowest) {
+      if (!one_rank) fail("Multiple CPUs for coarse grid (not implemented yet)");   // m_multigrid.f90:197-200
+      L.tail = true;
+    } else {
+      still = still && one_rank && cells <= h->tail_cells && lvl < h->highest;
+      L.tail = still;
+    }
+  }
+}
+
 // ---- tree ingestion ------------------------------------------------------------------------
 void set_tree(omg_handle* h, const omg_tree_desc* t) {
   CK(cudaSetDevice(h->device));
@@ -184,25 +204,7 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
     L.nb = (int)L.ids.size();
   }
 
-  // tail group: the coarsest levels, while they are small and live on one rank (the reference keeps
-  // everything below first_normal_lvl on one rank, src/m_load_balance.f90:79-81)
-  {
-    bool still = true; int owner = -1;
-    for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
-      LevelHost& L = h->L(lvl);
-      const std::vector<int>& ids = h->lvl_ids[lvl - h->lowest];
-      bool one_rank = true;
-      for (int id : ids) { if (owner < 0) owner = h->rank[id - 1]; if (h->rank[id - 1] != owner) one_rank = false; }
-      const long cells = (long)ids.size() * L.nc * L.nc * L.nc;
-      if (lvl == h->lowest) {
-        if (!one_rank) fail("Multiple CPUs for coarse grid (not implemented yet)");   // m_multigrid.f90:197-200
-        L.tail = true;
-      } else {
-        still = still && one_rank && cells <= h->tail_cells && lvl < h->highest;
-        L.tail = still;
-      }
-    }
-  }
+  compute_tail(h);
 
   // which (phase, level) pairs carry traffic on ANY rank: decided from the replicated tree, so every rank
   // emits the same exchange steps
@@ -1169,7 +1171,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "fast_kernels") h->fast_kernels = value;
     else if (k == "graph_multi") h->graph_multi = value;
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
-    else if (k == "tail_cells") { if (h->have_tree) fail("tail_cells must be set before omg_set_tree"); h->tail_cells = value; }
+    else if (k == "tail_cells") { h->tail_cells = value; if (h->have_tree) compute_tail(h); }
     else fail("unknown option " + k);
     invalidate_programs(h);
   });
