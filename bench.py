@@ -125,6 +125,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
     ap.add_argument("--no-fast", action="store_true", help="general-path kernels only")
+    ap.add_argument("--opt", action="append", default=[], help="library option key=value (omg_set_option), repeatable")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -193,6 +194,10 @@ def main():
         mg.set_option("use_graph", 0)
     if args.no_fast:
         mg.set_option("fast_kernels", 0)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        mg.set_option(k, int(v))
+        config.setdefault("options", {})[k] = int(v)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()

@@ -104,7 +104,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -371,6 +371,8 @@ void sync_meta(omg_handle* h) {
       if (L.xp.d_recv.n) CK(cudaMemsetAsync(L.xp.d_recv.p, 0, L.xp.d_recv.n * sizeof(double), s));
       L.meta_dirty = false;
     }
+    if (h->params.smoother_type == 1 && L.nb && !L.d_faces[IPHI].p)   // mg_smoother_gs: ghost snapshot of phi
+      L.d_faces[IPHI].alloc((size_t)L.nb * 6 * L.nc * L.nc);
     for (int v = 0; v < OMG_MAXV; ++v) { D.var[v] = L.d_var[v].p; D.faces[v] = L.d_faces[v].p; }
     D.fkind = L.d_fkind.p; D.farg = L.d_farg.p; D.ftype = L.d_ftype.p;
     D.fkind_old = L.d_fkind_old.p; D.farg_old = L.d_farg_old.p;
@@ -560,7 +562,8 @@ void exec_steps(omg_handle* h, Program& P) {
     switch (st.kind) {
       case S_SMOOTH: {
         LevelHost& L = h->L(st.l);
-        if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, s))) omgk::smooth(L.dev, PD, st.a, s);
+        if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; }
+        else if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, s))) omgk::smooth(L.dev, PD, st.a, s);
         h->launches++;
       } break;
       case S_RESID: {
@@ -591,7 +594,12 @@ void exec_steps(omg_handle* h, Program& P) {
       } break;
       case S_RB_FILL: omgk::rb_fill(h->L(st.l).dev, h->L(st.l - 1).dev, PD, 0, st.a, s); h->launches++; break;
       case S_COPY_OLD: { LevelHost& L = h->L(st.l); omgk::copy(L.d_var[IOLD].p, L.d_var[IPHI].p, L.d_var[IPHI].n, s); h->launches++; } break;
-      case S_TAIL: omgk::tail(h->d_levels.p, PD, P.d_ops.p + st.a, st.b, h->d_scal.p, s); h->launches++; break;
+      case S_TAIL: {
+        // stage the tail levels in shared memory when all four variables of all of them fit (option "tail_smem")
+        int n_stage = 0; size_t bytes = 0;
+        if (h->tail_smem) for (LevelHost& L : h->levels) { if (!L.tail) break; ++n_stage; bytes += (size_t)4 * L.nb * L.dev.bs * sizeof(double); }
+        omgk::tail(h->d_levels.p, PD, P.d_ops.p + st.a, st.b, h->d_scal.p, n_stage, bytes, s); h->launches++;
+      } break;
       case S_ZERO_PHI: {
         LevelHost& L = h->L(st.l);
         if (L.d_var[IPHI].n) CK(cudaMemsetAsync(L.d_var[IPHI].p, 0, L.d_var[IPHI].n * sizeof(double), s));
@@ -644,10 +652,7 @@ void check_supported(omg_handle* h) {
   const omg_params& p = h->params;
   if (p.operator_type < 1 || p.operator_type > 5) fail("mg_set_methods: unknown operator");
   if (p.geometry_type != 1) fail("set_methods: unsupported geometry");
-  if (p.smoother_type != 2) {
-    if (p.smoother_type == 1) fail("mg_smoother_gs is not available on the device path; use mg_smoother_gsrb");
-    fail("set_methods: unsupported smoother type");
-  }
+  if (p.smoother_type != 1 && p.smoother_type != 2) fail("set_methods: unsupported smoother type");
   if ((p.operator_type == OP_VLPL || p.operator_type == OP_VHELMH) && h->n_extra < 1) fail("set_methods: mg%n_extra_vars == 0");
   if (p.operator_type == OP_AHELMH && h->n_extra < 3) fail("ahelmholtz_set_methods: mg%n_extra_vars < 3");
 }
@@ -1170,6 +1175,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     if (k == "use_graph") h->use_graph = value;
     else if (k == "fast_kernels") h->fast_kernels = value;
     else if (k == "graph_multi") h->graph_multi = value;
+    else if (k == "tail_smem") h->tail_smem = value;
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
     else if (k == "tail_cells") { h->tail_cells = value; if (h->have_tree) compute_tail(h); }
     else fail("unknown option " + k);

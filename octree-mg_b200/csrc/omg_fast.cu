@@ -8,6 +8,7 @@
 #include "omg_fast.h"
 
 #include <cstdint>
+#include <cstdlib>
 
 namespace {
 
@@ -18,6 +19,11 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// raise the expected transaction bytes without arriving (the phase stays open until the final arrive)
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
@@ -80,25 +86,34 @@ __global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_const
   double* __restrict__ Ag = L.var[0] + boxoff + (size_t)colour * L.cs;  // colour being updated
   const double* __restrict__ Rg = L.var[1] + boxoff + (size_t)colour * L.cs;
 
+  // the tile itself depends on nothing but the box index: its copy starts before the face table is read
+  if (tid == 0) {
+    mbar_init(&S.bar, 1);
+    mbar_expect_tx(&S.bar, KT * NC * HX * 8);
+    bulk_g2s(&S.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+  }
+  // rhs of this thread's cells (in flight while the bulk copies land)
+  constexpr int PER = KT * NC * HX / kThreads;
+  double rhs[PER];
+#pragma unroll
+  for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)k0 * NC * HX + q * kThreads + tid];
+
   int kind[6], arg[6];
 #pragma unroll
   for (int f = 0; f < 6; ++f) { kind[f] = L.fkind[b * 6 + f]; arg[f] = L.farg[b * 6 + f]; }
   // z faces of an interior slab come from the box itself
   const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
-
-  if (tid == 0) mbar_init(&S.bar, 1);
   __syncthreads();
 
   if (tid < 32) {
-    // ---- warp 0: all TMA bulk copies of this tile ----
+    // ---- warp 0: the TMA bulk copies of the ghost layer ----
     if (tid == 0) {
-      uint32_t bytes = KT * NC * HX * 8;
+      uint32_t bytes = 0;
       if (zlo_in || kind[4] == FK_SAME) bytes += NC * HX * 8;
       if (zhi_in || kind[5] == FK_SAME) bytes += NC * HX * 8;
       if (kind[2] == FK_SAME) bytes += KT * HX * 8;
       if (kind[3] == FK_SAME) bytes += KT * HX * 8;
       mbar_arrive_expect_tx(&S.bar, bytes);
-      bulk_g2s(&S.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
     }
     __syncwarp();
     if (tid == 1) {
@@ -150,12 +165,6 @@ __global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_const
         if (kind[f] == FK_PLANE) S.xg[kk][j] = gpl[(size_t)arg[f] * NC * NC + k * NC + j];
       }
   }
-
-  // rhs of this thread's cells (issued before the wait so that the loads overlap the bulk copies)
-  constexpr int PER = KT * NC * HX / kThreads;
-  double rhs[PER];
-#pragma unroll
-  for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)k0 * NC * HX + q * kThreads + tid];
 
   mbar_wait(&S.bar, 0);
   __syncthreads();
@@ -260,8 +269,8 @@ struct StencilSmem {
   uint64_t bar;
 };
 
-template <int NC, int KT, int MODE, bool HELM>
-__global__ void __launch_bounds__(kThreads) k_stencil_fast(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
+template <int NC, int KT, int MODE, bool HELM, int MB>
+__global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
                                                            const __grid_constant__ ParamsDev P, double* maxslot) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
@@ -275,24 +284,51 @@ __global__ void __launch_bounds__(kThreads) k_stencil_fast(const __grid_constant
   const double* __restrict__ phi = L.var[0];
   const size_t boxoff = (size_t)b * L.bs;
 
-  int kind[6], arg[6];
-#pragma unroll
-  for (int f = 0; f < 6; ++f) { kind[f] = L.fkind[b * 6 + f]; arg[f] = L.farg[b * 6 + f]; }
-  const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
-
-  if (tid == 0) mbar_init(&S.bar, 1);
-  __syncthreads();
-
+  // the tile itself depends on nothing but the box index: its copies start before the face table is read
   if (tid == 0) {
-    uint32_t bytes = 2 * KT * NC * HX * 8;
-    if (zlo_in || kind[4] == FK_SAME) bytes += 2 * NC * HX * 8;
-    if (zhi_in || kind[5] == FK_SAME) bytes += 2 * NC * HX * 8;
-    mbar_arrive_expect_tx(&S.bar, bytes);
+    mbar_init(&S.bar, 1);
+    mbar_expect_tx(&S.bar, 2 * KT * NC * HX * 8);
     if (TILES == 1) bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff, 2 * KT * NC * HX * 8, &S.bar);   // whole box: one 32 KiB copy
     else {
       bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
       bulk_g2s(&S.Ph[1][0][0][0], phi + boxoff + L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
     }
+  }
+  // rhs (or res) of this thread's first coarse cell: issued before the wait so that the loads overlap the bulk copies
+  const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], lambda = P.lambda;
+  const double* __restrict__ in1 = (MODE == MODE_CRHS ? L.var[3] : L.var[1]) + boxoff;   // res (crhs) or rhs
+  double* __restrict__ out1 = (MODE == MODE_CRHS ? L.var[1] : L.var[3]) + boxoff;        // rhs (crhs) or res
+  double* __restrict__ out2 = L.var[2] + boxoff;                                         // old (crhs)
+  double vmax = 0.0;
+  int p = -1, ox = 0, oy = 0, oz = 0;
+  if (MODE == MODE_RESID_RESTRICT) {
+    p = L.parent[b];
+    const int off = L.coff[b];
+    ox = off & 1023; oy = (off >> 10) & 1023; oz = (off >> 20) & 1023;
+  }
+  constexpr int HC = NC / 2, NCOARSE = (KT / 2) * HC * HC, NIT = NCOARSE / kThreads;
+  static_assert(NCOARSE % kThreads == 0, "coarse cells must tile the CTA");
+  const int cs = L.cs;
+  // global offset of fine cell (di, slot s, dk) of coarse cell q (its colour is (di + dj + dk) & 1: k0, 2I, 2J, 2Kc are even)
+  auto goff = [&](int q, int di, int s, int dk) -> size_t {
+    const int I = q % HC, J = (q / HC) % HC, Kc = q / (HC * HC);
+    const int dj = s ^ (J & 1);
+    return (size_t)((di + dj + dk) & 1) * cs + ((size_t)(k0 + 2 * Kc + dk) * NC + (2 * J + dj)) * HX + I;
+  };
+  double nxt[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) nxt[e] = in1[goff(tid, e & 1, (e >> 1) & 1, e >> 2)];
+  int kind[6], arg[6];
+#pragma unroll
+  for (int f = 0; f < 6; ++f) { kind[f] = L.fkind[b * 6 + f]; arg[f] = L.farg[b * 6 + f]; }
+  const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
+  __syncthreads();
+
+  if (tid == 0) {
+    uint32_t bytes = 0;
+    if (zlo_in || kind[4] == FK_SAME) bytes += 2 * NC * HX * 8;
+    if (zhi_in || kind[5] == FK_SAME) bytes += 2 * NC * HX * 8;
+    mbar_arrive_expect_tx(&S.bar, bytes);
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       if (zlo_in) bulk_g2s(&S.zlo[c][0][0], phi + boxoff + (size_t)c * L.cs + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
@@ -382,57 +418,75 @@ __global__ void __launch_bounds__(kThreads) k_stencil_fast(const __grid_constant
     __syncthreads();
   }
 
-  // value at ghosted tile coordinates (one coordinate may leave the tile)
-  auto at = [&](int i, int j, int kk) -> double {
-    const int c = (i + j + k0 + kk) & 1;
-    if (i < 0) return S.xlo[kk][j];
-    if (i >= NC) return S.xhi[kk][j];
-    if (j < 0) return S.ylo[c][kk][i >> 1];
-    if (j >= NC) return S.yhi[c][kk][i >> 1];
-    if (kk < 0) return S.zlo[c][j][i >> 1];
-    if (kk >= KT) return S.zhi[c][j][i >> 1];
-    return S.Ph[c][kk][j][i >> 1];
-  };
-
-  const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], lambda = P.lambda;
-  const double* __restrict__ in1 = (MODE == MODE_CRHS ? L.var[3] : L.var[1]) + boxoff;   // res (crhs) or rhs
-  double* __restrict__ out1 = (MODE == MODE_CRHS ? L.var[1] : L.var[3]) + boxoff;        // rhs (crhs) or res
-  double* __restrict__ out2 = L.var[2] + boxoff;                                         // old (crhs)
-  double vmax = 0.0;
-  int p = -1, ox = 0, oy = 0, oz = 0;
-  if (MODE == MODE_RESID_RESTRICT) {
-    p = L.parent[b];
-    const int off = L.coff[b];
-    ox = off & 1023; oy = (off >> 10) & 1023; oz = (off >> 20) & 1023;
-  }
-  constexpr int HC = NC / 2, NCOARSE = (KT / 2) * HC * HC;
-#pragma unroll 1
-  for (int cidx_ = tid; cidx_ < NCOARSE; cidx_ += kThreads) {
-    const int I = cidx_ % HC, J = (cidx_ / HC) % HC, Kc = cidx_ / (HC * HC);
-    double sphi = 0.0, sres = 0.0;
+  // ---- compute: one thread per coarse cell = 2x2x2 fine cells held in registers (8 + 24 shared-memory loads per
+  // block instead of 8 x 7).  Rows j and j+2 are 16 doubles apart = the same banks, so odd-J threads visit their
+  // two rows in the opposite order (slot s <-> dj = s ^ sw): a half-warp then reads rows 3 apart, conflict-free.
 #pragma unroll
-    for (int dk = 0; dk < 2; ++dk)
+  for (int it = 0; it < NIT; ++it) {
+    const int q = it * kThreads + tid;
+    const int I = q % HC, J = (q / HC) % HC, Kc = q / (HC * HC);
+    const int sw = J & 1;
+    double cur[8];
 #pragma unroll
-      for (int dj = 0; dj < 2; ++dj)
+    for (int e = 0; e < 8; ++e) cur[e] = nxt[e];
+    if (it + 1 < NIT) {
 #pragma unroll
-        for (int di = 0; di < 2; ++di) {
-          const int i = 2 * I + di, j = 2 * J + dj, kk = 2 * Kc + dk;
-          const double u0 = at(i, j, kk);
-          double lap = idx2 * (at(i - 1, j, kk) + at(i + 1, j, kk) - 2 * u0) + idy2 * (at(i, j - 1, kk) + at(i, j + 1, kk) - 2 * u0) +
-                       idz2 * (at(i, j, kk - 1) + at(i, j, kk + 1) - 2 * u0);
-          if (HELM) lap = lap - lambda * u0;
-          const size_t g = (size_t)((di + dj + dk) & 1) * L.cs + ((size_t)(k0 + kk) * NC + j) * HX + I;
-          if (MODE == MODE_CRHS) {
-            out1[g] = lap + in1[g];
-            out2[g] = u0;
-          } else {
-            const double r = in1[g] - lap;
-            out1[g] = r;
-            if (MODE == MODE_RESID_MAX) vmax = fmax(vmax, fabs(r));
-            else { sphi = sphi + u0; sres = sres + r; }
-          }
-        }
+      for (int e = 0; e < 8; ++e) nxt[e] = in1[goff(q + kThreads, e & 1, (e >> 1) & 1, e >> 2)];
+    }
+    double u[8], r[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int di = e & 1, dj = ((e >> 1) & 1) ^ sw, dk = e >> 2;
+      u[e] = S.Ph[(di + dj + dk) & 1][2 * Kc + dk][2 * J + dj][I];
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int di = e & 1, s = (e >> 1) & 1, dk = e >> 2;
+      const int dj = s ^ sw, j = 2 * J + dj, kk = 2 * Kc + dk;
+      const int oc = (di + dj + dk + 1) & 1;                       // colour of the six neighbours
+      const double u0 = u[e];
+      // x: the neighbour inside the block is u[e ^ 1]
+      double xo;
+      if (di == 0) xo = I > 0 ? S.Ph[oc][kk][j][I - 1] : S.xlo[kk][j];
+      else xo = I < HC - 1 ? S.Ph[oc][kk][j][I + 1] : S.xhi[kk][j];
+      const double xl = di ? u[e ^ 1] : xo, xh = di ? xo : u[e ^ 1];
+      // y: inside neighbour u[e ^ 2]; the outside row is j - 1 (dj = 0) or j + 1 (dj = 1)
+      const int jo = dj ? j + 1 : j - 1;
+      double yo;
+      if (jo < 0) yo = S.ylo[oc][kk][I];
+      else if (jo >= NC) yo = S.yhi[oc][kk][I];
+      else yo = S.Ph[oc][kk][jo][I];
+      const double yl = dj ? u[e ^ 2] : yo, yh = dj ? yo : u[e ^ 2];
+      // z: inside neighbour u[e ^ 4]
+      double zo;
+      if (dk == 0) zo = kk > 0 ? S.Ph[oc][kk - 1][j][I] : S.zlo[oc][j][I];
+      else zo = kk < KT - 1 ? S.Ph[oc][kk + 1][j][I] : S.zhi[oc][j][I];
+      const double zl = dk ? u[e ^ 4] : zo, zh = dk ? zo : u[e ^ 4];
+      double lap = idx2 * (xl + xh - 2 * u0) + idy2 * (yl + yh - 2 * u0) + idz2 * (zl + zh - 2 * u0);
+      if (HELM) lap = lap - lambda * u0;
+      const size_t g = goff(q, di, s, dk);
+      if (MODE == MODE_CRHS) {
+        out1[g] = lap + cur[e];
+        out2[g] = u0;
+      } else {
+        r[e] = cur[e] - lap;
+        out1[g] = r[e];
+        if (MODE == MODE_RESID_MAX) vmax = fmax(vmax, fabs(r[e]));
+      }
+    }
     if (MODE == MODE_RESID_RESTRICT && p >= 0) {
+      // 0.125 * sum(2x2x2) in Fortran element order (i fastest, then j, then k): undo the row swap
+      double sphi = 0.0, sres = 0.0;
+#pragma unroll
+      for (int dk = 0; dk < 2; ++dk)
+#pragma unroll
+        for (int dj = 0; dj < 2; ++dj)
+#pragma unroll
+          for (int di = 0; di < 2; ++di) {
+            const int ea = di | (dj << 1) | (dk << 2), eb = ea ^ 2;
+            sphi = sphi + (sw ? u[eb] : u[ea]);
+            sres = sres + (sw ? r[eb] : r[ea]);
+          }
       const int ic = ox + I, jc = oy + J, kc = oz + (k0 >> 1) + Kc;
       const size_t gc = (size_t)p * Lc.bs + (size_t)((ic + jc + kc) & 1) * Lc.cs + ((size_t)kc * NC + jc) * HX + (ic >> 1);
       Lc.var[0][gc] = 0.125 * sphi;
@@ -451,24 +505,38 @@ __global__ void __launch_bounds__(kThreads) k_stencil_fast(const __grid_constant
   }
 }
 
-template <int NC, int KT, int MODE, bool HELM>
+template <int NC, int KT, int MODE, bool HELM, int MB>
 bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(StencilSmem<NC, KT>);
   if (!configured) {
-    if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_stencil_fast<NC, KT, MODE, HELM><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot);
+  k_stencil_fast<NC, KT, MODE, HELM, MB><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot);
   return true;
 }
 
+// resident CTAs per SM the register allocation is tuned for (OMG_STENCIL_MB = 2 | 3 | 4 overrides, for tuning runs)
+inline int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e && *e ? atoi(e) : dflt;
+}
+template <int MODE, bool HELM>
+bool dispatch_stencil_h(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+  static const int mb = env_int("OMG_STENCIL_MB", 3);
+  if (L.nc == 16) {
+    if (mb == 2) return launch_stencil<16, 16, MODE, HELM, 2>(L, Lc, P, nboxes, maxslot, s);
+    if (mb == 4) return launch_stencil<16, 16, MODE, HELM, 4>(L, Lc, P, nboxes, maxslot, s);
+    return launch_stencil<16, 16, MODE, HELM, 3>(L, Lc, P, nboxes, maxslot, s);
+  }
+  if (L.nc == 32) return launch_stencil<32, 8, MODE, HELM, 2>(L, Lc, P, nboxes, maxslot, s);
+  return false;
+}
 template <int MODE>
 bool dispatch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
-  const bool helm = (P.op == OP_HELMH);
-  if (L.nc == 16) return helm ? launch_stencil<16, 16, MODE, true>(L, Lc, P, nboxes, maxslot, s) : launch_stencil<16, 16, MODE, false>(L, Lc, P, nboxes, maxslot, s);
-  if (L.nc == 32) return helm ? launch_stencil<32, 8, MODE, true>(L, Lc, P, nboxes, maxslot, s) : launch_stencil<32, 8, MODE, false>(L, Lc, P, nboxes, maxslot, s);
-  return false;
+  return P.op == OP_HELMH ? dispatch_stencil_h<MODE, true>(L, Lc, P, nboxes, maxslot, s)
+                          : dispatch_stencil_h<MODE, false>(L, Lc, P, nboxes, maxslot, s);
 }
 
 
@@ -479,10 +547,11 @@ bool dispatch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P,
 // face kind works), then every thread prolongs coarse cells onto 2x2x2 fine cells and adds them to phi.
 //   18 B per fine cell (read + write phi_f, 1/8 of phi_c and old_c) + 1 B for the stored coarse res.
 // =================================================================================================
-template <int NC>
-__global__ void __launch_bounds__(kThreads) k_corr_prolong_fast(const __grid_constant__ LevelDev Lf, const __grid_constant__ LevelDev Lc,
+template <int NC, int MB>
+__global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid_constant__ LevelDev Lf, const __grid_constant__ LevelDev Lc,
                                                                 const __grid_constant__ ParamsDev P) {
-  constexpr int HC = NC / 2, HX = NC / 2, PW = HC + 2;
+  constexpr int HC = NC / 2, HX = NC / 2, PW = HC + 2, NIT = HC * HC * HC / kThreads;
+  static_assert((HC * HC * HC) % kThreads == 0, "coarse cells must tile the CTA");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* corr = reinterpret_cast<double*>(smem_raw);       // [PW][PW][PW]
   const int tid = threadIdx.x, b = blockIdx.x;
@@ -490,51 +559,83 @@ __global__ void __launch_bounds__(kThreads) k_corr_prolong_fast(const __grid_con
   if (p == -1) return;
   const int off = Lf.coff[b];
   const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  double* __restrict__ phi = Lf.var[0] + (size_t)b * Lf.bs;
+  const int fcs = Lf.cs;
+  // offset of fine cell e = di | dj << 1 | dk << 2 of coarse cell q inside the fine box
+  auto goff = [&](int q, int e) -> int {
+    const int I = q % HC, J = (q / HC) % HC, K = q / (HC * HC);
+    const int di = e & 1, dj = (e >> 1) & 1, dk = e >> 2;
+    return ((di + dj + dk) & 1) * fcs + ((2 * K + dk) * NC + (2 * J + dj)) * HX + I;
+  };
+  // fine phi of this thread's first coarse cell: in flight while the correction patch is gathered
+  double nxt[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) nxt[e] = phi[goff(tid, e)];
+
   if (p <= -2) {   // parent on another rank: the patch arrived with the prolong exchange
     const double* __restrict__ patch = Lf.ppatch + (size_t)(-(p + 2)) * PW * PW * PW;
     for (int r = tid; r < PW * PW * PW; r += kThreads) corr[r] = patch[r];
-  } else
-  for (int r = tid; r < PW * PW * PW; r += kThreads) {
-    const int a = r % PW, bb = (r / PW) % PW, c = r / (PW * PW);
-    const int nedge = (a == 0 || a == PW - 1) + (bb == 0 || bb == PW - 1) + (c == 0 || c == PW - 1);
-    if (nedge > 1) continue;                                   // never read by the 7-point prolongation
-    const int ic = ox + a - 1, jc = oy + bb - 1, kc = oz + c - 1;
-    const double v = cell_at<GM_PHI>(Lc, P, Lc.var[0], nullptr, p, ic, jc, kc) - cell_at<GM_OLD>(Lc, P, Lc.var[2], nullptr, p, ic, jc, kc);
-    corr[r] = v;
-    if (nedge == 0) Lc.var[3][(size_t)p * Lc.bs + cidx(Lc, ic, jc, kc)] = v;   // res_c = phi_c - old_c on the parent (:396-398)
+  } else {
+    // (a) the child's octant of the parent: always interior cells; res_c = phi_c - old_c is stored there (:396-398)
+    const double* __restrict__ pc = Lc.var[0] + (size_t)p * Lc.bs;
+    const double* __restrict__ po = Lc.var[2] + (size_t)p * Lc.bs;
+    double* __restrict__ pr = Lc.var[3] + (size_t)p * Lc.bs;
+    const int ccs = Lc.cs;
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int r = it * kThreads + tid;
+      const int a = r % HC, bb = (r / HC) % HC, c = r / (HC * HC);
+      const int ic = ox + a, jc = oy + bb, kc = oz + c;
+      const int g = ((ic + jc + kc) & 1) * ccs + (kc * NC + jc) * HX + (ic >> 1);
+      const double v = pc[g] - po[g];
+      corr[((c + 1) * PW + (bb + 1)) * PW + (a + 1)] = v;
+      pr[g] = v;
+    }
+    // (b) the six HC x HC halo faces of the patch: parent cells of the neighbouring octant or parent ghost cells
+    // (edges and corners of the patch are never read by the 7-point prolongation)
+    for (int r = tid; r < 6 * HC * HC; r += kThreads) {
+      const int f = r / (HC * HC), t = r % (HC * HC), t1 = t % HC + 1, t2 = t / HC + 1;
+      const int e = (f & 1) ? PW - 1 : 0;
+      int a, bb, c;
+      if (f < 2) { a = e; bb = t1; c = t2; } else if (f < 4) { a = t1; bb = e; c = t2; } else { a = t1; bb = t2; c = e; }
+      const int ic = ox + a - 1, jc = oy + bb - 1, kc = oz + c - 1;
+      corr[(c * PW + bb) * PW + a] = cell_at<GM_PHI>(Lc, P, Lc.var[0], nullptr, p, ic, jc, kc) - cell_at<GM_OLD>(Lc, P, Lc.var[2], nullptr, p, ic, jc, kc);
+    }
   }
   __syncthreads();
-  double* __restrict__ phi = Lf.var[0] + (size_t)b * Lf.bs;
-#pragma unroll 1
-  for (int r = tid; r < HC * HC * HC; r += kThreads) {
-    const int I = r % HC, J = (r / HC) % HC, K = r / (HC * HC);
-    const int q = ((K + 1) * PW + (J + 1)) * PW + (I + 1);
-    const double f0 = 0.25 * corr[q];
-    const double flx = 0.25 * corr[q - 1], fhx = 0.25 * corr[q + 1];
-    const double fly = 0.25 * corr[q - PW], fhy = 0.25 * corr[q + PW];
-    const double flz = 0.25 * corr[q - PW * PW], fhz = 0.25 * corr[q + PW * PW];
+#pragma unroll(NIT <= 4 ? NIT : 2)
+  for (int it = 0; it < NIT; ++it) {
+    const int q = it * kThreads + tid;
+    double cur[8];
 #pragma unroll
-    for (int dk = 0; dk < 2; ++dk)
+    for (int e = 0; e < 8; ++e) cur[e] = nxt[e];
+    if (it + 1 < NIT) {
 #pragma unroll
-      for (int dj = 0; dj < 2; ++dj)
+      for (int e = 0; e < 8; ++e) nxt[e] = phi[goff(q + kThreads, e)];
+    }
+    const int I = q % HC, J = (q / HC) % HC, K = q / (HC * HC);
+    const int c = ((K + 1) * PW + (J + 1)) * PW + (I + 1);
+    const double f0 = 0.25 * corr[c];
+    const double flx = 0.25 * corr[c - 1], fhx = 0.25 * corr[c + 1];
+    const double fly = 0.25 * corr[c - PW], fhy = 0.25 * corr[c + PW];
+    const double flz = 0.25 * corr[c - PW * PW], fhz = 0.25 * corr[c + PW * PW];
 #pragma unroll
-        for (int di = 0; di < 2; ++di) {
-          const double fine = f0 + (di ? fhx : flx) + (dj ? fhy : fly) + (dk ? fhz : flz);
-          const size_t g = (size_t)((di + dj + dk) & 1) * Lf.cs + ((size_t)(2 * K + dk) * NC + (2 * J + dj)) * HX + I;
-          phi[g] = phi[g] + fine;
-        }
+    for (int e = 0; e < 8; ++e) {
+      const double fine = f0 + ((e & 1) ? fhx : flx) + ((e & 2) ? fhy : fly) + ((e & 4) ? fhz : flz);
+      phi[goff(q, e)] = cur[e] + fine;
+    }
   }
 }
 
-template <int NC>
+template <int NC, int MB>
 bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(double) * (NC / 2 + 2) * (NC / 2 + 2) * (NC / 2 + 2);
   if (!configured) {
-    if (cudaFuncSetAttribute(k_corr_prolong_fast<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(k_corr_prolong_fast<NC, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_corr_prolong_fast<NC><<<Lf.nb, kThreads, smem, s>>>(Lf, Lc, P);
+  k_corr_prolong_fast<NC, MB><<<Lf.nb, kThreads, smem, s>>>(Lf, Lc, P);
   return true;
 }
 
@@ -545,7 +646,8 @@ namespace omgf {
 bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, cudaStream_t s) {
   if (!all_fast || L.nb == 0) return false;
   if (P.op != OP_LPL && P.op != OP_HELMH) return false;
-  if (L.nc == 16) return launch_smooth<16, 16>(L, P, colour, s);
+  static const int kt = env_int("OMG_SMOOTH_KT", 16);
+  if (L.nc == 16) return kt == 8 ? launch_smooth<16, 8>(L, P, colour, s) : launch_smooth<16, 16>(L, P, colour, s);
   if (L.nc == 32) return launch_smooth<32, 8>(L, P, colour, s);
   return false;
 }
@@ -566,8 +668,9 @@ bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s) 
 }
 bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool, cudaStream_t s) {
   if (Lf.nb == 0 || Lc.nc != Lf.nc) return false;
-  if (Lf.nc == 16) return launch_corr_prolong<16>(Lf, Lc, P, s);
-  if (Lf.nc == 32) return launch_corr_prolong<32>(Lf, Lc, P, s);
+  static const int mb = env_int("OMG_PROLONG_MB", 4);
+  if (Lf.nc == 16) return mb == 4 ? launch_corr_prolong<16, 4>(Lf, Lc, P, s) : mb == 2 ? launch_corr_prolong<16, 2>(Lf, Lc, P, s) : launch_corr_prolong<16, 3>(Lf, Lc, P, s);
+  if (Lf.nc == 32) return launch_corr_prolong<32, 3>(Lf, Lc, P, s);
   return false;
 }
 

@@ -23,6 +23,17 @@ __global__ void __launch_bounds__(kThreads) k_smooth(const __grid_constant__ Lev
   do_smooth<OP>(L, P, blockIdx.x, colour, threadIdx.x, blockDim.x);
 }
 
+// mg_smoother_gs: ghost snapshot (= the ghost fill preceding the sweep) and the in-box lexicographic sweep
+__global__ void __launch_bounds__(kThreads) k_gs_snapshot(const __grid_constant__ LevelDev L,
+                                                          const __grid_constant__ ParamsDev P) {
+  do_gs_snapshot(L, P, blockIdx.x, threadIdx.x, blockDim.x);
+}
+template <int OP>
+__global__ void __launch_bounds__(kThreads) k_smooth_gs(const __grid_constant__ LevelDev L,
+                                                        const __grid_constant__ ParamsDev P) {
+  do_gs_sweep<OP>(L, P, blockIdx.x, threadIdx.x, blockDim.x);
+}
+
 template <int OP>
 __global__ void __launch_bounds__(kThreads) k_resid(const __grid_constant__ LevelDev L,
                                                     const __grid_constant__ ParamsDev P, double* maxslot) {
@@ -176,7 +187,11 @@ __global__ void k_scale_scalar(double* acc, double inv_volume) { *acc = *acc / i
 // ------------------------------------------------------------------ tail interpreter ---------
 template <int OP>
 __device__ void tail_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
-  if (L.nc & 1) {   // odd box size: Jacobi between boxes, see do_smooth_staged
+  if (P.smoother == 1) {   // mg_smoother_gs
+    for (int b = 0; b < L.nb; ++b) do_gs_snapshot(L, P, b, tid, nthr);
+    __syncthreads();
+    for (int b = 0; b < L.nb; ++b) do_gs_sweep<OP>(L, P, b, tid, nthr);
+  } else if (L.nc & 1) {   // odd box size: Jacobi between boxes, see do_smooth_staged
     for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 0, tid, nthr);
     __syncthreads();
     for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 1, tid, nthr);
@@ -186,7 +201,7 @@ __device__ void tail_smooth(const LevelDev& L, const ParamsDev& P, int colour, i
 }
 
 template <int OP>
-__device__ void tail_run(const LevelDev* __restrict__ levels, const ParamsDev& P, const TailOp* __restrict__ ops, int n_ops,
+__device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailOp* __restrict__ ops, int n_ops,
                          double* scal, double* red) {
   const int tid = threadIdx.x, nthr = blockDim.x;
   for (int o = 0; o < n_ops; ++o) {
@@ -249,10 +264,50 @@ __device__ void tail_run(const LevelDev* __restrict__ levels, const ParamsDev& P
   }
 }
 
+// The tail levels are tiny (<= tail_cells cells each), so when phi, rhs, old and res of ALL of them fit in shared
+// memory (n_stage > 0) they are staged there for the whole launch: the interpreter then runs on copies of the level
+// descriptors whose var[0..3] point into shared memory (generic addressing), and every op of the coarse end of the
+// cycle costs shared-memory instead of L2 latency.  Everything else (face tables, planes, eps) stays in global memory.
+constexpr int kMaxStageLevels = 12;
 __global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ levels, const __grid_constant__ ParamsDev P,
-                                               const TailOp* __restrict__ ops, int n_ops, double* scal) {
+                                               const TailOp* __restrict__ ops, int n_ops, double* scal, int n_stage) {
   __shared__ double red[32];
-  OMG_SWITCH_OP(P.op, tail_run<OP>(levels, P, ops, n_ops, scal, red));
+  __shared__ LevelDev slev[kMaxStageLevels];
+  extern __shared__ __align__(16) double stage[];
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  if (n_stage > 0) {
+    if (tid == 0) {
+      size_t off = 0;
+      for (int l = 0; l < n_stage; ++l) {
+        slev[l] = levels[l];
+        const size_t n = (size_t)levels[l].nb * levels[l].bs;
+        for (int v = 0; v < 4; ++v) { slev[l].var[v] = stage + off; off += n; }
+      }
+    }
+    __syncthreads();
+    for (int l = 0; l < n_stage; ++l) {
+      const int n = levels[l].nb * levels[l].bs;
+      for (int v = 0; v < 4; ++v) {
+        const double* __restrict__ src = levels[l].var[v];
+        double* dst = slev[l].var[v];
+        for (int i = tid; i < n; i += nthr) dst[i] = src[i];
+      }
+    }
+    __syncthreads();
+  }
+  const LevelDev* lv = n_stage > 0 ? slev : levels;
+  OMG_SWITCH_OP(P.op, tail_run<OP>(lv, P, ops, n_ops, scal, red));
+  if (n_stage > 0) {
+    __syncthreads();
+    for (int l = 0; l < n_stage; ++l) {
+      const int n = levels[l].nb * levels[l].bs;
+      for (int v = 0; v < 4; ++v) {
+        double* __restrict__ dst = levels[l].var[v];
+        const double* src = slev[l].var[v];
+        for (int i = tid; i < n; i += nthr) dst[i] = src[i];
+      }
+    }
+  }
 }
 
 // ------------------------------------------------------------------ host <-> device layout ----
@@ -321,6 +376,11 @@ void smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s) {
   if (L.nb == 0) return;
   OMG_SWITCH_OP(P.op, (k_smooth<OP><<<L.nb, kThreads, 0, s>>>(L, P, colour)));
 }
+void smooth_gs(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
+  if (L.nb == 0) return;
+  k_gs_snapshot<<<L.nb, kThreads, 0, s>>>(L, P);
+  OMG_SWITCH_OP(P.op, (k_smooth_gs<OP><<<L.nb, kThreads, 0, s>>>(L, P)));
+}
 void resid(const LevelDev& L, const ParamsDev& P, double* maxslot, cudaStream_t s) {
   if (L.nb == 0) return;
   OMG_SWITCH_OP(P.op, (k_resid<OP><<<L.nb, kThreads, 0, s>>>(L, P, maxslot)));
@@ -379,8 +439,16 @@ void box_sums(const LevelDev& L, int iv, double w, double* partial, cudaStream_t
 }
 void final_sum(const double* partial, int n, double* acc, cudaStream_t s) { if (n) k_final_sum<<<1, 1024, 0, s>>>(partial, n, acc); }
 void div_scalar(double* acc, double denom, cudaStream_t s) { k_scale_scalar<<<1, 1, 0, s>>>(acc, denom); }
-void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, cudaStream_t s) {
-  if (n_ops) k_tail<<<1, 1024, 0, s>>>(levels, P, ops, n_ops, scal);
+void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, int n_stage, size_t stage_bytes,
+          cudaStream_t s) {
+  if (!n_ops) return;
+  static size_t configured = 0;
+  if (n_stage > kMaxStageLevels || stage_bytes > (size_t)200 * 1024) { n_stage = 0; stage_bytes = 0; }
+  if (stage_bytes > configured) {
+    if (cudaFuncSetAttribute(k_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes) != cudaSuccess) { n_stage = 0; stage_bytes = 0; }
+    else configured = stage_bytes;
+  }
+  k_tail<<<1, 1024, stage_bytes, s>>>(levels, P, ops, n_ops, scal, n_stage);
 }
 void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, cudaStream_t s) {
   if (n) k_unpack<<<n, kThreads, 0, s>>>(L, iv, boxes, stage, with_faces);

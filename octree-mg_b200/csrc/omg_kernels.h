@@ -19,6 +19,8 @@ enum ScalSlot : int {
 
 namespace omgk {
 void smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s);
+// mg_smoother_gs: ghost snapshot into L.faces[0] + in-box lexicographic sweep (two launches)
+void smooth_gs(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
 void resid(const LevelDev& L, const ParamsDev& P, double* maxslot, cudaStream_t s);
 void restrict2(const LevelDev& Lf, const LevelDev& Lc, int iv0, int iv1, cudaStream_t s);
 void crhs(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
@@ -38,7 +40,9 @@ void sub_scalar(double* p, size_t n, const double* mean, cudaStream_t s);
 void box_sums(const LevelDev& L, int iv, double w, double* partial, cudaStream_t s);
 void final_sum(const double* partial, int n, double* acc, cudaStream_t s);
 void div_scalar(double* acc, double denom, cudaStream_t s);
-void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, cudaStream_t s);
+// n_stage > 0: the first n_stage levels are staged in shared memory for the launch (stage_bytes = 4 * 8 * their cells)
+void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, int n_stage, size_t stage_bytes,
+          cudaStream_t s);
 void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, cudaStream_t s);
 void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, cudaStream_t s);
 }  // namespace omgk

@@ -33,6 +33,37 @@ __device__ void do_smooth_staged(const LevelDev& L, const ParamsDev& P, int b, i
   }
 }
 
+// ---- mg_smoother_gs: lexicographic Gauss-Seidel inside each box, Jacobi between boxes -----------------
+// (box_gs_* with redblack = .false., e.g. src/m_laplacian.f90:99-111: i0 = 1, stride 1, loop order k, j, i.)
+// The reference sweeps every box against ghost cells filled BEFORE the sweep, so the ghost faces are first
+// snapshotted (do_gs_snapshot = the ghost fill), then each box is swept in place.  A lexicographic sweep only
+// depends on already-updated lower neighbours (i-1, j-1, k-1) and not-yet-updated upper ones, so updating the
+// hyperplanes i + j + k = w for w = 0, 1, ... in turn performs exactly the same arithmetic on the same values.
+__device__ void do_gs_snapshot(const LevelDev& L, const ParamsDev& P, int b, int tid, int nthr) {
+  const int nc = L.nc;
+  double* out = L.faces[0] + (size_t)b * 6 * nc * nc;
+  for (int idx = tid; idx < 6 * nc * nc; idx += nthr) {
+    const int f = idx / (nc * nc), r = idx - f * nc * nc, t1 = r % nc, t2 = r / nc;
+    const int g = (f & 1) ? nc : -1;
+    int i, j, k;
+    if (f < 2) { i = g; j = t1; k = t2; } else if (f < 4) { i = t1; j = g; k = t2; } else { i = t1; j = t2; k = g; }
+    out[idx] = cell_at<GM_PHI>(L, P, L.var[0], nullptr, b, i, j, k);
+  }
+}
+// all threads of the CTA must call this (it synchronises between hyperplanes)
+template <int OP>
+__device__ void do_gs_sweep(const LevelDev& L, const ParamsDev& P, int b, int tid, int nthr) {
+  const int nc = L.nc;
+  double* phi = L.var[0] + (size_t)b * L.bs;
+  for (int w = 0; w <= 3 * (nc - 1); ++w) {
+    for (int idx = tid; idx < nc * nc; idx += nthr) {
+      const int j = idx % nc, k = idx / nc, i = w - j - k;
+      if (i >= 0 && i < nc) phi[cidx(L, i, j, k)] = gs_at<OP, GM_STORED>(L, P, b, i, j, k);
+    }
+    __syncthreads();
+  }
+}
+
 // residual_box src/m_multigrid.f90:426-436; returns the thread-local max |res|
 template <int OP>
 __device__ double do_resid(const LevelDev& L, const ParamsDev& P, int b, int tid, int nthr) {

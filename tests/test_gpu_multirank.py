@@ -122,3 +122,14 @@ def test_coarse_level_collapse(oracle, product):
     check(P.run_cycles(orc, 3, False), P.run_cycles(mg, 3, False))
     check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
     assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("n_cpu", [2, 4])
+def test_gs_smoother_ranks(oracle, product, n_cpu):
+    """mg_smoother_gs across ranks: with Gauss-Seidel the result depends on the box size but not on the number of
+    ranks; the ghost snapshot taken before each sweep reads remote faces from the exchanged plane pool."""
+    orc, _ = P.uniform_problem(oracle.OracleMg, 32, 8, smoother=P.mg_smoother_gs, n_cpu=n_cpu)
+    mg, _ = P.uniform_problem(group_cls(product, n_cpu), 32, 8, smoother=P.mg_smoother_gs)
+    check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    check(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)

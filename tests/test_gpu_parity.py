@@ -164,12 +164,42 @@ def test_resident_mode_and_graph_replay(oracle, product):
 
 def test_no_cpu_fallback_errors(product):
     """error behaviour of the boundary (the reference error-stops; the C ABI returns codes + messages)."""
-    mg = product.Mg(P.mg_laplacian, P.mg_smoother_gs)
+    mg = product.Mg(P.mg_laplacian, P.mg_smoother_gsrb)
     mg.mg_set_methods()
     mg.mg_build_rectangle([32] * 3, 8, [1.0 / 32] * 3, [0.0] * 3, [False] * 3)
     mg.mg_load_balance()
     mg.mg_allocate_storage()
-    with pytest.raises(product.MgError, match="mg_smoother_gs"):
+    mg.set_int("smoother_type", 7)
+    with pytest.raises(product.MgError, match="unsupported smoother"):
         mg.mg_fas_vcycle()
+    mg.set_int("smoother_type", P.mg_smoother_gsrb)
     with pytest.raises(product.MgError, match="lvl > highest_lvl"):
         mg.mg_fill_ghost_cells_lvl(5, P.mg_iphi)
+
+
+@pytest.mark.parametrize("fmg", [False, True])
+@pytest.mark.parametrize("op,bc,lam,n,box", [
+    (P.mg_laplacian, "callback", 0.0, 32, 8),       # the literal setting of tests/test_uniform_grid.f90:64
+    (P.mg_laplacian, "callback", 0.0, 64, 16),
+    (P.mg_helmholtz, "neumann0", 1.0, 32, 8),
+    (P.mg_vlaplacian, "mixed", 0.0, 32, 8),
+    (P.mg_ahelmholtz, "mixed", 0.5, 32, 4),
+])
+def test_gs_smoother(oracle, product, op, bc, lam, n, box, fmg):
+    """mg_smoother_gs, the reference's default and what its test programs hard-code: lexicographic
+    Gauss-Seidel inside each box against ghost cells filled before the sweep.  The device sweeps hyperplanes
+    i + j + k = const, which performs the same arithmetic on the same values: bitwise equal to the oracle."""
+    orc, i_sol = P.uniform_problem(oracle.OracleMg, n, box, operator_type=op, bc=bc, lam=lam, smoother=P.mg_smoother_gs)
+    mg, _ = P.uniform_problem(product.Mg, n, box, operator_type=op, bc=bc, lam=lam, smoother=P.mg_smoother_gs)
+    assert mg.lowest_lvl == orc.lowest_lvl
+    check_histories(P.run_cycles(orc, 3, fmg), P.run_cycles(mg, 3, fmg))
+    assert_state_equal(orc, mg)
+
+
+def test_gs_smoother_refinement(oracle, product):
+    """tests/test_refinement.f90 as shipped (mg_smoother_gs, :65) on the AMR grid."""
+    orc, i_sol = P.refinement_problem(oracle.OracleMg, 3, 8, 32, smoother=P.mg_smoother_gs)
+    mg, _ = P.refinement_problem(product.Mg, 3, 8, 32, smoother=P.mg_smoother_gs)
+    check_histories(P.run_cycles(orc, 3, True), P.run_cycles(mg, 3, True))
+    check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
