@@ -35,6 +35,23 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(n, box):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE finest-level smoother launch, from the committed
+    `ncu --set full` capture of this very command (profiles/, tools/ncu_summary.py); None for other workloads."""
+    if (n, box) != (512, 16):
+        return None, None
+    cands = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("ncu_smooth_finest.txt"))
+    if not cands:
+        return None, None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    for line in open(os.path.join(ROOT, "profiles", cands[-1])):
+        f = line.split()
+        if len(f) >= 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            tot += float(f[1]) * unit.get(f[2], 1.0)
+    return (tot or None), "profiles/" + cands[-1]
+
+
 class ClockSampler:
     def __init__(self, index=0):
         self.rows, self.index, self.proc = [], index, None
@@ -125,6 +142,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
     ap.add_argument("--no-fast", action="store_true", help="general-path kernels only")
+    ap.add_argument("--op", default="laplacian", choices=["laplacian", "vlaplacian", "helmholtz", "vhelmholtz"],
+                    help="operator (BASELINE.json configs[3]: vlaplacian / helmholtz with Neumann BC); default = the headline Laplacian")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (omg_set_option), repeatable")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -162,14 +181,23 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     # tests/test_performance.f90:51-66 without host cc arrays (the run is device-resident)
-    mg = om.Mg(P.mg_laplacian, P.mg_smoother_gsrb, n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
+    op = {"laplacian": P.mg_laplacian, "vlaplacian": P.mg_vlaplacian, "helmholtz": P.mg_helmholtz, "vhelmholtz": P.mg_vhelmholtz}[args.op]
+    mg = om.Mg(op, P.mg_smoother_gsrb, n_extra_vars=P.n_eps(op), n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
     mg.set_int("host_cc", 0)
+    if args.op != "laplacian":
+        config["workload"] = config["workload"].replace("7-point Laplacian", "%s (eps = 1, lambda = 1), Neumann-0 BC%s" % (
+            args.op, " + Dirichlet on -x" if args.op == "vlaplacian" else ""))
+        if op in (P.mg_helmholtz, P.mg_vhelmholtz):
+            mg.set_lambda(1.0)
     collapse = args.collapse if args.collapse >= 0 else 128
     if world > 1:
         mg.set_int("coarse_collapse_boxes", collapse)
         config["coarse_collapse_boxes_per_rank"] = collapse
     for nb in range(1, 7):
-        mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
+        if args.op == "laplacian" or (args.op == "vlaplacian" and nb == 1):
+            mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
+        else:
+            mg.set_bc(nb, P.mg_iphi, P.mg_bc_neumann, 0.0)
     mg.mg_set_methods()
     mg.mg_build_rectangle(dims, args.box, [1.0 / dims[0]] * 3, [0.0] * 3, [False] * 3)
     mg.mg_load_balance()
@@ -188,6 +216,8 @@ def main():
     # device-resident initial state: rhs = 1 on the interior of every level, phi = 0 (no host transfer needed)
     mg._gck(G.omg_set_var_const(gpu, P.mg_irhs, -20, 20, 1.0, 1))
     mg._gck(G.omg_set_var_const(gpu, P.mg_iphi, -20, 20, 0.0, 0))
+    if P.n_eps(op):
+        mg._gck(G.omg_set_var_const(gpu, P.mg_iveps, -20, 20, 1.0, 0))     # eps = 1 incl. ghost faces
     if args.tail_cells >= 0:
         mg.set_option("tail_cells", args.tail_cells)
     if args.no_graph:
@@ -233,11 +263,12 @@ def main():
     prof = {k: float(G.omg_last_ms(gpu, k.encode())) for k in ("smooth", "resid_restrict", "corr_prolong", "resid")}
     mg.set_option("profile", 0)
     peak, peak_src = peaks()
+    traffic, traffic_src = ncu_traffic(args.n, args.box)
     cells_per_rank = dof / world
     achieved = SMOOTH_BYTES_PER_CELL * cells_per_rank / (sm_ms * 1e-3) / 1e9 if sm_ms > 0 else None
     roofline = {"bound": "hbm", "kernel": "gsrb colour half-sweep, finest level (%d launches timed)" % n_sm,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": SMOOTH_BYTES_PER_CELL * cells_per_rank,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": SMOOTH_BYTES_PER_CELL * cells_per_rank,
                 "ms_per_launch": sm_ms, "finest_level_ms": prof}
     value = dof * args.steps / (ms * 1e-3) / 1e9
     cycle_frac = (BYTES_PER_DOF_VCYCLE + (BYTES_PER_DOF_MAXRES if args.max_res else 0.0)) * value / peak / world

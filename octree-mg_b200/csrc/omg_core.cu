@@ -42,7 +42,7 @@ template <class T> struct DevBuf {
 enum StepKind : int {
   S_SMOOTH, S_RESID, S_RESTRICT, S_CRHS, S_OLDPL, S_CORR_PROLONG, S_RB_FILL, S_COPY_OLD, S_COARSE_SOLVE,
   S_TAIL, S_ZERO_PHI, S_SUBMEAN, S_CLEAR_SLOT, S_COPY_SLOT, S_HALO, S_XRESTRICT, S_XPROLONG, S_ALLREDUCE_MAX,
-  S_RESID_RESTRICT
+  S_RESID_RESTRICT, S_HALO_FORK, S_HALO_JOIN
 };
 struct Step { int kind, l, a, b, c; };
 
@@ -72,6 +72,10 @@ struct LevelHost {
   DevBuf<double> d_gpl, d_gpl_old, d_bcpl;
   DevBuf<double> d_var[OMG_MAXV], d_faces[OMG_MAXV];
   LevelDev dev;
+  // boxes with a same-level neighbour on another rank (they send and receive ghost faces) and the rest: the halo
+  // exchange of a colour half-sweep overlaps the half-sweep of the interior boxes
+  std::vector<int> h_bnd, h_int;
+  DevBuf<int> d_bnd, d_int;
   bool all_fast = false;                // every face of every box is FK_SAME or FK_PHYS (fast kernels apply)
 };
 
@@ -82,6 +86,8 @@ struct Program { std::vector<Step> steps; std::vector<TailOp> ops; DevBuf<TailOp
 struct omg_handle {
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;          // halo exchanges that overlap interior smoothing
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::string err;
   // tree
   bool have_tree = false;
@@ -104,7 +110,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -136,7 +142,7 @@ void free_levels(omg_handle* h) {
   for (LevelHost& L : h->levels) {
     L.d_fkind.free(); L.d_farg.free(); L.d_ftype.free(); L.d_fkind_old.free(); L.d_farg_old.free();
     L.d_parent.free(); L.d_coff.free(); L.d_parents.free(); L.d_leaves.free(); L.d_rb.free(); L.d_oldpl.free();
-    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free();
+    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free(); L.d_bnd.free(); L.d_int.free();
     for (int v = 0; v < OMG_MAXV; ++v) { L.d_var[v].free(); L.d_faces[v].free(); }
     L.xg.free(); L.xr.free(); L.xp.free();
   }
@@ -261,6 +267,12 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
       const int id = L.ids[b];
       const bool is_parent = has_children(h, id);
       (is_parent ? L.h_parents : L.h_leaves).push_back(b);
+      bool on_partition_face = false;
+      for (int f = 0; f < 6; ++f) {
+        const int nbid = h->neighbors[(size_t)(id - 1) * 6 + f];
+        if (nbid > 0 && h->rank[nbid - 1] != me) on_partition_face = true;
+      }
+      (on_partition_face ? L.h_bnd : L.h_int).push_back(b);
       const int p = h->parent[id - 1];
       if (p > 0 && h->rank[p - 1] == me) L.h_parent[b] = h->loc[p];
       L.h_coff[b] = coff_of(id, lvl);
@@ -366,6 +378,7 @@ void sync_meta(omg_handle* h) {
       L.d_parent.upload(L.h_parent, s); L.d_coff.upload(L.h_coff, s);
       L.d_parents.upload(L.h_parents, s); L.d_leaves.upload(L.h_leaves, s);
       L.d_rb.upload(L.h_rb, s); L.d_oldpl.upload(L.h_oldpl, s);
+      L.d_bnd.upload(L.h_bnd, s); L.d_int.upload(L.h_int, s);
       L.d_bcpl.upload(L.h_bcpl, s);
       for (PhasePlan* X : {&L.xg, &L.xr, &L.xp}) { X->d_sdesc.upload(X->h_sdesc, s); X->d_rdesc.upload(X->h_rdesc, s); }
       if (L.xp.d_recv.n) CK(cudaMemsetAsync(L.xp.d_recv.p, 0, L.xp.d_recv.n * sizeof(double), s));
@@ -416,15 +429,31 @@ struct Builder {
   void step(int kind, int lvl, int a = 0, int b = 0, int c = 0) { flush(); P.steps.push_back({kind, lvl, a, b, c}); }
 
   // mg_fill_ghost_cells_lvl(lvl, mg_iphi): only ghost values with remote inputs are materialised
-  void gf(int lvl) {
-    if (h->L(lvl).xg.any) step(S_HALO, lvl, (lvl > h->lowest && h->gz[lvl - 1 - OMG_LVL_LO]) ? 1 : 0);
+  int halo_flag(int lvl) const { return (lvl > h->lowest && h->gz[lvl - 1 - OMG_LVL_LO]) ? 1 : 0; }
+  void gf_local(int lvl) {
     if (!h->L(lvl).h_rb.empty()) emit(lvl, TOP_RB_FILL, S_RB_FILL, h->gz[lvl - 1 - OMG_LVL_LO] ? 1 : 0);
     h->gz[lvl - OMG_LVL_LO] = false;
   }
-  // smooth_boxes src/m_multigrid.f90:404-424
+  void gf(int lvl) {
+    if (h->L(lvl).xg.any) step(S_HALO, lvl, halo_flag(lvl));
+    gf_local(lvl);
+  }
+  // smooth_boxes src/m_multigrid.f90:404-424.  On a distributed level a red-black half-sweep runs boundary-first:
+  // boxes on partition faces, then [pack + NCCL exchange on the second stream || the interior boxes], then join
+  // (a GSRB half-sweep reads only the other colour, so the two subsets are independent; the decision uses the
+  // replicated tree only, so every rank emits the same steps).
   void smooth_boxes(int lvl, int n_cycle) {
     const int sub = (h->params.smoother_type == 2) ? 2 : 1;
-    for (int n = 1; n <= n_cycle * sub; ++n) { emit(lvl, TOP_SMOOTH, S_SMOOTH, (n - 1) & 1); gf(lvl); }
+    const bool split = h->overlap && !h->profile && sub == 2 && h->L(lvl).xg.any && !h->L(lvl).tail;
+    for (int n = 1; n <= n_cycle * sub; ++n) {
+      if (split) {
+        step(S_SMOOTH, lvl, (n - 1) & 1, 1);
+        step(S_HALO_FORK, lvl, halo_flag(lvl));
+        step(S_SMOOTH, lvl, (n - 1) & 1, 2);
+        step(S_HALO_JOIN, lvl);
+        gf_local(lvl);
+      } else { emit(lvl, TOP_SMOOTH, S_SMOOTH, (n - 1) & 1); gf(lvl); }
+    }
   }
   // update_coarse :347-384
   void update_coarse(int lvl) {
@@ -562,8 +591,12 @@ void exec_steps(omg_handle* h, Program& P) {
     switch (st.kind) {
       case S_SMOOTH: {
         LevelHost& L = h->L(st.l);
+        const int* list = st.b == 1 ? L.d_bnd.p : st.b == 2 ? L.d_int.p : nullptr;
+        const int nlist = st.b == 1 ? (int)L.h_bnd.size() : st.b == 2 ? (int)L.h_int.size() : 0;
+        if (st.b && nlist == 0) break;
         if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; }
-        else if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, s))) omgk::smooth(L.dev, PD, st.a, s);
+        else if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, s)))
+          omgk::smooth(L.dev, PD, st.a, st.b ? list : nullptr, nlist, s);
         h->launches++;
       } break;
       case S_RESID: {
@@ -609,6 +642,13 @@ void exec_steps(omg_handle* h, Program& P) {
       case S_CLEAR_SLOT: CK(cudaMemsetAsync(h->d_scal.p + st.a, 0, sizeof(double), s)); break;
       case S_COPY_SLOT: CK(cudaMemcpyAsync(h->d_scal.p + st.a, h->d_scal.p + st.b, sizeof(double), cudaMemcpyDeviceToDevice, s)); break;
       case S_HALO: exchange_ghost(h, st.l, st.a, s); break;
+      case S_HALO_FORK:
+        CK(cudaEventRecord(h->ev_fork, s));
+        CK(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+        exchange_ghost(h, st.l, st.a, h->stream2);
+        CK(cudaEventRecord(h->ev_join, h->stream2));
+        break;
+      case S_HALO_JOIN: CK(cudaStreamWaitEvent(s, h->ev_join, 0)); break;
       case S_XRESTRICT: exchange_restrict(h, st.l, st.a, st.b, s); break;
       case S_XPROLONG: exchange_prolong(h, st.l, s); break;
       case S_ALLREDUCE_MAX: need_comm(h); omg_comm_allreduce(h->comm, h->d_scal.p + st.a, OMG_RED_MAX, s); break;
@@ -877,6 +917,8 @@ int omg_create(int device, omg_handle** out) {
   h->device = device;
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return 3; }
   cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
+  cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+  cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming); cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
   for (int v = 0; v < OMG_MAXV; ++v) for (int f = 0; f < 6; ++f) { h->bc_type[v][f] = -10; h->bc_value[v][f] = 0.0; }
   // defaults of type(mg_t), src/m_data_structures.f90:300-327
   h->params.operator_type = 1; h->params.smoother_type = 1; h->params.geometry_type = 1;
@@ -902,6 +944,8 @@ int omg_destroy(omg_handle* h) {
     if (h->stage_ev[q]) cudaEventDestroy(h->stage_ev[q]);
   }
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+  cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
+  cudaStreamDestroy(h->stream2);
   cudaStreamDestroy(h->stream);
   delete h;
   return 0;
@@ -1176,6 +1220,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "fast_kernels") h->fast_kernels = value;
     else if (k == "graph_multi") h->graph_multi = value;
     else if (k == "tail_smem") h->tail_smem = value;
+    else if (k == "overlap") h->overlap = value;
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
     else if (k == "tail_cells") { h->tail_cells = value; if (h->have_tree) compute_tail(h); }
     else fail("unknown option " + k);

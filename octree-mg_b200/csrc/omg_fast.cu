@@ -9,6 +9,7 @@
 
 #include <cstdint>
 #include <cstdlib>
+#include <type_traits>
 
 namespace {
 
@@ -59,25 +60,37 @@ __device__ __forceinline__ void bc_coeffs(int type, double dr, int f, double& c0
 //   algorithmic bytes: 12 B per cell of the level per launch
 // Shared memory per CTA (NC=16, KT=16): 16 KiB tile + 6 KiB ghost layer.
 // =================================================================================================
+//
+// VC = true: the variable-coefficient operators (box_gs_vlpl src/m_vlaplacian.f90:51-128, box_gs_vhelmh
+// src/m_vhelmholtz.f90:61-141): the other colour of eps is staged the same way (its ghost layer comes from the
+// stored-face pool: eps ghost cells are host data), eps of the updated cells is prefetched like rhs, and the six
+// harmonic-mean face coefficients are recomputed per cell (6 fp64 divisions; precomputed face arrays would cost
+// 24 B per cell and half-sweep instead of 8).  Algorithmic bytes: 12 + 8 (eps, both colours) per cell and launch.
 template <int NC, int KT>
-struct SmoothSmem {
+struct TileSmem {
   static constexpr int HX = NC / 2;
   double B[KT][NC][HX];     // other colour, dense as in global memory
   double zlo[NC][HX], zhi[NC][HX];
   double ylo[KT][HX], yhi[KT][HX];
   double xg[KT][NC];        // the single x ghost each row needs (low side if the row's updated cells start at i=0, else high side)
+};
+struct NoSmem {};
+template <int NC, int KT, bool VC>
+struct SmoothSmem : TileSmem<NC, KT> {
+  typename std::conditional<VC, TileSmem<NC, KT>, NoSmem>::type E;   // the same tile of eps
   uint64_t bar;
 };
 
-template <int NC, int KT>
-__global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
-                                                              const __grid_constant__ ParamsDev P, int colour) {
+template <int NC, int KT, bool VC>
+__global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
+                                                                          const __grid_constant__ ParamsDev P, int colour,
+                                                                          const int* __restrict__ boxlist) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  SmoothSmem<NC, KT>& S = *reinterpret_cast<SmoothSmem<NC, KT>*>(smem_raw);
+  SmoothSmem<NC, KT, VC>& S = *reinterpret_cast<SmoothSmem<NC, KT, VC>*>(smem_raw);
   const int tid = threadIdx.x;
-  const int b = blockIdx.x / TILES;
+  const int b = boxlist ? boxlist[blockIdx.x / TILES] : blockIdx.x / TILES;   // a subset of the level (partition-face / interior boxes)
   const int k0 = (blockIdx.x % TILES) * KT;
   const int oc = colour ^ 1;
   const double* __restrict__ phi = L.var[0];
@@ -89,14 +102,20 @@ __global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_const
   // the tile itself depends on nothing but the box index: its copy starts before the face table is read
   if (tid == 0) {
     mbar_init(&S.bar, 1);
-    mbar_expect_tx(&S.bar, KT * NC * HX * 8);
+    mbar_expect_tx(&S.bar, (VC ? 2 : 1) * KT * NC * HX * 8);
     bulk_g2s(&S.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+    if constexpr (VC) bulk_g2s(&S.E.B[0][0][0], L.var[4] + boxoff + (size_t)oc * L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
   }
-  // rhs of this thread's cells (in flight while the bulk copies land)
+  // rhs (and eps) of this thread's cells (in flight while the bulk copies land)
   constexpr int PER = KT * NC * HX / kThreads;
-  double rhs[PER];
+  double rhs[PER], eps0[VC ? PER : 1];
 #pragma unroll
   for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)k0 * NC * HX + q * kThreads + tid];
+  if constexpr (VC) {
+    const double* __restrict__ Eg0 = L.var[4] + boxoff + (size_t)colour * L.cs;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) eps0[q] = Eg0[(size_t)k0 * NC * HX + q * kThreads + tid];
+  }
 
   int kind[6], arg[6];
 #pragma unroll
@@ -113,9 +132,16 @@ __global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_const
       if (zhi_in || kind[5] == FK_SAME) bytes += NC * HX * 8;
       if (kind[2] == FK_SAME) bytes += KT * HX * 8;
       if (kind[3] == FK_SAME) bytes += KT * HX * 8;
+      if (VC && zlo_in) bytes += NC * HX * 8;
+      if (VC && zhi_in) bytes += NC * HX * 8;
       mbar_arrive_expect_tx(&S.bar, bytes);
     }
     __syncwarp();
+    if constexpr (VC) {
+      const double* __restrict__ Eg = L.var[4] + boxoff + (size_t)oc * L.cs;
+      if (tid == 3 && zlo_in) bulk_g2s(&S.E.zlo[0][0], Eg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
+      if (tid == 4 && zhi_in) bulk_g2s(&S.E.zhi[0][0], Eg + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
+    }
     if (tid == 1) {
       if (zlo_in) bulk_g2s(&S.zlo[0][0], Bg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
       else if (kind[4] == FK_SAME) bulk_g2s(&S.zlo[0][0], phi + (size_t)arg[4] * L.bs + (size_t)oc * L.cs + (size_t)(NC - 1) * NC * HX, NC * HX * 8, &S.bar);
@@ -164,6 +190,25 @@ __global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_const
         const int f = (colour ^ ((j + k) & 1)) ? 1 : 0;
         if (kind[f] == FK_PLANE) S.xg[kk][j] = gpl[(size_t)arg[f] * NC * NC + k * NC + j];
       }
+  }
+
+  // ---- ghost layer of eps: the other-colour entries of the stored ghost faces (host data, any face kind) ----
+  if constexpr (VC) {
+    const double* __restrict__ fc = L.faces[4] + (size_t)b * 6 * NC * NC;
+    if (!zlo_in)
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.E.zlo[j][m] = fc[4 * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)]; }
+    if (!zhi_in)
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.E.zhi[j][m] = fc[5 * NC * NC + j * NC + 2 * m + ((oc ^ j) & 1)]; }
+    for (int r = tid; r < KT * HX; r += kThreads) {
+      const int kk = r / HX, m = r % HX, k = k0 + kk;
+      S.E.ylo[kk][m] = fc[2 * NC * NC + k * NC + 2 * m + ((oc ^ (k + 1)) & 1)];
+      S.E.yhi[kk][m] = fc[3 * NC * NC + k * NC + 2 * m + ((oc ^ k) & 1)];
+    }
+    for (int r = tid; r < KT * NC; r += kThreads) {
+      const int kk = r / NC, j = r % NC, k = k0 + kk;
+      const int f = (colour ^ ((j + k) & 1)) ? 1 : 0;
+      S.E.xg[kk][j] = fc[f * NC * NC + k * NC + j];
+    }
   }
 
   mbar_wait(&S.bar, 0);
@@ -230,19 +275,33 @@ __global__ void __launch_bounds__(kThreads) k_smooth_lpl_fast(const __grid_const
     const double yhi = j < NC - 1 ? S.B[kk][j + 1][m] : S.yhi[kk][m];
     const double zlo = kk > 0 ? S.B[kk - 1][j][m] : S.zlo[j][m];
     const double zhi = kk < KT - 1 ? S.B[kk + 1][j][m] : S.zhi[j][m];
-    Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - rhs[q]);
+    if constexpr (VC) {
+      const double u[6] = {xlo, xhi, ylo, yhi, zlo, zhi};
+      double a0[6], a[6];
+#pragma unroll
+      for (int f = 0; f < 6; ++f) a0[f] = eps0[q];
+      a[0] = ml >= 0 ? S.E.B[kk][j][ml] : S.E.xg[kk][j];
+      a[1] = mh < HX ? S.E.B[kk][j][mh] : S.E.xg[kk][j];
+      a[2] = j > 0 ? S.E.B[kk][j - 1][m] : S.E.ylo[kk][m];
+      a[3] = j < NC - 1 ? S.E.B[kk][j + 1][m] : S.E.yhi[kk][m];
+      a[4] = kk > 0 ? S.E.B[kk - 1][j][m] : S.E.zlo[j][m];
+      a[5] = kk < KT - 1 ? S.E.B[kk + 1][j][m] : S.E.zhi[j][m];
+      Ag[(size_t)k0 * NC * HX + idx] = gs_vlpl_value(L.idr2, u, a0, a, rhs[q], P.lambda, P.op != OP_VLPL);
+    } else {
+      Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - rhs[q]);
+    }
   }
 }
 
-template <int NC, int KT>
-bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s) {
+template <int NC, int KT, bool VC>
+bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, cudaStream_t s) {
   static bool configured = false;
-  const size_t smem = sizeof(SmoothSmem<NC, KT>);
+  const size_t smem = sizeof(SmoothSmem<NC, KT, VC>);
   if (!configured) {
-    if (cudaFuncSetAttribute(k_smooth_lpl_fast<NC, KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(k_smooth_lpl_fast<NC, KT, VC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_smooth_lpl_fast<NC, KT><<<L.nb * (NC / KT), kThreads, smem, s>>>(L, P, colour);
+  k_smooth_lpl_fast<NC, KT, VC><<<(list ? n : L.nb) * (NC / KT), kThreads, smem, s>>>(L, P, colour, list);
   return true;
 }
 
@@ -258,23 +317,54 @@ bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream
 // =================================================================================================
 enum { MODE_RESID_RESTRICT = 0, MODE_RESID_MAX = 1, MODE_CRHS = 2 };
 
+// VC = true (vlaplacian / vhelmholtz: box_vlpl src/m_vlaplacian.f90:131-189, box_vhelmh src/m_vhelmholtz.f90:144-205):
+// eps is staged like phi (its ghost layer from the stored-face pool) and the operator becomes
+// sum_f 2 idr2 a0 a_f / (a0 + a_f) (u_f - u0) [- lambda u0]; + 8 B per cell.
 template <int NC, int KT>
-struct StencilSmem {
+struct BothSmem {
   static constexpr int HX = NC / 2;
   double Ph[2][KT][NC][HX];
   double zlo[2][NC][HX], zhi[2][NC][HX];
   double ylo[2][KT][HX], yhi[2][KT][HX];
   double xlo[KT][NC], xhi[KT][NC];
+};
+template <int NC, int KT, bool VC>
+struct StencilSmem : BothSmem<NC, KT> {
+  typename std::conditional<VC, BothSmem<NC, KT>, NoSmem>::type E;
   double red[32];
   uint64_t bar;
 };
 
-template <int NC, int KT, int MODE, bool HELM, int MB>
+// the six neighbours (face order -x, +x, -y, +y, -z, +z) of fine cell e = di | slot << 1 | dk << 2 of the 2x2x2 block
+// (I, J, Kc) whose own values are u[8]; dj = slot ^ sw (see the row-order note in k_stencil_fast)
+template <int NC, int KT>
+__device__ __forceinline__ void block_neighbours(const BothSmem<NC, KT>& F, const double (&u)[8], int e, int I, int J, int Kc, int sw, double (&n)[6]) {
+  constexpr int HC = NC / 2;
+  const int di = e & 1, s = (e >> 1) & 1, dk = e >> 2;
+  const int dj = s ^ sw, j = 2 * J + dj, kk = 2 * Kc + dk;
+  const int oc = (di + dj + dk + 1) & 1;                       // colour of the six neighbours
+  double xo;                                                   // x: the neighbour inside the block is u[e ^ 1]
+  if (di == 0) xo = I > 0 ? F.Ph[oc][kk][j][I - 1] : F.xlo[kk][j];
+  else xo = I < HC - 1 ? F.Ph[oc][kk][j][I + 1] : F.xhi[kk][j];
+  n[0] = di ? u[e ^ 1] : xo; n[1] = di ? xo : u[e ^ 1];
+  const int jo = dj ? j + 1 : j - 1;                           // y: inside neighbour u[e ^ 2]
+  double yo;
+  if (jo < 0) yo = F.ylo[oc][kk][I];
+  else if (jo >= NC) yo = F.yhi[oc][kk][I];
+  else yo = F.Ph[oc][kk][jo][I];
+  n[2] = dj ? u[e ^ 2] : yo; n[3] = dj ? yo : u[e ^ 2];
+  double zo;                                                   // z: inside neighbour u[e ^ 4]
+  if (dk == 0) zo = kk > 0 ? F.Ph[oc][kk - 1][j][I] : F.zlo[oc][j][I];
+  else zo = kk < KT - 1 ? F.Ph[oc][kk + 1][j][I] : F.zhi[oc][j][I];
+  n[4] = dk ? u[e ^ 4] : zo; n[5] = dk ? zo : u[e ^ 4];
+}
+
+template <int NC, int KT, int MODE, bool HELM, int MB, bool VC>
 __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
                                                            const __grid_constant__ ParamsDev P, double* maxslot) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
-  using SM = StencilSmem<NC, KT>;
+  using SM = StencilSmem<NC, KT, VC>;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SM& S = *reinterpret_cast<SM*>(smem_raw);
   const int tid = threadIdx.x;
@@ -287,11 +377,19 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   // the tile itself depends on nothing but the box index: its copies start before the face table is read
   if (tid == 0) {
     mbar_init(&S.bar, 1);
-    mbar_expect_tx(&S.bar, 2 * KT * NC * HX * 8);
+    mbar_expect_tx(&S.bar, (VC ? 2 : 1) * 2 * KT * NC * HX * 8);
     if (TILES == 1) bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff, 2 * KT * NC * HX * 8, &S.bar);   // whole box: one 32 KiB copy
     else {
       bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
       bulk_g2s(&S.Ph[1][0][0][0], phi + boxoff + L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+    }
+    if constexpr (VC) {
+      const double* __restrict__ eps = L.var[4] + boxoff;
+      if (TILES == 1) bulk_g2s(&S.E.Ph[0][0][0][0], eps, 2 * KT * NC * HX * 8, &S.bar);
+      else {
+        bulk_g2s(&S.E.Ph[0][0][0][0], eps + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+        bulk_g2s(&S.E.Ph[1][0][0][0], eps + L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+      }
     }
   }
   // rhs (or res) of this thread's first coarse cell: issued before the wait so that the loads overlap the bulk copies
@@ -328,7 +426,17 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
     uint32_t bytes = 0;
     if (zlo_in || kind[4] == FK_SAME) bytes += 2 * NC * HX * 8;
     if (zhi_in || kind[5] == FK_SAME) bytes += 2 * NC * HX * 8;
+    if (VC && zlo_in) bytes += 2 * NC * HX * 8;
+    if (VC && zhi_in) bytes += 2 * NC * HX * 8;
     mbar_arrive_expect_tx(&S.bar, bytes);
+    if constexpr (VC) {
+      const double* __restrict__ eps = L.var[4] + boxoff;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        if (zlo_in) bulk_g2s(&S.E.zlo[c][0][0], eps + (size_t)c * L.cs + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
+        if (zhi_in) bulk_g2s(&S.E.zhi[c][0][0], eps + (size_t)c * L.cs + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
+      }
+    }
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       if (zlo_in) bulk_g2s(&S.zlo[c][0][0], phi + boxoff + (size_t)c * L.cs + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
@@ -368,6 +476,21 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
       for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xlo[kk][j] = gpl[(size_t)arg[0] * NC * NC + (k0 + kk) * NC + j]; }
     if (kind[1] == FK_PLANE)
       for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xhi[kk][j] = gpl[(size_t)arg[1] * NC * NC + (k0 + kk) * NC + j]; }
+  }
+  if constexpr (VC) {
+    // ghost layer of eps: stored ghost faces (host data, any face kind), de-interleaved by colour
+    const double* __restrict__ fc = L.faces[4] + (size_t)b * 6 * NC * NC;
+    if (!zlo_in)
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.E.zlo[(i + j + 1) & 1][j][i >> 1] = fc[4 * NC * NC + r]; }
+    if (!zhi_in)
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.E.zhi[(i + j) & 1][j][i >> 1] = fc[5 * NC * NC + r]; }
+    for (int r = tid; r < KT * NC; r += kThreads) {
+      const int kk = r / NC, i = r % NC, k = k0 + kk;
+      S.E.ylo[(i + k + 1) & 1][kk][i >> 1] = fc[2 * NC * NC + k * NC + i];
+      S.E.yhi[(i + k) & 1][kk][i >> 1] = fc[3 * NC * NC + k * NC + i];
+      S.E.xlo[kk][i] = fc[0 * NC * NC + k * NC + i];       // (here i runs over j)
+      S.E.xhi[kk][i] = fc[1 * NC * NC + k * NC + i];
+    }
   }
   mbar_wait(&S.bar, 0);
   __syncthreads();
@@ -433,36 +556,29 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
 #pragma unroll
       for (int e = 0; e < 8; ++e) nxt[e] = in1[goff(q + kThreads, e & 1, (e >> 1) & 1, e >> 2)];
     }
-    double u[8], r[8];
+    double u[8], r[8], ue[VC ? 8 : 1];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int di = e & 1, dj = ((e >> 1) & 1) ^ sw, dk = e >> 2;
       u[e] = S.Ph[(di + dj + dk) & 1][2 * Kc + dk][2 * J + dj][I];
+      if constexpr (VC) ue[e] = S.E.Ph[(di + dj + dk) & 1][2 * Kc + dk][2 * J + dj][I];
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int di = e & 1, s = (e >> 1) & 1, dk = e >> 2;
-      const int dj = s ^ sw, j = 2 * J + dj, kk = 2 * Kc + dk;
-      const int oc = (di + dj + dk + 1) & 1;                       // colour of the six neighbours
       const double u0 = u[e];
-      // x: the neighbour inside the block is u[e ^ 1]
-      double xo;
-      if (di == 0) xo = I > 0 ? S.Ph[oc][kk][j][I - 1] : S.xlo[kk][j];
-      else xo = I < HC - 1 ? S.Ph[oc][kk][j][I + 1] : S.xhi[kk][j];
-      const double xl = di ? u[e ^ 1] : xo, xh = di ? xo : u[e ^ 1];
-      // y: inside neighbour u[e ^ 2]; the outside row is j - 1 (dj = 0) or j + 1 (dj = 1)
-      const int jo = dj ? j + 1 : j - 1;
-      double yo;
-      if (jo < 0) yo = S.ylo[oc][kk][I];
-      else if (jo >= NC) yo = S.yhi[oc][kk][I];
-      else yo = S.Ph[oc][kk][jo][I];
-      const double yl = dj ? u[e ^ 2] : yo, yh = dj ? yo : u[e ^ 2];
-      // z: inside neighbour u[e ^ 4]
-      double zo;
-      if (dk == 0) zo = kk > 0 ? S.Ph[oc][kk - 1][j][I] : S.zlo[oc][j][I];
-      else zo = kk < KT - 1 ? S.Ph[oc][kk + 1][j][I] : S.zhi[oc][j][I];
-      const double zl = dk ? u[e ^ 4] : zo, zh = dk ? zo : u[e ^ 4];
-      double lap = idx2 * (xl + xh - 2 * u0) + idy2 * (yl + yh - 2 * u0) + idz2 * (zl + zh - 2 * u0);
+      double n[6];
+      block_neighbours<NC, KT>(S, u, e, I, J, Kc, sw, n);
+      double lap;
+      if constexpr (VC) {
+        double an[6], a0[6];
+        block_neighbours<NC, KT>(S.E, ue, e, I, J, Kc, sw, an);
+#pragma unroll
+        for (int f = 0; f < 6; ++f) a0[f] = ue[e];
+        lap = vlpl_value(L.idr2, u0, n, a0, an);
+      } else {
+        lap = idx2 * (n[0] + n[1] - 2 * u0) + idy2 * (n[2] + n[3] - 2 * u0) + idz2 * (n[4] + n[5] - 2 * u0);
+      }
       if (HELM) lap = lap - lambda * u0;
       const size_t g = goff(q, di, s, dk);
       if (MODE == MODE_CRHS) {
@@ -505,15 +621,15 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   }
 }
 
-template <int NC, int KT, int MODE, bool HELM, int MB>
+template <int NC, int KT, int MODE, bool HELM, int MB, bool VC = false>
 bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   static bool configured = false;
-  const size_t smem = sizeof(StencilSmem<NC, KT>);
+  const size_t smem = sizeof(StencilSmem<NC, KT, VC>);
   if (!configured) {
-    if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM, MB, VC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_stencil_fast<NC, KT, MODE, HELM, MB><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot);
+  k_stencil_fast<NC, KT, MODE, HELM, MB, VC><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot);
   return true;
 }
 
@@ -533,8 +649,17 @@ bool dispatch_stencil_h(const LevelDev& L, const LevelDev& Lc, const ParamsDev& 
   if (L.nc == 32) return launch_stencil<32, 8, MODE, HELM, 2>(L, Lc, P, nboxes, maxslot, s);
   return false;
 }
+template <int MODE, bool HELM>
+bool dispatch_stencil_vc(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+  if (!L.var[4] || !L.faces[4]) return false;
+  if (L.nc == 16) return launch_stencil<16, 16, MODE, HELM, 2, true>(L, Lc, P, nboxes, maxslot, s);
+  if (L.nc == 32) return launch_stencil<32, 8, MODE, HELM, 1, true>(L, Lc, P, nboxes, maxslot, s);
+  return false;
+}
 template <int MODE>
 bool dispatch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+  if (P.op == OP_VLPL) return dispatch_stencil_vc<MODE, false>(L, Lc, P, nboxes, maxslot, s);
+  if (P.op == OP_VHELMH) return dispatch_stencil_vc<MODE, true>(L, Lc, P, nboxes, maxslot, s);
   return P.op == OP_HELMH ? dispatch_stencil_h<MODE, true>(L, Lc, P, nboxes, maxslot, s)
                           : dispatch_stencil_h<MODE, false>(L, Lc, P, nboxes, maxslot, s);
 }
@@ -643,27 +768,33 @@ bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev
 
 namespace omgf {
 
-bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, cudaStream_t s) {
+bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, cudaStream_t s) {
   if (!all_fast || L.nb == 0) return false;
+  if (list && n == 0) return true;
+  if (P.op == OP_VLPL || P.op == OP_VHELMH) {
+    if (!L.var[4] || !L.faces[4]) return false;
+    if (L.nc == 16) return launch_smooth<16, 16, true>(L, P, colour, list, n, s);
+    if (L.nc == 32) return launch_smooth<32, 8, true>(L, P, colour, list, n, s);
+    return false;
+  }
   if (P.op != OP_LPL && P.op != OP_HELMH) return false;
-  static const int kt = env_int("OMG_SMOOTH_KT", 16);
-  if (L.nc == 16) return kt == 8 ? launch_smooth<16, 8>(L, P, colour, s) : launch_smooth<16, 16>(L, P, colour, s);
-  if (L.nc == 32) return launch_smooth<32, 8>(L, P, colour, s);
+  if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, s);
+  if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, s);
   return false;
 }
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s) {
   if (!all_fast || Lf.nb == 0 || Lc.nc != Lf.nc) return false;
-  if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  if (P.op == OP_AHELMH) return false;
   return dispatch_stencil<MODE_RESID_RESTRICT>(Lf, Lc, P, Lf.nb, nullptr, s);
 }
 bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s) {
   if (!all_fast || L.nb == 0 || !maxslot) return false;
-  if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  if (P.op == OP_AHELMH) return false;
   return dispatch_stencil<MODE_RESID_MAX>(L, L, P, L.nb, maxslot, s);
 }
 bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s) {
   if (!all_fast || L.n_parents == 0) return false;
-  if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  if (P.op == OP_AHELMH) return false;
   return dispatch_stencil<MODE_CRHS>(L, L, P, L.n_parents, nullptr, s);
 }
 bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool, cudaStream_t s) {

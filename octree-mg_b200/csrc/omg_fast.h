@@ -6,7 +6,8 @@
 #include "omg_device.cuh"
 
 namespace omgf {
-bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, cudaStream_t s);
+// list != null: only the n boxes of the list (partition-face / interior split of a distributed level)
+bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, cudaStream_t s);
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s);
 bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s);
 bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s);

@@ -19,8 +19,9 @@ constexpr int kThreads = 256;
 // ------------------------------------------------------------------ batched kernels ----------
 template <int OP>
 __global__ void __launch_bounds__(kThreads) k_smooth(const __grid_constant__ LevelDev L,
-                                                     const __grid_constant__ ParamsDev P, int colour) {
-  do_smooth<OP>(L, P, blockIdx.x, colour, threadIdx.x, blockDim.x);
+                                                     const __grid_constant__ ParamsDev P, int colour,
+                                                     const int* __restrict__ boxlist) {
+  do_smooth<OP>(L, P, boxlist ? boxlist[blockIdx.x] : blockIdx.x, colour, threadIdx.x, blockDim.x);
 }
 
 // mg_smoother_gs: ghost snapshot (= the ghost fill preceding the sweep) and the in-box lexicographic sweep
@@ -372,9 +373,10 @@ inline int grid_for(size_t n) { size_t g = (n + 255) / 256; return (int)(g > 148
 // ------------------------------------------------------------------ launch wrappers -----------
 namespace omgk {
 
-void smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s) {
-  if (L.nb == 0) return;
-  OMG_SWITCH_OP(P.op, (k_smooth<OP><<<L.nb, kThreads, 0, s>>>(L, P, colour)));
+void smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, cudaStream_t s) {
+  const int nb = list ? n : L.nb;
+  if (nb == 0) return;
+  OMG_SWITCH_OP(P.op, (k_smooth<OP><<<nb, kThreads, 0, s>>>(L, P, colour, list)));
 }
 void smooth_gs(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
   if (L.nb == 0) return;

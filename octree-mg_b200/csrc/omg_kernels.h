@@ -18,7 +18,7 @@ enum ScalSlot : int {
 };
 
 namespace omgk {
-void smooth(const LevelDev& L, const ParamsDev& P, int colour, cudaStream_t s);
+void smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, cudaStream_t s);   // list: subset of boxes or null
 // mg_smoother_gs: ghost snapshot into L.faces[0] + in-box lexicographic sweep (two launches)
 void smooth_gs(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
 void resid(const LevelDev& L, const ParamsDev& P, double* maxslot, cudaStream_t s);

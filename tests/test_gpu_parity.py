@@ -203,3 +203,20 @@ def test_gs_smoother_refinement(oracle, product):
     check_histories(P.run_cycles(orc, 3, True), P.run_cycles(mg, 3, True))
     check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
     assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("op,bc,lam,n,box", [
+    (P.mg_vlaplacian, "mixed", 0.0, 64, 16),
+    (P.mg_vlaplacian, "callback", 0.0, (64, 32, 32), 16),
+    (P.mg_vhelmholtz, "neumann0", 1.0, 64, 16),
+    (P.mg_vhelmholtz, "mixed", 0.5, 64, 32),
+    (P.mg_helmholtz, "neumann0", 1.0, 64, 16),
+])
+def test_fast_kernels_variable_coefficient(oracle, product, op, bc, lam, n, box):
+    """config 4 at box sizes 16 / 32: the TMA-staged kernels of the variable-coefficient operators (eps tile + stored
+    eps ghost faces, harmonic-mean face coefficients recomputed per cell) against the oracle, bitwise."""
+    orc, _ = P.uniform_problem(oracle.OracleMg, n, box, operator_type=op, bc=bc, lam=lam)
+    mg, _ = P.uniform_problem(product.Mg, n, box, operator_type=op, bc=bc, lam=lam)
+    check_histories(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
