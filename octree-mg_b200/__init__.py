@@ -443,6 +443,14 @@ class Mg:
     def sync(self):
         self._gck(self.G.omg_sync(self.gpu))
 
+    def mg_timers(self):
+        """{name: seconds} of the reference's seven timers (mg_timers_show, src/m_data_structures.f90:562-581)."""
+        n = C.c_int(0)
+        self._gck(self.G.omg_timers(self.gpu, C.byref(n), None, None))
+        names, secs = (C.c_char_p * n.value)(), (C.c_double * n.value)()
+        self._gck(self.G.omg_timers(self.gpu, C.byref(n), names, secs))
+        return {names[i].decode(): secs[i] for i in range(n.value)}
+
     # -- building blocks of the cycle (private in the reference; exposed for per-kernel parity tests) -------
     def _step(self, what, lvl, arg=0):
         """device-resident single step; in drop-in mode the four variables are pushed before and pulled after"""

@@ -30,6 +30,7 @@ struct NcclApi {
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 const NcclApi& nccl_api() {
@@ -49,6 +50,7 @@ const NcclApi& nccl_api() {
     api.Send = (decltype(api.Send))sym("ncclSend");
     api.Recv = (decltype(api.Recv))sym("ncclRecv");
     api.AllReduce = (decltype(api.AllReduce))sym("ncclAllReduce");
+    api.AllGather = (decltype(api.AllGather))sym("ncclAllGather");
     api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
   });
   if (!err.empty()) cfail(err);
@@ -63,6 +65,42 @@ __global__ void k_reduce_slots(const double* __restrict__ slots, int n, int op, 
   for (int r = 1; r < n; ++r) v = (op == OMG_RED_MAX) ? fmax(v, slots[r]) : v + slots[r];
   *out = v;
 }
+
+// ---- peer-mapped puts: signalling ---------------------------------------------------------------------------------
+struct PeerList { int n; int peer[31]; };
+constexpr int kMaxRanks = 32;
+// flags[channel][r]: number of put phases rank r has completed towards me on that channel (written by r through its
+// mapping of my flag array).  *epoch: number of put phases I have completed on the channel; all ranks run the same
+// sequence of phases, so "flags[p] >= my epoch" means p's puts of the current phase have landed.
+__device__ __forceinline__ void wait_flag(const volatile unsigned long long* f, unsigned long long want, int* err) {
+  unsigned long long t0 = 0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while (*f < want) {
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 4000000000ull) { atomicExch(err, 1); break; }     // 4 s: the peer is gone; never hang the GPU
+    __nanosleep(100);
+  }
+}
+// signal = 1: raise my flag at the peers (my puts precede this kernel in stream order), wait for theirs, bump the epoch.
+// signal = 0: only wait for the peers' flags of the current epoch (puts that were signalled from inside a kernel).
+__global__ void k_signal_wait(PeerList pl, int channel, int me, int nranks, unsigned long long* const* __restrict__ peer_flags,
+                              unsigned long long* flags, unsigned long long* epoch, int* err, int signal) {
+  const int t = threadIdx.x;
+  const unsigned long long e = *epoch + (signal ? 1ull : 0ull);
+  if (t < pl.n) {
+    const int p = pl.peer[t];
+    if (signal) {
+      __threadfence_system();
+      *(volatile unsigned long long*)(peer_flags[p] + channel * nranks + me) = e;
+    }
+    wait_flag(flags + channel * nranks + p, e, err);
+    __threadfence_system();
+  }
+  __syncthreads();
+  if (t == 0 && signal) *epoch = e;
+}
+__global__ void k_bump_epoch(unsigned long long* epoch) { *epoch = *epoch + 1; }
 }  // namespace
 
 struct omg_local_group {
@@ -73,6 +111,7 @@ struct omg_local_group {
   unsigned long gen = 0;
   bool broken = false;
   std::vector<omg_comm*> comms;
+  std::vector<void*> share_tbl;             // omg_comm_share: the pointer every emulated rank contributes
 
   // all emulated ranks meet here; a rank that failed (or never arrives) breaks the group instead of hanging it
   void barrier() {
@@ -98,6 +137,13 @@ struct omg_comm {
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
   double* d_stage = nullptr;                // my contribution to an allreduce
   double* d_gather = nullptr;               // [n] contributions of all ranks
+  // peer-mapped puts (NCCL back end)
+  bool p2p = false;
+  unsigned long long* d_flags = nullptr;    // [OMG_P2P_CHANNELS][n], written by the peers
+  unsigned long long** d_peer_flags = nullptr;
+  int* d_err = nullptr;
+  std::vector<void*> ipc_opened;
+  void* ipc_scratch = nullptr;
 };
 
 int omg_comm_unique_id(char out[128]) {
@@ -118,12 +164,28 @@ omg_comm* omg_comm_create_nccl(const char uid[128], int rank, int nranks, int de
   ncclResult_t r;
   try { r = nccl_api().CommInitRank(&c->nccl, nranks, id, rank); } catch (...) { delete c; throw; }
   if (r != ncclSuccess) { delete c; cfail(std::string("ncclCommInitRank: ") + nccl_api().GetErrorString(r)); }
+  // flag array for peer-mapped puts, shared with every rank; OMG_P2P=0 keeps everything on ncclSend/ncclRecv
+  const char* env = getenv("OMG_P2P");
+  if (nranks <= kMaxRanks && !(env && *env == '0')) {
+    try {
+      const size_t nf = (size_t)OMG_P2P_CHANNELS * nranks;
+      CCK(cudaMalloc(&c->d_flags, nf * sizeof(unsigned long long)));
+      CCK(cudaMemset(c->d_flags, 0, nf * sizeof(unsigned long long)));
+      CCK(cudaMalloc(&c->d_err, sizeof(int)));
+      CCK(cudaMemset(c->d_err, 0, sizeof(int)));
+      CCK(cudaMalloc(&c->d_peer_flags, nranks * sizeof(void*)));
+      std::vector<void*> pf(nranks, nullptr);
+      c->p2p = true;                                   // omg_comm_share clears it again (on every rank) if IPC is unavailable
+      omg_comm_share(c, c->d_flags, pf.data());
+      if (c->p2p) CCK(cudaMemcpy(c->d_peer_flags, pf.data(), nranks * sizeof(void*), cudaMemcpyHostToDevice));
+    } catch (...) { c->p2p = false; }
+  }
   return c;
 }
 
 omg_local_group* omg_local_group_create(int nranks) {
   omg_local_group* g = new omg_local_group();
-  g->n = nranks; g->comms.assign(nranks, nullptr);
+  g->n = nranks; g->comms.assign(nranks, nullptr); g->share_tbl.assign(nranks, nullptr);
   return g;
 }
 
@@ -143,6 +205,11 @@ omg_comm* omg_comm_create_local(omg_local_group* g, int rank, int device) {
 void omg_comm_destroy(omg_comm* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  for (void* p : c->ipc_opened) cudaIpcCloseMemHandle(p);
+  if (c->d_flags) cudaFree(c->d_flags);
+  if (c->ipc_scratch) cudaFree(c->ipc_scratch);
+  if (c->d_err) cudaFree(c->d_err);
+  if (c->d_peer_flags) cudaFree(c->d_peer_flags);
   if (c->nccl) nccl_api().CommDestroy(c->nccl);
   if (c->g) {
     c->g->abort_group();                    // a group cannot continue without one of its ranks
@@ -220,4 +287,124 @@ void omg_comm_allreduce(omg_comm* c, double* d_val, int op, cudaStream_t s) {
     for (int r = 0; r < c->n; ++r) if (g->comms[r]) CCK(cudaStreamWaitEvent(s, g->comms[r]->ev_done, 0));
     g->barrier();
   } catch (...) { g->abort_group(); throw; }
+}
+
+// ---- peer-mapped puts ------------------------------------------------------------------------------------------------
+bool omg_comm_p2p(const omg_comm* c) { return c->g ? true : c->p2p; }
+
+void omg_comm_share(omg_comm* c, void* ptr, void** peer_ptrs) {
+  if (c->g) {
+    omg_local_group* g = c->g;
+    try {
+      { std::lock_guard<std::mutex> lk(g->m); g->share_tbl[c->rank] = ptr; }
+      g->barrier();
+      for (int r = 0; r < c->n; ++r) {
+        peer_ptrs[r] = g->share_tbl[r];
+        if (r != c->rank && g->comms[r] && g->comms[r]->device != c->device) {
+          cudaError_t e = cudaDeviceEnablePeerAccess(g->comms[r]->device, 0);
+          if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) cfail("local share: no peer access between the devices of two emulated ranks");
+          cudaGetLastError();
+        }
+      }
+      g->barrier();
+    } catch (...) { g->abort_group(); throw; }
+    return;
+  }
+  // NCCL back end: CUDA IPC handles through ncclAllGather.  Every rank must reach the same verdict, so the handle
+  // travels with a validity byte and the mapping result is agreed on with a second gather.
+  const NcclApi& N = nccl_api();
+  if (!c->p2p) { for (int r = 0; r < c->n; ++r) peer_ptrs[r] = (r == c->rank) ? ptr : nullptr; return; }
+  constexpr size_t kRec = 128;
+  static_assert(sizeof(cudaIpcMemHandle_t) < kRec, "IPC handle larger than the record");
+  std::vector<unsigned char> rec((size_t)c->n * kRec, 0);
+  cudaIpcMemHandle_t hd;
+  const bool got = cudaIpcGetMemHandle(&hd, ptr) == cudaSuccess;
+  if (!got) cudaGetLastError();
+  std::memcpy(&rec[(size_t)c->rank * kRec], &hd, sizeof(hd));
+  rec[(size_t)c->rank * kRec + kRec - 1] = got ? 1 : 0;
+  unsigned char* d = nullptr;
+  CCK(cudaMalloc(&d, rec.size()));
+  auto gather = [&]() {
+    CCK(cudaMemcpy(d + (size_t)c->rank * kRec, &rec[(size_t)c->rank * kRec], kRec, cudaMemcpyHostToDevice));
+    NCK(N.AllGather(d + (size_t)c->rank * kRec, d, kRec, ncclChar, c->nccl, 0));
+    CCK(cudaStreamSynchronize(0));
+    CCK(cudaMemcpy(rec.data(), d, rec.size(), cudaMemcpyDeviceToHost));
+  };
+  gather();
+  bool ok = true;
+  for (int r = 0; r < c->n; ++r) ok = ok && rec[(size_t)r * kRec + kRec - 1] == 1;
+  std::vector<void*> opened;
+  if (ok) {
+    for (int r = 0; r < c->n && ok; ++r) {
+      if (r == c->rank) { peer_ptrs[r] = ptr; continue; }
+      cudaIpcMemHandle_t hr;
+      std::memcpy(&hr, &rec[(size_t)r * kRec], sizeof(hr));
+      void* q = nullptr;
+      if (cudaIpcOpenMemHandle(&q, hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+      peer_ptrs[r] = q; opened.push_back(q);
+    }
+  }
+  rec[(size_t)c->rank * kRec + kRec - 1] = ok ? 1 : 0;      // agree: did every rank map every peer?
+  gather();
+  for (int r = 0; r < c->n; ++r) ok = ok && rec[(size_t)r * kRec + kRec - 1] == 1;
+  cudaFree(d);
+  if (!ok) {
+    for (void* q : opened) cudaIpcCloseMemHandle(q);
+    c->p2p = false;
+    for (int r = 0; r < c->n; ++r) peer_ptrs[r] = (r == c->rank) ? ptr : nullptr;
+    return;
+  }
+  c->ipc_opened.insert(c->ipc_opened.end(), opened.begin(), opened.end());
+}
+
+void omg_comm_signal_wait(omg_comm* c, int channel, const int* peers, int npeers, unsigned long long* epoch, int signal, cudaStream_t s) {
+  if (channel < 0 || channel >= OMG_P2P_CHANNELS) cfail("signal_wait: channel out of range");
+  if (c->g) {
+    omg_local_group* g = c->g;
+    try {
+      CCK(cudaEventRecord(c->ev_ready, s));                  // my puts are complete once this fires
+      g->barrier();
+      for (int i = 0; i < npeers; ++i) {
+        omg_comm* p = g->comms[peers[i]];
+        if (!p) cfail("local signal_wait: peer rank is gone");
+        CCK(cudaStreamWaitEvent(s, p->ev_ready, 0));
+      }
+      if (signal) k_bump_epoch<<<1, 1, 0, s>>>(epoch);
+      g->barrier();                                          // events may be re-recorded only after everyone waited on them
+    } catch (...) { g->abort_group(); throw; }
+    return;
+  }
+  if (!c->p2p) cfail("signal_wait without peer-mapped memory");
+  if (npeers > 31) cfail("signal_wait: too many peers");
+  PeerList pl; pl.n = npeers;
+  for (int i = 0; i < npeers; ++i) pl.peer[i] = peers[i];
+  k_signal_wait<<<1, 32, 0, s>>>(pl, channel, c->rank, c->n, c->d_peer_flags, c->d_flags, epoch, c->d_err, signal);
+  CCK(cudaGetLastError());
+}
+
+void omg_comm_p2p_ptrs(omg_comm* c, unsigned long long* const** peer_flags, unsigned long long** flags, int** err) {
+  if (c->g) {
+    // emulated ranks: in-kernel signalling writes to scratch slots nobody waits on (ordering comes from the host barrier)
+    if (!c->d_flags) {
+      const size_t nf = (size_t)OMG_P2P_CHANNELS * c->n;
+      CCK(cudaMalloc(&c->d_flags, nf * sizeof(unsigned long long)));
+      CCK(cudaMemset(c->d_flags, 0xff, nf * sizeof(unsigned long long)));    // "already arrived": waits return at once
+      CCK(cudaMalloc(&c->d_err, sizeof(int)));
+      CCK(cudaMemset(c->d_err, 0, sizeof(int)));
+      CCK(cudaMalloc(&c->d_peer_flags, c->n * sizeof(void*)));
+      unsigned long long* scratch = nullptr;
+      CCK(cudaMalloc(&scratch, nf * sizeof(unsigned long long)));
+      c->ipc_scratch = scratch;
+      std::vector<unsigned long long*> pf(c->n, scratch);
+      CCK(cudaMemcpy(c->d_peer_flags, pf.data(), c->n * sizeof(void*), cudaMemcpyHostToDevice));
+    }
+  }
+  *peer_flags = c->d_peer_flags; *flags = c->d_flags; *err = c->d_err;
+}
+
+int omg_comm_p2p_error(omg_comm* c) {
+  if (!c->d_err) return 0;
+  int e = 0;
+  cudaMemcpy(&e, c->d_err, sizeof(int), cudaMemcpyDeviceToHost);
+  return e;
 }

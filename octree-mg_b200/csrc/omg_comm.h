@@ -28,6 +28,28 @@ void omg_comm_destroy(omg_comm* c);
 int omg_comm_rank(const omg_comm* c);
 int omg_comm_size(const omg_comm* c);
 bool omg_comm_graph_safe(const omg_comm* c);   // may the exchange be captured into a CUDA graph?
+// ---- peer-mapped puts (the halo exchange of the smoother) ---------------------------------------------------------
+// Instead of send/recv pairs, a rank's pack kernel stores faces straight into the receiver's plane pool through a
+// peer mapping of that allocation (NVLink P2P stores); omg_comm_signal_wait then tells the peers "my puts are done" and
+// waits for theirs.  NCCL back end: CUDA IPC handles exchanged once with ncclAllGather; signalling is one single-CTA
+// kernel that writes a monotonically increasing epoch into each peer's flag slot and polls its own slots (bounded:
+// a peer that never arrives raises an error flag instead of hanging the GPU).  Local back end: pointers are shared
+// inside the process; signalling is an event + host barrier like the exchange below.
+bool omg_comm_p2p(const omg_comm* c);
+// collective: every rank contributes ONE device allocation (base pointer as returned by cudaMalloc); peer_ptrs[r]
+// becomes a pointer to rank r's allocation valid on this rank's device (peer_ptrs[me] = ptr)
+void omg_comm_share(omg_comm* c, void* ptr, void** peer_ptrs);
+// `epoch` (device, one counter per channel) is incremented when the wait completes: kernels launched after it see the
+// new value, which selects the plane buffer the peers have just filled
+// signal = 0: wait only (the puts of the current epoch were signalled from inside a kernel, see omg_fast.cu)
+void omg_comm_signal_wait(omg_comm* c, int channel, const int* peers, int npeers, unsigned long long* epoch, int signal, cudaStream_t s);
+// device pointers for in-kernel signalling: peer_flags[r] = rank r's flag array mapped here, flags = mine,
+// both indexed [channel * nranks + writer rank]; err = bounded-wait error word
+void omg_comm_p2p_ptrs(omg_comm* c, unsigned long long* const** peer_flags, unsigned long long** flags, int** err);
+// non-zero once a bounded wait has expired (NCCL back end)
+int omg_comm_p2p_error(omg_comm* c);
+enum { OMG_P2P_CHANNELS = 64 };
+
 // all ranks call these at the same program points with matching segments (throws std::runtime_error)
 void omg_comm_exchange(omg_comm* c, const OmgXfer* segs, int nsegs, cudaStream_t s);
 void omg_comm_allreduce(omg_comm* c, double* d_val, int op, cudaStream_t s);

@@ -42,7 +42,7 @@ template <class T> struct DevBuf {
 enum StepKind : int {
   S_SMOOTH, S_RESID, S_RESTRICT, S_CRHS, S_OLDPL, S_CORR_PROLONG, S_RB_FILL, S_COPY_OLD, S_COARSE_SOLVE,
   S_TAIL, S_ZERO_PHI, S_SUBMEAN, S_CLEAR_SLOT, S_COPY_SLOT, S_HALO, S_XRESTRICT, S_XPROLONG, S_ALLREDUCE_MAX,
-  S_RESID_RESTRICT, S_HALO_FORK, S_HALO_JOIN
+  S_RESID_RESTRICT, S_HALO_FORK, S_HALO_JOIN, S_PUT_WAIT
 };
 struct Step { int kind, l, a, b, c; };
 
@@ -53,9 +53,15 @@ struct PhasePlan {
   int n_send = 0, n_recv = 0;
   bool any = false;                     // some rank has traffic in this phase on this level (same on all ranks)
   std::vector<int> h_sdesc, h_rdesc;
-  DevBuf<int> d_sdesc, d_rdesc;
+  std::vector<int> h_dst;               // ghost phase as peer-mapped puts: per send item {receiver rank, plane in its pool}
+  DevBuf<int> d_sdesc, d_rdesc, d_dst;
+  std::vector<int> peers;               // ranks I exchange with in this phase
+  DevBuf<double*> d_peer_base;          // [n_cpu] the peers' plane pools mapped on this device
+  std::vector<long long> h_peer_stride;  // [n_cpu] distance between the two copies of each rank's pool (doubles)
+  DevBuf<long long> d_peer_stride;
+  bool shared = false;
   DevBuf<double> d_send, d_recv;
-  void free() { d_sdesc.free(); d_rdesc.free(); d_send.free(); d_recv.free(); }
+  void free() { d_sdesc.free(); d_rdesc.free(); d_dst.free(); d_peer_base.free(); d_peer_stride.free(); d_send.free(); d_recv.free(); }
 };
 
 struct LevelHost {
@@ -76,6 +82,12 @@ struct LevelHost {
   // exchange of a colour half-sweep overlaps the half-sweep of the interior boxes
   std::vector<int> h_bnd, h_int;
   DevBuf<int> d_bnd, d_int;
+  // in-kernel exchange (PutDev): launch order = partition-face boxes, then the rest; per partition-face box the faces it
+  // sends {receiver's face, receiver rank, plane in its pool}
+  bool rb_remote_any = false;           // some rank receives interpolated coarse faces on this level (replicated-tree fact)
+  std::vector<int> h_order, h_put_ptr, h_put_item;
+  DevBuf<int> d_order, d_put_ptr, d_put_item;
+  DevBuf<unsigned int> d_done;
   bool all_fast = false;                // every face of every box is FK_SAME or FK_PHYS (fast kernels apply)
 };
 
@@ -119,13 +131,19 @@ struct omg_handle {
   size_t stage_doubles = 0; int stage_boxes = 0;
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
   // stats / timers
-  int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0, exchanges = 0;
+  int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0, exchanges = 0, fused_smooths = 0, puts = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_ms = 0.0;
   omg_comm* comm = nullptr;
+  int fused = 1;                            // in-kernel exchange in the smoother where fused_level() allows (option "fused")
+  int p2p = 1;                              // ghost faces as peer-mapped puts where the plane pools are shared (option "p2p")
+  DevBuf<unsigned long long> d_epoch;       // [OMG_NLVL] completed ghost exchanges per level (selects the plane-pool copy)
   // per-step CUDA-event profile of the finest level (option "profile"): kind -> (events, count)
   int profile = 0;
-  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_events;
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_events;   // first = kind * 2 + (finest level ? 1 : 0)
+  // the reference's timers (mg_add_timers, src/m_multigrid.f90:72-81), seconds; totals always, phases in "profile" mode
+  double timer_acc[7] = {0, 0, 0, 0, 0, 0, 0};
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> total_events;   // (timer index, events) not yet read
   std::map<int, std::pair<double, int64_t>> prof_acc;   // step kind -> (ms, launches)
 
   LevelHost& L(int lvl) { return levels[lvl - lowest]; }
@@ -142,7 +160,7 @@ void free_levels(omg_handle* h) {
   for (LevelHost& L : h->levels) {
     L.d_fkind.free(); L.d_farg.free(); L.d_ftype.free(); L.d_fkind_old.free(); L.d_farg_old.free();
     L.d_parent.free(); L.d_coff.free(); L.d_parents.free(); L.d_leaves.free(); L.d_rb.free(); L.d_oldpl.free();
-    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free(); L.d_bnd.free(); L.d_int.free();
+    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free(); L.d_bnd.free(); L.d_int.free(); L.d_order.free(); L.d_put_ptr.free(); L.d_put_item.free(); L.d_done.free();
     for (int v = 0; v < OMG_MAXV; ++v) { L.d_var[v].free(); L.d_faces[v].free(); }
     L.xg.free(); L.xr.free(); L.xp.free();
   }
@@ -226,7 +244,7 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
         if (nbid > 0) { if (h->rank[nbid - 1] != r) L.xg.any = true; }
         else if (nbid == 0 && p > 0) {
           const int cnb = h->neighbors[(size_t)(p - 1) * 6 + f];
-          if (cnb > 0 && h->rank[cnb - 1] != r) L.xg.any = true;
+          if (cnb > 0 && h->rank[cnb - 1] != r) { L.xg.any = true; L.rb_remote_any = true; }
         }
       }
     }
@@ -244,17 +262,37 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
     // ghost-phase plan: planes received from peer ranks go straight into the plane pool, one contiguous
     // run per peer (same-level faces first, then interpolated coarse faces), see omg_plan.h
     std::map<std::pair<int, int>, int> remote_plane;
+    std::map<int, std::vector<int>> put_by_box;          // sender's local box -> {receiver face, rank, plane}*
     if (L.xg.any) {
       omgp::LevelPlan pl = omgp::build_plan(*t, me, omgp::PH_GHOST, lvl);
       int soff = 0, roff = 0;
+      // refinement-boundary faces per rank (each owns one plane in its pool, after the planes it receives)
+      std::vector<long long> n_rb_of(h->n_cpu, 0);
+      for (int id : h->lvl_ids[lvl - h->lowest])
+        for (int f = 0; f < 6; ++f) if (h->neighbors[(size_t)(id - 1) * 6 + f] == 0) n_rb_of[h->rank[id - 1]]++;
+      L.xg.h_peer_stride.assign(h->n_cpu, 1);
       for (const omgp::PeerPlan& pp : pl.peers) {
         L.xg.seg.push_back({pp.peer, soff, (int)pp.send.size(), roff, (int)pp.recv.size()});
         for (const omgp::Item& it : pp.recv) remote_plane[{it.box, it.face}] = roff++;
+        // where my items land in the receiver's plane pool: its recv planes are numbered peer by peer in its own plan
+        int rbase = -1;
+        {
+          omgp::LevelPlan theirs = omgp::build_plan(*t, pp.peer, omgp::PH_GHOST, lvl);
+          int ro = 0;
+          for (const omgp::PeerPlan& q : theirs.peers) { if (q.peer == me) { rbase = ro; if (q.recv.size() != pp.send.size()) fail("omg_set_tree: exchange plans of two ranks disagree"); } ro += (int)q.recv.size(); }
+          L.xg.h_peer_stride[pp.peer] = std::max<long long>((ro + n_rb_of[pp.peer]) * (long long)nc * nc, 1);   // = its d_gpl.n / 2
+        }
+        if (!pp.send.empty() && rbase < 0) fail("omg_set_tree: exchange plans of two ranks disagree");
+        int k = 0;
         for (const omgp::Item& it : pp.send) {
           L.xg.h_sdesc.push_back(it.kind); L.xg.h_sdesc.push_back(h->loc[it.src]); L.xg.h_sdesc.push_back(it.face);
           L.xg.h_sdesc.push_back(it.kind == omgp::IT_RB ? coff_of(it.box, lvl) : 0);
+          L.xg.h_dst.push_back(pp.peer); L.xg.h_dst.push_back(rbase + k);
+          if (it.kind == omgp::IT_SAME) { std::vector<int>& v = put_by_box[h->loc[it.src]]; v.push_back(it.face); v.push_back(pp.peer); v.push_back(rbase + k); }
+          ++k;
           ++soff;
         }
+        L.xg.peers.push_back(pp.peer);
       }
       L.xg.n_send = soff; L.xg.n_recv = roff;
       L.n_gpl = roff;
@@ -271,6 +309,8 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
       for (int f = 0; f < 6; ++f) {
         const int nbid = h->neighbors[(size_t)(id - 1) * 6 + f];
         if (nbid > 0 && h->rank[nbid - 1] != me) on_partition_face = true;
+        if (nbid == 0) on_partition_face = true;    // refinement-boundary planes live in the pool copy selected by the epoch,
+                                                    // which flips while the "interior" boxes are being swept
       }
       (on_partition_face ? L.h_bnd : L.h_int).push_back(b);
       const int p = h->parent[id - 1];
@@ -302,6 +342,14 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
           L.h_fkind_old[q] = FK_PHYS; L.h_farg_old[q] = -1;
         }
       }
+    }
+    L.h_order = L.h_bnd;
+    L.h_order.insert(L.h_order.end(), L.h_int.begin(), L.h_int.end());
+    L.h_put_ptr.assign(1, 0);
+    for (int b : L.h_bnd) {
+      auto it = put_by_box.find(b);
+      if (it != put_by_box.end()) L.h_put_item.insert(L.h_put_item.end(), it->second.begin(), it->second.end());
+      L.h_put_ptr.push_back((int)L.h_put_item.size() / 3);
     }
     // restrict (children on this level -> parents on lvl-1) and prolong (parents on lvl-1 -> children here)
     if (L.xr.any) {
@@ -340,8 +388,10 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
         if (nb) CK(cudaMemsetAsync(L.d_faces[v].p, 0, (size_t)nb * 6 * nc * nc * sizeof(double), h->stream));
       }
     }
-    L.d_gpl.alloc((size_t)L.n_gpl * nc * nc);
-    if (L.n_gpl) CK(cudaMemsetAsync(L.d_gpl.p, 0, L.d_gpl.n * sizeof(double), h->stream));
+    // distributed levels keep two copies of the plane pool (peer-mapped puts fill one while the other is read,
+    // omg_device.cuh); every rank allocates it, even with no planes of its own, so that the mapping is collective
+    L.d_gpl.alloc(L.xg.any ? std::max<size_t>((size_t)2 * L.n_gpl * nc * nc, 2) : (size_t)L.n_gpl * nc * nc);
+    if (L.d_gpl.n) CK(cudaMemsetAsync(L.d_gpl.p, 0, L.d_gpl.n * sizeof(double), h->stream));
     L.d_gpl_old.alloc((size_t)L.n_gpl_old * nc * nc);
     if (L.n_gpl_old) CK(cudaMemsetAsync(L.d_gpl_old.p, 0, L.d_gpl_old.n * sizeof(double), h->stream));
     L.meta_dirty = true;
@@ -362,6 +412,16 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
   h->d_partial.alloc(maxleaves);
 }
 
+// May the smoother of this level exchange its partition faces in-kernel?  Every input is the same on all ranks
+// (replicated tree, parameters, options, and the collectively established pool mapping).
+bool fused_level(const omg_handle* h, const LevelHost& L) {
+  if (!h->comm || !h->p2p || !h->fused || !L.xg.any || !L.xg.shared || L.rb_remote_any || L.tail) return false;
+  if (L.nc != 16 && L.nc != 32) return false;
+  const int op = h->params.operator_type;
+  if (op < 1 || op > 4 || h->params.smoother_type != 2 || !h->fast_kernels) return false;
+  return h->n_cpu <= 9;                       // PutDev holds up to 8 peers
+}
+
 // upload metadata that changed (face tables, bc planes, parameters) and refresh the LevelDev copies
 void sync_meta(omg_handle* h) {
   if (!h->have_tree) fail("no tree: call omg_set_tree first");
@@ -379,8 +439,10 @@ void sync_meta(omg_handle* h) {
       L.d_parents.upload(L.h_parents, s); L.d_leaves.upload(L.h_leaves, s);
       L.d_rb.upload(L.h_rb, s); L.d_oldpl.upload(L.h_oldpl, s);
       L.d_bnd.upload(L.h_bnd, s); L.d_int.upload(L.h_int, s);
+      L.d_order.upload(L.h_order, s); L.d_put_ptr.upload(L.h_put_ptr, s); L.d_put_item.upload(L.h_put_item, s);
+      if (!L.d_done.p) { L.d_done.alloc(1); CK(cudaMemsetAsync(L.d_done.p, 0, sizeof(unsigned int), s)); }
       L.d_bcpl.upload(L.h_bcpl, s);
-      for (PhasePlan* X : {&L.xg, &L.xr, &L.xp}) { X->d_sdesc.upload(X->h_sdesc, s); X->d_rdesc.upload(X->h_rdesc, s); }
+      for (PhasePlan* X : {&L.xg, &L.xr, &L.xp}) { X->d_sdesc.upload(X->h_sdesc, s); X->d_rdesc.upload(X->h_rdesc, s); X->d_dst.upload(X->h_dst, s); X->d_peer_stride.upload(X->h_peer_stride, s); }
       if (L.xp.d_recv.n) CK(cudaMemsetAsync(L.xp.d_recv.p, 0, L.xp.d_recv.n * sizeof(double), s));
       L.meta_dirty = false;
     }
@@ -390,6 +452,21 @@ void sync_meta(omg_handle* h) {
     D.fkind = L.d_fkind.p; D.farg = L.d_farg.p; D.ftype = L.d_ftype.p;
     D.fkind_old = L.d_fkind_old.p; D.farg_old = L.d_farg_old.p;
     D.gpl = L.d_gpl.p; D.gpl_old = L.d_gpl_old.p; D.bcpl = L.d_bcpl.p;
+    const bool put = h->p2p && L.xg.shared;
+    D.gpl_sel = put ? h->d_epoch.p + (L.lvl - OMG_LVL_LO) : nullptr;
+    D.gpl_stride = (long long)(L.d_gpl.n / 2);
+    std::memset(&D.put, 0, sizeof(D.put));
+    if (fused_level(h, L)) {
+      PutDev& U = D.put;
+      U.n_bnd = (int)L.h_bnd.size(); U.me = h->my_rank; U.nranks = h->n_cpu; U.channel = L.lvl - OMG_LVL_LO;
+      U.n_peers = (int)L.xg.peers.size();
+      for (int q = 0; q < U.n_peers; ++q) U.peers[q] = L.xg.peers[q];
+      U.ptr = L.d_put_ptr.p; U.item = L.d_put_item.p; U.peer_base = L.xg.d_peer_base.p; U.peer_stride = L.xg.d_peer_stride.p;
+      unsigned long long* const* pf = nullptr; unsigned long long* fl = nullptr; int* er = nullptr;
+      try { omg_comm_p2p_ptrs(h->comm, &pf, &fl, &er); } catch (const std::exception& e) { fail(e.what()); }
+      U.peer_flags = pf; U.flags = fl; U.err = er;
+      U.epoch = h->d_epoch.p + (L.lvl - OMG_LVL_LO); U.done = L.d_done.p;
+    }
     D.parent = L.d_parent.p; D.coff = L.d_coff.p; D.ppatch = L.xp.d_recv.p;
     D.parents_list = L.d_parents.p; D.n_parents = (int)L.h_parents.size();
     D.leaves_list = L.d_leaves.p; D.n_leaves = (int)L.h_leaves.size();
@@ -444,9 +521,16 @@ struct Builder {
   // replicated tree only, so every rank emits the same steps).
   void smooth_boxes(int lvl, int n_cycle) {
     const int sub = (h->params.smoother_type == 2) ? 2 : 1;
-    const bool split = h->overlap && !h->profile && sub == 2 && h->L(lvl).xg.any && !h->L(lvl).tail;
+    const bool fusedx = !h->profile && fused_level(h, h->L(lvl));
+    const bool split = !fusedx && h->overlap && !h->profile && sub == 2 && h->L(lvl).xg.any && !h->L(lvl).tail;
     for (int n = 1; n <= n_cycle * sub; ++n) {
-      if (split) {
+      if (fusedx) {
+        // the partition-face boxes of this launch wait for the peers' previous faces, store their own into the peers'
+        // pools and signal; consumers other than the next half-sweep need the explicit wait emitted after the loop
+        step(S_SMOOTH, lvl, (n - 1) & 1, 3);
+        h->gz[lvl - OMG_LVL_LO] = false;
+        if (n == n_cycle * sub) step(S_PUT_WAIT, lvl);
+      } else if (split) {
         step(S_SMOOTH, lvl, (n - 1) & 1, 1);
         step(S_HALO_FORK, lvl, halo_flag(lvl));
         step(S_SMOOTH, lvl, (n - 1) & 1, 2);
@@ -531,11 +615,32 @@ void run_exchange(omg_handle* h, const PhasePlan& X, const double* send, double*
 
 // mg_fill_ghost_cells_lvl, communication part (src/m_ghost_cells.f90:142-168): faces owned by other ranks
 // arrive directly in this level's plane pool
-void exchange_ghost(omg_handle* h, int lvl, int gz, cudaStream_t s) {
+// Two transports.  put (peer-mapped pools): the pack kernel stores the faces straight into the
+// receivers' plane pools over NVLink, then one tiny kernel signals the peers and waits for their signal.
+// send/recv: pack into a send buffer, one ncclSend/ncclRecv pair per peer.
+bool ghost_by_put(omg_handle* h, int lvl) { return h->p2p && h->L(lvl).xg.shared; }
+void pack_ghost(omg_handle* h, int lvl, int gz, cudaStream_t s) {
   LevelHost& L = h->L(lvl);
   const LevelDev& Lc = lvl > h->lowest ? h->L(lvl - 1).dev : L.dev;
-  if (L.xg.n_send) { omgk::pack_ghost(L.dev, Lc, h->pdev, L.xg.d_sdesc.p, L.xg.n_send, L.xg.d_send.p, gz, s); h->launches++; }
-  run_exchange(h, L.xg, L.xg.d_send.p, L.d_gpl.p, (size_t)L.nc * L.nc, s);
+  if (!L.xg.n_send) return;
+  if (ghost_by_put(h, lvl))
+    omgk::put_ghost(L.dev, Lc, h->pdev, L.xg.d_sdesc.p, L.xg.d_dst.p, L.xg.n_send, L.xg.d_peer_base.p, L.xg.d_peer_stride.p,
+                    h->d_epoch.p + (lvl - OMG_LVL_LO), gz, s), h->puts++;
+  else omgk::pack_ghost(L.dev, Lc, h->pdev, L.xg.d_sdesc.p, L.xg.n_send, L.xg.d_send.p, gz, s);
+  h->launches++;
+}
+void transfer_ghost(omg_handle* h, int lvl, cudaStream_t s) {
+  LevelHost& L = h->L(lvl);
+  if (ghost_by_put(h, lvl)) {
+    need_comm(h);
+    try { omg_comm_signal_wait(h->comm, lvl - OMG_LVL_LO, L.xg.peers.data(), (int)L.xg.peers.size(), h->d_epoch.p + (lvl - OMG_LVL_LO), 1, s); }
+    catch (const std::exception& e) { fail(e.what()); }
+    h->exchanges++; h->launches++;
+  } else run_exchange(h, L.xg, L.xg.d_send.p, L.d_gpl.p, (size_t)L.nc * L.nc, s);
+}
+void exchange_ghost(omg_handle* h, int lvl, int gz, cudaStream_t s) {
+  pack_ghost(h, lvl, gz, s);
+  transfer_ghost(h, lvl, s);
 }
 // mg_restrict_lvl, communication part (src/m_restrict.f90:94-108); both variables of update_coarse in one message
 void exchange_restrict(omg_handle* h, int lvl, int iv0, int iv1, cudaStream_t s) {
@@ -584,18 +689,31 @@ void exec_steps(omg_handle* h, Program& P) {
   cudaStream_t s = h->stream;
   const ParamsDev& PD = h->pdev;
   for (const Step& st : P.steps) {
-    const bool prof = h->profile && st.l == h->highest && st.kind != S_TAIL && st.kind != S_SUBMEAN &&
-                      st.kind != S_CLEAR_SLOT && st.kind != S_COPY_SLOT && st.kind != S_ZERO_PHI;
+    const bool prof = h->profile && st.kind != S_SUBMEAN && st.kind != S_CLEAR_SLOT && st.kind != S_COPY_SLOT &&
+                      st.kind != S_ZERO_PHI && st.kind != S_HALO_FORK && st.kind != S_HALO_JOIN;
     cudaEvent_t pe0 = nullptr, pe1 = nullptr;
     if (prof) { CK(cudaEventCreate(&pe0)); CK(cudaEventCreate(&pe1)); CK(cudaEventRecord(pe0, s)); }
     switch (st.kind) {
       case S_SMOOTH: {
         LevelHost& L = h->L(st.l);
+        if (st.b == 3) {   // in-kernel exchange: whole level, partition-face boxes first
+          if (L.nb) {
+            if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, L.d_order.p, L.nb, 1, s)) fail("fused smoother does not apply to this level");
+            h->launches++; h->exchanges++; h->fused_smooths++;
+          }
+          // emulated ranks share one GPU: a kernel must never wait for a kernel that may not be running, so the ranks
+          // meet on the host and order their streams with events; the in-kernel waits then return at once
+          if (!omg_comm_graph_safe(h->comm)) {
+            try { omg_comm_signal_wait(h->comm, st.l - OMG_LVL_LO, L.xg.peers.data(), (int)L.xg.peers.size(), h->d_epoch.p + (st.l - OMG_LVL_LO), 0, s); }
+            catch (const std::exception& e) { fail(e.what()); }
+          }
+          break;
+        }
         const int* list = st.b == 1 ? L.d_bnd.p : st.b == 2 ? L.d_int.p : nullptr;
         const int nlist = st.b == 1 ? (int)L.h_bnd.size() : st.b == 2 ? (int)L.h_int.size() : 0;
         if (st.b && nlist == 0) break;
         if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; }
-        else if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, s)))
+        else if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, 0, s)))
           omgk::smooth(L.dev, PD, st.a, st.b ? list : nullptr, nlist, s);
         h->launches++;
       } break;
@@ -642,19 +760,31 @@ void exec_steps(omg_handle* h, Program& P) {
       case S_CLEAR_SLOT: CK(cudaMemsetAsync(h->d_scal.p + st.a, 0, sizeof(double), s)); break;
       case S_COPY_SLOT: CK(cudaMemcpyAsync(h->d_scal.p + st.a, h->d_scal.p + st.b, sizeof(double), cudaMemcpyDeviceToDevice, s)); break;
       case S_HALO: exchange_ghost(h, st.l, st.a, s); break;
-      case S_HALO_FORK:
+      case S_HALO_FORK: {
+        // pack on the compute stream, then fork: the NCCL kernel needs (nearly) empty SMs, so it must be dispatched
+        // before the interior half-sweep floods the machine -- the exchange stream has the higher priority and both
+        // kernels become ready at the same event
+        pack_ghost(h, st.l, st.a, s);
         CK(cudaEventRecord(h->ev_fork, s));
         CK(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
-        exchange_ghost(h, st.l, st.a, h->stream2);
+        transfer_ghost(h, st.l, h->stream2);
         CK(cudaEventRecord(h->ev_join, h->stream2));
-        break;
+      } break;
       case S_HALO_JOIN: CK(cudaStreamWaitEvent(s, h->ev_join, 0)); break;
+      case S_PUT_WAIT: {
+        LevelHost& L = h->L(st.l);
+        if (omg_comm_graph_safe(h->comm)) {    // NCCL back end: one single-CTA kernel polling the peers' flags
+          try { omg_comm_signal_wait(h->comm, st.l - OMG_LVL_LO, L.xg.peers.data(), (int)L.xg.peers.size(), h->d_epoch.p + (st.l - OMG_LVL_LO), 0, s); }
+          catch (const std::exception& e) { fail(e.what()); }
+          h->launches++;
+        }
+      } break;
       case S_XRESTRICT: exchange_restrict(h, st.l, st.a, st.b, s); break;
       case S_XPROLONG: exchange_prolong(h, st.l, s); break;
       case S_ALLREDUCE_MAX: need_comm(h); omg_comm_allreduce(h->comm, h->d_scal.p + st.a, OMG_RED_MAX, s); break;
       default: fail("exec_steps: unknown step");
     }
-    if (prof) { CK(cudaEventRecord(pe1, s)); h->prof_events.push_back({st.kind, {pe0, pe1}}); }
+    if (prof) { CK(cudaEventRecord(pe1, s)); h->prof_events.push_back({st.kind * 2 + (st.kind != S_TAIL && st.l == h->highest ? 1 : 0), {pe0, pe1}}); }
   }
   CK(cudaGetLastError());
 }
@@ -680,6 +810,28 @@ void run_program(omg_handle* h, Program& P) {
   CK(cudaGraphLaunch(P.graph, h->stream));
   h->launches += P.launches_per_run;
   h->graph_launches++;
+}
+
+// totals "mg total V-cycle" / "mg total FMG cycle": CUDA events around the program, read lazily
+void drain_totals(omg_handle* h, bool wait) {
+  size_t keep = 0;
+  for (auto& e : h->total_events) {
+    if (!wait && cudaEventQuery(e.second.second) != cudaSuccess) { h->total_events[keep++] = e; continue; }
+    if (wait) CK(cudaEventSynchronize(e.second.second));
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, e.second.first, e.second.second) == cudaSuccess) h->timer_acc[e.first] += ms * 1e-3;
+    cudaEventDestroy(e.second.first); cudaEventDestroy(e.second.second);
+  }
+  h->total_events.resize(keep);
+}
+void timed_run(omg_handle* h, Program& P, int timer) {
+  drain_totals(h, h->total_events.size() > 64);
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  CK(cudaEventRecord(e0, h->stream));
+  try { run_program(h, P); } catch (...) { cudaEventDestroy(e0); cudaEventDestroy(e1); throw; }
+  CK(cudaEventRecord(e1, h->stream));
+  h->total_events.push_back({timer, {e0, e1}});
 }
 
 Program& get_program(omg_handle* h, const std::string& key, bool& fresh) {
@@ -712,7 +864,7 @@ void fas_vcycle(omg_handle* h, int has_highest, int highest_lvl, int standalone,
     B.vcycle(has_highest != 0, highest_lvl, standalone != 0, want_res != 0, SCAL_MAXRES);
     B.flush();
   }
-  run_program(h, P);
+  timed_run(h, P, 0);
   if (want_res && max_res) {
     CK(cudaMemcpyAsync(max_res, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
@@ -733,7 +885,7 @@ void fas_fmg(omg_handle* h, int have_guess, int want_res, double* max_res) {
     B.fmg(have_guess != 0, want_res != 0);
     B.flush();
   }
-  run_program(h, P);
+  timed_run(h, P, 1);
   if (want_res && max_res) {
     CK(cudaMemcpyAsync(max_res, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
@@ -764,7 +916,19 @@ void collect_profile(omg_handle* h) {
   CK(cudaStreamSynchronize(h->stream));
   for (auto& e : h->prof_events) {
     float ms = 0; CK(cudaEventElapsedTime(&ms, e.second.first, e.second.second));
-    auto& acc = h->prof_acc[e.first]; acc.first += ms; acc.second += 1;
+    const int kind = e.first >> 1;
+    if (e.first & 1) { auto& acc = h->prof_acc[kind]; acc.first += ms; acc.second += 1; }
+    // phase timers of the reference: smoother, smoother g.c., coarse, correct, update coarse
+    int t = -1;
+    switch (kind) {
+      case S_SMOOTH: t = 2; break;
+      case S_HALO: case S_RB_FILL: t = 3; break;
+      case S_TAIL: case S_COARSE_SOLVE: t = 4; break;
+      case S_CORR_PROLONG: case S_XPROLONG: t = 5; break;
+      case S_RESID_RESTRICT: case S_RESID: case S_RESTRICT: case S_XRESTRICT: case S_CRHS: case S_OLDPL: case S_COPY_OLD: t = 6; break;
+      default: break;
+    }
+    if (t >= 0) h->timer_acc[t] += ms * 1e-3;
     cudaEventDestroy(e.second.first); cudaEventDestroy(e.second.second);
   }
   h->prof_events.clear();
@@ -917,7 +1081,13 @@ int omg_create(int device, omg_handle** out) {
   h->device = device;
   if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return 3; }
   cudaEventCreate(&h->ev0); cudaEventCreate(&h->ev1);
-  cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+  {
+    // the exchange stream outranks the compute stream: its pack / NCCL kernels must be dispatched as soon as SM
+    // resources free up, not after the interior half-sweep has drained
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    cudaStreamCreateWithPriority(&h->stream2, cudaStreamNonBlocking, prio_hi);
+  }
   cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming); cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
   for (int v = 0; v < OMG_MAXV; ++v) for (int f = 0; f < 6; ++f) { h->bc_type[v][f] = -10; h->bc_value[v][f] = 0.0; }
   // defaults of type(mg_t), src/m_data_structures.f90:300-327
@@ -934,8 +1104,8 @@ int omg_destroy(omg_handle* h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   if (h->comm) omg_comm_destroy(h->comm);
-  try { free_levels(h); } catch (...) {}
-  h->d_scal.free(); h->d_partial.free();
+  try { drain_totals(h, true); collect_profile(h); free_levels(h); } catch (...) {}
+  h->d_scal.free(); h->d_partial.free(); h->d_epoch.free();
   for (int q = 0; q < 2; ++q) {
     if (h->h_stage[q]) cudaFreeHost(h->h_stage[q]);
     if (h->d_stage[q]) cudaFree(h->d_stage[q]);
@@ -1057,6 +1227,7 @@ int omg_fas_vcycles(omg_handle* h, int n, double* residuals) {
     if (want && n) CK(cudaMemcpyAsync(residuals, h->d_scal.p + SCAL_RESHIST, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1)); h->last_ms = ms;
+    h->timer_acc[0] += ms * 1e-3;
   });
 }
 
@@ -1075,6 +1246,8 @@ int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* ou
     for (int l = 0; l < OMG_NLVL; ++l) h->gz[l] = false;
     Builder B{h, P, {}};
     if (w == "smooth_boxes") B.smooth_boxes(lvl, arg);
+    else if (w == "smooth_only") { for (int n = 1; n <= 2 * arg; ++n) B.emit(lvl, TOP_SMOOTH, S_SMOOTH, (n - 1) & 1); }   // timing probe: no ghost exchange
+    else if (w == "halo_only") { for (int n = 1; n <= 2 * arg; ++n) B.gf(lvl); }                                          // timing probe
     else if (w == "update_coarse") { if (lvl <= h->lowest) fail("update_coarse: lvl <= lowest_lvl"); B.update_coarse(lvl); }
     else if (w == "correct_children") { if (lvl >= h->highest) fail("correct_children: lvl >= highest_lvl"); B.correct_children_onto(lvl + 1); B.gf(lvl + 1); }
     else if (w == "coarse_solve") {
@@ -1152,10 +1325,36 @@ int omg_apply_op(omg_handle* h, int i_out) {
 }
 
 int omg_nccl_unique_id(char out[128]) { return omg_comm_unique_id(out); }
+// After the communicator exists: map every distributed level's plane pool of every rank (collective, same level
+// order on all ranks because xg.any comes from the replicated tree).  Call order contract: omg_set_tree, then
+// omg_comm_init (mg_comm_init runs before mg_allocate_storage in the reference, but the device tree only exists
+// after it; the host mirror / shim call omg_comm_init last).
+void reset_epochs(omg_handle* h) {
+  CK(cudaSetDevice(h->device));
+  if (!h->d_epoch.p) h->d_epoch.alloc(OMG_NLVL);
+  CK(cudaMemset(h->d_epoch.p, 0, OMG_NLVL * sizeof(unsigned long long)));
+  h->params_dirty = true;                    // LevelDev copies carry gpl_sel
+}
 int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks) {
   OMG_TRY(h, {
     if (h->comm) { omg_comm_destroy(h->comm); h->comm = nullptr; }
     try { h->comm = omg_comm_create_nccl(uid, rank, nranks, h->device); } catch (const std::exception& e) { fail(e.what()); }
+    reset_epochs(h);
+    for (LevelHost& L : h->levels) L.xg.shared = false;
+    if (h->have_tree && omg_comm_p2p(h->comm)) {
+      std::vector<void*> ptrs(nranks, nullptr);
+      for (LevelHost& L : h->levels) {
+        if (!L.xg.any) continue;
+        try { omg_comm_share(h->comm, L.d_gpl.p, ptrs.data()); } catch (const std::exception& e) { fail(e.what()); }
+        if (!omg_comm_p2p(h->comm)) break;                       // IPC unavailable: every rank falls back to send/recv
+        std::vector<double*> pb(nranks);
+        for (int r = 0; r < nranks; ++r) pb[r] = static_cast<double*>(ptrs[r]);
+        L.xg.d_peer_base.upload(pb, h->stream);
+        CK(cudaStreamSynchronize(h->stream));
+        L.xg.shared = true;
+      }
+      if (!omg_comm_p2p(h->comm)) for (LevelHost& L : h->levels) L.xg.shared = false;
+    }
     invalidate_programs(h);
   });
 }
@@ -1169,6 +1368,29 @@ int omg_comm_init_local(omg_handle* const* handles, int nranks) {
       if (h->comm) { omg_comm_destroy(h->comm); h->comm = nullptr; }
       try { h->comm = omg_comm_create_local(g, r, h->device); } catch (const std::exception& e) { fail(e.what()); }
       invalidate_programs(h);
+      reset_epochs(h);
+    }
+    // emulated ranks live in one process: the "peer mappings" are the other handles' pointers themselves
+    for (int r = 0; r < nranks; ++r) {
+      omg_handle* h = handles[r];
+      if (!h->have_tree) continue;
+      CK(cudaSetDevice(h->device));
+      for (size_t l = 0; l < h->levels.size(); ++l) {
+        LevelHost& L = h->levels[l];
+        L.xg.shared = false;
+        if (!L.xg.any) continue;
+        std::vector<double*> pb(nranks, nullptr);
+        bool ok = true;
+        for (int q = 0; q < nranks; ++q) {
+          omg_handle* hq = handles[q];
+          if (!hq->have_tree || hq->levels.size() != h->levels.size() || hq->device != h->device) { ok = false; break; }
+          pb[q] = hq->levels[l].d_gpl.p;
+        }
+        if (!ok) continue;
+        L.xg.d_peer_base.upload(pb, h->stream);
+        CK(cudaStreamSynchronize(h->stream));
+        L.xg.shared = true;
+      }
     }
   });
 }
@@ -1191,8 +1413,21 @@ int omg_exchange_plan(const omg_tree_desc* t, int me, int phase, int lvl, int pe
 
 int omg_sync(omg_handle* h) { OMG_TRY(h, { CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream)); }); }
 
+// mg_timers_show (src/m_data_structures.f90:562-581): the seven timers mg_add_timers registers
+// (src/m_multigrid.f90:72-81), accumulated seconds on this rank.  The two totals are always measured (CUDA events
+// around each mg_fas_vcycle / mg_fas_fmg); the five phase timers only accumulate while option "profile" is set
+// (a cycle replayed as one CUDA graph has no phase boundaries to time).  Call with names == seconds == NULL to get n.
 int omg_timers(omg_handle* h, int* n, const char** names, double* seconds) {
-  (void)h; (void)names; (void)seconds; if (n) *n = 0; return 0;
+  static const char* kNames[7] = {"mg total V-cycle", "mg total FMG cycle", "mg smoother", "mg smoother g.c.",
+                                  "mg coarse", "mg correct", "mg update coarse"};
+  OMG_TRY(h, {
+    if (n) *n = 7;
+    if (!names && !seconds) return 0;
+    CK(cudaSetDevice(h->device));
+    drain_totals(h, true);
+    collect_profile(h);
+    for (int t = 0; t < 7; ++t) { if (names) names[t] = kNames[t]; if (seconds) seconds[t] = h->timer_acc[t]; }
+  });
 }
 
 int64_t omg_stat(omg_handle* h, const char* key) {
@@ -1203,6 +1438,8 @@ int64_t omg_stat(omg_handle* h, const char* key) {
   if (k == "bytes_h2d") return h->bytes_h2d;
   if (k == "bytes_d2h") return h->bytes_d2h;
   if (k == "exchanges") return h->exchanges;
+  if (k == "fused_smooths") return h->fused_smooths;     // half-sweeps that exchanged their partition faces in-kernel
+  if (k == "puts") return h->puts;                       // ghost phases sent as peer-mapped puts
   if (k == "coarse_iters") {
     double v = 0; cudaSetDevice(h->device); cudaStreamSynchronize(h->stream);
     if (h->d_scal.p) cudaMemcpy(&v, h->d_scal.p + SCAL_COARSE_ITERS, sizeof(double), cudaMemcpyDeviceToHost);
@@ -1221,6 +1458,8 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "graph_multi") h->graph_multi = value;
     else if (k == "tail_smem") h->tail_smem = value;
     else if (k == "overlap") h->overlap = value;
+    else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
+    else if (k == "fused") { h->fused = value; h->params_dirty = true; }
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
     else if (k == "tail_cells") { h->tail_cells = value; if (h->have_tree) compute_tail(h); }
     else fail("unknown option " + k);

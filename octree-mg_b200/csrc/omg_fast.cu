@@ -46,6 +46,18 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// bounded wait for a peer's flag (see omg_comm.cu): never hang the GPU on a rank that is gone
+__device__ __forceinline__ void wait_flag(const volatile unsigned long long* f, unsigned long long want, int* err) {
+  unsigned long long t0 = 0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while (*f < want) {
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 4000000000ull) { atomicExch(err, 1); break; }
+    __nanosleep(64);
+  }
+}
+
 __device__ __forceinline__ void bc_coeffs(int type, double dr, int f, double& c0, double& c1, double& c2) {
   // bc_to_gc, src/m_ghost_cells.f90:682-698
   if (type == -10) { c0 = 2; c1 = -1; c2 = 0; }
@@ -84,12 +96,14 @@ struct SmoothSmem : TileSmem<NC, KT> {
 template <int NC, int KT, bool VC>
 __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
                                                                           const __grid_constant__ ParamsDev P, int colour,
-                                                                          const int* __restrict__ boxlist) {
+                                                                          const int* __restrict__ boxlist, int fused_put) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SmoothSmem<NC, KT, VC>& S = *reinterpret_cast<SmoothSmem<NC, KT, VC>*>(smem_raw);
   const int tid = threadIdx.x;
+  // in-kernel halo exchange (PutDev, omg_device.cuh): the first n_bnd boxes of the launch order sit on partition faces
+  const bool bnd_put = fused_put && (int)(blockIdx.x / TILES) < L.put.n_bnd;
   const int b = boxlist ? boxlist[blockIdx.x / TILES] : blockIdx.x / TILES;   // a subset of the level (partition-face / interior boxes)
   const int k0 = (blockIdx.x % TILES) * KT;
   const int oc = colour ^ 1;
@@ -122,6 +136,9 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   for (int f = 0; f < 6; ++f) { kind[f] = L.fkind[b * 6 + f]; arg[f] = L.farg[b * 6 + f]; }
   // z faces of an interior slab come from the box itself
   const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
+  // the peers' faces of the previous half-sweep must have landed in the plane pool before they are read below
+  if (bnd_put && tid >= 64 && tid < 64 + L.put.n_peers)
+    wait_flag(L.put.flags + L.put.channel * L.put.nranks + L.put.peers[tid - 64], *L.put.epoch, L.put.err);
   __syncthreads();
 
   if (tid < 32) {
@@ -175,7 +192,7 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
 #pragma unroll
   for (int f = 0; f < 6; ++f) any_plane = any_plane || (kind[f] == FK_PLANE);
   if (any_plane) {
-    const double* __restrict__ gpl = L.gpl;
+    const double* __restrict__ gpl = gpl_cur(L);
     if (!zlo_in && kind[4] == FK_PLANE)
       for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.zlo[j][m] = gpl[(size_t)arg[4] * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)]; }
     if (!zhi_in && kind[5] == FK_PLANE)
@@ -291,17 +308,55 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
       Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - rhs[q]);
     }
   }
+
+  // ---- partition-face box: store the fresh face layers into the neighbour ranks' plane pools (the copy they are not
+  // reading, (epoch + 1) & 1); the last such CTA of the launch signals the peers and bumps the epoch ----
+  if (bnd_put) {
+    __syncthreads();
+    const int slot = blockIdx.x / TILES;
+    const unsigned long long e = *L.put.epoch;
+    const double* Abox = L.var[0] + boxoff;
+    for (int it = L.put.ptr[slot]; it < L.put.ptr[slot + 1]; ++it) {
+      const int f = L.put.item[3 * it], pr = L.put.item[3 * it + 1], pl = L.put.item[3 * it + 2];
+      double* o = L.put.peer_base[pr] + (size_t)((e + 1ull) & 1ull) * (size_t)L.put.peer_stride[pr] + (size_t)pl * NC * NC;
+      const int layer = (f & 1) ? 0 : NC - 1;          // f = the RECEIVER's face (buffer_for_nb, src/m_ghost_cells.f90:348-383)
+      if (f < 4) {
+        for (int r = tid; r < KT * NC; r += kThreads) {
+          const int k = k0 + r / NC, t1 = r % NC;
+          const int i = f < 2 ? layer : t1, j = f < 2 ? t1 : layer;
+          o[k * NC + t1] = __ldcg(Abox + ((i + j + k) & 1) * L.cs + (k * NC + j) * HX + (i >> 1));
+        }
+      } else if (layer >= k0 && layer < k0 + KT) {
+        for (int r = tid; r < NC * NC; r += kThreads) {
+          const int i = r % NC, j = r / NC;
+          o[r] = __ldcg(Abox + ((i + j + layer) & 1) * L.cs + (layer * NC + j) * HX + (i >> 1));
+        }
+      }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned int prev = atomicAdd(L.put.done, 1u);
+      if (prev == (unsigned int)(L.put.n_bnd * TILES) - 1u) {
+        *L.put.done = 0u;
+        __threadfence_system();
+        for (int q = 0; q < L.put.n_peers; ++q)
+          *(volatile unsigned long long*)(L.put.peer_flags[L.put.peers[q]] + L.put.channel * L.put.nranks + L.put.me) = e + 1ull;
+        *L.put.epoch = e + 1ull;
+      }
+    }
+  }
 }
 
 template <int NC, int KT, bool VC>
-bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, cudaStream_t s) {
+bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(SmoothSmem<NC, KT, VC>);
   if (!configured) {
     if (cudaFuncSetAttribute(k_smooth_lpl_fast<NC, KT, VC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_smooth_lpl_fast<NC, KT, VC><<<(list ? n : L.nb) * (NC / KT), kThreads, smem, s>>>(L, P, colour, list);
+  k_smooth_lpl_fast<NC, KT, VC><<<(list ? n : L.nb) * (NC / KT), kThreads, smem, s>>>(L, P, colour, list, fused);
   return true;
 }
 
@@ -463,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   }
   {
     // ghost planes materialised elsewhere (refinement boundaries, faces owned by another rank)
-    const double* __restrict__ gpl = L.gpl;
+    const double* __restrict__ gpl = gpl_cur(L);
     if (!zlo_in && kind[4] == FK_PLANE)
       for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.zlo[(i + j + 1) & 1][j][i >> 1] = gpl[(size_t)arg[4] * NC * NC + r]; }
     if (!zhi_in && kind[5] == FK_PLANE)
@@ -768,18 +823,23 @@ bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev
 
 namespace omgf {
 
-bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, cudaStream_t s) {
+bool smooth_applies(const LevelDev& L, const ParamsDev& P) {
+  if (L.nc != 16 && L.nc != 32) return false;
+  if (P.op == OP_VLPL || P.op == OP_VHELMH) return L.var[4] && L.faces[4];
+  return P.op == OP_LPL || P.op == OP_HELMH;
+}
+bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, int fused, cudaStream_t s) {
   if (!all_fast || L.nb == 0) return false;
   if (list && n == 0) return true;
   if (P.op == OP_VLPL || P.op == OP_VHELMH) {
     if (!L.var[4] || !L.faces[4]) return false;
-    if (L.nc == 16) return launch_smooth<16, 16, true>(L, P, colour, list, n, s);
-    if (L.nc == 32) return launch_smooth<32, 8, true>(L, P, colour, list, n, s);
+    if (L.nc == 16) return launch_smooth<16, 16, true>(L, P, colour, list, n, fused, s);
+    if (L.nc == 32) return launch_smooth<32, 8, true>(L, P, colour, list, n, fused, s);
     return false;
   }
   if (P.op != OP_LPL && P.op != OP_HELMH) return false;
-  if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, s);
-  if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, s);
+  if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, fused, s);
+  if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, fused, s);
   return false;
 }
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s) {

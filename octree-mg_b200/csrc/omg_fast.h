@@ -7,7 +7,9 @@
 
 namespace omgf {
 // list != null: only the n boxes of the list (partition-face / interior split of a distributed level)
-bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, cudaStream_t s);
+// fused: the list is the level in launch order, partition-face boxes first; they exchange their faces in-kernel (PutDev)
+bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, int fused, cudaStream_t s);
+bool smooth_applies(const LevelDev& L, const ParamsDev& P);   // would smooth() take this level / operator?
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s);
 bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s);
 bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s);

@@ -109,6 +109,20 @@ __global__ void __launch_bounds__(kThreads) k_pack_ghost(const __grid_constant__
   else if (gz) do_pack_rb_face<GM_PHI_GZ>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
   else do_pack_rb_face<GM_PHI>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
 }
+// the same items as peer-mapped puts: item e goes straight into plane dst[2e+1] of the plane pool of rank dst[2e]
+// (peer_base[rank], mapped over NVLink), into the copy the receiver is NOT reading: (epoch + 1) & 1
+__global__ void __launch_bounds__(kThreads) k_put_ghost(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
+                                                        const __grid_constant__ ParamsDev P, const int* __restrict__ desc,
+                                                        const int* __restrict__ dst, double* const* __restrict__ peer_base,
+                                                        const long long* __restrict__ peer_stride, const unsigned long long* __restrict__ epoch, int gz) {
+  const int e = blockIdx.x;
+  const int kind = desc[4 * e], sb = desc[4 * e + 1], f = desc[4 * e + 2], off = desc[4 * e + 3];
+  double* o = peer_base[dst[2 * e]] + (size_t)((*epoch + 1ull) & 1ull) * (size_t)peer_stride[dst[2 * e]] + (size_t)dst[2 * e + 1] * L.nc * L.nc;
+  if (kind == 0) do_pack_face(L, sb, f, o, threadIdx.x, blockDim.x);
+  else if (gz) do_pack_rb_face<GM_PHI_GZ>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
+  else do_pack_rb_face<GM_PHI>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
+  __threadfence_system();
+}
 // restrict phase: desc[e] = child's local box; item = nvar blocks of (nc/2)^3
 __global__ void __launch_bounds__(kThreads) k_pack_restrict(const __grid_constant__ LevelDev Lf, const int* __restrict__ desc,
                                                             double* __restrict__ out, int iv0, int iv1) {
@@ -423,6 +437,10 @@ void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, 
 }
 void pack_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int gz, cudaStream_t s) {
   if (n) k_pack_ghost<<<n, kThreads, 0, s>>>(L, Lc, P, desc, out, gz);
+}
+void put_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, const int* dst, int n, double* const* peer_base,
+               const long long* peer_stride, const unsigned long long* epoch, int gz, cudaStream_t s) {
+  if (n) k_put_ghost<<<n, kThreads, 0, s>>>(L, Lc, P, desc, dst, peer_base, peer_stride, epoch, gz);
 }
 void pack_restrict(const LevelDev& Lf, const int* desc, int n, double* out, int iv0, int iv1, cudaStream_t s) {
   if (n) k_pack_restrict<<<n, kThreads, 0, s>>>(Lf, desc, out, iv0, iv1);

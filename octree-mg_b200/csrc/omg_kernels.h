@@ -31,6 +31,9 @@ void rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv,
 void apply_op(const LevelDev& L, const ParamsDev& P, int i_out, cudaStream_t s);
 void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv, cudaStream_t s);
 void pack_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int gz, cudaStream_t s);
+// ghost items stored directly into the receivers' plane pools (peer-mapped), copy (epoch + 1) & 1
+void put_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, const int* dst, int n, double* const* peer_base,
+               const long long* peer_stride, const unsigned long long* epoch, int gz, cudaStream_t s);
 void pack_restrict(const LevelDev& Lf, const int* desc, int n, double* out, int iv0, int iv1, cudaStream_t s);
 void unpack_restrict(const LevelDev& Lc, const int* desc, int n, const double* in, int h, int iv0, int iv1, cudaStream_t s);
 void pack_prolong(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, cudaStream_t s);

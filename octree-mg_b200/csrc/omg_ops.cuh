@@ -309,8 +309,8 @@ __device__ void do_rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsD
   const double* fv = Lf.var[iv] + (size_t)b * Lf.bs;
   const int ix = (f & 1) ? nc - 1 : 0, dix = (f & 1) ? -1 : 1;
   // coarse neighbour on another rank: the interpolated coarse values arrived with the halo exchange
-  const double* gcpl = cb <= -2 ? Lf.gpl + (size_t)(-(cb + 2)) * nc * nc : nullptr;
-  double* out = (iv == 0) ? Lf.gpl + (size_t)pl * nc * nc : Lf.faces[iv] + ((size_t)b * 6 + f) * nc * nc;
+  const double* gcpl = cb <= -2 ? gpl_cur(Lf) + (size_t)(-(cb + 2)) * nc * nc : nullptr;
+  double* out = (iv == 0) ? gpl_cur(Lf) + (size_t)pl * nc * nc : Lf.faces[iv] + ((size_t)b * 6 + f) * nc * nc;
   for (int idx = tid; idx < nc * nc; idx += nthr) {
     const int A = idx % nc, B = idx / nc;          // 0-based fine tangential indices
     const double gc = gcpl ? gcpl[idx] : rb_gc_value<GMC>(Lc, P, iv, cb, di, f, A, B);

@@ -39,6 +39,24 @@ def test_fast_kernels_with_remote_faces(oracle, product, lb):
     check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
     check(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
     assert_state_equal(orc, mg)
+    # the halo exchange of the smoother ran inside the smoother kernels (peer-mapped puts + flags), the other ghost
+    # fills as put kernels
+    assert mg.stat("fused_smooths") > 0 and mg.stat("puts") > 0
+
+
+@pytest.mark.parametrize("opts", [{"fused": 0}, {"fused": 0, "overlap": 0}, {"p2p": 0}, {"p2p": 0, "overlap": 0}])
+def test_exchange_transports(oracle, product, opts):
+    """every transport of the ghost exchange gives the same bits: in-kernel puts (default), stand-alone put kernels with
+    and without the boundary-first overlap, and packed send/recv messages (the ncclSend/ncclRecv path)"""
+    orc, _ = P.uniform_problem(oracle.OracleMg, (64, 32, 32), 16, n_cpu=4)
+    mg, _ = P.uniform_problem(group_cls(product, 4), (64, 32, 32), 16)
+    for k, v in opts.items():
+        mg.set_option(k, v)
+    check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    check(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
+    assert mg.stat("fused_smooths") == 0
+    assert (mg.stat("puts") > 0) == (opts.get("p2p", 1) == 1)
 
 
 @pytest.mark.parametrize("op,bc,lam", [(P.mg_helmholtz, "neumann0", 1.0), (P.mg_vlaplacian, "mixed", 0.0)])

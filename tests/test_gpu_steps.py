@@ -76,3 +76,20 @@ def test_max_residual_every_level(oracle, product, n, box, op, bc, lam):
     for lvl in range(orc.lowest_lvl, orc.highest_lvl + 1):
         assert orc.max_residual_lvl(lvl) == mg.max_residual_lvl(lvl)
         assert_state_equal(orc, mg, variables=(4,), ghosts_of=(), levels=[lvl])
+
+
+def test_timers(product):
+    """mg_timers_show: the reference's seven timers (src/m_multigrid.f90:72-81); totals always, phases in profile mode."""
+    mg, _ = P.uniform_problem(product.Mg, 32, 8)
+    mg.mg_fas_fmg(False)
+    mg.mg_fas_vcycle()
+    t = mg.mg_timers()
+    assert list(t) == ["mg total V-cycle", "mg total FMG cycle", "mg smoother", "mg smoother g.c.", "mg coarse",
+                       "mg correct", "mg update coarse"]
+    assert t["mg total V-cycle"] > 0 and t["mg total FMG cycle"] > 0 and t["mg smoother"] == 0
+    mg.set_option("profile", 1)
+    mg.mg_fas_vcycle()
+    mg.set_option("profile", 0)
+    t2 = mg.mg_timers()
+    assert t2["mg smoother"] > 0 and t2["mg coarse"] > 0 and t2["mg correct"] > 0 and t2["mg update coarse"] > 0
+    assert t2["mg total V-cycle"] > t["mg total V-cycle"]
