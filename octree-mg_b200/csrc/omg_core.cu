@@ -85,8 +85,8 @@ struct LevelHost {
   // in-kernel exchange (PutDev): launch order = partition-face boxes, then the rest; per partition-face box the faces it
   // sends {receiver's face, receiver rank, plane in its pool}
   bool rb_remote_any = false;           // some rank receives interpolated coarse faces on this level (replicated-tree fact)
-  std::vector<int> h_order, h_put_ptr, h_put_item;
-  DevBuf<int> d_order, d_put_ptr, d_put_item;
+  std::vector<int> h_order, h_put_ptr, h_put_item, h_launch;
+  DevBuf<int> d_order, d_put_ptr, d_put_item, d_launch;
   DevBuf<unsigned int> d_done;
   bool all_fast = false;                // every face of every box is FK_SAME or FK_PHYS (fast kernels apply)
 };
@@ -135,6 +135,7 @@ struct omg_handle {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_ms = 0.0;
   omg_comm* comm = nullptr;
+  int bnd_first_boxes = 8192;               // levels up to this many boxes launch their partition-face boxes first
   int fused = 1;                            // in-kernel exchange in the smoother where fused_level() allows (option "fused")
   int p2p = 1;                              // ghost faces as peer-mapped puts where the plane pools are shared (option "p2p")
   DevBuf<unsigned long long> d_epoch;       // [OMG_NLVL] completed ghost exchanges per level (selects the plane-pool copy)
@@ -160,7 +161,7 @@ void free_levels(omg_handle* h) {
   for (LevelHost& L : h->levels) {
     L.d_fkind.free(); L.d_farg.free(); L.d_ftype.free(); L.d_fkind_old.free(); L.d_farg_old.free();
     L.d_parent.free(); L.d_coff.free(); L.d_parents.free(); L.d_leaves.free(); L.d_rb.free(); L.d_oldpl.free();
-    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free(); L.d_bnd.free(); L.d_int.free(); L.d_order.free(); L.d_put_ptr.free(); L.d_put_item.free(); L.d_done.free();
+    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free(); L.d_bnd.free(); L.d_int.free(); L.d_order.free(); L.d_launch.free(); L.d_put_ptr.free(); L.d_put_item.free(); L.d_done.free();
     for (int v = 0; v < OMG_MAXV; ++v) { L.d_var[v].free(); L.d_faces[v].free(); }
     L.xg.free(); L.xr.free(); L.xp.free();
   }
@@ -243,6 +244,8 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
         const int nbid = h->neighbors[(size_t)(id - 1) * 6 + f];
         if (nbid > 0) { if (h->rank[nbid - 1] != r) L.xg.any = true; }
         else if (nbid == 0 && p > 0) {
+          L.rb_remote_any = true;       // any refinement boundary on the level rules the in-kernel exchange out (its
+                                        // planes are refilled by a separate kernel after every exchange)
           const int cnb = h->neighbors[(size_t)(p - 1) * 6 + f];
           if (cnb > 0 && h->rank[cnb - 1] != r) { L.xg.any = true; L.rb_remote_any = true; }
         }
@@ -343,8 +346,12 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
         }
       }
     }
-    L.h_order = L.h_bnd;
-    L.h_order.insert(L.h_order.end(), L.h_int.begin(), L.h_int.end());
+    L.h_order.assign(nb, -1);                          // box -> index among the partition-face boxes
+    for (size_t j = 0; j < L.h_bnd.size(); ++j) L.h_order[L.h_bnd[j]] = (int)j;
+    // launch order with the partition-face boxes first: on small levels their faces then leave early in the kernel
+    // (on big levels the extra indirection at every CTA start costs more than it hides, measured)
+    L.h_launch = L.h_bnd;
+    L.h_launch.insert(L.h_launch.end(), L.h_int.begin(), L.h_int.end());
     L.h_put_ptr.assign(1, 0);
     for (int b : L.h_bnd) {
       auto it = put_by_box.find(b);
@@ -439,7 +446,7 @@ void sync_meta(omg_handle* h) {
       L.d_parents.upload(L.h_parents, s); L.d_leaves.upload(L.h_leaves, s);
       L.d_rb.upload(L.h_rb, s); L.d_oldpl.upload(L.h_oldpl, s);
       L.d_bnd.upload(L.h_bnd, s); L.d_int.upload(L.h_int, s);
-      L.d_order.upload(L.h_order, s); L.d_put_ptr.upload(L.h_put_ptr, s); L.d_put_item.upload(L.h_put_item, s);
+      L.d_order.upload(L.h_order, s); L.d_launch.upload(L.h_launch, s); L.d_put_ptr.upload(L.h_put_ptr, s); L.d_put_item.upload(L.h_put_item, s);
       if (!L.d_done.p) { L.d_done.alloc(1); CK(cudaMemsetAsync(L.d_done.p, 0, sizeof(unsigned int), s)); }
       L.d_bcpl.upload(L.h_bcpl, s);
       for (PhasePlan* X : {&L.xg, &L.xr, &L.xp}) { X->d_sdesc.upload(X->h_sdesc, s); X->d_rdesc.upload(X->h_rdesc, s); X->d_dst.upload(X->h_dst, s); X->d_peer_stride.upload(X->h_peer_stride, s); }
@@ -461,7 +468,7 @@ void sync_meta(omg_handle* h) {
       U.n_bnd = (int)L.h_bnd.size(); U.me = h->my_rank; U.nranks = h->n_cpu; U.channel = L.lvl - OMG_LVL_LO;
       U.n_peers = (int)L.xg.peers.size();
       for (int q = 0; q < U.n_peers; ++q) U.peers[q] = L.xg.peers[q];
-      U.ptr = L.d_put_ptr.p; U.item = L.d_put_item.p; U.peer_base = L.xg.d_peer_base.p; U.peer_stride = L.xg.d_peer_stride.p;
+      U.slot_of = L.d_order.p; U.ptr = L.d_put_ptr.p; U.item = L.d_put_item.p; U.peer_base = L.xg.d_peer_base.p; U.peer_stride = L.xg.d_peer_stride.p;
       unsigned long long* const* pf = nullptr; unsigned long long* fl = nullptr; int* er = nullptr;
       try { omg_comm_p2p_ptrs(h->comm, &pf, &fl, &er); } catch (const std::exception& e) { fail(e.what()); }
       U.peer_flags = pf; U.flags = fl; U.err = er;
@@ -696,9 +703,9 @@ void exec_steps(omg_handle* h, Program& P) {
     switch (st.kind) {
       case S_SMOOTH: {
         LevelHost& L = h->L(st.l);
-        if (st.b == 3) {   // in-kernel exchange: whole level, partition-face boxes first
+        if (st.b == 3) {   // in-kernel exchange: whole level in one launch
           if (L.nb) {
-            if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, L.d_order.p, L.nb, 1, s)) fail("fused smoother does not apply to this level");
+            if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, L.nb <= h->bnd_first_boxes ? L.d_launch.p : nullptr, L.nb, 1, s)) fail("fused smoother does not apply to this level");
             h->launches++; h->exchanges++; h->fused_smooths++;
           }
           // emulated ranks share one GPU: a kernel must never wait for a kernel that may not be running, so the ranks
@@ -1460,6 +1467,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "overlap") h->overlap = value;
     else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
     else if (k == "fused") { h->fused = value; h->params_dirty = true; }
+    else if (k == "bnd_first_boxes") h->bnd_first_boxes = value;
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
     else if (k == "tail_cells") { h->tail_cells = value; if (h->have_tree) compute_tail(h); }
     else fail("unknown option " + k);

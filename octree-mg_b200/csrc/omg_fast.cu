@@ -102,9 +102,11 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SmoothSmem<NC, KT, VC>& S = *reinterpret_cast<SmoothSmem<NC, KT, VC>*>(smem_raw);
   const int tid = threadIdx.x;
-  // in-kernel halo exchange (PutDev, omg_device.cuh): the first n_bnd boxes of the launch order sit on partition faces
-  const bool bnd_put = fused_put && (int)(blockIdx.x / TILES) < L.put.n_bnd;
+
   const int b = boxlist ? boxlist[blockIdx.x / TILES] : blockIdx.x / TILES;   // a subset of the level (partition-face / interior boxes)
+  // in-kernel halo exchange (PutDev, omg_device.cuh): is this box on a partition face?
+  const int put_slot = fused_put ? L.put.slot_of[b] : -1;
+  const bool bnd_put = put_slot >= 0;
   const int k0 = (blockIdx.x % TILES) * KT;
   const int oc = colour ^ 1;
   const double* __restrict__ phi = L.var[0];
@@ -313,7 +315,7 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   // reading, (epoch + 1) & 1); the last such CTA of the launch signals the peers and bumps the epoch ----
   if (bnd_put) {
     __syncthreads();
-    const int slot = blockIdx.x / TILES;
+    const int slot = put_slot;
     const unsigned long long e = *L.put.epoch;
     const double* Abox = L.var[0] + boxoff;
     for (int it = L.put.ptr[slot]; it < L.put.ptr[slot + 1]; ++it) {
