@@ -113,6 +113,10 @@ int omg_restrict_lvl(omg_handle* h, int iv, int lvl);
 int omg_prolong(omg_handle* h, int lvl, int iv, int iv_to, int add);
 /* mg_apply_op with the built-in operator, src/m_multigrid.f90:439-456 */
 int omg_apply_op(omg_handle* h, int i_out);
+/* set_rhs of the implicit diffusion solvers, src/m_diffusion.f90:159-173: rhs <- f1 * phi + f2 * rhs on the owned
+ * leaves of levels 1..highest.  diffusion_solve / _vcoeff / _acoeff (:19-157) are this call between omg_set_params
+ * (lambda), omg_apply_op (order 2), omg_fas_fmg and omg_fas_vcycle: nothing but the residual leaves the device. */
+int omg_diffusion_set_rhs(omg_handle* h, double f1, double f2);
 /* repeat n V-cycles back to back without host round trips (benchmark loop of
  * tests/test_performance.f90:68-76); residuals[n] receives max_res per cycle when non-null */
 int omg_fas_vcycles(omg_handle* h, int n, double* residuals);

@@ -102,6 +102,7 @@ def _declare(G, H):
     G.omg_restrict_lvl.argtypes = [vp, ci, ci]
     G.omg_prolong.argtypes = [vp, ci, ci, ci, ci]
     G.omg_apply_op.argtypes = [vp, ci]
+    G.omg_diffusion_set_rhs.argtypes = [vp, cd, cd]
     G.omg_nccl_unique_id.argtypes = [C.c_char_p]
     G.omg_comm_init.argtypes = [vp, C.c_char_p, ci, ci]
     G.omg_comm_init_local.argtypes = [C.POINTER(vp), ci]
@@ -152,6 +153,7 @@ def _declare(G, H):
     H.omgh_box_cc.argtypes = [vp, ci]
     H.omgh_fas_vcycle.argtypes = [vp, ci, ci, ci, C.POINTER(cd), ci]
     H.omgh_fas_fmg.argtypes = [vp, ci, ci, C.POINTER(cd)]
+    H.omgh_diffusion_solve.argtypes = [vp, ci, cd, cd, ci, cd, C.POINTER(cd), C.POINTER(ci)]
 
 
 def _arr(vals, ctype):
@@ -410,6 +412,24 @@ class Mg:
         r = C.c_double(0.0)
         self._ck(self.H.omgh_fas_fmg(self.h, int(bool(have_guess)), int(want_res), C.byref(r)))
         return r.value if want_res else None
+
+    # src/m_diffusion.f90:19-157; return (last max residual, V-cycles added after the FMG cycle)
+    def _diffusion(self, kind, dt, coeff, order, max_res):
+        r, n = C.c_double(0.0), C.c_int(0)
+        self._ck(self.H.omgh_diffusion_solve(self.h, kind, dt, coeff, order, max_res, C.byref(r), C.byref(n)))
+        return r.value, n.value
+
+    def diffusion_solve(self, dt, diffusion_coeff, order, max_res):
+        return self._diffusion(0, dt, diffusion_coeff, order, max_res)
+
+    def diffusion_solve_vcoeff(self, dt, order, max_res):
+        return self._diffusion(1, dt, 1.0, order, max_res)
+
+    def diffusion_solve_acoeff(self, dt, order, max_res):
+        return self._diffusion(2, dt, 1.0, order, max_res)
+
+    def diffusion_set_rhs(self, f1, f2):
+        self._gck(self.G.omg_diffusion_set_rhs(self.gpu, f1, f2))
 
     def mg_gpu_push(self, iv):
         self._ck(self.H.omgh_gpu_push(self.h, iv))

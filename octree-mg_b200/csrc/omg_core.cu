@@ -1331,6 +1331,20 @@ int omg_apply_op(omg_handle* h, int i_out) {
   });
 }
 
+// set_rhs of src/m_diffusion.f90:159-173: rhs <- f1 * phi + f2 * rhs on the owned leaves of levels 1..highest
+int omg_diffusion_set_rhs(omg_handle* h, double f1, double f2) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    if (!h->have_tree) fail("no tree: call omg_set_tree first");
+    sync_meta(h);
+    for (int lvl = std::max(1, h->lowest); lvl <= h->highest; ++lvl) {
+      LevelHost& L = h->L(lvl);
+      if (L.h_leaves.empty()) continue;
+      omgk::axpby_leaves(L.dev, IPHI, IRHS, f1, f2, h->stream); h->launches++;
+    }
+  });
+}
+
 int omg_nccl_unique_id(char out[128]) { return omg_comm_unique_id(out); }
 // After the communicator exists: map every distributed level's plane pool of every rank (collective, same level
 // order on all ranks because xg.any comes from the replicated tree).  Call order contract: omg_set_tree, then

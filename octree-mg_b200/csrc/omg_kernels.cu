@@ -164,6 +164,21 @@ __global__ void k_sub_scalar_planes(double* p, size_t n, const double* mean) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = p[i] - m;
 }
 
+// set_rhs of m_diffusion (src/m_diffusion.f90:159-173): rhs <- f1 * phi + f2 * rhs on the leaves of a level, interior
+// cells (the only cells stored).  One CTA per leaf box, 16-B accesses (the box stride 2*cs is even); 24 B per cell.
+__global__ void __launch_bounds__(kThreads) k_axpby_leaves(const __grid_constant__ LevelDev L, int iv_x, int iv_y, double f1, double f2) {
+  const int b = L.leaves_list[blockIdx.x];
+  const double2* x = reinterpret_cast<const double2*>(L.var[iv_x] + (size_t)b * L.bs);
+  double2* y = reinterpret_cast<double2*>(L.var[iv_y] + (size_t)b * L.bs);
+  for (int idx = threadIdx.x; idx < L.bs / 2; idx += blockDim.x) {
+    const double2 xv = x[idx];
+    double2 yv = y[idx];
+    const double a0 = f1 * xv.x, b0 = f2 * yv.x, a1 = f1 * xv.y, b1 = f2 * yv.y;
+    yv.x = a0 + b0; yv.y = a1 + b1;
+    y[idx] = yv;
+  }
+}
+
 // get_sum (src/m_multigrid.f90:278-294): deterministic two-stage sum.  Stage 1: one partial per leaf
 // box (fixed in-block tree order); stage 2: one thread adds the partials in box order.
 __global__ void __launch_bounds__(kThreads) k_box_sums(const __grid_constant__ LevelDev L, int iv, double w, double* partial) {
@@ -456,6 +471,9 @@ void copy(double* dst, const double* src, size_t n, cudaStream_t s) { if (n) k_c
 void sub_scalar(double* p, size_t n, const double* mean, cudaStream_t s) { if (n) k_sub_scalar<<<grid_for(n), 256, 0, s>>>(p, n, mean); }
 void box_sums(const LevelDev& L, int iv, double w, double* partial, cudaStream_t s) {
   if (L.n_leaves) k_box_sums<<<L.n_leaves, kThreads, 0, s>>>(L, iv, w, partial);
+}
+void axpby_leaves(const LevelDev& L, int iv_x, int iv_y, double f1, double f2, cudaStream_t s) {
+  if (L.n_leaves) k_axpby_leaves<<<L.n_leaves, kThreads, 0, s>>>(L, iv_x, iv_y, f1, f2);
 }
 void final_sum(const double* partial, int n, double* acc, cudaStream_t s) { if (n) k_final_sum<<<1, 1024, 0, s>>>(partial, n, acc); }
 void div_scalar(double* acc, double denom, cudaStream_t s) { k_scale_scalar<<<1, 1, 0, s>>>(acc, denom); }

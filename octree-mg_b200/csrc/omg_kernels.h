@@ -41,6 +41,7 @@ void fill(double* p, size_t n, double v, cudaStream_t s);
 void copy(double* dst, const double* src, size_t n, cudaStream_t s);
 void sub_scalar(double* p, size_t n, const double* mean, cudaStream_t s);
 void box_sums(const LevelDev& L, int iv, double w, double* partial, cudaStream_t s);
+void axpby_leaves(const LevelDev& L, int iv_x, int iv_y, double f1, double f2, cudaStream_t s);   // y <- f1 x + f2 y on leaves
 void final_sum(const double* partial, int n, double* acc, cudaStream_t s);
 void div_scalar(double* acc, double denom, cudaStream_t s);
 // n_stage > 0: the first n_stage levels are staged in shared memory for the launch (stage_bytes = 4 * 8 * their cells)

@@ -85,6 +85,9 @@ module m_gpu_multigrid
      integer(c_int) function omg_apply_op(h, i_out) bind(C, name="omg_apply_op")
        import; type(c_ptr), value :: h; integer(c_int), value :: i_out
      end function omg_apply_op
+     integer(c_int) function omg_diffusion_set_rhs(h, f1, f2) bind(C, name="omg_diffusion_set_rhs")
+       import; type(c_ptr), value :: h; real(c_double), value :: f1, f2
+     end function omg_diffusion_set_rhs
      integer(c_int) function omg_nccl_unique_id(uid) bind(C, name="omg_nccl_unique_id")
        import; character(kind=c_char) :: uid(128)
      end function omg_nccl_unique_id
@@ -109,6 +112,7 @@ module m_gpu_multigrid
   public :: mg_gpu_attach, mg_gpu_detach, mg_gpu_set_resident, mg_gpu_set_lambda
   public :: mg_gpu_push, mg_gpu_pull
   public :: mg_fas_fmg, mg_fas_vcycle, mg_apply_op
+  public :: diffusion_solve, diffusion_solve_vcoeff, diffusion_solve_acoeff
   public :: mg_fill_ghost_cells_lvl, mg_fill_ghost_cells, mg_restrict_lvl, mg_restrict, mg_prolong
 
 contains
@@ -442,5 +446,77 @@ contains
     call check(omg_prolong(gpu%handle, lvl, iv, iv_to, merge(1, 0, add)), "mg_prolong")
     if (.not. gpu%resident) call transfer(mg, iv_to, lvl + 1, lvl + 1, .false., .false.)
   end subroutine mg_prolong
+
+  !> The three solvers of src/m_diffusion.f90 (:19-58, :64-106, :113-157) share this body: operator `op`,
+  !> lambda = order/scale, rhs from set_rhs (:159-173) on the device, FMG with a guess, V-cycles until max_res.
+  !> One push on entry and one pull on exit; in between only the residual crosses PCIe.
+  subroutine diffusion_common(mg, op, scale, order, max_res)
+    use m_multigrid, only: mg_set_methods    ! stays the reference's (host-side bookkeeping only, :27-60)
+    type(mg_t), intent(inout) :: mg
+    integer, intent(in)       :: op, order
+    real(dp), intent(in)      :: scale, max_res
+    integer, parameter        :: max_its = 10
+    integer                   :: n, e
+    real(c_double)            :: res
+    logical                   :: was_resident
+
+    if (order /= 1 .and. order /= 2) error stop "diffusion_solve: order should be 1 or 2"
+    mg%operator_type = op
+    call mg_set_methods(mg)           ! the host's own (reference) routine: bc of eps vars, subtract_mean, checks
+    was_resident = gpu%resident
+    if (.not. was_resident) then
+       call mg_gpu_push(mg, mg_iphi)
+       call mg_gpu_push(mg, mg_irhs)
+       do e = 1, n_eps_vars(mg)
+          call mg_gpu_push(mg, mg_iveps + e - 1)
+       end do
+    end if
+    if (order == 1) then
+       call mg_gpu_set_lambda(1/scale)
+       call push_params(mg)
+       call check(omg_diffusion_set_rhs(gpu%handle, -1/scale, 0.0_dp), "diffusion_solve")
+    else
+       call mg_gpu_set_lambda(0.0_dp)
+       call push_params(mg)
+       call check(omg_apply_op(gpu%handle, mg_irhs), "diffusion_solve")
+       call mg_gpu_set_lambda(2/scale)
+       call push_params(mg)
+       call check(omg_diffusion_set_rhs(gpu%handle, -2/scale, -1.0_dp), "diffusion_solve")
+    end if
+    call check(omg_fas_fmg(gpu%handle, 1, 1, res), "diffusion_solve")
+    do n = 1, max_its
+       if (res <= max_res) exit
+       call check(omg_fas_vcycle(gpu%handle, 0, 0, 1, 1, res), "diffusion_solve")
+    end do
+    call sync_out(mg)
+    if (n == max_its + 1) then
+       if (mg%my_rank == 0) print *, "Did you specify boundary conditions correctly?"
+       error stop "diffusion_solve: no convergence"
+    end if
+  end subroutine diffusion_common
+
+  !> Same interface as src/m_diffusion.f90:19
+  subroutine diffusion_solve(mg, dt, diffusion_coeff, order, max_res)
+    type(mg_t), intent(inout) :: mg
+    real(dp), intent(in)      :: dt, diffusion_coeff, max_res
+    integer, intent(in)       :: order
+    call diffusion_common(mg, mg_helmholtz, dt * diffusion_coeff, order, max_res)
+  end subroutine diffusion_solve
+
+  !> Same interface as src/m_diffusion.f90:64 (coefficient in mg_iveps on all levels)
+  subroutine diffusion_solve_vcoeff(mg, dt, order, max_res)
+    type(mg_t), intent(inout) :: mg
+    real(dp), intent(in)      :: dt, max_res
+    integer, intent(in)       :: order
+    call diffusion_common(mg, mg_vhelmholtz, dt, order, max_res)
+  end subroutine diffusion_solve_vcoeff
+
+  !> Same interface as src/m_diffusion.f90:113 (coefficients in mg_iveps1..3 on all levels)
+  subroutine diffusion_solve_acoeff(mg, dt, order, max_res)
+    type(mg_t), intent(inout) :: mg
+    real(dp), intent(in)      :: dt, max_res
+    integer, intent(in)       :: order
+    call diffusion_common(mg, mg_ahelmholtz, dt, order, max_res)
+  end subroutine diffusion_solve_acoeff
 
 end module m_gpu_multigrid

@@ -553,6 +553,55 @@ void mg_apply_op(mg_t& mg, int i_out) {                                         
   if (!mg.gpu_resident) mg_gpu_pull(mg, i_out, false);
 }
 
+// ------------------------------------------------------------------------------------------------
+// m_diffusion: the three solvers differ only in the operator and in what lambda is scaled by
+// ------------------------------------------------------------------------------------------------
+static int diffusion_common(mg_t& mg, int op, double scale, int order, double max_res, double* res_out, const char* hint) {
+  const int max_its = 10;                                                         // m_diffusion.f90:25
+  if (order != 1 && order != 2) stop("diffusion_solve: order should be 1 or 2");
+  mg.operator_type = op;
+  mg_set_methods(mg);                                                             // :29-30
+  // one push on entry, one pull on exit: the FMG cycle and the V-cycles below run device-resident
+  if (!mg.gpu_resident) {
+    need_gpu(mg);
+    mg_gpu_push(mg, mg_iphi);
+    mg_gpu_push(mg, mg_irhs);                                                     // order 1 multiplies it by f2 = 0: NaN/inf must behave as in the reference
+    for (int e = 0; e < n_eps_vars(mg); ++e) mg_gpu_push(mg, mg_iveps + e);
+  }
+  if (order == 1) {                                                               // :33-35
+    helmholtz_set_lambda(mg, 1 / scale);
+    push_params(mg);
+    gpu_check(mg, omg_diffusion_set_rhs(mg.gpu, -1 / scale, 0.0), "diffusion_solve");
+  } else {                                                                        // :36-40
+    helmholtz_set_lambda(mg, 0.0);
+    push_params(mg);
+    gpu_check(mg, omg_apply_op(mg.gpu, mg_irhs), "diffusion_solve");
+    helmholtz_set_lambda(mg, 2 / scale);
+    push_params(mg);
+    gpu_check(mg, omg_diffusion_set_rhs(mg.gpu, -2 / scale, -1.0), "diffusion_solve");
+  }
+  double res = 0.0;
+  gpu_check(mg, omg_fas_fmg(mg.gpu, 1, 1, &res), "diffusion_solve");              // :46
+  int n;
+  for (n = 1; n <= max_its; ++n) {                                                // :49-52
+    if (res <= max_res) break;
+    gpu_check(mg, omg_fas_vcycle(mg.gpu, 0, 0, 1, 1, &res), "diffusion_solve");
+  }
+  if (res_out) *res_out = res;
+  sync_out(mg);
+  if (n == max_its + 1) stop(std::string("diffusion_solve: no convergence (") + hint + ")");   // :54-58
+  return n - 1;
+}
+int diffusion_solve(mg_t& mg, double dt, double diffusion_coeff, int order, double max_res, double* res) {   // :19-58
+  return diffusion_common(mg, mg_helmholtz, dt * diffusion_coeff, order, max_res, res, "did you specify boundary conditions correctly?");
+}
+int diffusion_solve_vcoeff(mg_t& mg, double dt, int order, double max_res, double* res) {                    // :64-106
+  return diffusion_common(mg, mg_vhelmholtz, dt, order, max_res, res, "boundary conditions? or is the variation in diffusion too large?");
+}
+int diffusion_solve_acoeff(mg_t& mg, double dt, int order, double max_res, double* res) {                    // :113-157
+  return diffusion_common(mg, mg_ahelmholtz, dt, order, max_res, res, "boundary conditions? or is the variation in diffusion too large?");
+}
+
 void mg_fill_ghost_cells_lvl(mg_t& mg, int lvl, int iv) {                          // m_ghost_cells.f90:131-175
   push_params(mg);
   if (iv != mg_iphi && mg.bc[0][iv - 1].boundary_cond) stop("mg_fill_ghost_cells_lvl: boundary_cond callbacks are only supported for mg_iphi on the device");
@@ -701,6 +750,13 @@ int omgh_fas_fmg(void* h, int have_guess, int want_res, double* max_res) {
   Wrapped* w = (Wrapped*)h; H_TRY(w, mg_fas_fmg(w->mg, have_guess != 0, want_res ? max_res : nullptr));
 }
 int omgh_apply_op(void* h, int i_out) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_apply_op(w->mg, i_out)); }
+int omgh_diffusion_solve(void* h, int kind, double dt, double coeff, int order, double max_res, double* res, int* n_vcycles) {
+  Wrapped* w = (Wrapped*)h;
+  H_TRY(w, { const int n = kind == 0 ? diffusion_solve(w->mg, dt, coeff, order, max_res, res)
+                         : kind == 1 ? diffusion_solve_vcoeff(w->mg, dt, order, max_res, res)
+                                     : diffusion_solve_acoeff(w->mg, dt, order, max_res, res);
+             if (n_vcycles) *n_vcycles = n; });
+}
 int omgh_fill_ghost_cells_lvl(void* h, int lvl, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_fill_ghost_cells_lvl(w->mg, lvl, iv)); }
 int omgh_fill_ghost_cells(void* h, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_fill_ghost_cells(w->mg, iv)); }
 int omgh_phi_bc_store(void* h) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_phi_bc_store(w->mg)); }

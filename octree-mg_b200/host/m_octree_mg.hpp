@@ -130,6 +130,12 @@ void mg_fas_fmg(mg_t& mg, bool have_guess, double* max_res = nullptr);
 void mg_fas_vcycle(mg_t& mg, const int* highest_lvl = nullptr, double* max_res = nullptr, bool standalone = true);
 void mg_apply_op(mg_t& mg, int i_out);
 
+// ---- m_diffusion (src/m_diffusion.f90:19-157): implicit diffusion steps; phi(t) in mg_iphi -> phi(t + dt) ----------
+// Return the number of V-cycles added after the FMG cycle; *res (optional) receives the last max residual.
+int diffusion_solve(mg_t& mg, double dt, double diffusion_coeff, int order, double max_res, double* res = nullptr);
+int diffusion_solve_vcoeff(mg_t& mg, double dt, int order, double max_res, double* res = nullptr);   // eps in mg_iveps
+int diffusion_solve_acoeff(mg_t& mg, double dt, int order, double max_res, double* res = nullptr);   // eps in mg_iveps1..3
+
 // ---- m_ghost_cells / m_restrict / m_prolong level-wide entry points ---------------------------------
 void mg_fill_ghost_cells_lvl(mg_t& mg, int lvl, int iv);
 void mg_fill_ghost_cells(mg_t& mg, int iv);

@@ -1254,6 +1254,53 @@ void apply_op(Mg& mg, int i_out) {
     for (int id : mg.L(lvl).ids) box_op(mg, id, mg.bsl(lvl), i_out);
 }
 
+// ===========================================================================
+// Implicit diffusion: src/m_diffusion.f90 (the production caller of the cycle)
+// ===========================================================================
+// set_rhs :159-173 -- leaves of levels 1..highest only, interior cells
+void diffusion_set_rhs(Mg& mg, double f1, double f2) {
+  for (int lvl = 1; lvl <= mg.highest_lvl; ++lvl) {
+    const int nc = mg.bsl(lvl), n2 = nc + 2;
+    for (int id : mg.L(lvl).leaves) {
+      double* cc = mg.boxes[id].cc.data();
+      for (int k = 1; k <= nc; ++k) for (int j = 1; j <= nc; ++j) for (int i = 1; i <= nc; ++i) {
+        const double a = f1 * cc[cix(n2, i, j, k, IPHI)];
+        const double b = f2 * cc[cix(n2, i, j, k, IRHS)];
+        cc[cix(n2, i, j, k, IRHS)] = a + b;
+      }
+    }
+  }
+}
+
+// diffusion_solve :19-58 (op = helmholtz, coefficient folded into lambda), diffusion_solve_vcoeff :64-106,
+// diffusion_solve_acoeff :113-157 (lambda = 1/dt or 2/dt).  Returns the number of V-cycles added after the FMG cycle.
+int diffusion_solve(Mg& mg, int op, double dt, double diffusion_coeff, int order, double max_res, double* res_out) {
+  const int max_its = 10;
+  if (op != OP_HELMHOLTZ && op != OP_VHELMHOLTZ && op != OP_AHELMHOLTZ) fail("diffusion_solve: operator must be a Helmholtz variant");
+  mg.operator_type = op;
+  set_methods(mg);
+  const double scale = (op == OP_HELMHOLTZ) ? dt * diffusion_coeff : dt;
+  if (order == 1) {
+    mg.helmholtz_lambda = 1 / scale;
+    diffusion_set_rhs(mg, -1 / scale, 0.0);
+  } else if (order == 2) {
+    mg.helmholtz_lambda = 0.0;
+    apply_op(mg, IRHS);
+    mg.helmholtz_lambda = 2 / scale;
+    diffusion_set_rhs(mg, -2 / scale, -1.0);
+  } else fail("diffusion_solve: order should be 1 or 2");
+  double res = 0.0;
+  fas_fmg(mg, true, true, &res);
+  int n;
+  for (n = 1; n <= max_its; ++n) {
+    if (res <= max_res) break;
+    fas_vcycle(mg, false, 0, true, &res, true);
+  }
+  if (res_out) *res_out = res;
+  if (n == max_its + 1) fail("diffusion_solve: no convergence");
+  return n - 1;
+}
+
 }  // namespace
 
 // ===========================================================================
@@ -1395,6 +1442,10 @@ int orc_fas_vcycle(void* h, int has_highest, int highest_lvl, int want_res, doub
 }
 int orc_fas_fmg(void* h, int have_guess, int want_res, double* max_res) {
   Mg* mg = (Mg*)h; ORC_TRY(mg, fas_fmg(*mg, have_guess != 0, want_res != 0, max_res));
+}
+int orc_diffusion_set_rhs(void* h, double f1, double f2) { Mg* mg = (Mg*)h; ORC_TRY(mg, diffusion_set_rhs(*mg, f1, f2)); }
+int orc_diffusion_solve(void* h, int op, double dt, double diffusion_coeff, int order, double max_res, double* res, int* n_vcycles) {
+  Mg* mg = (Mg*)h; ORC_TRY(mg, { int n = diffusion_solve(*mg, op, dt, diffusion_coeff, order, max_res, res); if (n_vcycles) *n_vcycles = n; });
 }
 double orc_timer(void* h, int t) { return ((Mg*)h)->timers[t].t; }
 int orc_omp_threads() {

@@ -75,6 +75,9 @@ def lib():
         L.orc_fas_vcycle.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int]
         L.orc_fas_fmg.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
         L.orc_max_residual_lvl.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double)]
+        L.orc_diffusion_set_rhs.argtypes = [C.c_void_p, C.c_double, C.c_double]
+        L.orc_diffusion_solve.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, C.c_double,
+                                          C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.orc_set_omp_threads.argtypes = [C.c_int]
         _LIB = L
     return _LIB
@@ -308,6 +311,24 @@ class OracleMg:
         r = C.c_double(0.0)
         self._ck(self.L.orc_fas_fmg(self.h, int(bool(have_guess)), int(want_res), C.byref(r)))
         return r.value if want_res else None
+
+    # src/m_diffusion.f90: diffusion_solve (:19-58), diffusion_solve_vcoeff (:64-106), diffusion_solve_acoeff (:113-157)
+    def _diffusion(self, op, dt, coeff, order, max_res):
+        r, n = C.c_double(0.0), C.c_int(0)
+        self._ck(self.L.orc_diffusion_solve(self.h, op, dt, coeff, order, max_res, C.byref(r), C.byref(n)))
+        return r.value, n.value
+
+    def diffusion_solve(self, dt, diffusion_coeff, order, max_res):
+        return self._diffusion(3, dt, diffusion_coeff, order, max_res)
+
+    def diffusion_solve_vcoeff(self, dt, order, max_res):
+        return self._diffusion(4, dt, 1.0, order, max_res)
+
+    def diffusion_solve_acoeff(self, dt, order, max_res):
+        return self._diffusion(5, dt, 1.0, order, max_res)
+
+    def diffusion_set_rhs(self, f1, f2):
+        self._ck(self.L.orc_diffusion_set_rhs(self.h, f1, f2))
 
     def timers(self):
         names = ["mg total V-cycle", "mg total FMG cycle", "mg smoother", "mg smoother g.c.", "mg coarse",

@@ -228,6 +228,46 @@ def refinement_problem(cls, n_levels, box, n, smoother=mg_smoother_gsrb, refine=
     return mg, i_sol
 
 
+DIFF_MODES = (1, 2, 3)
+
+
+def diffusion_mode(X, Y, Z):
+    """a discrete eigenfunction of the cell-centred 7-point Laplacian with homogeneous Dirichlet faces on [0,1]^3"""
+    return np.sin(np.pi * DIFF_MODES[0] * X) * np.sin(np.pi * DIFF_MODES[1] * Y) * np.sin(np.pi * DIFF_MODES[2] * Z)
+
+
+def diffusion_eigenvalue(n3):
+    """sum_d (4/h_d^2) sin^2(pi m_d h_d / 2) >= 0: -Laplacian_h(mode) = this * mode"""
+    return sum(4.0 * n ** 2 * np.sin(np.pi * m / (2.0 * n)) ** 2 for n, m in zip(n3, DIFF_MODES))
+
+
+def diffusion_problem(cls, n, box, operator_type=mg_helmholtz, amr_levels=0, **kw):
+    """input of the solvers of src/m_diffusion.f90: phi(t) on every box, homogeneous Dirichlet faces, the
+    diffusion coefficient(s) of the variable-coefficient solvers in mg_iveps.. on all levels incl. ghost cells"""
+    n3 = [n] * 3 if np.isscalar(n) else list(n)
+    ne = n_eps(operator_type)
+    mg = cls(operator_type, mg_smoother_gsrb, n_extra_vars=ne, **kw)
+    for nb in range(1, 7):
+        mg.set_bc(nb, mg_iphi, mg_bc_dirichlet, 0.0)
+    mg.mg_set_methods()
+    if amr_levels:
+        build_amr_tree(mg, amr_levels, n3, box, [1.0 / n3[0]] * 3)
+    else:
+        mg.mg_build_rectangle(n3, box, [1.0 / n3[0]] * 3, [0.0] * 3, [False] * 3)
+        mg.mg_load_balance()
+        mg.mg_allocate_storage()
+    owned = hasattr(mg, "my_ids")
+    for lvl in range(mg.lowest_lvl, mg.highest_lvl + 1):
+        nc = mg.box_size_lvl(lvl)
+        for id_ in (mg.my_ids(lvl) if owned else mg.ids(lvl)):
+            cc = mg.cc(id_, nc)
+            X, Y, Z = cell_coords(mg, id_, lvl)
+            cc[mg_iphi - 1] = diffusion_mode(X, Y, Z)
+            for d in range(ne):
+                cc[mg_iveps - 1 + d] = eps_field(X, Y, Z, d)
+    return mg
+
+
 def leaf_phi(mg, iv=mg_iphi):
     """{id: interior of variable iv} over all leaves (copy)."""
     out = {}
