@@ -126,6 +126,9 @@ int omg_fas_vcycles(omg_handle* h, int n, double* residuals);
  * :387-402 plus the ghost fill that follows), "coarse_solve" (:202-208), "max_residual_lvl" (lvl; :296-311,
  * result in *out). */
 int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* out);
+/* Self-test of the branch-free fp64 division the variable-coefficient kernels use (omg_device.cuh: ddiv_batch):
+ * out[i] = a[i] / b[i] on the device, batched = 1 through ddiv_batch<6>, 0 through the compiler's `/`; host arrays. */
+int omg_debug_ddiv(int device, const double* a, const double* b, double* out, int64_t n, int batched);
 
 /* ---- multi-GPU (replaces mg_comm_init + sort_and_transfer_buffers, src/m_communication.f90) */
 int omg_nccl_unique_id(char out[128]);

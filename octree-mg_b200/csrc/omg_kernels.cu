@@ -496,3 +496,30 @@ void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n
 }
 
 }  // namespace omgk
+
+// ---- self-test of ddiv_batch (tests/test_gpu_steps.py) -------------------------------------------------------
+namespace {
+__global__ void k_debug_ddiv(const double* a, const double* b, double* out, long long n, int batched) {
+  const long long i0 = 6 * (blockIdx.x * (long long)blockDim.x + threadIdx.x);
+  if (i0 >= n) return;
+  double x[6], y[6], q[6];
+  for (int f = 0; f < 6; ++f) { const long long i = i0 + f < n ? i0 + f : n - 1; x[f] = a[i]; y[f] = b[i]; }
+  if (batched) ddiv_batch<6>(x, y, q);
+  else for (int f = 0; f < 6; ++f) q[f] = x[f] / y[f];
+  for (int f = 0; f < 6; ++f) if (i0 + f < n) out[i0 + f] = q[f];
+}
+}  // namespace
+extern "C" int omg_debug_ddiv(int device, const double* a, const double* b, double* out, int64_t n, int batched) {
+  if (n <= 0) return 0;
+  double *da = nullptr, *db = nullptr, *dc = nullptr;
+  int rc = 1;
+  if (cudaSetDevice(device) == cudaSuccess && cudaMalloc(&da, n * 8) == cudaSuccess && cudaMalloc(&db, n * 8) == cudaSuccess &&
+      cudaMalloc(&dc, n * 8) == cudaSuccess && cudaMemcpy(da, a, n * 8, cudaMemcpyHostToDevice) == cudaSuccess &&
+      cudaMemcpy(db, b, n * 8, cudaMemcpyHostToDevice) == cudaSuccess) {
+    const long long thr = (n + 5) / 6;
+    k_debug_ddiv<<<(unsigned)((thr + 255) / 256), 256>>>(da, db, dc, n, batched);
+    if (cudaMemcpy(out, dc, n * 8, cudaMemcpyDeviceToHost) == cudaSuccess) rc = 0;
+  }
+  cudaFree(da); cudaFree(db); cudaFree(dc);
+  return rc;
+}

@@ -93,3 +93,31 @@ def test_timers(product):
     t2 = mg.mg_timers()
     assert t2["mg smoother"] > 0 and t2["mg coarse"] > 0 and t2["mg correct"] > 0 and t2["mg update coarse"] > 0
     assert t2["mg total V-cycle"] > t["mg total V-cycle"]
+
+
+def test_batched_division_is_ieee_division(product):
+    """ddiv_batch (omg_device.cuh), the branch-free division of the variable-coefficient kernels, against the
+    compiler's `/` on the device and numpy's on the host: bitwise, including the operands nvcc's fast path rejects"""
+    import ctypes as C
+    G, _ = product.libs()
+    rng = np.random.default_rng(7)
+    n = 6 * 200000
+    a = rng.uniform(-4.0, 4.0, n) * 10.0 ** rng.integers(-3, 4, n)
+    b = rng.uniform(0.25, 4.0, n) * 10.0 ** rng.integers(-3, 4, n)
+    wide = slice(0, n // 3)                       # full exponent range: slow-path candidates mixed into batches
+    a[wide] = rng.uniform(-2, 2, n // 3) * 2.0 ** rng.integers(-1070, 1023, n // 3)
+    b[wide] = rng.uniform(1, 2, n // 3) * 2.0 ** rng.integers(-1070, 1023, n // 3) * rng.choice([-1.0, 1.0], n // 3)
+    special = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 5e-324, 2.2250738585072014e-308, 1.7976931348623157e308, 1.0, 3.0])
+    k = len(special)
+    a[n - k * k:] = np.repeat(special, k)
+    b[n - k * k:] = np.tile(special, k)
+    out = [np.empty(n), np.empty(n)]
+    for batched in (0, 1):
+        rc = G.omg_debug_ddiv(0, a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p),
+                              out[batched].ctypes.data_as(C.c_void_p), n, batched)
+        assert rc == 0
+    with np.errstate(all="ignore"):
+        ref = a / b
+    for got in out:
+        same = (got.view(np.uint64) == ref.view(np.uint64)) | (np.isnan(got) & np.isnan(ref))
+        assert same.all(), (a[~same][:5], b[~same][:5], got[~same][:5], ref[~same][:5])
