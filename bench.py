@@ -140,21 +140,25 @@ def main():
     ap.add_argument("--tail-cells", type=int, default=-1, help="levels up to this many cells run inside the single-launch coarse tail")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-cc", action="store_true", help="end-to-end leg moves cc slabs with ghost shells (omg_push/pull_var_packed) "
+                    "instead of interior cells (omg_copy_to/from_tree)")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
     ap.add_argument("--no-fast", action="store_true", help="general-path kernels only")
     ap.add_argument("--op", default="laplacian", choices=["laplacian", "vlaplacian", "helmholtz", "vhelmholtz"],
                     help="operator (BASELINE.json configs[3]: vlaplacian / helmholtz with Neumann BC); default = the headline Laplacian")
+    ap.add_argument("--strong", action="store_true", help="N > 1: keep the TOTAL domain at n^3 (BASELINE.json configs[4]: 1024^3 "
+                    "strong scaling) instead of n^3 per GPU")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (omg_set_option), repeatable")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    dims = domain_for(args.n, world)
+    dims = [args.n] * 3 if args.strong else domain_for(args.n, world)
     config = {"workload": "test_performance %s box %d: 7-point Laplacian, rhs=1, Dirichlet 0, standalone V(2,2) GSRB cycles%s"
                           % ("x".join(map(str, dims)), args.box, " with max_res" if args.max_res else " (mg_fas_vcycle(mg) as in test_performance.f90:68-76)"),
               "n_cycle_down": 2, "n_cycle_up": 2, "smoother": "gsrb", "box_size": args.box, "domain": dims,
               "partition": "mg_load_balance (Morton-contiguous), %d rank(s)" % world,
-              "l2": "inputs larger than L2 (4 x %.2f GB per GPU vs 126 MB)" % (args.n ** 3 * 8 / 1e9)}
+              "l2": "inputs larger than L2 (4 x %.2f GB per GPU vs 126 MB)" % (dims[0] * dims[1] * dims[2] / world * 8 / 1e9)}
 
     if args.impl == "reference":
         if rank != 0:
@@ -273,20 +277,36 @@ def main():
     value = dof * args.steps / (ms * 1e-3) / 1e9
     cycle_frac = (BYTES_PER_DOF_VCYCLE + (BYTES_PER_DOF_MAXRES if args.max_res else 0.0)) * value / peak / world
 
-    # --- end to end through the C ABI with host buffers: push phi + rhs (pinned), cycle, pull phi
+    # --- end to end through the C ABI with host buffers: the application's phi and rhs (pinned host arrays, interior
+    # cells of the grid leaves, as mg_copy_to_tree of coupling_amrvac/mod_multigrid_coupling.t:133-171 takes them) go to
+    # the device tree, one V-cycle runs, phi comes back (mg_copy_from_tree :206-234).  Leaves carry every input:
+    # mg_fas_vcycle overwrites phi and rhs of all parent boxes from the finer level before reading them (update_coarse,
+    # src/m_multigrid.f90:347-384), and phi's ghost cells are derived on the device.  --e2e-cc moves the reference's
+    # cc slabs (ghost shells included) of the leaf level instead.
     e2e = None
     if not args.no_e2e:
-        nd = int(G.omg_packed_size(gpu, -20, 20))
+        top = mg.highest_lvl
+        if args.e2e_cc:
+            nd = int(G.omg_packed_size(gpu, top, top))
+        else:
+            nd = int(G.omg_copy_size(gpu, -20, 20, 1, 0))
         hphi = torch.zeros(nd, dtype=torch.float64).pin_memory()
         hrhs = torch.ones(nd, dtype=torch.float64).pin_memory()
         r = C.c_double(0.0)
         k2 = max(1, min(args.steps, 3))
 
         def step():
-            mg._gck(G.omg_push_var_packed(gpu, P.mg_iphi, -20, 20, C.c_void_p(hphi.data_ptr()), nd))
-            mg._gck(G.omg_push_var_packed(gpu, P.mg_irhs, -20, 20, C.c_void_p(hrhs.data_ptr()), nd))
+            if args.e2e_cc:
+                mg._gck(G.omg_push_var_packed(gpu, P.mg_iphi, top, top, C.c_void_p(hphi.data_ptr()), nd))
+                mg._gck(G.omg_push_var_packed(gpu, P.mg_irhs, top, top, C.c_void_p(hrhs.data_ptr()), nd))
+            else:
+                mg._gck(G.omg_copy_to_tree(gpu, P.mg_iphi, -20, 20, 1, 0, C.c_void_p(hphi.data_ptr()), nd))
+                mg._gck(G.omg_copy_to_tree(gpu, P.mg_irhs, -20, 20, 1, 0, C.c_void_p(hrhs.data_ptr()), nd))
             mg._gck(G.omg_fas_vcycle(gpu, 0, 0, 1, int(args.max_res), C.byref(r)))
-            mg._gck(G.omg_pull_var_packed(gpu, P.mg_iphi, -20, 20, C.c_void_p(hphi.data_ptr()), nd, 1))
+            if args.e2e_cc:
+                mg._gck(G.omg_pull_var_packed(gpu, P.mg_iphi, top, top, C.c_void_p(hphi.data_ptr()), nd, 1))
+            else:
+                mg._gck(G.omg_copy_from_tree(gpu, P.mg_iphi, -20, 20, 1, 0, C.c_void_p(hphi.data_ptr()), nd))
         step()
         barrier()
         t0 = time.perf_counter()
@@ -300,7 +320,8 @@ def main():
             dt = float(tt.item())
         e2e = {"value": dof * k2 / dt / 1e9, "unit": "GDOF/s", "h2d_bytes_per_step": 2 * nd * 8 * world,
                "d2h_bytes_per_step": nd * 8 * world + 8, "steps": k2, "ms_per_step": dt / k2 * 1e3,
-               "what": "omg_push_var_packed(phi, rhs) from pinned host slabs (ghost shells included) + omg_fas_vcycle + omg_pull_var_packed(phi)"}
+               "what": ("omg_push_var_packed(phi, rhs) of the leaf level from pinned host slabs in the reference's cc layout (ghost shells included) + omg_fas_vcycle + omg_pull_var_packed(phi with ghost cells)"
+                        if args.e2e_cc else "omg_copy_to_tree(phi, rhs: interior cells of the leaves, pinned host arrays) + omg_fas_vcycle + omg_copy_from_tree(phi)")}
 
     if rank != 0:
         return
@@ -310,7 +331,7 @@ def main():
         cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     line = {"metric": "3D Poisson FAS V-cycle throughput", "value": value, "unit": "GDOF/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+            "scaling": "strong" if args.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
             "roofline": roofline, "cycle_hbm_frac": cycle_frac, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": launches_per_step * args.steps if launches_per_step else None,
             "launches_per_step": launches_per_step, "clocks": clocks, "residuals": res, "max_res_after": res_after,

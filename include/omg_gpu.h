@@ -97,6 +97,14 @@ int omg_push_var_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const dou
 int omg_pull_var_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, double* buf, int64_t n_doubles, int with_ghosts);
 int64_t omg_packed_size(omg_handle* h, int lvl_lo, int lvl_hi);  /* doubles needed by the packed calls */
 int omg_set_var_const(omg_handle* h, int iv, int lvl_lo, int lvl_hi, double value, int interior_only);
+/* mg_copy_to_tree / mg_copy_from_tree / mg_copy_from_tree_gc of the reference's application coupling
+ * (coupling_amrvac/mod_multigrid_coupling.t:133-171, 206-234, 238-267): application data <-> one variable of the tree,
+ * straight between a host buffer and the device tree.  The buffer holds the owned boxes of levels lvl_lo..lvl_hi in
+ * my_ids order (leaves_only = 1: the owned leaves, as the coupling copies grid leaves), per box nc^3 interior cells
+ * (with_ghosts = 0) or (nc+2)^3 cells incl. one ghost layer (with_ghosts = 1), i fastest.  omg_copy_size = doubles needed. */
+int omg_copy_to_tree(omg_handle* h, int iv, int lvl_lo, int lvl_hi, int leaves_only, int with_ghosts, const double* buf, int64_t n_doubles);
+int omg_copy_from_tree(omg_handle* h, int iv, int lvl_lo, int lvl_hi, int leaves_only, int with_ghosts, double* buf, int64_t n_doubles);
+int64_t omg_copy_size(omg_handle* h, int lvl_lo, int lvl_hi, int leaves_only, int with_ghosts);
 
 /* ---- the hot path -------------------------------------------------------- */
 /* mg_fas_vcycle(mg, highest_lvl, max_res, standalone), src/m_multigrid.f90:150-243.

@@ -94,6 +94,10 @@ def _declare(G, H):
     G.omg_packed_size.restype = C.c_int64
     G.omg_packed_size.argtypes = [vp, ci, ci]
     G.omg_set_var_const.argtypes = [vp, ci, ci, ci, cd, ci]
+    G.omg_copy_to_tree.argtypes = [vp, ci, ci, ci, ci, ci, vp, C.c_int64]
+    G.omg_copy_from_tree.argtypes = [vp, ci, ci, ci, ci, ci, vp, C.c_int64]
+    G.omg_copy_size.restype = C.c_int64
+    G.omg_copy_size.argtypes = [vp, ci, ci, ci, ci]
     G.omg_fas_vcycle.argtypes = [vp, ci, ci, ci, ci, C.POINTER(cd)]
     G.omg_fas_fmg.argtypes = [vp, ci, ci, C.POINTER(cd)]
     G.omg_fas_vcycles.argtypes = [vp, ci, C.POINTER(cd)]
@@ -431,6 +435,21 @@ class Mg:
 
     def diffusion_set_rhs(self, f1, f2):
         self._gck(self.G.omg_diffusion_set_rhs(self.gpu, f1, f2))
+
+    # coupling_amrvac/mod_multigrid_coupling.t:133-267: application arrays <-> device tree, no host cc arrays in between
+    def copy_size(self, leaves_only=True, with_ghosts=False, lvl_lo=-20, lvl_hi=20):
+        return int(self.G.omg_copy_size(self.gpu, lvl_lo, lvl_hi, int(leaves_only), int(with_ghosts)))
+
+    def mg_copy_to_tree(self, iv, buf, leaves_only=True, with_ghosts=False, lvl_lo=-20, lvl_hi=20):
+        buf = np.ascontiguousarray(buf, dtype=np.float64)
+        self._gck(self.G.omg_copy_to_tree(self.gpu, iv, lvl_lo, lvl_hi, int(leaves_only), int(with_ghosts),
+                                          buf.ctypes.data_as(C.c_void_p), buf.size))
+
+    def mg_copy_from_tree(self, iv, leaves_only=True, with_ghosts=False, lvl_lo=-20, lvl_hi=20):
+        out = np.empty(self.copy_size(leaves_only, with_ghosts, lvl_lo, lvl_hi))
+        self._gck(self.G.omg_copy_from_tree(self.gpu, iv, lvl_lo, lvl_hi, int(leaves_only), int(with_ghosts),
+                                            out.ctypes.data_as(C.c_void_p), out.size))
+        return out
 
     def mg_gpu_push(self, iv):
         self._ck(self.H.omgh_gpu_push(self.h, iv))

@@ -964,8 +964,8 @@ void scatter_slab(double* dst, const double* src, int nc, bool faces) {
 }
 
 // transfer a list of (local box, host pointer) pairs of one level; packed: host slabs are contiguous from base
-void push_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxes, const double* const* ptrs, const double* packed) {
-  const size_t slab = (size_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2);
+void push_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxes, const double* const* ptrs, const double* packed, int shell = 1) {
+  const size_t slab = (size_t)(L.nc + 2 * shell) * (L.nc + 2 * shell) * (L.nc + 2 * shell);
   ensure_stage(h, slab);
   const int chunk = h->stage_boxes;
   int q = 0;
@@ -981,15 +981,15 @@ void push_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxe
     std::memcpy(h->h_boxidx[q], boxes.data() + c0, n * sizeof(int));
     CK(cudaMemcpyAsync(h->d_stage[q], src, (size_t)n * slab * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->d_boxidx[q], h->h_boxidx[q], n * sizeof(int), cudaMemcpyHostToDevice, h->stream));
-    omgk::unpack(L.dev, v, h->d_boxidx[q], n, h->d_stage[q], v >= 4, h->stream);
+    omgk::unpack(L.dev, v, h->d_boxidx[q], n, h->d_stage[q], v >= 4, shell, h->stream);
     CK(cudaEventRecord(h->stage_ev[q], h->stream));
     h->launches++; h->bytes_h2d += (int64_t)n * slab * sizeof(double);
   }
   CK(cudaStreamSynchronize(h->stream));
 }
 
-void pull_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxes, double* const* ptrs, double* packed, int with_ghosts) {
-  const size_t slab = (size_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2);
+void pull_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxes, double* const* ptrs, double* packed, int with_ghosts, int shell = 1) {
+  const size_t slab = (size_t)(L.nc + 2 * shell) * (L.nc + 2 * shell) * (L.nc + 2 * shell);
   ensure_stage(h, slab);
   const int chunk = h->stage_boxes;
   const int gm = with_ghosts ? ghost_mode_for(v) : -1;
@@ -1005,7 +1005,7 @@ void pull_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxe
     const int n = (int)std::min<size_t>(chunk, boxes.size() - c0);
     std::memcpy(h->h_boxidx[q], boxes.data() + c0, n * sizeof(int));
     CK(cudaMemcpyAsync(h->d_boxidx[q], h->h_boxidx[q], n * sizeof(int), cudaMemcpyHostToDevice, h->stream));
-    omgk::pack(L.dev, h->pdev, v, h->d_boxidx[q], n, h->d_stage[q], gm, h->stream);
+    omgk::pack(L.dev, h->pdev, v, h->d_boxidx[q], n, h->d_stage[q], gm, shell, h->stream);
     double* dst = packed ? packed + c0 * slab : h->h_stage[q];
     CK(cudaMemcpyAsync(dst, h->d_stage[q], (size_t)n * slab * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaEventRecord(h->stage_ev[q], h->stream));
@@ -1046,7 +1046,17 @@ void push_pull_ids(omg_handle* h, int iv, int n, const int32_t* ids, const doubl
   }
 }
 
-void push_pull_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const double* cbuf, double* buf, int64_t n_doubles, int with_ghosts, bool push) {
+// boxes of a level taking part in a packed transfer: all local boxes, or the local leaves only (in box order)
+std::vector<int> packed_boxes(const LevelHost& L, bool leaves_only) {
+  if (leaves_only) return L.h_leaves;
+  std::vector<int> boxes(L.nb);
+  for (int b = 0; b < L.nb; ++b) boxes[b] = b;
+  return boxes;
+}
+
+// shell = 1: slabs in the reference's cc layout (ghost shell included); shell = 0: interior cells only
+void push_pull_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const double* cbuf, double* buf, int64_t n_doubles, int with_ghosts, bool push,
+                      int shell = 1, bool leaves_only = false) {
   CK(cudaSetDevice(h->device));
   sync_meta(h);
   const int v = check_iv(h, iv);
@@ -1055,12 +1065,13 @@ void push_pull_packed(omg_handle* h, int iv, int lvl_lo, int lvl_hi, const doubl
   int64_t off = 0;
   for (int lvl = lvl_lo; lvl <= lvl_hi; ++lvl) {
     LevelHost& L = h->L(lvl);
-    const int64_t slab = (int64_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2);
-    if (off + slab * L.nb > n_doubles) fail("packed transfer: buffer too small");
-    std::vector<int> boxes(L.nb); for (int b = 0; b < L.nb; ++b) boxes[b] = b;
-    if (push) push_level(h, L, v, boxes, nullptr, cbuf + off);
-    else pull_level(h, L, v, boxes, nullptr, buf + off, with_ghosts);
-    off += slab * L.nb;
+    const int64_t edge = L.nc + 2 * shell, slab = edge * edge * edge;
+    const std::vector<int> boxes = packed_boxes(L, leaves_only);
+    if (boxes.empty()) continue;
+    if (off + slab * (int64_t)boxes.size() > n_doubles) fail("packed transfer: buffer too small");
+    if (push) push_level(h, L, v, boxes, nullptr, cbuf + off, shell);
+    else pull_level(h, L, v, boxes, nullptr, buf + off, with_ghosts, shell);
+    off += slab * (int64_t)boxes.size();
   }
 }
 
@@ -1189,6 +1200,24 @@ int64_t omg_packed_size(omg_handle* h, int lvl_lo, int lvl_hi) {
   for (int lvl = std::max(lvl_lo, h->lowest); lvl <= std::min(lvl_hi, h->highest); ++lvl) {
     LevelHost& L = h->L(lvl);
     n += (int64_t)(L.nc + 2) * (L.nc + 2) * (L.nc + 2) * L.nb;
+  }
+  return n;
+}
+// mg_copy_to_tree / mg_copy_from_tree[_gc] (coupling_amrvac/mod_multigrid_coupling.t:133-171,206-267): the application's
+// grids <-> the tree, here host buffer <-> device tree in one pipelined pass (no host cc arrays in between)
+int omg_copy_to_tree(omg_handle* h, int iv, int lvl_lo, int lvl_hi, int leaves_only, int with_ghosts, const double* buf, int64_t n_doubles) {
+  OMG_TRY(h, push_pull_packed(h, iv, lvl_lo, lvl_hi, buf, nullptr, n_doubles, 0, true, with_ghosts ? 1 : 0, leaves_only != 0));
+}
+int omg_copy_from_tree(omg_handle* h, int iv, int lvl_lo, int lvl_hi, int leaves_only, int with_ghosts, double* buf, int64_t n_doubles) {
+  OMG_TRY(h, push_pull_packed(h, iv, lvl_lo, lvl_hi, nullptr, buf, n_doubles, with_ghosts, false, with_ghosts ? 1 : 0, leaves_only != 0));
+}
+int64_t omg_copy_size(omg_handle* h, int lvl_lo, int lvl_hi, int leaves_only, int with_ghosts) {
+  if (!h || !h->have_tree) return -1;
+  int64_t n = 0;
+  for (int lvl = std::max(lvl_lo, h->lowest); lvl <= std::min(lvl_hi, h->highest); ++lvl) {
+    LevelHost& L = h->L(lvl);
+    const int64_t edge = L.nc + (with_ghosts ? 2 : 0);
+    n += edge * edge * edge * (int64_t)(leaves_only ? L.h_leaves.size() : (size_t)L.nb);
   }
   return n;
 }

@@ -341,20 +341,21 @@ __global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ leve
 }
 
 // ------------------------------------------------------------------ host <-> device layout ----
-// staging slab per box: (nc+2)^3 doubles, reference order cc(i, j, k) i fastest, ghost shell included.
+// staging slab per box: (nc+2*shell)^3 doubles, reference order cc(i, j, k) i fastest; shell = 1: ghost shell included
+// (the reference's cc arrays), shell = 0: interior cells only (mg_copy_from_tree, coupling_amrvac/mod_multigrid_coupling.t:206-234).
 __global__ void __launch_bounds__(kThreads) k_unpack(const __grid_constant__ LevelDev L, int iv, const int* __restrict__ boxes,
-                                                     const double* __restrict__ stage, int with_faces) {
+                                                     const double* __restrict__ stage, int with_faces, int shell) {
   const int b = boxes[blockIdx.x];
-  const int nc = L.nc, n2 = nc + 2;
+  const int nc = L.nc, n2 = nc + 2 * shell;
   const double* s = stage + (size_t)blockIdx.x * n2 * n2 * n2;
   double* v = L.var[iv] + (size_t)b * L.bs;
   for (int idx = threadIdx.x; idx < L.bs; idx += blockDim.x) {
     const int colour = idx / L.cs;
     int i, j, k;
     if (!decode_colour(L, colour, idx - colour * L.cs, i, j, k)) continue;
-    v[idx] = s[((size_t)(k + 1) * n2 + (j + 1)) * n2 + (i + 1)];
+    v[idx] = s[((size_t)(k + shell) * n2 + (j + shell)) * n2 + (i + shell)];
   }
-  if (with_faces && L.faces[iv]) {
+  if (with_faces && shell && L.faces[iv]) {
     double* fc = L.faces[iv] + (size_t)b * 6 * nc * nc;
     for (int idx = threadIdx.x; idx < 6 * nc * nc; idx += blockDim.x) {
       const int f = idx / (nc * nc), r = idx - f * nc * nc, t1 = r % nc, t2 = r / nc;
@@ -368,20 +369,22 @@ __global__ void __launch_bounds__(kThreads) k_unpack(const __grid_constant__ Lev
 
 // ghost_mode: -1 none, else GhostMode for the six faces
 __global__ void __launch_bounds__(kThreads) k_pack(const __grid_constant__ LevelDev L, const __grid_constant__ ParamsDev P, int iv,
-                                                   const int* __restrict__ boxes, double* __restrict__ stage, int ghost_mode) {
+                                                   const int* __restrict__ boxes, double* __restrict__ stage, int ghost_mode, int shell) {
   const int b = boxes[blockIdx.x];
-  const int nc = L.nc, n2 = nc + 2;
+  const int nc = L.nc, n2 = nc + 2 * shell;
   double* s = stage + (size_t)blockIdx.x * n2 * n2 * n2;
   const double* v = L.var[iv] + (size_t)b * L.bs;
-  for (int idx = threadIdx.x; idx < n2 * n2 * n2; idx += blockDim.x) s[idx] = 0.0;
-  __syncthreads();
+  if (shell) {
+    for (int idx = threadIdx.x; idx < n2 * n2 * n2; idx += blockDim.x) s[idx] = 0.0;
+    __syncthreads();
+  }
   for (int idx = threadIdx.x; idx < L.bs; idx += blockDim.x) {
     const int colour = idx / L.cs;
     int i, j, k;
     if (!decode_colour(L, colour, idx - colour * L.cs, i, j, k)) continue;
-    s[((size_t)(k + 1) * n2 + (j + 1)) * n2 + (i + 1)] = v[idx];
+    s[((size_t)(k + shell) * n2 + (j + shell)) * n2 + (i + shell)] = v[idx];
   }
-  if (ghost_mode >= 0) {
+  if (ghost_mode >= 0 && shell) {
     for (int idx = threadIdx.x; idx < 6 * nc * nc; idx += blockDim.x) {
       const int f = idx / (nc * nc), r = idx - f * nc * nc, t1 = r % nc, t2 = r / nc;
       const int g = (f & 1) ? nc : -1;
@@ -488,11 +491,11 @@ void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_o
   }
   k_tail<<<1, 1024, stage_bytes, s>>>(levels, P, ops, n_ops, scal, n_stage);
 }
-void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, cudaStream_t s) {
-  if (n) k_unpack<<<n, kThreads, 0, s>>>(L, iv, boxes, stage, with_faces);
+void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, int shell, cudaStream_t s) {
+  if (n) k_unpack<<<n, kThreads, 0, s>>>(L, iv, boxes, stage, with_faces, shell);
 }
-void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, cudaStream_t s) {
-  if (n) k_pack<<<n, kThreads, 0, s>>>(L, P, iv, boxes, stage, ghost_mode);
+void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, int shell, cudaStream_t s) {
+  if (n) k_pack<<<n, kThreads, 0, s>>>(L, P, iv, boxes, stage, ghost_mode, shell);
 }
 
 }  // namespace omgk

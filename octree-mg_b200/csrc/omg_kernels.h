@@ -47,6 +47,7 @@ void div_scalar(double* acc, double denom, cudaStream_t s);
 // n_stage > 0: the first n_stage levels are staged in shared memory for the launch (stage_bytes = 4 * 8 * their cells)
 void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, int n_stage, size_t stage_bytes,
           cudaStream_t s);
-void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, cudaStream_t s);
-void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, cudaStream_t s);
+// shell = 1: slabs of (nc+2)^3 with the ghost shell (the reference's cc arrays); 0: interior cells only, nc^3
+void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, int shell, cudaStream_t s);
+void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, int shell, cudaStream_t s);
 }  // namespace omgk

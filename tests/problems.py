@@ -265,6 +265,10 @@ def diffusion_problem(cls, n, box, operator_type=mg_helmholtz, amr_levels=0, **k
             cc[mg_iphi - 1] = diffusion_mode(X, Y, Z)
             for d in range(ne):
                 cc[mg_iveps - 1 + d] = eps_field(X, Y, Z, d)
+    # The order-2 solvers apply the operator to phi(t) first (m_diffusion.f90:36-38), which reads phi's ghost cells:
+    # make them the ones a ghost-cell fill produces, as they are after any previous solve.  (The device never stores
+    # phi ghost cells -- it derives them, DESIGN.md section 3 -- so for it this is the only possible state.)
+    mg.mg_fill_ghost_cells(mg_iphi)
     return mg
 
 

@@ -121,3 +121,53 @@ def test_batched_division_is_ieee_division(product):
     for got in out:
         same = (got.view(np.uint64) == ref.view(np.uint64)) | (np.isnan(got) & np.isnan(ref))
         assert same.all(), (a[~same][:5], b[~same][:5], got[~same][:5], ref[~same][:5])
+
+
+@pytest.mark.parametrize("amr", [False, True])
+def test_copy_to_and_from_tree(product, amr):
+    """omg_copy_to_tree / omg_copy_from_tree (mg_copy_to_tree, mg_copy_from_tree[_gc] of
+    coupling_amrvac/mod_multigrid_coupling.t:133-267): host buffer <-> device tree, leaves or whole levels, with or
+    without the ghost layer, against the host cc arrays moved by mg_gpu_push / mg_gpu_pull"""
+    if amr:
+        mg, _ = P.refinement_problem(product.Mg, 3, 8, 16, gpu_resident=True)
+    else:
+        mg, _ = P.uniform_problem(product.Mg, 32, 8, bc="dirichlet0", gpu_resident=True)
+    rng = np.random.default_rng(3)
+    lvls = range(mg.lowest_lvl, mg.highest_lvl + 1)
+    for leaves_only in (True, False):
+        boxes = [(lvl, id_) for lvl in lvls for id_ in (mg.leaves(lvl) if leaves_only else mg.ids(lvl))]
+        # interior cells in: every other cell of the device copy must keep its previous value
+        for _, id_ in P.all_ids(mg):
+            mg.cc(id_)[P.mg_irhs - 1] = -7.0
+        mg.mg_gpu_push(P.mg_irhs)
+        parts = [rng.standard_normal(mg.box_size_lvl(lvl) ** 3) for lvl, _ in boxes]
+        assert mg.copy_size(leaves_only, False) == sum(p.size for p in parts)
+        mg.mg_copy_to_tree(P.mg_irhs, np.concatenate(parts), leaves_only=leaves_only)
+        mg.mg_gpu_pull(P.mg_irhs, False)
+        touched = {id_ for _, id_ in boxes}
+        for (lvl, id_), part in zip(boxes, parts):
+            nc = mg.box_size_lvl(lvl)
+            assert np.array_equal(mg.cc(id_)[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1], part.reshape(nc, nc, nc))
+        for _, id_ in P.all_ids(mg):
+            if id_ not in touched:
+                assert np.all(mg.cc(id_)[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1] == -7.0)
+        # out again, interior only and with the ghost layer phi's boundary conditions / neighbours define
+        got = mg.mg_copy_from_tree(P.mg_irhs, leaves_only=leaves_only)
+        assert np.array_equal(got, np.concatenate(parts))
+        for _, id_ in P.all_ids(mg):
+            cc = mg.cc(id_)
+            cc[P.mg_iphi - 1] = rng.standard_normal(cc[P.mg_iphi - 1].shape)
+        mg.mg_gpu_push(P.mg_iphi)
+        got = mg.mg_copy_from_tree(P.mg_iphi, leaves_only=leaves_only, with_ghosts=True)
+        mg.mg_gpu_pull(P.mg_iphi, True)
+        want = np.concatenate([mg.cc(id_)[P.mg_iphi - 1].ravel() for _, id_ in boxes])
+        from compare import face_slices
+        off = 0
+        for lvl, id_ in boxes:          # compare interiors and the six faces (edges / corners of the shell are not defined)
+            n2 = mg.box_size_lvl(lvl) + 2
+            a = got[off:off + n2 ** 3].reshape(n2, n2, n2)
+            b = want[off:off + n2 ** 3].reshape(n2, n2, n2)
+            assert np.array_equal(a[1:-1, 1:-1, 1:-1], b[1:-1, 1:-1, 1:-1])
+            for sl in face_slices(n2 - 2):
+                assert np.array_equal(a[sl], b[sl])
+            off += n2 ** 3
