@@ -406,6 +406,8 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
     LevelDev& D = L.dev;
     std::memset(&D, 0, sizeof(D));
     D.lvl = lvl; D.nc = nc; D.hx = hx; D.nb = nb; D.cs = nc * nc * hx; D.bs = 2 * D.cs;
+    D.sh_nc = D.sh_hx = -1;
+    if (nc >= 2 && (nc & (nc - 1)) == 0) { D.sh_nc = 0; while ((1 << D.sh_nc) < nc) ++D.sh_nc; D.sh_hx = D.sh_nc - 1; }
     for (int d = 0; d < 3; ++d) {
       const double dr = t->dr[(size_t)(lvl - OMG_LVL_LO) * 3 + d];
       D.dr[d] = dr; D.idr2[d] = 1 / (dr * dr);
@@ -755,7 +757,7 @@ void exec_steps(omg_handle* h, Program& P) {
       case S_TAIL: {
         // stage the tail levels in shared memory when all four variables of all of them fit (option "tail_smem")
         int n_stage = 0; size_t bytes = 0;
-        if (h->tail_smem) for (LevelHost& L : h->levels) { if (!L.tail) break; ++n_stage; bytes += (size_t)4 * L.nb * L.dev.bs * sizeof(double); }
+        if (h->tail_smem) for (LevelHost& L : h->levels) { if (!L.tail) break; ++n_stage; bytes += (size_t)4 * L.nb * L.dev.bs * sizeof(double) + (size_t)32 * L.nb * sizeof(int); }   // variables + face / box tables (k_tail)
         omgk::tail(h->d_levels.p, PD, P.d_ops.p + st.a, st.b, h->d_scal.p, n_stage, bytes, s); h->launches++;
       } break;
       case S_ZERO_PHI: {

@@ -313,6 +313,15 @@ __global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ leve
         const size_t n = (size_t)levels[l].nb * levels[l].bs;
         for (int v = 0; v < 4; ++v) { slev[l].var[v] = stage + off; off += n; }
       }
+      // the per-face and per-box tables follow the variables: every boundary cell's neighbour gather starts with a
+      // dependent fkind -> farg -> ftype chain, which costs an L2 round trip each when the tables stay in global memory
+      int* it = reinterpret_cast<int*>(stage + off);
+      for (int l = 0; l < n_stage; ++l) {
+        const int nf = levels[l].nb * 6, nb = levels[l].nb;
+        slev[l].fkind = it; it += nf; slev[l].farg = it; it += nf; slev[l].ftype = it; it += nf;
+        slev[l].fkind_old = it; it += nf; slev[l].farg_old = it; it += nf;
+        slev[l].parent = it; it += nb; slev[l].coff = it; it += nb;
+      }
     }
     __syncthreads();
     for (int l = 0; l < n_stage; ++l) {
@@ -321,6 +330,15 @@ __global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ leve
         const double* __restrict__ src = levels[l].var[v];
         double* dst = slev[l].var[v];
         for (int i = tid; i < n; i += nthr) dst[i] = src[i];
+      }
+      const int nf = levels[l].nb * 6, nb = levels[l].nb;
+      for (int i = tid; i < nf; i += nthr) {
+        const_cast<int*>(slev[l].fkind)[i] = levels[l].fkind[i]; const_cast<int*>(slev[l].farg)[i] = levels[l].farg[i];
+        const_cast<int*>(slev[l].ftype)[i] = levels[l].ftype[i];
+        const_cast<int*>(slev[l].fkind_old)[i] = levels[l].fkind_old[i]; const_cast<int*>(slev[l].farg_old)[i] = levels[l].farg_old[i];
+      }
+      for (int i = tid; i < nb; i += nthr) {
+        const_cast<int*>(slev[l].parent)[i] = levels[l].parent[i]; const_cast<int*>(slev[l].coff)[i] = levels[l].coff[i];
       }
     }
     __syncthreads();

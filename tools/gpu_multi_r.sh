@@ -1,0 +1,20 @@
+#!/bin/bash
+# weak (512^3 per GPU) and strong (1024^3 in total, BASELINE configs[4]) scaling at the GPU counts given as arguments
+mkdir -p gpurun_out
+nvidia-smi -L > gpurun_out/gpus.txt
+for N in "$@"; do
+  for MODE in weak strong; do
+    EXTRA=""; [ $MODE = strong ] && EXTRA="--strong --n 1024"
+    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 \
+      bench.py --gpus $N --steps 10 --warmup 3 $EXTRA > gpurun_out/bench_n${N}_${MODE}.json 2> gpurun_out/bench_n${N}_${MODE}.err
+    echo "N=$N $MODE rc=$?"; python - <<PY
+import json
+try:
+    d=json.loads([l for l in open('gpurun_out/bench_n${N}_${MODE}.json') if l.startswith('{')][-1])
+    print(d['n_gpus'], d['scaling'], round(d['value'],2), 'GDOF/s', round(d['ms_per_step'],3), 'ms', d['launches_per_step'], d['config']['domain'], d['max_res_after'], 'e2e', d['e2e'] and round(d['e2e']['value'],2))
+except Exception as e:
+    print('FAILED', e)
+PY
+    grep -v "OMP_NUM_THREADS\|^\*\*\*\|destroy_process_group" gpurun_out/bench_n${N}_${MODE}.err | tail -3
+  done
+done
