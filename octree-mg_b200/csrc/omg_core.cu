@@ -122,7 +122,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -476,6 +476,8 @@ void sync_meta(omg_handle* h) {
       U.peer_flags = pf; U.flags = fl; U.err = er;
       U.epoch = h->d_epoch.p + (L.lvl - OMG_LVL_LO); U.done = L.d_done.p;
     }
+    D.simple = (h->tail_simple && L.nb == 1 && D.sh_nc >= 0) ? 1 : 0;
+    for (int f = 0; f < 6 && D.simple; ++f) if (L.h_fkind[f] != FK_PHYS || L.h_farg[f] >= 0) D.simple = 0;
     D.parent = L.d_parent.p; D.coff = L.d_coff.p; D.ppatch = L.xp.d_recv.p;
     D.parents_list = L.d_parents.p; D.n_parents = (int)L.h_parents.size();
     D.leaves_list = L.d_leaves.p; D.n_leaves = (int)L.h_leaves.size();
@@ -1509,6 +1511,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "fast_kernels") h->fast_kernels = value;
     else if (k == "graph_multi") h->graph_multi = value;
     else if (k == "tail_smem") h->tail_smem = value;
+    else if (k == "tail_simple") { h->tail_simple = value; h->params_dirty = true; }
     else if (k == "overlap") h->overlap = value;
     else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
     else if (k == "fused") { h->fused = value; h->params_dirty = true; }

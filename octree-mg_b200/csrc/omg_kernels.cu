@@ -217,7 +217,9 @@ __global__ void k_scale_scalar(double* acc, double inv_volume) { *acc = *acc / i
 // ------------------------------------------------------------------ tail interpreter ---------
 template <int OP>
 __device__ void tail_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
-  if (P.smoother == 1) {   // mg_smoother_gs
+  if ((OP == OP_LPL || OP == OP_HELMH) && L.simple && P.smoother == 2) {
+    simple_smooth(L, P, colour, tid, nthr);
+  } else if (P.smoother == 1) {   // mg_smoother_gs
     for (int b = 0; b < L.nb; ++b) do_gs_snapshot(L, P, b, tid, nthr);
     __syncthreads();
     for (int b = 0; b < L.nb; ++b) do_gs_sweep<OP>(L, P, b, tid, nthr);
@@ -237,13 +239,16 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
   for (int o = 0; o < n_ops; ++o) {
     const TailOp op = ops[o];
     const LevelDev& L = levels[op.l];
+    // one box between constant physical boundaries, Laplacian / Helmholtz: branch-free neighbour gathers (omg_ops.cuh)
+    const bool fast = (OP == OP_LPL || OP == OP_HELMH) && L.simple && P.smoother == 2;
     switch (op.type) {
       case TOP_SMOOTH:
         tail_smooth<OP>(L, P, op.a, tid, nthr);
         break;
       case TOP_RESID: {
         double m = 0.0;
-        for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
+        if (fast) m = simple_resid<OP>(L, P, tid, nthr);
+        else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
         if (op.a >= 0) { m = block_max(m, red); if (tid == 0) atomic_max_nonneg(&scal[op.a], m); }
       } break;
       case TOP_RESTRICT: {
@@ -251,7 +256,8 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
         for (int b = 0; b < L.nb; ++b) { do_restrict(L, Lc, op.a, b, tid, nthr); if (op.b >= 0) do_restrict(L, Lc, op.b, b, tid, nthr); }
       } break;
       case TOP_CRHS:
-        for (int q = 0; q < L.n_parents; ++q) do_crhs<OP>(L, P, L.parents_list[q], tid, nthr);
+        if (fast && L.n_parents == 1) simple_crhs<OP>(L, P, tid, nthr);
+        else for (int q = 0; q < L.n_parents; ++q) do_crhs<OP>(L, P, L.parents_list[q], tid, nthr);
         break;
       case TOP_OLDPL:
         for (int e = 0; e < L.n_oldpl; ++e) do_oldpl(L, P, e, tid, nthr);
@@ -272,7 +278,8 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
       case TOP_COARSE_SOLVE: {
         // coarse loop of mg_fas_vcycle, src/m_multigrid.f90:202-208
         double m = 0.0;
-        for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
+        if (fast) m = simple_resid<OP>(L, P, tid, nthr);
+        else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
         const double init_res = block_max(m, red);
         int it = 0;
         for (int i = 1; i <= op.b; ++i) {
@@ -281,7 +288,8 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
             __syncthreads();
           }
           m = 0.0;
-          for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
+          if (fast) m = simple_resid<OP>(L, P, tid, nthr);
+          else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
           const double res = block_max(m, red);
           it = i;
           if (res < scal[SCAL_COARSE_REL] * init_res || res < scal[SCAL_COARSE_ABS]) break;

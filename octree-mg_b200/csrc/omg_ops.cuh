@@ -366,6 +366,88 @@ __device__ void do_fill_stored(const LevelDev& L, const ParamsDev& P, int iv, co
   }
 }
 
+// ---- "simple" levels of the tail: ONE power-of-two box whose six faces are physical boundaries with constant
+// values (LevelDev::simple; the coarse end of every uniform grid).  The general path classifies each of the six
+// neighbours of each cell through cell_at (~900 instructions per cell, ncu r01r); here the six in-box neighbours are
+// loaded with clamped indices and a ghost value replaces the out-of-box one by a select -- the same expression
+// c0*b + c1*phi(1) + c2*phi(2) as cell_at / bc_to_gc (m_ghost_cells.f90:665-766), where phi(1) is the cell itself
+// and phi(2) its in-box neighbour on the other side.  Laplacian / Helmholtz, GSRB only.
+struct SimpleBc { double t0[6], c1[6], c2[6]; };
+__device__ __forceinline__ void simple_bc(const LevelDev& L, const ParamsDev& P, SimpleBc& B) {
+#pragma unroll
+  for (int f = 0; f < 6; ++f) {
+    int type = L.ftype[f];
+    if (type == 0) type = P.bc_type[f];
+    double c0, c1, c2;
+    if (type == -10) { c0 = 2; c1 = -1; c2 = 0; }
+    else if (type == -11) { c0 = L.dr[f >> 1] * ((f & 1) ? 1.0 : -1.0); c1 = 1; c2 = 0; }
+    else { c0 = 0; c1 = 2; c2 = -1; }
+    B.t0[f] = c0 * P.bc_value[f]; B.c1[f] = c1; B.c2[f] = c2;
+  }
+}
+// u[0..5] of cell (colour, idx) of box 0; u0 = the cell's own value
+__device__ __forceinline__ void simple_gather(const LevelDev& L, const SimpleBc& B, const double* __restrict__ phi, int colour, int idx,
+                                              double u0, double* u) {
+  const int nc = L.nc, hx = L.hx;
+  const int m = idx & (hx - 1), r = idx >> L.sh_hx, j = r & (nc - 1), k = r >> L.sh_nc;
+  const int s = colour ^ ((j + k) & 1);
+  const double* oth = phi + (colour ^ 1) * L.cs;
+  const int ml = m - 1 + s, mh = m + s;
+  const int row = (k * nc + j) * hx;
+  const double xl = oth[row + (ml < 0 ? 0 : ml)], xh = oth[row + (mh >= hx ? hx - 1 : mh)];
+  const double yl = oth[(k * nc + (j > 0 ? j - 1 : 0)) * hx + m], yh = oth[(k * nc + (j < nc - 1 ? j + 1 : j)) * hx + m];
+  const double zl = oth[((k > 0 ? k - 1 : 0) * nc + j) * hx + m], zh = oth[((k < nc - 1 ? k + 1 : k) * nc + j) * hx + m];
+  u[0] = ml < 0 ? B.t0[0] + B.c1[0] * u0 + B.c2[0] * xh : xl;
+  u[1] = mh >= hx ? B.t0[1] + B.c1[1] * u0 + B.c2[1] * xl : xh;
+  u[2] = j == 0 ? B.t0[2] + B.c1[2] * u0 + B.c2[2] * yh : yl;
+  u[3] = j == nc - 1 ? B.t0[3] + B.c1[3] * u0 + B.c2[3] * yl : yh;
+  u[4] = k == 0 ? B.t0[4] + B.c1[4] * u0 + B.c2[4] * zh : zl;
+  u[5] = k == nc - 1 ? B.t0[5] + B.c1[5] * u0 + B.c2[5] * zl : zh;
+}
+// one GSRB colour half-sweep (do_smooth)
+__device__ void simple_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
+  SimpleBc B; simple_bc(L, P, B);
+  double* phi = L.var[0];
+  const double* __restrict__ rhs = L.var[1];
+  for (int idx = tid; idx < L.cs; idx += nthr) {
+    const int g = colour * L.cs + idx;
+    double u[6];
+    simple_gather(L, B, phi, colour, idx, phi[g], u);
+    phi[g] = gs_lpl_value(L.idr2, L.fac, u, rhs[g]);
+  }
+}
+template <int OP>
+__device__ __forceinline__ double simple_op(const LevelDev& L, const ParamsDev& P, const SimpleBc& B, int g) {
+  const int colour = g >= L.cs ? 1 : 0;
+  const double u0 = L.var[0][g];
+  double u[6];
+  simple_gather(L, B, L.var[0], colour, g - colour * L.cs, u0, u);
+  double v = lpl_value(L.idr2, u0, u);
+  if (OP == OP_HELMH) v = v - P.lambda * u0;
+  return v;
+}
+// residual_box (do_resid); returns the thread-local max |res|
+template <int OP>
+__device__ double simple_resid(const LevelDev& L, const ParamsDev& P, int tid, int nthr) {
+  SimpleBc B; simple_bc(L, P, B);
+  double m = 0.0;
+  for (int g = tid; g < L.bs; g += nthr) {
+    const double r = L.var[1][g] - simple_op<OP>(L, P, B, g);
+    L.var[3][g] = r;
+    m = fmax(m, fabs(r));
+  }
+  return m;
+}
+// tail of update_coarse on the (only) box when it is a parent (do_crhs)
+template <int OP>
+__device__ void simple_crhs(const LevelDev& L, const ParamsDev& P, int tid, int nthr) {
+  SimpleBc B; simple_bc(L, P, B);
+  for (int g = tid; g < L.bs; g += nthr) {
+    L.var[1][g] = simple_op<OP>(L, P, B, g) + L.var[3][g];
+    L.var[2][g] = L.var[0][g];
+  }
+}
+
 // block-wide max of non-negative doubles; result valid in thread 0 (and broadcast through smem)
 __device__ double block_max(double v, double* smem /* >= 32 doubles */) {
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
