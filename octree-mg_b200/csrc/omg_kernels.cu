@@ -264,7 +264,8 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
         break;
       case TOP_CORR_PROLONG: {
         const LevelDev& Lc = levels[op.l - 1];
-        for (int b = 0; b < L.nb; ++b) do_corr_prolong(L, Lc, P, b, tid, nthr);
+        if (fast && Lc.simple && L.parent[0] == 0 && L.coff[0] == 0 && (L.nc >> 1) == Lc.nc) simple_corr_prolong(L, Lc, P, tid, nthr);
+        else for (int b = 0; b < L.nb; ++b) do_corr_prolong(L, Lc, P, b, tid, nthr);
       } break;
       case TOP_RB_FILL: {
         const LevelDev& Lc = levels[op.l - 1];

@@ -448,6 +448,42 @@ __device__ void simple_crhs(const LevelDev& L, const ParamsDev& P, int tid, int 
   }
 }
 
+// correct_children + mg_prolong_sparse between two simple levels (do_corr_prolong with the child = the whole fine box,
+// offset 0): the correction phi_c - old_c at a coarse cell and at its six neighbours, ghost values of phi and old
+// from the same boundary expression
+__device__ void simple_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int tid, int nthr) {
+  SimpleBc B; simple_bc(Lc, P, B);
+  const double* __restrict__ pc = Lc.var[0];
+  const double* __restrict__ oc = Lc.var[2];
+  double* phi = Lf.var[0];
+  const int nc = Lc.nc, hx = Lc.hx;
+  for (int g = tid; g < Lc.bs; g += nthr) {
+    const int colour = g >= Lc.cs ? 1 : 0, idx = g - colour * Lc.cs;
+    const int m = idx & (hx - 1), r = idx >> Lc.sh_hx, J = r & (nc - 1), K = r >> Lc.sh_nc;
+    const int I = 2 * m + (colour ^ ((J + K) & 1));
+    const double u0 = pc[g], o0 = oc[g];
+    double up[6], uo[6];
+    simple_gather(Lc, B, pc, colour, idx, u0, up);
+    simple_gather(Lc, B, oc, colour, idx, o0, uo);
+    const double c = u0 - o0;
+    Lc.var[3][g] = c;
+    const double f0 = 0.25 * c;
+    const double flx = 0.25 * (up[0] - uo[0]), fhx = 0.25 * (up[1] - uo[1]);
+    const double fly = 0.25 * (up[2] - uo[2]), fhy = 0.25 * (up[3] - uo[3]);
+    const double flz = 0.25 * (up[4] - uo[4]), fhz = 0.25 * (up[5] - uo[5]);
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+        for (int ii = 0; ii < 2; ++ii) {
+          const double fine = f0 + (ii ? fhx : flx) + (jj ? fhy : fly) + (kk ? fhz : flz);
+          const int q = cidx(Lf, 2 * I + ii, 2 * J + jj, 2 * K + kk);
+          phi[q] = phi[q] + fine;
+        }
+  }
+}
+
 // block-wide max of non-negative doubles; result valid in thread 0 (and broadcast through smem)
 __device__ double block_max(double v, double* smem /* >= 32 doubles */) {
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
