@@ -308,6 +308,7 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
 // descriptors whose var[0..3] point into shared memory (generic addressing), and every op of the coarse end of the
 // cycle costs shared-memory instead of L2 latency.  Everything else (face tables, planes, eps) stays in global memory.
 constexpr int kMaxStageLevels = 12;
+constexpr int kMaxStageOps = 192;
 __global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ levels, const __grid_constant__ ParamsDev P,
                                                const TailOp* __restrict__ ops, int n_ops, double* scal, int n_stage) {
   __shared__ double red[32];
@@ -353,6 +354,13 @@ __global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ leve
     __syncthreads();
   }
   const LevelDev* lv = n_stage > 0 ? slev : levels;
+  // the op list too: every op starts with a broadcast load of its descriptor, an L2 round trip from global memory
+  __shared__ TailOp sops[kMaxStageOps];
+  if (n_ops <= kMaxStageOps) {
+    for (int i = tid; i < n_ops; i += nthr) sops[i] = ops[i];
+    __syncthreads();
+    ops = sops;
+  }
   OMG_SWITCH_OP(P.op, tail_run<OP>(lv, P, ops, n_ops, scal, red));
   if (n_stage > 0) {
     __syncthreads();

@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-1 pass s: tail fast path for single-box levels between constant physical boundaries
+# round-1 pass s: tail fast path for single-box levels between constant physical boundaries (smooth, residual, coarse rhs, correction)
 set -x
 mkdir -p gpurun_out
 timeout 1700 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_s.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_s.log
