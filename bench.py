@@ -133,7 +133,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--n", type=int, default=512)
+    ap.add_argument("--n", "--cells", dest="n", type=int, default=512, help="cells per direction (per GPU, or in total with --strong); "
+                    "use --cells under torchrun, whose own parser trips over the abbreviation --n")
     ap.add_argument("--box", type=int, default=16)
     ap.add_argument("--max-res", action="store_true", help="request max_res in every timed cycle (extra residual pass over all levels)")
     ap.add_argument("--collapse", type=int, default=-1, help="coarse levels with fewer boxes per rank than this live on one GPU (N > 1; -1: default)")
@@ -324,6 +325,7 @@ def main():
                         if args.e2e_cc else "omg_copy_to_tree(phi, rhs: interior cells of the leaves, pinned host arrays) + omg_fas_vcycle + omg_copy_from_tree(phi)")}
 
     if rank != 0:
+        finish(world)
         return
     cpu = None
     if not args.no_cpu_baseline and world == 1:
@@ -337,6 +339,17 @@ def main():
             "launches_per_step": launches_per_step, "clocks": clocks, "residuals": res, "max_res_after": res_after,
             "ref_style_unknowns_per_us": None}
     print(json.dumps(line))
+    finish(world)
+
+
+def finish(world):
+    """Multi-rank runs leave through os._exit once their output is flushed: the measurement is complete, and the
+    interpreter's unordered teardown of NCCL communicators, CUDA IPC mappings and the process group across ranks that
+    exit at different moments was observed to block (pass t, 2 and 4 GPUs: line printed, processes never exited)."""
+    sys.stdout.flush()
+    sys.stderr.flush()
+    if world > 1:
+        os._exit(0)
 
 
 if __name__ == "__main__":
