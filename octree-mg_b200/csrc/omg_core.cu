@@ -476,8 +476,13 @@ void sync_meta(omg_handle* h) {
       U.peer_flags = pf; U.flags = fl; U.err = er;
       U.epoch = h->d_epoch.p + (L.lvl - OMG_LVL_LO); U.done = L.d_done.p;
     }
-    D.simple = (h->tail_simple && L.nb == 1 && D.sh_nc >= 0) ? 1 : 0;
-    for (int f = 0; f < 6 && D.simple; ++f) if (L.h_fkind[f] != FK_PHYS || L.h_farg[f] >= 0) D.simple = 0;
+    // tail fast path (omg_ops.cuh simple_*): every face a constant physical boundary or a local same-level neighbour
+    D.simple = (h->tail_simple && L.nb >= 1 && D.sh_nc >= 0) ? 1 : 0;
+    for (size_t q = 0; q < L.h_fkind.size() && D.simple; ++q) {
+      const bool phi_ok = L.h_fkind[q] == FK_SAME || (L.h_fkind[q] == FK_PHYS && L.h_farg[q] < 0);
+      const bool old_ok = L.h_fkind_old[q] == FK_SAME || (L.h_fkind_old[q] == FK_PHYS && L.h_farg_old[q] < 0);
+      if (!phi_ok || !old_ok) D.simple = 0;
+    }
     D.parent = L.d_parent.p; D.coff = L.d_coff.p; D.ppatch = L.xp.d_recv.p;
     D.parents_list = L.d_parents.p; D.n_parents = (int)L.h_parents.size();
     D.leaves_list = L.d_leaves.p; D.n_leaves = (int)L.h_leaves.size();

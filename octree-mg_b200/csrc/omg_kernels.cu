@@ -239,7 +239,8 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
   for (int o = 0; o < n_ops; ++o) {
     const TailOp op = ops[o];
     const LevelDev& L = levels[op.l];
-    // one box between constant physical boundaries, Laplacian / Helmholtz: branch-free neighbour gathers (omg_ops.cuh)
+    // boxes between constant physical boundaries and local neighbours, Laplacian / Helmholtz: neighbour gathers without
+    // per-cell face classification (omg_ops.cuh)
     const bool fast = (OP == OP_LPL || OP == OP_HELMH) && L.simple && P.smoother == 2;
     switch (op.type) {
       case TOP_SMOOTH:
@@ -256,7 +257,7 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
         for (int b = 0; b < L.nb; ++b) { do_restrict(L, Lc, op.a, b, tid, nthr); if (op.b >= 0) do_restrict(L, Lc, op.b, b, tid, nthr); }
       } break;
       case TOP_CRHS:
-        if (fast && L.n_parents == 1) simple_crhs<OP>(L, P, tid, nthr);
+        if (fast) for (int q = 0; q < L.n_parents; ++q) simple_crhs<OP>(L, P, L.parents_list[q], tid, nthr);
         else for (int q = 0; q < L.n_parents; ++q) do_crhs<OP>(L, P, L.parents_list[q], tid, nthr);
         break;
       case TOP_OLDPL:
@@ -264,7 +265,7 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
         break;
       case TOP_CORR_PROLONG: {
         const LevelDev& Lc = levels[op.l - 1];
-        if (fast && Lc.simple && L.parent[0] == 0 && L.coff[0] == 0 && (L.nc >> 1) == Lc.nc) simple_corr_prolong(L, Lc, P, tid, nthr);
+        if (fast && Lc.simple) for (int b = 0; b < L.nb; ++b) simple_corr_prolong(L, Lc, P, b, tid, nthr);
         else for (int b = 0; b < L.nb; ++b) do_corr_prolong(L, Lc, P, b, tid, nthr);
       } break;
       case TOP_RB_FILL: {

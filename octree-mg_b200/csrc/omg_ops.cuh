@@ -366,17 +366,18 @@ __device__ void do_fill_stored(const LevelDev& L, const ParamsDev& P, int iv, co
   }
 }
 
-// ---- "simple" levels of the tail: ONE power-of-two box whose six faces are physical boundaries with constant
-// values (LevelDev::simple; the coarse end of every uniform grid).  The general path classifies each of the six
-// neighbours of each cell through cell_at (~900 instructions per cell, ncu r01r); here the six in-box neighbours are
-// loaded with clamped indices and a ghost value replaces the out-of-box one by a select -- the same expression
-// c0*b + c1*phi(1) + c2*phi(2) as cell_at / bc_to_gc (m_ghost_cells.f90:665-766), where phi(1) is the cell itself
-// and phi(2) its in-box neighbour on the other side.  Laplacian / Helmholtz, GSRB only.
+// ---- "simple" levels of the tail: power-of-two boxes whose faces are either physical boundaries with constant
+// values or local same-level neighbours (LevelDev::simple; the coarse end of every uniform grid).  The general path
+// classifies each of the six neighbours of each cell through cell_at (~900 instructions per cell, ncu r01r); here the
+// six in-box neighbours are loaded with clamped indices and the out-of-box one is replaced by the neighbour box's face
+// cell or by the ghost value c0*b + c1*phi(1) + c2*phi(2) of cell_at / bc_to_gc (m_ghost_cells.f90:665-766), where
+// phi(1) is the cell itself and phi(2) its in-box neighbour on the other side.  Laplacian / Helmholtz, GSRB only.
+// tests/device_host compiles these functions on the host and checks them bit for bit against the general ones.
 struct SimpleBc { double t0[6], c1[6], c2[6]; };
-__device__ __forceinline__ void simple_bc(const LevelDev& L, const ParamsDev& P, SimpleBc& B) {
+__device__ __forceinline__ void simple_bc(const LevelDev& L, const ParamsDev& P, int b, SimpleBc& B) {
 #pragma unroll
   for (int f = 0; f < 6; ++f) {
-    int type = L.ftype[f];
+    int type = L.ftype[b * 6 + f];
     if (type == 0) type = P.bc_type[f];
     double c0, c1, c2;
     if (type == -10) { c0 = 2; c1 = -1; c2 = 0; }
@@ -385,86 +386,105 @@ __device__ __forceinline__ void simple_bc(const LevelDev& L, const ParamsDev& P,
     B.t0[f] = c0 * P.bc_value[f]; B.c1[f] = c1; B.c2[f] = c2;
   }
 }
-// u[0..5] of cell (colour, idx) of box 0; u0 = the cell's own value
-__device__ __forceinline__ void simple_gather(const LevelDev& L, const SimpleBc& B, const double* __restrict__ phi, int colour, int idx,
-                                              double u0, double* u) {
+// u[0..5] of cell (colour, idx) of box b of variable `var`; u0 = the cell's own value; kind / arg = the variable's
+// face tables (fkind / farg for phi, fkind_old / farg_old for old)
+__device__ __forceinline__ void simple_gather(const LevelDev& L, const SimpleBc& B, const int* __restrict__ kind,
+                                              const int* __restrict__ arg, const double* __restrict__ var, int b, int colour,
+                                              int idx, double u0, double* u) {
   const int nc = L.nc, hx = L.hx;
   const int m = idx & (hx - 1), r = idx >> L.sh_hx, j = r & (nc - 1), k = r >> L.sh_nc;
   const int s = colour ^ ((j + k) & 1);
-  const double* oth = phi + (colour ^ 1) * L.cs;
+  const int ocol = (colour ^ 1) * L.cs;
+  const double* oth = var + (size_t)b * L.bs + ocol;
   const int ml = m - 1 + s, mh = m + s;
   const int row = (k * nc + j) * hx;
   const double xl = oth[row + (ml < 0 ? 0 : ml)], xh = oth[row + (mh >= hx ? hx - 1 : mh)];
   const double yl = oth[(k * nc + (j > 0 ? j - 1 : 0)) * hx + m], yh = oth[(k * nc + (j < nc - 1 ? j + 1 : j)) * hx + m];
   const double zl = oth[((k > 0 ? k - 1 : 0) * nc + j) * hx + m], zh = oth[((k < nc - 1 ? k + 1 : k) * nc + j) * hx + m];
-  u[0] = ml < 0 ? B.t0[0] + B.c1[0] * u0 + B.c2[0] * xh : xl;
-  u[1] = mh >= hx ? B.t0[1] + B.c1[1] * u0 + B.c2[1] * xl : xh;
-  u[2] = j == 0 ? B.t0[2] + B.c1[2] * u0 + B.c2[2] * yh : yl;
-  u[3] = j == nc - 1 ? B.t0[3] + B.c1[3] * u0 + B.c2[3] * yl : yh;
-  u[4] = k == 0 ? B.t0[4] + B.c1[4] * u0 + B.c2[4] * zh : zl;
-  u[5] = k == nc - 1 ? B.t0[5] + B.c1[5] * u0 + B.c2[5] * zl : zh;
+  // out-of-box neighbour through face f: the cell at `pos` of the neighbour box's other-colour block, or the ghost value
+  auto outside = [&](int f, double x2, int pos) -> double {
+    const int q = b * 6 + f;
+    if (kind[q] == FK_SAME) return var[(size_t)arg[q] * L.bs + ocol + pos];
+    return B.t0[f] + B.c1[f] * u0 + B.c2[f] * x2;
+  };
+  u[0] = ml < 0 ? outside(0, xh, row + hx - 1) : xl;
+  u[1] = mh >= hx ? outside(1, xl, row) : xh;
+  u[2] = j == 0 ? outside(2, yh, (k * nc + nc - 1) * hx + m) : yl;
+  u[3] = j == nc - 1 ? outside(3, yl, (k * nc) * hx + m) : yh;
+  u[4] = k == 0 ? outside(4, zh, ((nc - 1) * nc + j) * hx + m) : zl;
+  u[5] = k == nc - 1 ? outside(5, zl, j * hx + m) : zh;
 }
-// one GSRB colour half-sweep (do_smooth)
+// one GSRB colour half-sweep over all boxes (do_smooth)
 __device__ void simple_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
-  SimpleBc B; simple_bc(L, P, B);
   double* phi = L.var[0];
   const double* __restrict__ rhs = L.var[1];
-  for (int idx = tid; idx < L.cs; idx += nthr) {
-    const int g = colour * L.cs + idx;
-    double u[6];
-    simple_gather(L, B, phi, colour, idx, phi[g], u);
-    phi[g] = gs_lpl_value(L.idr2, L.fac, u, rhs[g]);
+  for (int b = 0; b < L.nb; ++b) {
+    SimpleBc B; simple_bc(L, P, b, B);
+    for (int idx = tid; idx < L.cs; idx += nthr) {
+      const size_t g = (size_t)b * L.bs + colour * L.cs + idx;
+      double u[6];
+      simple_gather(L, B, L.fkind, L.farg, phi, b, colour, idx, phi[g], u);
+      phi[g] = gs_lpl_value(L.idr2, L.fac, u, rhs[g]);
+    }
   }
 }
 template <int OP>
-__device__ __forceinline__ double simple_op(const LevelDev& L, const ParamsDev& P, const SimpleBc& B, int g) {
-  const int colour = g >= L.cs ? 1 : 0;
-  const double u0 = L.var[0][g];
+__device__ __forceinline__ double simple_op(const LevelDev& L, const ParamsDev& P, const SimpleBc& B, int b, int q) {
+  const int colour = q >= L.cs ? 1 : 0;
+  const double u0 = L.var[0][(size_t)b * L.bs + q];
   double u[6];
-  simple_gather(L, B, L.var[0], colour, g - colour * L.cs, u0, u);
+  simple_gather(L, B, L.fkind, L.farg, L.var[0], b, colour, q - colour * L.cs, u0, u);
   double v = lpl_value(L.idr2, u0, u);
   if (OP == OP_HELMH) v = v - P.lambda * u0;
   return v;
 }
-// residual_box (do_resid); returns the thread-local max |res|
+// residual_box on all boxes (do_resid); returns the thread-local max |res|
 template <int OP>
 __device__ double simple_resid(const LevelDev& L, const ParamsDev& P, int tid, int nthr) {
-  SimpleBc B; simple_bc(L, P, B);
   double m = 0.0;
-  for (int g = tid; g < L.bs; g += nthr) {
-    const double r = L.var[1][g] - simple_op<OP>(L, P, B, g);
-    L.var[3][g] = r;
-    m = fmax(m, fabs(r));
+  for (int b = 0; b < L.nb; ++b) {
+    SimpleBc B; simple_bc(L, P, b, B);
+    for (int q = tid; q < L.bs; q += nthr) {
+      const size_t g = (size_t)b * L.bs + q;
+      const double r = L.var[1][g] - simple_op<OP>(L, P, B, b, q);
+      L.var[3][g] = r;
+      m = fmax(m, fabs(r));
+    }
   }
   return m;
 }
-// tail of update_coarse on the (only) box when it is a parent (do_crhs)
+// tail of update_coarse on one parent box (do_crhs)
 template <int OP>
-__device__ void simple_crhs(const LevelDev& L, const ParamsDev& P, int tid, int nthr) {
-  SimpleBc B; simple_bc(L, P, B);
-  for (int g = tid; g < L.bs; g += nthr) {
-    L.var[1][g] = simple_op<OP>(L, P, B, g) + L.var[3][g];
+__device__ void simple_crhs(const LevelDev& L, const ParamsDev& P, int b, int tid, int nthr) {
+  SimpleBc B; simple_bc(L, P, b, B);
+  for (int q = tid; q < L.bs; q += nthr) {
+    const size_t g = (size_t)b * L.bs + q;
+    L.var[1][g] = simple_op<OP>(L, P, B, b, q) + L.var[3][g];
     L.var[2][g] = L.var[0][g];
   }
 }
-
-// correct_children + mg_prolong_sparse between two simple levels (do_corr_prolong with the child = the whole fine box,
-// offset 0): the correction phi_c - old_c at a coarse cell and at its six neighbours, ghost values of phi and old
-// from the same boundary expression
-__device__ void simple_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int tid, int nthr) {
-  SimpleBc B; simple_bc(Lc, P, B);
+// correct_children + mg_prolong_sparse onto the fine box b from its (local) parent on a simple coarse level
+// (do_corr_prolong): the correction phi_c - old_c at a coarse cell and at its six neighbours, out-of-box values of phi
+// and old through their own face tables
+__device__ void simple_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int b, int tid, int nthr) {
+  const int p = Lf.parent[b];
+  if (p < 0) return;
+  const int off = Lf.coff[b];
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  SimpleBc B; simple_bc(Lc, P, p, B);
   const double* __restrict__ pc = Lc.var[0];
   const double* __restrict__ oc = Lc.var[2];
-  double* phi = Lf.var[0];
-  const int nc = Lc.nc, hx = Lc.hx;
-  for (int g = tid; g < Lc.bs; g += nthr) {
-    const int colour = g >= Lc.cs ? 1 : 0, idx = g - colour * Lc.cs;
-    const int m = idx & (hx - 1), r = idx >> Lc.sh_hx, J = r & (nc - 1), K = r >> Lc.sh_nc;
-    const int I = 2 * m + (colour ^ ((J + K) & 1));
+  double* phi = Lf.var[0] + (size_t)b * Lf.bs;
+  const int h = Lf.nc >> 1, sh = Lf.sh_nc - 1;
+  for (int idx = tid; idx < h * h * h; idx += nthr) {
+    const int I = idx & (h - 1), J = (idx >> sh) & (h - 1), K = idx >> (2 * sh);
+    const int ci = ox + I, cj = oy + J, ck = oz + K;
+    const int colour = (ci + cj + ck) & 1, idxc = (ck * Lc.nc + cj) * Lc.hx + (ci >> 1);
+    const size_t g = (size_t)p * Lc.bs + colour * Lc.cs + idxc;
     const double u0 = pc[g], o0 = oc[g];
     double up[6], uo[6];
-    simple_gather(Lc, B, pc, colour, idx, u0, up);
-    simple_gather(Lc, B, oc, colour, idx, o0, uo);
+    simple_gather(Lc, B, Lc.fkind, Lc.farg, pc, p, colour, idxc, u0, up);
+    simple_gather(Lc, B, Lc.fkind_old, Lc.farg_old, oc, p, colour, idxc, o0, uo);
     const double c = u0 - o0;
     Lc.var[3][g] = c;
     const double f0 = 0.25 * c;

@@ -1,0 +1,170 @@
+// Host build of the product's per-cell device code (octree-mg_b200/csrc/omg_device.cuh, omg_ops.cuh) for CPU tests.
+//
+// Test infrastructure: g++ compiles the SAME headers the kernels are built from (CUDA qualifiers reduced to nothing,
+// the few intrinsics stubbed below) with -ffp-contract=off, and tests/test_device_host.py checks on random levels that
+// the tail's fast functions (simple_*) produce the bits of the general ones (do_*), i.e. of the path the GPU parity
+// tests pin to the oracle.  One "thread" (tid = 0, nthr = 1) walks every loop; a GSRB colour half-sweep only reads the
+// other colour and a cell's own value, so the sequential walk performs the same arithmetic as the parallel one.
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include <cuda_runtime.h>   // type definitions only (g++ sees __device__ etc. as attributes it ignores)
+
+// ---- stand-ins for device intrinsics -----------------------------------------------------------------------
+struct FakeDim { unsigned x = 0, y = 0, z = 0; };
+static FakeDim threadIdx, blockIdx;
+static FakeDim blockDim = {1, 1, 1};
+static inline void __syncthreads() {}
+static inline double __shfl_xor_sync(unsigned, double v, int) { return v; }
+static inline int __double2hiint(double d) { int64_t b; std::memcpy(&b, &d, 8); return (int)(b >> 32); }
+static inline double __hiloint2double(int hi, int lo) {
+  const int64_t b = ((int64_t)hi << 32) | (uint32_t)lo; double d; std::memcpy(&d, &b, 8); return d;
+}
+static inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
+static inline long long __double_as_longlong(double d) { long long b; std::memcpy(&b, &d, 8); return b; }
+static inline unsigned long long atomicMax(unsigned long long* a, unsigned long long v) {
+  const unsigned long long o = *a; if (v > o) *a = v; return o;
+}
+static inline double __ldcg(const double* p) { return *p; }
+
+#include "../../octree-mg_b200/csrc/omg_ops.cuh"
+
+namespace {
+
+// a level of nbx x nby x nbz boxes of nc^3 cells in the colour-split layout, boxes in x-fastest order, physical
+// boundaries with constant values around the brick, FK_SAME between its boxes
+struct HostLevel {
+  LevelDev L;
+  std::vector<double> var[4];
+  std::vector<int> fkind, farg, ftype, fkind_old, farg_old, parent, coff;
+};
+
+void build_level(HostLevel& H, int nc, int nbx, int nby, int nbz, const int* bc_types, double dr) {
+  LevelDev& L = H.L;
+  std::memset(&L, 0, sizeof(L));
+  const int nb = nbx * nby * nbz;
+  L.nc = nc; L.hx = (nc + 1) / 2; L.nb = nb; L.cs = nc * nc * L.hx; L.bs = 2 * L.cs; L.lvl = 0;
+  L.sh_nc = L.sh_hx = -1;
+  if (nc >= 2 && (nc & (nc - 1)) == 0) { L.sh_nc = 0; while ((1 << L.sh_nc) < nc) ++L.sh_nc; L.sh_hx = L.sh_nc - 1; }
+  for (int d = 0; d < 3; ++d) { L.dr[d] = dr * (1.0 + 0.25 * d); L.idr2[d] = 1.0 / (L.dr[d] * L.dr[d]); }
+  for (int v = 0; v < 4; ++v) { H.var[v].assign((size_t)nb * L.bs, 0.0); L.var[v] = H.var[v].data(); }
+  H.fkind.assign(nb * 6, FK_PHYS); H.farg.assign(nb * 6, -1); H.ftype.assign(nb * 6, 0);
+  H.parent.assign(nb, -1); H.coff.assign(nb, 0);
+  for (int bz = 0; bz < nbz; ++bz) for (int by = 0; by < nby; ++by) for (int bx = 0; bx < nbx; ++bx) {
+    const int b = (bz * nby + by) * nbx + bx;
+    const int pos[3] = {bx, by, bz}, ext[3] = {nbx, nby, nbz}, stride[3] = {1, nbx, nbx * nby};
+    for (int f = 0; f < 6; ++f) {
+      const int d = f >> 1, q = pos[d] + ((f & 1) ? 1 : -1);
+      if (q >= 0 && q < ext[d]) { H.fkind[b * 6 + f] = FK_SAME; H.farg[b * 6 + f] = b + ((f & 1) ? stride[d] : -stride[d]); }
+      else H.ftype[b * 6 + f] = bc_types[f];
+    }
+  }
+  H.fkind_old = H.fkind; H.farg_old = H.farg;
+  L.fkind = H.fkind.data(); L.farg = H.farg.data(); L.ftype = H.ftype.data();
+  L.fkind_old = H.fkind_old.data(); L.farg_old = H.farg_old.data();
+  L.parent = H.parent.data(); L.coff = H.coff.data();
+  L.simple = 1;
+}
+
+struct Rng {   // xorshift: reproducible values in (-1, 1)
+  uint64_t s;
+  double next() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return (double)(int64_t)(s >> 11) / (double)(1ll << 52) - 1.0; }
+};
+void randomise(HostLevel& H, uint64_t seed) {
+  Rng r{seed * 2654435761u + 88172645463325252ull};
+  for (int v = 0; v < 4; ++v) for (double& x : H.var[v]) x = r.next();
+}
+
+ParamsDev params(int op, double lambda, const int* bc_types, const double* bc_values) {
+  ParamsDev P;
+  std::memset(&P, 0, sizeof(P));
+  P.op = op; P.smoother = 2; P.lambda = lambda;
+  for (int f = 0; f < 6; ++f) { P.bc_type[f] = bc_types[f]; P.bc_value[f] = bc_values[f]; }
+  return P;
+}
+
+int differing(const HostLevel& A, const HostLevel& B) {
+  int n = 0;
+  for (int v = 0; v < 4; ++v) n += std::memcmp(A.var[v].data(), B.var[v].data(), A.var[v].size() * sizeof(double)) != 0;
+  return n;
+}
+
+template <int OP>
+int run_case(int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda, uint64_t seed) {
+  HostLevel G, S;                    // general / simple
+  build_level(G, nc, nbx, nby, nbz, bc_types, 0.01);
+  build_level(S, nc, nbx, nby, nbz, bc_types, 0.01);
+  ParamsDev P = params(OP, lambda, bc_types, bc_values);
+  const double sum = G.L.idr2[0] + G.L.idr2[1] + G.L.idr2[2];
+  G.L.fac = S.L.fac = (OP == OP_HELMH) ? 1.0 / (2 * sum + lambda) : 0.5 / sum;
+  randomise(G, seed);
+  for (int v = 0; v < 4; ++v) S.var[v] = G.var[v];
+  for (int v = 0; v < 4; ++v) S.L.var[v] = S.var[v].data();
+  int bad = 0;
+  // two full GSRB sweeps
+  for (int n = 0; n < 4; ++n) {
+    for (int b = 0; b < G.L.nb; ++b) do_smooth<OP>(G.L, P, b, n & 1, 0, 1);
+    simple_smooth(S.L, P, n & 1, 0, 1);
+    bad += differing(G, S) ? 1 : 0;
+  }
+  // residual (and its max)
+  double mg = 0.0, ms;
+  for (int b = 0; b < G.L.nb; ++b) mg = fmax(mg, do_resid<OP>(G.L, P, b, 0, 1));
+  ms = simple_resid<OP>(S.L, P, 0, 1);
+  bad += (std::memcmp(&mg, &ms, 8) != 0) + (differing(G, S) ? 1 : 0);
+  // coarse right-hand side on every box
+  for (int b = 0; b < G.L.nb; ++b) do_crhs<OP>(G.L, P, b, 0, 1);
+  for (int b = 0; b < S.L.nb; ++b) simple_crhs<OP>(S.L, P, b, 0, 1);
+  bad += differing(G, S) ? 1 : 0;
+  return bad;
+}
+
+// correction + prolongation from a coarse level onto a fine level whose boxes are the octants (same box size) or the
+// whole refined box (coarse box of half the size, the single-box coarsening levels)
+int run_prolong(int ncf, int nbx, int nby, int nbz, bool half_size_coarse, const int* bc_types, const double* bc_values, uint64_t seed) {
+  int bad = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    HostLevel F, C;
+    if (half_size_coarse) { build_level(F, ncf, 1, 1, 1, bc_types, 0.01); build_level(C, ncf / 2, 1, 1, 1, bc_types, 0.02); }
+    else { build_level(F, ncf, 2 * nbx, 2 * nby, 2 * nbz, bc_types, 0.01); build_level(C, ncf, nbx, nby, nbz, bc_types, 0.02); }
+    for (int b = 0; b < F.L.nb; ++b) {
+      if (half_size_coarse) { F.parent[b] = 0; F.coff[b] = 0; continue; }
+      const int fx = b % (2 * nbx), fy = (b / (2 * nbx)) % (2 * nby), fz = b / (4 * nbx * nby);
+      F.parent[b] = ((fz / 2) * nby + fy / 2) * nbx + fx / 2;
+      const int h = ncf / 2;
+      F.coff[b] = ((fx & 1) * h) | (((fy & 1) * h) << 10) | (((fz & 1) * h) << 20);
+    }
+    ParamsDev P = params(OP_LPL, 0.0, bc_types, bc_values);
+    randomise(F, seed); randomise(C, seed + 17);
+    static std::vector<double> keep[2][8];
+    if (pass == 0) for (int b = 0; b < F.L.nb; ++b) do_corr_prolong(F.L, C.L, P, b, 0, 1);
+    else for (int b = 0; b < F.L.nb; ++b) simple_corr_prolong(F.L, C.L, P, b, 0, 1);
+    for (int v = 0; v < 4; ++v) {
+      if (pass == 0) { keep[0][v] = F.var[v]; keep[1][v] = C.var[v]; }
+      else bad += (keep[0][v] != F.var[v]) + (keep[1][v] != C.var[v]);
+    }
+  }
+  return bad;
+}
+
+}  // namespace
+
+extern "C" {
+// number of mismatching comparisons (0 = the fast path reproduces the general path bit for bit)
+int dh_compare_simple(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
+                      unsigned long long seed) {
+  if (op == OP_LPL) return run_case<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+  return run_case<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+}
+int dh_compare_prolong(int ncf, int nbx, int nby, int nbz, int half_size_coarse, const int* bc_types, const double* bc_values,
+                       unsigned long long seed) {
+  return run_prolong(ncf, nbx, nby, nbz, half_size_coarse != 0, bc_types, bc_values, seed);
+}
+// the batched division against the compiler's (host build: exact-reciprocal seed instead of MUFU.RCP64H)
+int dh_ddiv(const double* a, const double* b, double* out, int n) {
+  for (int i = 0; i + 6 <= n; i += 6) ddiv_batch<6>(a + i, b + i, out + i);
+  return 0;
+}
+}

@@ -1,0 +1,78 @@
+"""CPU tests of the product's per-cell device code, compiled for the host (tests/device_host/harness.cpp).
+
+The single-CTA tail of the cycle has a fast path for "simple" levels (power-of-two boxes whose faces are constant
+physical boundaries or local neighbours, omg_ops.cuh simple_*).  The same headers the kernels are built from are
+compiled with g++ -ffp-contract=off here, and the fast functions must reproduce the general ones -- the path the GPU
+parity tests pin to the oracle -- bit for bit on random data: smoothing, residual, coarse right-hand side and
+correction + prolongation, one or several boxes, every boundary-condition type."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "device_host", "harness.cpp")
+LIB = os.path.join(HERE, "device_host", "libdevhost.so")
+CSRC = os.path.join(os.path.dirname(HERE), "octree-mg_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def devhost():
+    deps = [SRC] + [os.path.join(CSRC, f) for f in ("omg_device.cuh", "omg_ops.cuh")]
+    if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
+        cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+        subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-std=c++17", "-fPIC", "-shared", "-w", "-I" + cuda_inc,
+                               SRC, "-o", LIB])
+    L = C.CDLL(LIB)
+    L.dh_compare_simple.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
+    L.dh_compare_prolong.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_ulonglong]
+    L.dh_ddiv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    return L
+
+
+BC_SETS = [[-10] * 6, [-11] * 6, [-12, -12, -10, -10, -11, -11], [-10, -11, -12, -10, -11, -12]]
+BC_VALUES = [0.3, -0.7, 1.1, 0.0, 2.0, -1.5]
+SHAPES = [(1, 1, 1), (2, 1, 1), (1, 2, 1), (1, 1, 2), (2, 2, 2), (3, 2, 1)]
+
+
+def six(ctype, values):
+    return (ctype * 6)(*values)
+
+
+@pytest.mark.parametrize("types", BC_SETS)
+@pytest.mark.parametrize("nc", [2, 4, 8, 16])
+def test_simple_level_functions_match_general_path(devhost, types, nc):
+    for shape in SHAPES:
+        for op, lam in ((1, 0.0), (3, 2.5)):          # mg_laplacian, mg_helmholtz
+            bad = devhost.dh_compare_simple(op, nc, *shape, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 7 * nc + op)
+            assert bad == 0, (types, nc, shape, op)
+
+
+@pytest.mark.parametrize("types", BC_SETS)
+@pytest.mark.parametrize("nc", [2, 4, 8, 16])
+def test_simple_correction_and_prolongation_match_general_path(devhost, types, nc):
+    for shape in SHAPES:                               # children = octants of parents of the same box size
+        assert devhost.dh_compare_prolong(nc, *shape, 0, six(C.c_int, types), six(C.c_double, BC_VALUES), nc) == 0, shape
+    if nc >= 4:                                        # single-box coarsening: the coarse box has half the size
+        assert devhost.dh_compare_prolong(nc, 1, 1, 1, 1, six(C.c_int, types), six(C.c_double, BC_VALUES), nc) == 0
+
+
+def test_batched_division_logic_on_host(devhost):
+    """ddiv_batch with an exact-reciprocal seed in place of MUFU.RCP64H: the Newton / residual-correction sequence and
+    the range test that sends a batch to the plain division (the device version is tested in test_gpu_steps.py)"""
+    rng = np.random.default_rng(11)
+    n = 6 * 20000
+    a = rng.uniform(-4, 4, n) * 2.0 ** rng.integers(-1060, 1020, n)
+    b = rng.uniform(1, 2, n) * 2.0 ** rng.integers(-1060, 1020, n) * rng.choice([-1.0, 1.0], n)
+    special = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 5e-324, 2.2250738585072014e-308, 1.7976931348623157e308, 1.0, 3.0])
+    k = len(special)
+    a[:k * k] = np.repeat(special, k)
+    b[:k * k] = np.tile(special, k)
+    out = np.empty(n)
+    devhost.dh_ddiv(a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), n)
+    with np.errstate(all="ignore"):
+        ref = a / b
+    same = (out.view(np.uint64) == ref.view(np.uint64)) | (np.isnan(out) & np.isnan(ref))
+    assert same.all(), (a[~same][:5], b[~same][:5], out[~same][:5], ref[~same][:5])
