@@ -353,4 +353,9 @@ def finish(world):
 
 
 if __name__ == "__main__":
+    # a run that blocks (a peer that never arrives, a teardown that never returns) must not hold the box: leave after
+    # 25 minutes with a non-zero status instead
+    _watchdog = threading.Timer(1500.0, lambda: (sys.stderr.write("bench.py: watchdog expired\n"), sys.stderr.flush(), os._exit(3)))
+    _watchdog.daemon = True
+    _watchdog.start()
     main()
