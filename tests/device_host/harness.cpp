@@ -162,6 +162,41 @@ int dh_compare_prolong(int ncf, int nbx, int nby, int nbz, int half_size_coarse,
                        unsigned long long seed) {
   return run_prolong(ncf, nbx, nby, nbz, half_size_coarse != 0, bc_types, bc_values, seed);
 }
+// One operation of the GENERAL device path (do_smooth / do_resid, what the batched kernels and the tail run) on a brick
+// of nbx x nby x nbz boxes between constant physical boundaries, for the comparison with the oracle on the CPU.
+// Arrays: interior cells only, [box (x fastest)][k][j][i].  what = 0: one GSRB sweep (colour 0 = the cells the
+// reference updates first, then colour 1) of phi; what = 1: res = rhs - L(phi), returns max |res| through *out_max.
+int dh_level_op(int what, int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
+                const double* dr, double* phi, const double* rhs, double* res, double* out_max) {
+  HostLevel H;
+  build_level(H, nc, nbx, nby, nbz, bc_types, 1.0);
+  LevelDev& L = H.L;
+  for (int d = 0; d < 3; ++d) { L.dr[d] = dr[d]; L.idr2[d] = 1.0 / (dr[d] * dr[d]); }
+  const double sum = L.idr2[0] + L.idr2[1] + L.idr2[2];
+  L.fac = (op == OP_HELMH) ? 1.0 / (2 * sum + lambda) : 0.5 / sum;
+  ParamsDev P = params(op, lambda, bc_types, bc_values);
+  const size_t n3 = (size_t)nc * nc * nc;
+  for (int b = 0; b < L.nb; ++b) for (int k = 0; k < nc; ++k) for (int j = 0; j < nc; ++j) for (int i = 0; i < nc; ++i) {
+    const size_t src = b * n3 + ((size_t)k * nc + j) * nc + i, dst = (size_t)b * L.bs + cidx(L, i, j, k);
+    H.var[0][dst] = phi[src]; H.var[1][dst] = rhs[src];
+  }
+  double m = 0.0;
+  if (what == 0) {
+    for (int colour = 0; colour < 2; ++colour)
+      for (int b = 0; b < L.nb; ++b) {
+        if (op == OP_LPL) do_smooth<OP_LPL>(L, P, b, colour, 0, 1); else do_smooth<OP_HELMH>(L, P, b, colour, 0, 1);
+      }
+  } else {
+    for (int b = 0; b < L.nb; ++b)
+      m = fmax(m, op == OP_LPL ? do_resid<OP_LPL>(L, P, b, 0, 1) : do_resid<OP_HELMH>(L, P, b, 0, 1));
+  }
+  for (int b = 0; b < L.nb; ++b) for (int k = 0; k < nc; ++k) for (int j = 0; j < nc; ++j) for (int i = 0; i < nc; ++i) {
+    const size_t dst = b * n3 + ((size_t)k * nc + j) * nc + i, src = (size_t)b * L.bs + cidx(L, i, j, k);
+    phi[dst] = H.var[0][src]; res[dst] = H.var[3][src];
+  }
+  if (out_max) *out_max = m;
+  return 0;
+}
 // the batched division against the compiler's (host build: exact-reciprocal seed instead of MUFU.RCP64H)
 int dh_ddiv(const double* a, const double* b, double* out, int n) {
   for (int i = 0; i + 6 <= n; i += 6) ddiv_batch<6>(a + i, b + i, out + i);

@@ -76,3 +76,52 @@ def test_batched_division_logic_on_host(devhost):
         ref = a / b
     same = (out.view(np.uint64) == ref.view(np.uint64)) | (np.isnan(out) & np.isnan(ref))
     assert same.all(), (a[~same][:5], b[~same][:5], out[~same][:5], ref[~same][:5])
+
+
+BC_OF = {"dirichlet0": ([-10] * 6, [0.0] * 6), "neumann0": ([-11] * 6, [0.0] * 6),
+         "mixed": ([-10] + [-11] * 5, [0.25] + [0.5] * 5), "continuous_x": ([-12, -12, -10, -10, -10, -10], [0.0, 0.0, 1.0, 1.0, 1.0, 1.0])}
+
+
+@pytest.mark.parametrize("bc", sorted(BC_OF))
+@pytest.mark.parametrize("op,lam", [(1, 0.0), (3, 1.75)])
+def test_general_device_path_matches_oracle_on_one_level(devhost, oracle, op, lam, bc):
+    """the device's general per-cell path (do_smooth, do_resid: colour-split layout, ghost values derived on the fly)
+    against the oracle's smooth_boxes / max_residual_lvl (ghost cells stored and refilled, src/m_multigrid.f90:404-436)
+    on the 2 x 2 x 2 boxes of one level with random data: same bits, on the CPU"""
+    import problems as P
+    devhost.dh_level_op.argtypes = [C.c_int] * 6 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double),
+                                                   C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
+    nc = 8
+    orc, _ = P.uniform_problem(oracle.OracleMg, 16, nc, operator_type=op, bc=bc, lam=lam)
+    lvl = orc.highest_lvl
+    ids = orc.ids(lvl)
+    assert len(ids) == 8
+    rng = np.random.default_rng(5)
+    pos = {}
+    for id_ in ids:
+        ix = orc.box_info(id_)["ix"]
+        pos[id_] = ((ix[2] - 1) * 2 + (ix[1] - 1)) * 2 + (ix[0] - 1)
+        cc = orc.cc(id_, nc)
+        cc[P.mg_iphi - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((nc, nc, nc))
+        cc[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((nc, nc, nc)) * 100.0
+    orc.mg_fill_ghost_cells_lvl(lvl, P.mg_iphi)
+
+    def gather(iv):
+        out = np.empty((8, nc, nc, nc))
+        for id_ in ids:
+            out[pos[id_]] = orc.cc(id_, nc)[iv - 1, 1:-1, 1:-1, 1:-1]
+        return out
+
+    types, values = BC_OF[bc]
+    dr = (C.c_double * 3)(*orc.dr(lvl))
+    phi, rhs = gather(P.mg_iphi), gather(P.mg_irhs)
+    res = np.zeros_like(phi)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)          # noqa: E731
+    for sweep in range(2):
+        devhost.dh_level_op(0, op, nc, 2, 2, 2, six(C.c_int, types), six(C.c_double, values), lam, dr, vp(phi), vp(rhs), vp(res), None)
+        orc.smooth_boxes(lvl, 1)
+        assert np.array_equal(phi, gather(P.mg_iphi)), "GSRB sweep %d differs" % sweep
+    m = C.c_double(0.0)
+    devhost.dh_level_op(1, op, nc, 2, 2, 2, six(C.c_int, types), six(C.c_double, values), lam, dr, vp(phi), vp(rhs), vp(res), C.byref(m))
+    assert orc.max_residual_lvl(lvl) == m.value
+    assert np.array_equal(res, gather(P.mg_ires))
