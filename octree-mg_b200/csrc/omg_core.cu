@@ -476,11 +476,11 @@ void sync_meta(omg_handle* h) {
       U.peer_flags = pf; U.flags = fl; U.err = er;
       U.epoch = h->d_epoch.p + (L.lvl - OMG_LVL_LO); U.done = L.d_done.p;
     }
-    // tail fast path (omg_ops.cuh simple_*): every face a constant physical boundary or a local same-level neighbour
+    // tail fast path (omg_ops.cuh simple_*): every face a physical boundary or a local same-level neighbour
     D.simple = (h->tail_simple && L.nb >= 1 && D.sh_nc >= 0) ? 1 : 0;
     for (size_t q = 0; q < L.h_fkind.size() && D.simple; ++q) {
-      const bool phi_ok = L.h_fkind[q] == FK_SAME || (L.h_fkind[q] == FK_PHYS && L.h_farg[q] < 0);
-      const bool old_ok = L.h_fkind_old[q] == FK_SAME || (L.h_fkind_old[q] == FK_PHYS && L.h_farg_old[q] < 0);
+      const bool phi_ok = L.h_fkind[q] == FK_SAME || L.h_fkind[q] == FK_PHYS;
+      const bool old_ok = L.h_fkind_old[q] == FK_SAME || L.h_fkind_old[q] == FK_PHYS;
       if (!phi_ok || !old_ok) D.simple = 0;
     }
     D.parent = L.d_parent.p; D.coff = L.d_coff.p; D.ppatch = L.xp.d_recv.p;

@@ -366,14 +366,14 @@ __device__ void do_fill_stored(const LevelDev& L, const ParamsDev& P, int iv, co
   }
 }
 
-// ---- "simple" levels of the tail: power-of-two boxes whose faces are either physical boundaries with constant
-// values or local same-level neighbours (LevelDev::simple; the coarse end of every uniform grid).  The general path
+// ---- "simple" levels of the tail: power-of-two boxes whose faces are either physical boundaries (constant values or
+// stored planes) or local same-level neighbours (LevelDev::simple; the coarse end of every uniform grid).  The general path
 // classifies each of the six neighbours of each cell through cell_at (~900 instructions per cell, ncu r01r); here the
 // six in-box neighbours are loaded with clamped indices and the out-of-box one is replaced by the neighbour box's face
 // cell or by the ghost value c0*b + c1*phi(1) + c2*phi(2) of cell_at / bc_to_gc (m_ghost_cells.f90:665-766), where
 // phi(1) is the cell itself and phi(2) its in-box neighbour on the other side.  Laplacian / Helmholtz, GSRB only.
 // tests/device_host compiles these functions on the host and checks them bit for bit against the general ones.
-struct SimpleBc { double t0[6], c1[6], c2[6]; };
+struct SimpleBc { double c0[6], c1[6], c2[6], bv[6]; };
 __device__ __forceinline__ void simple_bc(const LevelDev& L, const ParamsDev& P, int b, SimpleBc& B) {
 #pragma unroll
   for (int f = 0; f < 6; ++f) {
@@ -383,7 +383,7 @@ __device__ __forceinline__ void simple_bc(const LevelDev& L, const ParamsDev& P,
     if (type == -10) { c0 = 2; c1 = -1; c2 = 0; }
     else if (type == -11) { c0 = L.dr[f >> 1] * ((f & 1) ? 1.0 : -1.0); c1 = 1; c2 = 0; }
     else { c0 = 0; c1 = 2; c2 = -1; }
-    B.t0[f] = c0 * P.bc_value[f]; B.c1[f] = c1; B.c2[f] = c2;
+    B.c0[f] = c0; B.c1[f] = c1; B.c2[f] = c2; B.bv[f] = P.bc_value[f];
   }
 }
 // u[0..5] of cell (colour, idx) of box b of variable `var`; u0 = the cell's own value; kind / arg = the variable's
@@ -402,17 +402,21 @@ __device__ __forceinline__ void simple_gather(const LevelDev& L, const SimpleBc&
   const double yl = oth[(k * nc + (j > 0 ? j - 1 : 0)) * hx + m], yh = oth[(k * nc + (j < nc - 1 ? j + 1 : j)) * hx + m];
   const double zl = oth[((k > 0 ? k - 1 : 0) * nc + j) * hx + m], zh = oth[((k < nc - 1 ? k + 1 : k) * nc + j) * hx + m];
   // out-of-box neighbour through face f: the cell at `pos` of the neighbour box's other-colour block, or the ghost value
-  auto outside = [&](int f, double x2, int pos) -> double {
+  // with the boundary value b from the constant or from the stored plane (callback / mg_phi_bc_store values) at (t1, t2)
+  auto outside = [&](int f, double x2, int pos, int t1, int t2) -> double {
     const int q = b * 6 + f;
-    if (kind[q] == FK_SAME) return var[(size_t)arg[q] * L.bs + ocol + pos];
-    return B.t0[f] + B.c1[f] * u0 + B.c2[f] * x2;
+    const int a = arg[q];
+    if (kind[q] == FK_SAME) return var[(size_t)a * L.bs + ocol + pos];
+    const double bv = a >= 0 ? L.bcpl[(size_t)a * nc * nc + t2 * nc + t1] : B.bv[f];
+    return B.c0[f] * bv + B.c1[f] * u0 + B.c2[f] * x2;
   };
-  u[0] = ml < 0 ? outside(0, xh, row + hx - 1) : xl;
-  u[1] = mh >= hx ? outside(1, xl, row) : xh;
-  u[2] = j == 0 ? outside(2, yh, (k * nc + nc - 1) * hx + m) : yl;
-  u[3] = j == nc - 1 ? outside(3, yl, (k * nc) * hx + m) : yh;
-  u[4] = k == 0 ? outside(4, zh, ((nc - 1) * nc + j) * hx + m) : zl;
-  u[5] = k == nc - 1 ? outside(5, zl, j * hx + m) : zh;
+  const int i = 2 * m + s;
+  u[0] = ml < 0 ? outside(0, xh, row + hx - 1, j, k) : xl;
+  u[1] = mh >= hx ? outside(1, xl, row, j, k) : xh;
+  u[2] = j == 0 ? outside(2, yh, (k * nc + nc - 1) * hx + m, i, k) : yl;
+  u[3] = j == nc - 1 ? outside(3, yl, (k * nc) * hx + m, i, k) : yh;
+  u[4] = k == 0 ? outside(4, zh, ((nc - 1) * nc + j) * hx + m, i, j) : zl;
+  u[5] = k == nc - 1 ? outside(5, zl, j * hx + m, i, j) : zh;
 }
 // one GSRB colour half-sweep over all boxes (do_smooth)
 __device__ void simple_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {

@@ -39,7 +39,9 @@ struct HostLevel {
   LevelDev L;
   std::vector<double> var[4];
   std::vector<int> fkind, farg, ftype, fkind_old, farg_old, parent, coff;
+  std::vector<double> bcpl;
 };
+int g_planes = 0;   // 1: physical faces carry stored planes of boundary values (callbacks / mg_phi_bc_store) instead of constants
 
 void build_level(HostLevel& H, int nc, int nbx, int nby, int nbz, const int* bc_types, double dr) {
   LevelDev& L = H.L;
@@ -58,9 +60,16 @@ void build_level(HostLevel& H, int nc, int nbx, int nby, int nbz, const int* bc_
     for (int f = 0; f < 6; ++f) {
       const int d = f >> 1, q = pos[d] + ((f & 1) ? 1 : -1);
       if (q >= 0 && q < ext[d]) { H.fkind[b * 6 + f] = FK_SAME; H.farg[b * 6 + f] = b + ((f & 1) ? stride[d] : -stride[d]); }
-      else H.ftype[b * 6 + f] = bc_types[f];
+      else {
+        H.ftype[b * 6 + f] = bc_types[f];
+        if (g_planes) {
+          H.farg[b * 6 + f] = (int)(H.bcpl.size() / ((size_t)nc * nc));
+          for (int t = 0; t < nc * nc; ++t) H.bcpl.push_back(0.01 * (double)((b * 6 + f) * 131 + t * 7 % 97) - 0.3);
+        }
+      }
     }
   }
+  L.bcpl = H.bcpl.data();
   H.fkind_old = H.fkind; H.farg_old = H.farg;
   L.fkind = H.fkind.data(); L.farg = H.farg.data(); L.ftype = H.ftype.data();
   L.fkind_old = H.fkind_old.data(); L.farg_old = H.farg_old.data();
@@ -152,6 +161,7 @@ int run_prolong(int ncf, int nbx, int nby, int nbz, bool half_size_coarse, const
 }  // namespace
 
 extern "C" {
+void dh_set_planes(int on) { g_planes = on; }
 // number of mismatching comparisons (0 = the fast path reproduces the general path bit for bit)
 int dh_compare_simple(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
                       unsigned long long seed) {

@@ -41,22 +41,28 @@ def six(ctype, values):
     return (ctype * 6)(*values)
 
 
+@pytest.mark.parametrize("planes", [0, 1])           # boundary values: constants / stored planes (callbacks)
 @pytest.mark.parametrize("types", BC_SETS)
 @pytest.mark.parametrize("nc", [2, 4, 8, 16])
-def test_simple_level_functions_match_general_path(devhost, types, nc):
+def test_simple_level_functions_match_general_path(devhost, types, nc, planes):
+    devhost.dh_set_planes(planes)
     for shape in SHAPES:
         for op, lam in ((1, 0.0), (3, 2.5)):          # mg_laplacian, mg_helmholtz
             bad = devhost.dh_compare_simple(op, nc, *shape, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 7 * nc + op)
             assert bad == 0, (types, nc, shape, op)
+    devhost.dh_set_planes(0)
 
 
+@pytest.mark.parametrize("planes", [0, 1])
 @pytest.mark.parametrize("types", BC_SETS)
 @pytest.mark.parametrize("nc", [2, 4, 8, 16])
-def test_simple_correction_and_prolongation_match_general_path(devhost, types, nc):
+def test_simple_correction_and_prolongation_match_general_path(devhost, types, nc, planes):
+    devhost.dh_set_planes(planes)
     for shape in SHAPES:                               # children = octants of parents of the same box size
         assert devhost.dh_compare_prolong(nc, *shape, 0, six(C.c_int, types), six(C.c_double, BC_VALUES), nc) == 0, shape
     if nc >= 4:                                        # single-box coarsening: the coarse box has half the size
         assert devhost.dh_compare_prolong(nc, 1, 1, 1, 1, six(C.c_int, types), six(C.c_double, BC_VALUES), nc) == 0
+    devhost.dh_set_planes(0)
 
 
 def test_batched_division_logic_on_host(devhost):
