@@ -217,8 +217,8 @@ __global__ void k_scale_scalar(double* acc, double inv_volume) { *acc = *acc / i
 // ------------------------------------------------------------------ tail interpreter ---------
 template <int OP>
 __device__ void tail_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
-  if ((OP == OP_LPL || OP == OP_HELMH) && L.simple && P.smoother == 2) {
-    simple_smooth(L, P, colour, tid, nthr);
+  if (L.simple && P.smoother == 2) {
+    simple_smooth<OP>(L, P, colour, tid, nthr);
   } else if (P.smoother == 1) {   // mg_smoother_gs
     for (int b = 0; b < L.nb; ++b) do_gs_snapshot(L, P, b, tid, nthr);
     __syncthreads();
@@ -239,9 +239,9 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
   for (int o = 0; o < n_ops; ++o) {
     const TailOp op = ops[o];
     const LevelDev& L = levels[op.l];
-    // boxes between constant physical boundaries and local neighbours, Laplacian / Helmholtz: neighbour gathers without
+    // boxes between physical boundaries and local neighbours: neighbour gathers without
     // per-cell face classification (omg_ops.cuh)
-    const bool fast = (OP == OP_LPL || OP == OP_HELMH) && L.simple && P.smoother == 2;
+    const bool fast = L.simple && P.smoother == 2;
     switch (op.type) {
       case TOP_SMOOTH:
         tail_smooth<OP>(L, P, op.a, tid, nthr);

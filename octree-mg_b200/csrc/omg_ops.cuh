@@ -371,7 +371,7 @@ __device__ void do_fill_stored(const LevelDev& L, const ParamsDev& P, int iv, co
 // classifies each of the six neighbours of each cell through cell_at (~900 instructions per cell, ncu r01r); here the
 // six in-box neighbours are loaded with clamped indices and the out-of-box one is replaced by the neighbour box's face
 // cell or by the ghost value c0*b + c1*phi(1) + c2*phi(2) of cell_at / bc_to_gc (m_ghost_cells.f90:665-766), where
-// phi(1) is the cell itself and phi(2) its in-box neighbour on the other side.  Laplacian / Helmholtz, GSRB only.
+// phi(1) is the cell itself and phi(2) its in-box neighbour on the other side.  All five operators (eps ghost faces from the stored faces pool), GSRB only.
 // tests/device_host compiles these functions on the host and checks them bit for bit against the general ones.
 struct SimpleBc { double c0[6], c1[6], c2[6], bv[6]; };
 __device__ __forceinline__ void simple_bc(const LevelDev& L, const ParamsDev& P, int b, SimpleBc& B) {
@@ -418,7 +418,45 @@ __device__ __forceinline__ void simple_gather(const LevelDev& L, const SimpleBc&
   u[4] = k == 0 ? outside(4, zh, ((nc - 1) * nc + j) * hx + m, i, j) : zl;
   u[5] = k == nc - 1 ? outside(5, zl, j * hx + m, i, j) : zh;
 }
+// the six neighbours of a variable whose ghost faces are stored (eps: GM_STORED, gather_eps): in-box cells of the other
+// colour, out-of-box values from the faces pool [box][face][t2][t1]
+__device__ __forceinline__ void simple_gather_stored(const LevelDev& L, const double* __restrict__ var, const double* __restrict__ faces,
+                                                     int b, int colour, int idx, double* a) {
+  const int nc = L.nc, hx = L.hx;
+  const int m = idx & (hx - 1), r = idx >> L.sh_hx, j = r & (nc - 1), k = r >> L.sh_nc;
+  const int s = colour ^ ((j + k) & 1), i = 2 * m + s;
+  const double* oth = var + (size_t)b * L.bs + (colour ^ 1) * L.cs;
+  const double* fc = faces + (size_t)b * 6 * nc * nc;
+  const int ml = m - 1 + s, mh = m + s;
+  const int row = (k * nc + j) * hx;
+  a[0] = ml < 0 ? fc[k * nc + j] : oth[row + ml];
+  a[1] = mh >= hx ? fc[nc * nc + k * nc + j] : oth[row + mh];
+  a[2] = j == 0 ? fc[2 * nc * nc + k * nc + i] : oth[(k * nc + j - 1) * hx + m];
+  a[3] = j == nc - 1 ? fc[3 * nc * nc + k * nc + i] : oth[(k * nc + j + 1) * hx + m];
+  a[4] = k == 0 ? fc[4 * nc * nc + j * nc + i] : oth[((k - 1) * nc + j) * hx + m];
+  a[5] = k == nc - 1 ? fc[5 * nc * nc + j * nc + i] : oth[((k + 1) * nc + j) * hx + m];
+}
+// eps coefficients of one cell in face order (gather_eps): a0 = the cell's own, a = the neighbour's
+template <int OP>
+__device__ __forceinline__ void simple_eps(const LevelDev& L, int b, int colour, int idx, double* a0, double* a) {
+  const size_t g = (size_t)b * L.bs + colour * L.cs + idx;
+  if (OP == OP_AHELMH) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      double t[6];
+      simple_gather_stored(L, L.var[4 + d], L.faces[4 + d], b, colour, idx, t);
+      const double c = L.var[4 + d][g];
+      a0[2 * d] = c; a0[2 * d + 1] = c; a[2 * d] = t[2 * d]; a[2 * d + 1] = t[2 * d + 1];
+    }
+  } else {
+    const double c = L.var[4][g];
+#pragma unroll
+    for (int f = 0; f < 6; ++f) a0[f] = c;
+    simple_gather_stored(L, L.var[4], L.faces[4], b, colour, idx, a);
+  }
+}
 // one GSRB colour half-sweep over all boxes (do_smooth)
+template <int OP>
 __device__ void simple_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
   double* phi = L.var[0];
   const double* __restrict__ rhs = L.var[1];
@@ -428,7 +466,12 @@ __device__ void simple_smooth(const LevelDev& L, const ParamsDev& P, int colour,
       const size_t g = (size_t)b * L.bs + colour * L.cs + idx;
       double u[6];
       simple_gather(L, B, L.fkind, L.farg, phi, b, colour, idx, phi[g], u);
-      phi[g] = gs_lpl_value(L.idr2, L.fac, u, rhs[g]);
+      if (OP == OP_LPL || OP == OP_HELMH) phi[g] = gs_lpl_value(L.idr2, L.fac, u, rhs[g]);
+      else {
+        double a0[6], a[6];
+        simple_eps<OP>(L, b, colour, idx, a0, a);
+        phi[g] = gs_vlpl_value(L.idr2, u, a0, a, rhs[g], P.lambda, OP != OP_VLPL);
+      }
     }
   }
 }
@@ -438,8 +481,12 @@ __device__ __forceinline__ double simple_op(const LevelDev& L, const ParamsDev& 
   const double u0 = L.var[0][(size_t)b * L.bs + q];
   double u[6];
   simple_gather(L, B, L.fkind, L.farg, L.var[0], b, colour, q - colour * L.cs, u0, u);
-  double v = lpl_value(L.idr2, u0, u);
-  if (OP == OP_HELMH) v = v - P.lambda * u0;
+  if (OP == OP_LPL) return lpl_value(L.idr2, u0, u);
+  if (OP == OP_HELMH) return lpl_value(L.idr2, u0, u) - P.lambda * u0;
+  double a0[6], a[6];
+  simple_eps<OP>(L, b, colour, q - colour * L.cs, a0, a);
+  double v = vlpl_value(L.idr2, u0, u, a0, a);
+  if (OP != OP_VLPL) v = v - P.lambda * u0;
   return v;
 }
 // residual_box on all boxes (do_resid); returns the thread-local max |res|

@@ -38,6 +38,7 @@ namespace {
 struct HostLevel {
   LevelDev L;
   std::vector<double> var[4];
+  std::vector<double> eps[3], epsf[3];   // variables 5..7 (eps) and their stored ghost faces [box][6][nc*nc]
   std::vector<int> fkind, farg, ftype, fkind_old, farg_old, parent, coff;
   std::vector<double> bcpl;
 };
@@ -52,6 +53,10 @@ void build_level(HostLevel& H, int nc, int nbx, int nby, int nbz, const int* bc_
   if (nc >= 2 && (nc & (nc - 1)) == 0) { L.sh_nc = 0; while ((1 << L.sh_nc) < nc) ++L.sh_nc; L.sh_hx = L.sh_nc - 1; }
   for (int d = 0; d < 3; ++d) { L.dr[d] = dr * (1.0 + 0.25 * d); L.idr2[d] = 1.0 / (L.dr[d] * L.dr[d]); }
   for (int v = 0; v < 4; ++v) { H.var[v].assign((size_t)nb * L.bs, 0.0); L.var[v] = H.var[v].data(); }
+  for (int d = 0; d < 3; ++d) {
+    H.eps[d].assign((size_t)nb * L.bs, 1.0); H.epsf[d].assign((size_t)nb * 6 * nc * nc, 1.0);
+    L.var[4 + d] = H.eps[d].data(); L.faces[4 + d] = H.epsf[d].data();
+  }
   H.fkind.assign(nb * 6, FK_PHYS); H.farg.assign(nb * 6, -1); H.ftype.assign(nb * 6, 0);
   H.parent.assign(nb, -1); H.coff.assign(nb, 0);
   for (int bz = 0; bz < nbz; ++bz) for (int by = 0; by < nby; ++by) for (int bx = 0; bx < nbx; ++bx) {
@@ -84,6 +89,10 @@ struct Rng {   // xorshift: reproducible values in (-1, 1)
 void randomise(HostLevel& H, uint64_t seed) {
   Rng r{seed * 2654435761u + 88172645463325252ull};
   for (int v = 0; v < 4; ++v) for (double& x : H.var[v]) x = r.next();
+  for (int d = 0; d < 3; ++d) {        // positive coefficients
+    for (double& x : H.eps[d]) x = 1.5 + r.next();
+    for (double& x : H.epsf[d]) x = 1.5 + r.next();
+  }
 }
 
 ParamsDev params(int op, double lambda, const int* bc_types, const double* bc_values) {
@@ -111,11 +120,12 @@ int run_case(int nc, int nbx, int nby, int nbz, const int* bc_types, const doubl
   randomise(G, seed);
   for (int v = 0; v < 4; ++v) S.var[v] = G.var[v];
   for (int v = 0; v < 4; ++v) S.L.var[v] = S.var[v].data();
+  for (int d = 0; d < 3; ++d) { S.eps[d] = G.eps[d]; S.epsf[d] = G.epsf[d]; S.L.var[4 + d] = S.eps[d].data(); S.L.faces[4 + d] = S.epsf[d].data(); }
   int bad = 0;
   // two full GSRB sweeps
   for (int n = 0; n < 4; ++n) {
     for (int b = 0; b < G.L.nb; ++b) do_smooth<OP>(G.L, P, b, n & 1, 0, 1);
-    simple_smooth(S.L, P, n & 1, 0, 1);
+    simple_smooth<OP>(S.L, P, n & 1, 0, 1);
     bad += differing(G, S) ? 1 : 0;
   }
   // residual (and its max)
@@ -165,8 +175,13 @@ void dh_set_planes(int on) { g_planes = on; }
 // number of mismatching comparisons (0 = the fast path reproduces the general path bit for bit)
 int dh_compare_simple(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
                       unsigned long long seed) {
-  if (op == OP_LPL) return run_case<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
-  return run_case<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+  switch (op) {
+    case OP_LPL: return run_case<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_VLPL: return run_case<OP_VLPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_HELMH: return run_case<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_VHELMH: return run_case<OP_VHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    default: return run_case<OP_AHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+  }
 }
 int dh_compare_prolong(int ncf, int nbx, int nby, int nbz, int half_size_coarse, const int* bc_types, const double* bc_values,
                        unsigned long long seed) {

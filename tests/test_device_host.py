@@ -47,7 +47,7 @@ def six(ctype, values):
 def test_simple_level_functions_match_general_path(devhost, types, nc, planes):
     devhost.dh_set_planes(planes)
     for shape in SHAPES:
-        for op, lam in ((1, 0.0), (3, 2.5)):          # mg_laplacian, mg_helmholtz
+        for op, lam in ((1, 0.0), (2, 0.0), (3, 2.5), (4, 0.75), (5, 1.25)):   # mg_laplacian ... mg_ahelmholtz
             bad = devhost.dh_compare_simple(op, nc, *shape, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 7 * nc + op)
             assert bad == 0, (types, nc, shape, op)
     devhost.dh_set_planes(0)
