@@ -477,10 +477,15 @@ void sync_meta(omg_handle* h) {
       U.epoch = h->d_epoch.p + (L.lvl - OMG_LVL_LO); U.done = L.d_done.p;
     }
     // tail fast path (omg_ops.cuh simple_*): every face a physical boundary or a local same-level neighbour
+    // Option "tail_simple": 1 (default) = Laplacian / Helmholtz between constant boundaries -- the part that has run on
+    // a B200 (bitwise, profiles/r01u_*); 2 = also boundary planes and the variable-coefficient operators, which so far
+    // are verified on the host build only (tests/test_device_host.py) and wait for a GPU pass.
     D.simple = (h->tail_simple && L.nb >= 1 && D.sh_nc >= 0) ? 1 : 0;
+    const bool all_variants = h->tail_simple >= 2;
+    if (!all_variants && h->params.operator_type != 1 && h->params.operator_type != 3) D.simple = 0;
     for (size_t q = 0; q < L.h_fkind.size() && D.simple; ++q) {
-      const bool phi_ok = L.h_fkind[q] == FK_SAME || L.h_fkind[q] == FK_PHYS;
-      const bool old_ok = L.h_fkind_old[q] == FK_SAME || L.h_fkind_old[q] == FK_PHYS;
+      const bool phi_ok = L.h_fkind[q] == FK_SAME || (L.h_fkind[q] == FK_PHYS && (all_variants || L.h_farg[q] < 0));
+      const bool old_ok = L.h_fkind_old[q] == FK_SAME || (L.h_fkind_old[q] == FK_PHYS && (all_variants || L.h_farg_old[q] < 0));
       if (!phi_ok || !old_ok) D.simple = 0;
     }
     D.parent = L.d_parent.p; D.coff = L.d_coff.p; D.ppatch = L.xp.d_recv.p;
