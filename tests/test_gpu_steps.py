@@ -1,6 +1,8 @@
 """Per-kernel GPU parity: every building block of the cycle (smooth_boxes, update_coarse = residual +
 restriction + coarse rhs, correct_children = correction + prolongation, max_residual_lvl) run on its own on
 seeded random states and compared bitwise with the oracle, level by level."""
+import os
+
 import numpy as np
 import pytest
 
@@ -171,3 +173,18 @@ def test_copy_to_and_from_tree(product, amr):
             for sl in face_slices(n2 - 2):
                 assert np.array_equal(a[sl], b[sl])
             off += n2 ** 3
+
+
+@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1",
+                    reason="tail_simple = 2 (boundary planes, variable coefficients in the tail fast path) was written after the "
+                           "round's GPU budget was spent: host-verified only (tests/test_device_host.py); set OMG_TEST_UNVERIFIED=1")
+@pytest.mark.parametrize("op,bc,lam", [(P.mg_laplacian, "callback", 0.0), (P.mg_helmholtz, "callback", 2.5),
+                                       (P.mg_vlaplacian, "mixed", 0.0), (P.mg_vhelmholtz, "neumann0", 1.0),
+                                       (P.mg_ahelmholtz, "mixed", 0.5)])
+def test_tail_fast_path_all_variants(oracle, product, op, bc, lam):
+    orc, _ = P.uniform_problem(oracle.OracleMg, (64, 32, 32), 16, operator_type=op, bc=bc, lam=lam)
+    mg, _ = P.uniform_problem(product.Mg, (64, 32, 32), 16, operator_type=op, bc=bc, lam=lam)
+    mg.set_option("tail_simple", 2)
+    assert P.run_cycles(orc, 3, True) == P.run_cycles(mg, 3, True)
+    assert P.run_cycles(orc, 2, False) == P.run_cycles(mg, 2, False)
+    assert_state_equal(orc, mg)
