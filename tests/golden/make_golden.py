@@ -27,6 +27,10 @@ CASES = {
     "helmholtz32_neumann_fmg": dict(kind="uniform", n=32, box=8, fmg=True, its=3, op=P.mg_helmholtz, bc="neumann0", lam=1.0),
     "vlaplacian32_mixed_fmg": dict(kind="uniform", n=32, box=8, fmg=True, its=3, op=P.mg_vlaplacian, bc="mixed"),
     "refinement3_box8_fmg": dict(kind="amr", n=32, box=8, levels=3, fmg=True, its=3),
+    # implicit diffusion steps (src/m_diffusion.f90): residuals = [last max residual, number of V-cycles added] per step
+    "diffusion32_box8_order1": dict(kind="diffusion", n=32, box=8, order=1, steps=2, op=P.mg_helmholtz),
+    "diffusion32_box8_order2": dict(kind="diffusion", n=32, box=8, order=2, steps=2, op=P.mg_helmholtz),
+    "diffusion32_box8_vcoeff_order2": dict(kind="diffusion", n=32, box=8, order=2, steps=1, op=P.mg_vhelmholtz),
 }
 
 
@@ -51,6 +55,8 @@ def build(cls, name, **kw):
                                   bc=c.get("bc", "callback"), lam=c.get("lam", 0.0), **kw)
     elif c["kind"] == "perf":
         mg = P.performance_problem(cls, c["n"], c["box"], **kw)
+    elif c["kind"] == "diffusion":
+        mg = P.diffusion_problem(cls, c["n"], c["box"], operator_type=c["op"], **kw)
     else:
         mg, _ = P.refinement_problem(cls, c["levels"], c["box"], c["n"], **kw)
     return mg
@@ -59,7 +65,14 @@ def build(cls, name, **kw):
 def run_case(cls, name, **kw):
     c = CASES[name]
     mg = build(cls, name, **kw)
-    res = P.run_cycles(mg, c["its"], c["fmg"])
+    if c["kind"] == "diffusion":
+        res = []
+        for _ in range(c["steps"]):
+            r, n = (mg.diffusion_solve(2.0e-3, 1.5, c["order"], 1e-9) if c["op"] == P.mg_helmholtz
+                    else mg.diffusion_solve_vcoeff(2.0e-3, c["order"], 1e-9))
+            res += [r, float(n)]
+    else:
+        res = P.run_cycles(mg, c["its"], c["fmg"])
     return dict(name=name, residuals=[float(r).hex() for r in res], phi_checksum=checksum(mg))
 
 

@@ -220,3 +220,19 @@ def test_fast_kernels_variable_coefficient(oracle, product, op, bc, lam, n, box)
     check_histories(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
     check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
     assert_state_equal(orc, mg)
+
+
+def test_golden_fixtures_on_the_device(product):
+    """the committed fixtures (tests/golden/golden.json, oracle output): residual histories as exact hex floats and a
+    position-weighted checksum of phi on the leaves, reproduced by the CUDA path without running the oracle"""
+    import json
+    import os
+
+    import golden.make_golden as mk
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")) as f:
+        gold = json.load(f)
+    assert len(gold["cases"]) >= 10
+    for case in gold["cases"]:
+        got = mk.run_case(product.Mg, case["name"])
+        assert got["residuals"] == case["residuals"], case["name"]
+        assert got["phi_checksum"] == case["phi_checksum"], case["name"]
