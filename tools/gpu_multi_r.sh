@@ -5,7 +5,7 @@ nvidia-smi -L > gpurun_out/gpus.txt
 for N in "$@"; do
   for MODE in weak strong; do
     EXTRA=""; [ $MODE = strong ] && EXTRA="--strong --cells 1024"
-    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 \
+    timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 \
       bench.py --gpus $N --steps 10 --warmup 3 $EXTRA > gpurun_out/bench_n${N}_${MODE}.json 2> gpurun_out/bench_n${N}_${MODE}.err
     echo "N=$N $MODE rc=$?"; python - <<PY
 import json
