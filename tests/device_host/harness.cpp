@@ -222,6 +222,54 @@ int dh_level_op(int what, int op, int nc, int nbx, int nby, int nbz, const int* 
   if (out_max) *out_max = m;
   return 0;
 }
+// Two levels: a coarse level of ONE box of nc^3 and the fine level of its 2 x 2 x 2 children (same box size), constant
+// physical boundaries.  Arrays [box][k][j][i], interior cells; fine boxes in x-fastest octant order.
+//   what = 0: update_coarse (src/m_multigrid.f90:347-384) = residual on the fine level, restriction of phi and res,
+//             rhs_c = L(phi_c) + res_c and old_c = phi_c on the parent        (do_resid, do_restrict, do_crhs)
+//   what = 1: correct_children (:387-402) = res_c = phi_c - old_c, phi_f += prolongation of it (do_corr_prolong)
+// simple != 0 runs the tail's fast functions where they exist.  f* / c* = fine / coarse phi, rhs, old, res (in and out).
+int dh_two_level(int what, int simple, int op, int nc, const int* bc_types, const double* bc_values, double lambda, const double* dr_f,
+                 double* f_phi, double* f_rhs, double* f_old, double* f_res, double* c_phi, double* c_rhs, double* c_old, double* c_res) {
+  HostLevel F, C;
+  build_level(F, nc, 2, 2, 2, bc_types, 1.0);
+  build_level(C, nc, 1, 1, 1, bc_types, 1.0);
+  for (int d = 0; d < 3; ++d) {
+    F.L.dr[d] = dr_f[d]; F.L.idr2[d] = 1.0 / (dr_f[d] * dr_f[d]);
+    C.L.dr[d] = 2 * dr_f[d]; C.L.idr2[d] = 1.0 / (C.L.dr[d] * C.L.dr[d]);
+  }
+  for (HostLevel* H : {&F, &C}) {
+    const double sum = H->L.idr2[0] + H->L.idr2[1] + H->L.idr2[2];
+    H->L.fac = (op == OP_HELMH) ? 1.0 / (2 * sum + lambda) : 0.5 / sum;
+  }
+  const int h = nc / 2;
+  for (int b = 0; b < 8; ++b) { F.parent[b] = 0; F.coff[b] = ((b & 1) * h) | ((((b >> 1) & 1) * h) << 10) | ((((b >> 2) & 1) * h) << 20); }
+  std::vector<int> parents_list{0};
+  C.L.parents_list = parents_list.data(); C.L.n_parents = 1;
+  ParamsDev P = params(op, lambda, bc_types, bc_values);
+  const size_t n3 = (size_t)nc * nc * nc;
+  double* fa[4] = {f_phi, f_rhs, f_old, f_res};
+  double* ca[4] = {c_phi, c_rhs, c_old, c_res};
+  auto move = [&](HostLevel& H, double** a, bool in) {
+    for (int v = 0; v < 4; ++v) for (int b = 0; b < H.L.nb; ++b)
+      for (int k = 0; k < nc; ++k) for (int j = 0; j < nc; ++j) for (int i = 0; i < nc; ++i) {
+        double& dev = H.var[v][(size_t)b * H.L.bs + cidx(H.L, i, j, k)];
+        double& nat = a[v][b * n3 + ((size_t)k * nc + j) * nc + i];
+        if (in) dev = nat; else nat = dev;
+      }
+  };
+  move(F, fa, true); move(C, ca, true);
+  if (what == 0) {
+    if (simple) { if (op == OP_LPL) simple_resid<OP_LPL>(F.L, P, 0, 1); else simple_resid<OP_HELMH>(F.L, P, 0, 1); }
+    else for (int b = 0; b < 8; ++b) { if (op == OP_LPL) do_resid<OP_LPL>(F.L, P, b, 0, 1); else do_resid<OP_HELMH>(F.L, P, b, 0, 1); }
+    for (int b = 0; b < 8; ++b) { do_restrict(F.L, C.L, 0, b, 0, 1); do_restrict(F.L, C.L, 3, b, 0, 1); }
+    if (simple) { if (op == OP_LPL) simple_crhs<OP_LPL>(C.L, P, 0, 0, 1); else simple_crhs<OP_HELMH>(C.L, P, 0, 0, 1); }
+    else { if (op == OP_LPL) do_crhs<OP_LPL>(C.L, P, 0, 0, 1); else do_crhs<OP_HELMH>(C.L, P, 0, 0, 1); }
+  } else {
+    for (int b = 0; b < 8; ++b) { if (simple) simple_corr_prolong(F.L, C.L, P, b, 0, 1); else do_corr_prolong(F.L, C.L, P, b, 0, 1); }
+  }
+  move(F, fa, false); move(C, ca, false);
+  return 0;
+}
 // the batched division against the compiler's (host build: exact-reciprocal seed instead of MUFU.RCP64H)
 int dh_ddiv(const double* a, const double* b, double* out, int n) {
   for (int i = 0; i + 6 <= n; i += 6) ddiv_batch<6>(a + i, b + i, out + i);

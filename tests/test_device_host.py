@@ -131,3 +131,59 @@ def test_general_device_path_matches_oracle_on_one_level(devhost, oracle, op, la
     devhost.dh_level_op(1, op, nc, 2, 2, 2, six(C.c_int, types), six(C.c_double, values), lam, dr, vp(phi), vp(rhs), vp(res), C.byref(m))
     assert orc.max_residual_lvl(lvl) == m.value
     assert np.array_equal(res, gather(P.mg_ires))
+
+
+@pytest.mark.parametrize("simple", [0, 1])
+@pytest.mark.parametrize("bc", sorted(BC_OF))
+@pytest.mark.parametrize("op,lam", [(1, 0.0), (3, 1.75)])
+def test_device_transfer_operators_match_oracle(devhost, oracle, op, lam, bc, simple):
+    """update_coarse (residual, restriction, coarse right-hand side, old = phi) and correct_children (correction +
+    prolongation) of the device code -- general and fast variants -- against the oracle on two levels (one parent box,
+    its eight children) with random data: same bits, on the CPU"""
+    import problems as P
+    devhost.dh_two_level.argtypes = [C.c_int] * 4 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double)] + [C.c_void_p] * 8
+    nc = 8
+    orc, _ = P.uniform_problem(oracle.OracleMg, 16, nc, operator_type=op, bc=bc, lam=lam)
+    fine, coarse = orc.highest_lvl, orc.highest_lvl - 1
+    fids, (cid,) = orc.ids(fine), orc.ids(coarse)
+    assert len(fids) == 8 and orc.box_size_lvl(coarse) == nc
+    rng = np.random.default_rng(9)
+    pos = {}
+    for id_ in fids:
+        ix = orc.box_info(id_)["ix"]
+        pos[id_] = ((ix[2] - 1) * 2 + (ix[1] - 1)) * 2 + (ix[0] - 1)
+    for id_ in list(fids) + [cid]:
+        cc = orc.cc(id_, nc)
+        for iv in (P.mg_iphi, P.mg_irhs, P.mg_iold, P.mg_ires):
+            cc[iv - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((nc, nc, nc))
+    orc.mg_fill_ghost_cells_lvl(fine, P.mg_iphi)
+    orc.mg_fill_ghost_cells_lvl(coarse, P.mg_iphi)
+
+    def gather(ids, iv):
+        out = np.empty((len(ids), nc, nc, nc))
+        for id_ in ids:
+            out[pos.get(id_, 0)] = orc.cc(id_, nc)[iv - 1, 1:-1, 1:-1, 1:-1]
+        return out
+
+    ivs = (P.mg_iphi, P.mg_irhs, P.mg_iold, P.mg_ires)
+    f = [gather(fids, iv) for iv in ivs]
+    c = [gather([cid], iv) for iv in ivs]
+    types, values = BC_OF[bc]
+    dr = (C.c_double * 3)(*orc.dr(fine))
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)          # noqa: E731
+    call = lambda what: devhost.dh_two_level(what, simple, op, nc, six(C.c_int, types), six(C.c_double, values), lam, dr,   # noqa: E731
+                                             *[vp(a) for a in f], *[vp(a) for a in c])
+    call(0)
+    orc.update_coarse(fine)
+    assert np.array_equal(f[3], gather(fids, P.mg_ires)), "fine residual"
+    for k, iv in enumerate(ivs):
+        assert np.array_equal(c[k], gather([cid], iv)), "coarse variable %d after update_coarse" % iv
+    # a coarse "solve": new phi_c, ghost cells refilled as smooth_boxes would leave them
+    new_phi = rng.standard_normal((nc, nc, nc))
+    orc.cc(cid, nc)[P.mg_iphi - 1, 1:-1, 1:-1, 1:-1] = new_phi
+    orc.mg_fill_ghost_cells_lvl(coarse, P.mg_iphi)
+    c[0][0] = new_phi
+    call(1)
+    orc.correct_children(coarse)
+    assert np.array_equal(f[0], gather(fids, P.mg_iphi)), "fine phi after correct_children"
+    assert np.array_equal(c[3], gather([cid], P.mg_ires)), "coarse correction"
