@@ -142,3 +142,33 @@ def test_cpp_host_example_converges_on_the_device():
     r = subprocess.run([exe, "16", "64", "64", "64", "6", "t", "gsrb"], capture_output=True, text=True, check=True)
     errs = [float(m.group(1)) for m in re.finditer(r"max solution error\s+(\S+)", r.stdout)]
     assert len(errs) == 7 and errs[-1] < 1e-9 * max(1.0, errs[0])      # the reference test's pass criterion (:132-202)
+
+
+def test_host_side_error_stops_keep_the_reference_wording(product):
+    """SURVEY 8b "error convention": the reference `error stop`s with a text; the mirror raises with the same text
+    (src/m_build_tree.f90:32-34, src/m_multigrid.f90:50, src/m_helmholtz.f90:42-43, src/m_allocate_storage.f90:63,
+    src/m_laplacian.f90:46).  All of these are decided on the host: no device needed."""
+    def fresh(op=P.mg_laplacian):
+        mg = product.Mg(op, P.mg_smoother_gsrb)
+        for nb in range(1, 7):
+            mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
+        return mg
+
+    with pytest.raises(product.MgError, match="box_size should be even"):
+        fresh().mg_build_rectangle([30, 30, 30], 5, [1 / 30.0] * 3, [0.0] * 3, [False] * 3)
+    with pytest.raises(product.MgError, match="box_size does not divide domain_size"):
+        fresh().mg_build_rectangle([32, 32, 20], 8, [1 / 32.0] * 3, [0.0] * 3, [False] * 3)
+    with pytest.raises(product.MgError, match="mg_set_methods: unknown operator"):
+        fresh(op=9).mg_set_methods()
+    with pytest.raises(product.MgError, match="lambda < 0 not allowed"):
+        fresh(op=P.mg_helmholtz).set_lambda(-1.0)
+    with pytest.raises(product.MgError, match="allocate_storage: tree is not yet created"):
+        fresh().mg_allocate_storage()
+    mg = fresh()
+    mg.set_int("geometry_type", 2)                      # mg_cylindrical: 2-D only in the reference, unsupported here
+    with pytest.raises(product.MgError, match="unsupported geometry"):
+        mg.mg_set_methods()
+    mg = fresh()
+    mg.set_int("smoother_type", 3)                      # mg_smoother_jacobi is declared but not implemented by the reference either
+    with pytest.raises(product.MgError, match="unsupported smoother type"):
+        mg.mg_set_methods()
