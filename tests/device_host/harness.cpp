@@ -5,6 +5,7 @@
 // the tail's fast functions (simple_*) produce the bits of the general ones (do_*), i.e. of the path the GPU parity
 // tests pin to the oracle.  One "thread" (tid = 0, nthr = 1) walks every loop; a GSRB colour half-sweep only reads the
 // other colour and a cell's own value, so the sequential walk performs the same arithmetic as the parallel one.
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -269,6 +270,86 @@ int dh_two_level(int what, int simple, int op, int nc, const int* bc_types, cons
   }
   move(F, fa, false); move(C, ca, false);
   return 0;
+}
+// ---- prototype (NOT product code): temporal blocking of S GSRB half-sweeps in one pass over phi and rhs ------------
+// DESIGN.md "next round" item: the finest-level smoother is at its per-launch HBM roofline, the way past it is to apply
+// several half-sweeps while a tile streams through on-chip memory.  This host prototype fixes the dependency logic the
+// CUDA kernel will need and checks it bit for bit against S separate half-sweeps of the general device path:
+//   * xy tile of tx x ty cells plus a halo of S cells (clipped at the domain), streamed in +z;
+//   * at step k half-sweep s (s = 1..S, colour (s-1)&1) is applied IN PLACE to plane k-s+1 on the region
+//     tile +- (S-s), stages in increasing order within a step: plane k-s+2 then holds state s-1 and plane k-s has not yet
+//     received stage s+1, which is exactly what stage s must read (a Gauss-Seidel update reads the other colour only);
+//   * cells outside the region of their stage keep stale values that no later stage of this tile reads;
+//   * boundary ghosts c0*b + c1*phi(1) + c2*phi(2) use the cell's own CURRENT value, so the in-place window gives
+//     them for free; only the tile interior (stage S region) is written back.
+// Window: planes k-S+1 .. k+1 (S + 1 planes; the prototype keeps S + 2) of (tx + 2S) x (ty + 2S) cells -- 5 planes of 56 x 56 doubles = 125 KB
+// for S = 4 and 48 x 48 tiles.  Traffic per two full sweeps: phi in + out and rhs once, x (56/48)^2 = 27 B per cell
+// against 48 B for four separate half-sweeps.
+int dh_fused_proto(int nc, int nbx, int nby, int nbz, int tx, int ty, int S, const int* bc_types, const double* bc_values, unsigned long long seed) {
+  HostLevel G;
+  build_level(G, nc, nbx, nby, nbz, bc_types, 0.01);
+  ParamsDev P = params(OP_LPL, 0.0, bc_types, bc_values);
+  const double sum = G.L.idr2[0] + G.L.idr2[1] + G.L.idr2[2];
+  G.L.fac = 0.5 / sum;
+  randomise(G, seed);
+  const int NX = nc * nbx, NY = nc * nby, NZ = nc * nbz;
+  auto at = [&](std::vector<double>& v, int x, int y, int z) -> double& {
+    const int b = ((z / nc) * nby + y / nc) * nbx + x / nc;
+    return v[(size_t)b * G.L.bs + cidx(G.L, x % nc, y % nc, z % nc)];
+  };
+  // global copies of phi and rhs, then the reference result: S half-sweeps of the general path
+  std::vector<double> phi((size_t)NX * NY * NZ), rhs(phi.size()), out(phi.size());
+  auto gi = [&](int x, int y, int z) { return ((size_t)z * NY + y) * NX + x; };
+  for (int z = 0; z < NZ; ++z) for (int y = 0; y < NY; ++y) for (int x = 0; x < NX; ++x) { phi[gi(x, y, z)] = at(G.var[0], x, y, z); rhs[gi(x, y, z)] = at(G.var[1], x, y, z); }
+  for (int s = 1; s <= S; ++s) for (int b = 0; b < G.L.nb; ++b) do_smooth<OP_LPL>(G.L, P, b, (s - 1) & 1, 0, 1);
+  // boundary coefficients per face (constant boundaries), as simple_bc
+  double c0[6], c1[6], c2[6];
+  for (int f = 0; f < 6; ++f) {
+    const int type = bc_types[f];
+    if (type == -10) { c0[f] = 2; c1[f] = -1; c2[f] = 0; }
+    else if (type == -11) { c0[f] = G.L.dr[f >> 1] * ((f & 1) ? 1.0 : -1.0); c1[f] = 1; c2[f] = 0; }
+    else { c0[f] = 0; c1[f] = 2; c2[f] = -1; }
+  }
+  const int H = S, N[3] = {NX, NY, NZ};        // stage 1 updates tile +- (S-1) and reads original values one cell further out
+  for (int y0 = 0; y0 < NY; y0 += ty) for (int x0 = 0; x0 < NX; x0 += tx) {
+    const int xa = std::max(0, x0 - H), xb = std::min(NX, x0 + tx + H), ya = std::max(0, y0 - H), yb = std::min(NY, y0 + ty + H);
+    const int wx = xb - xa, wy = yb - ya;
+    std::vector<double> win((size_t)(S + 2) * wx * wy);             // ring of S + 2 planes
+    auto W = [&](int x, int y, int z) -> double& { return win[((size_t)((z + S + 2) % (S + 2)) * wy + (y - ya)) * wx + (x - xa)]; };
+    for (int y = ya; y < yb; ++y) for (int x = xa; x < xb; ++x) W(x, y, 0) = phi[gi(x, y, 0)];
+    for (int k = 0; k < NZ + S; ++k) {                                // step k: plane k + 1 enters (stage 1 at plane k reads it), plane k - S + 1 leaves
+      if (k + 1 < NZ) for (int y = ya; y < yb; ++y) for (int x = xa; x < xb; ++x) W(x, y, k + 1) = phi[gi(x, y, k + 1)];
+      for (int s = 1; s <= S; ++s) {
+        const int z = k - s + 1, colour = (s - 1) & 1, h = S - s;
+        if (z < 0 || z >= NZ) continue;
+        for (int y = std::max(ya, y0 - h); y < std::min(yb, y0 + ty + h); ++y) for (int x = std::max(xa, x0 - h); x < std::min(xb, x0 + tx + h); ++x) {
+          // colour 0 = cells with (x + y + z) even in 0-based box-local indices (boxes have even size: global parity is the same)
+          if (((x + y + z) & 1) != colour) continue;
+          const int p[3] = {x, y, z};
+          const double u0 = W(x, y, z);
+          double u[6];
+          for (int f = 0; f < 6; ++f) {
+            const int d = f >> 1, dir = (f & 1) ? 1 : -1;
+            int q[3] = {x, y, z}; q[d] += dir;
+            if (q[d] < 0 || q[d] >= N[d]) {                           // physical boundary: ghost from own value and the opposite neighbour
+              int r[3] = {x, y, z}; r[d] -= dir;
+              u[f] = c0[f] * bc_values[f] + c1[f] * u0 + c2[f] * W(r[0], r[1], r[2]);
+            } else u[f] = W(q[0], q[1], q[2]);
+          }
+          (void)p;
+          W(x, y, z) = gs_lpl_value(G.L.idr2, G.L.fac, u, rhs[gi(x, y, z)]);
+        }
+      }
+      const int zo = k - S + 1;                                       // plane that has received all S stages
+      if (zo >= 0 && zo < NZ) for (int y = y0; y < std::min(NY, y0 + ty); ++y) for (int x = x0; x < std::min(NX, x0 + tx); ++x) out[gi(x, y, zo)] = W(x, y, zo);
+    }
+  }
+  int bad = 0;
+  for (int z = 0; z < NZ; ++z) for (int y = 0; y < NY; ++y) for (int x = 0; x < NX; ++x) {
+    const double a = out[gi(x, y, z)], b = at(G.var[0], x, y, z);
+    bad += std::memcmp(&a, &b, 8) != 0;
+  }
+  return bad;
 }
 // the batched division against the compiler's (host build: exact-reciprocal seed instead of MUFU.RCP64H)
 int dh_ddiv(const double* a, const double* b, double* out, int n) {

@@ -187,3 +187,15 @@ def test_device_transfer_operators_match_oracle(devhost, oracle, op, lam, bc, si
     orc.correct_children(coarse)
     assert np.array_equal(f[0], gather(fids, P.mg_iphi)), "fine phi after correct_children"
     assert np.array_equal(c[3], gather([cid], P.mg_ires)), "coarse correction"
+
+
+@pytest.mark.parametrize("types", BC_SETS[:3])
+@pytest.mark.parametrize("nc,shape,tx,ty,S", [(8, (2, 2, 2), 8, 8, 4), (8, (3, 2, 2), 16, 8, 4), (4, (4, 4, 2), 8, 8, 2),
+                                              (8, (2, 2, 1), 4, 4, 4), (8, (2, 2, 2), 16, 16, 6), (16, (2, 1, 1), 16, 8, 4),
+                                              (8, (2, 2, 2), 6, 10, 3)])
+def test_temporal_blocking_prototype_matches_separate_half_sweeps(devhost, types, nc, shape, tx, ty, S):
+    """next-round groundwork (harness.cpp dh_fused_proto): S GSRB half-sweeps applied in one
+    z-streaming pass over xy tiles with an S-cell halo, in place, give the bits of S separate half-sweeps of the
+    general device path -- for every tiling, S = 2..6 and every boundary-condition type"""
+    devhost.dh_fused_proto.argtypes = [C.c_int] * 7 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_ulonglong]
+    assert devhost.dh_fused_proto(nc, *shape, tx, ty, S, six(C.c_int, types), six(C.c_double, BC_VALUES), 5) == 0
