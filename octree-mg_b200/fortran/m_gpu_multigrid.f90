@@ -88,6 +88,19 @@ module m_gpu_multigrid
      integer(c_int) function omg_diffusion_set_rhs(h, f1, f2) bind(C, name="omg_diffusion_set_rhs")
        import; type(c_ptr), value :: h; real(c_double), value :: f1, f2
      end function omg_diffusion_set_rhs
+     integer(c_int) function omg_copy_to_tree(h, iv, lvl_lo, lvl_hi, leaves_only, with_ghosts, buf, n) &
+          bind(C, name="omg_copy_to_tree")
+       import; type(c_ptr), value :: h; integer(c_int), value :: iv, lvl_lo, lvl_hi, leaves_only, with_ghosts
+       real(c_double), intent(in) :: buf(*); integer(c_int64_t), value :: n
+     end function omg_copy_to_tree
+     integer(c_int) function omg_copy_from_tree(h, iv, lvl_lo, lvl_hi, leaves_only, with_ghosts, buf, n) &
+          bind(C, name="omg_copy_from_tree")
+       import; type(c_ptr), value :: h; integer(c_int), value :: iv, lvl_lo, lvl_hi, leaves_only, with_ghosts
+       real(c_double), intent(inout) :: buf(*); integer(c_int64_t), value :: n
+     end function omg_copy_from_tree
+     integer(c_int64_t) function omg_copy_size(h, lvl_lo, lvl_hi, leaves_only, with_ghosts) bind(C, name="omg_copy_size")
+       import; type(c_ptr), value :: h; integer(c_int), value :: lvl_lo, lvl_hi, leaves_only, with_ghosts
+     end function omg_copy_size
      integer(c_int) function omg_nccl_unique_id(uid) bind(C, name="omg_nccl_unique_id")
        import; character(kind=c_char) :: uid(128)
      end function omg_nccl_unique_id
@@ -113,6 +126,7 @@ module m_gpu_multigrid
   public :: mg_gpu_push, mg_gpu_pull
   public :: mg_fas_fmg, mg_fas_vcycle, mg_apply_op
   public :: diffusion_solve, diffusion_solve_vcoeff, diffusion_solve_acoeff
+  public :: mg_gpu_copy_size, mg_gpu_copy_to_tree, mg_gpu_copy_from_tree
   public :: mg_fill_ghost_cells_lvl, mg_fill_ghost_cells, mg_restrict_lvl, mg_restrict, mg_prolong
 
 contains
@@ -518,5 +532,36 @@ contains
     integer, intent(in)       :: order
     call diffusion_common(mg, mg_ahelmholtz, dt, order, max_res)
   end subroutine diffusion_solve_acoeff
+
+  !> Doubles a buffer of the two routines below holds: owned leaves (or all owned boxes), nc**3 or (nc+2)**3 per box
+  integer(c_int64_t) function mg_gpu_copy_size(leaves_only, with_ghosts)
+    logical, intent(in) :: leaves_only, with_ghosts
+    mg_gpu_copy_size = omg_copy_size(gpu%handle, mg_lvl_lo, mg_lvl_hi, merge(1, 0, leaves_only), merge(1, 0, with_ghosts))
+  end function mg_gpu_copy_size
+
+  !> mg_copy_to_tree of the application coupling (coupling_amrvac/mod_multigrid_coupling.t:133-171) straight onto the
+  !> device: buf = the grid leaves in my_leaves order, interior cells (or with one ghost layer), i fastest
+  subroutine mg_gpu_copy_to_tree(mg, iv, buf, leaves_only, with_ghosts)
+    type(mg_t), intent(inout) :: mg
+    integer, intent(in)       :: iv
+    real(dp), intent(in)      :: buf(:)
+    logical, intent(in)       :: leaves_only, with_ghosts
+    if (.not. mg%is_allocated) error stop "mg_copy_to_tree: tree not allocated yet"
+    call push_params(mg)
+    call check(omg_copy_to_tree(gpu%handle, iv, mg_lvl_lo, mg_lvl_hi, merge(1, 0, leaves_only), &
+         merge(1, 0, with_ghosts), buf, int(size(buf), c_int64_t)), "mg_copy_to_tree")
+  end subroutine mg_gpu_copy_to_tree
+
+  !> mg_copy_from_tree / mg_copy_from_tree_gc (:206-267)
+  subroutine mg_gpu_copy_from_tree(mg, iv, buf, leaves_only, with_ghosts)
+    type(mg_t), intent(inout) :: mg
+    integer, intent(in)       :: iv
+    real(dp), intent(inout)   :: buf(:)
+    logical, intent(in)       :: leaves_only, with_ghosts
+    if (.not. mg%is_allocated) error stop "mg_copy_from_tree: tree not allocated yet"
+    call push_params(mg)
+    call check(omg_copy_from_tree(gpu%handle, iv, mg_lvl_lo, mg_lvl_hi, merge(1, 0, leaves_only), &
+         merge(1, 0, with_ghosts), buf, int(size(buf), c_int64_t)), "mg_copy_from_tree")
+  end subroutine mg_gpu_copy_from_tree
 
 end module m_gpu_multigrid

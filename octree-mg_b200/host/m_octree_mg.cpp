@@ -630,6 +630,22 @@ void mg_prolong(mg_t& mg, int lvl, int iv, int iv_to, bool add) {               
   if (!mg.gpu_resident) transfer(mg, iv_to, false, false, lvl + 1, lvl + 1);
 }
 
+// coupling_amrvac/mod_multigrid_coupling.t:133-171, 206-267 on the device tree (no host cc arrays in between)
+int64_t mg_copy_size(const mg_t& mg, bool leaves_only, bool with_ghosts) {
+  need_gpu(mg);
+  return omg_copy_size(mg.gpu, mg_lvl_lo, mg_lvl_hi, leaves_only ? 1 : 0, with_ghosts ? 1 : 0);
+}
+void mg_copy_to_tree(mg_t& mg, int iv, const double* buf, int64_t n_doubles, bool leaves_only, bool with_ghosts) {
+  if (!mg.is_allocated) stop("mg_copy_to_tree: tree not allocated yet");                  // :144-145
+  push_params(mg);
+  gpu_check(mg, omg_copy_to_tree(mg.gpu, iv, mg_lvl_lo, mg_lvl_hi, leaves_only ? 1 : 0, with_ghosts ? 1 : 0, buf, n_doubles), "mg_copy_to_tree");
+}
+void mg_copy_from_tree(mg_t& mg, int iv, double* buf, int64_t n_doubles, bool leaves_only, bool with_ghosts) {
+  if (!mg.is_allocated) stop("mg_copy_from_tree: tree not allocated yet");                // :215-216
+  push_params(mg);
+  gpu_check(mg, omg_copy_from_tree(mg.gpu, iv, mg_lvl_lo, mg_lvl_hi, leaves_only ? 1 : 0, with_ghosts ? 1 : 0, buf, n_doubles), "mg_copy_from_tree");
+}
+
 }  // namespace omg
 
 // =====================================================================================================

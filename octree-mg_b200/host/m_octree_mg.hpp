@@ -144,6 +144,13 @@ void mg_restrict_lvl(mg_t& mg, int iv, int lvl);
 void mg_restrict(mg_t& mg, int iv);
 void mg_prolong(mg_t& mg, int lvl, int iv, int iv_to, bool add);
 
+// ---- application arrays <-> device tree (mg_copy_to_tree / mg_copy_from_tree[_gc],
+//      coupling_amrvac/mod_multigrid_coupling.t:133-267): `buf` holds the owned leaves (leaves_only) or all owned boxes of
+//      every level in my_ids order, nc^3 interior cells per box or (nc+2)^3 with one ghost layer, i fastest ------------
+int64_t mg_copy_size(const mg_t& mg, bool leaves_only = true, bool with_ghosts = false);
+void mg_copy_to_tree(mg_t& mg, int iv, const double* buf, int64_t n_doubles, bool leaves_only = true, bool with_ghosts = false);
+void mg_copy_from_tree(mg_t& mg, int iv, double* buf, int64_t n_doubles, bool leaves_only = true, bool with_ghosts = false);
+
 // ---- host <-> device coherence ------------------------------------------------------
 void mg_gpu_push(mg_t& mg, int iv);                       // all levels, owned boxes
 void mg_gpu_pull(mg_t& mg, int iv, bool with_ghosts = true);
