@@ -122,7 +122,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -709,6 +709,7 @@ void run_submean(omg_handle* h, int iv, int with_ghosts) {
 void exec_steps(omg_handle* h, Program& P) {
   cudaStream_t s = h->stream;
   const ParamsDev& PD = h->pdev;
+  omgf::set_pdl(h->pdl && h->n_cpu == 1 && !h->profile);
   for (const Step& st : P.steps) {
     const bool prof = h->profile && st.kind != S_SUBMEAN && st.kind != S_CLEAR_SLOT && st.kind != S_COPY_SLOT &&
                       st.kind != S_ZERO_PHI && st.kind != S_HALO_FORK && st.kind != S_HALO_JOIN;
@@ -1523,6 +1524,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "tail_smem") h->tail_smem = value;
     else if (k == "tail_simple") { h->tail_simple = value; h->params_dirty = true; }
     else if (k == "overlap") h->overlap = value;
+    else if (k == "pdl") h->pdl = value;
     else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
     else if (k == "fused") { h->fused = value; h->params_dirty = true; }
     else if (k == "bnd_first_boxes") h->bnd_first_boxes = value;

@@ -58,6 +58,16 @@ __device__ __forceinline__ void wait_flag(const volatile unsigned long long* f, 
   }
 }
 
+// Programmatic dependent launch (option "pdl", off by default): the next kernel of the stream may become resident while
+// this grid's last wave drains; it then blocks in pdl_sync() until this grid has completed and its stores are visible.
+// Everything before pdl_sync() may only touch data no kernel writes (index / face tables, parameters, barrier set-up).
+__device__ __forceinline__ void pdl_sync(int pdl) {
+  if (pdl) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+  }
+}
+
 __device__ __forceinline__ void bc_coeffs(int type, double dr, int f, double& c0, double& c1, double& c2) {
   // bc_to_gc, src/m_ghost_cells.f90:682-698
   if (type == -10) { c0 = 2; c1 = -1; c2 = 0; }
@@ -96,7 +106,7 @@ struct SmoothSmem : TileSmem<NC, KT> {
 template <int NC, int KT, bool VC>
 __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
                                                                           const __grid_constant__ ParamsDev P, int colour,
-                                                                          const int* __restrict__ boxlist, int fused_put) {
+                                                                          const int* __restrict__ boxlist, int fused_put, int pdl) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -116,8 +126,9 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   const double* __restrict__ Rg = L.var[1] + boxoff + (size_t)colour * L.cs;
 
   // the tile itself depends on nothing but the box index: its copy starts before the face table is read
+  if (tid == 0) mbar_init(&S.bar, 1);
+  pdl_sync(pdl);
   if (tid == 0) {
-    mbar_init(&S.bar, 1);
     mbar_expect_tx(&S.bar, (VC ? 2 : 1) * KT * NC * HX * 8);
     bulk_g2s(&S.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
     if constexpr (VC) bulk_g2s(&S.E.B[0][0][0], L.var[4] + boxoff + (size_t)oc * L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
@@ -350,6 +361,20 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   }
 }
 
+// launch with the programmatic-stream-serialization attribute: the kernel may start before its predecessor in the stream
+// has finished and orders itself with pdl_sync()
+bool g_pdl = false;
+template <typename... KArgs, typename... Args>
+bool launch_pdl(void (*kern)(KArgs...), int grid, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...) == cudaSuccess;
+}
+
 template <int NC, int KT, bool VC>
 bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
   static bool configured = false;
@@ -358,7 +383,9 @@ bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, const int*
     if (cudaFuncSetAttribute(k_smooth_lpl_fast<NC, KT, VC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_smooth_lpl_fast<NC, KT, VC><<<(list ? n : L.nb) * (NC / KT), kThreads, smem, s>>>(L, P, colour, list, fused);
+  const int grid = (list ? n : L.nb) * (NC / KT);
+  if (g_pdl && !fused) return launch_pdl(k_smooth_lpl_fast<NC, KT, VC>, grid, smem, s, L, P, colour, list, fused, 1);
+  k_smooth_lpl_fast<NC, KT, VC><<<grid, kThreads, smem, s>>>(L, P, colour, list, fused, 0);
   return true;
 }
 
@@ -418,7 +445,7 @@ __device__ __forceinline__ void block_neighbours(const BothSmem<NC, KT>& F, cons
 
 template <int NC, int KT, int MODE, bool HELM, int MB, bool VC>
 __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
-                                                           const __grid_constant__ ParamsDev P, double* maxslot) {
+                                                           const __grid_constant__ ParamsDev P, double* maxslot, int pdl) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
   using SM = StencilSmem<NC, KT, VC>;
@@ -432,8 +459,9 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   const size_t boxoff = (size_t)b * L.bs;
 
   // the tile itself depends on nothing but the box index: its copies start before the face table is read
+  if (tid == 0) mbar_init(&S.bar, 1);
+  pdl_sync(pdl);
   if (tid == 0) {
-    mbar_init(&S.bar, 1);
     mbar_expect_tx(&S.bar, (VC ? 2 : 1) * 2 * KT * NC * HX * 8);
     if (TILES == 1) bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff, 2 * KT * NC * HX * 8, &S.bar);   // whole box: one 32 KiB copy
     else {
@@ -686,7 +714,8 @@ bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, i
     if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM, MB, VC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_stencil_fast<NC, KT, MODE, HELM, MB, VC><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot);
+  if (g_pdl) return launch_pdl(k_stencil_fast<NC, KT, MODE, HELM, MB, VC>, nboxes * (NC / KT), smem, s, L, Lc, P, maxslot, 1);
+  k_stencil_fast<NC, KT, MODE, HELM, MB, VC><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot, 0);
   return true;
 }
 
@@ -731,15 +760,16 @@ bool dispatch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P,
 // =================================================================================================
 template <int NC, int MB>
 __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid_constant__ LevelDev Lf, const __grid_constant__ LevelDev Lc,
-                                                                const __grid_constant__ ParamsDev P) {
+                                                                const __grid_constant__ ParamsDev P, int pdl) {
   constexpr int HC = NC / 2, HX = NC / 2, PW = HC + 2, NIT = HC * HC * HC / kThreads;
   static_assert((HC * HC * HC) % kThreads == 0, "coarse cells must tile the CTA");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* corr = reinterpret_cast<double*>(smem_raw);       // [PW][PW][PW]
   const int tid = threadIdx.x, b = blockIdx.x;
   const int p = Lf.parent[b];
-  if (p == -1) return;
   const int off = Lf.coff[b];
+  pdl_sync(pdl);
+  if (p == -1) return;
   const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
   double* __restrict__ phi = Lf.var[0] + (size_t)b * Lf.bs;
   const int fcs = Lf.cs;
@@ -817,13 +847,16 @@ bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev
     if (cudaFuncSetAttribute(k_corr_prolong_fast<NC, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  k_corr_prolong_fast<NC, MB><<<Lf.nb, kThreads, smem, s>>>(Lf, Lc, P);
+  if (g_pdl) return launch_pdl(k_corr_prolong_fast<NC, MB>, Lf.nb, smem, s, Lf, Lc, P, 1);
+  k_corr_prolong_fast<NC, MB><<<Lf.nb, kThreads, smem, s>>>(Lf, Lc, P, 0);
   return true;
 }
 
 }  // namespace
 
 namespace omgf {
+
+void set_pdl(bool on) { g_pdl = on; }
 
 bool smooth_applies(const LevelDev& L, const ParamsDev& P) {
   if (L.nc != 16 && L.nc != 32) return false;

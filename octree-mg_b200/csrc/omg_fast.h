@@ -6,6 +6,9 @@
 #include "omg_device.cuh"
 
 namespace omgf {
+// option "pdl": launch the kernels below with programmatic stream serialization (they order themselves with
+// griddepcontrol.wait); single-rank cycles only, off by default
+void set_pdl(bool on);
 // list != null: only the n boxes of the list (partition-face / interior split of a distributed level)
 // fused: the list is the level in launch order, partition-face boxes first; they exchange their faces in-kernel (PutDev)
 bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, int fused, cudaStream_t s);

@@ -188,3 +188,19 @@ def test_tail_fast_path_all_variants(oracle, product, op, bc, lam):
     assert P.run_cycles(orc, 3, True) == P.run_cycles(mg, 3, True)
     assert P.run_cycles(orc, 2, False) == P.run_cycles(mg, 2, False)
     assert_state_equal(orc, mg)
+
+
+@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1",
+                    reason="option pdl (programmatic dependent launch of the TMA-staged kernels) was written after the round's "
+                           "GPU budget was spent; off by default; set OMG_TEST_UNVERIFIED=1")
+@pytest.mark.parametrize("op,lam", [(P.mg_laplacian, 0.0), (P.mg_vhelmholtz, 1.5)])
+@pytest.mark.parametrize("graph", [0, 1])
+def test_pdl_launches_change_nothing(oracle, product, op, lam, graph):
+    orc, _ = P.uniform_problem(oracle.OracleMg, (64, 64, 32), 16, operator_type=op, bc="mixed", lam=lam)
+    mg, _ = P.uniform_problem(product.Mg, (64, 64, 32), 16, operator_type=op, bc="mixed", lam=lam)
+    mg.set_option("tail_cells", 512)      # several levels on the TMA-staged kernels, back to back
+    mg.set_option("use_graph", graph)
+    mg.set_option("pdl", 1)
+    assert P.run_cycles(orc, 3, True) == P.run_cycles(mg, 3, True)
+    assert P.run_cycles(orc, 3, False) == P.run_cycles(mg, 3, False)
+    assert_state_equal(orc, mg)

@@ -1,6 +1,6 @@
 #!/bin/bash
 # First GPU call of the next round (1 GPU, ~6 min): everything that was written after round 1's GPU budget ran out.
-#   1. the whole GPU suite incl. the opt-in tests (tail_simple = 2 variants, the C++ example)
+#   1. the whole GPU suite incl. the opt-in tests (tail_simple = 2 variants, option pdl, the C++ example)
 #   2. bitwise quick check + tail timing with the gated variants switched on
 #   3. default bench line, launch list
 set -x
@@ -15,6 +15,8 @@ for OP in vlaplacian vhelmholtz; do
     timeout 600 python bench.py --no-cpu-baseline --no-e2e --op $OP --opt tail_simple=$TS > gpurun_out/bench_r2_${OP}_ts$TS.json 2> gpurun_out/bench_r2_${OP}_ts$TS.err
   done
 done
+# programmatic dependent launch of the TMA-staged kernels (option pdl, gated): effect on the default bench
+timeout 600 python bench.py --no-cpu-baseline --no-e2e --opt pdl=1 > gpurun_out/bench_r2_pdl.json 2> gpurun_out/bench_r2_pdl.err
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_r2.csv $CMD > gpurun_out/ncu_list_r2.log 2>&1
 python - <<'PY'
