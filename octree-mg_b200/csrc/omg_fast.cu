@@ -15,6 +15,7 @@ namespace {
 
 constexpr int kThreads = 256;
 
+#ifndef OMG_HOST_EMU   // tests/device_host/fast_emu.cpp supplies host stand-ins for this block and the three macros below
 // ---- mbarrier / TMA bulk-copy PTX ---------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -57,15 +58,16 @@ __device__ __forceinline__ void wait_flag(const volatile unsigned long long* f, 
     __nanosleep(64);
   }
 }
+#define OMG_DYN_SMEM(name, al) extern __shared__ __align__(al) unsigned char name[]
+#define OMG_LAUNCH(kern, grid, smem, stream, ...) kern<<<(grid), kThreads, (smem), (stream)>>>(__VA_ARGS__)
+#define OMG_PDL_ASM() do { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); asm volatile("griddepcontrol.wait;" ::: "memory"); } while (0)
+#endif
 
 // Programmatic dependent launch (option "pdl", off by default): the next kernel of the stream may become resident while
 // this grid's last wave drains; it then blocks in pdl_sync() until this grid has completed and its stores are visible.
 // Everything before pdl_sync() may only touch data no kernel writes (index / face tables, parameters, barrier set-up).
 __device__ __forceinline__ void pdl_sync(int pdl) {
-  if (pdl) {
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-  }
+  if (pdl) OMG_PDL_ASM();
 }
 
 __device__ __forceinline__ void bc_coeffs(int type, double dr, int f, double& c0, double& c1, double& c2) {
@@ -109,7 +111,7 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
                                                                           const int* __restrict__ boxlist, int fused_put, int pdl) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  OMG_DYN_SMEM(smem_raw, 128);
   SmoothSmem<NC, KT, VC>& S = *reinterpret_cast<SmoothSmem<NC, KT, VC>*>(smem_raw);
   const int tid = threadIdx.x;
 
@@ -366,6 +368,9 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
 bool g_pdl = false;
 template <typename... KArgs, typename... Args>
 bool launch_pdl(void (*kern)(KArgs...), int grid, size_t smem, cudaStream_t s, Args&&... args) {
+#ifdef OMG_HOST_EMU
+  return false;
+#else
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem; cfg.stream = s;
   cudaLaunchAttribute at[1];
@@ -373,6 +378,7 @@ bool launch_pdl(void (*kern)(KArgs...), int grid, size_t smem, cudaStream_t s, A
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...) == cudaSuccess;
+#endif
 }
 
 template <int NC, int KT, bool VC>
@@ -385,7 +391,8 @@ bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, const int*
   }
   const int grid = (list ? n : L.nb) * (NC / KT);
   if (g_pdl && !fused) return launch_pdl(k_smooth_lpl_fast<NC, KT, VC>, grid, smem, s, L, P, colour, list, fused, 1);
-  k_smooth_lpl_fast<NC, KT, VC><<<grid, kThreads, smem, s>>>(L, P, colour, list, fused, 0);
+  auto kern = k_smooth_lpl_fast<NC, KT, VC>;
+  OMG_LAUNCH(kern, grid, smem, s, L, P, colour, list, fused, 0);
   return true;
 }
 
@@ -449,7 +456,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
   using SM = StencilSmem<NC, KT, VC>;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  OMG_DYN_SMEM(smem_raw, 128);
   SM& S = *reinterpret_cast<SM*>(smem_raw);
   const int tid = threadIdx.x;
   const int bq = blockIdx.x / TILES;
@@ -715,7 +722,8 @@ bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, i
     configured = true;
   }
   if (g_pdl) return launch_pdl(k_stencil_fast<NC, KT, MODE, HELM, MB, VC>, nboxes * (NC / KT), smem, s, L, Lc, P, maxslot, 1);
-  k_stencil_fast<NC, KT, MODE, HELM, MB, VC><<<nboxes * (NC / KT), kThreads, smem, s>>>(L, Lc, P, maxslot, 0);
+  auto kern = k_stencil_fast<NC, KT, MODE, HELM, MB, VC>;
+  OMG_LAUNCH(kern, nboxes * (NC / KT), smem, s, L, Lc, P, maxslot, 0);
   return true;
 }
 
@@ -763,7 +771,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid
                                                                 const __grid_constant__ ParamsDev P, int pdl) {
   constexpr int HC = NC / 2, HX = NC / 2, PW = HC + 2, NIT = HC * HC * HC / kThreads;
   static_assert((HC * HC * HC) % kThreads == 0, "coarse cells must tile the CTA");
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  OMG_DYN_SMEM(smem_raw, 16);
   double* corr = reinterpret_cast<double*>(smem_raw);       // [PW][PW][PW]
   const int tid = threadIdx.x, b = blockIdx.x;
   const int p = Lf.parent[b];
@@ -848,7 +856,8 @@ bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev
     configured = true;
   }
   if (g_pdl) return launch_pdl(k_corr_prolong_fast<NC, MB>, Lf.nb, smem, s, Lf, Lc, P, 1);
-  k_corr_prolong_fast<NC, MB><<<Lf.nb, kThreads, smem, s>>>(Lf, Lc, P, 0);
+  auto kern = k_corr_prolong_fast<NC, MB>;
+  OMG_LAUNCH(kern, Lf.nb, smem, s, Lf, Lc, P, 0);
   return true;
 }
 

@@ -1,0 +1,215 @@
+// CTA emulator: a host build of the TMA-staged kernels (octree-mg_b200/csrc/omg_fast.cu) for CPU tests.
+//
+// Test infrastructure.  g++ compiles the SAME kernel source the GPU runs -- omg_fast.cu is included below -- with the
+// CUDA execution model reduced to what these kernels use: the 256 threads of a CTA are 256 host threads, __syncthreads is
+// a barrier, warp shuffles go through a per-warp exchange buffer, a TMA bulk copy (cp.async.bulk + mbarrier) is a memcpy
+// whose alignment, size, destination range and expect_tx accounting are CHECKED (a mismatch there would hang or fault
+// on the GPU), CTAs run one after the other.  What this proves: indexing, staging, boundary handling and arithmetic of the
+// fast kernels against the general per-cell path (omg_ops.cuh do_*, the path the GPU parity tests and
+// test_device_host.py pin to the oracle), bit for bit.  What it cannot show: races between CTAs, performance.
+#include <pthread.h>
+
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <thread>
+#include <vector>
+
+#define OMG_EMU_THREADS 1
+#define OMG_HOST_EMU 1
+
+struct FakeDim { unsigned x = 0, y = 0, z = 0; };
+namespace emu {
+constexpr int NT = 256;
+unsigned char* g_smem = nullptr;      // the CTA's dynamic shared memory
+size_t g_smem_bytes = 0;              // as passed to the launch
+pthread_barrier_t g_cta_bar, g_warp_bar[NT / 32];
+double g_shfl[NT];
+std::atomic<long long> g_tx_expected{0}, g_tx_done{0};
+std::atomic<int> g_violations{0};
+void violation(const char* what) {
+  if (g_violations.fetch_add(1) < 5) std::fprintf(stderr, "fast_emu: %s\n", what);
+}
+}  // namespace emu
+
+static thread_local FakeDim threadIdx, blockIdx;
+static FakeDim blockDim = {emu::NT, 1, 1};
+static inline void __syncthreads() { pthread_barrier_wait(&emu::g_cta_bar); }
+static inline void __syncwarp() {}
+static inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
+static inline double __shfl_xor_sync(unsigned, double v, int o) {
+  const int t = (int)threadIdx.x;
+  emu::g_shfl[t] = v;
+  pthread_barrier_wait(&emu::g_warp_bar[t >> 5]);
+  const double r = emu::g_shfl[t ^ o];
+  pthread_barrier_wait(&emu::g_warp_bar[t >> 5]);
+  return r;
+}
+static inline unsigned long long atomicMax(unsigned long long* a, unsigned long long v) {
+  unsigned long long o = __atomic_load_n(a, __ATOMIC_RELAXED);
+  while (o < v && !__atomic_compare_exchange_n(a, &o, v, false, __ATOMIC_SEQ_CST, __ATOMIC_RELAXED)) {}
+  return o;
+}
+static inline unsigned int atomicAdd(unsigned int* a, unsigned int v) { return __atomic_fetch_add(a, v, __ATOMIC_SEQ_CST); }
+static inline int atomicExch(int* a, int v) { return __atomic_exchange_n(a, v, __ATOMIC_SEQ_CST); }
+
+#include "harness.cpp"   // HostLevel, build_level, randomise, params + the general device path (omg_ops.cuh)
+
+// ---- stand-ins for the PTX helper block of omg_fast.cu ------------------------------------------------------
+static inline void mbar_init(uint64_t*, uint32_t) {}
+static inline void mbar_expect_tx(uint64_t*, uint32_t bytes) { emu::g_tx_expected += bytes; }
+static inline void mbar_arrive_expect_tx(uint64_t*, uint32_t bytes) { emu::g_tx_expected += bytes; }
+static inline void mbar_wait(uint64_t*, uint32_t) {}   // every use is followed by __syncthreads before the data is read
+static inline void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t*) {
+  const unsigned char* d = static_cast<unsigned char*>(dst);
+  if (((uintptr_t)dst & 15) || ((uintptr_t)src & 15) || (bytes & 15) || bytes == 0) emu::violation("bulk copy: address or size not a multiple of 16");
+  if (d < emu::g_smem || d + bytes > emu::g_smem + emu::g_smem_bytes) emu::violation("bulk copy: destination outside the CTA's shared memory");
+  std::memcpy(dst, src, bytes);
+  emu::g_tx_done += bytes;
+}
+static inline void wait_flag(const volatile unsigned long long*, unsigned long long, int*) {}
+#define OMG_DYN_SMEM(name, al) unsigned char* name = emu::g_smem
+#define OMG_PDL_ASM() do {} while (0)
+#define OMG_LAUNCH(kern, grid, smem, stream, ...) emu::launch((grid), (smem), [&]() { kern(__VA_ARGS__); })
+#define cudaFuncSetAttribute(...) cudaSuccess
+#undef __launch_bounds__
+#define __launch_bounds__(...)
+#undef __grid_constant__
+#define __grid_constant__
+
+namespace emu {
+void launch(int grid, size_t smem, const std::function<void()>& body) {
+  static unsigned char* buf = static_cast<unsigned char*>(aligned_alloc(1024, 256 * 1024));
+  g_smem = buf; g_smem_bytes = smem;
+  if (smem > 227 * 1024) violation("launch: more than 227 KB of shared memory");
+  pthread_barrier_init(&g_cta_bar, nullptr, NT);
+  for (auto& w : g_warp_bar) pthread_barrier_init(&w, nullptr, 32);
+  std::vector<std::thread> th;
+  th.reserve(NT);
+  for (int t = 0; t < NT; ++t)
+    th.emplace_back([&, t]() {
+      for (int b = 0; b < grid; ++b) {
+        threadIdx.x = (unsigned)t; blockIdx.x = (unsigned)b;
+        if (t == 0) { g_tx_expected = 0; g_tx_done = 0; std::memset(g_smem, 0xff, smem); }   // NaN-fill: stale reads show
+        pthread_barrier_wait(&g_cta_bar);
+        body();
+        pthread_barrier_wait(&g_cta_bar);
+        if (t == 0 && g_tx_expected != g_tx_done) violation("mbarrier: expected bytes differ from the bytes copied (the GPU would hang)");
+      }
+    });
+  for (auto& x : th) x.join();
+  pthread_barrier_destroy(&g_cta_bar);
+  for (auto& w : g_warp_bar) pthread_barrier_destroy(&w);
+}
+}  // namespace emu
+
+#include "../../octree-mg_b200/csrc/omg_fast.cu"
+
+namespace {
+
+void copy_data(HostLevel& dst, const HostLevel& src) {   // same shape: values only (the LevelDev pointers stay the level's own)
+  for (int v = 0; v < 4; ++v) std::copy(src.var[v].begin(), src.var[v].end(), dst.var[v].begin());
+  for (int d = 0; d < 3; ++d) {
+    std::copy(src.eps[d].begin(), src.eps[d].end(), dst.eps[d].begin());
+    std::copy(src.epsf[d].begin(), src.epsf[d].end(), dst.epsf[d].begin());
+  }
+}
+void set_fac(HostLevel& H, int op, double lambda) {
+  const double sum = H.L.idr2[0] + H.L.idr2[1] + H.L.idr2[2];
+  H.L.fac = (op == OP_HELMH) ? 1.0 / (2 * sum + lambda) : 0.5 / sum;
+}
+void link_children(HostLevel& F, int ncf, int nbx, int nby) {   // fine boxes = octants of the coarse boxes, x fastest
+  for (int b = 0; b < F.L.nb; ++b) {
+    const int fx = b % (2 * nbx), fy = (b / (2 * nbx)) % (2 * nby), fz = b / (4 * nbx * nby);
+    F.parent[b] = ((fz / 2) * nby + fy / 2) * nbx + fx / 2;
+    const int h = ncf / 2;
+    F.coff[b] = ((fx & 1) * h) | (((fy & 1) * h) << 10) | (((fz & 1) * h) << 20);
+  }
+}
+
+template <int OP>
+int one_level(int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda, uint64_t seed) {
+  HostLevel G, F;                    // general path / fast kernels
+  build_level(G, nc, nbx, nby, nbz, bc_types, 0.01);
+  build_level(F, nc, nbx, nby, nbz, bc_types, 0.01);
+  ParamsDev P = params(OP, lambda, bc_types, bc_values);
+  set_fac(G, OP, lambda); set_fac(F, OP, lambda);
+  randomise(G, seed);
+  copy_data(F, G);
+  std::vector<int> all(G.L.nb);
+  for (int b = 0; b < G.L.nb; ++b) all[b] = b;
+  G.L.parents_list = F.L.parents_list = all.data(); G.L.n_parents = F.L.n_parents = G.L.nb;
+  int bad = 0;
+  for (int n = 0; n < 4; ++n) {      // two GSRB sweeps
+    for (int b = 0; b < G.L.nb; ++b) do_smooth<OP>(G.L, P, b, n & 1, 0, 1);
+    if (!omgf::smooth(F.L, P, n & 1, true, nullptr, 0, 0, nullptr)) return -1;
+    bad += differing(G, F) ? 1 : 0;
+  }
+  {                                  // a box list (the partition-face / interior split launches subsets)
+    std::vector<int> some;
+    for (int b = 0; b < G.L.nb; b += 2) some.push_back(b);
+    for (int b : some) do_smooth<OP>(G.L, P, b, 0, 0, 1);
+    if (!omgf::smooth(F.L, P, 0, true, some.data(), (int)some.size(), 0, nullptr)) return -1;
+    bad += differing(G, F) ? 1 : 0;
+  }
+  double mg = 0.0, mf = 0.0;         // residual and its maximum
+  for (int b = 0; b < G.L.nb; ++b) mg = fmax(mg, do_resid<OP>(G.L, P, b, 0, 1));
+  if (!omgf::resid_max(F.L, P, true, &mf, nullptr)) return -1;
+  bad += (std::memcmp(&mg, &mf, 8) != 0) + (differing(G, F) ? 1 : 0);
+  for (int b = 0; b < G.L.nb; ++b) do_crhs<OP>(G.L, P, b, 0, 1);   // coarse right-hand side on every box
+  if (!omgf::crhs(F.L, P, true, nullptr)) return -1;
+  bad += differing(G, F) ? 1 : 0;
+  return bad;
+}
+
+template <int OP>
+int two_levels(int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda, uint64_t seed) {
+  HostLevel Gf, Gc, Ff, Fc;
+  build_level(Gf, nc, 2 * nbx, 2 * nby, 2 * nbz, bc_types, 0.01); build_level(Gc, nc, nbx, nby, nbz, bc_types, 0.02);
+  build_level(Ff, nc, 2 * nbx, 2 * nby, 2 * nbz, bc_types, 0.01); build_level(Fc, nc, nbx, nby, nbz, bc_types, 0.02);
+  link_children(Gf, nc, nbx, nby); link_children(Ff, nc, nbx, nby);
+  ParamsDev P = params(OP, lambda, bc_types, bc_values);
+  for (HostLevel* H : {&Gf, &Gc, &Ff, &Fc}) set_fac(*H, OP, lambda);
+  randomise(Gf, seed); randomise(Gc, seed + 17);
+  copy_data(Ff, Gf); copy_data(Fc, Gc);
+  int bad = 0;
+  // update_coarse without its coarse right-hand side: residual + restriction of phi and res
+  for (int b = 0; b < Gf.L.nb; ++b) { do_resid<OP>(Gf.L, P, b, 0, 1); do_restrict(Gf.L, Gc.L, 0, b, 0, 1); do_restrict(Gf.L, Gc.L, 3, b, 0, 1); }
+  if (!omgf::resid_restrict(Ff.L, Fc.L, P, true, nullptr)) return -1;
+  bad += (differing(Gf, Ff) ? 1 : 0) + (differing(Gc, Fc) ? 1 : 0);
+  // correct_children
+  randomise(Gc, seed + 31); copy_data(Fc, Gc);
+  for (int b = 0; b < Gf.L.nb; ++b) do_corr_prolong(Gf.L, Gc.L, P, b, 0, 1);
+  if (!omgf::corr_prolong(Ff.L, Fc.L, P, true, nullptr)) return -1;
+  bad += (differing(Gf, Ff) ? 1 : 0) + (differing(Gc, Fc) ? 1 : 0);
+  return bad;
+}
+
+}  // namespace
+
+extern "C" {
+// mismatching comparisons between the fast kernels and the general path (0 = same bits); -1: a kernel did not apply
+int fe_one_level(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
+                 unsigned long long seed) {
+  switch (op) {
+    case OP_LPL: return one_level<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_VLPL: return one_level<OP_VLPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_HELMH: return one_level<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    default: return one_level<OP_VHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+  }
+}
+int fe_two_levels(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
+                  unsigned long long seed) {
+  switch (op) {
+    case OP_LPL: return two_levels<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_VLPL: return two_levels<OP_VLPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_HELMH: return two_levels<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    default: return two_levels<OP_VHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+  }
+}
+// checks of the emulated TMA / mbarrier / shared-memory rules that failed so far
+int fe_violations() { return emu::g_violations.load(); }
+}

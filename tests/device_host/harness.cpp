@@ -14,20 +14,22 @@
 #include <cuda_runtime.h>   // type definitions only (g++ sees __device__ etc. as attributes it ignores)
 
 // ---- stand-ins for device intrinsics -----------------------------------------------------------------------
+#ifndef OMG_EMU_THREADS   // fast_emu.cpp (the CTA emulator) brings thread-aware versions of these
 struct FakeDim { unsigned x = 0, y = 0, z = 0; };
 static FakeDim threadIdx, blockIdx;
 static FakeDim blockDim = {1, 1, 1};
 static inline void __syncthreads() {}
 static inline double __shfl_xor_sync(unsigned, double v, int) { return v; }
+static inline unsigned long long atomicMax(unsigned long long* a, unsigned long long v) {
+  const unsigned long long o = *a; if (v > o) *a = v; return o;
+}
+#endif
 static inline int __double2hiint(double d) { int64_t b; std::memcpy(&b, &d, 8); return (int)(b >> 32); }
 static inline double __hiloint2double(int hi, int lo) {
   const int64_t b = ((int64_t)hi << 32) | (uint32_t)lo; double d; std::memcpy(&d, &b, 8); return d;
 }
 static inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
 static inline long long __double_as_longlong(double d) { long long b; std::memcpy(&b, &d, 8); return b; }
-static inline unsigned long long atomicMax(unsigned long long* a, unsigned long long v) {
-  const unsigned long long o = *a; if (v > o) *a = v; return o;
-}
 static inline double __ldcg(const double* p) { return *p; }
 
 #include "../../octree-mg_b200/csrc/omg_ops.cuh"
@@ -41,9 +43,9 @@ struct HostLevel {
   std::vector<double> var[4];
   std::vector<double> eps[3], epsf[3];   // variables 5..7 (eps) and their stored ghost faces [box][6][nc*nc]
   std::vector<int> fkind, farg, ftype, fkind_old, farg_old, parent, coff;
-  std::vector<double> bcpl;
+  std::vector<double> bcpl, gpl;
 };
-int g_planes = 0;   // 1: physical faces carry stored planes of boundary values (callbacks / mg_phi_bc_store) instead of constants
+int g_planes = 0;   // 2: physical faces become FK_PLANE ghost planes (as behind refinement / partition boundaries); 1: physical faces carry stored planes of boundary values (callbacks / mg_phi_bc_store) instead of constants
 
 void build_level(HostLevel& H, int nc, int nbx, int nby, int nbz, const int* bc_types, double dr) {
   LevelDev& L = H.L;
@@ -68,7 +70,11 @@ void build_level(HostLevel& H, int nc, int nbx, int nby, int nbz, const int* bc_
       if (q >= 0 && q < ext[d]) { H.fkind[b * 6 + f] = FK_SAME; H.farg[b * 6 + f] = b + ((f & 1) ? stride[d] : -stride[d]); }
       else {
         H.ftype[b * 6 + f] = bc_types[f];
-        if (g_planes) {
+        if (g_planes == 2) {
+          H.fkind[b * 6 + f] = FK_PLANE;
+          H.farg[b * 6 + f] = (int)(H.gpl.size() / ((size_t)nc * nc));
+          for (int t = 0; t < nc * nc; ++t) H.gpl.push_back(0.02 * (double)(((b * 6 + f) * 53 + t * 11) % 89) - 0.7);
+        } else if (g_planes) {
           H.farg[b * 6 + f] = (int)(H.bcpl.size() / ((size_t)nc * nc));
           for (int t = 0; t < nc * nc; ++t) H.bcpl.push_back(0.01 * (double)((b * 6 + f) * 131 + t * 7 % 97) - 0.3);
         }
@@ -76,6 +82,7 @@ void build_level(HostLevel& H, int nc, int nbx, int nby, int nbz, const int* bc_
     }
   }
   L.bcpl = H.bcpl.data();
+  L.gpl = L.gpl_old = H.gpl.data();
   H.fkind_old = H.fkind; H.farg_old = H.farg;
   L.fkind = H.fkind.data(); L.farg = H.farg.data(); L.ftype = H.ftype.data();
   L.fkind_old = H.fkind_old.data(); L.farg_old = H.farg_old.data();

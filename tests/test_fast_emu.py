@@ -1,0 +1,73 @@
+"""CPU tests of the TMA-staged kernels (octree-mg_b200/csrc/omg_fast.cu) through the CTA emulator
+(tests/device_host/fast_emu.cpp).
+
+g++ compiles the kernel source the GPU runs; 256 host threads stand in for a CTA, a TMA bulk copy is a memcpy whose
+alignment, size, destination and mbarrier byte count are checked.  On random levels the fast kernels must reproduce the
+general per-cell path (omg_ops.cuh do_*) bit for bit -- the path test_device_host.py pins to the oracle on the CPU and
+the GPU parity tests pin on the device: GSRB half-sweeps (whole level and box lists), residual + maximum, coarse
+right-hand side, residual fused with restriction, correction fused with prolongation; box size 16 (whole-box tiles)
+and 32 (four slabs per box); Laplacian, Helmholtz and their variable-coefficient forms; every boundary-condition type
+as a constant, as stored planes, and ghost planes (refinement / partition boundaries)."""
+import ctypes as C
+import os
+import subprocess
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+DH = os.path.join(HERE, "device_host")
+LIB = os.path.join(DH, "libfastemu.so")
+CSRC = os.path.join(os.path.dirname(HERE), "octree-mg_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    deps = [os.path.join(DH, "fast_emu.cpp"), os.path.join(DH, "harness.cpp")] + \
+           [os.path.join(CSRC, f) for f in ("omg_device.cuh", "omg_ops.cuh", "omg_fast.cu", "omg_fast.h")]
+    if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
+        cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+        subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-std=c++17", "-fPIC", "-shared", "-w", "-pthread",
+                               "-I" + cuda_inc, os.path.join(DH, "fast_emu.cpp"), "-o", LIB])
+    L = C.CDLL(LIB)
+    for f in (L.fe_one_level, L.fe_two_levels):
+        f.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
+    L.dh_set_planes.argtypes = [C.c_int]
+    return L
+
+
+BC_SETS = [[-10] * 6, [-11] * 6, [-12, -12, -10, -10, -11, -11], [-10, -11, -12, -10, -11, -12]]
+BC_VALUES = [0.3, -0.7, 1.1, 0.0, 2.0, -1.5]
+OPS = [(1, 0.0), (2, 0.0), (3, 2.5), (4, 0.75)]      # mg_laplacian, mg_vlaplacian, mg_helmholtz, mg_vhelmholtz
+
+
+def six(ctype, values):
+    return (ctype * 6)(*values)
+
+
+@pytest.mark.parametrize("planes", [0, 1, 2])        # boundary constants / stored boundary planes / ghost planes
+@pytest.mark.parametrize("op,lam", OPS)
+@pytest.mark.parametrize("nc", [16, 32])
+def test_fast_kernels_match_general_path_on_one_level(emu, nc, op, lam, planes):
+    emu.dh_set_planes(planes)
+    try:
+        for types, shape in zip(BC_SETS, [(2, 2, 1), (1, 2, 2), (2, 1, 2), (3, 1, 1)]):
+            bad = emu.fe_one_level(op, nc, *shape, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 13 * nc + op)
+            assert bad == 0, (types, shape)
+        assert emu.fe_violations() == 0
+    finally:
+        emu.dh_set_planes(0)
+
+
+@pytest.mark.parametrize("planes", [0, 1, 2])
+@pytest.mark.parametrize("op,lam", OPS)
+@pytest.mark.parametrize("nc", [16, 32])
+def test_fast_transfer_kernels_match_general_path(emu, nc, op, lam, planes):
+    """update_coarse's residual + restriction and correct_children on a coarse level and the level of its octants"""
+    emu.dh_set_planes(planes)
+    try:
+        for types, shape in zip(BC_SETS[2:], [(1, 1, 1), (2, 1, 1)]):
+            bad = emu.fe_two_levels(op, nc, *shape, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 5 * nc + op)
+            assert bad == 0, (types, shape)
+        assert emu.fe_violations() == 0
+    finally:
+        emu.dh_set_planes(0)
