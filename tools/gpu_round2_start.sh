@@ -17,6 +17,11 @@ for OP in vlaplacian vhelmholtz; do
 done
 # programmatic dependent launch of the TMA-staged kernels (option pdl, gated): effect on the default bench
 timeout 600 python bench.py --no-cpu-baseline --no-e2e --opt pdl=1 > gpurun_out/bench_r2_pdl.json 2> gpurun_out/bench_r2_pdl.err
+# the tail got 2.4x faster after the tail_cells sweep of pass c: does a larger tail pay now?
+for TC in 32768; do
+  timeout 600 python bench.py --no-cpu-baseline --no-e2e --opt tail_cells=$TC > gpurun_out/bench_r2_tc$TC.json 2> gpurun_out/bench_r2_tc$TC.err
+  timeout 600 python bench.py --no-cpu-baseline --no-e2e --opt tail_cells=$TC --opt pdl=1 > gpurun_out/bench_r2_tc${TC}_pdl.json 2> gpurun_out/bench_r2_tc${TC}_pdl.err
+done
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_r2.csv $CMD > gpurun_out/ncu_list_r2.log 2>&1
 python - <<'PY'
