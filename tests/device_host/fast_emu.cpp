@@ -70,7 +70,10 @@ static inline void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t
   std::memcpy(dst, src, bytes);
   emu::g_tx_done += bytes;
 }
-static inline void wait_flag(const volatile unsigned long long*, unsigned long long, int*) {}
+// the emulated ranks run one after the other, so a flag a kernel would wait for must already be there
+static inline void wait_flag(const volatile unsigned long long* f, unsigned long long want, int*) {
+  if (*f < want) emu::violation("wait_flag: the peer's signal is missing (the GPU would time out)");
+}
 #define OMG_DYN_SMEM(name, al) unsigned char* name = emu::g_smem
 #define OMG_PDL_ASM() do {} while (0)
 #define OMG_LAUNCH(kern, grid, smem, stream, ...) emu::launch((grid), (smem), [&]() { kern(__VA_ARGS__); })
@@ -188,9 +191,135 @@ int two_levels(int nc, int nbx, int nby, int nbz, const int* bc_types, const dou
   return bad;
 }
 
+
+// ---- the in-kernel halo exchange (PutDev) between emulated ranks -------------------------------------------------------
+// A brick of boxes is cut into n_ranks contiguous chunks of the x-fastest box order.  Every rank gets its own level
+// (faces towards another rank are FK_PLANE entries of its double-buffered plane pool), the PutDev tables the library
+// builds in sync_meta (omg_core.cu) and plain pointers to the other ranks' pools and flags where the GPU has peer
+// mappings.  The ranks run each half-sweep one after the other; the state must follow the single-rank general path.
+struct RankLevel {
+  HostLevel H;
+  std::vector<int> gid, slot_of, ptr, item, launch;
+  std::vector<double> pool;
+  std::vector<unsigned long long> flags;
+  unsigned long long epoch = 0;
+  unsigned int done = 0;
+  int err = 0, n_planes = 0;
+  std::vector<double*> peer_base; std::vector<long long> peer_stride; std::vector<unsigned long long*> peer_flags;
+};
+
+template <int OP>
+int ranks_case(int nc, int nbx, int nby, int nbz, int n_ranks, int bnd_first, const int* bc_types, const double* bc_values,
+               double lambda, uint64_t seed) {
+  const int nb = nbx * nby * nbz;
+  HostLevel G;
+  build_level(G, nc, nbx, nby, nbz, bc_types, 0.01);
+  ParamsDev P = params(OP, lambda, bc_types, bc_values);
+  set_fac(G, OP, lambda);
+  randomise(G, seed);
+  auto owner = [&](int b) { return (int)((long long)b * n_ranks / nb); };
+  std::vector<RankLevel> R(n_ranks);
+  std::vector<int> local_of(nb);
+  for (int b = 0; b < nb; ++b) { RankLevel& r = R[owner(b)]; local_of[b] = (int)r.gid.size(); r.gid.push_back(b); }
+  struct Send { int box, f, to, plane; };
+  std::vector<std::vector<Send>> sends(n_ranks);
+  const int save_planes = g_planes; g_planes = 0;
+  for (int me = 0; me < n_ranks; ++me) {
+    RankLevel& r = R[me];
+    const int nl = (int)r.gid.size();
+    if (nl == 0) { g_planes = save_planes; return -2; }
+    build_level(r.H, nc, nl, 1, 1, bc_types, 0.01);
+    set_fac(r.H, OP, lambda);
+    for (int lb = 0; lb < nl; ++lb) {
+      const int g = r.gid[lb];
+      const int pos[3] = {g % nbx, (g / nbx) % nby, g / (nbx * nby)}, ext[3] = {nbx, nby, nbz}, stride[3] = {1, nbx, nbx * nby};
+      for (int f = 0; f < 6; ++f) {
+        const int d = f >> 1, q = pos[d] + ((f & 1) ? 1 : -1);
+        int& kind = r.H.fkind[lb * 6 + f]; int& arg = r.H.farg[lb * 6 + f];
+        r.H.ftype[lb * 6 + f] = 0;
+        if (q < 0 || q >= ext[d]) { kind = FK_PHYS; arg = -1; r.H.ftype[lb * 6 + f] = bc_types[f]; continue; }
+        const int ng = g + ((f & 1) ? stride[d] : -stride[d]);
+        if (owner(ng) == me) { kind = FK_SAME; arg = local_of[ng]; }
+        else { kind = FK_PLANE; arg = r.n_planes; sends[owner(ng)].push_back({local_of[ng], f, me, r.n_planes}); ++r.n_planes; }
+      }
+      for (int v = 0; v < 4; ++v)
+        std::copy(G.var[v].begin() + (size_t)g * G.L.bs, G.var[v].begin() + (size_t)(g + 1) * G.L.bs, r.H.var[v].begin() + (size_t)lb * G.L.bs);
+      std::copy(G.eps[0].begin() + (size_t)g * G.L.bs, G.eps[0].begin() + (size_t)(g + 1) * G.L.bs, r.H.eps[0].begin() + (size_t)lb * G.L.bs);
+      std::copy(G.epsf[0].begin() + (size_t)g * 6 * nc * nc, G.epsf[0].begin() + (size_t)(g + 1) * 6 * nc * nc, r.H.epsf[0].begin() + (size_t)lb * 6 * nc * nc);
+    }
+    r.H.fkind_old = r.H.fkind; r.H.farg_old = r.H.farg;
+    r.H.L.fkind_old = r.H.fkind_old.data(); r.H.L.farg_old = r.H.farg_old.data();
+    r.pool.assign((size_t)2 * std::max(1, r.n_planes) * nc * nc, -7.0);
+    r.flags.assign(n_ranks, 0ull);
+  }
+  g_planes = save_planes;
+  for (int me = 0; me < n_ranks; ++me) {
+    RankLevel& r = R[me];
+    const int nl = (int)r.gid.size();
+    LevelDev& L = r.H.L;
+    L.gpl = L.gpl_old = r.pool.data(); L.gpl_stride = (long long)std::max(1, r.n_planes) * nc * nc; L.gpl_sel = &r.epoch;
+    // partition-face boxes and their items, as sync_meta lays them out
+    r.slot_of.assign(nl, -1); r.ptr.assign(1, 0);
+    std::vector<int> bnd;
+    for (const Send& s : sends[me]) if (r.slot_of[s.box] < 0) { r.slot_of[s.box] = (int)bnd.size(); bnd.push_back(s.box); }
+    for (int lb : bnd) {
+      for (const Send& s : sends[me]) if (s.box == lb) { r.item.push_back(s.f); r.item.push_back(s.to); r.item.push_back(s.plane); }
+      r.ptr.push_back((int)r.item.size() / 3);
+    }
+    for (int lb : bnd) r.launch.push_back(lb);
+    for (int lb = 0; lb < nl; ++lb) if (r.slot_of[lb] < 0) r.launch.push_back(lb);
+    PutDev& U = L.put;
+    std::memset(&U, 0, sizeof(U));
+    U.n_bnd = (int)bnd.size(); U.me = me; U.nranks = n_ranks; U.channel = 0;
+    std::vector<int> peers;
+    for (const Send& s : sends[me]) if (std::find(peers.begin(), peers.end(), s.to) == peers.end()) peers.push_back(s.to);
+    if (peers.size() > 8) return -3;
+    U.n_peers = (int)peers.size();
+    for (int q = 0; q < U.n_peers; ++q) U.peers[q] = peers[q];
+    for (int q = 0; q < n_ranks; ++q) { r.peer_base.push_back(R[q].pool.data()); r.peer_stride.push_back((long long)std::max(1, R[q].n_planes) * nc * nc); r.peer_flags.push_back(R[q].flags.data()); }
+    U.slot_of = r.slot_of.data(); U.ptr = r.ptr.data(); U.item = r.item.data();
+    U.peer_base = r.peer_base.data(); U.peer_stride = r.peer_stride.data(); U.peer_flags = r.peer_flags.data();
+    U.flags = r.flags.data(); U.epoch = &r.epoch; U.done = &r.done; U.err = &r.err;
+  }
+  // the exchange that precedes the first fused half-sweep (S_HALO): current faces into copy epoch & 1 = 0 of the pools
+  for (int me = 0; me < n_ranks; ++me)
+    for (const Send& s : sends[me]) {
+      const int g = R[me].gid[s.box], layer = (s.f & 1) ? 0 : nc - 1;
+      double* o = R[s.to].pool.data() + (size_t)s.plane * nc * nc;
+      for (int t2 = 0; t2 < nc; ++t2) for (int t1 = 0; t1 < nc; ++t1) {
+        const int i = s.f < 2 ? layer : t1, j = s.f < 2 ? t1 : (s.f < 4 ? layer : t2), k = s.f < 4 ? t2 : layer;
+        o[t2 * nc + t1] = G.var[0][(size_t)g * G.L.bs + cidx(G.L, i, j, k)];
+      }
+    }
+  int bad = 0;
+  for (int n = 0; n < 4; ++n) {
+    for (int b = 0; b < nb; ++b) do_smooth<OP>(G.L, P, b, n & 1, 0, 1);
+    for (int me = 0; me < n_ranks; ++me) {
+      RankLevel& r = R[me];
+      if (!omgf::smooth(r.H.L, P, n & 1, true, bnd_first ? r.launch.data() : nullptr, r.H.L.nb, 1, nullptr)) return -1;
+      if (r.epoch != (unsigned long long)(n + 1) && r.H.L.put.n_bnd > 0) ++bad;      // the last partition-face CTA bumps the epoch
+      if (r.err) ++bad;
+    }
+    for (int me = 0; me < n_ranks; ++me)
+      for (size_t lb = 0; lb < R[me].gid.size(); ++lb)
+        bad += std::memcmp(&R[me].H.var[0][lb * G.L.bs], &G.var[0][(size_t)R[me].gid[lb] * G.L.bs], sizeof(double) * G.L.bs) != 0;
+  }
+  return bad;
+}
+
 }  // namespace
 
 extern "C" {
+// fused half-sweeps with the in-kernel exchange on n_ranks emulated ranks against the single-rank general path
+int fe_ranks(int op, int nc, int nbx, int nby, int nbz, int n_ranks, int bnd_first, const int* bc_types, const double* bc_values,
+             double lambda, unsigned long long seed) {
+  switch (op) {
+    case OP_LPL: return ranks_case<OP_LPL>(nc, nbx, nby, nbz, n_ranks, bnd_first, bc_types, bc_values, lambda, seed);
+    case OP_VLPL: return ranks_case<OP_VLPL>(nc, nbx, nby, nbz, n_ranks, bnd_first, bc_types, bc_values, lambda, seed);
+    case OP_HELMH: return ranks_case<OP_HELMH>(nc, nbx, nby, nbz, n_ranks, bnd_first, bc_types, bc_values, lambda, seed);
+    default: return ranks_case<OP_VHELMH>(nc, nbx, nby, nbz, n_ranks, bnd_first, bc_types, bc_values, lambda, seed);
+  }
+}
 // mismatching comparisons between the fast kernels and the general path (0 = same bits); -1: a kernel did not apply
 int fe_one_level(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
                  unsigned long long seed) {

@@ -71,3 +71,18 @@ def test_fast_transfer_kernels_match_general_path(emu, nc, op, lam, planes):
         assert emu.fe_violations() == 0
     finally:
         emu.dh_set_planes(0)
+
+
+@pytest.mark.parametrize("op,lam", OPS)
+@pytest.mark.parametrize("nc", [16, 32])
+def test_in_kernel_halo_exchange_between_emulated_ranks(emu, nc, op, lam):
+    """the smoother's in-kernel exchange (PutDev: partition-face boxes store their fresh face layers into the neighbour
+    ranks' double-buffered plane pools, the last such CTA signals and bumps the epoch) with the
+    ranks' pools and flags as plain host pointers: four fused half-sweeps on 2, 3 and 4 emulated ranks follow the
+    single-rank general path bit for bit, in box order and with the partition-face boxes launched first"""
+    emu.fe_ranks.argtypes = [C.c_int] * 7 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
+    for types, shape, n_ranks in zip(BC_SETS, [(2, 2, 2), (3, 2, 2), (2, 2, 1), (1, 2, 3)], [2, 3, 4, 2]):
+        for bnd_first in (0, 1):
+            bad = emu.fe_ranks(op, nc, *shape, n_ranks, bnd_first, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 3 * nc + op)
+            assert bad == 0, (types, shape, n_ranks, bnd_first)
+    assert emu.fe_violations() == 0
