@@ -26,7 +26,8 @@ def emu():
            [os.path.join(CSRC, f) for f in ("omg_device.cuh", "omg_ops.cuh", "omg_fast.cu", "omg_fast.h")]
     if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
-        subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-std=c++17", "-fPIC", "-shared", "-w", "-pthread",
+        # -Bsymbolic: the emulator's omgf::* must not be interposed by libomg_b200.so when other tests loaded it first
+        subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-std=c++17", "-fPIC", "-shared", "-w", "-pthread", "-Wl,-Bsymbolic",
                                "-I" + cuda_inc, os.path.join(DH, "fast_emu.cpp"), "-o", LIB])
     L = C.CDLL(LIB)
     for f in (L.fe_one_level, L.fe_two_levels):
@@ -81,7 +82,8 @@ def test_in_kernel_halo_exchange_between_emulated_ranks(emu, nc, op, lam):
     ranks' pools and flags as plain host pointers: four fused half-sweeps on 2, 3 and 4 emulated ranks follow the
     single-rank general path bit for bit, in box order and with the partition-face boxes launched first"""
     emu.fe_ranks.argtypes = [C.c_int] * 7 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
-    for types, shape, n_ranks in zip(BC_SETS, [(2, 2, 2), (3, 2, 2), (2, 2, 1), (1, 2, 3)], [2, 3, 4, 2]):
+    cases = list(zip(BC_SETS, [(2, 2, 2), (3, 2, 2), (2, 2, 1), (1, 2, 3)], [2, 3, 4, 2]))
+    for types, shape, n_ranks in (cases if nc == 16 else cases[1:3]):   # box 32: four slabs per box, fewer cases
         for bnd_first in (0, 1):
             bad = emu.fe_ranks(op, nc, *shape, n_ranks, bnd_first, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 3 * nc + op)
             assert bad == 0, (types, shape, n_ranks, bnd_first)
