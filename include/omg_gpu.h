@@ -155,7 +155,14 @@ int omg_exchange_plan(const omg_tree_desc* t, int me, int phase, int lvl, int pe
 int omg_sync(omg_handle* h);                                          /* cudaStreamSynchronize */
 int omg_timers(omg_handle* h, int* n, const char** names, double* seconds);  /* mg_timers_show */
 int64_t omg_stat(omg_handle* h, const char* key);                     /* "launches", "bytes_h2d", ... */
-int omg_set_option(omg_handle* h, const char* key, int value);        /* "use_graph", "fast_kernels", ... */
+/* Tuning / diagnostic switches (defaults in brackets); none changes results:
+ *   "use_graph" [1] CUDA graph per cycle program, "graph_multi" [1] also with several ranks, "fast_kernels" [1] TMA-staged
+ *   kernels where they apply, "tail_cells" [4096] levels up to this many cells run in the single-CTA tail, "tail_smem" [1]
+ *   tail levels staged in shared memory, "tail_simple" [1; 2 = also plane boundaries / variable coefficients, host-verified
+ *   only so far], "overlap" [1] halo exchange overlapped with interior boxes, "p2p" / "fused" [1] peer-mapped puts / issued
+ *   from inside the smoother, "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; unmeasured),
+ *   "profile" [0] per-kernel-class CUDA-event timing (omg_last_ms). */
+int omg_set_option(omg_handle* h, const char* key, int value);
 /* CUDA-event timing of the last omg_fas_vcycles call (ms), and of one kernel class inside it */
 double omg_last_ms(omg_handle* h, const char* what);
 void* omg_stream(omg_handle* h);                                       /* cudaStream_t used by the handle */
