@@ -150,6 +150,9 @@ def main():
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the TOTAL domain at n^3 (BASELINE.json configs[4]: 1024^3 "
                     "strong scaling) instead of n^3 per GPU")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (omg_set_option), repeatable")
+    ap.add_argument("--trace", default=None, metavar="PREFIX",
+                    help="after the measurement: run 2 V-cycles with option trace and write the per-step timeline of every rank "
+                         "to PREFIX.rank<r>.json (diagnostic; not part of any reported number)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -267,6 +270,19 @@ def main():
     n_sm = int(G.omg_last_ms(gpu, b"n_smooth"))
     prof = {k: float(G.omg_last_ms(gpu, k.encode())) for k in ("smooth", "resid_restrict", "corr_prolong", "resid")}
     mg.set_option("profile", 0)
+    if args.trace:
+        mg.set_option("trace", 1)
+        mg.fas_vcycles(2)
+        steps_tr = mg.trace()
+        mg.set_option("trace", 0)
+        by = {}
+        for name, lvl, a, b, t in steps_tr:
+            k = "%s@%d" % (name, lvl)
+            by[k] = [by.get(k, [0.0, 0])[0] + t, by.get(k, [0.0, 0])[1] + 1]
+        with open("%s.rank%d.json" % (args.trace, rank), "w") as f:
+            json.dump({"cycles": 2, "total_ms": sum(t for *_, t in steps_tr),
+                       "by_step_ms": {k: [round(v[0], 4), v[1]] for k, v in sorted(by.items(), key=lambda kv: -kv[1][0])},
+                       "steps": [[n_, l_, a_, b_, round(t_, 4)] for n_, l_, a_, b_, t_ in steps_tr]}, f)
     peak, peak_src = peaks()
     traffic, traffic_src = ncu_traffic(args.n, args.box)
     cells_per_rank = dof / world

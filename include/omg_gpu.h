@@ -161,8 +161,13 @@ int64_t omg_stat(omg_handle* h, const char* key);                     /* "launch
  *   tail levels staged in shared memory, "tail_simple" [1; 2 = also plane boundaries / variable coefficients, host-verified
  *   only so far], "overlap" [1] halo exchange overlapped with interior boxes, "p2p" / "fused" [1] peer-mapped puts / issued
  *   from inside the smoother, "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; unmeasured),
- *   "profile" [0] per-kernel-class CUDA-event timing (omg_last_ms). */
+ *   "profile" [0] per-kernel-class CUDA-event timing (omg_last_ms), "trace" [0] per-step timeline (omg_trace). */
 int omg_set_option(omg_handle* h, const char* key, int value);
+/* Per-step timeline (option "trace" = 1: every step of the cycle programs timed with its own CUDA-event pair, no graph,
+ * in-kernel exchange left on): rec[i] = {step kind, level, a, b}, ms[i]; at most cap records are written, *n = number
+ * recorded since the option was set or the last call; omg_step_name names a step kind. */
+int omg_trace(omg_handle* h, int cap, int* rec, double* ms, int* n);
+const char* omg_step_name(int kind);
 /* CUDA-event timing of the last omg_fas_vcycles call (ms), and of one kernel class inside it */
 double omg_last_ms(omg_handle* h, const char* what);
 void* omg_stream(omg_handle* h);                                       /* cudaStream_t used by the handle */

@@ -117,6 +117,9 @@ def _declare(G, H):
     G.omg_stat.restype = C.c_int64
     G.omg_stat.argtypes = [vp, C.c_char_p]
     G.omg_set_option.argtypes = [vp, C.c_char_p, ci]
+    G.omg_trace.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int)]
+    G.omg_step_name.restype = C.c_char_p
+    G.omg_step_name.argtypes = [C.c_int]
     G.omg_last_ms.restype = cd
     G.omg_last_ms.argtypes = [vp, C.c_char_p]
     G.omg_stream.restype = vp
@@ -479,6 +482,15 @@ class Mg:
         res = (C.c_double * max(n, 1))()
         self._gck(self.G.omg_fas_vcycles(self.gpu, n, res if want_res else None))
         return (list(res[:n]) if want_res else None), float(self.G.omg_last_ms(self.gpu, b"cycles"))
+
+    def trace(self, cap=100000):
+        """steps recorded since set_option("trace", 1): list of (name, lvl, a, b, ms)"""
+        rec = (C.c_int * (4 * cap))()
+        ms = (C.c_double * cap)()
+        n = C.c_int(0)
+        self._gck(self.G.omg_trace(self.gpu, cap, rec, ms, C.byref(n)))
+        return [(self.G.omg_step_name(rec[4 * i]).decode(), rec[4 * i + 1], rec[4 * i + 2], rec[4 * i + 3], ms[i])
+                for i in range(min(n.value, cap))]
 
     def sync(self):
         self._gck(self.G.omg_sync(self.gpu))

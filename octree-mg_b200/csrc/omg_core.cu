@@ -146,6 +146,11 @@ struct omg_handle {
   double timer_acc[7] = {0, 0, 0, 0, 0, 0, 0};
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> total_events;   // (timer index, events) not yet read
   std::map<int, std::pair<double, int64_t>> prof_acc;   // step kind -> (ms, launches)
+  // option "trace": every step of every program run timed with its own event pair, cycle programs unchanged (the in-kernel
+  // exchange stays on, unlike "profile"); read with omg_trace
+  int trace = 0;
+  struct TraceRec { int kind, l, a, b; cudaEvent_t e0, e1; };
+  std::vector<TraceRec> trace_events;
 
   LevelHost& L(int lvl) { return levels[lvl - lowest]; }
 };
@@ -715,6 +720,8 @@ void exec_steps(omg_handle* h, Program& P) {
                       st.kind != S_ZERO_PHI && st.kind != S_HALO_FORK && st.kind != S_HALO_JOIN;
     cudaEvent_t pe0 = nullptr, pe1 = nullptr;
     if (prof) { CK(cudaEventCreate(&pe0)); CK(cudaEventCreate(&pe1)); CK(cudaEventRecord(pe0, s)); }
+    cudaEvent_t te0 = nullptr, te1 = nullptr;
+    if (h->trace) { CK(cudaEventCreate(&te0)); CK(cudaEventCreate(&te1)); CK(cudaEventRecord(te0, s)); }
     switch (st.kind) {
       case S_SMOOTH: {
         LevelHost& L = h->L(st.l);
@@ -807,6 +814,7 @@ void exec_steps(omg_handle* h, Program& P) {
       default: fail("exec_steps: unknown step");
     }
     if (prof) { CK(cudaEventRecord(pe1, s)); h->prof_events.push_back({st.kind * 2 + (st.kind != S_TAIL && st.l == h->highest ? 1 : 0), {pe0, pe1}}); }
+    if (h->trace) { CK(cudaEventRecord(te1, s)); h->trace_events.push_back({st.kind, st.l, st.a, st.b, te0, te1}); }
   }
   CK(cudaGetLastError());
 }
@@ -816,7 +824,7 @@ void run_program(omg_handle* h, Program& P) {
     P.d_ops.upload(P.ops, h->stream);
     CK(cudaStreamSynchronize(h->stream));
   }
-  const bool graph_ok = h->use_graph && !h->profile && (h->n_cpu == 1 || (h->comm && h->graph_multi && omg_comm_graph_safe(h->comm)));
+  const bool graph_ok = h->use_graph && !h->profile && !h->trace && (h->n_cpu == 1 || (h->comm && h->graph_multi && omg_comm_graph_safe(h->comm)));
   if (!graph_ok) { exec_steps(h, P); return; }
   if (!P.graph) {
     cudaGraph_t g = nullptr;
@@ -1138,6 +1146,8 @@ int omg_destroy(omg_handle* h) {
   cudaStreamSynchronize(h->stream);
   if (h->comm) omg_comm_destroy(h->comm);
   try { drain_totals(h, true); collect_profile(h); free_levels(h); } catch (...) {}
+  for (auto& r : h->trace_events) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  h->trace_events.clear();
   h->d_scal.free(); h->d_partial.free(); h->d_epoch.free();
   for (int q = 0; q < 2; ++q) {
     if (h->h_stage[q]) cudaFreeHost(h->h_stage[q]);
@@ -1525,6 +1535,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "tail_simple") { h->tail_simple = value; h->params_dirty = true; }
     else if (k == "overlap") h->overlap = value;
     else if (k == "pdl") h->pdl = value;
+    else if (k == "trace") { h->trace = value; for (auto& r : h->trace_events) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); } h->trace_events.clear(); }
     else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
     else if (k == "fused") { h->fused = value; h->params_dirty = true; }
     else if (k == "bnd_first_boxes") h->bnd_first_boxes = value;
@@ -1552,6 +1563,32 @@ double omg_last_ms(omg_handle* h, const char* what) {
   auto it = h->prof_acc.find(kind);
   if (it == h->prof_acc.end() || it->second.second == 0) return count ? 0.0 : -1.0;
   return count ? (double)it->second.second : it->second.first / (double)it->second.second;
+}
+// Steps recorded since option "trace" was set: rec[i] = {step kind, level, a, b}, ms[i] = elapsed time of the step on the
+// cycle's stream (steps that fork to the exchange stream show their issue cost; the join shows the wait).  At most cap
+// records are written, *n receives the number available; the record list is cleared.
+int omg_trace(omg_handle* h, int cap, int* rec, double* ms, int* n) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    int i = 0;
+    for (auto& r : h->trace_events) {
+      if (i < cap && rec && ms) {
+        float t = 0; CK(cudaEventElapsedTime(&t, r.e0, r.e1));
+        rec[4 * i] = r.kind; rec[4 * i + 1] = r.l; rec[4 * i + 2] = r.a; rec[4 * i + 3] = r.b; ms[i] = t;
+      }
+      cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+      ++i;
+    }
+    if (n) *n = i;
+    h->trace_events.clear();
+  });
+}
+const char* omg_step_name(int kind) {
+  static const char* names[] = {"smooth", "resid", "restrict", "crhs", "oldpl", "corr_prolong", "rb_fill", "copy_old", "coarse_solve",
+                                "tail", "zero_phi", "submean", "clear_slot", "copy_slot", "halo", "xrestrict", "xprolong", "allreduce_max",
+                                "resid_restrict", "halo_fork", "halo_join", "put_wait"};
+  return (kind >= 0 && kind < (int)(sizeof(names) / sizeof(names[0]))) ? names[kind] : "?";
 }
 void* omg_stream(omg_handle* h) { return h ? (void*)h->stream : nullptr; }
 

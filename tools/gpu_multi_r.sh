@@ -6,7 +6,7 @@ for N in "$@"; do
   for MODE in weak strong; do
     EXTRA=""; [ $MODE = strong ] && EXTRA="--strong --cells 1024"
     timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 \
-      bench.py --gpus $N --steps 10 --warmup 3 $EXTRA > gpurun_out/bench_n${N}_${MODE}.json 2> gpurun_out/bench_n${N}_${MODE}.err
+      bench.py --gpus $N --steps 10 --warmup 3 $EXTRA --trace gpurun_out/trace_n${N}_${MODE} > gpurun_out/bench_n${N}_${MODE}.json 2> gpurun_out/bench_n${N}_${MODE}.err
     echo "N=$N $MODE rc=$?"; python - <<PY
 import json
 try:
@@ -14,6 +14,14 @@ try:
     print(d['n_gpus'], d['scaling'], round(d['value'],2), 'GDOF/s', round(d['ms_per_step'],3), 'ms', d['launches_per_step'], d['config']['domain'], d['max_res_after'], 'e2e', d['e2e'] and round(d['e2e']['value'],2))
 except Exception as e:
     print('FAILED', e)
+PY
+    python - <<PY
+import json
+try:
+    t=json.load(open('gpurun_out/trace_n${N}_${MODE}.rank0.json'))
+    print('  trace rank 0: %.3f ms per cycle;' % (t['total_ms'] / t['cycles']), ', '.join('%s %.3f' % (k, v[0] / t['cycles']) for k, v in list(t['by_step_ms'].items())[:8]))
+except Exception as e:
+    print('  no trace', e)
 PY
     grep -v "OMP_NUM_THREADS\|^\*\*\*\|destroy_process_group" gpurun_out/bench_n${N}_${MODE}.err | tail -3
   done
