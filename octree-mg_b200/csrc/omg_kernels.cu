@@ -4,14 +4,7 @@
 #include "omg_kernels.h"
 #include "omg_ops.cuh"
 
-#define OMG_SWITCH_OP(op, CALL)                      \
-  switch (op) {                                      \
-    case OP_LPL: { constexpr int OP = OP_LPL; CALL; } break;       \
-    case OP_VLPL: { constexpr int OP = OP_VLPL; CALL; } break;     \
-    case OP_HELMH: { constexpr int OP = OP_HELMH; CALL; } break;   \
-    case OP_VHELMH: { constexpr int OP = OP_VHELMH; CALL; } break; \
-    default: { constexpr int OP = OP_AHELMH; CALL; } break;        \
-  }
+#include "omg_tail.cuh"
 
 namespace {
 constexpr int kThreads = 256;
@@ -213,168 +206,6 @@ __global__ void k_final_sum(const double* partial, int n, double* acc) {
   if (threadIdx.x == 0) *acc = *acc + sm[0];
 }
 __global__ void k_scale_scalar(double* acc, double inv_volume) { *acc = *acc / inv_volume; }
-
-// ------------------------------------------------------------------ tail interpreter ---------
-template <int OP>
-__device__ void tail_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
-  if (L.simple && P.smoother == 2) {
-    simple_smooth<OP>(L, P, colour, tid, nthr);
-  } else if (P.smoother == 1) {   // mg_smoother_gs
-    for (int b = 0; b < L.nb; ++b) do_gs_snapshot(L, P, b, tid, nthr);
-    __syncthreads();
-    for (int b = 0; b < L.nb; ++b) do_gs_sweep<OP>(L, P, b, tid, nthr);
-  } else if (L.nc & 1) {   // odd box size: Jacobi between boxes, see do_smooth_staged
-    for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 0, tid, nthr);
-    __syncthreads();
-    for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 1, tid, nthr);
-  } else {
-    for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, colour, tid, nthr);
-  }
-}
-
-template <int OP>
-__device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailOp* __restrict__ ops, int n_ops,
-                         double* scal, double* red) {
-  const int tid = threadIdx.x, nthr = blockDim.x;
-  for (int o = 0; o < n_ops; ++o) {
-    const TailOp op = ops[o];
-    const LevelDev& L = levels[op.l];
-    // boxes between physical boundaries and local neighbours: neighbour gathers without
-    // per-cell face classification (omg_ops.cuh)
-    const bool fast = L.simple && P.smoother == 2;
-    switch (op.type) {
-      case TOP_SMOOTH:
-        tail_smooth<OP>(L, P, op.a, tid, nthr);
-        break;
-      case TOP_RESID: {
-        double m = 0.0;
-        if (fast) m = simple_resid<OP>(L, P, tid, nthr);
-        else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
-        if (op.a >= 0) { m = block_max(m, red); if (tid == 0) atomic_max_nonneg(&scal[op.a], m); }
-      } break;
-      case TOP_RESTRICT: {
-        const LevelDev& Lc = levels[op.l - 1];
-        for (int b = 0; b < L.nb; ++b) { do_restrict(L, Lc, op.a, b, tid, nthr); if (op.b >= 0) do_restrict(L, Lc, op.b, b, tid, nthr); }
-      } break;
-      case TOP_CRHS:
-        if (fast) for (int q = 0; q < L.n_parents; ++q) simple_crhs<OP>(L, P, L.parents_list[q], tid, nthr);
-        else for (int q = 0; q < L.n_parents; ++q) do_crhs<OP>(L, P, L.parents_list[q], tid, nthr);
-        break;
-      case TOP_OLDPL:
-        for (int e = 0; e < L.n_oldpl; ++e) do_oldpl(L, P, e, tid, nthr);
-        break;
-      case TOP_CORR_PROLONG: {
-        const LevelDev& Lc = levels[op.l - 1];
-        if (fast && Lc.simple) for (int b = 0; b < L.nb; ++b) simple_corr_prolong(L, Lc, P, b, tid, nthr);
-        else for (int b = 0; b < L.nb; ++b) do_corr_prolong(L, Lc, P, b, tid, nthr);
-      } break;
-      case TOP_RB_FILL: {
-        const LevelDev& Lc = levels[op.l - 1];
-        for (int e = 0; e < L.n_rb; ++e) {
-          if (op.a) do_rb_fill<GM_PHI_GZ>(L, Lc, P, 0, e, tid, nthr); else do_rb_fill<GM_PHI>(L, Lc, P, 0, e, tid, nthr);
-        }
-      } break;
-      case TOP_COPY_OLD:
-        for (size_t i = tid; i < (size_t)L.nb * L.bs; i += nthr) L.var[2][i] = L.var[0][i];
-        break;
-      case TOP_COARSE_SOLVE: {
-        // coarse loop of mg_fas_vcycle, src/m_multigrid.f90:202-208
-        double m = 0.0;
-        if (fast) m = simple_resid<OP>(L, P, tid, nthr);
-        else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
-        const double init_res = block_max(m, red);
-        int it = 0;
-        for (int i = 1; i <= op.b; ++i) {
-          for (int n = 1; n <= op.a; ++n) {
-            tail_smooth<OP>(L, P, (n - 1) & 1, tid, nthr);
-            __syncthreads();
-          }
-          m = 0.0;
-          if (fast) m = simple_resid<OP>(L, P, tid, nthr);
-          else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
-          const double res = block_max(m, red);
-          it = i;
-          if (res < scal[SCAL_COARSE_REL] * init_res || res < scal[SCAL_COARSE_ABS]) break;
-        }
-        if (tid == 0) scal[SCAL_COARSE_ITERS] = (double)it;
-      } break;
-      default: break;
-    }
-    __syncthreads();
-  }
-}
-
-// The tail levels are tiny (<= tail_cells cells each), so when phi, rhs, old and res of ALL of them fit in shared
-// memory (n_stage > 0) they are staged there for the whole launch: the interpreter then runs on copies of the level
-// descriptors whose var[0..3] point into shared memory (generic addressing), and every op of the coarse end of the
-// cycle costs shared-memory instead of L2 latency.  Everything else (face tables, planes, eps) stays in global memory.
-constexpr int kMaxStageLevels = 12;
-constexpr int kMaxStageOps = 192;
-__global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ levels, const __grid_constant__ ParamsDev P,
-                                               const TailOp* __restrict__ ops, int n_ops, double* scal, int n_stage) {
-  __shared__ double red[32];
-  __shared__ LevelDev slev[kMaxStageLevels];
-  extern __shared__ __align__(16) double stage[];
-  const int tid = threadIdx.x, nthr = blockDim.x;
-  if (n_stage > 0) {
-    if (tid == 0) {
-      size_t off = 0;
-      for (int l = 0; l < n_stage; ++l) {
-        slev[l] = levels[l];
-        const size_t n = (size_t)levels[l].nb * levels[l].bs;
-        for (int v = 0; v < 4; ++v) { slev[l].var[v] = stage + off; off += n; }
-      }
-      // the per-face and per-box tables follow the variables: every boundary cell's neighbour gather starts with a
-      // dependent fkind -> farg -> ftype chain, which costs an L2 round trip each when the tables stay in global memory
-      int* it = reinterpret_cast<int*>(stage + off);
-      for (int l = 0; l < n_stage; ++l) {
-        const int nf = levels[l].nb * 6, nb = levels[l].nb;
-        slev[l].fkind = it; it += nf; slev[l].farg = it; it += nf; slev[l].ftype = it; it += nf;
-        slev[l].fkind_old = it; it += nf; slev[l].farg_old = it; it += nf;
-        slev[l].parent = it; it += nb; slev[l].coff = it; it += nb;
-      }
-    }
-    __syncthreads();
-    for (int l = 0; l < n_stage; ++l) {
-      const int n = levels[l].nb * levels[l].bs;
-      for (int v = 0; v < 4; ++v) {
-        const double* __restrict__ src = levels[l].var[v];
-        double* dst = slev[l].var[v];
-        for (int i = tid; i < n; i += nthr) dst[i] = src[i];
-      }
-      const int nf = levels[l].nb * 6, nb = levels[l].nb;
-      for (int i = tid; i < nf; i += nthr) {
-        const_cast<int*>(slev[l].fkind)[i] = levels[l].fkind[i]; const_cast<int*>(slev[l].farg)[i] = levels[l].farg[i];
-        const_cast<int*>(slev[l].ftype)[i] = levels[l].ftype[i];
-        const_cast<int*>(slev[l].fkind_old)[i] = levels[l].fkind_old[i]; const_cast<int*>(slev[l].farg_old)[i] = levels[l].farg_old[i];
-      }
-      for (int i = tid; i < nb; i += nthr) {
-        const_cast<int*>(slev[l].parent)[i] = levels[l].parent[i]; const_cast<int*>(slev[l].coff)[i] = levels[l].coff[i];
-      }
-    }
-    __syncthreads();
-  }
-  const LevelDev* lv = n_stage > 0 ? slev : levels;
-  // the op list too: every op starts with a broadcast load of its descriptor, an L2 round trip from global memory
-  __shared__ TailOp sops[kMaxStageOps];
-  if (n_ops <= kMaxStageOps) {
-    for (int i = tid; i < n_ops; i += nthr) sops[i] = ops[i];
-    __syncthreads();
-    ops = sops;
-  }
-  OMG_SWITCH_OP(P.op, tail_run<OP>(lv, P, ops, n_ops, scal, red));
-  if (n_stage > 0) {
-    __syncthreads();
-    for (int l = 0; l < n_stage; ++l) {
-      const int n = levels[l].nb * levels[l].bs;
-      for (int v = 0; v < 4; ++v) {
-        double* __restrict__ dst = levels[l].var[v];
-        const double* src = slev[l].var[v];
-        for (int i = tid; i < n; i += nthr) dst[i] = src[i];
-      }
-    }
-  }
-}
 
 // ------------------------------------------------------------------ host <-> device layout ----
 // staging slab per box: (nc+2*shell)^3 doubles, reference order cc(i, j, k) i fastest; shell = 1: ghost shell included

@@ -23,11 +23,11 @@
 
 struct FakeDim { unsigned x = 0, y = 0, z = 0; };
 namespace emu {
-constexpr int NT = 256;
+constexpr int MAXT = 1024;
 unsigned char* g_smem = nullptr;      // the CTA's dynamic shared memory
 size_t g_smem_bytes = 0;              // as passed to the launch
-pthread_barrier_t g_cta_bar, g_warp_bar[NT / 32];
-double g_shfl[NT];
+pthread_barrier_t g_cta_bar, g_warp_bar[MAXT / 32];
+double g_shfl[MAXT];
 std::atomic<long long> g_tx_expected{0}, g_tx_done{0};
 std::atomic<int> g_violations{0};
 void violation(const char* what) {
@@ -36,7 +36,7 @@ void violation(const char* what) {
 }  // namespace emu
 
 static thread_local FakeDim threadIdx, blockIdx;
-static FakeDim blockDim = {emu::NT, 1, 1};
+static FakeDim blockDim = {256, 1, 1};
 static inline void __syncthreads() { pthread_barrier_wait(&emu::g_cta_bar); }
 static inline void __syncwarp() {}
 static inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
@@ -76,7 +76,8 @@ static inline void wait_flag(const volatile unsigned long long* f, unsigned long
 }
 #define OMG_DYN_SMEM(name, al) unsigned char* name = emu::g_smem
 #define OMG_PDL_ASM() do {} while (0)
-#define OMG_LAUNCH(kern, grid, smem, stream, ...) emu::launch((grid), (smem), [&]() { kern(__VA_ARGS__); })
+#define OMG_LAUNCH(kern, grid, smem, stream, ...) emu::launch((grid), 256, (smem), [&]() { kern(__VA_ARGS__); })
+#define OMG_TAIL_DYN_SMEM(name) double* name = reinterpret_cast<double*>(emu::g_smem)
 #define cudaFuncSetAttribute(...) cudaSuccess
 #undef __launch_bounds__
 #define __launch_bounds__(...)
@@ -84,15 +85,16 @@ static inline void wait_flag(const volatile unsigned long long* f, unsigned long
 #define __grid_constant__
 
 namespace emu {
-void launch(int grid, size_t smem, const std::function<void()>& body) {
+void launch(int grid, int nthreads, size_t smem, const std::function<void()>& body) {
   static unsigned char* buf = static_cast<unsigned char*>(aligned_alloc(1024, 256 * 1024));
   g_smem = buf; g_smem_bytes = smem;
   if (smem > 227 * 1024) violation("launch: more than 227 KB of shared memory");
-  pthread_barrier_init(&g_cta_bar, nullptr, NT);
+  blockDim.x = (unsigned)nthreads;
+  pthread_barrier_init(&g_cta_bar, nullptr, nthreads);
   for (auto& w : g_warp_bar) pthread_barrier_init(&w, nullptr, 32);
   std::vector<std::thread> th;
-  th.reserve(NT);
-  for (int t = 0; t < NT; ++t)
+  th.reserve(nthreads);
+  for (int t = 0; t < nthreads; ++t)
     th.emplace_back([&, t]() {
       for (int b = 0; b < grid; ++b) {
         threadIdx.x = (unsigned)t; blockIdx.x = (unsigned)b;
@@ -110,6 +112,11 @@ void launch(int grid, size_t smem, const std::function<void()>& body) {
 }  // namespace emu
 
 #include "../../octree-mg_b200/csrc/omg_fast.cu"
+
+// the tail interpreter: static __shared__ arrays become function-level statics (one CTA at a time)
+#undef __shared__
+#define __shared__ static
+#include "../../octree-mg_b200/csrc/omg_tail.cuh"
 
 namespace {
 
@@ -341,4 +348,114 @@ int fe_two_levels(int op, int nc, int nbx, int nby, int nbz, const int* bc_types
 }
 // checks of the emulated TMA / mbarrier / shared-memory rules that failed so far
 int fe_violations() { return emu::g_violations.load(); }
+}
+
+// ---- the single-CTA tail (k_tail, omg_tail.cuh) on a hierarchy of coarse levels ---------------------------------------
+// n_levels levels of nbx x nby x nbz boxes of 2^3, 4^3, 8^3, 16^3 cells (the single-box / few-box coarsening levels below
+// first_normal_lvl: box b of a level is refined into box b of the next, src/m_build_tree.f90:60-110), a V(2,2) op list as
+// the program builder emits it (omg_core.cu Builder::vcycle) incl. the coarse solve, run by 1024 emulated threads with and
+// without shared-memory staging, against the same ops applied one after the other by the general per-cell functions.
+namespace {
+
+struct Hier {
+  std::vector<HostLevel> H;
+  std::vector<std::vector<int>> plist;
+  std::vector<LevelDev> dev;
+};
+void build_hier(Hier& Q, int n_levels, int nbx, int nby, int nbz, const int* bc_types, int op, double lambda, int simple) {
+  Q.H.resize(n_levels); Q.plist.resize(n_levels);
+  for (int l = 0; l < n_levels; ++l) {
+    HostLevel& H = Q.H[l];
+    build_level(H, 2 << l, nbx, nby, nbz, bc_types, 0.08 / (1 << l));
+    set_fac(H, op, lambda);
+    H.L.lvl = l; H.L.simple = simple;
+    for (int b = 0; b < H.L.nb; ++b) { H.parent[b] = l > 0 ? b : -1; H.coff[b] = 0; }
+    if (l + 1 < n_levels) { for (int b = 0; b < H.L.nb; ++b) Q.plist[l].push_back(b); H.L.parents_list = Q.plist[l].data(); H.L.n_parents = H.L.nb; }
+  }
+}
+void sync_dev(Hier& Q) { Q.dev.clear(); for (HostLevel& H : Q.H) Q.dev.push_back(H.L); }
+
+std::vector<TailOp> vcycle_ops(int n_levels, int coarse_sub, int max_coarse) {
+  std::vector<TailOp> ops;
+  const int top = n_levels - 1;
+  for (int l = top; l >= 1; --l) {
+    for (int n = 0; n < 4; ++n) ops.push_back({TOP_SMOOTH, l, n & 1, 0});
+    ops.push_back({TOP_RESID, l, -1, 0});
+    ops.push_back({TOP_RESTRICT, l, 0, 3});
+    ops.push_back({TOP_CRHS, l - 1, 0, 0});
+  }
+  ops.push_back({TOP_COARSE_SOLVE, 0, coarse_sub, max_coarse});
+  for (int l = 1; l <= top; ++l) {
+    ops.push_back({TOP_CORR_PROLONG, l, 0, 0});
+    for (int n = 0; n < 4; ++n) ops.push_back({TOP_SMOOTH, l, n & 1, 0});
+  }
+  for (int l = 0; l <= top; ++l) ops.push_back({TOP_RESID, l, SCAL_MAXRES, 0});
+  return ops;
+}
+
+template <int OP>
+void reference_ops(Hier& Q, const ParamsDev& P, const std::vector<TailOp>& ops, double* scal) {
+  auto resid_max = [&](const LevelDev& L) { double m = 0.0; for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, 0, 1)); return m; };
+  for (const TailOp& op : ops) {
+    const LevelDev& L = Q.H[op.l].L;
+    switch (op.type) {
+      case TOP_SMOOTH: for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, op.a, 0, 1); break;
+      case TOP_RESID: { const double m = resid_max(L); if (op.a >= 0 && m > scal[op.a]) scal[op.a] = m; } break;
+      case TOP_RESTRICT: for (int b = 0; b < L.nb; ++b) { do_restrict(L, Q.H[op.l - 1].L, op.a, b, 0, 1); if (op.b >= 0) do_restrict(L, Q.H[op.l - 1].L, op.b, b, 0, 1); } break;
+      case TOP_CRHS: for (int q = 0; q < L.n_parents; ++q) do_crhs<OP>(L, P, L.parents_list[q], 0, 1); break;
+      case TOP_CORR_PROLONG: for (int b = 0; b < L.nb; ++b) do_corr_prolong(L, Q.H[op.l - 1].L, P, b, 0, 1); break;
+      case TOP_COARSE_SOLVE: {                     // src/m_multigrid.f90:202-208
+        const double init_res = resid_max(L);
+        int it = 0;
+        for (int i = 1; i <= op.b; ++i) {
+          for (int n = 1; n <= op.a; ++n) for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, (n - 1) & 1, 0, 1);
+          const double res = resid_max(L);
+          it = i;
+          if (res < scal[SCAL_COARSE_REL] * init_res || res < scal[SCAL_COARSE_ABS]) break;
+        }
+        scal[SCAL_COARSE_ITERS] = (double)it;
+      } break;
+      default: break;
+    }
+  }
+}
+
+template <int OP>
+int tail_case(int n_levels, int nbx, int nby, int nbz, int simple, int staged, const int* bc_types, const double* bc_values, double lambda, uint64_t seed) {
+  Hier G, T;
+  build_hier(G, n_levels, nbx, nby, nbz, bc_types, OP, lambda, 0);
+  build_hier(T, n_levels, nbx, nby, nbz, bc_types, OP, lambda, simple);
+  for (int l = 0; l < n_levels; ++l) { randomise(G.H[l], seed + 5 * l); copy_data(T.H[l], G.H[l]); }
+  ParamsDev P = params(OP, lambda, bc_types, bc_values);
+  const std::vector<TailOp> ops = vcycle_ops(n_levels, 4, 8);
+  std::vector<double> sg(SCAL_COUNT, 0.0), st(SCAL_COUNT, 0.0);
+  sg[SCAL_COARSE_REL] = st[SCAL_COARSE_REL] = 0.05;   // ends after a few iterations where the coarse problem converges, at the limit where it is singular
+  sg[SCAL_COARSE_ABS] = st[SCAL_COARSE_ABS] = 1e-300;
+  reference_ops<OP>(G, P, ops, sg.data());
+  sync_dev(T);
+  size_t stage_bytes = 0;
+  if (staged) for (const LevelDev& L : T.dev) stage_bytes += (size_t)4 * L.nb * L.bs * 8 + (size_t)32 * L.nb * sizeof(int);
+  if (stage_bytes > (size_t)200 * 1024) return -2;
+  const LevelDev* levels = T.dev.data(); const TailOp* po = ops.data(); double* scal = st.data();
+  const int n_ops = (int)ops.size(), n_stage = staged ? n_levels : 0;
+  emu::launch(1, 1024, stage_bytes, [&]() { k_tail(levels, P, po, n_ops, scal, n_stage); });
+  int bad = 0;
+  for (int l = 0; l < n_levels; ++l) bad += differing(G.H[l], T.H[l]);
+  bad += std::memcmp(&sg[SCAL_COARSE_ITERS], &st[SCAL_COARSE_ITERS], 8) != 0;
+  bad += std::memcmp(&sg[SCAL_MAXRES], &st[SCAL_MAXRES], 8) != 0;
+  if (sg[SCAL_COARSE_ITERS] < 1.0) bad += 100;
+  return bad;
+}
+
+}  // namespace
+
+extern "C" int fe_tail(int op, int n_levels, int nbx, int nby, int nbz, int simple, int staged, const int* bc_types, const double* bc_values, double lambda,
+                       unsigned long long seed) {
+  switch (op) {
+    case OP_LPL: return tail_case<OP_LPL>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    case OP_VLPL: return tail_case<OP_VLPL>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    case OP_HELMH: return tail_case<OP_HELMH>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    case OP_VHELMH: return tail_case<OP_VHELMH>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    default: return tail_case<OP_AHELMH>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+  }
 }

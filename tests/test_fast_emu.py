@@ -23,7 +23,7 @@ CSRC = os.path.join(os.path.dirname(HERE), "octree-mg_b200", "csrc")
 @pytest.fixture(scope="module")
 def emu():
     deps = [os.path.join(DH, "fast_emu.cpp"), os.path.join(DH, "harness.cpp")] + \
-           [os.path.join(CSRC, f) for f in ("omg_device.cuh", "omg_ops.cuh", "omg_fast.cu", "omg_fast.h")]
+           [os.path.join(CSRC, f) for f in ("omg_device.cuh", "omg_ops.cuh", "omg_fast.cu", "omg_fast.h", "omg_tail.cuh", "omg_kernels.h")]
     if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
         # -Bsymbolic: the emulator's omgf::* must not be interposed by libomg_b200.so when other tests loaded it first
@@ -88,3 +88,26 @@ def test_in_kernel_halo_exchange_between_emulated_ranks(emu, nc, op, lam):
             bad = emu.fe_ranks(op, nc, *shape, n_ranks, bnd_first, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 3 * nc + op)
             assert bad == 0, (types, shape, n_ranks, bnd_first)
     assert emu.fe_violations() == 0
+
+
+@pytest.mark.parametrize("planes", [0, 1])
+@pytest.mark.parametrize("op,lam", OPS + [(5, 1.25)])
+def test_tail_interpreter_runs_a_vcycle_like_the_general_path(emu, op, lam, planes):
+    """k_tail (omg_tail.cuh) with 1024 emulated threads: the V(2,2) op list of the coarse levels incl. the coarse solve and
+    its residual test, on single-box and two-box hierarchies, general and fast (simple_*) per-cell functions, with and
+    without staging the levels and their tables in shared memory -- state of every level, coarse iteration count and
+    maximum residual equal to the ops applied one by one through the general functions"""
+    emu.fe_tail.argtypes = [C.c_int] * 7 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
+    emu.dh_set_planes(planes)
+    try:
+        cases = list(zip(BC_SETS, [(4, (1, 1, 1)), (4, (2, 1, 1)), (3, (1, 2, 1)), (3, (1, 1, 2))]))
+        for types, (n_levels, shape) in (cases[2:] if planes else cases):
+            for simple in (0, 1):
+                for staged in (0, 1):
+                    if staged and n_levels == 4 and shape != (1, 1, 1):
+                        continue                      # four variables of all levels exceed the shared-memory budget: not staged
+                    bad = emu.fe_tail(op, n_levels, *shape, simple, staged, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 7 + op)
+                    assert bad == 0, (types, n_levels, shape, simple, staged)
+        assert emu.fe_violations() == 0
+    finally:
+        emu.dh_set_planes(0)
