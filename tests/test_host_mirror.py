@@ -110,11 +110,11 @@ def test_product_does_not_reference_the_oracle():
                 assert "liboracle" not in src and "import oracle" not in src and "from oracle" not in src, f
 
 
-def _build_cpp_example():
+def _build_cpp_example(name="test_uniform_grid"):
     import subprocess
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    exe = os.path.join(root, "examples", "test_uniform_grid")
-    subprocess.check_call(["g++", "-O2", "-std=c++17", os.path.join(root, "examples", "test_uniform_grid.cpp"), "-o", exe,
+    exe = os.path.join(root, "examples", name)
+    subprocess.check_call(["g++", "-O2", "-std=c++17", os.path.join(root, "examples", name + ".cpp"), "-o", exe,
                            "-L" + os.path.join(root, "octree-mg_b200"), "-lomg_host", "-lomg_b200",
                            "-Wl,-rpath," + os.path.join(root, "octree-mg_b200")])
     return exe
@@ -131,6 +131,33 @@ def test_cpp_host_example_builds_and_fails_loudly_without_a_device(product):
     r = subprocess.run([exe, "16", "32", "32", "32", "2", "t", "gsrb"], capture_output=True, text=True)
     assert r.returncode == 1
     assert "no CUDA device available (there is no CPU fallback)" in r.stderr
+
+
+def test_cpp_performance_example_builds_and_fails_loudly_without_a_device(product):
+    """examples/test_performance.cpp = the reference's tests/test_performance.f90 (the program of the headline number)"""
+    import subprocess
+    import torch
+    exe = _build_cpp_example("test_performance")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "Usage" in r.stderr
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present: the example would run (see the gpu-marked test)")
+    r = subprocess.run([exe, "16", "32", "32", "32", "2", "f", "gsrb"], capture_output=True, text=True)
+    assert r.returncode == 1
+    assert "no CUDA device available (there is no CPU fallback)" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1", reason="written after the round's GPU budget was spent; never run on a GPU yet")
+def test_cpp_performance_example_runs_on_the_device():
+    import re
+    import subprocess
+    exe = _build_cpp_example("test_performance")
+    for fmg, sm in (("f", "gsrb"), ("t", "gs")):
+        r = subprocess.run([exe, "16", "64", "64", "64", "5", fmg, sm], capture_output=True, text=True, check=True)
+        assert re.search(r"unknowns/microsec\s+\S+", r.stdout), r.stdout
+        res = float(re.search(r"max residual\s+(\S+)", r.stdout).group(1))
+        assert 0.0 <= res < 1e-3, r.stdout            # rhs = 1: five cycles take the residual far below its initial 1
 
 
 @pytest.mark.gpu
