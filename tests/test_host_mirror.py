@@ -147,6 +147,34 @@ def test_cpp_performance_example_builds_and_fails_loudly_without_a_device(produc
     assert "no CUDA device available (there is no CPU fallback)" in r.stderr
 
 
+def test_cpp_refinement_example_builds_and_fails_loudly_without_a_device(product):
+    """examples/test_refinement.cpp = the reference's tests/test_refinement.f90: the AMR tree is built through the mirror's
+    mg_add_children / mg_set_* calls before storage is allocated, so the tree code runs here even without a GPU"""
+    import subprocess
+    import torch
+    exe = _build_cpp_example("test_refinement")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "Usage" in r.stderr
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present: the example would run (see the gpu-marked test)")
+    r = subprocess.run([exe, "3", "8", "32", "32", "32", "2", "t", "gsrb"], capture_output=True, text=True)
+    assert r.returncode == 1
+    assert "no CUDA device available (there is no CPU fallback)" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1", reason="written after the round's GPU budget was spent; never run on a GPU yet")
+def test_cpp_refinement_example_converges_on_the_device():
+    import re
+    import subprocess
+    exe = _build_cpp_example("test_refinement")
+    r = subprocess.run([exe, "3", "8", "32", "32", "32", "8", "t", "gsrb"], capture_output=True, text=True, check=True)
+    errs = [float(m.group(1)) for m in re.finditer(r"max err\s+(\S+)", r.stdout)]
+    # the oracle's history for this set-up: 0.999, 1.0e-2, 2.3e-4, 1.3e-5, 8.7e-7, 6.0e-8, 4.2e-9, 2.9e-10, 2.0e-11
+    assert len(errs) == 9 and 0.9 < errs[0] < 1.0 and errs[-1] < 1e-9, r.stdout
+    assert "lvl_3: 64 boxes, 64 leaves, box size: 8" in r.stdout, r.stdout
+
+
 @pytest.mark.gpu
 @pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1", reason="written after the round's GPU budget was spent; never run on a GPU yet")
 def test_cpp_performance_example_runs_on_the_device():

@@ -1,6 +1,6 @@
 #!/bin/bash
 # First GPU call of the next round (1 GPU, ~6 min): everything that was written after round 1's GPU budget ran out.
-#   1. the whole GPU suite incl. the opt-in tests (tail_simple = 2 variants, option pdl, the two C++ examples)
+#   1. the whole GPU suite incl. the opt-in tests (tail_simple = 2 variants, option pdl, the three C++ examples)
 #   2. bitwise quick check + tail timing with the gated variants switched on
 #   3. default bench line, launch list
 set -x
