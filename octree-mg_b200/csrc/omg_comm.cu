@@ -202,10 +202,43 @@ omg_comm* omg_comm_create_local(omg_local_group* g, int rank, int device) {
   return c;
 }
 
+// Ordered release of the peer mappings (OMG_ORDERED_TEARDOWN=1; off until a multi-GPU pass has run it -- written after round
+// 1's GPU budget was spent).  Freeing memory a peer still has mapped is undefined (CUDA IPC rules) and
+// the ranks of a job leave at different moments, so when every rank deallocates (the reference's mg_deallocate_storage is
+// called by all of them) the order becomes: all ranks arrive (bounded flag wait over the mappings themselves -- a missing rank
+// gives up after the wait's time limit instead of hanging) -> everyone closes what it imported -> NCCL barrier -> the
+// exported memory is freed by the callers.  Returns true when the ranks met.
+static bool teardown_rendezvous(omg_comm* c) {
+  const char* e = getenv("OMG_ORDERED_TEARDOWN");
+  if (!e || !*e || atoi(e) == 0) return false;
+  if (!c->nccl || !c->p2p || c->n < 2 || c->n > kMaxRanks || !c->d_peer_flags || !c->d_flags || !c->d_err) return false;
+  int herr = 0;
+  if (cudaMemcpy(&herr, c->d_err, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess || herr) return false;   // an exchange already failed
+  unsigned long long* ep = nullptr;
+  if (cudaMalloc(&ep, sizeof(unsigned long long)) != cudaSuccess) return false;
+  cudaMemset(ep, 0, sizeof(unsigned long long));
+  PeerList pl; pl.n = 0;
+  for (int r = 0; r < c->n; ++r) if (r != c->rank) pl.peer[pl.n++] = r;
+  k_signal_wait<<<1, 32>>>(pl, OMG_P2P_CHANNELS - 1, c->rank, c->n, c->d_peer_flags, c->d_flags, ep, c->d_err, 1);
+  bool ok = cudaDeviceSynchronize() == cudaSuccess;
+  ok = ok && cudaMemcpy(&herr, c->d_err, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess && herr == 0;
+  cudaFree(ep);
+  return ok;
+}
+
 void omg_comm_destroy(omg_comm* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  const bool met = teardown_rendezvous(c);
   for (void* p : c->ipc_opened) cudaIpcCloseMemHandle(p);
+  if (met) {                                 // nobody frees before everybody has closed
+    double* d = nullptr;
+    if (cudaMalloc(&d, sizeof(double)) == cudaSuccess) {
+      cudaMemset(d, 0, sizeof(double));
+      if (nccl_api().AllReduce(d, d, 1, ncclDouble, ncclSum, c->nccl, 0) == ncclSuccess) cudaDeviceSynchronize();
+      cudaFree(d);
+    }
+  }
   if (c->d_flags) cudaFree(c->d_flags);
   if (c->ipc_scratch) cudaFree(c->ipc_scratch);
   if (c->d_err) cudaFree(c->d_err);

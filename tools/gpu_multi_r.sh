@@ -26,3 +26,13 @@ PY
     grep -v "OMP_NUM_THREADS\|^\*\*\*\|destroy_process_group" gpurun_out/bench_n${N}_${MODE}.err | tail -3
   done
 done
+
+# Teardown experiment: does a multi-rank run with the end-to-end leg leave on its own when the
+# library releases its peer mappings in order?  Short timeout: round 1 lost 80 GPU-minutes to runs that never exited.
+N=${1:-2}
+for ORD in 1 0; do
+  t0=$(date +%s)
+  OMG_ORDERED_TEARDOWN=$ORD OMG_BENCH_PLAIN_EXIT=1 timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 \
+    --master-port 29613 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/teardown_n${N}_ord$ORD.json 2> gpurun_out/teardown_n${N}_ord$ORD.err
+  echo "teardown N=$N ordered=$ORD rc=$? after $(( $(date +%s) - t0 )) s (124 = never exited)"
+done
