@@ -353,7 +353,7 @@ int fe_violations() { return emu::g_violations.load(); }
 // ---- the single-CTA tail (k_tail, omg_tail.cuh) on a hierarchy of coarse levels ---------------------------------------
 // n_levels levels of nbx x nby x nbz boxes of 2^3, 4^3, 8^3, 16^3 cells (the single-box / few-box coarsening levels below
 // first_normal_lvl: box b of a level is refined into box b of the next, src/m_build_tree.f90:60-110), a V(2,2) op list as
-// the program builder emits it (omg_core.cu Builder::vcycle) incl. the coarse solve, run by 1024 emulated threads with and
+// the program builder emits it (omg_core.cu Builder::vcycle) incl. the coarse solve, run by 1024 (as launched) or fewer emulated threads with and
 // without shared-memory staging, against the same ops applied one after the other by the general per-cell functions.
 namespace {
 
@@ -421,7 +421,7 @@ void reference_ops(Hier& Q, const ParamsDev& P, const std::vector<TailOp>& ops, 
 }
 
 template <int OP>
-int tail_case(int n_levels, int nbx, int nby, int nbz, int simple, int staged, const int* bc_types, const double* bc_values, double lambda, uint64_t seed) {
+int tail_case(int n_threads, int n_levels, int nbx, int nby, int nbz, int simple, int staged, const int* bc_types, const double* bc_values, double lambda, uint64_t seed) {
   Hier G, T;
   build_hier(G, n_levels, nbx, nby, nbz, bc_types, OP, lambda, 0);
   build_hier(T, n_levels, nbx, nby, nbz, bc_types, OP, lambda, simple);
@@ -438,7 +438,7 @@ int tail_case(int n_levels, int nbx, int nby, int nbz, int simple, int staged, c
   if (stage_bytes > (size_t)200 * 1024) return -2;
   const LevelDev* levels = T.dev.data(); const TailOp* po = ops.data(); double* scal = st.data();
   const int n_ops = (int)ops.size(), n_stage = staged ? n_levels : 0;
-  emu::launch(1, 1024, stage_bytes, [&]() { k_tail(levels, P, po, n_ops, scal, n_stage); });
+  emu::launch(1, n_threads, stage_bytes, [&]() { k_tail(levels, P, po, n_ops, scal, n_stage); });
   int bad = 0;
   for (int l = 0; l < n_levels; ++l) bad += differing(G.H[l], T.H[l]);
   bad += std::memcmp(&sg[SCAL_COARSE_ITERS], &st[SCAL_COARSE_ITERS], 8) != 0;
@@ -449,13 +449,13 @@ int tail_case(int n_levels, int nbx, int nby, int nbz, int simple, int staged, c
 
 }  // namespace
 
-extern "C" int fe_tail(int op, int n_levels, int nbx, int nby, int nbz, int simple, int staged, const int* bc_types, const double* bc_values, double lambda,
+extern "C" int fe_tail(int op, int n_threads, int n_levels, int nbx, int nby, int nbz, int simple, int staged, const int* bc_types, const double* bc_values, double lambda,
                        unsigned long long seed) {
   switch (op) {
-    case OP_LPL: return tail_case<OP_LPL>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
-    case OP_VLPL: return tail_case<OP_VLPL>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
-    case OP_HELMH: return tail_case<OP_HELMH>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
-    case OP_VHELMH: return tail_case<OP_VHELMH>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
-    default: return tail_case<OP_AHELMH>(n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    case OP_LPL: return tail_case<OP_LPL>(n_threads, n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    case OP_VLPL: return tail_case<OP_VLPL>(n_threads, n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    case OP_HELMH: return tail_case<OP_HELMH>(n_threads, n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    case OP_VHELMH: return tail_case<OP_VHELMH>(n_threads, n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
+    default: return tail_case<OP_AHELMH>(n_threads, n_levels, nbx, nby, nbz, simple, staged, bc_types, bc_values, lambda, seed);
   }
 }
