@@ -27,6 +27,9 @@ CASES = {
     "helmholtz32_neumann_fmg": dict(kind="uniform", n=32, box=8, fmg=True, its=3, op=P.mg_helmholtz, bc="neumann0", lam=1.0),
     "vlaplacian32_mixed_fmg": dict(kind="uniform", n=32, box=8, fmg=True, its=3, op=P.mg_vlaplacian, bc="mixed"),
     "refinement3_box8_fmg": dict(kind="amr", n=32, box=8, levels=3, fmg=True, its=3),
+    "uniform32_box8_gs_vcycle": dict(kind="uniform", n=32, box=8, fmg=False, its=4, smoother=P.mg_smoother_gs),
+    "ahelmholtz32_mixed_fmg": dict(kind="uniform", n=32, box=8, fmg=True, its=3, op=P.mg_ahelmholtz, bc="mixed", lam=0.5),
+    "noncubic64x32x32_box16_fmg": dict(kind="uniform", n=[64, 32, 32], box=16, fmg=True, its=3, bc="dirichlet0"),
     # implicit diffusion steps (src/m_diffusion.f90): residuals = [last max residual, number of V-cycles added] per step
     "diffusion32_box8_order1": dict(kind="diffusion", n=32, box=8, order=1, steps=2, op=P.mg_helmholtz),
     "diffusion32_box8_order2": dict(kind="diffusion", n=32, box=8, order=2, steps=2, op=P.mg_helmholtz),
@@ -52,7 +55,8 @@ def build(cls, name, **kw):
     c = CASES[name]
     if c["kind"] == "uniform":
         mg, _ = P.uniform_problem(cls, c["n"], c["box"], operator_type=c.get("op", P.mg_laplacian),
-                                  bc=c.get("bc", "callback"), lam=c.get("lam", 0.0), **kw)
+                                  smoother=c.get("smoother", P.mg_smoother_gsrb), bc=c.get("bc", "callback"),
+                                  lam=c.get("lam", 0.0), **kw)
     elif c["kind"] == "perf":
         mg = P.performance_problem(cls, c["n"], c["box"], **kw)
     elif c["kind"] == "diffusion":
