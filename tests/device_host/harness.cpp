@@ -197,7 +197,7 @@ int dh_compare_prolong(int ncf, int nbx, int nby, int nbz, int half_size_coarse,
 }
 // One operation of the GENERAL device path (do_smooth / do_resid, what the batched kernels and the tail run) on a brick
 // of nbx x nby x nbz boxes between constant physical boundaries, for the comparison with the oracle on the CPU.
-// Arrays: interior cells only, [box (x fastest)][k][j][i].  what = 0: one GSRB sweep (colour 0 = the cells the
+// Arrays: interior cells only, [box (x fastest)][k][j][i].  what = 2: one sweep of mg_smoother_gs; what = 0: one GSRB sweep (colour 0 = the cells the
 // reference updates first, then colour 1) of phi; what = 1: res = rhs - L(phi), returns max |res| through *out_max.
 int dh_level_op(int what, int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
                 const double* dr, double* phi, const double* rhs, double* res, double* out_max) {
@@ -214,11 +214,22 @@ int dh_level_op(int what, int op, int nc, int nbx, int nby, int nbz, const int* 
     H.var[0][dst] = phi[src]; H.var[1][dst] = rhs[src];
   }
   double m = 0.0;
+  std::vector<double> snap;
   if (what == 0) {
     for (int colour = 0; colour < 2; ++colour)
       for (int b = 0; b < L.nb; ++b) {
         if (op == OP_LPL) do_smooth<OP_LPL>(L, P, b, colour, 0, 1); else do_smooth<OP_HELMH>(L, P, b, colour, 0, 1);
       }
+  } else if (what == 2) {
+    // mg_smoother_gs: ghost snapshot of every box (= the ghost fill before the sweep), then the in-box sweep over
+    // hyperplanes i + j + k = w, which must equal the reference's lexicographic k, j, i loop
+    snap.assign((size_t)L.nb * 6 * nc * nc, 0.0);
+    L.faces[0] = snap.data();
+    P.smoother = 1;
+    for (int b = 0; b < L.nb; ++b) do_gs_snapshot(L, P, b, 0, 1);
+    for (int b = 0; b < L.nb; ++b) {
+      if (op == OP_LPL) do_gs_sweep<OP_LPL>(L, P, b, 0, 1); else do_gs_sweep<OP_HELMH>(L, P, b, 0, 1);
+    }
   } else {
     for (int b = 0; b < L.nb; ++b)
       m = fmax(m, op == OP_LPL ? do_resid<OP_LPL>(L, P, b, 0, 1) : do_resid<OP_HELMH>(L, P, b, 0, 1));

@@ -133,6 +133,46 @@ def test_general_device_path_matches_oracle_on_one_level(devhost, oracle, op, la
     assert np.array_equal(res, gather(P.mg_ires))
 
 
+@pytest.mark.parametrize("bc", sorted(BC_OF))
+@pytest.mark.parametrize("op,lam", [(1, 0.0), (3, 1.75)])
+def test_device_lexicographic_smoother_matches_oracle_on_one_level(devhost, oracle, op, lam, bc):
+    """mg_smoother_gs, the reference's default smoother: the device sweeps hyperplanes i + j + k = w against a snapshot of
+    the ghost faces (do_gs_snapshot + do_gs_sweep); the oracle runs the reference's lexicographic k, j, i loop per box after
+    a ghost fill (box_gs_lpl with redblack = .false., src/m_laplacian.f90:99-111) -- same bits after every sweep"""
+    import problems as P
+    devhost.dh_level_op.argtypes = [C.c_int] * 6 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double),
+                                                   C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
+    nc = 8
+    orc, _ = P.uniform_problem(oracle.OracleMg, 16, nc, operator_type=op, bc=bc, lam=lam, smoother=P.mg_smoother_gs)
+    lvl = orc.highest_lvl
+    ids = orc.ids(lvl)
+    rng = np.random.default_rng(17)
+    pos = {}
+    for id_ in ids:
+        ix = orc.box_info(id_)["ix"]
+        pos[id_] = ((ix[2] - 1) * 2 + (ix[1] - 1)) * 2 + (ix[0] - 1)
+        cc = orc.cc(id_, nc)
+        cc[P.mg_iphi - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((nc, nc, nc))
+        cc[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((nc, nc, nc)) * 100.0
+    orc.mg_fill_ghost_cells_lvl(lvl, P.mg_iphi)
+
+    def gather(iv):
+        out = np.empty((8, nc, nc, nc))
+        for id_ in ids:
+            out[pos[id_]] = orc.cc(id_, nc)[iv - 1, 1:-1, 1:-1, 1:-1]
+        return out
+
+    types, values = BC_OF[bc]
+    dr = (C.c_double * 3)(*orc.dr(lvl))
+    phi, rhs = gather(P.mg_iphi), gather(P.mg_irhs)
+    res = np.zeros_like(phi)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)          # noqa: E731
+    for sweep in range(3):
+        devhost.dh_level_op(2, op, nc, 2, 2, 2, six(C.c_int, types), six(C.c_double, values), lam, dr, vp(phi), vp(rhs), vp(res), None)
+        orc.smooth_boxes(lvl, 1)
+        assert np.array_equal(phi, gather(P.mg_iphi)), "lexicographic sweep %d differs" % sweep
+
+
 @pytest.mark.parametrize("simple", [0, 1])
 @pytest.mark.parametrize("bc", sorted(BC_OF))
 @pytest.mark.parametrize("op,lam", [(1, 0.0), (3, 1.75)])
