@@ -241,6 +241,54 @@ int dh_level_op(int what, int op, int nc, int nbx, int nby, int nbz, const int* 
   if (out_max) *out_max = m;
   return 0;
 }
+// The same for the variable-coefficient operators (mg_vlaplacian, mg_vhelmholtz, mg_ahelmholtz): eps_cc holds the n_eps
+// coefficient variables as the reference stores them, [variable][box][(nc+2)^3] with their ghost shell (host data); the
+// device layout keeps their interior cells colour-split and their ghost cells as stored faces [box][6][nc*nc].
+// what = 0: one GSRB sweep, 1: residual + its maximum.
+}  // extern "C"
+template <int OP>
+double level_op_vc(int what, LevelDev& L, const ParamsDev& P) {
+  double m = 0.0;
+  if (what == 0) { for (int colour = 0; colour < 2; ++colour) for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, colour, 0, 1); }
+  else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, 0, 1));
+  return m;
+}
+extern "C" {
+int dh_level_op_vc(int what, int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,
+                   const double* dr, double* phi, const double* rhs, double* res, const double* eps_cc, int n_eps, double* out_max) {
+  HostLevel H;
+  build_level(H, nc, nbx, nby, nbz, bc_types, 1.0);
+  LevelDev& L = H.L;
+  for (int d = 0; d < 3; ++d) { L.dr[d] = dr[d]; L.idr2[d] = 1.0 / (dr[d] * dr[d]); }
+  ParamsDev P = params(op, lambda, bc_types, bc_values);
+  const size_t n3 = (size_t)nc * nc * nc, n2 = nc + 2, g3 = n2 * n2 * n2;
+  for (int b = 0; b < L.nb; ++b) for (int k = 0; k < nc; ++k) for (int j = 0; j < nc; ++j) for (int i = 0; i < nc; ++i) {
+    const size_t src = b * n3 + ((size_t)k * nc + j) * nc + i, dst = (size_t)b * L.bs + cidx(L, i, j, k);
+    H.var[0][dst] = phi[src]; H.var[1][dst] = rhs[src];
+  }
+  for (int v = 0; v < n_eps; ++v) for (int b = 0; b < L.nb; ++b) {
+    const double* cc = eps_cc + ((size_t)v * L.nb + b) * g3;
+    auto at = [&](int i, int j, int k) { return cc[((size_t)(k + 1) * n2 + (j + 1)) * n2 + (i + 1)]; };   // ghosted indices -1 .. nc
+    for (int k = 0; k < nc; ++k) for (int j = 0; j < nc; ++j) for (int i = 0; i < nc; ++i) H.eps[v][(size_t)b * L.bs + cidx(L, i, j, k)] = at(i, j, k);
+    for (int f = 0; f < 6; ++f) for (int t2 = 0; t2 < nc; ++t2) for (int t1 = 0; t1 < nc; ++t1) {
+      const int g = (f & 1) ? nc : -1;
+      const double val = f < 2 ? at(g, t1, t2) : f < 4 ? at(t1, g, t2) : at(t1, t2, g);
+      H.epsf[v][((size_t)b * 6 + f) * nc * nc + (size_t)t2 * nc + t1] = val;
+    }
+  }
+  double m = 0.0;
+  switch (op) {
+    case OP_VLPL: m = level_op_vc<OP_VLPL>(what, L, P); break;
+    case OP_VHELMH: m = level_op_vc<OP_VHELMH>(what, L, P); break;
+    default: m = level_op_vc<OP_AHELMH>(what, L, P); break;
+  }
+  for (int b = 0; b < L.nb; ++b) for (int k = 0; k < nc; ++k) for (int j = 0; j < nc; ++j) for (int i = 0; i < nc; ++i) {
+    const size_t dst = b * n3 + ((size_t)k * nc + j) * nc + i, src = (size_t)b * L.bs + cidx(L, i, j, k);
+    phi[dst] = H.var[0][src]; res[dst] = H.var[3][src];
+  }
+  if (out_max) *out_max = m;
+  return 0;
+}
 // Two levels: a coarse level of ONE box of nc^3 and the fine level of its 2 x 2 x 2 children (same box size), constant
 // physical boundaries.  Arrays [box][k][j][i], interior cells; fine boxes in x-fastest octant order.
 //   what = 0: update_coarse (src/m_multigrid.f90:347-384) = residual on the fine level, restriction of phi and res,

@@ -173,6 +173,55 @@ def test_device_lexicographic_smoother_matches_oracle_on_one_level(devhost, orac
         assert np.array_equal(phi, gather(P.mg_iphi)), "lexicographic sweep %d differs" % sweep
 
 
+@pytest.mark.parametrize("bc", ["dirichlet0", "mixed"])
+@pytest.mark.parametrize("op,lam", [(2, 0.0), (4, 1.75), (5, 0.5)])
+def test_variable_coefficient_device_path_matches_oracle_on_one_level(devhost, oracle, op, lam, bc):
+    """mg_vlaplacian / mg_vhelmholtz / mg_ahelmholtz: the device's general path (harmonic-mean face coefficients through the
+    batched division, eps ghost cells as stored faces) against the oracle's box_gs_v* / box_v* (src/m_vlaplacian.f90:51-189,
+    m_vhelmholtz.f90:61-205, m_ahelmholtz.f90:69-237) on 2 x 2 x 2 boxes with random phi and rhs: same bits, on the CPU"""
+    import problems as P
+    devhost.dh_level_op_vc.argtypes = [C.c_int] * 6 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double),
+                                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_double)]
+    nc = 8
+    orc, _ = P.uniform_problem(oracle.OracleMg, 16, nc, operator_type=op, bc=bc, lam=lam)
+    ne = P.n_eps(op)
+    lvl = orc.highest_lvl
+    ids = orc.ids(lvl)
+    rng = np.random.default_rng(23)
+    pos = {}
+    eps_cc = np.empty((ne, 8, nc + 2, nc + 2, nc + 2))
+    for id_ in ids:
+        ix = orc.box_info(id_)["ix"]
+        pos[id_] = ((ix[2] - 1) * 2 + (ix[1] - 1)) * 2 + (ix[0] - 1)
+        cc = orc.cc(id_, nc)
+        cc[P.mg_iphi - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((nc, nc, nc))
+        cc[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((nc, nc, nc)) * 100.0
+        for d in range(ne):
+            eps_cc[d, pos[id_]] = cc[P.mg_iveps - 1 + d]
+    orc.mg_fill_ghost_cells_lvl(lvl, P.mg_iphi)
+
+    def gather(iv):
+        out = np.empty((8, nc, nc, nc))
+        for id_ in ids:
+            out[pos[id_]] = orc.cc(id_, nc)[iv - 1, 1:-1, 1:-1, 1:-1]
+        return out
+
+    types, values = BC_OF[bc]
+    dr = (C.c_double * 3)(*orc.dr(lvl))
+    phi, rhs = gather(P.mg_iphi), gather(P.mg_irhs)
+    res = np.zeros_like(phi)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)          # noqa: E731
+    args = (op, nc, 2, 2, 2, six(C.c_int, types), six(C.c_double, values), lam, dr, vp(phi), vp(rhs), vp(res), vp(eps_cc), ne)
+    for sweep in range(2):
+        devhost.dh_level_op_vc(0, *args, None)
+        orc.smooth_boxes(lvl, 1)
+        assert np.array_equal(phi, gather(P.mg_iphi)), "GSRB sweep %d differs" % sweep
+    m = C.c_double(0.0)
+    devhost.dh_level_op_vc(1, *args, C.byref(m))
+    assert orc.max_residual_lvl(lvl) == m.value
+    assert np.array_equal(res, gather(P.mg_ires))
+
+
 @pytest.mark.parametrize("simple", [0, 1])
 @pytest.mark.parametrize("bc", sorted(BC_OF))
 @pytest.mark.parametrize("op,lam", [(1, 0.0), (3, 1.75)])
