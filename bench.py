@@ -1,14 +1,19 @@
 #!/usr/bin/env python
 """bench.py -- 3D Poisson FAS V-cycle throughput (GDOF/s) on B200, with the roofline of the dominant kernel,
-an end-to-end number through the C ABI with host buffers, and the CPU oracle timed beside it.
+an end-to-end number through the C ABI with host buffers, a strong-scaling record of the 1024^3 domain, a bitwise
+parity check of the data plane actually timed, and the CPU oracle timed beside it.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--n 512] [--box 16]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--cells 512] [--box 16]
 
 A step is one standalone V(2,2) GSRB cycle (mg_fas_vcycle, src/m_multigrid.f90:150-243) of the
 tests/test_performance.f90 problem (rhs = 1, phi0 = 0, homogeneous Dirichlet), called as in that program's timed
 loop (:68-76: `call mg_fas_vcycle(mg)`, no max_res; --max-res adds the all-level residual pass).
 N = 1: BASELINE.json configs[1] (512^3, box 16).  N > 1: weak scaling, 512^3 per GPU along the reference's
-Morton partition (N = 8 is configs[4], 1024^3).
+Morton partition (N = 8 is configs[4], 1024^3).  Every line also carries
+  "strong":       the SAME 1024^3 domain (configs[4]) timed on the N GPUs of this run (N = 1 included),
+  "parity_check": FMG + 3 V-cycles of a 256^3 test_uniform_grid problem on the communicator of this run (all N
+                  processes: CUDA-IPC puts + NCCL), residual history and a checksum of phi compared bit for bit
+                  with the CPU oracle on rank 0; a mismatch makes the run exit non-zero.
 """
 import argparse
 import ctypes as C
@@ -26,6 +31,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 BYTES_PER_DOF_VCYCLE = 155.4            # Laplacian V(2,2); + 18.3 when max_res is requested
 BYTES_PER_DOF_MAXRES = 18.3
 SMOOTH_BYTES_PER_CELL = 12.0            # one colour half-sweep launched on its own
+CPU_NS_PER_CELL_CYCLE = 80.0            # oracle, one thread: pessimistic estimate used only to bound the CPU arm's run time
 
 
 def peaks():
@@ -36,7 +42,7 @@ def peaks():
 
 
 def ncu_traffic(n, box):
-    """dram__bytes_read.sum + dram__bytes_write.sum of ONE finest-level smoother launch, from the committed
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE finest-level smoother launch, from the newest committed
     `ncu --set full` capture of this very command (profiles/, tools/ncu_summary.py); None for other workloads."""
     if (n, box) != (512, 16):
         return None, None
@@ -101,30 +107,192 @@ def domain_for(n, world):
     return dims
 
 
-def cpu_reference_line(args, sample_n=None):
-    """the CPU arm: the oracle (C++ restatement of the reference; the Fortran/MPI reference cannot be built in
-    this image) on all host cores, one OpenMP thread per emulated MPI rank, on a bounded sample."""
-    import problems as P
-    from oracle import oracle as O
-    cores = os.cpu_count() or 1
+def workload_text(dims, box, max_res):
+    return ("test_performance %s box %d: 7-point Laplacian, rhs=1, Dirichlet 0, standalone V(2,2) GSRB cycles%s"
+            % ("x".join(map(str, dims)), box, " with max_res" if max_res else " (mg_fas_vcycle(mg) as in test_performance.f90:68-76)"))
+
+
+def host_threads():
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     ranks = 1
     while ranks * 2 <= cores:
         ranks *= 2
-    n = sample_n or min(args.n, 256)
+    return ranks
+
+
+def mem_available_bytes():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) * 1024
+    except Exception:
+        pass
+    return 16 << 30
+
+
+def cpu_reference_line(dims, box, steps, warmup, max_res, budget_s):
+    """The CPU arm: the oracle (C++ restatement of the reference; the Fortran/MPI reference cannot be built in this
+    image) with one OpenMP thread per emulated MPI rank, all host cores.  It runs the workload it is given -- same
+    domain, box size, cycle, steps and warm-up as the GPU arm -- unless the estimated run time exceeds budget_s or the
+    domain does not fit the host's memory; then the cycle count / the domain are cut down and the record says exactly
+    what ran ("ran": domain, steps, warmup)."""
+    import problems as P
+    from oracle import oracle as O
+    ranks = host_threads()
+    dims = list(dims)
+    note = []
+    # memory: 4 variables with ghost shells per box, all levels (x 8/7), + slack
+    def footprint(d):
+        return d[0] * d[1] * d[2] / box ** 3 * (8.0 / 7.0) * 4 * (box + 2) ** 3 * 8 * 1.15
+    while footprint(dims) > 0.6 * mem_available_bytes() and max(dims) > 128:
+        dims[dims.index(max(dims))] //= 2
+        note.append("domain halved to fit host memory")
+    def est(d, cycles):
+        return d[0] * d[1] * d[2] * CPU_NS_PER_CELL_CYCLE * 1e-9 / ranks * cycles
+    while est(dims, 4) > budget_s and max(dims) > 128:
+        dims[dims.index(max(dims))] //= 2
+        note.append("domain halved to bound the run time")
+    w = max(0, warmup)
+    k = max(1, steps)
+    while est(dims, w + k) > budget_s and (w > 1 or k > 3):
+        if w > 1:
+            w -= 1
+        else:
+            k = max(3, k - 1)
     O.lib().orc_set_omp_threads(ranks)
-    mg = P.performance_problem(O.OracleMg, n, args.box, n_cpu=ranks)
-    dof = n ** 3
-    for _ in range(max(args.warmup, 0) and 1):
-        mg.mg_fas_vcycle(want_res=args.max_res)
-    k = max(1, min(args.steps, 3))
+    mg = P.performance_problem(O.OracleMg, dims, box, n_cpu=ranks)
+    dof = dims[0] * dims[1] * dims[2]
+    for _ in range(w):
+        mg.mg_fas_vcycle(want_res=max_res)
     t0 = time.perf_counter()
     for _ in range(k):
-        mg.mg_fas_vcycle(want_res=args.max_res)
+        mg.mg_fas_vcycle(want_res=max_res)
     dt = time.perf_counter() - t0
     val = dof * k / dt / 1e9
+    ran = {"domain": dims, "steps": k, "warmup": w}
     return {"value": val, "unit": "GDOF/s", "cores": ranks, "kind": "port",
-            "sample": "%d^3 box %d, %d V(2,2) GSRB cycles%s, oracle/omg_oracle.cpp, %d OpenMP threads = emulated MPI ranks"
-                      % (n, args.box, k, " with max_res" if args.max_res else "", ranks), "ms_per_step": dt / k * 1e3}
+            "sample": "%s box %d, %d timed V(2,2) GSRB cycles after %d warm-up%s, oracle/omg_oracle.cpp, %d OpenMP threads = emulated MPI ranks%s"
+                      % ("x".join(map(str, dims)), box, k, w, " with max_res" if max_res else "", ranks,
+                         ("; " + ", ".join(sorted(set(note)))) if note else ""),
+            "ms_per_step": dt / k * 1e3, "ran": ran,
+            "ref_style_unknowns_per_us": mg.n_boxes * box ** 3 * k / (dt * 1e6)}
+
+
+def phi_checksum(mg, P):
+    """order-independent exact checksum (mod 2^64) of phi on the owned leaves: bit patterns weighted by position and box id"""
+    import numpy as np
+    tot = np.uint64(0)
+    with np.errstate(over="ignore"):
+        for lvl in range(mg.lowest_lvl, mg.highest_lvl + 1):
+            nc = mg.box_size_lvl(lvl)
+            w = (np.arange(nc ** 3, dtype=np.uint64) * np.uint64(2) + np.uint64(1)) * np.uint64(0x9E3779B97F4A7C15)
+            mine = mg.my_leaves(lvl) if hasattr(mg, "my_leaves") else mg.leaves(lvl)
+            for id_ in mine:
+                v = np.ascontiguousarray(mg.cc(id_, nc)[P.mg_iphi - 1, 1:-1, 1:-1, 1:-1]).view(np.uint64).ravel()
+                v = np.where(v == np.uint64(1 << 63), np.uint64(0), v)      # -0.0 == +0.0
+                tot = tot + (v * w).sum(dtype=np.uint64) * np.uint64(2 * id_ + 1)
+    return int(tot)
+
+
+def comm_init(mg, dist, rank, world):
+    """mg_comm_init of the GPU library: NCCL unique id from rank 0, broadcast through torch.distributed"""
+    import torch
+    uid = C.create_string_buffer(128)
+    if rank == 0:
+        mg.G.omg_nccl_unique_id(uid)
+    t = torch.frombuffer(bytearray(uid.raw), dtype=torch.uint8).cuda()
+    dist.broadcast(t, 0)
+    uid = C.create_string_buffer(bytes(t.cpu().numpy().tobytes()), 128)
+    mg._gck(mg.G.omg_comm_init(mg.gpu, uid, rank, world))
+
+
+def parity_check(om, P, n, box, rank, world, local, dist, collapse):
+    """FMG + 3 V-cycles of the test_uniform_grid problem (n^3 in total, Dirichlet planes from the manufactured solution)
+    on the communicator this run timed, against the oracle (rank 0): residual history and phi checksum, bit for bit"""
+    import torch
+
+    def setup(mg):
+        if world > 1:
+            mg.set_int("coarse_collapse_boxes", collapse)
+    mg, _ = P.uniform_problem(om.Mg, n, box, load_balance="parents", setup=setup,
+                              after_alloc=(lambda m: comm_init(m, dist, rank, world)) if world > 1 else None,
+                              n_cpu=world, my_rank=rank, device=local)
+    f0, g0 = mg.stat("fast_launches"), mg.stat("general_launches")
+    hist = [mg.mg_fas_fmg(False)] + [mg.mg_fas_vcycle() for _ in range(3)]
+    fast, general = mg.stat("fast_launches") - f0, mg.stat("general_launches") - g0
+    ck = phi_checksum(mg, P)
+    fused, puts = mg.stat("fused_smooths"), mg.stat("puts")
+    if world > 1:
+        t = torch.tensor([ck - (1 << 64) if ck >= (1 << 63) else ck], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)            # two's-complement wrap-around = sum mod 2^64
+        ck = int(t.item()) % (1 << 64)
+    mg.mg_deallocate_storage()
+    out = {"n_ranks": world, "problem": "test_uniform_grid %d^3 box %d, FMG + 3 V(2,2) GSRB cycles" % (n, box),
+           "fast_launches": fast, "general_launches": general, "fused_smooths": fused, "put_phases": puts}
+    if rank == 0:
+        from oracle import oracle as O
+        O.lib().orc_set_omp_threads(host_threads())
+        orc, _ = P.uniform_problem(O.OracleMg, n, box, load_balance="parents", n_cpu=host_threads())
+        h_o = [orc.mg_fas_fmg(False)] + [orc.mg_fas_vcycle() for _ in range(3)]
+        ck_o = phi_checksum(orc, P)
+        out.update({"residuals": [float(x).hex() for x in hist], "oracle_residuals": [float(x).hex() for x in h_o],
+                    "phi_checksum": "%016x" % ck, "oracle_phi_checksum": "%016x" % ck_o,
+                    "bitwise": bool(h_o == hist and ck == ck_o)})
+    return out
+
+
+def build_performance_mg(om, P, args, dims, op, rank, world, local, dist, collapse):
+    """tests/test_performance.f90:51-66 without host cc arrays (the run is device-resident)"""
+    mg = om.Mg(op, P.mg_smoother_gsrb, n_extra_vars=P.n_eps(op), n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
+    mg.set_int("host_cc", 0)
+    if op in (P.mg_helmholtz, P.mg_vhelmholtz):
+        mg.set_lambda(1.0)
+    if world > 1:
+        mg.set_int("coarse_collapse_boxes", collapse)
+    for nb in range(1, 7):
+        if args.op == "laplacian" or (args.op == "vlaplacian" and nb == 1):
+            mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
+        else:
+            mg.set_bc(nb, P.mg_iphi, P.mg_bc_neumann, 0.0)
+    mg.mg_set_methods()
+    mg.mg_build_rectangle(dims, args.box, [1.0 / dims[0]] * 3, [0.0] * 3, [False] * 3)
+    mg.mg_load_balance()
+    mg.mg_load_balance_parents()
+    mg.mg_allocate_storage()
+    if world > 1:
+        comm_init(mg, dist, rank, world)
+    G, gpu = mg.G, mg.gpu
+    # device-resident initial state: rhs = 1 on the interior of every level, phi = 0 (no host transfer needed)
+    mg._gck(G.omg_set_var_const(gpu, P.mg_irhs, -20, 20, 1.0, 1))
+    mg._gck(G.omg_set_var_const(gpu, P.mg_iphi, -20, 20, 0.0, 0))
+    for d in range(P.n_eps(op)):
+        mg._gck(G.omg_set_var_const(gpu, P.mg_iveps + d, -20, 20, 1.0, 0))     # eps = 1 incl. ghost faces
+    if args.tail_cells >= 0:
+        mg.set_option("tail_cells", args.tail_cells)
+    if args.no_graph:
+        mg.set_option("use_graph", 0)
+    if args.no_fast:
+        mg.set_option("fast_kernels", 0)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        mg.set_option(k, int(v))
+    return mg
+
+
+def timed_cycles(mg, args, barrier, dist, steps, warmup):
+    """W warm-up cycles, then K cycles bracketed by barrier + synchronize; CUDA events on the handle's stream; max over ranks"""
+    import torch
+    mg.mg_fas_vcycle(want_res=args.max_res)               # uploads parameters; first cycle also builds the graph
+    for _ in range(max(warmup - 1, 0)):
+        mg.fas_vcycles(1, want_res=args.max_res)
+    barrier()
+    res, ms = mg.fas_vcycles(steps, want_res=args.max_res)
+    barrier()
+    if dist is not None:
+        tms = torch.tensor([ms], device="cuda")
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    return res, ms
 
 
 def main():
@@ -141,14 +309,18 @@ def main():
     ap.add_argument("--tail-cells", type=int, default=-1, help="levels up to this many cells run inside the single-launch coarse tail")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the 1024^3 strong-scaling record")
+    ap.add_argument("--no-parity", action="store_true", help="skip the bitwise parity check of the timed data plane")
+    ap.add_argument("--strong-cells", type=int, default=1024, help="total domain of the strong-scaling record (BASELINE configs[4])")
+    ap.add_argument("--parity-cells", type=int, default=256, help="total domain of the parity check")
+    ap.add_argument("--cpu-budget", type=float, default=150.0, help="seconds the CPU arm may take (it cuts its cycle count, then its domain, to fit)")
     ap.add_argument("--e2e-cc", action="store_true", help="end-to-end leg moves cc slabs with ghost shells (omg_push/pull_var_packed) "
                     "instead of interior cells (omg_copy_to/from_tree)")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
     ap.add_argument("--no-fast", action="store_true", help="general-path kernels only")
-    ap.add_argument("--op", default="laplacian", choices=["laplacian", "vlaplacian", "helmholtz", "vhelmholtz"],
+    ap.add_argument("--op", default="laplacian", choices=["laplacian", "vlaplacian", "helmholtz", "vhelmholtz", "ahelmholtz"],
                     help="operator (BASELINE.json configs[3]: vlaplacian / helmholtz with Neumann BC); default = the headline Laplacian")
-    ap.add_argument("--strong", action="store_true", help="N > 1: keep the TOTAL domain at n^3 (BASELINE.json configs[4]: 1024^3 "
-                    "strong scaling) instead of n^3 per GPU")
+    ap.add_argument("--strong", action="store_true", help="N > 1: keep the TOTAL domain at n^3 instead of n^3 per GPU for the headline value")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (omg_set_option), repeatable")
     ap.add_argument("--trace", default=None, metavar="PREFIX",
                     help="after the measurement: run 2 V-cycles with option trace and write the per-step timeline of every rank "
@@ -158,8 +330,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dims = [args.n] * 3 if args.strong else domain_for(args.n, world)
-    config = {"workload": "test_performance %s box %d: 7-point Laplacian, rhs=1, Dirichlet 0, standalone V(2,2) GSRB cycles%s"
-                          % ("x".join(map(str, dims)), args.box, " with max_res" if args.max_res else " (mg_fas_vcycle(mg) as in test_performance.f90:68-76)"),
+    config = {"workload": workload_text(dims, args.box, args.max_res),
               "n_cycle_down": 2, "n_cycle_up": 2, "smoother": "gsrb", "box_size": args.box, "domain": dims,
               "partition": "mg_load_balance (Morton-contiguous), %d rank(s)" % world,
               "l2": "inputs larger than L2 (4 x %.2f GB per GPU vs 126 MB)" % (dims[0] * dims[1] * dims[2] / world * 8 / 1e9)}
@@ -167,13 +338,23 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        cb = cpu_reference_line(args)
+        cb = cpu_reference_line(dims, args.box, args.steps, args.warmup, args.max_res, args.cpu_budget)
+        ran = cb["ran"]
+        # the line describes what RAN: when the budget cut the domain or the cycle count, config / steps / warmup say so
+        if ran["domain"] != dims:
+            config["sample_of"] = config["workload"]
+            config["workload"] = workload_text(ran["domain"], args.box, args.max_res)
+            config["domain"] = ran["domain"]
+        config["partition"] = "%d emulated MPI ranks (OpenMP threads), mg_load_balance" % cb["cores"]
+        config["l2"] = "host arm"
         line = {"impl": "reference", "metric": "3D Poisson FAS V-cycle throughput", "value": cb["value"], "unit": "GDOF/s",
-                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
+                "n_gpus": args.gpus, "steps": ran["steps"], "warmup": ran["warmup"], "requested": {"steps": args.steps, "warmup": args.warmup},
+                "ms_per_step": cb["ms_per_step"],
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": config, "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": cb["value"], "unit": "GDOF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "note": "reference MPI Fortran build unavailable on this box (no Fortran compiler / MPI); CPU arm = oracle port"}
+                "ref_style_unknowns_per_us": cb["ref_style_unknowns_per_us"],
+                "note": "reference MPI Fortran build unavailable on this box (no Fortran compiler / MPI, profiles/fortran_probe_r02.txt); CPU arm = oracle port"}
         print(json.dumps(line))
         return
 
@@ -188,60 +369,20 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    # tests/test_performance.f90:51-66 without host cc arrays (the run is device-resident)
-    op = {"laplacian": P.mg_laplacian, "vlaplacian": P.mg_vlaplacian, "helmholtz": P.mg_helmholtz, "vhelmholtz": P.mg_vhelmholtz}[args.op]
-    mg = om.Mg(op, P.mg_smoother_gsrb, n_extra_vars=P.n_eps(op), n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
-    mg.set_int("host_cc", 0)
+    op = {"laplacian": P.mg_laplacian, "vlaplacian": P.mg_vlaplacian, "helmholtz": P.mg_helmholtz, "vhelmholtz": P.mg_vhelmholtz,
+          "ahelmholtz": P.mg_ahelmholtz}[args.op]
     if args.op != "laplacian":
         config["workload"] = config["workload"].replace("7-point Laplacian", "%s (eps = 1, lambda = 1), Neumann-0 BC%s" % (
             args.op, " + Dirichlet on -x" if args.op == "vlaplacian" else ""))
-        if op in (P.mg_helmholtz, P.mg_vhelmholtz):
-            mg.set_lambda(1.0)
     collapse = args.collapse if args.collapse >= 0 else 128
     if world > 1:
-        mg.set_int("coarse_collapse_boxes", collapse)
         config["coarse_collapse_boxes_per_rank"] = collapse
-    for nb in range(1, 7):
-        if args.op == "laplacian" or (args.op == "vlaplacian" and nb == 1):
-            mg.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
-        else:
-            mg.set_bc(nb, P.mg_iphi, P.mg_bc_neumann, 0.0)
-    mg.mg_set_methods()
-    mg.mg_build_rectangle(dims, args.box, [1.0 / dims[0]] * 3, [0.0] * 3, [False] * 3)
-    mg.mg_load_balance()
-    mg.mg_load_balance_parents()
-    mg.mg_allocate_storage()
-    if world > 1:
-        uid = C.create_string_buffer(128)
-        if rank == 0:
-            mg.G.omg_nccl_unique_id(uid)
-        t = torch.frombuffer(bytearray(uid.raw), dtype=torch.uint8).cuda()
-        dist.broadcast(t, 0)
-        uid = C.create_string_buffer(bytes(t.cpu().numpy().tobytes()), 128)
-        mg._gck(mg.G.omg_comm_init(mg.gpu, uid, rank, world))
-    dof = dims[0] * dims[1] * dims[2]
-    G, gpu = mg.G, mg.gpu
-    # device-resident initial state: rhs = 1 on the interior of every level, phi = 0 (no host transfer needed)
-    mg._gck(G.omg_set_var_const(gpu, P.mg_irhs, -20, 20, 1.0, 1))
-    mg._gck(G.omg_set_var_const(gpu, P.mg_iphi, -20, 20, 0.0, 0))
-    if P.n_eps(op):
-        mg._gck(G.omg_set_var_const(gpu, P.mg_iveps, -20, 20, 1.0, 0))     # eps = 1 incl. ghost faces
-    if args.tail_cells >= 0:
-        mg.set_option("tail_cells", args.tail_cells)
-    if args.no_graph:
-        mg.set_option("use_graph", 0)
-    if args.no_fast:
-        mg.set_option("fast_kernels", 0)
     for kv in args.opt:
         k, v = kv.split("=")
-        mg.set_option(k, int(v))
         config.setdefault("options", {})[k] = int(v)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    mg.mg_fas_vcycle(want_res=args.max_res)               # uploads parameters; first cycle also builds the graph
-    for _ in range(max(args.warmup - 1, 0)):
-        mg.fas_vcycles(1, want_res=args.max_res)
+    mg = build_performance_mg(om, P, args, dims, op, rank, world, local, dist, collapse)
+    dof = dims[0] * dims[1] * dims[2]
+    G, gpu = mg.G, mg.gpu
 
     def barrier():
         torch.cuda.synchronize()
@@ -249,19 +390,17 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    barrier()
-    res, ms = mg.fas_vcycles(args.steps, want_res=args.max_res)   # CUDA events on the handle's stream bracket the K cycles
-    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    res, ms = timed_cycles(mg, args, barrier, dist, args.steps, args.warmup)
     clocks = sampler.stop() if rank == 0 else None
-    if dist is not None:
-        tms = torch.tensor([ms], device="cuda")
-        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-        ms = float(tms.item())
-    launches_per_step = None
-    l0 = mg.stat("launches")
+    l0, f0, g0 = mg.stat("launches"), mg.stat("fast_launches"), mg.stat("general_launches")
     mg.fas_vcycles(1, want_res=args.max_res)
     launches_per_step = mg.stat("launches") - l0
+    fast_per_step, general_per_step = mg.stat("fast_launches") - f0, mg.stat("general_launches") - g0
     res_after, _ = mg.fas_vcycles(1, want_res=True)      # untimed: residual after warm-up + timed + 2 cycles
+    n_boxes_total = mg.n_boxes
 
     # --- roofline of the dominant kernel (finest-level GSRB colour half-sweep), timed live with CUDA events
     mg.set_option("profile", 1)
@@ -270,6 +409,7 @@ def main():
     n_sm = int(G.omg_last_ms(gpu, b"n_smooth"))
     prof = {k: float(G.omg_last_ms(gpu, k.encode())) for k in ("smooth", "resid_restrict", "corr_prolong", "resid")}
     mg.set_option("profile", 0)
+    timers = mg.mg_timers()
     if args.trace:
         mg.set_option("trace", 1)
         mg.fas_vcycles(2)
@@ -293,6 +433,17 @@ def main():
                 "ms_per_launch": sm_ms, "finest_level_ms": prof}
     value = dof * args.steps / (ms * 1e-3) / 1e9
     cycle_frac = (BYTES_PER_DOF_VCYCLE + (BYTES_PER_DOF_MAXRES if args.max_res else 0.0)) * value / peak / world
+    # mg_timers_show (src/m_data_structures.f90:562-581): min / max over ranks of the accumulated timers
+    timers_minmax = None
+    if dist is not None:
+        names = sorted(timers)
+        tv = torch.tensor([timers[k] for k in names], dtype=torch.float64, device="cuda")
+        tmin, tmax = tv.clone(), tv.clone()
+        dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        timers_minmax = {k: [float(a), float(b)] for k, a, b in zip(names, tmin.tolist(), tmax.tolist())}
+    else:
+        timers_minmax = {k: [v, v] for k, v in timers.items()}
 
     # --- end to end through the C ABI with host buffers: the application's phi and rhs (pinned host arrays, interior
     # cells of the grid leaves, as mg_copy_to_tree of coupling_amrvac/mod_multigrid_coupling.t:133-171 takes them) go to
@@ -337,35 +488,88 @@ def main():
             dt = float(tt.item())
         e2e = {"value": dof * k2 / dt / 1e9, "unit": "GDOF/s", "h2d_bytes_per_step": 2 * nd * 8 * world,
                "d2h_bytes_per_step": nd * 8 * world + 8, "steps": k2, "ms_per_step": dt / k2 * 1e3,
+               "pcie_gbs_per_gpu": 3 * nd * 8 / (dt / k2) / 1e9,
                "what": ("omg_push_var_packed(phi, rhs) of the leaf level from pinned host slabs in the reference's cc layout (ghost shells included) + omg_fas_vcycle + omg_pull_var_packed(phi with ghost cells)"
                         if args.e2e_cc else "omg_copy_to_tree(phi, rhs: interior cells of the leaves, pinned host arrays) + omg_fas_vcycle + omg_copy_from_tree(phi)")}
+        del hphi, hrhs
+
+    # mg_deallocate_storage on every rank (ordered release of the peer mappings), then the follow-up problems are
+    # created on the same process group: create / destroy / create of the multi-rank handle is part of every run
+    mg.mg_deallocate_storage()
+    del mg
+    barrier()
+
+    # --- strong scaling of BASELINE configs[4]: the same 1024^3 domain on the N GPUs of this run
+    strong = None
+    if not args.no_strong and args.op == "laplacian":
+        sdims = [args.strong_cells] * 3
+        if sdims == dims:
+            strong = {"domain": sdims, "n_gpus": world, "ms_per_step": ms / args.steps, "value": value, "unit": "GDOF/s",
+                      "steps": args.steps, "warmup": args.warmup, "same_run_as_value": True}
+        else:
+            smg = build_performance_mg(om, P, args, sdims, op, rank, world, local, dist, collapse)
+            ks = max(3, min(args.steps, 10))
+            _, sms = timed_cycles(smg, args, barrier, dist, ks, 3)
+            sres, _ = smg.fas_vcycles(1, want_res=True)
+            strong = {"domain": sdims, "n_gpus": world, "ms_per_step": sms / ks, "value": sdims[0] ** 3 * ks / (sms * 1e-3) / 1e9,
+                      "unit": "GDOF/s", "steps": ks, "warmup": 3, "max_res_after": sres[0], "launches_per_step": None}
+            l0 = smg.stat("launches")
+            smg.fas_vcycles(1, want_res=args.max_res)
+            strong["launches_per_step"] = smg.stat("launches") - l0
+            smg.mg_deallocate_storage()
+            del smg
+            barrier()
+
+    # --- bitwise parity of the data plane that was just timed
+    parity = None
+    if not args.no_parity and args.op == "laplacian":
+        parity = parity_check(om, P, args.parity_cells, args.box, rank, world, local, dist, collapse)
 
     if rank != 0:
-        finish(world)
+        finish(world, dist)
         return
     cpu = None
     if not args.no_cpu_baseline and world == 1:
-        cb = cpu_reference_line(args)
+        cb = cpu_reference_line(dims, args.box, 3, 1, args.max_res, 60.0)
         cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     line = {"metric": "3D Poisson FAS V-cycle throughput", "value": value, "unit": "GDOF/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong" if args.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
             "roofline": roofline, "cycle_hbm_frac": cycle_frac, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": launches_per_step * args.steps if launches_per_step else None,
-            "launches_per_step": launches_per_step, "clocks": clocks, "residuals": res, "max_res_after": res_after,
-            "ref_style_unknowns_per_us": None}
+            "launches_per_step": launches_per_step, "fast_launches_per_step": fast_per_step, "general_launches_per_step": general_per_step,
+            "clocks": clocks, "residuals": res, "max_res_after": res_after,
+            # tests/test_performance.f90:90-92: n_boxes * box_size^3 (all boxes on all levels) per microsecond
+            "ref_style_unknowns_per_us": n_boxes_total * args.box ** 3 / (ms / args.steps * 1e3),
+            "timers_min_max_s": timers_minmax, "strong": strong, "parity_check": parity}
     print(json.dumps(line))
-    finish(world)
+    finish(world, dist)
+    if parity is not None and not parity.get("bitwise", False):
+        sys.stderr.write("bench.py: parity check FAILED: %r\n" % parity)
+        sys.exit(4)
 
 
-def finish(world):
-    """Multi-rank runs leave through os._exit once their output is flushed: the measurement is complete, and the
-    interpreter's unordered teardown of NCCL communicators, CUDA IPC mappings and the process group across ranks that
-    exit at different moments was observed to block (pass t, 2 and 4 GPUs: line printed, processes never exited)."""
+def finish(world, dist):
+    """Multi-rank runs: the library handles are already destroyed (ordered release, omg_comm.cu); destroy the process
+    group and leave through the interpreter.  A watchdog turns a teardown that blocks (round 1: runs that printed their
+    line and never exited) into a plain exit with a message instead of a hung box."""
     sys.stdout.flush()
     sys.stderr.flush()
-    if world > 1 and os.environ.get("OMG_BENCH_PLAIN_EXIT") != "1":   # =1: leave through the interpreter (teardown experiments)
+    if world == 1:
+        return
+    if os.environ.get("OMG_BENCH_PLAIN_EXIT") == "0":
         os._exit(0)
+    wd = threading.Timer(60.0, lambda: (sys.stderr.write("bench.py: teardown did not finish within 60 s; leaving through os._exit\n"),
+                                        sys.stderr.flush(), os._exit(0)))
+    wd.daemon = True
+    wd.start()
+    try:
+        dist.barrier()
+        dist.destroy_process_group()
+        sys.stderr.write("bench.py: rank %s teardown clean\n" % os.environ.get("RANK", "0"))
+    except Exception as e:      # noqa: BLE001
+        sys.stderr.write("bench.py: teardown raised %r\n" % (e,))
+    sys.stderr.flush()
 
 
 if __name__ == "__main__":

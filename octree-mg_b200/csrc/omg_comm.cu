@@ -72,33 +72,43 @@ constexpr int kMaxRanks = 32;
 // flags[channel][r]: number of put phases rank r has completed towards me on that channel (written by r through its
 // mapping of my flag array).  *epoch: number of put phases I have completed on the channel; all ranks run the same
 // sequence of phases, so "flags[p] >= my epoch" means p's puts of the current phase have landed.
-__device__ __forceinline__ void wait_flag(const volatile unsigned long long* f, unsigned long long want, int* err) {
+// The wait is an acquire (ld.acquire.sys): the peer's puts, released by its st.release.sys of the flag, are visible to
+// everything this thread does afterwards; callers follow it with a CTA barrier for the other threads.
+// timeout_ns = 0: wait for ever (MPI_Waitall semantics); else a peer that has not arrived after that long raises the
+// error word (omg_p2p_err_code: peer + channel) -- the host finds it at its next synchronisation point and poisons the
+// handle -- and the waiter returns false, so that the caller leaves its epoch alone.
+__device__ __forceinline__ bool wait_flag(const unsigned long long* f, unsigned long long want, int* err, unsigned long long timeout_ns, int code) {
   unsigned long long t0 = 0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-  while (*f < want) {
+  for (;;) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+    if (v >= want) return true;
     unsigned long long t1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-    if (t1 - t0 > 4000000000ull) { atomicExch(err, 1); break; }     // 4 s: the peer is gone; never hang the GPU
+    if (timeout_ns && t1 - t0 > timeout_ns) { *(volatile int*)err = code; __threadfence_system(); return false; }
     __nanosleep(100);
   }
+}
+__device__ __forceinline__ void signal_flag(unsigned long long* f, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(v) : "memory");
 }
 // signal = 1: raise my flag at the peers (my puts precede this kernel in stream order), wait for theirs, bump the epoch.
 // signal = 0: only wait for the peers' flags of the current epoch (puts that were signalled from inside a kernel).
 __global__ void k_signal_wait(PeerList pl, int channel, int me, int nranks, unsigned long long* const* __restrict__ peer_flags,
-                              unsigned long long* flags, unsigned long long* epoch, int* err, int signal) {
+                              unsigned long long* flags, unsigned long long* epoch, int* err, int signal, unsigned long long timeout_ns) {
   const int t = threadIdx.x;
   const unsigned long long e = *epoch + (signal ? 1ull : 0ull);
+  __shared__ int ok;
+  if (t == 0) ok = 1;
+  __syncthreads();
   if (t < pl.n) {
     const int p = pl.peer[t];
-    if (signal) {
-      __threadfence_system();
-      *(volatile unsigned long long*)(peer_flags[p] + channel * nranks + me) = e;
-    }
-    wait_flag(flags + channel * nranks + p, e, err);
-    __threadfence_system();
+    if (signal) signal_flag(peer_flags[p] + channel * nranks + me, e);     // release: my puts precede this kernel in stream order
+    if (!wait_flag(flags + channel * nranks + p, e, err, timeout_ns, omg_p2p_err_code(p, channel))) ok = 0;
   }
   __syncthreads();
-  if (t == 0 && signal) *epoch = e;
+  if (t == 0 && signal && ok) *epoch = e;       // a failed wait leaves the epoch alone: the handle is poisoned on the host
 }
 __global__ void k_bump_epoch(unsigned long long* epoch) { *epoch = *epoch + 1; }
 }  // namespace
@@ -141,10 +151,24 @@ struct omg_comm {
   bool p2p = false;
   unsigned long long* d_flags = nullptr;    // [OMG_P2P_CHANNELS][n], written by the peers
   unsigned long long** d_peer_flags = nullptr;
-  int* d_err = nullptr;
+  int* d_err = nullptr;                     // bounded-wait error word: mapped pinned host memory (h_err is the host view),
+  volatile int* h_err = nullptr;            // so the host reads it without touching the device
+  unsigned long long timeout_ns = 0;
   std::vector<void*> ipc_opened;
   void* ipc_scratch = nullptr;
 };
+
+// error word of the bounded waits + the bound itself (OMG_P2P_TIMEOUT_S seconds, default 120, 0 = wait for ever)
+static void alloc_err(omg_comm* c) {
+  int* hp = nullptr;
+  CCK(cudaHostAlloc(&hp, sizeof(int), cudaHostAllocMapped));
+  *hp = 0;
+  c->h_err = hp;
+  CCK(cudaHostGetDevicePointer(&c->d_err, hp, 0));
+  const char* e = getenv("OMG_P2P_TIMEOUT_S");
+  const double sec = (e && *e) ? atof(e) : 120.0;
+  c->timeout_ns = sec > 0 ? (unsigned long long)(sec * 1e9) : 0ull;
+}
 
 int omg_comm_unique_id(char out[128]) {
   static_assert(sizeof(ncclUniqueId) <= 128, "ncclUniqueId larger than the ABI buffer");
@@ -171,8 +195,7 @@ omg_comm* omg_comm_create_nccl(const char uid[128], int rank, int nranks, int de
       const size_t nf = (size_t)OMG_P2P_CHANNELS * nranks;
       CCK(cudaMalloc(&c->d_flags, nf * sizeof(unsigned long long)));
       CCK(cudaMemset(c->d_flags, 0, nf * sizeof(unsigned long long)));
-      CCK(cudaMalloc(&c->d_err, sizeof(int)));
-      CCK(cudaMemset(c->d_err, 0, sizeof(int)));
+      alloc_err(c);
       CCK(cudaMalloc(&c->d_peer_flags, nranks * sizeof(void*)));
       std::vector<void*> pf(nranks, nullptr);
       c->p2p = true;                                   // omg_comm_share clears it again (on every rank) if IPC is unavailable
@@ -202,26 +225,26 @@ omg_comm* omg_comm_create_local(omg_local_group* g, int rank, int device) {
   return c;
 }
 
-// Ordered release of the peer mappings (OMG_ORDERED_TEARDOWN=1; off until a multi-GPU pass has run it -- written after round
-// 1's GPU budget was spent).  Freeing memory a peer still has mapped is undefined (CUDA IPC rules) and
-// the ranks of a job leave at different moments, so when every rank deallocates (the reference's mg_deallocate_storage is
-// called by all of them) the order becomes: all ranks arrive (bounded flag wait over the mappings themselves -- a missing rank
-// gives up after the wait's time limit instead of hanging) -> everyone closes what it imported -> NCCL barrier -> the
-// exported memory is freed by the callers.  Returns true when the ranks met.
+// Ordered release of the peer mappings (default; OMG_ORDERED_TEARDOWN=0 switches it off).  Freeing memory a peer still
+// has mapped is undefined (CUDA IPC rules) and the ranks of a job leave at different moments, so when every rank
+// deallocates (the reference's mg_deallocate_storage is called by all of them) the order is: all ranks arrive (bounded
+// flag wait over the mappings themselves -- a missing rank makes the others give up after 20 s instead of hanging) ->
+// everyone closes what it imported -> NCCL barrier -> the exported memory is freed by the callers.  Returns true when
+// the ranks met.
 static bool teardown_rendezvous(omg_comm* c) {
   const char* e = getenv("OMG_ORDERED_TEARDOWN");
-  if (!e || !*e || atoi(e) == 0) return false;
+  if (e && *e && atoi(e) == 0) return false;
   if (!c->nccl || !c->p2p || c->n < 2 || c->n > kMaxRanks || !c->d_peer_flags || !c->d_flags || !c->d_err) return false;
-  int herr = 0;
-  if (cudaMemcpy(&herr, c->d_err, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess || herr) return false;   // an exchange already failed
+  if (*c->h_err) return false;   // an exchange already failed
   unsigned long long* ep = nullptr;
   if (cudaMalloc(&ep, sizeof(unsigned long long)) != cudaSuccess) return false;
   cudaMemset(ep, 0, sizeof(unsigned long long));
   PeerList pl; pl.n = 0;
   for (int r = 0; r < c->n; ++r) if (r != c->rank) pl.peer[pl.n++] = r;
-  k_signal_wait<<<1, 32>>>(pl, OMG_P2P_CHANNELS - 1, c->rank, c->n, c->d_peer_flags, c->d_flags, ep, c->d_err, 1);
+  const unsigned long long bound = 20000000000ull;          // 20 s: ranks that deallocate together arrive together
+  k_signal_wait<<<1, 32>>>(pl, OMG_P2P_CHANNELS - 1, c->rank, c->n, c->d_peer_flags, c->d_flags, ep, c->d_err, 1, bound);
   bool ok = cudaDeviceSynchronize() == cudaSuccess;
-  ok = ok && cudaMemcpy(&herr, c->d_err, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess && herr == 0;
+  ok = ok && *c->h_err == 0;
   cudaFree(ep);
   return ok;
 }
@@ -241,7 +264,7 @@ void omg_comm_destroy(omg_comm* c) {
   }
   if (c->d_flags) cudaFree(c->d_flags);
   if (c->ipc_scratch) cudaFree(c->ipc_scratch);
-  if (c->d_err) cudaFree(c->d_err);
+  if (c->h_err) cudaFreeHost((void*)c->h_err);
   if (c->d_peer_flags) cudaFree(c->d_peer_flags);
   if (c->nccl) nccl_api().CommDestroy(c->nccl);
   if (c->g) {
@@ -411,7 +434,7 @@ void omg_comm_signal_wait(omg_comm* c, int channel, const int* peers, int npeers
   if (npeers > 31) cfail("signal_wait: too many peers");
   PeerList pl; pl.n = npeers;
   for (int i = 0; i < npeers; ++i) pl.peer[i] = peers[i];
-  k_signal_wait<<<1, 32, 0, s>>>(pl, channel, c->rank, c->n, c->d_peer_flags, c->d_flags, epoch, c->d_err, signal);
+  k_signal_wait<<<1, 32, 0, s>>>(pl, channel, c->rank, c->n, c->d_peer_flags, c->d_flags, epoch, c->d_err, signal, c->timeout_ns);
   CCK(cudaGetLastError());
 }
 
@@ -422,8 +445,7 @@ void omg_comm_p2p_ptrs(omg_comm* c, unsigned long long* const** peer_flags, unsi
       const size_t nf = (size_t)OMG_P2P_CHANNELS * c->n;
       CCK(cudaMalloc(&c->d_flags, nf * sizeof(unsigned long long)));
       CCK(cudaMemset(c->d_flags, 0xff, nf * sizeof(unsigned long long)));    // "already arrived": waits return at once
-      CCK(cudaMalloc(&c->d_err, sizeof(int)));
-      CCK(cudaMemset(c->d_err, 0, sizeof(int)));
+      alloc_err(c);
       CCK(cudaMalloc(&c->d_peer_flags, c->n * sizeof(void*)));
       unsigned long long* scratch = nullptr;
       CCK(cudaMalloc(&scratch, nf * sizeof(unsigned long long)));
@@ -435,9 +457,5 @@ void omg_comm_p2p_ptrs(omg_comm* c, unsigned long long* const** peer_flags, unsi
   *peer_flags = c->d_peer_flags; *flags = c->d_flags; *err = c->d_err;
 }
 
-int omg_comm_p2p_error(omg_comm* c) {
-  if (!c->d_err) return 0;
-  int e = 0;
-  cudaMemcpy(&e, c->d_err, sizeof(int), cudaMemcpyDeviceToHost);
-  return e;
-}
+int omg_comm_p2p_error(omg_comm* c) { return c->h_err ? *c->h_err : 0; }
+unsigned long long omg_comm_p2p_timeout_ns(const omg_comm* c) { return c->timeout_ns; }

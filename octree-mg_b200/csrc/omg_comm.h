@@ -46,9 +46,15 @@ void omg_comm_signal_wait(omg_comm* c, int channel, const int* peers, int npeers
 // device pointers for in-kernel signalling: peer_flags[r] = rank r's flag array mapped here, flags = mine,
 // both indexed [channel * nranks + writer rank]; err = bounded-wait error word
 void omg_comm_p2p_ptrs(omg_comm* c, unsigned long long* const** peer_flags, unsigned long long** flags, int** err);
-// non-zero once a bounded wait has expired (NCCL back end)
+// non-zero once a bounded wait has expired: omg_p2p_err_code(peer, channel) of the first wait that gave up.  The word
+// lives in mapped pinned host memory, so this is a plain host load (no device synchronisation).
 int omg_comm_p2p_error(omg_comm* c);
+// the bound of the in-kernel waits in ns (OMG_P2P_TIMEOUT_S, default 120 s; 0 = unbounded like MPI_Waitall)
+unsigned long long omg_comm_p2p_timeout_ns(const omg_comm* c);
 enum { OMG_P2P_CHANNELS = 64 };
+__host__ __device__ inline int omg_p2p_err_code(int peer, int channel) { return 1 + peer + 64 * channel; }
+inline int omg_p2p_err_peer(int code) { return (code - 1) % 64; }
+inline int omg_p2p_err_channel(int code) { return (code - 1) / 64; }
 
 // all ranks call these at the same program points with matching segments (throws std::runtime_error)
 void omg_comm_exchange(omg_comm* c, const OmgXfer* segs, int nsegs, cudaStream_t s);

@@ -88,10 +88,11 @@ struct LevelHost {
   std::vector<int> h_order, h_put_ptr, h_put_item, h_launch;
   DevBuf<int> d_order, d_put_ptr, d_put_item, d_launch;
   DevBuf<unsigned int> d_done;
-  bool all_fast = false;                // every face of every box is FK_SAME or FK_PHYS (fast kernels apply)
+  bool all_fast = false;                // every face of every box has a kind the fast kernels serve (FK_SAME, FK_PHYS, FK_PLANE)
 };
 
-struct Program { std::vector<Step> steps; std::vector<TailOp> ops; DevBuf<TailOp> d_ops; cudaGraphExec_t graph = nullptr; int64_t launches_per_run = 0; };
+struct Program { std::vector<Step> steps; std::vector<TailOp> ops; DevBuf<TailOp> d_ops; cudaGraphExec_t graph = nullptr;
+                 int64_t launches_per_run = 0, fast_per_run = 0, general_per_run = 0; };
 
 }  // namespace
 
@@ -132,6 +133,9 @@ struct omg_handle {
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
   // stats / timers
   int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0, exchanges = 0, fused_smooths = 0, puts = 0;
+  // level kernels launched through the TMA-staged path (omg_fast.cu) / through the general one-CTA-per-box path
+  // (omg_kernels.cu); the single-CTA tail and the pack / exchange kernels count in neither
+  int64_t fast_launches = 0, general_launches = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_ms = 0.0;
   omg_comm* comm = nullptr;
@@ -308,7 +312,7 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
     L.h_fkind.assign((size_t)nb * 6, FK_NONE); L.h_farg.assign((size_t)nb * 6, -1); L.h_ftype.assign((size_t)nb * 6, 0);
     L.h_fkind_old.assign((size_t)nb * 6, FK_NONE); L.h_farg_old.assign((size_t)nb * 6, -1);
     L.h_parent.assign(nb, -1); L.h_coff.assign(nb, 0);
-    L.all_fast = true;
+    L.all_fast = true;                 // cleared below if a face keeps FK_NONE
     for (int b = 0; b < nb; ++b) {
       const int id = L.ids[b];
       const bool is_parent = has_children(h, id);
@@ -349,6 +353,7 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
           L.h_fkind[q] = FK_PHYS; L.h_farg[q] = -1; L.h_ftype[q] = (nbid == -1) ? 0 : nbid;
           L.h_fkind_old[q] = FK_PHYS; L.h_farg_old[q] = -1;
         }
+        if (L.h_fkind[q] == FK_NONE) L.all_fast = false;
       }
     }
     L.h_order.assign(nb, -1);                          // box -> index among the partition-face boxes
@@ -478,7 +483,7 @@ void sync_meta(omg_handle* h) {
       U.slot_of = L.d_order.p; U.ptr = L.d_put_ptr.p; U.item = L.d_put_item.p; U.peer_base = L.xg.d_peer_base.p; U.peer_stride = L.xg.d_peer_stride.p;
       unsigned long long* const* pf = nullptr; unsigned long long* fl = nullptr; int* er = nullptr;
       try { omg_comm_p2p_ptrs(h->comm, &pf, &fl, &er); } catch (const std::exception& e) { fail(e.what()); }
-      U.peer_flags = pf; U.flags = fl; U.err = er;
+      U.peer_flags = pf; U.flags = fl; U.err = er; U.timeout_ns = omg_comm_p2p_timeout_ns(h->comm);
       U.epoch = h->d_epoch.p + (L.lvl - OMG_LVL_LO); U.done = L.d_done.p;
     }
     // tail fast path (omg_ops.cuh simple_*): every face a physical boundary or a local same-level neighbour
@@ -623,6 +628,23 @@ struct Builder {
   }
 };
 
+// A bounded in-kernel wait for a peer's halo signal expired (omg_comm.cu wait_flag): the cycle went on with stale
+// planes, so everything computed since is void.  The error word lives in mapped host memory: checking it is a host
+// load.  Called at every host synchronisation point and at the start of every entry point; once raised the handle
+// stays poisoned (the reference's MPI_Waitall would have blocked for ever or aborted the job).
+void check_p2p(omg_handle* h) {
+  if (!h->comm) return;
+  const int code = omg_comm_p2p_error(h->comm);
+  if (!code) return;
+  const int ch = omg_p2p_err_channel(code);
+  char buf[256];
+  std::snprintf(buf, sizeof buf, "halo exchange timed out: rank %d waited more than %.0f s for rank %d on %s (peer gone or too far behind; "
+                "OMG_P2P_TIMEOUT_S sets the bound, 0 = none); results of this handle are invalid from here on",
+                h->my_rank, omg_comm_p2p_timeout_ns(h->comm) * 1e-9, omg_p2p_err_peer(code),
+                ch == OMG_P2P_CHANNELS - 1 ? "the teardown rendezvous" : ("level " + std::to_string(ch + OMG_LVL_LO)).c_str());
+  fail(buf);
+}
+
 // ---- executor ------------------------------------------------------------------------------------
 void need_comm(omg_handle* h) {
   if (!h->comm) fail("several ranks but no communicator: call omg_comm_init (mg_comm_init) after omg_set_tree");
@@ -728,7 +750,7 @@ void exec_steps(omg_handle* h, Program& P) {
         if (st.b == 3) {   // in-kernel exchange: whole level in one launch
           if (L.nb) {
             if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, L.nb <= h->bnd_first_boxes ? L.d_launch.p : nullptr, L.nb, 1, s)) fail("fused smoother does not apply to this level");
-            h->launches++; h->exchanges++; h->fused_smooths++;
+            h->launches++; h->exchanges++; h->fused_smooths++; h->fast_launches++;
           }
           // emulated ranks share one GPU: a kernel must never wait for a kernel that may not be running, so the ranks
           // meet on the host and order their streams with events; the in-kernel waits then return at once
@@ -741,35 +763,39 @@ void exec_steps(omg_handle* h, Program& P) {
         const int* list = st.b == 1 ? L.d_bnd.p : st.b == 2 ? L.d_int.p : nullptr;
         const int nlist = st.b == 1 ? (int)L.h_bnd.size() : st.b == 2 ? (int)L.h_int.size() : 0;
         if (st.b && nlist == 0) break;
-        if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; }
-        else if (!(h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, 0, s)))
-          omgk::smooth(L.dev, PD, st.a, st.b ? list : nullptr, nlist, s);
+        if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; h->general_launches++; }
+        else if (h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, 0, s)) h->fast_launches++;
+        else { omgk::smooth(L.dev, PD, st.a, st.b ? list : nullptr, nlist, s); h->general_launches++; }
         h->launches++;
       } break;
       case S_RESID: {
         LevelHost& L = h->L(st.l);
         double* slot = st.a >= 0 ? h->d_scal.p + st.a : nullptr;
-        if (!(h->fast_kernels && omgf::resid_max(L.dev, PD, L.all_fast, slot, s))) omgk::resid(L.dev, PD, slot, s);
+        if (h->fast_kernels && omgf::resid_max(L.dev, PD, L.all_fast, slot, s)) h->fast_launches++;
+        else { omgk::resid(L.dev, PD, slot, s); h->general_launches++; }
         h->launches++;
       } break;
-      case S_RESTRICT: omgk::restrict2(h->L(st.l).dev, h->L(st.l - 1).dev, st.a, st.b, s); h->launches++; break;
+      case S_RESTRICT: omgk::restrict2(h->L(st.l).dev, h->L(st.l - 1).dev, st.a, st.b, s); h->launches++; h->general_launches++; break;
       case S_RESID_RESTRICT: {
         LevelHost& L = h->L(st.l);
-        if (!(h->fast_kernels && omgf::resid_restrict(L.dev, h->L(st.l - 1).dev, PD, L.all_fast, s))) {
+        if (h->fast_kernels && omgf::resid_restrict(L.dev, h->L(st.l - 1).dev, PD, L.all_fast, s)) h->fast_launches++;
+        else {
           omgk::resid(L.dev, PD, nullptr, s); omgk::restrict2(L.dev, h->L(st.l - 1).dev, IPHI, IRES, s); h->launches++;
+          h->general_launches += 2;
         }
         h->launches++;
       } break;
       case S_CRHS: {
         LevelHost& L = h->L(st.l);
-        if (!(h->fast_kernels && omgf::crhs(L.dev, PD, L.all_fast, s))) omgk::crhs(L.dev, PD, s);
+        if (h->fast_kernels && omgf::crhs(L.dev, PD, L.all_fast, s)) h->fast_launches++;
+        else { omgk::crhs(L.dev, PD, s); h->general_launches++; }
         h->launches++;
       } break;
       case S_OLDPL: omgk::oldpl(h->L(st.l).dev, PD, s); h->launches++; break;
       case S_CORR_PROLONG: {
         LevelHost& L = h->L(st.l);
-        if (!(h->fast_kernels && omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, s)))
-          omgk::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, s);
+        if (h->fast_kernels && omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, s)) h->fast_launches++;
+        else { omgk::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, s); h->general_launches++; }
         h->launches++;
       } break;
       case S_RB_FILL: omgk::rb_fill(h->L(st.l).dev, h->L(st.l - 1).dev, PD, 0, st.a, s); h->launches++; break;
@@ -828,17 +854,17 @@ void run_program(omg_handle* h, Program& P) {
   if (!graph_ok) { exec_steps(h, P); return; }
   if (!P.graph) {
     cudaGraph_t g = nullptr;
-    const int64_t l0 = h->launches;
+    const int64_t l0 = h->launches, f0 = h->fast_launches, g0 = h->general_launches;
     CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
     try { exec_steps(h, P); } catch (...) { cudaStreamEndCapture(h->stream, &g); if (g) cudaGraphDestroy(g); throw; }
     CK(cudaStreamEndCapture(h->stream, &g));
     CK(cudaGraphInstantiate(&P.graph, g, 0));
     CK(cudaGraphDestroy(g));
-    P.launches_per_run = h->launches - l0;
-    h->launches = l0;
+    P.launches_per_run = h->launches - l0; P.fast_per_run = h->fast_launches - f0; P.general_per_run = h->general_launches - g0;
+    h->launches = l0; h->fast_launches = f0; h->general_launches = g0;
   }
   CK(cudaGraphLaunch(P.graph, h->stream));
-  h->launches += P.launches_per_run;
+  h->launches += P.launches_per_run; h->fast_launches += P.fast_per_run; h->general_launches += P.general_per_run;
   h->graph_launches++;
 }
 
@@ -881,6 +907,7 @@ void check_supported(omg_handle* h) {
 
 void fas_vcycle(omg_handle* h, int has_highest, int highest_lvl, int standalone, int want_res, double* max_res) {
   CK(cudaSetDevice(h->device));
+  check_p2p(h);
   sync_meta(h);
   check_supported(h);
   if (has_highest && (highest_lvl < h->lowest || highest_lvl > h->highest)) fail("mg_fas_vcycle: highest_lvl out of range");
@@ -898,11 +925,13 @@ void fas_vcycle(omg_handle* h, int has_highest, int highest_lvl, int standalone,
   if (want_res && max_res) {
     CK(cudaMemcpyAsync(max_res, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    check_p2p(h);
   }
 }
 
 void fas_fmg(omg_handle* h, int have_guess, int want_res, double* max_res) {
   CK(cudaSetDevice(h->device));
+  check_p2p(h);
   sync_meta(h);
   check_supported(h);
   char key[64];
@@ -919,6 +948,7 @@ void fas_fmg(omg_handle* h, int have_guess, int want_res, double* max_res) {
   if (want_res && max_res) {
     CK(cudaMemcpyAsync(max_res, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    check_p2p(h);
   }
 }
 
@@ -1009,6 +1039,7 @@ void push_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxe
     h->launches++; h->bytes_h2d += (int64_t)n * slab * sizeof(double);
   }
   CK(cudaStreamSynchronize(h->stream));
+  check_p2p(h);
 }
 
 void pull_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxes, double* const* ptrs, double* packed, int with_ghosts, int shell = 1) {
@@ -1038,6 +1069,7 @@ void pull_level(omg_handle* h, LevelHost& L, int v, const std::vector<int>& boxe
   }
   drain(prev);
   CK(cudaStreamSynchronize(h->stream));
+  check_p2p(h);
 }
 
 int check_iv(omg_handle* h, int iv) {
@@ -1271,6 +1303,7 @@ int omg_fas_vcycles(omg_handle* h, int n, double* residuals) {
   OMG_TRY(h, {
     CK(cudaSetDevice(h->device));
     if (n < 0 || n > 256) fail("omg_fas_vcycles: n out of range (0..256)");
+    check_p2p(h);
     sync_meta(h);
     check_supported(h);
     const int want = residuals ? 1 : 0;
@@ -1287,6 +1320,7 @@ int omg_fas_vcycles(omg_handle* h, int n, double* residuals) {
     CK(cudaEventRecord(h->ev1, h->stream));
     if (want && n) CK(cudaMemcpyAsync(residuals, h->d_scal.p + SCAL_RESHIST, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    check_p2p(h);
     float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1)); h->last_ms = ms;
     h->timer_acc[0] += ms * 1e-3;
   });
@@ -1299,6 +1333,7 @@ int omg_fas_vcycles(omg_handle* h, int n, double* residuals) {
 int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* out) {
   OMG_TRY(h, {
     CK(cudaSetDevice(h->device));
+    check_p2p(h);
     sync_meta(h);
     check_supported(h);
     const std::string w(what);
@@ -1324,6 +1359,7 @@ int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* ou
     try { run_program(h, P); } catch (...) { h->use_graph = ug; P.d_ops.free(); throw; }
     h->use_graph = ug;
     CK(cudaStreamSynchronize(h->stream));
+    check_p2p(h);
     P.d_ops.free();
     if (out) CK(cudaMemcpy(out, h->d_scal.p + SCAL_MAXRES, sizeof(double), cudaMemcpyDeviceToHost));
   });
@@ -1332,6 +1368,7 @@ int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* ou
 int omg_fill_ghost_cells_lvl(omg_handle* h, int lvl, int iv) {
   OMG_TRY(h, {
     CK(cudaSetDevice(h->device));
+    check_p2p(h);
     sync_meta(h);
     const int v = check_iv(h, iv);
     if (lvl < h->lowest) fail("fill_ghost_cells_lvl: lvl < lowest_lvl");
@@ -1352,6 +1389,7 @@ int omg_fill_ghost_cells_lvl(omg_handle* h, int lvl, int iv) {
 int omg_restrict_lvl(omg_handle* h, int iv, int lvl) {
   OMG_TRY(h, {
     CK(cudaSetDevice(h->device));
+    check_p2p(h);
     sync_meta(h);
     const int v = check_iv(h, iv);
     if (lvl <= h->lowest || lvl > h->highest) fail("cannot restrict lvl <= lowest_lvl");
@@ -1486,7 +1524,7 @@ int omg_exchange_plan(const omg_tree_desc* t, int me, int phase, int lvl, int pe
   return 0;
 }
 
-int omg_sync(omg_handle* h) { OMG_TRY(h, { CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream)); }); }
+int omg_sync(omg_handle* h) { OMG_TRY(h, { CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream)); check_p2p(h); }); }
 
 // mg_timers_show (src/m_data_structures.f90:562-581): the seven timers mg_add_timers registers
 // (src/m_multigrid.f90:72-81), accumulated seconds on this rank.  The two totals are always measured (CUDA events
@@ -1509,6 +1547,8 @@ int64_t omg_stat(omg_handle* h, const char* key) {
   if (!h) return -1;
   const std::string k(key);
   if (k == "launches") return h->launches;
+  if (k == "fast_launches") return h->fast_launches;         // level kernels on the TMA-staged path (omg_fast.cu)
+  if (k == "general_launches") return h->general_launches;   // level kernels on the general path (omg_kernels.cu)
   if (k == "graph_launches") return h->graph_launches;
   if (k == "bytes_h2d") return h->bytes_h2d;
   if (k == "bytes_d2h") return h->bytes_d2h;

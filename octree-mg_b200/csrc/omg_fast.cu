@@ -1,5 +1,6 @@
-// omg_fast.cu -- tuned sm_100a kernels for big uniform levels (box size 16 or 32, every ghost face of
-// every box FK_SAME or FK_PHYS).  One CTA per tile = (box, slab of KT k-planes).  The tile and its ghost
+// omg_fast.cu -- tuned sm_100a kernels for levels of box size 16 or 32 (any face kind: FK_SAME / FK_PHYS ghost
+// layers are staged or evaluated in shared memory, FK_PLANE faces -- refinement boundaries, faces of another rank --
+// come from the level's plane pool).  One CTA per tile = (box, slab of KT k-planes).  The tile and its ghost
 // layer are staged in shared memory with TMA bulk copies (cp.async.bulk, completion on an mbarrier):
 // thanks to the colour-split layout a colour half-sweep needs exactly the OTHER colour of the box, which
 // is one contiguous 16 KiB block, plus 1 KiB (z) / 16 x 64 B (y) face slices of the neighbours' blocks.
@@ -47,17 +48,26 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// bounded wait for a peer's flag (see omg_comm.cu): never hang the GPU on a rank that is gone
-__device__ __forceinline__ void wait_flag(const volatile unsigned long long* f, unsigned long long want, int* err) {
+// wait for a peer's flag (same protocol as omg_comm.cu): an acquire load, so that the peer's puts -- released by its
+// st.release.sys of the flag -- are visible afterwards; bounded by timeout_ns (0 = wait for ever): a peer that does not
+// arrive raises the error word, which the host finds at its next synchronisation point (the handle is then poisoned)
+__device__ __forceinline__ bool wait_flag(const unsigned long long* f, unsigned long long want, int* err, unsigned long long timeout_ns, int code) {
   unsigned long long t0 = 0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-  while (*f < want) {
+  for (;;) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+    if (v >= want) return true;
     unsigned long long t1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-    if (t1 - t0 > 4000000000ull) { atomicExch(err, 1); break; }
+    if (timeout_ns && t1 - t0 > timeout_ns) { *(volatile int*)err = code; __threadfence_system(); return false; }
     __nanosleep(64);
   }
 }
+__device__ __forceinline__ void signal_flag(unsigned long long* f, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(v) : "memory");
+}
+__device__ __forceinline__ double ld_plane(const double* p) { return __ldcg(p); }   // peer-written planes: L2, never the read-only path
 #define OMG_DYN_SMEM(name, al) extern __shared__ __align__(al) unsigned char name[]
 #define OMG_LAUNCH(kern, grid, smem, stream, ...) kern<<<(grid), kThreads, (smem), (stream)>>>(__VA_ARGS__)
 #define OMG_PDL_ASM() do { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); asm volatile("griddepcontrol.wait;" ::: "memory"); } while (0)
@@ -153,7 +163,8 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
   // the peers' faces of the previous half-sweep must have landed in the plane pool before they are read below
   if (bnd_put && tid >= 64 && tid < 64 + L.put.n_peers)
-    wait_flag(L.put.flags + L.put.channel * L.put.nranks + L.put.peers[tid - 64], *L.put.epoch, L.put.err);
+    wait_flag(L.put.flags + L.put.channel * L.put.nranks + L.put.peers[tid - 64], *L.put.epoch, L.put.err, L.put.timeout_ns,
+              1 + L.put.peers[tid - 64] + 64 * L.put.channel);
   __syncthreads();
 
   if (tid < 32) {
@@ -207,20 +218,20 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
 #pragma unroll
   for (int f = 0; f < 6; ++f) any_plane = any_plane || (kind[f] == FK_PLANE);
   if (any_plane) {
-    const double* __restrict__ gpl = gpl_cur(L);
+    const double* gpl = gpl_cur(L);
     if (!zlo_in && kind[4] == FK_PLANE)
-      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.zlo[j][m] = gpl[(size_t)arg[4] * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)]; }
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.zlo[j][m] = ld_plane(gpl + (size_t)arg[4] * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)); }
     if (!zhi_in && kind[5] == FK_PLANE)
-      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.zhi[j][m] = gpl[(size_t)arg[5] * NC * NC + j * NC + 2 * m + ((oc ^ j) & 1)]; }
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.zhi[j][m] = ld_plane(gpl + (size_t)arg[5] * NC * NC + j * NC + 2 * m + ((oc ^ j) & 1)); }
     if (kind[2] == FK_PLANE)
-      for (int r = tid; r < KT * HX; r += kThreads) { const int kk = r / HX, m = r % HX, k = k0 + kk; S.ylo[kk][m] = gpl[(size_t)arg[2] * NC * NC + k * NC + 2 * m + ((oc ^ (k + 1)) & 1)]; }
+      for (int r = tid; r < KT * HX; r += kThreads) { const int kk = r / HX, m = r % HX, k = k0 + kk; S.ylo[kk][m] = ld_plane(gpl + (size_t)arg[2] * NC * NC + k * NC + 2 * m + ((oc ^ (k + 1)) & 1)); }
     if (kind[3] == FK_PLANE)
-      for (int r = tid; r < KT * HX; r += kThreads) { const int kk = r / HX, m = r % HX, k = k0 + kk; S.yhi[kk][m] = gpl[(size_t)arg[3] * NC * NC + k * NC + 2 * m + ((oc ^ k) & 1)]; }
+      for (int r = tid; r < KT * HX; r += kThreads) { const int kk = r / HX, m = r % HX, k = k0 + kk; S.yhi[kk][m] = ld_plane(gpl + (size_t)arg[3] * NC * NC + k * NC + 2 * m + ((oc ^ k) & 1)); }
     if (kind[0] == FK_PLANE || kind[1] == FK_PLANE)
       for (int r = tid; r < KT * NC; r += kThreads) {
         const int kk = r / NC, j = r % NC, k = k0 + kk;
         const int f = (colour ^ ((j + k) & 1)) ? 1 : 0;
-        if (kind[f] == FK_PLANE) S.xg[kk][j] = gpl[(size_t)arg[f] * NC * NC + k * NC + j];
+        if (kind[f] == FK_PLANE) S.xg[kk][j] = ld_plane(gpl + (size_t)arg[f] * NC * NC + k * NC + j);
       }
   }
 
@@ -355,9 +366,11 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
       if (prev == (unsigned int)(L.put.n_bnd * TILES) - 1u) {
         *L.put.done = 0u;
         __threadfence_system();
-        for (int q = 0; q < L.put.n_peers; ++q)
-          *(volatile unsigned long long*)(L.put.peer_flags[L.put.peers[q]] + L.put.channel * L.put.nranks + L.put.me) = e + 1ull;
-        *L.put.epoch = e + 1ull;
+        if (*(volatile int*)L.put.err == 0) {      // after a failed wait the exchange stops: no signal, epoch left alone
+          for (int q = 0; q < L.put.n_peers; ++q)
+            signal_flag(L.put.peer_flags[L.put.peers[q]] + L.put.channel * L.put.nranks + L.put.me, e + 1ull);
+          *L.put.epoch = e + 1ull;
+        }
       }
     }
   }
@@ -555,19 +568,19 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   }
   {
     // ghost planes materialised elsewhere (refinement boundaries, faces owned by another rank)
-    const double* __restrict__ gpl = gpl_cur(L);
+    const double* gpl = gpl_cur(L);
     if (!zlo_in && kind[4] == FK_PLANE)
-      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.zlo[(i + j + 1) & 1][j][i >> 1] = gpl[(size_t)arg[4] * NC * NC + r]; }
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.zlo[(i + j + 1) & 1][j][i >> 1] = ld_plane(gpl + (size_t)arg[4] * NC * NC + r); }
     if (!zhi_in && kind[5] == FK_PLANE)
-      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.zhi[(i + j) & 1][j][i >> 1] = gpl[(size_t)arg[5] * NC * NC + r]; }
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.zhi[(i + j) & 1][j][i >> 1] = ld_plane(gpl + (size_t)arg[5] * NC * NC + r); }
     if (kind[2] == FK_PLANE)
-      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, i = r % NC, k = k0 + kk; S.ylo[(i + k + 1) & 1][kk][i >> 1] = gpl[(size_t)arg[2] * NC * NC + k * NC + i]; }
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, i = r % NC, k = k0 + kk; S.ylo[(i + k + 1) & 1][kk][i >> 1] = ld_plane(gpl + (size_t)arg[2] * NC * NC + k * NC + i); }
     if (kind[3] == FK_PLANE)
-      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, i = r % NC, k = k0 + kk; S.yhi[(i + k) & 1][kk][i >> 1] = gpl[(size_t)arg[3] * NC * NC + k * NC + i]; }
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, i = r % NC, k = k0 + kk; S.yhi[(i + k) & 1][kk][i >> 1] = ld_plane(gpl + (size_t)arg[3] * NC * NC + k * NC + i); }
     if (kind[0] == FK_PLANE)
-      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xlo[kk][j] = gpl[(size_t)arg[0] * NC * NC + (k0 + kk) * NC + j]; }
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xlo[kk][j] = ld_plane(gpl + (size_t)arg[0] * NC * NC + (k0 + kk) * NC + j); }
     if (kind[1] == FK_PLANE)
-      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xhi[kk][j] = gpl[(size_t)arg[1] * NC * NC + (k0 + kk) * NC + j]; }
+      for (int r = tid; r < KT * NC; r += kThreads) { const int kk = r / NC, j = r % NC; S.xhi[kk][j] = ld_plane(gpl + (size_t)arg[1] * NC * NC + (k0 + kk) * NC + j); }
   }
   if constexpr (VC) {
     // ghost layer of eps: stored ghost faces (host data, any face kind), de-interleaved by colour

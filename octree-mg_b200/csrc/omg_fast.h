@@ -1,6 +1,9 @@
-// omg_fast.h -- tuned sm_100a kernels for big uniform levels (box size 16 / 32, every ghost face
-// FK_SAME or FK_PHYS).  Each launcher returns false when it does not apply; the caller then uses
-// the general path of omg_kernels.cu.  Results are bitwise identical between the two paths.
+// omg_fast.h -- tuned sm_100a kernels for levels of box size 16 / 32.  Every face kind is served: FK_SAME and
+// FK_PHYS ghost layers are staged / evaluated in shared memory, FK_PLANE faces (refinement boundaries, faces owned
+// by another rank) are read from the level's plane pool -- so AMR and distributed levels take this path too.
+// Each launcher returns false when it does not apply (other box sizes, ahelmholtz in some modes, all_fast == false);
+// the caller then uses the general path of omg_kernels.cu and counts the launch as "general_launches"
+// (omg_stat).  Results are bitwise identical between the two paths.
 #pragma once
 #include <cuda_runtime.h>
 #include "omg_device.cuh"

@@ -71,9 +71,12 @@ static inline void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t
   emu::g_tx_done += bytes;
 }
 // the emulated ranks run one after the other, so a flag a kernel would wait for must already be there
-static inline void wait_flag(const volatile unsigned long long* f, unsigned long long want, int*) {
-  if (*f < want) emu::violation("wait_flag: the peer's signal is missing (the GPU would time out)");
+static inline bool wait_flag(const unsigned long long* f, unsigned long long want, int*, unsigned long long, int) {
+  if (__atomic_load_n(f, __ATOMIC_ACQUIRE) < want) emu::violation("wait_flag: the peer's signal is missing (the GPU would time out)");
+  return true;
 }
+static inline void signal_flag(unsigned long long* f, unsigned long long v) { __atomic_store_n(f, v, __ATOMIC_RELEASE); }
+static inline double ld_plane(const double* p) { return *p; }
 #define OMG_DYN_SMEM(name, al) unsigned char* name = emu::g_smem
 #define OMG_PDL_ASM() do {} while (0)
 #define OMG_LAUNCH(kern, grid, smem, stream, ...) emu::launch((grid), 256, (smem), [&]() { kern(__VA_ARGS__); })

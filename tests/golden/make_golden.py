@@ -29,6 +29,10 @@ CASES = {
     "refinement3_box8_fmg": dict(kind="amr", n=32, box=8, levels=3, fmg=True, its=3),
     "uniform32_box8_gs_vcycle": dict(kind="uniform", n=32, box=8, fmg=False, its=4, smoother=P.mg_smoother_gs),
     "ahelmholtz32_mixed_fmg": dict(kind="uniform", n=32, box=8, fmg=True, its=3, op=P.mg_ahelmholtz, bc="mixed", lam=0.5),
+    # BASELINE.json configs[0]: test_uniform_grid 128^3, box 16, 10 iterations, FMG and V-cycle, GSRB and the program's own GS
+    "config0_uniform128_box16_fmg": dict(kind="uniform", n=128, box=16, fmg=True, its=10),
+    "config0_uniform128_box16_vcycle": dict(kind="uniform", n=128, box=16, fmg=False, its=10),
+    "config0_uniform128_box16_gs_fmg": dict(kind="uniform", n=128, box=16, fmg=True, its=10, smoother=P.mg_smoother_gs),
     "noncubic64x32x32_box16_fmg": dict(kind="uniform", n=[64, 32, 32], box=16, fmg=True, its=3, bc="dirichlet0"),
     # implicit diffusion steps (src/m_diffusion.f90): residuals = [last max residual, number of V-cycles added] per step
     "diffusion32_box8_order1": dict(kind="diffusion", n=32, box=8, order=1, steps=2, op=P.mg_helmholtz),

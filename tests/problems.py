@@ -93,7 +93,7 @@ def all_ids(mg):
 
 
 def uniform_problem(cls, n, box, operator_type=mg_laplacian, smoother=mg_smoother_gsrb, bc="callback", lam=0.0,
-                    periodic=(False, False, False), load_balance="default", **kw):
+                    periodic=(False, False, False), load_balance="default", setup=None, after_alloc=None, **kw):
     """test_uniform_grid semantics.  bc: 'callback' (Dirichlet planes of the exact solution),
     'dirichlet0', 'neumann0', 'mixed' (Neumann-0 everywhere, Dirichlet on -x), 'continuous_x'."""
     n3 = [n] * 3 if np.isscalar(n) else list(n)
@@ -117,6 +117,8 @@ def uniform_problem(cls, n, box, operator_type=mg_laplacian, smoother=mg_smoothe
         else:
             raise ValueError(bc)
     mg.mg_set_methods()
+    if setup is not None:          # e.g. host-mirror extensions that must be set before the partition is made
+        setup(mg)
     dr = [1.0 / n3[0]] * 3
     mg.mg_build_rectangle(n3, box, dr, [0.0] * 3, list(periodic))
     if load_balance == "default":
@@ -127,6 +129,8 @@ def uniform_problem(cls, n, box, operator_type=mg_laplacian, smoother=mg_smoothe
         mg.mg_load_balance()
         mg.mg_load_balance_parents()
     mg.mg_allocate_storage()
+    if after_alloc is not None:    # e.g. the communicator of a multi-process run (omg_comm_init follows omg_set_tree)
+        after_alloc(mg)
     owned = hasattr(mg, "my_ids")
     for lvl in range(mg.lowest_lvl, mg.highest_lvl + 1):
         nc = mg.box_size_lvl(lvl)

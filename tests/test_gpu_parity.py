@@ -21,6 +21,15 @@ def check_histories(h_o, h_g):
     assert h_o == h_g, "residual histories differ in the last bits: %r vs %r" % (h_o, h_g)
 
 
+def assert_fast_path(mg, general_ok=False):
+    """the TMA-staged kernels of omg_fast.cu must have run (omg_stat counters): a silent fall-back to the general
+    one-CTA-per-box path would keep the numbers right and the performance claim wrong"""
+    f, g = mg.stat("fast_launches"), mg.stat("general_launches")
+    assert f > 0, "no TMA-staged kernel ran (fast %d, general %d)" % (f, g)
+    if not general_ok:
+        assert g == 0, "level kernels fell back to the general path (fast %d, general %d)" % (f, g)
+
+
 def check_tolerance(orc, mg):
     d = state_diff(orc, mg, variables=(1,))["phi"]
     assert d[0] <= SOL_RTOL * d[1]
@@ -39,6 +48,43 @@ def test_uniform_grid_laplacian(oracle, product, n, box, fmg):
     assert_state_equal(orc, mg)
     # the reference test's own pass criterion: the error against the manufactured solution collapses
     assert P.max_error(mg, i_sol) < (1e-6 if fmg else 1e-4)
+    if box == 16:
+        assert_fast_path(mg)
+    else:
+        assert mg.stat("fast_launches") == 0 and mg.stat("general_launches") > 0     # box 8: general path only
+
+
+@pytest.mark.parametrize("fmg", [False, True])
+@pytest.mark.parametrize("smoother", [P.mg_smoother_gsrb, P.mg_smoother_gs])
+def test_baseline_config0_uniform_128(oracle, product, smoother, fmg):
+    """BASELINE.json configs[0] literally: tests/test_uniform_grid 128^3, box size 16, Dirichlet callback (the reference
+    program's boundary condition), 10 iterations, FMG (`t`) and V-cycles (`f`), with the north-star's GSRB and
+    with the program's own mg_smoother_gs.  588 boxes, levels 1..-5, four of them on the TMA-staged kernels."""
+    orc, i_sol = P.uniform_problem(oracle.OracleMg, 128, 16, smoother=smoother)
+    mg, _ = P.uniform_problem(product.Mg, 128, 16, smoother=smoother)
+    assert mg.n_boxes == 588 and mg.lowest_lvl == -5
+    h_o = P.run_cycles(orc, 10, fmg)
+    h_g = P.run_cycles(mg, 10, fmg)
+    check_histories(h_o, h_g)
+    check_tolerance(orc, mg)
+    assert_state_equal(orc, mg)
+    assert P.max_error(mg, i_sol) < 1e-9       # "max solution error" of the program after 10 iterations: rounding level
+    if smoother == P.mg_smoother_gsrb:
+        assert_fast_path(mg)
+    else:                                      # the lexicographic in-box sweep runs on the general path; transfers stay fast
+        assert_fast_path(mg, general_ok=True)
+
+
+def test_baseline_config1_performance_256(oracle, product):
+    """BASELINE.json configs[1] (tests/test_performance: rhs = 1, homogeneous Dirichlet, V(2,2) GSRB cycles) at 256^3 /
+    box 16: 4681 boxes, five levels on the TMA-staged kernels -- the same program the bench times at 512^3, bitwise
+    against the oracle incl. the full state (phi, rhs, old, res and phi's ghost faces) of every level."""
+    orc = P.performance_problem(oracle.OracleMg, 256, 16)
+    mg = P.performance_problem(product.Mg, 256, 16)
+    assert mg.n_boxes == 4681
+    check_histories(P.run_cycles(orc, 4, False), P.run_cycles(mg, 4, False))
+    assert_state_equal(orc, mg)
+    assert_fast_path(mg)
 
 
 def test_performance_problem(oracle, product):
@@ -47,6 +93,7 @@ def test_performance_problem(oracle, product):
     mg = P.performance_problem(product.Mg, 64, 16)
     check_histories(P.run_cycles(orc, 4, False), P.run_cycles(mg, 4, False))
     assert_state_equal(orc, mg)
+    assert_fast_path(mg)
 
 
 @pytest.mark.parametrize("op,bc,lam", [
@@ -220,6 +267,20 @@ def test_fast_kernels_variable_coefficient(oracle, product, op, bc, lam, n, box)
     check_histories(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
     check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
     assert_state_equal(orc, mg)
+    assert_fast_path(mg)
+
+
+def test_refinement_on_fast_kernels(oracle, product):
+    """BASELINE.json configs[2] with boxes of 16 (`test_refinement 3 16 64 64 64`): levels with refinement-boundary faces
+    (FK_PLANE, filled by sides_rb) run the TMA-staged kernels too -- only k_rb_fill / k_oldpl are general-path helpers"""
+    orc, i_sol = P.refinement_problem(oracle.OracleMg, 3, 16, 64)
+    mg, _ = P.refinement_problem(product.Mg, 3, 16, 64)
+    f0, g0 = mg.stat("fast_launches"), mg.stat("general_launches")
+    check_histories(P.run_cycles(orc, 3, True), P.run_cycles(mg, 3, True))
+    check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
+    assert P.max_error(mg, i_sol, leaves_only=True) < 1e-3
+    assert mg.stat("fast_launches") > f0 and mg.stat("general_launches") == g0
 
 
 def test_golden_fixtures_on_the_device(product):

@@ -175,9 +175,6 @@ def test_copy_to_and_from_tree(product, amr):
             off += n2 ** 3
 
 
-@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1",
-                    reason="tail_simple = 2 (boundary planes, variable coefficients in the tail fast path) was written after the "
-                           "round's GPU budget was spent: host-verified only (tests/test_device_host.py); set OMG_TEST_UNVERIFIED=1")
 @pytest.mark.parametrize("op,bc,lam", [(P.mg_laplacian, "callback", 0.0), (P.mg_helmholtz, "callback", 2.5),
                                        (P.mg_vlaplacian, "mixed", 0.0), (P.mg_vhelmholtz, "neumann0", 1.0),
                                        (P.mg_ahelmholtz, "mixed", 0.5)])
@@ -190,9 +187,6 @@ def test_tail_fast_path_all_variants(oracle, product, op, bc, lam):
     assert_state_equal(orc, mg)
 
 
-@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1",
-                    reason="option pdl (programmatic dependent launch of the TMA-staged kernels) was written after the round's "
-                           "GPU budget was spent; off by default; set OMG_TEST_UNVERIFIED=1")
 @pytest.mark.parametrize("op,lam", [(P.mg_laplacian, 0.0), (P.mg_vhelmholtz, 1.5)])
 @pytest.mark.parametrize("graph", [0, 1])
 def test_pdl_launches_change_nothing(oracle, product, op, lam, graph):

@@ -163,7 +163,6 @@ def test_cpp_refinement_example_builds_and_fails_loudly_without_a_device(product
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1", reason="written after the round's GPU budget was spent; never run on a GPU yet")
 def test_cpp_refinement_example_converges_on_the_device():
     import re
     import subprocess
@@ -176,7 +175,6 @@ def test_cpp_refinement_example_converges_on_the_device():
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1", reason="written after the round's GPU budget was spent; never run on a GPU yet")
 def test_cpp_performance_example_runs_on_the_device():
     import re
     import subprocess
@@ -189,7 +187,6 @@ def test_cpp_performance_example_runs_on_the_device():
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("OMG_TEST_UNVERIFIED") != "1", reason="written after the round's GPU budget was spent; never run on a GPU yet")
 def test_cpp_host_example_converges_on_the_device():
     import re
     import subprocess
