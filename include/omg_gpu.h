@@ -160,7 +160,10 @@ int64_t omg_stat(omg_handle* h, const char* key);                     /* "launch
  *   kernels where they apply, "tail_cells" [4096] levels up to this many cells run in the single-CTA tail, "tail_smem" [1]
  *   tail levels staged in shared memory, "tail_simple" [1; 2 = also plane boundaries / variable coefficients, host-verified
  *   only so far], "overlap" [1] halo exchange overlapped with interior boxes, "p2p" / "fused" [1] peer-mapped puts / issued
- *   from inside the smoother, "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; unmeasured),
+ *   from inside the smoother, "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; measured: no gain),
+ *   "ring" [1] persistent ring smoother on big levels (2 = every level it serves, 0 = one tile per CTA),
+ *   "store_fine_residual" [1] (0: the level's own residual, mg_ires, is not written by the cycle -- the one switch that
+ *   changes what the host can read back: only for device-resident hosts that never read mg_ires),
  *   "profile" [0] per-kernel-class CUDA-event timing (omg_last_ms), "trace" [0] per-step timeline (omg_trace). */
 int omg_set_option(omg_handle* h, const char* key, int value);
 /* Per-step timeline (option "trace" = 1: every step of the cycle programs timed with its own CUDA-event pair, no graph,

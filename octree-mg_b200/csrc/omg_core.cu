@@ -92,7 +92,7 @@ struct LevelHost {
 };
 
 struct Program { std::vector<Step> steps; std::vector<TailOp> ops; DevBuf<TailOp> d_ops; cudaGraphExec_t graph = nullptr;
-                 int64_t launches_per_run = 0, fast_per_run = 0, general_per_run = 0; };
+                 int64_t launches_per_run = 0, fast_per_run = 0, general_per_run = 0, fastc_per_run = 0, generalc_per_run = 0; };
 
 }  // namespace
 
@@ -123,7 +123,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -136,6 +136,7 @@ struct omg_handle {
   // level kernels launched through the TMA-staged path (omg_fast.cu) / through the general one-CTA-per-box path
   // (omg_kernels.cu); the single-CTA tail and the pack / exchange kernels count in neither
   int64_t fast_launches = 0, general_launches = 0;
+  int64_t fast_cells = 0, general_cells = 0;   // the same, weighted by the cells of the level each launch ran on
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_ms = 0.0;
   omg_comm* comm = nullptr;
@@ -737,6 +738,11 @@ void exec_steps(omg_handle* h, Program& P) {
   cudaStream_t s = h->stream;
   const ParamsDev& PD = h->pdev;
   omgf::set_pdl(h->pdl && h->n_cpu == 1 && !h->profile);
+  omgf::set_ring(h->ring);
+  omgf::set_store_res(h->store_fine_residual);
+  auto cells_of = [](const LevelHost& L) { return (int64_t)L.nb * L.nc * L.nc * L.nc; };
+  auto fast = [&](const LevelHost& L, int n = 1) { h->fast_launches += n; h->fast_cells += n * cells_of(L); };
+  auto general = [&](const LevelHost& L, int n = 1) { h->general_launches += n; h->general_cells += n * cells_of(L); };
   for (const Step& st : P.steps) {
     const bool prof = h->profile && st.kind != S_SUBMEAN && st.kind != S_CLEAR_SLOT && st.kind != S_COPY_SLOT &&
                       st.kind != S_ZERO_PHI && st.kind != S_HALO_FORK && st.kind != S_HALO_JOIN;
@@ -750,7 +756,7 @@ void exec_steps(omg_handle* h, Program& P) {
         if (st.b == 3) {   // in-kernel exchange: whole level in one launch
           if (L.nb) {
             if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, L.nb <= h->bnd_first_boxes ? L.d_launch.p : nullptr, L.nb, 1, s)) fail("fused smoother does not apply to this level");
-            h->launches++; h->exchanges++; h->fused_smooths++; h->fast_launches++;
+            h->launches++; h->exchanges++; h->fused_smooths++; fast(L);
           }
           // emulated ranks share one GPU: a kernel must never wait for a kernel that may not be running, so the ranks
           // meet on the host and order their streams with events; the in-kernel waits then return at once
@@ -763,39 +769,39 @@ void exec_steps(omg_handle* h, Program& P) {
         const int* list = st.b == 1 ? L.d_bnd.p : st.b == 2 ? L.d_int.p : nullptr;
         const int nlist = st.b == 1 ? (int)L.h_bnd.size() : st.b == 2 ? (int)L.h_int.size() : 0;
         if (st.b && nlist == 0) break;
-        if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; h->general_launches++; }
-        else if (h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, 0, s)) h->fast_launches++;
-        else { omgk::smooth(L.dev, PD, st.a, st.b ? list : nullptr, nlist, s); h->general_launches++; }
+        if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; general(L); }
+        else if (h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, 0, s)) fast(L);
+        else { omgk::smooth(L.dev, PD, st.a, st.b ? list : nullptr, nlist, s); general(L); }
         h->launches++;
       } break;
       case S_RESID: {
         LevelHost& L = h->L(st.l);
         double* slot = st.a >= 0 ? h->d_scal.p + st.a : nullptr;
-        if (h->fast_kernels && omgf::resid_max(L.dev, PD, L.all_fast, slot, s)) h->fast_launches++;
-        else { omgk::resid(L.dev, PD, slot, s); h->general_launches++; }
+        if (h->fast_kernels && omgf::resid_max(L.dev, PD, L.all_fast, slot, s)) fast(L);
+        else { omgk::resid(L.dev, PD, slot, s); general(L); }
         h->launches++;
       } break;
-      case S_RESTRICT: omgk::restrict2(h->L(st.l).dev, h->L(st.l - 1).dev, st.a, st.b, s); h->launches++; h->general_launches++; break;
+      case S_RESTRICT: omgk::restrict2(h->L(st.l).dev, h->L(st.l - 1).dev, st.a, st.b, s); h->launches++; general(h->L(st.l)); break;
       case S_RESID_RESTRICT: {
         LevelHost& L = h->L(st.l);
-        if (h->fast_kernels && omgf::resid_restrict(L.dev, h->L(st.l - 1).dev, PD, L.all_fast, s)) h->fast_launches++;
+        if (h->fast_kernels && omgf::resid_restrict(L.dev, h->L(st.l - 1).dev, PD, L.all_fast, s)) fast(L);
         else {
           omgk::resid(L.dev, PD, nullptr, s); omgk::restrict2(L.dev, h->L(st.l - 1).dev, IPHI, IRES, s); h->launches++;
-          h->general_launches += 2;
+          general(L, 2);
         }
         h->launches++;
       } break;
       case S_CRHS: {
         LevelHost& L = h->L(st.l);
-        if (h->fast_kernels && omgf::crhs(L.dev, PD, L.all_fast, s)) h->fast_launches++;
-        else { omgk::crhs(L.dev, PD, s); h->general_launches++; }
+        if (h->fast_kernels && omgf::crhs(L.dev, PD, L.all_fast, s)) fast(L);
+        else { omgk::crhs(L.dev, PD, s); general(L); }
         h->launches++;
       } break;
       case S_OLDPL: omgk::oldpl(h->L(st.l).dev, PD, s); h->launches++; break;
       case S_CORR_PROLONG: {
         LevelHost& L = h->L(st.l);
-        if (h->fast_kernels && omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, s)) h->fast_launches++;
-        else { omgk::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, s); h->general_launches++; }
+        if (h->fast_kernels && omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, s)) fast(L);
+        else { omgk::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, s); general(L); }
         h->launches++;
       } break;
       case S_RB_FILL: omgk::rb_fill(h->L(st.l).dev, h->L(st.l - 1).dev, PD, 0, st.a, s); h->launches++; break;
@@ -854,17 +860,19 @@ void run_program(omg_handle* h, Program& P) {
   if (!graph_ok) { exec_steps(h, P); return; }
   if (!P.graph) {
     cudaGraph_t g = nullptr;
-    const int64_t l0 = h->launches, f0 = h->fast_launches, g0 = h->general_launches;
+    const int64_t l0 = h->launches, f0 = h->fast_launches, g0 = h->general_launches, fc0 = h->fast_cells, gc0 = h->general_cells;
     CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
     try { exec_steps(h, P); } catch (...) { cudaStreamEndCapture(h->stream, &g); if (g) cudaGraphDestroy(g); throw; }
     CK(cudaStreamEndCapture(h->stream, &g));
     CK(cudaGraphInstantiate(&P.graph, g, 0));
     CK(cudaGraphDestroy(g));
     P.launches_per_run = h->launches - l0; P.fast_per_run = h->fast_launches - f0; P.general_per_run = h->general_launches - g0;
-    h->launches = l0; h->fast_launches = f0; h->general_launches = g0;
+    P.fastc_per_run = h->fast_cells - fc0; P.generalc_per_run = h->general_cells - gc0;
+    h->launches = l0; h->fast_launches = f0; h->general_launches = g0; h->fast_cells = fc0; h->general_cells = gc0;
   }
   CK(cudaGraphLaunch(P.graph, h->stream));
   h->launches += P.launches_per_run; h->fast_launches += P.fast_per_run; h->general_launches += P.general_per_run;
+  h->fast_cells += P.fastc_per_run; h->general_cells += P.generalc_per_run;
   h->graph_launches++;
 }
 
@@ -1549,6 +1557,8 @@ int64_t omg_stat(omg_handle* h, const char* key) {
   if (k == "launches") return h->launches;
   if (k == "fast_launches") return h->fast_launches;         // level kernels on the TMA-staged path (omg_fast.cu)
   if (k == "general_launches") return h->general_launches;   // level kernels on the general path (omg_kernels.cu)
+  if (k == "fast_cells") return h->fast_cells;               // the same two, weighted by the cells of the level of each launch
+  if (k == "general_cells") return h->general_cells;
   if (k == "graph_launches") return h->graph_launches;
   if (k == "bytes_h2d") return h->bytes_h2d;
   if (k == "bytes_d2h") return h->bytes_d2h;
@@ -1575,6 +1585,8 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "tail_simple") { h->tail_simple = value; h->params_dirty = true; }
     else if (k == "overlap") h->overlap = value;
     else if (k == "pdl") h->pdl = value;
+    else if (k == "ring") h->ring = value;
+    else if (k == "store_fine_residual") h->store_fine_residual = value;
     else if (k == "trace") { h->trace = value; for (auto& r : h->trace_events) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); } h->trace_events.clear(); }
     else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
     else if (k == "fused") { h->fused = value; h->params_dirty = true; }

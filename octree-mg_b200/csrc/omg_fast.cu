@@ -68,8 +68,29 @@ __device__ __forceinline__ void signal_flag(unsigned long long* f, unsigned long
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(v) : "memory");
 }
 __device__ __forceinline__ double ld_plane(const double* p) { return __ldcg(p); }   // peer-written planes: L2, never the read-only path
+// ---- pieces of the persistent ring kernel (k_smooth_ring) ----
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {      // release.cta: the arriving thread's earlier writes are visible after the wait
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 8-byte asynchronous global -> shared copy (LDGSTS); completion is reported to an mbarrier by cp_async_arrive
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+// generic-proxy writes to shared memory (ghost fix-ups) before the stage is handed back to the async proxy (TMA)
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// one arrival on the mbarrier once all cp.async of this thread issued so far have landed (noinc: counted in the init count)
+__device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// barrier among the consumer warps only (barrier 1; the producer warp never joins)
+__device__ __forceinline__ void consumer_sync(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
+__device__ __forceinline__ int shfl_int(int v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 #define OMG_DYN_SMEM(name, al) extern __shared__ __align__(al) unsigned char name[]
 #define OMG_LAUNCH(kern, grid, smem, stream, ...) kern<<<(grid), kThreads, (smem), (stream)>>>(__VA_ARGS__)
+#define OMG_LAUNCH_T(kern, grid, threads, smem, stream, ...) kern<<<(grid), (threads), (smem), (stream)>>>(__VA_ARGS__)
 #define OMG_PDL_ASM() do { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); asm volatile("griddepcontrol.wait;" ::: "memory"); } while (0)
 #endif
 
@@ -376,6 +397,293 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   }
 }
 
+// =================================================================================================
+// Persistent ring version of the GSRB colour half-sweep (Laplacian / Helmholtz; same arithmetic, same bits as
+// k_smooth_lpl_fast).  One CTA per SM walks the tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  A producer warp
+// keeps RING_STAGES tiles in flight: per tile one 16 KiB TMA bulk copy of the other colour, one of the rhs of the
+// updated colour, bulk copies of the z / y ghost slices and 8-byte cp.async copies of the x ghosts, all completing on
+// the stage's "full" mbarrier; eight consumer warps update tile n while the copies of tiles n+1 .. n+STAGES-1 are in
+// flight and hand the stage back through its "empty" mbarrier.  This removes what bounded the one-tile-per-CTA kernel
+// (load -> wait -> compute -> store in sequence, overlap only between co-resident CTAs, a partly empty last wave).
+// Physical-boundary faces: the producer stages the box's OWN first layer (the phi(1) of bc_to_gc) in the ghost slot,
+// the consumers turn it into the ghost value in place; plane faces (refinement boundaries, other ranks) are read from
+// the plane pool by the consumers.  Both need one consumer-only barrier, paid by boundary tiles only.
+// =================================================================================================
+constexpr int kRingConsumers = 256;              // 8 consumer warps (PER cells per thread as in k_smooth_lpl_fast)
+constexpr int kRingThreads = kRingConsumers + 32;   // + 1 producer warp
+template <int NC, int KT>
+struct RingStage {
+  static constexpr int HX = NC / 2;
+  double B[KT][NC][HX];     // other colour
+  double R[KT][NC][HX];     // rhs of the updated colour
+  double zlo[NC][HX], zhi[NC][HX];
+  double ylo[KT][HX], yhi[KT][HX];
+  double xg[KT][NC];
+  int hdr[16];              // kind[6], arg[6], box, k0, put slot, spare: written by the producer before its arrive
+};
+template <int NC, int KT, int STAGES>
+struct RingSmem {
+  RingStage<NC, KT> st[STAGES];
+  uint64_t full[STAGES], empty[STAGES];
+};
+
+template <int NC, int KT, int STAGES>
+__global__ void __launch_bounds__(kRingThreads, 1) k_smooth_ring(const __grid_constant__ LevelDev L, const __grid_constant__ ParamsDev P, int colour,
+                                                             const int* __restrict__ boxlist, int n_tiles, int fused_put) {
+  constexpr int HX = NC / 2;
+  constexpr int TILES = NC / KT;
+  using SM = RingSmem<NC, KT, STAGES>;
+  OMG_DYN_SMEM(smem_raw, 128);
+  SM& S = *reinterpret_cast<SM*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int oc = colour ^ 1;
+  const double* __restrict__ phi = L.var[0];
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&S.full[s], 1 + 32); mbar_init(&S.empty[s], kRingConsumers / 32); }
+  }
+  __syncthreads();
+
+  if (tid >= kRingConsumers) {
+    // ------------------------------------------------ producer warp ------------------------------------------------
+    int it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+      const int s = it % STAGES, use = it / STAGES;
+      if (use > 0) mbar_wait(&S.empty[s], (use - 1) & 1);       // the consumers have finished with the stage's previous tile
+      RingStage<NC, KT>& T = S.st[s];
+      const int b = boxlist ? boxlist[t / TILES] : t / TILES;
+      const int k0 = (t % TILES) * KT;
+      int kv = 0, av = 0;
+      if (lane < 6) { kv = L.fkind[b * 6 + lane]; av = L.farg[b * 6 + lane]; }
+      int kind[6], arg[6];
+#pragma unroll
+      for (int f = 0; f < 6; ++f) { kind[f] = shfl_int(kv, f); arg[f] = shfl_int(av, f); }
+      int put_slot = -1;
+      if (fused_put) { if (lane == 0) put_slot = L.put.slot_of[b]; put_slot = shfl_int(put_slot, 0); }
+      // partition-face box: the peers' faces of the previous half-sweep must have landed before the consumers read them
+      if (put_slot >= 0 && lane < L.put.n_peers)
+        wait_flag(L.put.flags + L.put.channel * L.put.nranks + L.put.peers[lane], *L.put.epoch, L.put.err, L.put.timeout_ns,
+                  1 + L.put.peers[lane] + 64 * L.put.channel);
+      __syncwarp();
+      const size_t boxoff = (size_t)b * L.bs;
+      const double* __restrict__ Bg = phi + boxoff + (size_t)oc * L.cs;        // other colour of this box
+      const double* __restrict__ Ag = phi + boxoff + (size_t)colour * L.cs;    // colour being updated (its old values: phi(1) of bc_to_gc)
+      const double* __restrict__ Rg = L.var[1] + boxoff + (size_t)colour * L.cs;
+      const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
+      if (lane == 0) {
+#pragma unroll
+        for (int f = 0; f < 6; ++f) { T.hdr[f] = kind[f]; T.hdr[6 + f] = arg[f]; }
+        T.hdr[12] = b; T.hdr[13] = k0; T.hdr[14] = put_slot;
+        uint32_t bytes = 2u * KT * NC * HX * 8;
+        if (zlo_in || kind[4] != FK_PLANE) bytes += NC * HX * 8;
+        if (zhi_in || kind[5] != FK_PLANE) bytes += NC * HX * 8;
+        mbar_arrive_expect_tx(&S.full[s], bytes);
+        bulk_g2s(&T.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.full[s]);
+      }
+      if (lane == 1) bulk_g2s(&T.R[0][0][0], Rg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.full[s]);
+      if (lane == 2) {
+        if (zlo_in) bulk_g2s(&T.zlo[0][0], Bg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.full[s]);
+        else if (kind[4] == FK_SAME) bulk_g2s(&T.zlo[0][0], phi + (size_t)arg[4] * L.bs + (size_t)oc * L.cs + (size_t)(NC - 1) * NC * HX, NC * HX * 8, &S.full[s]);
+        else if (kind[4] == FK_PHYS) bulk_g2s(&T.zlo[0][0], Ag, NC * HX * 8, &S.full[s]);                                  // own layer k = 0
+      }
+      if (lane == 3) {
+        if (zhi_in) bulk_g2s(&T.zhi[0][0], Bg + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.full[s]);
+        else if (kind[5] == FK_SAME) bulk_g2s(&T.zhi[0][0], phi + (size_t)arg[5] * L.bs + (size_t)oc * L.cs, NC * HX * 8, &S.full[s]);
+        else if (kind[5] == FK_PHYS) bulk_g2s(&T.zhi[0][0], Ag + (size_t)(NC - 1) * NC * HX, NC * HX * 8, &S.full[s]);       // own layer k = NC-1
+      }
+      // y faces: one 8*HX-byte row per k-plane: the neighbour's row j = NC-1 (low) / j = 0 (high), or the box's own row
+      // j = 0 / NC-1 at a physical boundary
+      // (16-byte cp.async pieces: 32 + 32 short rows per tile would keep the TMA unit busier than the four big copies)
+      constexpr int CH = HX / 2;                       // 16-byte pieces per row
+      for (int q = lane; q < 2 * KT * CH; q += 32) {
+        const int c = q % CH, kk = (q / CH) % KT, hi = q / (CH * KT);
+        const int kf = hi ? kind[3] : kind[2], af = hi ? arg[3] : arg[2];
+        const double* src = nullptr;
+        if (kf == FK_SAME) src = phi + (size_t)af * L.bs + (size_t)oc * L.cs + ((size_t)(k0 + kk) * NC + (hi ? 0 : NC - 1)) * HX;
+        else if (kf == FK_PHYS) src = Ag + ((size_t)(k0 + kk) * NC + (hi ? NC - 1 : 0)) * HX;
+        if (src) cp_async16((hi ? &T.yhi[kk][0] : &T.ylo[kk][0]) + 2 * c, src + 2 * c);
+      }
+      // x ghosts: one 8-byte value per row (strided in the neighbour / in the box itself)
+      for (int r = lane; r < KT * NC; r += 32) {
+        const int kk = r / NC, j = r % NC;
+        const int sA = colour ^ ((j + k0 + kk) & 1);     // 0: this row's updated cells are i = 0, 2, ..: needs i = -1
+        const int kf = sA ? kind[1] : kind[0], af = sA ? arg[1] : arg[0];
+        const size_t row = ((size_t)(k0 + kk) * NC + j) * HX;
+        if (kf == FK_SAME) cp_async8(&T.xg[kk][j], phi + (size_t)af * L.bs + (size_t)oc * L.cs + row + (sA ? 0 : HX - 1));
+        else if (kf == FK_PHYS) cp_async8(&T.xg[kk][j], Ag + row + (sA ? HX - 1 : 0));
+      }
+      cp_async_arrive(&S.full[s]);
+    }
+    return;
+  }
+
+  // -------------------------------------------------- consumer warps --------------------------------------------------
+  const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], fac = L.fac;
+  constexpr int PER = KT * NC * HX / kRingConsumers;
+  int it = 0;
+  for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+    const int s = it % STAGES, use = it / STAGES;
+    mbar_wait(&S.full[s], use & 1);
+    RingStage<NC, KT>& T = S.st[s];
+    int kind[6], arg[6];
+#pragma unroll
+    for (int f = 0; f < 6; ++f) { kind[f] = T.hdr[f]; arg[f] = T.hdr[6 + f]; }
+    const int b = T.hdr[12], k0 = T.hdr[13], put_slot = T.hdr[14];
+    const size_t boxoff = (size_t)b * L.bs;
+    double* __restrict__ Ag = L.var[0] + boxoff + (size_t)colour * L.cs;
+    const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
+    bool fix = false;
+#pragma unroll
+    for (int f = 0; f < 6; ++f) fix = fix || (kind[f] != FK_SAME);
+    if (fix) {
+      // ---- ghost planes materialised elsewhere: the other-colour entries of the nc x nc plane ----
+      const double* gpl = gpl_cur(L);
+      if (!zlo_in && kind[4] == FK_PLANE)
+        for (int r = tid; r < NC * HX; r += kRingConsumers) { const int j = r / HX, m = r % HX; T.zlo[j][m] = ld_plane(gpl + (size_t)arg[4] * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)); }
+      if (!zhi_in && kind[5] == FK_PLANE)
+        for (int r = tid; r < NC * HX; r += kRingConsumers) { const int j = r / HX, m = r % HX; T.zhi[j][m] = ld_plane(gpl + (size_t)arg[5] * NC * NC + j * NC + 2 * m + ((oc ^ j) & 1)); }
+      if (kind[2] == FK_PLANE)
+        for (int r = tid; r < KT * HX; r += kRingConsumers) { const int kk = r / HX, m = r % HX, k = k0 + kk; T.ylo[kk][m] = ld_plane(gpl + (size_t)arg[2] * NC * NC + k * NC + 2 * m + ((oc ^ (k + 1)) & 1)); }
+      if (kind[3] == FK_PLANE)
+        for (int r = tid; r < KT * HX; r += kRingConsumers) { const int kk = r / HX, m = r % HX, k = k0 + kk; T.yhi[kk][m] = ld_plane(gpl + (size_t)arg[3] * NC * NC + k * NC + 2 * m + ((oc ^ k) & 1)); }
+      if (kind[0] == FK_PLANE || kind[1] == FK_PLANE)
+        for (int r = tid; r < KT * NC; r += kRingConsumers) {
+          const int kk = r / NC, j = r % NC, k = k0 + kk;
+          const int f = (colour ^ ((j + k) & 1)) ? 1 : 0;
+          if ((f ? kind[1] : kind[0]) == FK_PLANE) T.xg[kk][j] = ld_plane(gpl + (size_t)(f ? arg[1] : arg[0]) * NC * NC + k * NC + j);
+        }
+      // ---- physical boundaries: ghost = c0*b + c1*phi(1) + c2*phi(2) (bc_to_gc); the slot holds phi(1) ----
+#pragma unroll
+      for (int f = 0; f < 6; ++f) {
+        if (kind[f] != FK_PHYS) continue;
+        if (f == 4 && zlo_in) continue;
+        if (f == 5 && zhi_in) continue;
+        int type = L.ftype[b * 6 + f];
+        if (type == 0) type = P.bc_type[f];
+        double c0, c1, c2;
+        bc_coeffs(type, L.dr[f >> 1], f, c0, c1, c2);
+        const double* pl = arg[f] >= 0 ? L.bcpl + (size_t)arg[f] * NC * NC : nullptr;
+        const double bconst = P.bc_value[f];
+        if (f < 2) {
+          for (int r = tid; r < KT * NC; r += kRingConsumers) {
+            const int kk = r / NC, j = r % NC, k = k0 + kk;
+            const int sA = colour ^ ((j + k) & 1);
+            if (sA != f) continue;                       // this row needs the other side
+            const int m = f ? HX - 1 : 0;
+            const double bv = pl ? pl[k * NC + j] : bconst;
+            T.xg[kk][j] = c0 * bv + c1 * T.xg[kk][j] + c2 * T.B[kk][j][m];
+          }
+        } else if (f < 4) {
+          const int j1 = (f & 1) ? NC - 1 : 0, j2 = (f & 1) ? NC - 2 : 1;
+          for (int r = tid; r < KT * HX; r += kRingConsumers) {
+            const int kk = r / HX, m = r % HX, k = k0 + kk;
+            const int i = 2 * m + (colour ^ ((j1 + k) & 1));
+            const double bv = pl ? pl[k * NC + i] : bconst;
+            double& g = (f & 1) ? T.yhi[kk][m] : T.ylo[kk][m];
+            g = c0 * bv + c1 * g + c2 * T.B[kk][j2][m];
+          }
+        } else {
+          const int k1 = (f & 1) ? NC - 1 : 0, kk1 = k1 - k0, kk2 = (f & 1) ? kk1 - 1 : kk1 + 1;
+          for (int r = tid; r < NC * HX; r += kRingConsumers) {
+            const int j = r / HX, m = r % HX;
+            const int i = 2 * m + (colour ^ ((j + k1) & 1));
+            const double bv = pl ? pl[j * NC + i] : bconst;
+            double& g = (f & 1) ? T.zhi[j][m] : T.zlo[j][m];
+            g = c0 * bv + c1 * g + c2 * T.B[kk2][j][m];
+          }
+        }
+      }
+      consumer_sync(kRingConsumers);
+    }
+
+    // ---- update this colour ----
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+      const int idx = q * kRingConsumers + tid;
+      const int m = idx % HX, j = (idx / HX) % NC, kk = idx / (HX * NC);
+      const int sA = colour ^ ((j + k0 + kk) & 1);
+      const int ml = m - 1 + sA, mh = m + sA;
+      const double xlo = ml >= 0 ? T.B[kk][j][ml] : T.xg[kk][j];
+      const double xhi = mh < HX ? T.B[kk][j][mh] : T.xg[kk][j];
+      const double ylo = j > 0 ? T.B[kk][j - 1][m] : T.ylo[kk][m];
+      const double yhi = j < NC - 1 ? T.B[kk][j + 1][m] : T.yhi[kk][m];
+      const double zlo = kk > 0 ? T.B[kk - 1][j][m] : T.zlo[j][m];
+      const double zhi = kk < KT - 1 ? T.B[kk + 1][j][m] : T.zhi[j][m];
+      Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - T.R[kk][j][m]);
+    }
+
+    // ---- partition-face box: store the fresh face layers into the neighbour ranks' plane pools (see k_smooth_lpl_fast) ----
+    if (put_slot >= 0) {
+      consumer_sync(kRingConsumers);
+      const unsigned long long e = *L.put.epoch;
+      const double* Abox = L.var[0] + boxoff;
+      for (int q = L.put.ptr[put_slot]; q < L.put.ptr[put_slot + 1]; ++q) {
+        const int f = L.put.item[3 * q], pr = L.put.item[3 * q + 1], pl = L.put.item[3 * q + 2];
+        double* o = L.put.peer_base[pr] + (size_t)((e + 1ull) & 1ull) * (size_t)L.put.peer_stride[pr] + (size_t)pl * NC * NC;
+        const int layer = (f & 1) ? 0 : NC - 1;          // f = the RECEIVER's face
+        if (f < 4) {
+          for (int r = tid; r < KT * NC; r += kRingConsumers) {
+            const int k = k0 + r / NC, t1 = r % NC;
+            const int i = f < 2 ? layer : t1, j = f < 2 ? t1 : layer;
+            o[k * NC + t1] = __ldcg(Abox + ((i + j + k) & 1) * L.cs + (k * NC + j) * HX + (i >> 1));
+          }
+        } else if (layer >= k0 && layer < k0 + KT) {
+          for (int r = tid; r < NC * NC; r += kRingConsumers) {
+            const int i = r % NC, j = r / NC;
+            o[r] = __ldcg(Abox + ((i + j + layer) & 1) * L.cs + (layer * NC + j) * HX + (i >> 1));
+          }
+        }
+      }
+      __threadfence_system();
+      consumer_sync(kRingConsumers);
+      if (tid == 0) {
+        const unsigned int prev = atomicAdd(L.put.done, 1u);
+        if (prev == (unsigned int)(L.put.n_bnd * TILES) - 1u) {
+          *L.put.done = 0u;
+          __threadfence_system();
+          if (*(volatile int*)L.put.err == 0) {
+            for (int q = 0; q < L.put.n_peers; ++q)
+              signal_flag(L.put.peer_flags[L.put.peers[q]] + L.put.channel * L.put.nranks + L.put.me, e + 1ull);
+            *L.put.epoch = e + 1ull;
+          }
+        }
+      }
+    }
+    if (fix) fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&S.empty[s]);
+  }
+}
+
+// number of SMs of the current device (grid of the persistent kernels)
+inline int sm_count() {
+  static int n = 0;
+  if (!n) {
+#ifdef OMG_HOST_EMU
+    n = 3;
+#else
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+#endif
+  }
+  return n;
+}
+int g_ring = 1;          // option "ring": 1 = persistent ring smoother on levels with at least 2 tiles per SM, 2 = always, 0 = never
+
+template <int NC, int KT, int STAGES>
+bool launch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
+  static bool configured = false;
+  const size_t smem = sizeof(RingSmem<NC, KT, STAGES>);
+  if (!configured) {
+    if (cudaFuncSetAttribute(k_smooth_ring<NC, KT, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    configured = true;
+  }
+  const int n_tiles = (list ? n : L.nb) * (NC / KT);
+  const int grid = n_tiles < sm_count() ? n_tiles : sm_count();
+  auto kern = k_smooth_ring<NC, KT, STAGES>;
+  OMG_LAUNCH_T(kern, grid, kRingThreads, smem, s, L, P, colour, list, n_tiles, fused);
+  return true;
+}
+
 // launch with the programmatic-stream-serialization attribute: the kernel may start before its predecessor in the stream
 // has finished and orders itself with pdl_sync()
 bool g_pdl = false;
@@ -463,7 +771,10 @@ __device__ __forceinline__ void block_neighbours(const BothSmem<NC, KT>& F, cons
   n[4] = dk ? u[e ^ 4] : zo; n[5] = dk ? zo : u[e ^ 4];
 }
 
-template <int NC, int KT, int MODE, bool HELM, int MB, bool VC>
+// STORE = false (option "store_fine_residual" = 0, for hosts that never read mg_ires): the residual of the level itself is
+// not written -- nothing on the device reads it again (update_coarse consumes it in registers, the next residual pass
+// overwrites it) -- which takes 8 B per cell off MODE_RESID_RESTRICT (26 -> 18 B) and MODE_RESID_MAX (24 -> 16 B).
+template <int NC, int KT, int MODE, bool HELM, int MB, bool VC, bool STORE>
 __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
                                                            const __grid_constant__ ParamsDev P, double* maxslot, int pdl) {
   constexpr int HX = NC / 2;
@@ -691,7 +1002,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
         out2[g] = u0;
       } else {
         r[e] = cur[e] - lap;
-        out1[g] = r[e];
+        if (STORE) out1[g] = r[e];
         if (MODE == MODE_RESID_MAX) vmax = fmax(vmax, fabs(r[e]));
       }
     }
@@ -726,18 +1037,24 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   }
 }
 
-template <int NC, int KT, int MODE, bool HELM, int MB, bool VC = false>
-bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+int g_store_res = 1;     // option "store_fine_residual"
+template <int NC, int KT, int MODE, bool HELM, int MB, bool VC, bool STORE>
+bool launch_stencil_s(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(StencilSmem<NC, KT, VC>);
   if (!configured) {
-    if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM, MB, VC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(k_stencil_fast<NC, KT, MODE, HELM, MB, VC, STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  if (g_pdl) return launch_pdl(k_stencil_fast<NC, KT, MODE, HELM, MB, VC>, nboxes * (NC / KT), smem, s, L, Lc, P, maxslot, 1);
-  auto kern = k_stencil_fast<NC, KT, MODE, HELM, MB, VC>;
+  if (g_pdl) return launch_pdl(k_stencil_fast<NC, KT, MODE, HELM, MB, VC, STORE>, nboxes * (NC / KT), smem, s, L, Lc, P, maxslot, 1);
+  auto kern = k_stencil_fast<NC, KT, MODE, HELM, MB, VC, STORE>;
   OMG_LAUNCH(kern, nboxes * (NC / KT), smem, s, L, Lc, P, maxslot, 0);
   return true;
+}
+template <int NC, int KT, int MODE, bool HELM, int MB, bool VC = false>
+bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+  if (MODE != MODE_CRHS && !g_store_res) return launch_stencil_s<NC, KT, MODE, HELM, MB, VC, false>(L, Lc, P, nboxes, maxslot, s);
+  return launch_stencil_s<NC, KT, MODE, HELM, MB, VC, true>(L, Lc, P, nboxes, maxslot, s);
 }
 
 // resident CTAs per SM the register allocation is tuned for (OMG_STENCIL_MB = 2 | 3 | 4 overrides, for tuning runs)
@@ -879,6 +1196,8 @@ bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev
 namespace omgf {
 
 void set_pdl(bool on) { g_pdl = on; }
+void set_ring(int mode) { g_ring = mode; }
+void set_store_res(int on) { g_store_res = on; }
 
 bool smooth_applies(const LevelDev& L, const ParamsDev& P) {
   if (L.nc != 16 && L.nc != 32) return false;
@@ -895,6 +1214,7 @@ bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, co
     return false;
   }
   if (P.op != OP_LPL && P.op != OP_HELMH) return false;
+  if (L.nc == 16 && g_ring && ((list ? n : L.nb) >= 2 * sm_count() || g_ring == 2)) return launch_smooth_ring<16, 16, 5>(L, P, colour, list, n, fused, s);
   if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, fused, s);
   if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, fused, s);
   return false;

@@ -12,6 +12,12 @@ namespace omgf {
 // option "pdl": launch the kernels below with programmatic stream serialization (they order themselves with
 // griddepcontrol.wait); single-rank cycles only, off by default
 void set_pdl(bool on);
+// option "ring": persistent ring smoother (k_smooth_ring): 1 = on levels with at least two tiles per SM (default), 2 = on
+// every level it serves, 0 = never (one tile per CTA, k_smooth_lpl_fast)
+void set_ring(int mode);
+// option "store_fine_residual" (default 1): 0 = the residual kernels do not write the level's own residual (mg_ires) --
+// for device-resident hosts that never read it; the cycle itself consumes the residual in registers
+void set_store_res(int on);
 // list != null: only the n boxes of the list (partition-face / interior split of a distributed level)
 // fused: the list is the level in launch order, partition-face boxes first; they exchange their faces in-kernel (PutDev)
 bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, int fused, cudaStream_t s);

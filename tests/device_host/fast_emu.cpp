@@ -10,11 +10,15 @@
 #include <pthread.h>
 
 #include <atomic>
+#include <chrono>
+#include <condition_variable>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <functional>
+#include <map>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -26,8 +30,16 @@ namespace emu {
 constexpr int MAXT = 1024;
 unsigned char* g_smem = nullptr;      // the CTA's dynamic shared memory
 size_t g_smem_bytes = 0;              // as passed to the launch
-pthread_barrier_t g_cta_bar, g_warp_bar[MAXT / 32];
+pthread_barrier_t g_cta_bar, g_warp_bar[MAXT / 32], g_named_bar;
 double g_shfl[MAXT];
+int g_shfl_i[MAXT];
+// mbarriers with their real semantics (the persistent ring kernel runs a producer warp ahead of the consumers): pending
+// arrivals + pending transaction bytes; a phase completes when both reach zero.  One lock for all of them.
+struct MBar { int count = 0, pending = 0; long long tx = 0; unsigned phase = 0; };
+std::mutex g_mb_m;
+std::condition_variable g_mb_cv;
+std::map<const void*, MBar> g_mb;
+inline void mb_check(MBar& b) { if (b.pending == 0 && b.tx == 0) { b.phase++; b.pending = b.count; g_mb_cv.notify_all(); } }
 std::atomic<long long> g_tx_expected{0}, g_tx_done{0};
 std::atomic<int> g_violations{0};
 void violation(const char* what) {
@@ -36,9 +48,9 @@ void violation(const char* what) {
 }  // namespace emu
 
 static thread_local FakeDim threadIdx, blockIdx;
-static FakeDim blockDim = {256, 1, 1};
+static FakeDim blockDim = {256, 1, 1}, gridDim = {1, 1, 1};
 static inline void __syncthreads() { pthread_barrier_wait(&emu::g_cta_bar); }
-static inline void __syncwarp() {}
+static inline void __syncwarp() { pthread_barrier_wait(&emu::g_warp_bar[threadIdx.x >> 5]); }   // every use is warp-uniform
 static inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 static inline double __shfl_xor_sync(unsigned, double v, int o) {
   const int t = (int)threadIdx.x;
@@ -59,16 +71,76 @@ static inline int atomicExch(int* a, int v) { return __atomic_exchange_n(a, v, _
 #include "harness.cpp"   // HostLevel, build_level, randomise, params + the general device path (omg_ops.cuh)
 
 // ---- stand-ins for the PTX helper block of omg_fast.cu ------------------------------------------------------
-static inline void mbar_init(uint64_t*, uint32_t) {}
-static inline void mbar_expect_tx(uint64_t*, uint32_t bytes) { emu::g_tx_expected += bytes; }
-static inline void mbar_arrive_expect_tx(uint64_t*, uint32_t bytes) { emu::g_tx_expected += bytes; }
-static inline void mbar_wait(uint64_t*, uint32_t) {}   // every use is followed by __syncthreads before the data is read
-static inline void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t*) {
-  const unsigned char* d = static_cast<unsigned char*>(dst);
+static inline bool in_smem(const void* p, size_t bytes) {
+  const unsigned char* d = static_cast<const unsigned char*>(p);
+  return d >= emu::g_smem && d + bytes <= emu::g_smem + emu::g_smem_bytes;
+}
+static inline emu::MBar& mb_of(uint64_t* bar) {
+  if (!in_smem(bar, 8) || ((uintptr_t)bar & 7)) emu::violation("mbarrier outside the CTA's shared memory or misaligned");
+  auto it = emu::g_mb.find(bar);
+  if (it == emu::g_mb.end()) { emu::violation("mbarrier used before mbarrier.init"); return emu::g_mb[bar]; }
+  return it->second;
+}
+static inline void mbar_init(uint64_t* bar, uint32_t count) {
+  std::lock_guard<std::mutex> lk(emu::g_mb_m);
+  emu::MBar b; b.count = b.pending = (int)count;
+  emu::g_mb[bar] = b;
+}
+static inline void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  std::lock_guard<std::mutex> lk(emu::g_mb_m);
+  mb_of(bar).tx += bytes; emu::g_tx_expected += bytes;
+}
+static inline void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  std::lock_guard<std::mutex> lk(emu::g_mb_m);
+  emu::MBar& b = mb_of(bar);
+  b.tx += bytes; emu::g_tx_expected += bytes;
+  if (b.pending <= 0) emu::violation("mbarrier: more arrivals than the init count");
+  b.pending--; emu::mb_check(b);
+}
+static inline void mbar_arrive(uint64_t* bar) {
+  std::lock_guard<std::mutex> lk(emu::g_mb_m);
+  emu::MBar& b = mb_of(bar);
+  if (b.pending <= 0) emu::violation("mbarrier: more arrivals than the init count");
+  b.pending--; emu::mb_check(b);
+}
+// try_wait.parity: true once the phase of that parity has completed, i.e. the phase in progress has the other parity
+static inline void mbar_wait(uint64_t* bar, uint32_t parity) {
+  std::unique_lock<std::mutex> lk(emu::g_mb_m);
+  emu::MBar& b = mb_of(bar);
+  if (!emu::g_mb_cv.wait_for(lk, std::chrono::seconds(60), [&] { return (b.phase & 1u) != (parity & 1u); }))
+    emu::violation("mbarrier wait: the phase never completed (the GPU would hang)");
+}
+static inline void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   if (((uintptr_t)dst & 15) || ((uintptr_t)src & 15) || (bytes & 15) || bytes == 0) emu::violation("bulk copy: address or size not a multiple of 16");
-  if (d < emu::g_smem || d + bytes > emu::g_smem + emu::g_smem_bytes) emu::violation("bulk copy: destination outside the CTA's shared memory");
+  if (!in_smem(dst, bytes)) emu::violation("bulk copy: destination outside the CTA's shared memory");
   std::memcpy(dst, src, bytes);
-  emu::g_tx_done += bytes;
+  std::lock_guard<std::mutex> lk(emu::g_mb_m);
+  emu::MBar& b = mb_of(bar);
+  b.tx -= bytes; emu::g_tx_done += bytes; emu::mb_check(b);
+}
+static inline void cp_async8(void* dst, const void* src) {
+  if (((uintptr_t)dst & 7) || ((uintptr_t)src & 7)) emu::violation("cp.async: address not a multiple of 8");
+  if (!in_smem(dst, 8)) emu::violation("cp.async: destination outside the CTA's shared memory");
+  std::memcpy(dst, src, 8);
+}
+static inline void cp_async16(void* dst, const void* src) {
+  if (((uintptr_t)dst & 15) || ((uintptr_t)src & 15)) emu::violation("cp.async: address not a multiple of 16");
+  if (!in_smem(dst, 16)) emu::violation("cp.async: destination outside the CTA's shared memory");
+  std::memcpy(dst, src, 16);
+}
+static inline void fence_proxy_async() {}
+static inline void cp_async_arrive(uint64_t* bar) { mbar_arrive(bar); }
+static inline void consumer_sync(int nthreads) {
+  if (nthreads != 256) emu::violation("named barrier: the emulator expects the 256 consumer threads");
+  pthread_barrier_wait(&emu::g_named_bar);
+}
+static inline int shfl_int(int v, int src) {
+  const int t = (int)threadIdx.x;
+  emu::g_shfl_i[t] = v;
+  pthread_barrier_wait(&emu::g_warp_bar[t >> 5]);
+  const int r = emu::g_shfl_i[(t & ~31) | (src & 31)];
+  pthread_barrier_wait(&emu::g_warp_bar[t >> 5]);
+  return r;
 }
 // the emulated ranks run one after the other, so a flag a kernel would wait for must already be there
 static inline bool wait_flag(const unsigned long long* f, unsigned long long want, int*, unsigned long long, int) {
@@ -80,6 +152,7 @@ static inline double ld_plane(const double* p) { return *p; }
 #define OMG_DYN_SMEM(name, al) unsigned char* name = emu::g_smem
 #define OMG_PDL_ASM() do {} while (0)
 #define OMG_LAUNCH(kern, grid, smem, stream, ...) emu::launch((grid), 256, (smem), [&]() { kern(__VA_ARGS__); })
+#define OMG_LAUNCH_T(kern, grid, threads, smem, stream, ...) emu::launch((grid), (threads), (smem), [&]() { kern(__VA_ARGS__); })
 #define OMG_TAIL_DYN_SMEM(name) double* name = reinterpret_cast<double*>(emu::g_smem)
 #define cudaFuncSetAttribute(...) cudaSuccess
 #undef __launch_bounds__
@@ -92,8 +165,9 @@ void launch(int grid, int nthreads, size_t smem, const std::function<void()>& bo
   static unsigned char* buf = static_cast<unsigned char*>(aligned_alloc(1024, 256 * 1024));
   g_smem = buf; g_smem_bytes = smem;
   if (smem > 227 * 1024) violation("launch: more than 227 KB of shared memory");
-  blockDim.x = (unsigned)nthreads;
+  blockDim.x = (unsigned)nthreads; gridDim.x = (unsigned)grid; if (getenv("FE_TRACE")) std::fprintf(stderr, "launch grid %d threads %d smem %zu\n", grid, nthreads, smem);
   pthread_barrier_init(&g_cta_bar, nullptr, nthreads);
+  pthread_barrier_init(&g_named_bar, nullptr, 256);
   for (auto& w : g_warp_bar) pthread_barrier_init(&w, nullptr, 32);
   std::vector<std::thread> th;
   th.reserve(nthreads);
@@ -101,7 +175,7 @@ void launch(int grid, int nthreads, size_t smem, const std::function<void()>& bo
     th.emplace_back([&, t]() {
       for (int b = 0; b < grid; ++b) {
         threadIdx.x = (unsigned)t; blockIdx.x = (unsigned)b;
-        if (t == 0) { g_tx_expected = 0; g_tx_done = 0; std::memset(g_smem, 0xff, smem); }   // NaN-fill: stale reads show
+        if (t == 0) { g_tx_expected = 0; g_tx_done = 0; std::memset(g_smem, 0xff, smem); g_mb.clear(); }   // NaN-fill: stale reads show
         pthread_barrier_wait(&g_cta_bar);
         body();
         pthread_barrier_wait(&g_cta_bar);
@@ -110,6 +184,7 @@ void launch(int grid, int nthreads, size_t smem, const std::function<void()>& bo
     });
   for (auto& x : th) x.join();
   pthread_barrier_destroy(&g_cta_bar);
+  pthread_barrier_destroy(&g_named_bar);
   for (auto& w : g_warp_bar) pthread_barrier_destroy(&w);
 }
 }  // namespace emu
@@ -349,6 +424,8 @@ int fe_two_levels(int op, int nc, int nbx, int nby, int nbz, const int* bc_types
     default: return two_levels<OP_VHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
   }
 }
+// 0 / 1 / 2: never / on big levels / always use the persistent ring smoother (omgf::set_ring)
+void fe_set_ring(int mode) { omgf::set_ring(mode); }
 // checks of the emulated TMA / mbarrier / shared-memory rules that failed so far
 int fe_violations() { return emu::g_violations.load(); }
 }

