@@ -8,6 +8,7 @@
 // program is replayed through a CUDA graph.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -1176,6 +1177,8 @@ int omg_create(int device, omg_handle** out) {
   h->params.n_cycle_down = 2; h->params.n_cycle_up = 2; h->params.max_coarse_cycles = 1000;
   h->params.residual_coarse_abs = 1e-8; h->params.residual_coarse_rel = 1e-8;
   h->have_params = true;
+  // tuning / bisecting aid: OMG_RING_DEFAULT overrides the default of option "ring" (omg_set_option still wins)
+  if (const char* e = getenv("OMG_RING_DEFAULT")) { if (*e) h->ring = atoi(e); }
   *out = h;
   return 0;
 }
