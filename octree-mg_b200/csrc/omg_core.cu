@@ -124,7 +124,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 0, store_fine_residual = 1;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -1389,9 +1389,19 @@ int omg_fill_ghost_cells_lvl(omg_handle* h, int lvl, int iv) {
       if (L.xg.any) exchange_ghost(h, lvl, 0, h->stream);
       if (!L.h_rb.empty()) omgk::rb_fill(L.dev, h->L(lvl - 1).dev, h->pdev, 0, 0, h->stream);
     } else if (v >= 4) {
-      if (h->n_cpu > 1) fail("fill_ghost_cells_lvl: extra variables on several ranks not supported yet");
-      omgk::fill_stored(L.dev, h->pdev, v, h->bc_type[v], h->bc_value[v], h->stream);
-      if (!L.h_rb.empty()) omgk::rb_fill(L.dev, h->L(lvl - 1).dev, h->pdev, v, 0, h->stream);
+      // faces owned by other ranks (buffer_for_nb / buffer_for_fine_nb with this variable, src/m_ghost_cells.f90:142-168):
+      // packed send/recv into a receive buffer, copied into the stored-face pool by fill_stored / used by rb_fill
+      const double* rpl = nullptr;
+      if (L.xg.any) {
+        const LevelDev& Lc = lvl > h->lowest ? h->L(lvl - 1).dev : L.dev;
+        if (L.xg.d_send.n < (size_t)L.xg.n_send * L.nc * L.nc) L.xg.d_send.alloc((size_t)L.xg.n_send * L.nc * L.nc);
+        if (L.xg.d_recv.n < (size_t)L.xg.n_recv * L.nc * L.nc) L.xg.d_recv.alloc((size_t)L.xg.n_recv * L.nc * L.nc);
+        if (L.xg.n_send) { omgk::pack_ghost(L.dev, Lc, h->pdev, L.xg.d_sdesc.p, L.xg.n_send, L.xg.d_send.p, 0, h->stream, v); h->launches++; }
+        run_exchange(h, L.xg, L.xg.d_send.p, L.xg.d_recv.p, (size_t)L.nc * L.nc, h->stream);
+        rpl = L.xg.d_recv.p;
+      }
+      omgk::fill_stored(L.dev, h->pdev, v, h->bc_type[v], h->bc_value[v], h->stream, rpl, L.xg.n_recv);
+      if (!L.h_rb.empty()) omgk::rb_fill(L.dev, h->L(lvl - 1).dev, h->pdev, v, 0, h->stream, rpl);
     } else fail("fill_ghost_cells_lvl: ghost cells of rhs/old/res are not tracked on the device");
     h->launches++;
   });
@@ -1418,7 +1428,14 @@ int omg_prolong(omg_handle* h, int lvl, int iv, int iv_to, int add) {
     if (lvl == h->highest) fail("cannot prolong highest level");
     if (lvl < h->lowest) fail("cannot prolong below lowest level");
     if (!(v == IPHI || v >= 4)) fail("omg_prolong: source must be phi or an extra variable (ghost cells of rhs/old/res are not tracked)");
-    if (h->L(lvl + 1).xp.any) fail("omg_prolong: standalone prolongation across ranks is not supported (the cycle's fused correction is)");
+    check_p2p(h);
+    if (h->L(lvl + 1).xp.any) {
+      // prolong_set_buffer (src/m_prolong.f90:91-121) as a patch of coarse values, see do_pack_prolong_var
+      LevelHost& Lf = h->L(lvl + 1);
+      const int pw = Lf.nc / 2 + 2;
+      if (Lf.xp.n_send) { omgk::pack_prolong_var(h->L(lvl).dev, h->pdev, Lf.xp.d_sdesc.p, Lf.xp.n_send, Lf.xp.d_send.p, Lf.nc, v, h->stream); h->launches++; }
+      run_exchange(h, Lf.xp, Lf.xp.d_send.p, Lf.xp.d_recv.p, (size_t)pw * pw * pw, h->stream);
+    }
     omgk::prolong_var(h->L(lvl + 1).dev, h->L(lvl).dev, h->pdev, v, vt, add, h->stream);
     h->launches++;
   });

@@ -168,9 +168,20 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   }
   // rhs (and eps) of this thread's cells (in flight while the bulk copies land)
   constexpr int PER = KT * NC * HX / kThreads;
+  // COLUMN = true (box 16, constant coefficients): a thread owns one (m, j) column and KP consecutive k-planes, as in
+  // k_smooth_ring (neighbour streams resolved once per thread, the centre value reused along k: 4 loads per cell)
+  constexpr bool COLUMN = !VC && (kThreads % (NC * HX) == 0) && (KT % (kThreads / (NC * HX)) == 0) && ((KT / (kThreads / (NC * HX))) % 2 == 0);
+  constexpr int COLS = NC * HX, KP = COLUMN ? KT / (kThreads / COLS) : 1;
+  const int col = tid % COLS, kb = COLUMN ? (tid / COLS) * KP : 0;
   double rhs[PER], eps0[VC ? PER : 1];
+  if constexpr (COLUMN) {
+    static_assert(!COLUMN || KP == PER, "one cell per plane and thread");
 #pragma unroll
-  for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)k0 * NC * HX + q * kThreads + tid];
+    for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)(k0 + kb + q) * COLS + col];
+  } else {
+#pragma unroll
+    for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)k0 * NC * HX + q * kThreads + tid];
+  }
   if constexpr (VC) {
     const double* __restrict__ Eg0 = L.var[4] + boxoff + (size_t)colour * L.cs;
 #pragma unroll
@@ -327,6 +338,32 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
 
   // ---- update this colour ----
   const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], fac = L.fac;
+  if constexpr (COLUMN) {
+    using TS = TileSmem<NC, KT>;
+    constexpr int oB = offsetof(TS, B) / 8, oZl = offsetof(TS, zlo) / 8, oZh = offsetof(TS, zhi) / 8, oYl = offsetof(TS, ylo) / 8,
+                  oYh = offsetof(TS, yhi) / 8, oXg = offsetof(TS, xg) / 8, PL = NC * HX;
+    const int m = col % HX, j = col / HX;
+    const int s0 = colour ^ ((j + k0 + kb) & 1);          // sA of the thread's first plane; alternates with kk
+    const int x0 = m > 0 ? oB + kb * PL + j * HX + m - 1 : oXg + kb * NC + j, x0s = m > 0 ? PL : NC;
+    const int x1 = m < HX - 1 ? oB + kb * PL + j * HX + m + 1 : oXg + kb * NC + j, x1s = m < HX - 1 ? PL : NC;
+    const int xe = s0 ? x1 : x0, xes = s0 ? x1s : x0s, xo = s0 ? x0 : x1, xos = s0 ? x0s : x1s;
+    const int yl = j > 0 ? oB + kb * PL + (j - 1) * HX + m : oYl + kb * HX + m, yls = j > 0 ? PL : HX;
+    const int yh = j < NC - 1 ? oB + kb * PL + (j + 1) * HX + m : oYh + kb * HX + m, yhs = j < NC - 1 ? PL : HX;
+    const int ctr = oB + kb * PL + j * HX + m;
+    const int zl = kb > 0 ? ctr - PL : oZl + j * HX + m;
+    const int zh = kb + KP < KT ? ctr + KP * PL : oZh + j * HX + m;
+    const double* __restrict__ W = reinterpret_cast<const double*>(static_cast<const TS*>(&S));
+    double* __restrict__ out = Ag + (size_t)(k0 + kb) * PL + col;
+    double cm = W[zl], c0 = W[ctr];
+#pragma unroll
+    for (int q = 0; q < KP; ++q) {
+      const double cp = q < KP - 1 ? W[ctr + (q + 1) * PL] : W[zh];
+      const double xn = (q & 1) ? W[xo + q * xos] : W[xe + q * xes];
+      const double ylo = W[yl + q * yls], yhi = W[yh + q * yhs];
+      out[q * PL] = fac * (idx2 * (xn + c0) + idy2 * (yhi + ylo) + idz2 * (cp + cm) - rhs[q]);
+      cm = c0; c0 = cp;
+    }
+  } else {
 #pragma unroll
   for (int q = 0; q < PER; ++q) {
     const int idx = q * kThreads + tid;
@@ -354,6 +391,7 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
     } else {
       Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - rhs[q]);
     }
+  }
   }
 
   // ---- partition-face box: store the fresh face layers into the neighbour ranks' plane pools (the copy they are not
@@ -409,8 +447,9 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
 // the consumers turn it into the ghost value in place; plane faces (refinement boundaries, other ranks) are read from
 // the plane pool by the consumers.  Both need one consumer-only barrier, paid by boundary tiles only.
 // =================================================================================================
-constexpr int kRingConsumers = 256;              // 8 consumer warps (PER cells per thread as in k_smooth_lpl_fast)
-constexpr int kRingThreads = kRingConsumers + 32;   // + 1 producer warp
+// NCONS consumer threads (+ 1 producer warp) per CTA, MINB CTAs per SM: the consumers' update is latency-bound per warp
+// (profiles/r02c_ncu_smooth_ring.txt: 8 consumer warps on an SM issue 23 % of the time and the half-sweep takes 0.50 ms
+// against 0.30 ms of the one-tile-per-CTA kernel), so an SM needs 16 .. 32 of them.
 template <int NC, int KT>
 struct RingStage {
   static constexpr int HX = NC / 2;
@@ -427,11 +466,12 @@ struct RingSmem {
   uint64_t full[STAGES], empty[STAGES];
 };
 
-template <int NC, int KT, int STAGES>
-__global__ void __launch_bounds__(kRingThreads, 1) k_smooth_ring(const __grid_constant__ LevelDev L, const __grid_constant__ ParamsDev P, int colour,
-                                                             const int* __restrict__ boxlist, int n_tiles, int fused_put) {
+template <int NC, int KT, int STAGES, int NCONS, int MINB>
+__global__ void __launch_bounds__(NCONS + 32, MINB) k_smooth_ring(const __grid_constant__ LevelDev L, const __grid_constant__ ParamsDev P, int colour,
+                                                              const int* __restrict__ boxlist, int n_tiles, int fused_put) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
+  constexpr int kRingConsumers = NCONS;
   using SM = RingSmem<NC, KT, STAGES>;
   OMG_DYN_SMEM(smem_raw, 128);
   SM& S = *reinterpret_cast<SM*>(smem_raw);
@@ -518,7 +558,28 @@ __global__ void __launch_bounds__(kRingThreads, 1) k_smooth_ring(const __grid_co
 
   // -------------------------------------------------- consumer warps --------------------------------------------------
   const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], fac = L.fac;
-  constexpr int PER = KT * NC * HX / kRingConsumers;
+  // Update loop: a thread owns one (m, j) column of the tile and KP consecutive k-planes of it.  Which neighbour lies
+  // outside the tile then depends on the thread only, so the stage-relative offsets of the six neighbour streams are
+  // computed once per kernel; and the other-colour value at (m, j) of plane kk is at once the z neighbour of planes
+  // kk -+ 1 and one of the two x neighbours of plane kk, so it is loaded once and kept in registers: 5 shared-memory
+  // loads per cell (rhs included) instead of 7.  (xhi + xlo and zhi + zlo are commutative: same bits.)
+  constexpr int COLS = NC * HX, NG = kRingConsumers / COLS, KP = KT / NG;
+  static_assert(kRingConsumers % COLS == 0 && KT % NG == 0 && KP % 2 == 0 && KT % 2 == 0, "consumer threads must tile the (m, j) columns");
+  using ST = RingStage<NC, KT>;
+  const int col = tid % COLS, m = col % HX, j = col / HX, kb = (tid / COLS) * KP;
+  constexpr int oB = offsetof(ST, B) / 8, oR = offsetof(ST, R) / 8, oZl = offsetof(ST, zlo) / 8, oZh = offsetof(ST, zhi) / 8,
+                oYl = offsetof(ST, ylo) / 8, oYh = offsetof(ST, yhi) / 8, oXg = offsetof(ST, xg) / 8, PL = NC * HX;
+  const int s0 = colour ^ ((j + kb) & 1);               // sA of the thread's first plane (k0 is even); alternates with kk
+  // x neighbour that is not the column itself: i - 1 where sA = 0, i + 1 where sA = 1
+  const int x0 = m > 0 ? oB + kb * PL + j * HX + m - 1 : oXg + kb * NC + j, x0s = m > 0 ? PL : NC;
+  const int x1 = m < HX - 1 ? oB + kb * PL + j * HX + m + 1 : oXg + kb * NC + j, x1s = m < HX - 1 ? PL : NC;
+  const int xe = s0 ? x1 : x0, xes = s0 ? x1s : x0s, xo = s0 ? x0 : x1, xos = s0 ? x0s : x1s;   // even / odd planes of the thread
+  const int yl = j > 0 ? oB + kb * PL + (j - 1) * HX + m : oYl + kb * HX + m, yls = j > 0 ? PL : HX;
+  const int yh = j < NC - 1 ? oB + kb * PL + (j + 1) * HX + m : oYh + kb * HX + m, yhs = j < NC - 1 ? PL : HX;
+  const int ctr = oB + kb * PL + j * HX + m;
+  const int zl = kb > 0 ? ctr - PL : oZl + j * HX + m;
+  const int zh = kb + KP < KT ? ctr + KP * PL : oZh + j * HX + m;
+  const int rr = oR + kb * PL + j * HX + m;
   int it = 0;
   for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
     const int s = it % STAGES, use = it / STAGES;
@@ -596,19 +657,18 @@ __global__ void __launch_bounds__(kRingThreads, 1) k_smooth_ring(const __grid_co
     }
 
     // ---- update this colour ----
+    {
+      const double* __restrict__ W = reinterpret_cast<const double*>(&T);
+      double* __restrict__ out = Ag + (size_t)(k0 + kb) * PL + col;
+      double cm = W[zl], c0 = W[ctr];
 #pragma unroll
-    for (int q = 0; q < PER; ++q) {
-      const int idx = q * kRingConsumers + tid;
-      const int m = idx % HX, j = (idx / HX) % NC, kk = idx / (HX * NC);
-      const int sA = colour ^ ((j + k0 + kk) & 1);
-      const int ml = m - 1 + sA, mh = m + sA;
-      const double xlo = ml >= 0 ? T.B[kk][j][ml] : T.xg[kk][j];
-      const double xhi = mh < HX ? T.B[kk][j][mh] : T.xg[kk][j];
-      const double ylo = j > 0 ? T.B[kk][j - 1][m] : T.ylo[kk][m];
-      const double yhi = j < NC - 1 ? T.B[kk][j + 1][m] : T.yhi[kk][m];
-      const double zlo = kk > 0 ? T.B[kk - 1][j][m] : T.zlo[j][m];
-      const double zhi = kk < KT - 1 ? T.B[kk + 1][j][m] : T.zhi[j][m];
-      Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - T.R[kk][j][m]);
+      for (int q = 0; q < KP; ++q) {
+        const double cp = q < KP - 1 ? W[ctr + (q + 1) * PL] : W[zh];
+        const double xn = (q & 1) ? W[xo + q * xos] : W[xe + q * xes];
+        const double ylo = W[yl + q * yls], yhi = W[yh + q * yhs];
+        out[q * PL] = fac * (idx2 * (xn + c0) + idy2 * (yhi + ylo) + idz2 * (cp + cm) - W[rr + q * PL]);
+        cm = c0; c0 = cp;
+      }
     }
 
     // ---- partition-face box: store the fresh face layers into the neighbour ranks' plane pools (see k_smooth_lpl_fast) ----
@@ -654,6 +714,11 @@ __global__ void __launch_bounds__(kRingThreads, 1) k_smooth_ring(const __grid_co
   }
 }
 
+// integer tuning knobs from the environment
+inline int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e && *e ? atoi(e) : dflt;
+}
 // number of SMs of the current device (grid of the persistent kernels)
 inline int sm_count() {
   static int n = 0;
@@ -667,21 +732,33 @@ inline int sm_count() {
   }
   return n;
 }
-int g_ring = 1;          // option "ring": 1 = persistent ring smoother on levels with at least 2 tiles per SM, 2 = always, 0 = never
+int g_ring = 0;          // option "ring": 1 = persistent ring smoother on levels with at least 2 tiles per SM, 2 = always, 0 = never
 
-template <int NC, int KT, int STAGES>
+template <int NC, int KT, int STAGES, int NCONS, int MINB>
 bool launch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(RingSmem<NC, KT, STAGES>);
+  auto kern = k_smooth_ring<NC, KT, STAGES, NCONS, MINB>;
   if (!configured) {
-    if (cudaFuncSetAttribute(k_smooth_ring<NC, KT, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
   const int n_tiles = (list ? n : L.nb) * (NC / KT);
-  const int grid = n_tiles < sm_count() ? n_tiles : sm_count();
-  auto kern = k_smooth_ring<NC, KT, STAGES>;
-  OMG_LAUNCH_T(kern, grid, kRingThreads, smem, s, L, P, colour, list, n_tiles, fused);
+  const int grid = n_tiles < MINB * sm_count() ? n_tiles : MINB * sm_count();
+  OMG_LAUNCH_T(kern, grid, NCONS + 32, smem, s, L, P, colour, list, n_tiles, fused);
   return true;
+}
+// shape of the ring kernel: OMG_RING_CFG = consumers * 100 + stages * 10 + CTAs per SM (tuning runs); default 512 / 2 / 2
+bool dispatch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
+  static const int cfg = env_int("OMG_RING_CFG", 51222);
+  switch (cfg) {
+    case 25651: return launch_smooth_ring<16, 16, 5, 256, 1>(L, P, colour, list, n, fused, s);
+    case 25622: return launch_smooth_ring<16, 16, 2, 256, 2>(L, P, colour, list, n, fused, s);
+    case 51251: return launch_smooth_ring<16, 16, 5, 512, 1>(L, P, colour, list, n, fused, s);
+    case 51231: return launch_smooth_ring<16, 16, 3, 512, 1>(L, P, colour, list, n, fused, s);
+    case 25613: return launch_smooth_ring<16, 16, 1, 256, 3>(L, P, colour, list, n, fused, s);
+    default: return launch_smooth_ring<16, 16, 2, 512, 2>(L, P, colour, list, n, fused, s);
+  }
 }
 
 // launch with the programmatic-stream-serialization attribute: the kernel may start before its predecessor in the stream
@@ -1057,11 +1134,6 @@ bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, i
   return launch_stencil_s<NC, KT, MODE, HELM, MB, VC, true>(L, Lc, P, nboxes, maxslot, s);
 }
 
-// resident CTAs per SM the register allocation is tuned for (OMG_STENCIL_MB = 2 | 3 | 4 overrides, for tuning runs)
-inline int env_int(const char* name, int dflt) {
-  const char* e = getenv(name);
-  return e && *e ? atoi(e) : dflt;
-}
 template <int MODE, bool HELM>
 bool dispatch_stencil_h(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   static const int mb = env_int("OMG_STENCIL_MB", 3);
@@ -1214,7 +1286,7 @@ bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, co
     return false;
   }
   if (P.op != OP_LPL && P.op != OP_HELMH) return false;
-  if (L.nc == 16 && g_ring && ((list ? n : L.nb) >= 2 * sm_count() || g_ring == 2)) return launch_smooth_ring<16, 16, 5>(L, P, colour, list, n, fused, s);
+  if (L.nc == 16 && g_ring && ((list ? n : L.nb) >= 2 * sm_count() || g_ring == 2)) return dispatch_smooth_ring(L, P, colour, list, n, fused, s);
   if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, fused, s);
   if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, fused, s);
   return false;

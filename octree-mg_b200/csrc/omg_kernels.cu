@@ -72,9 +72,9 @@ __global__ void __launch_bounds__(kThreads) k_prolong_var(const __grid_constant_
 
 __global__ void __launch_bounds__(kThreads) k_rb_fill(const __grid_constant__ LevelDev Lf,
                                                       const __grid_constant__ LevelDev Lc,
-                                                      const __grid_constant__ ParamsDev P, int iv, int gz) {
-  if (gz) do_rb_fill<GM_PHI_GZ>(Lf, Lc, P, iv, blockIdx.x, threadIdx.x, blockDim.x);
-  else do_rb_fill<GM_PHI>(Lf, Lc, P, iv, blockIdx.x, threadIdx.x, blockDim.x);
+                                                      const __grid_constant__ ParamsDev P, int iv, int gz, const double* rpl) {
+  if (gz) do_rb_fill<GM_PHI_GZ>(Lf, Lc, P, iv, blockIdx.x, threadIdx.x, blockDim.x, rpl);
+  else do_rb_fill<GM_PHI>(Lf, Lc, P, iv, blockIdx.x, threadIdx.x, blockDim.x, rpl);
 }
 
 template <int OP>
@@ -86,21 +86,21 @@ __global__ void __launch_bounds__(kThreads) k_apply_op(const __grid_constant__ L
 struct BcVar { int type[6]; double value[6]; };
 __global__ void __launch_bounds__(kThreads) k_fill_stored(const __grid_constant__ LevelDev L,
                                                           const __grid_constant__ ParamsDev P, int iv,
-                                                          const __grid_constant__ BcVar bc) {
-  do_fill_stored(L, P, iv, bc.type, bc.value, blockIdx.x, threadIdx.x, blockDim.x);
+                                                          const __grid_constant__ BcVar bc, const double* rpl, int n_recv) {
+  do_fill_stored(L, P, iv, bc.type, bc.value, blockIdx.x, threadIdx.x, blockDim.x, rpl, n_recv);
 }
 
 // ---- exchange pack / unpack (multi-rank; one CTA per message item) ---------------------------------
 // ghost phase: desc[4*e] = {kind (0 same-level, 1 coarse->fine), sender's local box, receiver's face, fine child offset}
 __global__ void __launch_bounds__(kThreads) k_pack_ghost(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
                                                          const __grid_constant__ ParamsDev P, const int* __restrict__ desc,
-                                                         double* __restrict__ out, int gz) {
+                                                         double* __restrict__ out, int gz, int iv) {
   const int e = blockIdx.x;
   const int kind = desc[4 * e], sb = desc[4 * e + 1], f = desc[4 * e + 2], off = desc[4 * e + 3];
   double* o = out + (size_t)e * L.nc * L.nc;
-  if (kind == 0) do_pack_face(L, sb, f, o, threadIdx.x, blockDim.x);
-  else if (gz) do_pack_rb_face<GM_PHI_GZ>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
-  else do_pack_rb_face<GM_PHI>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x);
+  if (kind == 0) do_pack_face(L, sb, f, o, threadIdx.x, blockDim.x, iv);
+  else if (gz) do_pack_rb_face<GM_PHI_GZ>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x, iv);
+  else do_pack_rb_face<GM_PHI>(Lc, P, sb, off, f, o, threadIdx.x, blockDim.x, iv);
 }
 // the same items as peer-mapped puts: item e goes straight into plane dst[2e+1] of the plane pool of rank dst[2e]
 // (peer_base[rank], mapped over NVLink), into the copy the receiver is NOT reading: (epoch + 1) & 1
@@ -138,6 +138,15 @@ __global__ void __launch_bounds__(kThreads) k_pack_prolong(const __grid_constant
   const int pw = (nc_f >> 1) + 2;
   do_pack_prolong(Lc, P, desc[2 * blockIdx.x], desc[2 * blockIdx.x + 1], out + (size_t)blockIdx.x * pw * pw * pw, nc_f,
                   threadIdx.x, blockDim.x);
+}
+
+// stand-alone mg_prolong of any variable: patch of coarse values (see do_pack_prolong_var)
+__global__ void __launch_bounds__(kThreads) k_pack_prolong_var(const __grid_constant__ LevelDev Lc, const __grid_constant__ ParamsDev P,
+                                                               const int* __restrict__ desc, double* __restrict__ out, int nc_f, int iv) {
+  const int pw = (nc_f >> 1) + 2;
+  double* o = out + (size_t)blockIdx.x * pw * pw * pw;
+  if (iv == 0) do_pack_prolong_var<GM_PHI>(Lc, P, iv, desc[2 * blockIdx.x], desc[2 * blockIdx.x + 1], o, nc_f, threadIdx.x, blockDim.x);
+  else do_pack_prolong_var<GM_STORED>(Lc, P, iv, desc[2 * blockIdx.x], desc[2 * blockIdx.x + 1], o, nc_f, threadIdx.x, blockDim.x);
 }
 
 // elementwise helpers over whole-level arrays
@@ -306,22 +315,25 @@ void prolong_var(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int
   if (Lf.nb == 0) return;
   k_prolong_var<<<Lf.nb, kThreads, 0, s>>>(Lf, Lc, P, iv, iv_to, add);
 }
-void rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int gz, cudaStream_t s) {
+void rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int gz, cudaStream_t s, const double* rpl) {
   if (Lf.n_rb == 0) return;
-  k_rb_fill<<<Lf.n_rb, kThreads, 0, s>>>(Lf, Lc, P, iv, gz);
+  k_rb_fill<<<Lf.n_rb, kThreads, 0, s>>>(Lf, Lc, P, iv, gz, rpl);
 }
 void apply_op(const LevelDev& L, const ParamsDev& P, int i_out, cudaStream_t s) {
   if (L.nb == 0) return;
   OMG_SWITCH_OP(P.op, (k_apply_op<OP><<<L.nb, kThreads, 0, s>>>(L, P, i_out)));
 }
-void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv, cudaStream_t s) {
+void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv, cudaStream_t s, const double* rpl, int n_recv) {
   if (L.nb == 0) return;
   BcVar bc;
   for (int f = 0; f < 6; ++f) { bc.type[f] = bct[f]; bc.value[f] = bcv[f]; }
-  k_fill_stored<<<L.nb, kThreads, 0, s>>>(L, P, iv, bc);
+  k_fill_stored<<<L.nb, kThreads, 0, s>>>(L, P, iv, bc, rpl, n_recv);
 }
-void pack_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int gz, cudaStream_t s) {
-  if (n) k_pack_ghost<<<n, kThreads, 0, s>>>(L, Lc, P, desc, out, gz);
+void pack_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int gz, cudaStream_t s, int iv) {
+  if (n) k_pack_ghost<<<n, kThreads, 0, s>>>(L, Lc, P, desc, out, gz, iv);
+}
+void pack_prolong_var(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, int iv, cudaStream_t s) {
+  if (n) k_pack_prolong_var<<<n, kThreads, 0, s>>>(Lc, P, desc, out, nc_f, iv);
 }
 void put_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, const int* dst, int n, double* const* peer_base,
                const long long* peer_stride, const unsigned long long* epoch, int gz, cudaStream_t s) {

@@ -27,16 +27,17 @@ void crhs(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
 void oldpl(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
 void corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s);
 void prolong_var(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int iv_to, int add, cudaStream_t s);
-void rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int gz, cudaStream_t s);
+void rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int gz, cudaStream_t s, const double* rpl = nullptr);
 void apply_op(const LevelDev& L, const ParamsDev& P, int i_out, cudaStream_t s);
-void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv, cudaStream_t s);
-void pack_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int gz, cudaStream_t s);
+void fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv, cudaStream_t s, const double* rpl = nullptr, int n_recv = 0);
+void pack_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int gz, cudaStream_t s, int iv = 0);
 // ghost items stored directly into the receivers' plane pools (peer-mapped), copy (epoch + 1) & 1
 void put_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const int* desc, const int* dst, int n, double* const* peer_base,
                const long long* peer_stride, const unsigned long long* epoch, int gz, cudaStream_t s);
 void pack_restrict(const LevelDev& Lf, const int* desc, int n, double* out, int iv0, int iv1, cudaStream_t s);
 void unpack_restrict(const LevelDev& Lc, const int* desc, int n, const double* in, int h, int iv0, int iv1, cudaStream_t s);
 void pack_prolong(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, cudaStream_t s);
+void pack_prolong_var(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, int iv, cudaStream_t s);
 void fill(double* p, size_t n, double v, cudaStream_t s);
 void copy(double* dst, const double* src, size_t n, cudaStream_t s);
 void sub_scalar(double* p, size_t n, const double* mean, cudaStream_t s);

@@ -190,6 +190,21 @@ __device__ void do_pack_prolong(const LevelDev& Lc, const ParamsDev& P, int p, i
   }
 }
 
+// the same for the stand-alone mg_prolong of any variable (src/m_prolong.f90:51-85): the patch holds the coarse VALUES
+// (ghost cells through cell_at with the variable's ghost mode); edges and corners are never read
+template <int GMV>
+__device__ void do_pack_prolong_var(const LevelDev& Lc, const ParamsDev& P, int iv, int p, int off, double* __restrict__ out, int nc_f,
+                                    int tid, int nthr) {
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  const int h = nc_f >> 1, pw = h + 2;
+  const double* cv = Lc.var[iv]; const double* cf = Lc.faces[iv];
+  for (int r = tid; r < pw * pw * pw; r += nthr) {
+    const int a = r % pw, bb = (r / pw) % pw, c = r / (pw * pw);
+    const int nedge = (a == 0 || a == pw - 1) + (bb == 0 || bb == pw - 1) + (c == 0 || c == pw - 1);
+    out[r] = nedge <= 1 ? cell_at<GMV>(Lc, P, cv, cf, p, ox + a - 1, oy + bb - 1, oz + c - 1) : 0.0;
+  }
+}
+
 // restrict_set_buffer (src/m_restrict.f90:116-163): restricted block of child b for a parent on another rank
 __device__ void do_pack_restrict(const LevelDev& Lf, int iv, int b, double* __restrict__ out, int tid, int nthr) {
   const int h = Lf.nc >> 1;
@@ -219,10 +234,10 @@ __device__ void do_unpack_restrict(const LevelDev& Lc, int iv, int p, int off, c
 
 // buffer_for_nb (src/m_ghost_cells.f90:348-383): the interior layer of box sb that a same-level
 // neighbour on another rank needs as its ghost face f (f = face of the RECEIVER)
-__device__ void do_pack_face(const LevelDev& L, int sb, int f, double* __restrict__ out, int tid, int nthr) {
+__device__ void do_pack_face(const LevelDev& L, int sb, int f, double* __restrict__ out, int tid, int nthr, int iv = 0) {
   const int nc = L.nc;
   const int layer = (f & 1) ? 0 : nc - 1;
-  const double* v = L.var[0] + (size_t)sb * L.bs;
+  const double* v = L.var[iv] + (size_t)sb * L.bs;
   for (int idx = tid; idx < nc * nc; idx += nthr) {
     const int t1 = idx % nc, t2 = idx / nc;
     int i, j, k;
@@ -236,19 +251,24 @@ template <int GMV>
 __device__ void do_prolong_var(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int iv_to, int add,
                                int b, int tid, int nthr) {
   const int p = Lf.parent[b];
-  if (p < 0) return;
+  if (p == -1) return;
   const int off = Lf.coff[b];
   const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
-  const int h = Lf.nc >> 1;
+  const int h = Lf.nc >> 1, pw = h + 2;
   const double* cv = Lc.var[iv]; const double* cf = Lc.faces[iv];
+  // parent on another rank: the (nc/2+2)^3 patch of coarse values around the octant arrived with the prolong exchange
+  const double* patch = p <= -2 ? Lf.ppatch + (size_t)(-(p + 2)) * pw * pw * pw : nullptr;
   double* dst = Lf.var[iv_to] + (size_t)b * Lf.bs;
+  auto C = [&](int a, int bb, int c) -> double {
+    if (patch) return patch[((size_t)(c + 1) * pw + (bb + 1)) * pw + (a + 1)];
+    return cell_at<GMV>(Lc, P, cv, cf, p, ox + a, oy + bb, oz + c);
+  };
   for (int idx = tid; idx < h * h * h; idx += nthr) {
     const int I = idx % h, J = (idx / h) % h, K = idx / (h * h);
-    const int ic = ox + I, jc = oy + J, kc = oz + K;
-    const double f0 = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc, kc);
-    const double flx = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic - 1, jc, kc), fhx = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic + 1, jc, kc);
-    const double fly = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc - 1, kc), fhy = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc + 1, kc);
-    const double flz = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc, kc - 1), fhz = 0.25 * cell_at<GMV>(Lc, P, cv, cf, p, ic, jc, kc + 1);
+    const double f0 = 0.25 * C(I, J, K);
+    const double flx = 0.25 * C(I - 1, J, K), fhx = 0.25 * C(I + 1, J, K);
+    const double fly = 0.25 * C(I, J - 1, K), fhy = 0.25 * C(I, J + 1, K);
+    const double flz = 0.25 * C(I, J, K - 1), fhz = 0.25 * C(I, J, K + 1);
     for (int kk = 0; kk < 2; ++kk) for (int jj = 0; jj < 2; ++jj) for (int ii = 0; ii < 2; ++ii) {
       const double fine = f0 + (ii ? fhx : flx) + (jj ? fhy : fly) + (kk ? fhz : flz);
       const int q = cidx(Lf, 2 * I + ii, 2 * J + jj, 2 * K + kk);
@@ -289,17 +309,18 @@ __device__ __forceinline__ double rb_gc_value(const LevelDev& Lc, const ParamsDe
 // box on another rank (fine child offset `off`, receiver face f) from its coarse box cb
 template <int GMC>
 __device__ void do_pack_rb_face(const LevelDev& Lc, const ParamsDev& P, int cb, int off, int f, double* __restrict__ out,
-                                int tid, int nthr) {
+                                int tid, int nthr, int iv = 0) {
   const int nc = Lc.nc;
   const int di[3] = {off & 1023, (off >> 10) & 1023, (off >> 20) & 1023};
-  for (int idx = tid; idx < nc * nc; idx += nthr) out[idx] = rb_gc_value<GMC>(Lc, P, 0, cb, di, f, idx % nc, idx / nc);
+  for (int idx = tid; idx < nc * nc; idx += nthr) out[idx] = rb_gc_value<GMC>(Lc, P, iv, cb, di, f, idx % nc, idx / nc);
 }
 
 // fill_refinement_bnd + box_gc_for_fine_neighbor + sides_rb (src/m_ghost_cells.f90:287-328, :500-577,
 // :769-861) for refinement-boundary entry e of the fine level: materialises the ghost plane.
 // GMC = GM_PHI normally, GM_PHI_GZ while the coarse ghosts are the zeros written by mg_fas_fmg.
 template <int GMC>
-__device__ void do_rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int e, int tid, int nthr) {
+__device__ void do_rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int iv, int e, int tid, int nthr,
+                           const double* rpl = nullptr) {
   const int b = Lf.rb_list[4 * e], f = Lf.rb_list[4 * e + 1], cb = Lf.rb_list[4 * e + 2], pl = Lf.rb_list[4 * e + 3];
   if (cb == -1) return;
   const int nc = Lf.nc;
@@ -309,7 +330,8 @@ __device__ void do_rb_fill(const LevelDev& Lf, const LevelDev& Lc, const ParamsD
   const double* fv = Lf.var[iv] + (size_t)b * Lf.bs;
   const int ix = (f & 1) ? nc - 1 : 0, dix = (f & 1) ? -1 : 1;
   // coarse neighbour on another rank: the interpolated coarse values arrived with the halo exchange
-  const double* gcpl = cb <= -2 ? gpl_cur(Lf) + (size_t)(-(cb + 2)) * nc * nc : nullptr;
+  // (extra variables: with their own exchange, in the receive buffer rpl)
+  const double* gcpl = cb <= -2 ? (rpl ? rpl : gpl_cur(Lf)) + (size_t)(-(cb + 2)) * nc * nc : nullptr;
   double* out = (iv == 0) ? gpl_cur(Lf) + (size_t)pl * nc * nc : Lf.faces[iv] + ((size_t)b * 6 + f) * nc * nc;
   for (int idx = tid; idx < nc * nc; idx += nthr) {
     const int A = idx % nc, B = idx / nc;          // 0-based fine tangential indices
@@ -334,8 +356,10 @@ __device__ void do_apply_op(const LevelDev& L, const ParamsDev& P, int i_out, in
 // materialise the ghost faces of a stored-face variable (mg_fill_ghost_cells_lvl for iv >= 5):
 // same-level copy and physical boundary (constant bc of that variable); refinement boundaries are
 // handled by do_rb_fill.  bc_type / bc_value are the variable's constants for face f.
+// rpl / n_recv: planes of this variable received from other ranks (same-level faces are planes 0 .. n_recv-1 of the
+// level's ghost plan, in plan order: the face table's FK_PLANE argument indexes them)
 __device__ void do_fill_stored(const LevelDev& L, const ParamsDev& P, int iv, const int* bct, const double* bcv,
-                               int b, int tid, int nthr) {
+                               int b, int tid, int nthr, const double* rpl = nullptr, int n_recv = 0) {
   const int nc = L.nc;
   const double* v = L.var[iv];
   for (int idx = tid; idx < 6 * nc * nc; idx += nthr) {
@@ -362,6 +386,8 @@ __device__ void do_fill_stored(const LevelDev& L, const ParamsDev& P, int iv, co
       const double x1 = v[(size_t)b * L.bs + cidx(L, i1, j1, k1)];
       const double x2 = nc > 1 ? v[(size_t)b * L.bs + cidx(L, i2, j2, k2)] : 0.0;
       *out = c0 * bcv[f] + c1 * x1 + c2 * x2;
+    } else if (kind == FK_PLANE && rpl && arg < n_recv) {
+      *out = rpl[(size_t)arg * nc * nc + r];
     }
   }
 }

@@ -31,6 +31,7 @@ constexpr int MAXT = 1024;
 unsigned char* g_smem = nullptr;      // the CTA's dynamic shared memory
 size_t g_smem_bytes = 0;              // as passed to the launch
 pthread_barrier_t g_cta_bar, g_warp_bar[MAXT / 32], g_named_bar;
+int g_named_count = 256;
 double g_shfl[MAXT];
 int g_shfl_i[MAXT];
 // mbarriers with their real semantics (the persistent ring kernel runs a producer warp ahead of the consumers): pending
@@ -131,7 +132,7 @@ static inline void cp_async16(void* dst, const void* src) {
 static inline void fence_proxy_async() {}
 static inline void cp_async_arrive(uint64_t* bar) { mbar_arrive(bar); }
 static inline void consumer_sync(int nthreads) {
-  if (nthreads != 256) emu::violation("named barrier: the emulator expects the 256 consumer threads");
+  if (nthreads != emu::g_named_count) emu::violation("named barrier: thread count differs from the CTA's consumer threads");
   pthread_barrier_wait(&emu::g_named_bar);
 }
 static inline int shfl_int(int v, int src) {
@@ -167,7 +168,8 @@ void launch(int grid, int nthreads, size_t smem, const std::function<void()>& bo
   if (smem > 227 * 1024) violation("launch: more than 227 KB of shared memory");
   blockDim.x = (unsigned)nthreads; gridDim.x = (unsigned)grid; if (getenv("FE_TRACE")) std::fprintf(stderr, "launch grid %d threads %d smem %zu\n", grid, nthreads, smem);
   pthread_barrier_init(&g_cta_bar, nullptr, nthreads);
-  pthread_barrier_init(&g_named_bar, nullptr, 256);
+  g_named_count = nthreads > 256 ? nthreads - 32 : 256;      // ring kernels: every warp but the producer
+  pthread_barrier_init(&g_named_bar, nullptr, g_named_count);
   for (auto& w : g_warp_bar) pthread_barrier_init(&w, nullptr, 32);
   std::vector<std::thread> th;
   th.reserve(nthreads);
