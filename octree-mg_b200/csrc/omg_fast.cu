@@ -48,6 +48,16 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// shared -> global bulk copy (TMA store), bulk-group completion: the issuing thread commits the group and waits until the
+// source has been read (the CTA may then exit; the writes themselves complete before the grid does)
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit_wait_read() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
 // wait for a peer's flag (same protocol as omg_comm.cu): an acquire load, so that the peer's puts -- released by its
 // st.release.sys of the flag -- are visible afterwards; bounded by timeout_ns (0 = wait for ever): a peer that does not
 // arrive raises the error word, which the host finds at its next synchronisation point (the handle is then poisoned)
@@ -466,12 +476,14 @@ struct RingSmem {
   uint64_t full[STAGES], empty[STAGES];
 };
 
-template <int NC, int KT, int STAGES, int NCONS, int MINB>
-__global__ void __launch_bounds__(NCONS + 32, MINB) k_smooth_ring(const __grid_constant__ LevelDev L, const __grid_constant__ ParamsDev P, int colour,
+template <int NC, int KT, int STAGES, int NCONS, int MINB, int NPW>
+__global__ void __launch_bounds__(NCONS + 32 * NPW, MINB) k_smooth_ring(const __grid_constant__ LevelDev L, const __grid_constant__ ParamsDev P, int colour,
                                                               const int* __restrict__ boxlist, int n_tiles, int fused_put) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
   constexpr int kRingConsumers = NCONS;
+  constexpr int NPT = 32 * NPW;                  // producer threads: one warp issues 645 instructions per tile (ncu r02e) = 3900 cycles,
+                                                 // more than the tile's share of the HBM time; NPW warps split the ghost gathers
   using SM = RingSmem<NC, KT, STAGES>;
   OMG_DYN_SMEM(smem_raw, 128);
   SM& S = *reinterpret_cast<SM*>(smem_raw);
@@ -479,37 +491,50 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) k_smooth_ring(const __grid_c
   const int oc = colour ^ 1;
   const double* __restrict__ phi = L.var[0];
   if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&S.full[s], 1 + 32); mbar_init(&S.empty[s], kRingConsumers / 32); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&S.full[s], 1 + NPT); mbar_init(&S.empty[s], kRingConsumers / 32); }
   }
   __syncthreads();
 
   if (tid >= kRingConsumers) {
     // ------------------------------------------------ producer warp ------------------------------------------------
+    // The face tables of a tile are read one tile ahead (box index of a box list: two ahead): a single warp that loaded
+    // them only when it needed them paid one global-memory latency per tile, which bounded the whole kernel at one tile
+    // per ~2.2 us and SM whatever the number of stages or consumers (profiles/r02d_*: 0.51 ms with one CTA per SM).
     int it = 0;
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+    const int stride = gridDim.x;
+    const int pt = tid - kRingConsumers;           // 0 .. NPT-1; warp 0 of the producers issues the bulk copies
+    auto box_of = [&](int tt) { return tt < n_tiles ? (boxlist ? boxlist[tt / TILES] : tt / TILES) : 0; };
+    int b_n = box_of(blockIdx.x), b_nn = box_of(blockIdx.x + stride);
+    int kv_n = 0, av_n = 0, slot_n = -1;
+    auto fetch_tables = [&](int bb) {
+      if (lane < 6) { kv_n = L.fkind[bb * 6 + lane]; av_n = L.farg[bb * 6 + lane]; }
+      if (fused_put && lane == 0) slot_n = L.put.slot_of[bb];
+    };
+    fetch_tables(b_n);
+    for (int t = blockIdx.x; t < n_tiles; t += stride, ++it) {
       const int s = it % STAGES, use = it / STAGES;
+      const int b = b_n, kv = kv_n, av = av_n, slot_l = slot_n;
+      b_n = b_nn; b_nn = box_of(t + 2 * stride);
+      if (t + stride < n_tiles) fetch_tables(b_n);              // in flight while this tile's copies are issued
       if (use > 0) mbar_wait(&S.empty[s], (use - 1) & 1);       // the consumers have finished with the stage's previous tile
       RingStage<NC, KT>& T = S.st[s];
-      const int b = boxlist ? boxlist[t / TILES] : t / TILES;
       const int k0 = (t % TILES) * KT;
-      int kv = 0, av = 0;
-      if (lane < 6) { kv = L.fkind[b * 6 + lane]; av = L.farg[b * 6 + lane]; }
       int kind[6], arg[6];
 #pragma unroll
       for (int f = 0; f < 6; ++f) { kind[f] = shfl_int(kv, f); arg[f] = shfl_int(av, f); }
       int put_slot = -1;
-      if (fused_put) { if (lane == 0) put_slot = L.put.slot_of[b]; put_slot = shfl_int(put_slot, 0); }
+      if (fused_put) put_slot = shfl_int(slot_l, 0);
       // partition-face box: the peers' faces of the previous half-sweep must have landed before the consumers read them
-      if (put_slot >= 0 && lane < L.put.n_peers)
-        wait_flag(L.put.flags + L.put.channel * L.put.nranks + L.put.peers[lane], *L.put.epoch, L.put.err, L.put.timeout_ns,
-                  1 + L.put.peers[lane] + 64 * L.put.channel);
+      if (put_slot >= 0 && pt < L.put.n_peers)
+        wait_flag(L.put.flags + L.put.channel * L.put.nranks + L.put.peers[pt], *L.put.epoch, L.put.err, L.put.timeout_ns,
+                  1 + L.put.peers[pt] + 64 * L.put.channel);
       __syncwarp();
       const size_t boxoff = (size_t)b * L.bs;
       const double* __restrict__ Bg = phi + boxoff + (size_t)oc * L.cs;        // other colour of this box
       const double* __restrict__ Ag = phi + boxoff + (size_t)colour * L.cs;    // colour being updated (its old values: phi(1) of bc_to_gc)
       const double* __restrict__ Rg = L.var[1] + boxoff + (size_t)colour * L.cs;
       const bool zlo_in = (k0 > 0), zhi_in = (k0 + KT < NC);
-      if (lane == 0) {
+      if (pt == 0) {
 #pragma unroll
         for (int f = 0; f < 6; ++f) { T.hdr[f] = kind[f]; T.hdr[6 + f] = arg[f]; }
         T.hdr[12] = b; T.hdr[13] = k0; T.hdr[14] = put_slot;
@@ -519,13 +544,13 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) k_smooth_ring(const __grid_c
         mbar_arrive_expect_tx(&S.full[s], bytes);
         bulk_g2s(&T.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.full[s]);
       }
-      if (lane == 1) bulk_g2s(&T.R[0][0][0], Rg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.full[s]);
-      if (lane == 2) {
+      if (pt == 1) bulk_g2s(&T.R[0][0][0], Rg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.full[s]);
+      if (pt == 2) {
         if (zlo_in) bulk_g2s(&T.zlo[0][0], Bg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.full[s]);
         else if (kind[4] == FK_SAME) bulk_g2s(&T.zlo[0][0], phi + (size_t)arg[4] * L.bs + (size_t)oc * L.cs + (size_t)(NC - 1) * NC * HX, NC * HX * 8, &S.full[s]);
         else if (kind[4] == FK_PHYS) bulk_g2s(&T.zlo[0][0], Ag, NC * HX * 8, &S.full[s]);                                  // own layer k = 0
       }
-      if (lane == 3) {
+      if (pt == 3) {
         if (zhi_in) bulk_g2s(&T.zhi[0][0], Bg + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.full[s]);
         else if (kind[5] == FK_SAME) bulk_g2s(&T.zhi[0][0], phi + (size_t)arg[5] * L.bs + (size_t)oc * L.cs, NC * HX * 8, &S.full[s]);
         else if (kind[5] == FK_PHYS) bulk_g2s(&T.zhi[0][0], Ag + (size_t)(NC - 1) * NC * HX, NC * HX * 8, &S.full[s]);       // own layer k = NC-1
@@ -534,7 +559,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) k_smooth_ring(const __grid_c
       // j = 0 / NC-1 at a physical boundary
       // (16-byte cp.async pieces: 32 + 32 short rows per tile would keep the TMA unit busier than the four big copies)
       constexpr int CH = HX / 2;                       // 16-byte pieces per row
-      for (int q = lane; q < 2 * KT * CH; q += 32) {
+      for (int q = pt; q < 2 * KT * CH; q += NPT) {
         const int c = q % CH, kk = (q / CH) % KT, hi = q / (CH * KT);
         const int kf = hi ? kind[3] : kind[2], af = hi ? arg[3] : arg[2];
         const double* src = nullptr;
@@ -543,7 +568,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) k_smooth_ring(const __grid_c
         if (src) cp_async16((hi ? &T.yhi[kk][0] : &T.ylo[kk][0]) + 2 * c, src + 2 * c);
       }
       // x ghosts: one 8-byte value per row (strided in the neighbour / in the box itself)
-      for (int r = lane; r < KT * NC; r += 32) {
+      for (int r = pt; r < KT * NC; r += NPT) {
         const int kk = r / NC, j = r % NC;
         const int sA = colour ^ ((j + k0 + kk) & 1);     // 0: this row's updated cells are i = 0, 2, ..: needs i = -1
         const int kf = sA ? kind[1] : kind[0], af = sA ? arg[1] : arg[0];
@@ -734,30 +759,32 @@ inline int sm_count() {
 }
 int g_ring = 0;          // option "ring": 1 = persistent ring smoother on levels with at least 2 tiles per SM, 2 = always, 0 = never
 
-template <int NC, int KT, int STAGES, int NCONS, int MINB>
+template <int NC, int KT, int STAGES, int NCONS, int MINB, int NPW>
 bool launch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(RingSmem<NC, KT, STAGES>);
-  auto kern = k_smooth_ring<NC, KT, STAGES, NCONS, MINB>;
+  auto kern = k_smooth_ring<NC, KT, STAGES, NCONS, MINB, NPW>;
   if (!configured) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
   const int n_tiles = (list ? n : L.nb) * (NC / KT);
   const int grid = n_tiles < MINB * sm_count() ? n_tiles : MINB * sm_count();
-  OMG_LAUNCH_T(kern, grid, NCONS + 32, smem, s, L, P, colour, list, n_tiles, fused);
+  OMG_LAUNCH_T(kern, grid, NCONS + 32 * NPW, smem, s, L, P, colour, list, n_tiles, fused);
   return true;
 }
-// shape of the ring kernel: OMG_RING_CFG = consumers * 100 + stages * 10 + CTAs per SM (tuning runs); default 512 / 2 / 2
+// shape of the ring kernel: OMG_RING_CFG = consumers * 1000 + stages * 100 + CTAs per SM * 10 + producer warps (tuning runs)
 bool dispatch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
-  static const int cfg = env_int("OMG_RING_CFG", 51222);
+  static const int cfg = env_int("OMG_RING_CFG", 256514);
   switch (cfg) {
-    case 25651: return launch_smooth_ring<16, 16, 5, 256, 1>(L, P, colour, list, n, fused, s);
-    case 25622: return launch_smooth_ring<16, 16, 2, 256, 2>(L, P, colour, list, n, fused, s);
-    case 51251: return launch_smooth_ring<16, 16, 5, 512, 1>(L, P, colour, list, n, fused, s);
-    case 51231: return launch_smooth_ring<16, 16, 3, 512, 1>(L, P, colour, list, n, fused, s);
-    case 25613: return launch_smooth_ring<16, 16, 1, 256, 3>(L, P, colour, list, n, fused, s);
-    default: return launch_smooth_ring<16, 16, 2, 512, 2>(L, P, colour, list, n, fused, s);
+    case 256511: return launch_smooth_ring<16, 16, 5, 256, 1, 1>(L, P, colour, list, n, fused, s);
+    case 256512: return launch_smooth_ring<16, 16, 5, 256, 1, 2>(L, P, colour, list, n, fused, s);
+    case 512514: return launch_smooth_ring<16, 16, 5, 512, 1, 4>(L, P, colour, list, n, fused, s);
+    case 512414: return launch_smooth_ring<16, 16, 4, 512, 1, 4>(L, P, colour, list, n, fused, s);
+    case 256221: return launch_smooth_ring<16, 16, 2, 256, 2, 1>(L, P, colour, list, n, fused, s);
+    case 256222: return launch_smooth_ring<16, 16, 2, 256, 2, 2>(L, P, colour, list, n, fused, s);
+    case 512222: return launch_smooth_ring<16, 16, 2, 512, 2, 2>(L, P, colour, list, n, fused, s);
+    default: return launch_smooth_ring<16, 16, 5, 256, 1, 4>(L, P, colour, list, n, fused, s);
   }
 }
 
@@ -1249,6 +1276,104 @@ __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid
   }
 }
 
+// Box 16, TMA version: the child's 32 KiB of phi (both colours, contiguous) arrive by ONE bulk copy that is in flight
+// from the first instruction -- it depends on nothing but the box index -- while the correction patch is gathered (a
+// chain of dependent loads: parent index -> parent cells / face table -> neighbour cells); the update happens in place in
+// shared memory and leaves by one bulk store.  The register-prefetch version above holds a CTA for ~8.9 us
+// (4 CTAs / SM, 0.49 ms per launch on 32768 boxes = 0.75 of the measured HBM peak, profiles/r02d_*): its phi loads
+// start only after the parent index has arrived and the second half of them only after the first half was consumed.
+template <int NC, int MB>
+__global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_tma(const __grid_constant__ LevelDev Lf, const __grid_constant__ LevelDev Lc,
+                                                               const __grid_constant__ ParamsDev P) {
+  constexpr int HC = NC / 2, HX = NC / 2, PW = HC + 2, NIT = HC * HC * HC / kThreads, BOX = 2 * NC * NC * HX;
+  static_assert((HC * HC * HC) % kThreads == 0, "coarse cells must tile the CTA");
+  OMG_DYN_SMEM(smem_raw, 128);
+  double* F = reinterpret_cast<double*>(smem_raw);                 // [2][NC][NC][HX]: the fine box as in global memory
+  double* corr = F + BOX;                                          // [PW][PW][PW]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(corr + PW * PW * PW + (PW * PW * PW & 1));
+  const int tid = threadIdx.x, b = blockIdx.x;
+  double* __restrict__ phi = Lf.var[0] + (size_t)b * Lf.bs;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    mbar_arrive_expect_tx(bar, BOX * 8);
+    bulk_g2s(F, phi, BOX * 8, bar);
+  }
+  const int p = Lf.parent[b];
+  const int off = Lf.coff[b];
+  if (p == -1) {                      // no parent (uniform across the CTA): the copy must still land before the CTA may exit
+    __syncthreads();
+    mbar_wait(bar, 0);
+    return;
+  }
+  const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
+  if (p <= -2) {   // parent on another rank: the patch arrived with the prolong exchange
+    const double* __restrict__ patch = Lf.ppatch + (size_t)(-(p + 2)) * PW * PW * PW;
+    for (int r = tid; r < PW * PW * PW; r += kThreads) corr[r] = patch[r];
+  } else {
+    const double* __restrict__ pc = Lc.var[0] + (size_t)p * Lc.bs;
+    const double* __restrict__ po = Lc.var[2] + (size_t)p * Lc.bs;
+    double* __restrict__ pr = Lc.var[3] + (size_t)p * Lc.bs;
+    const int ccs = Lc.cs;
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int r = it * kThreads + tid;
+      const int a = r % HC, bb = (r / HC) % HC, c = r / (HC * HC);
+      const int ic = ox + a, jc = oy + bb, kc = oz + c;
+      const int g = ((ic + jc + kc) & 1) * ccs + (kc * NC + jc) * HX + (ic >> 1);
+      const double v = pc[g] - po[g];
+      corr[((c + 1) * PW + (bb + 1)) * PW + (a + 1)] = v;
+      pr[g] = v;
+    }
+    for (int r = tid; r < 6 * HC * HC; r += kThreads) {
+      const int f = r / (HC * HC), t = r % (HC * HC), t1 = t % HC + 1, t2 = t / HC + 1;
+      const int e = (f & 1) ? PW - 1 : 0;
+      int a, bb, c;
+      if (f < 2) { a = e; bb = t1; c = t2; } else if (f < 4) { a = t1; bb = e; c = t2; } else { a = t1; bb = t2; c = e; }
+      const int ic = ox + a - 1, jc = oy + bb - 1, kc = oz + c - 1;
+      corr[(c * PW + bb) * PW + a] = cell_at<GM_PHI>(Lc, P, Lc.var[0], nullptr, p, ic, jc, kc) - cell_at<GM_OLD>(Lc, P, Lc.var[2], nullptr, p, ic, jc, kc);
+    }
+  }
+  __syncthreads();                    // corr complete (and the barrier initialisation visible to every thread)
+  mbar_wait(bar, 0);
+  // in place: one thread per coarse cell and iteration = 2x2x2 fine cells.  Rows 2J and 2J + 2 are 16 doubles apart = the
+  // same banks, so odd-J threads visit their two rows in the opposite order (as in k_stencil_fast).
+#pragma unroll
+  for (int it = 0; it < NIT; ++it) {
+    const int q = it * kThreads + tid;
+    const int I = q % HC, J = (q / HC) % HC, K = q / (HC * HC);
+    const int sw = J & 1;
+    const int c = ((K + 1) * PW + (J + 1)) * PW + (I + 1);
+    const double f0 = 0.25 * corr[c];
+    const double flx = 0.25 * corr[c - 1], fhx = 0.25 * corr[c + 1];
+    const double fly = 0.25 * corr[c - PW], fhy = 0.25 * corr[c + PW];
+    const double flz = 0.25 * corr[c - PW * PW], fhz = 0.25 * corr[c + PW * PW];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int di = e & 1, dj = ((e >> 1) & 1) ^ sw, dk = e >> 2;
+      const double fine = f0 + (di ? fhx : flx) + (dj ? fhy : fly) + (dk ? fhz : flz);
+      const int g = ((di + dj + dk) & 1) * (NC * NC * HX) + ((2 * K + dk) * NC + (2 * J + dj)) * HX + I;
+      F[g] = F[g] + fine;
+    }
+  }
+  fence_proxy_async();                // generic-proxy writes to F before the async proxy (TMA store) reads them
+  __syncthreads();
+  if (tid == 0) { bulk_s2g(phi, F, BOX * 8); bulk_commit_wait_read(); }
+}
+
+template <int NC, int MB>
+bool launch_corr_prolong_tma(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s) {
+  static bool configured = false;
+  constexpr int PW = NC / 2 + 2;
+  const size_t smem = sizeof(double) * (2 * NC * NC * (NC / 2) + PW * PW * PW + (PW * PW * PW & 1)) + 16;
+  auto kern = k_corr_prolong_tma<NC, MB>;
+  if (!configured) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    configured = true;
+  }
+  OMG_LAUNCH(kern, Lf.nb, smem, s, Lf, Lc, P);
+  return true;
+}
+
 template <int NC, int MB>
 bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s) {
   static bool configured = false;
@@ -1309,6 +1434,8 @@ bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s) 
 bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool, cudaStream_t s) {
   if (Lf.nb == 0 || Lc.nc != Lf.nc) return false;
   static const int mb = env_int("OMG_PROLONG_MB", 4);
+  static const int tma = env_int("OMG_PROLONG_TMA", 5);        // CTAs per SM of the TMA version (0: register-prefetch version)
+  if (Lf.nc == 16 && tma && !g_pdl) return tma == 4 ? launch_corr_prolong_tma<16, 4>(Lf, Lc, P, s) : tma == 3 ? launch_corr_prolong_tma<16, 3>(Lf, Lc, P, s) : launch_corr_prolong_tma<16, 5>(Lf, Lc, P, s);
   if (Lf.nc == 16) return mb == 4 ? launch_corr_prolong<16, 4>(Lf, Lc, P, s) : mb == 2 ? launch_corr_prolong<16, 2>(Lf, Lc, P, s) : launch_corr_prolong<16, 3>(Lf, Lc, P, s);
   if (Lf.nc == 32) return launch_corr_prolong<32, 3>(Lf, Lc, P, s);
   return false;

@@ -119,6 +119,13 @@ static inline void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t
   emu::MBar& b = mb_of(bar);
   b.tx -= bytes; emu::g_tx_done += bytes; emu::mb_check(b);
 }
+// TMA store: the source must lie in the CTA's shared memory; alignment rules as for the load
+static inline void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+  if (((uintptr_t)dst & 15) || ((uintptr_t)src & 15) || (bytes & 15) || bytes == 0) emu::violation("bulk store: address or size not a multiple of 16");
+  if (!in_smem(src, bytes)) emu::violation("bulk store: source outside the CTA's shared memory");
+  std::memcpy(dst, src, bytes);
+}
+static inline void bulk_commit_wait_read() {}
 static inline void cp_async8(void* dst, const void* src) {
   if (((uintptr_t)dst & 7) || ((uintptr_t)src & 7)) emu::violation("cp.async: address not a multiple of 8");
   if (!in_smem(dst, 8)) emu::violation("cp.async: destination outside the CTA's shared memory");
@@ -168,7 +175,7 @@ void launch(int grid, int nthreads, size_t smem, const std::function<void()>& bo
   if (smem > 227 * 1024) violation("launch: more than 227 KB of shared memory");
   blockDim.x = (unsigned)nthreads; gridDim.x = (unsigned)grid; if (getenv("FE_TRACE")) std::fprintf(stderr, "launch grid %d threads %d smem %zu\n", grid, nthreads, smem);
   pthread_barrier_init(&g_cta_bar, nullptr, nthreads);
-  g_named_count = nthreads > 256 ? nthreads - 32 : 256;      // ring kernels: every warp but the producer
+  g_named_count = nthreads > 256 ? (nthreads >= 512 ? 512 : 256) : 256;      // ring kernels: 256 or 512 consumer threads + producer warps
   pthread_barrier_init(&g_named_bar, nullptr, g_named_count);
   for (auto& w : g_warp_bar) pthread_barrier_init(&w, nullptr, 32);
   std::vector<std::thread> th;
