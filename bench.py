@@ -273,6 +273,10 @@ def build_performance_mg(om, P, args, dims, op, rank, world, local, dist, collap
         mg.set_option("use_graph", 0)
     if args.no_fast:
         mg.set_option("fast_kernels", 0)
+    # resident mode, and the host of this benchmark never reads mg_ires: the residual of a level is consumed in
+    # registers by update_coarse (restricted at once) and is not written back (8 B per cell less); --store-res keeps
+    # the reference's memory image of mg_ires
+    mg.set_option("store_fine_residual", 1 if args.store_res else 0)
     for kv in args.opt:
         k, v = kv.split("=")
         mg.set_option(k, int(v))
@@ -318,6 +322,8 @@ def main():
                     "instead of interior cells (omg_copy_to/from_tree)")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels directly instead of replaying a CUDA graph")
     ap.add_argument("--no-fast", action="store_true", help="general-path kernels only")
+    ap.add_argument("--store-res", action="store_true", help="write the residual of every level to mg_ires as the reference does "
+                    "(default: resident mode without it -- nothing on the device reads it and this host never pulls it)")
     ap.add_argument("--op", default="laplacian", choices=["laplacian", "vlaplacian", "helmholtz", "vhelmholtz", "ahelmholtz"],
                     help="operator (BASELINE.json configs[3]: vlaplacian / helmholtz with Neumann BC); default = the headline Laplacian")
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the TOTAL domain at n^3 instead of n^3 per GPU for the headline value")
@@ -377,9 +383,10 @@ def main():
     collapse = args.collapse if args.collapse >= 0 else 128
     if world > 1:
         config["coarse_collapse_boxes_per_rank"] = collapse
+    config["options"] = {"store_fine_residual": 1 if args.store_res else 0}
     for kv in args.opt:
         k, v = kv.split("=")
-        config.setdefault("options", {})[k] = int(v)
+        config["options"][k] = int(v)
     mg = build_performance_mg(om, P, args, dims, op, rank, world, local, dist, collapse)
     dof = dims[0] * dims[1] * dims[2]
     G, gpu = mg.G, mg.gpu

@@ -140,20 +140,25 @@ struct TileSmem {
   double xg[KT][NC];        // the single x ghost each row needs (low side if the row's updated cells start at i=0, else high side)
 };
 struct NoSmem {};
-template <int NC, int KT, bool VC>
+// NE = number of coefficient arrays: 0 (Laplacian / Helmholtz), 1 (vlaplacian / vhelmholtz: eps = variable 5 for all
+// three directions), 3 (ahelmholtz, box_gs_ahelmh src/m_ahelmholtz.f90:69-162: variables 5, 6, 7 = eps of the x, y, z
+// faces).  Array e is staged like phi; with NE = 3 array d only ever needs its ghost cells in direction d.
+template <int NC, int KT, int NE>
 struct SmoothSmem : TileSmem<NC, KT> {
-  typename std::conditional<VC, TileSmem<NC, KT>, NoSmem>::type E;   // the same tile of eps
+  typename std::conditional<(NE > 0), TileSmem<NC, KT>[(NE > 0 ? NE : 1)], NoSmem>::type E;   // the same tile of eps
   uint64_t bar;
 };
 
-template <int NC, int KT, bool VC>
-__global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
+template <int NC, int KT, int NE>
+__global__ void __launch_bounds__(kThreads, NE == 3 ? 4 : NE ? 3 : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
                                                                           const __grid_constant__ ParamsDev P, int colour,
                                                                           const int* __restrict__ boxlist, int fused_put, int pdl) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
   OMG_DYN_SMEM(smem_raw, 128);
-  SmoothSmem<NC, KT, VC>& S = *reinterpret_cast<SmoothSmem<NC, KT, VC>*>(smem_raw);
+  constexpr bool VC = NE > 0;
+  constexpr int EY = NE == 3 ? 1 : 0, EZ = NE == 3 ? 2 : 0;      // which array serves the y / z faces (x: array 0)
+  SmoothSmem<NC, KT, NE>& S = *reinterpret_cast<SmoothSmem<NC, KT, NE>*>(smem_raw);
   const int tid = threadIdx.x;
 
   const int b = boxlist ? boxlist[blockIdx.x / TILES] : blockIdx.x / TILES;   // a subset of the level (partition-face / interior boxes)
@@ -172,9 +177,12 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   if (tid == 0) mbar_init(&S.bar, 1);
   pdl_sync(pdl);
   if (tid == 0) {
-    mbar_expect_tx(&S.bar, (VC ? 2 : 1) * KT * NC * HX * 8);
+    mbar_expect_tx(&S.bar, (1 + NE) * KT * NC * HX * 8);
     bulk_g2s(&S.B[0][0][0], Bg + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
-    if constexpr (VC) bulk_g2s(&S.E.B[0][0][0], L.var[4] + boxoff + (size_t)oc * L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+    if constexpr (VC) {
+#pragma unroll
+      for (int e = 0; e < NE; ++e) bulk_g2s(&S.E[e].B[0][0][0], L.var[4 + e] + boxoff + (size_t)oc * L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+    }
   }
   // rhs (and eps) of this thread's cells (in flight while the bulk copies land)
   constexpr int PER = KT * NC * HX / kThreads;
@@ -183,7 +191,7 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   constexpr bool COLUMN = !VC && (kThreads % (NC * HX) == 0) && (KT % (kThreads / (NC * HX)) == 0) && ((KT / (kThreads / (NC * HX))) % 2 == 0);
   constexpr int COLS = NC * HX, KP = COLUMN ? KT / (kThreads / COLS) : 1;
   const int col = tid % COLS, kb = COLUMN ? (tid / COLS) * KP : 0;
-  double rhs[PER], eps0[VC ? PER : 1];
+  double rhs[PER], eps0[VC ? NE : 1][VC ? PER : 1];
   if constexpr (COLUMN) {
     static_assert(!COLUMN || KP == PER, "one cell per plane and thread");
 #pragma unroll
@@ -193,9 +201,12 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
     for (int q = 0; q < PER; ++q) rhs[q] = Rg[(size_t)k0 * NC * HX + q * kThreads + tid];
   }
   if constexpr (VC) {
-    const double* __restrict__ Eg0 = L.var[4] + boxoff + (size_t)colour * L.cs;
 #pragma unroll
-    for (int q = 0; q < PER; ++q) eps0[q] = Eg0[(size_t)k0 * NC * HX + q * kThreads + tid];
+    for (int e = 0; e < NE; ++e) {
+      const double* __restrict__ Eg0 = L.var[4 + e] + boxoff + (size_t)colour * L.cs;
+#pragma unroll
+      for (int q = 0; q < PER; ++q) eps0[e][q] = Eg0[(size_t)k0 * NC * HX + q * kThreads + tid];
+    }
   }
 
   int kind[6], arg[6];
@@ -223,9 +234,9 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
     }
     __syncwarp();
     if constexpr (VC) {
-      const double* __restrict__ Eg = L.var[4] + boxoff + (size_t)oc * L.cs;
-      if (tid == 3 && zlo_in) bulk_g2s(&S.E.zlo[0][0], Eg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
-      if (tid == 4 && zhi_in) bulk_g2s(&S.E.zhi[0][0], Eg + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
+      const double* __restrict__ Eg = L.var[4 + EZ] + boxoff + (size_t)oc * L.cs;
+      if (tid == 3 && zlo_in) bulk_g2s(&S.E[EZ].zlo[0][0], Eg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
+      if (tid == 4 && zhi_in) bulk_g2s(&S.E[EZ].zhi[0][0], Eg + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
     }
     if (tid == 1) {
       if (zlo_in) bulk_g2s(&S.zlo[0][0], Bg + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
@@ -280,19 +291,21 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
   // ---- ghost layer of eps: the other-colour entries of the stored ghost faces (host data, any face kind) ----
   if constexpr (VC) {
     const double* __restrict__ fc = L.faces[4] + (size_t)b * 6 * NC * NC;
+    const double* __restrict__ fcy = L.faces[4 + EY] + (size_t)b * 6 * NC * NC;
+    const double* __restrict__ fcz = L.faces[4 + EZ] + (size_t)b * 6 * NC * NC;
     if (!zlo_in)
-      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.E.zlo[j][m] = fc[4 * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)]; }
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.E[EZ].zlo[j][m] = fcz[4 * NC * NC + j * NC + 2 * m + ((oc ^ (j + 1)) & 1)]; }
     if (!zhi_in)
-      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.E.zhi[j][m] = fc[5 * NC * NC + j * NC + 2 * m + ((oc ^ j) & 1)]; }
+      for (int r = tid; r < NC * HX; r += kThreads) { const int j = r / HX, m = r % HX; S.E[EZ].zhi[j][m] = fcz[5 * NC * NC + j * NC + 2 * m + ((oc ^ j) & 1)]; }
     for (int r = tid; r < KT * HX; r += kThreads) {
       const int kk = r / HX, m = r % HX, k = k0 + kk;
-      S.E.ylo[kk][m] = fc[2 * NC * NC + k * NC + 2 * m + ((oc ^ (k + 1)) & 1)];
-      S.E.yhi[kk][m] = fc[3 * NC * NC + k * NC + 2 * m + ((oc ^ k) & 1)];
+      S.E[EY].ylo[kk][m] = fcy[2 * NC * NC + k * NC + 2 * m + ((oc ^ (k + 1)) & 1)];
+      S.E[EY].yhi[kk][m] = fcy[3 * NC * NC + k * NC + 2 * m + ((oc ^ k) & 1)];
     }
     for (int r = tid; r < KT * NC; r += kThreads) {
       const int kk = r / NC, j = r % NC, k = k0 + kk;
       const int f = (colour ^ ((j + k) & 1)) ? 1 : 0;
-      S.E.xg[kk][j] = fc[f * NC * NC + k * NC + j];
+      S.E[0].xg[kk][j] = fc[f * NC * NC + k * NC + j];
     }
   }
 
@@ -390,13 +403,13 @@ __global__ void __launch_bounds__(kThreads, VC ? 3 : (NC == 16 ? 5 : 4)) k_smoot
       const double u[6] = {xlo, xhi, ylo, yhi, zlo, zhi};
       double a0[6], a[6];
 #pragma unroll
-      for (int f = 0; f < 6; ++f) a0[f] = eps0[q];
-      a[0] = ml >= 0 ? S.E.B[kk][j][ml] : S.E.xg[kk][j];
-      a[1] = mh < HX ? S.E.B[kk][j][mh] : S.E.xg[kk][j];
-      a[2] = j > 0 ? S.E.B[kk][j - 1][m] : S.E.ylo[kk][m];
-      a[3] = j < NC - 1 ? S.E.B[kk][j + 1][m] : S.E.yhi[kk][m];
-      a[4] = kk > 0 ? S.E.B[kk - 1][j][m] : S.E.zlo[j][m];
-      a[5] = kk < KT - 1 ? S.E.B[kk + 1][j][m] : S.E.zhi[j][m];
+      for (int f = 0; f < 6; ++f) a0[f] = eps0[NE == 3 ? (f >> 1) : 0][q];
+      a[0] = ml >= 0 ? S.E[0].B[kk][j][ml] : S.E[0].xg[kk][j];
+      a[1] = mh < HX ? S.E[0].B[kk][j][mh] : S.E[0].xg[kk][j];
+      a[2] = j > 0 ? S.E[EY].B[kk][j - 1][m] : S.E[EY].ylo[kk][m];
+      a[3] = j < NC - 1 ? S.E[EY].B[kk][j + 1][m] : S.E[EY].yhi[kk][m];
+      a[4] = kk > 0 ? S.E[EZ].B[kk - 1][j][m] : S.E[EZ].zlo[j][m];
+      a[5] = kk < KT - 1 ? S.E[EZ].B[kk + 1][j][m] : S.E[EZ].zhi[j][m];
       Ag[(size_t)k0 * NC * HX + idx] = gs_vlpl_value(L.idr2, u, a0, a, rhs[q], P.lambda, P.op != OP_VLPL);
     } else {
       Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - rhs[q]);
@@ -757,7 +770,7 @@ inline int sm_count() {
   }
   return n;
 }
-int g_ring = 0;          // option "ring": 1 = persistent ring smoother on levels with at least 2 tiles per SM, 2 = always, 0 = never
+int g_ring = 1;          // option "ring": 1 = persistent ring smoother on levels with at least 4 tiles per SM, 2 = always, 0 = never
 
 template <int NC, int KT, int STAGES, int NCONS, int MINB, int NPW>
 bool launch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
@@ -775,16 +788,18 @@ bool launch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const
 }
 // shape of the ring kernel: OMG_RING_CFG = consumers * 1000 + stages * 100 + CTAs per SM * 10 + producer warps (tuning runs)
 bool dispatch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
-  static const int cfg = env_int("OMG_RING_CFG", 256514);
+  static const int cfg = env_int("OMG_RING_CFG", 256222);
   switch (cfg) {
     case 256511: return launch_smooth_ring<16, 16, 5, 256, 1, 1>(L, P, colour, list, n, fused, s);
     case 256512: return launch_smooth_ring<16, 16, 5, 256, 1, 2>(L, P, colour, list, n, fused, s);
     case 512514: return launch_smooth_ring<16, 16, 5, 512, 1, 4>(L, P, colour, list, n, fused, s);
     case 512414: return launch_smooth_ring<16, 16, 4, 512, 1, 4>(L, P, colour, list, n, fused, s);
     case 256221: return launch_smooth_ring<16, 16, 2, 256, 2, 1>(L, P, colour, list, n, fused, s);
-    case 256222: return launch_smooth_ring<16, 16, 2, 256, 2, 2>(L, P, colour, list, n, fused, s);
+    case 256224: return launch_smooth_ring<16, 16, 2, 256, 2, 4>(L, P, colour, list, n, fused, s);
+    case 256132: return launch_smooth_ring<16, 16, 1, 256, 3, 2>(L, P, colour, list, n, fused, s);
+    case 256514: return launch_smooth_ring<16, 16, 5, 256, 1, 4>(L, P, colour, list, n, fused, s);
     case 512222: return launch_smooth_ring<16, 16, 2, 512, 2, 2>(L, P, colour, list, n, fused, s);
-    default: return launch_smooth_ring<16, 16, 5, 256, 1, 4>(L, P, colour, list, n, fused, s);
+    default: return launch_smooth_ring<16, 16, 2, 256, 2, 2>(L, P, colour, list, n, fused, s);   // 0.270 ms per finest-level half-sweep at 512^3 (profiles/r02f_*)
   }
 }
 
@@ -806,7 +821,7 @@ bool launch_pdl(void (*kern)(KArgs...), int grid, size_t smem, cudaStream_t s, A
 #endif
 }
 
-template <int NC, int KT, bool VC>
+template <int NC, int KT, int VC>
 bool launch_smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, int fused, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(SmoothSmem<NC, KT, VC>);
@@ -844,9 +859,9 @@ struct BothSmem {
   double ylo[2][KT][HX], yhi[2][KT][HX];
   double xlo[KT][NC], xhi[KT][NC];
 };
-template <int NC, int KT, bool VC>
+template <int NC, int KT, int NE>
 struct StencilSmem : BothSmem<NC, KT> {
-  typename std::conditional<VC, BothSmem<NC, KT>, NoSmem>::type E;
+  typename std::conditional<(NE > 0), BothSmem<NC, KT>[(NE > 0 ? NE : 1)], NoSmem>::type E;   // NE coefficient arrays, see SmoothSmem
   double red[32];
   uint64_t bar;
 };
@@ -878,12 +893,14 @@ __device__ __forceinline__ void block_neighbours(const BothSmem<NC, KT>& F, cons
 // STORE = false (option "store_fine_residual" = 0, for hosts that never read mg_ires): the residual of the level itself is
 // not written -- nothing on the device reads it again (update_coarse consumes it in registers, the next residual pass
 // overwrites it) -- which takes 8 B per cell off MODE_RESID_RESTRICT (26 -> 18 B) and MODE_RESID_MAX (24 -> 16 B).
-template <int NC, int KT, int MODE, bool HELM, int MB, bool VC, bool STORE>
+template <int NC, int KT, int MODE, bool HELM, int MB, int NE, bool STORE>
 __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_constant__ LevelDev L, const __grid_constant__ LevelDev Lc,
                                                            const __grid_constant__ ParamsDev P, double* maxslot, int pdl) {
   constexpr int HX = NC / 2;
   constexpr int TILES = NC / KT;
-  using SM = StencilSmem<NC, KT, VC>;
+  constexpr bool VC = NE > 0;
+  constexpr int EY = NE == 3 ? 1 : 0, EZ = NE == 3 ? 2 : 0;      // which array serves the y / z faces (x: array 0)
+  using SM = StencilSmem<NC, KT, NE>;
   OMG_DYN_SMEM(smem_raw, 128);
   SM& S = *reinterpret_cast<SM*>(smem_raw);
   const int tid = threadIdx.x;
@@ -897,18 +914,21 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   if (tid == 0) mbar_init(&S.bar, 1);
   pdl_sync(pdl);
   if (tid == 0) {
-    mbar_expect_tx(&S.bar, (VC ? 2 : 1) * 2 * KT * NC * HX * 8);
+    mbar_expect_tx(&S.bar, (1 + NE) * 2 * KT * NC * HX * 8);
     if (TILES == 1) bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff, 2 * KT * NC * HX * 8, &S.bar);   // whole box: one 32 KiB copy
     else {
       bulk_g2s(&S.Ph[0][0][0][0], phi + boxoff + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
       bulk_g2s(&S.Ph[1][0][0][0], phi + boxoff + L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
     }
     if constexpr (VC) {
-      const double* __restrict__ eps = L.var[4] + boxoff;
-      if (TILES == 1) bulk_g2s(&S.E.Ph[0][0][0][0], eps, 2 * KT * NC * HX * 8, &S.bar);
-      else {
-        bulk_g2s(&S.E.Ph[0][0][0][0], eps + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
-        bulk_g2s(&S.E.Ph[1][0][0][0], eps + L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+#pragma unroll
+      for (int ee = 0; ee < NE; ++ee) {
+        const double* __restrict__ eps = L.var[4 + ee] + boxoff;
+        if (TILES == 1) bulk_g2s(&S.E[ee].Ph[0][0][0][0], eps, 2 * KT * NC * HX * 8, &S.bar);
+        else {
+          bulk_g2s(&S.E[ee].Ph[0][0][0][0], eps + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+          bulk_g2s(&S.E[ee].Ph[1][0][0][0], eps + L.cs + (size_t)k0 * NC * HX, KT * NC * HX * 8, &S.bar);
+        }
       }
     }
   }
@@ -950,11 +970,11 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
     if (VC && zhi_in) bytes += 2 * NC * HX * 8;
     mbar_arrive_expect_tx(&S.bar, bytes);
     if constexpr (VC) {
-      const double* __restrict__ eps = L.var[4] + boxoff;
+      const double* __restrict__ eps = L.var[4 + EZ] + boxoff;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
-        if (zlo_in) bulk_g2s(&S.E.zlo[c][0][0], eps + (size_t)c * L.cs + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
-        if (zhi_in) bulk_g2s(&S.E.zhi[c][0][0], eps + (size_t)c * L.cs + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
+        if (zlo_in) bulk_g2s(&S.E[EZ].zlo[c][0][0], eps + (size_t)c * L.cs + (size_t)(k0 - 1) * NC * HX, NC * HX * 8, &S.bar);
+        if (zhi_in) bulk_g2s(&S.E[EZ].zhi[c][0][0], eps + (size_t)c * L.cs + (size_t)(k0 + KT) * NC * HX, NC * HX * 8, &S.bar);
       }
     }
 #pragma unroll
@@ -1000,16 +1020,18 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
   if constexpr (VC) {
     // ghost layer of eps: stored ghost faces (host data, any face kind), de-interleaved by colour
     const double* __restrict__ fc = L.faces[4] + (size_t)b * 6 * NC * NC;
+    const double* __restrict__ fcy = L.faces[4 + EY] + (size_t)b * 6 * NC * NC;
+    const double* __restrict__ fcz = L.faces[4 + EZ] + (size_t)b * 6 * NC * NC;
     if (!zlo_in)
-      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.E.zlo[(i + j + 1) & 1][j][i >> 1] = fc[4 * NC * NC + r]; }
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.E[EZ].zlo[(i + j + 1) & 1][j][i >> 1] = fcz[4 * NC * NC + r]; }
     if (!zhi_in)
-      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.E.zhi[(i + j) & 1][j][i >> 1] = fc[5 * NC * NC + r]; }
+      for (int r = tid; r < NC * NC; r += kThreads) { const int j = r / NC, i = r % NC; S.E[EZ].zhi[(i + j) & 1][j][i >> 1] = fcz[5 * NC * NC + r]; }
     for (int r = tid; r < KT * NC; r += kThreads) {
       const int kk = r / NC, i = r % NC, k = k0 + kk;
-      S.E.ylo[(i + k + 1) & 1][kk][i >> 1] = fc[2 * NC * NC + k * NC + i];
-      S.E.yhi[(i + k) & 1][kk][i >> 1] = fc[3 * NC * NC + k * NC + i];
-      S.E.xlo[kk][i] = fc[0 * NC * NC + k * NC + i];       // (here i runs over j)
-      S.E.xhi[kk][i] = fc[1 * NC * NC + k * NC + i];
+      S.E[EY].ylo[(i + k + 1) & 1][kk][i >> 1] = fcy[2 * NC * NC + k * NC + i];
+      S.E[EY].yhi[(i + k) & 1][kk][i >> 1] = fcy[3 * NC * NC + k * NC + i];
+      S.E[0].xlo[kk][i] = fc[0 * NC * NC + k * NC + i];       // (here i runs over j)
+      S.E[0].xhi[kk][i] = fc[1 * NC * NC + k * NC + i];
     }
   }
   mbar_wait(&S.bar, 0);
@@ -1076,12 +1098,15 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
 #pragma unroll
       for (int e = 0; e < 8; ++e) nxt[e] = in1[goff(q + kThreads, e & 1, (e >> 1) & 1, e >> 2)];
     }
-    double u[8], r[8], ue[VC ? 8 : 1];
+    double u[8], r[8], ue[VC ? NE : 1][VC ? 8 : 1];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int di = e & 1, dj = ((e >> 1) & 1) ^ sw, dk = e >> 2;
       u[e] = S.Ph[(di + dj + dk) & 1][2 * Kc + dk][2 * J + dj][I];
-      if constexpr (VC) ue[e] = S.E.Ph[(di + dj + dk) & 1][2 * Kc + dk][2 * J + dj][I];
+      if constexpr (VC) {
+#pragma unroll
+        for (int ee = 0; ee < NE; ++ee) ue[ee][e] = S.E[ee].Ph[(di + dj + dk) & 1][2 * Kc + dk][2 * J + dj][I];
+      }
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -1092,9 +1117,19 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
       double lap;
       if constexpr (VC) {
         double an[6], a0[6];
-        block_neighbours<NC, KT>(S.E, ue, e, I, J, Kc, sw, an);
+        if constexpr (NE == 3) {       // each array is only needed along its own direction (the rest is dead code)
+          double ax[6], ay[6], az[6];
+          block_neighbours<NC, KT>(S.E[0], ue[0], e, I, J, Kc, sw, ax);
+          block_neighbours<NC, KT>(S.E[1], ue[1], e, I, J, Kc, sw, ay);
+          block_neighbours<NC, KT>(S.E[2], ue[2], e, I, J, Kc, sw, az);
+          an[0] = ax[0]; an[1] = ax[1]; an[2] = ay[2]; an[3] = ay[3]; an[4] = az[4]; an[5] = az[5];
 #pragma unroll
-        for (int f = 0; f < 6; ++f) a0[f] = ue[e];
+          for (int f = 0; f < 6; ++f) a0[f] = ue[f >> 1][e];
+        } else {
+          block_neighbours<NC, KT>(S.E[0], ue[0], e, I, J, Kc, sw, an);
+#pragma unroll
+          for (int f = 0; f < 6; ++f) a0[f] = ue[0][e];
+        }
         lap = vlpl_value(L.idr2, u0, n, a0, an);
       } else {
         lap = idx2 * (n[0] + n[1] - 2 * u0) + idy2 * (n[2] + n[3] - 2 * u0) + idz2 * (n[4] + n[5] - 2 * u0);
@@ -1142,7 +1177,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
 }
 
 int g_store_res = 1;     // option "store_fine_residual"
-template <int NC, int KT, int MODE, bool HELM, int MB, bool VC, bool STORE>
+template <int NC, int KT, int MODE, bool HELM, int MB, int VC, bool STORE>
 bool launch_stencil_s(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(StencilSmem<NC, KT, VC>);
@@ -1155,7 +1190,7 @@ bool launch_stencil_s(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P,
   OMG_LAUNCH(kern, nboxes * (NC / KT), smem, s, L, Lc, P, maxslot, 0);
   return true;
 }
-template <int NC, int KT, int MODE, bool HELM, int MB, bool VC = false>
+template <int NC, int KT, int MODE, bool HELM, int MB, int VC = 0>
 bool launch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   if (MODE != MODE_CRHS && !g_store_res) return launch_stencil_s<NC, KT, MODE, HELM, MB, VC, false>(L, Lc, P, nboxes, maxslot, s);
   return launch_stencil_s<NC, KT, MODE, HELM, MB, VC, true>(L, Lc, P, nboxes, maxslot, s);
@@ -1175,14 +1210,23 @@ bool dispatch_stencil_h(const LevelDev& L, const LevelDev& Lc, const ParamsDev& 
 template <int MODE, bool HELM>
 bool dispatch_stencil_vc(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   if (!L.var[4] || !L.faces[4]) return false;
-  if (L.nc == 16) return launch_stencil<16, 16, MODE, HELM, 2, true>(L, Lc, P, nboxes, maxslot, s);
-  if (L.nc == 32) return launch_stencil<32, 8, MODE, HELM, 1, true>(L, Lc, P, nboxes, maxslot, s);
+  if (L.nc == 16) return launch_stencil<16, 16, MODE, HELM, 2, 1>(L, Lc, P, nboxes, maxslot, s);
+  if (L.nc == 32) return launch_stencil<32, 8, MODE, HELM, 1, 1>(L, Lc, P, nboxes, maxslot, s);
+  return false;
+}
+// ahelmholtz (box_ahelmh src/m_ahelmholtz.f90:165-237): three coefficient arrays; half-box tiles at box 16 (4 x 24 KB)
+template <int MODE>
+bool dispatch_stencil_aniso(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
+  for (int e = 0; e < 3; ++e) if (!L.var[4 + e] || !L.faces[4 + e]) return false;
+  if (L.nc == 16) return launch_stencil<16, 8, MODE, true, 2, 3>(L, Lc, P, nboxes, maxslot, s);
+  if (L.nc == 32) return launch_stencil<32, 4, MODE, true, 1, 3>(L, Lc, P, nboxes, maxslot, s);
   return false;
 }
 template <int MODE>
 bool dispatch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   if (P.op == OP_VLPL) return dispatch_stencil_vc<MODE, false>(L, Lc, P, nboxes, maxslot, s);
   if (P.op == OP_VHELMH) return dispatch_stencil_vc<MODE, true>(L, Lc, P, nboxes, maxslot, s);
+  if (P.op == OP_AHELMH) return dispatch_stencil_aniso<MODE>(L, Lc, P, nboxes, maxslot, s);
   return P.op == OP_HELMH ? dispatch_stencil_h<MODE, true>(L, Lc, P, nboxes, maxslot, s)
                           : dispatch_stencil_h<MODE, false>(L, Lc, P, nboxes, maxslot, s);
 }
@@ -1399,6 +1443,7 @@ void set_store_res(int on) { g_store_res = on; }
 bool smooth_applies(const LevelDev& L, const ParamsDev& P) {
   if (L.nc != 16 && L.nc != 32) return false;
   if (P.op == OP_VLPL || P.op == OP_VHELMH) return L.var[4] && L.faces[4];
+  if (P.op == OP_AHELMH) return L.var[4] && L.faces[4] && L.var[5] && L.faces[5] && L.var[6] && L.faces[6];
   return P.op == OP_LPL || P.op == OP_HELMH;
 }
 bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, int fused, cudaStream_t s) {
@@ -1406,35 +1451,39 @@ bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, co
   if (list && n == 0) return true;
   if (P.op == OP_VLPL || P.op == OP_VHELMH) {
     if (!L.var[4] || !L.faces[4]) return false;
-    if (L.nc == 16) return launch_smooth<16, 16, true>(L, P, colour, list, n, fused, s);
-    if (L.nc == 32) return launch_smooth<32, 8, true>(L, P, colour, list, n, fused, s);
+    if (L.nc == 16) return launch_smooth<16, 16, 1>(L, P, colour, list, n, fused, s);
+    if (L.nc == 32) return launch_smooth<32, 8, 1>(L, P, colour, list, n, fused, s);
+    return false;
+  }
+  if (P.op == OP_AHELMH) {
+    for (int e = 0; e < 3; ++e) if (!L.var[4 + e] || !L.faces[4 + e]) return false;
+    if (L.nc == 16) return launch_smooth<16, 8, 3>(L, P, colour, list, n, fused, s);     // half-box tiles: 4 x 12 KB of shared memory
+    if (L.nc == 32) return launch_smooth<32, 8, 3>(L, P, colour, list, n, fused, s);
     return false;
   }
   if (P.op != OP_LPL && P.op != OP_HELMH) return false;
-  if (L.nc == 16 && g_ring && ((list ? n : L.nb) >= 2 * sm_count() || g_ring == 2)) return dispatch_smooth_ring(L, P, colour, list, n, fused, s);
+  if (L.nc == 16 && g_ring && ((list ? n : L.nb) >= 4 * sm_count() || g_ring == 2)) return dispatch_smooth_ring(L, P, colour, list, n, fused, s);
   if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, fused, s);
   if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, fused, s);
   return false;
 }
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s) {
   if (!all_fast || Lf.nb == 0 || Lc.nc != Lf.nc) return false;
-  if (P.op == OP_AHELMH) return false;
   return dispatch_stencil<MODE_RESID_RESTRICT>(Lf, Lc, P, Lf.nb, nullptr, s);
 }
 bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s) {
   if (!all_fast || L.nb == 0 || !maxslot) return false;
-  if (P.op == OP_AHELMH) return false;
   return dispatch_stencil<MODE_RESID_MAX>(L, L, P, L.nb, maxslot, s);
 }
 bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s) {
   if (!all_fast || L.n_parents == 0) return false;
-  if (P.op == OP_AHELMH) return false;
   return dispatch_stencil<MODE_CRHS>(L, L, P, L.n_parents, nullptr, s);
 }
 bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool, cudaStream_t s) {
   if (Lf.nb == 0 || Lc.nc != Lf.nc) return false;
   static const int mb = env_int("OMG_PROLONG_MB", 4);
-  static const int tma = env_int("OMG_PROLONG_TMA", 5);        // CTAs per SM of the TMA version (0: register-prefetch version)
+  static const int tma = env_int("OMG_PROLONG_TMA", 0);        // CTAs per SM of the TMA version; 0 (default): register-prefetch version --
+                                                               // measured equal within 1 % (0.488 / 0.492 / 0.492 / 0.516 ms for 0 / 3 / 4 / 5, profiles/r02f_*)
   if (Lf.nc == 16 && tma && !g_pdl) return tma == 4 ? launch_corr_prolong_tma<16, 4>(Lf, Lc, P, s) : tma == 3 ? launch_corr_prolong_tma<16, 3>(Lf, Lc, P, s) : launch_corr_prolong_tma<16, 5>(Lf, Lc, P, s);
   if (Lf.nc == 16) return mb == 4 ? launch_corr_prolong<16, 4>(Lf, Lc, P, s) : mb == 2 ? launch_corr_prolong<16, 2>(Lf, Lc, P, s) : launch_corr_prolong<16, 3>(Lf, Lc, P, s);
   if (Lf.nc == 32) return launch_corr_prolong<32, 3>(Lf, Lc, P, s);

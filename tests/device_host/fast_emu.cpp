@@ -421,6 +421,7 @@ int fe_one_level(int op, int nc, int nbx, int nby, int nbz, const int* bc_types,
     case OP_LPL: return one_level<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
     case OP_VLPL: return one_level<OP_VLPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
     case OP_HELMH: return one_level<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_AHELMH: return one_level<OP_AHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
     default: return one_level<OP_VHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
   }
 }
@@ -430,6 +431,7 @@ int fe_two_levels(int op, int nc, int nbx, int nby, int nbz, const int* bc_types
     case OP_LPL: return two_levels<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
     case OP_VLPL: return two_levels<OP_VLPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
     case OP_HELMH: return two_levels<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
+    case OP_AHELMH: return two_levels<OP_AHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
     default: return two_levels<OP_VHELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
   }
 }

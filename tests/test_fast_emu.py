@@ -38,7 +38,7 @@ def emu():
 
 BC_SETS = [[-10] * 6, [-11] * 6, [-12, -12, -10, -10, -11, -11], [-10, -11, -12, -10, -11, -12]]
 BC_VALUES = [0.3, -0.7, 1.1, 0.0, 2.0, -1.5]
-OPS = [(1, 0.0), (2, 0.0), (3, 2.5), (4, 0.75)]      # mg_laplacian, mg_vlaplacian, mg_helmholtz, mg_vhelmholtz
+OPS = [(1, 0.0), (2, 0.0), (3, 2.5), (4, 0.75), (5, 1.25)]      # mg_laplacian, mg_vlaplacian, mg_helmholtz, mg_vhelmholtz, mg_ahelmholtz
 
 
 def six(ctype, values):

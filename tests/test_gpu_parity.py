@@ -264,6 +264,9 @@ def test_gs_smoother_refinement(oracle, product):
     (P.mg_vhelmholtz, "neumann0", 1.0, 64, 16),
     (P.mg_vhelmholtz, "mixed", 0.5, 64, 32),
     (P.mg_helmholtz, "neumann0", 1.0, 64, 16),
+    (P.mg_ahelmholtz, "mixed", 0.75, 64, 16),               # three coefficient arrays (NE = 3 kernels, half-box tiles)
+    (P.mg_ahelmholtz, "callback", 1.5, (64, 32, 32), 16),
+    (P.mg_ahelmholtz, "neumann0", 1.0, 64, 32),
 ])
 def test_fast_kernels_variable_coefficient(oracle, product, op, bc, lam, n, box):
     """config 4 at box sizes 16 / 32: the TMA-staged kernels of the variable-coefficient operators (eps tile + stored
