@@ -245,7 +245,7 @@ def build_performance_mg(om, P, args, dims, op, rank, world, local, dist, collap
     """tests/test_performance.f90:51-66 without host cc arrays (the run is device-resident)"""
     mg = om.Mg(op, P.mg_smoother_gsrb, n_extra_vars=P.n_eps(op), n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
     mg.set_int("host_cc", 0)
-    if op in (P.mg_helmholtz, P.mg_vhelmholtz):
+    if op in (P.mg_helmholtz, P.mg_vhelmholtz, P.mg_ahelmholtz):
         mg.set_lambda(1.0)
     if world > 1:
         mg.set_int("coarse_collapse_boxes", collapse)

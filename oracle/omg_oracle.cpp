@@ -98,6 +98,7 @@ struct Buf {           // one per ordered (src rank, dst rank) pair
 };
 
 struct Timer { std::string name; double t = 0, t0 = 0; };
+struct FreeBc;                     // state of the free-space front end (free_space.inc)
 
 struct Mg {
   bool tree_created = false, is_allocated = false;
@@ -127,6 +128,7 @@ struct Mg {
   int last_coarse_iters = 0;
   Timer timers[8];
   std::string err;
+  FreeBc* free_bc = nullptr;
 
   int nvar() const { return NUM_VARS + n_extra_vars; }
   Lvl& L(int lvl) { return lvls[lvl - LVL_LO]; }
@@ -1301,6 +1303,8 @@ int diffusion_solve(Mg& mg, int op, double dt, double diffusion_coeff, int order
   return n - 1;
 }
 
+#include "free_space.inc"
+
 }  // namespace
 
 // ===========================================================================
@@ -1443,6 +1447,10 @@ int orc_fas_vcycle(void* h, int has_highest, int highest_lvl, int want_res, doub
 int orc_fas_fmg(void* h, int have_guess, int want_res, double* max_res) {
   Mg* mg = (Mg*)h; ORC_TRY(mg, fas_fmg(*mg, have_guess != 0, want_res != 0, max_res));
 }
+int orc_poisson_free_3d(void* h, int new_rhs, double max_fft_frac, int fmgcycle, int want_res, double* max_res) {
+  Mg* mg = (Mg*)h; ORC_TRY(mg, { if (!mg->methods_set) set_methods(*mg); poisson_free_3d(*mg, new_rhs != 0, max_fft_frac, fmgcycle != 0, want_res != 0, max_res); });
+}
+int orc_free_space_fft_lvl(void* h) { Mg* mg = (Mg*)h; return mg->free_bc ? mg->free_bc->fft_lvl : -999; }
 int orc_diffusion_set_rhs(void* h, double f1, double f2) { Mg* mg = (Mg*)h; ORC_TRY(mg, diffusion_set_rhs(*mg, f1, f2)); }
 int orc_diffusion_solve(void* h, int op, double dt, double diffusion_coeff, int order, double max_res, double* res, int* n_vcycles) {
   Mg* mg = (Mg*)h; ORC_TRY(mg, { int n = diffusion_solve(*mg, op, dt, diffusion_coeff, order, max_res, res); if (n_vcycles) *n_vcycles = n; });

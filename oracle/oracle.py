@@ -79,6 +79,8 @@ def lib():
         L.orc_diffusion_solve.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, C.c_double,
                                           C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.orc_set_omp_threads.argtypes = [C.c_int]
+        L.orc_poisson_free_3d.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        L.orc_free_space_fft_lvl.argtypes = [C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -329,6 +331,16 @@ class OracleMg:
 
     def diffusion_set_rhs(self, f1, f2):
         self._ck(self.L.orc_diffusion_set_rhs(self.h, f1, f2))
+
+    def mg_poisson_free_3d(self, new_rhs, max_fft_frac, fmgcycle=True, want_res=True):
+        """src/m_free_space.f90:36-214; returns max_res (None if not requested)"""
+        r = C.c_double(0.0)
+        self._ck(self.L.orc_poisson_free_3d(self.h, int(bool(new_rhs)), max_fft_frac, int(bool(fmgcycle)), int(bool(want_res)), C.byref(r)))
+        return r.value if want_res else None
+
+    @property
+    def free_space_fft_lvl(self):
+        return self.L.orc_free_space_fft_lvl(self.h)
 
     def timers(self):
         names = ["mg total V-cycle", "mg total FMG cycle", "mg smoother", "mg smoother g.c.", "mg coarse",
