@@ -397,6 +397,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    phase("handle built")
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -409,6 +410,7 @@ def main():
     res_after, _ = mg.fas_vcycles(1, want_res=True)      # untimed: residual after warm-up + timed + 2 cycles
     n_boxes_total = mg.n_boxes
 
+    phase("timed cycles done: %.3f ms per cycle" % (ms / args.steps))
     # --- roofline of the dominant kernel (finest-level GSRB colour half-sweep), timed live with CUDA events
     mg.set_option("profile", 1)
     mg.fas_vcycles(2)
@@ -458,6 +460,7 @@ def main():
     # mg_fas_vcycle overwrites phi and rhs of all parent boxes from the finer level before reading them (update_coarse,
     # src/m_multigrid.f90:347-384), and phi's ghost cells are derived on the device.  --e2e-cc moves the reference's
     # cc slabs (ghost shells included) of the leaf level instead.
+    phase("profile / trace done")
     e2e = None
     if not args.no_e2e:
         top = mg.highest_lvl
@@ -502,8 +505,10 @@ def main():
 
     # mg_deallocate_storage on every rank (ordered release of the peer mappings), then the follow-up problems are
     # created on the same process group: create / destroy / create of the multi-rank handle is part of every run
+    phase("end-to-end leg done; deallocating")
     mg.mg_deallocate_storage()
     del mg
+    phase("deallocated")
     barrier()
 
     # --- strong scaling of BASELINE configs[4]: the same 1024^3 domain on the N GPUs of this run
@@ -523,6 +528,7 @@ def main():
             l0 = smg.stat("launches")
             smg.fas_vcycles(1, want_res=args.max_res)
             strong["launches_per_step"] = smg.stat("launches") - l0
+            phase("strong record done: %.3f ms per cycle; deallocating" % (sms / ks))
             smg.mg_deallocate_storage()
             del smg
             barrier()
@@ -530,7 +536,9 @@ def main():
     # --- bitwise parity of the data plane that was just timed
     parity = None
     if not args.no_parity and args.op == "laplacian":
+        phase("parity check")
         parity = parity_check(om, P, args.parity_cells, args.box, rank, world, local, dist, collapse)
+        phase("parity check done")
 
     if rank != 0:
         finish(world, dist)
@@ -554,6 +562,16 @@ def main():
     if parity is not None and not parity.get("bitwise", False):
         sys.stderr.write("bench.py: parity check FAILED: %r\n" % parity)
         sys.exit(4)
+
+
+_T0 = time.time()
+
+
+def phase(msg):
+    """progress line on stderr (every rank): where a multi-rank run stands; the last line tells where a blocked run stopped"""
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 or os.environ.get("OMG_BENCH_VERBOSE"):
+        sys.stderr.write("[bench rank %s %.1fs] %s\n" % (os.environ.get("RANK", "0"), time.time() - _T0, msg))
+        sys.stderr.flush()
 
 
 def finish(world, dist):
@@ -585,4 +603,7 @@ if __name__ == "__main__":
     _watchdog = threading.Timer(1500.0, lambda: (sys.stderr.write("bench.py: watchdog expired\n"), sys.stderr.flush(), os._exit(3)))
     _watchdog.daemon = True
     _watchdog.start()
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        import faulthandler
+        faulthandler.dump_traceback_later(180, repeat=True, file=sys.stderr)     # a blocked rank shows where it stands
     main()

@@ -125,6 +125,22 @@ int omg_apply_op(omg_handle* h, int i_out);
  * leaves of levels 1..highest.  diffusion_solve / _vcoeff / _acoeff (:19-157) are this call between omg_set_params
  * (lambda), omg_apply_op (order 2), omg_fas_fmg and omg_fas_vcycle: nothing but the residual leaves the device. */
 int omg_diffusion_set_rhs(omg_handle* h, double f1, double f2);
+/* Free-space front end, mg_poisson_free_3d (src/m_free_space.f90:36-214).  The reference solves the free-space problem
+ * on a coarse fully refined level with the vendored BigDFT solver (createKernel :119, PSolver :160) and turns the result
+ * into Dirichlet planes (ghost_cells_free_bc / interp_bc :217-270) and an initial guess.  Device side:
+ * omg_free_space_kernel -- geometry of the FFT level + the kernel of 1/r in separable form, K(i, j, k) =
+ *   sum_g w[g] kx[g][|i|] ky[g][|j|] kz[g][|k|] (n_range + 1 entries per Gaussian; what createKernel builds before its
+ *   FFT), transformed once with cuFFT; also allots one Dirichlet plane to every physical-boundary face of every level.
+ * omg_free_space_solve -- rhs of the FFT level (all ranks: all-reduce) * rhs_fac -> zero-padded cuFFT convolution ->
+ *   potential on the (n+2)^3 grid * dr^3 -> the boundary planes of all levels by bilinear interpolation -> phi of the
+ *   FFT level.  The caller then restricts / prolongs phi and cycles (omg_restrict_lvl, omg_prolong,
+ *   omg_fill_ghost_cells_lvl, omg_fas_fmg / omg_fas_vcycle) exactly as :183-212 does. */
+int omg_free_space_kernel(omg_handle* h, int fft_lvl, const double r_min[3], int n_gauss, int n_range, const double* w,
+                          const double* kx, const double* ky, const double* kz);
+int omg_free_space_solve(omg_handle* h, double rhs_fac);
+/* the stored boundary plane of a physical-boundary face (what mg_phi_bc_store keeps in the ghost cells of mg_irhs,
+ * src/m_ghost_cells.f90:66-117): nc*nc values, first tangential index fastest; *bc_type receives its type */
+int omg_get_bc_plane(omg_handle* h, int box_id, int nb, int* bc_type, double* plane);
 /* repeat n V-cycles back to back without host round trips (benchmark loop of
  * tests/test_performance.f90:68-76); residuals[n] receives max_res per cycle when non-null */
 int omg_fas_vcycles(omg_handle* h, int n, double* residuals);

@@ -2,6 +2,7 @@
 // in-process emulation of several ranks for single-GPU parity tests.
 #include "omg_comm.h"
 
+#include <algorithm>
 #include <chrono>
 #include <condition_variable>
 #include <cstdlib>
@@ -111,6 +112,9 @@ __global__ void k_signal_wait(PeerList pl, int channel, int me, int nranks, unsi
   if (t == 0 && signal && ok) *epoch = e;       // a failed wait leaves the epoch alone: the handle is poisoned on the host
 }
 __global__ void k_bump_epoch(unsigned long long* epoch) { *epoch = *epoch + 1; }
+__global__ void k_add_vec(double* __restrict__ acc, const double* __restrict__ x, size_t n, int first) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) acc[i] = first ? x[i] : acc[i] + x[i];
+}
 }  // namespace
 
 struct omg_local_group {
@@ -147,6 +151,7 @@ struct omg_comm {
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
   double* d_stage = nullptr;                // my contribution to an allreduce
   double* d_gather = nullptr;               // [n] contributions of all ranks
+  double* d_vec = nullptr; size_t n_vec = 0;   // my contribution to a vector all-reduce
   // peer-mapped puts (NCCL back end)
   bool p2p = false;
   unsigned long long* d_flags = nullptr;    // [OMG_P2P_CHANNELS][n], written by the peers
@@ -273,6 +278,7 @@ void omg_comm_destroy(omg_comm* c) {
     if (c->ev_done) cudaEventDestroy(c->ev_done);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->d_gather) cudaFree(c->d_gather);
+    if (c->d_vec) cudaFree(c->d_vec);
     bool last;
     { std::lock_guard<std::mutex> lk(c->g->m); c->g->comms[c->rank] = nullptr; last = (--c->g->refs == 0); }
     if (last) delete c->g;
@@ -338,6 +344,29 @@ void omg_comm_allreduce(omg_comm* c, double* d_val, int op, cudaStream_t s) {
       CCK(cudaMemcpyAsync(c->d_gather + r, p->d_stage, sizeof(double), cudaMemcpyDefault, s));
     }
     k_reduce_slots<<<1, 1, 0, s>>>(c->d_gather, c->n, op, d_val);
+    CCK(cudaEventRecord(c->ev_done, s));
+    g->barrier();
+    for (int r = 0; r < c->n; ++r) if (g->comms[r]) CCK(cudaStreamWaitEvent(s, g->comms[r]->ev_done, 0));
+    g->barrier();
+  } catch (...) { g->abort_group(); throw; }
+}
+
+void omg_comm_allreduce_sum_vec(omg_comm* c, double* d_val, size_t n, cudaStream_t s) {
+  if (n == 0) return;
+  if (c->nccl) { NCK(nccl_api().AllReduce(d_val, d_val, n, ncclDouble, ncclSum, c->nccl, s)); return; }
+  omg_local_group* g = c->g;
+  try {
+    if (c->n_vec < n) { if (c->d_vec) cudaFree(c->d_vec); CCK(cudaMalloc(&c->d_vec, n * sizeof(double))); c->n_vec = n; }
+    CCK(cudaMemcpyAsync(c->d_vec, d_val, n * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    CCK(cudaEventRecord(c->ev_ready, s));
+    g->barrier();
+    const int grid = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
+    for (int r = 0; r < c->n; ++r) {
+      omg_comm* p = g->comms[r];
+      if (!p || p->n_vec < n) cfail("local allreduce: peer rank is gone or disagrees on the size");
+      CCK(cudaStreamWaitEvent(s, p->ev_ready, 0));
+      k_add_vec<<<grid, 256, 0, s>>>(d_val, p->d_vec, n, r == 0);
+    }
     CCK(cudaEventRecord(c->ev_done, s));
     g->barrier();
     for (int r = 0; r < c->n; ++r) if (g->comms[r]) CCK(cudaStreamWaitEvent(s, g->comms[r]->ev_done, 0));

@@ -59,3 +59,6 @@ inline int omg_p2p_err_channel(int code) { return (code - 1) / 64; }
 // all ranks call these at the same program points with matching segments (throws std::runtime_error)
 void omg_comm_exchange(omg_comm* c, const OmgXfer* segs, int nsegs, cudaStream_t s);
 void omg_comm_allreduce(omg_comm* c, double* d_val, int op, cudaStream_t s);
+// element-wise sum of n doubles over all ranks, in place (the mpi_allreduce of src/m_free_space.f90:152-153); the local
+// back end adds the contributions in rank order
+void omg_comm_allreduce_sum_vec(omg_comm* c, double* d_val, size_t n, cudaStream_t s);

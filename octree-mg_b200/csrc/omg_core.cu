@@ -19,6 +19,7 @@
 #include "../../include/omg_gpu.h"
 #include "omg_comm.h"
 #include "omg_fast.h"
+#include "omg_fs.h"
 #include "omg_kernels.h"
 #include "omg_plan.h"
 
@@ -158,6 +159,14 @@ struct omg_handle {
   struct TraceRec { int kind, l, a, b; cudaEvent_t e0, e1; };
   std::vector<TraceRec> trace_events;
 
+  // free-space front end (omg_fs.h): plan of the FFT level, box origins in its grid, the boundary faces of every level
+  omgfs::Plan* fs_plan = nullptr;
+  int fs_lvl = 0;
+  omgfs::Geom fs_geom{};
+  DevBuf<int> fs_origin;
+  std::vector<DevBuf<omgfs::Face>> fs_faces;     // per level
+  std::vector<int> fs_nfaces;
+
   LevelHost& L(int lvl) { return levels[lvl - lowest]; }
 };
 
@@ -178,6 +187,10 @@ void free_levels(omg_handle* h) {
   }
   h->levels.clear();
   h->d_levels.free();
+  if (h->fs_plan) { omgfs::destroy(h->fs_plan); h->fs_plan = nullptr; }
+  h->fs_origin.free();
+  for (auto& f : h->fs_faces) f.free();
+  h->fs_faces.clear(); h->fs_nfaces.clear();
   invalidate_programs(h);
 }
 
@@ -1462,6 +1475,100 @@ int omg_diffusion_set_rhs(omg_handle* h, double f1, double f2) {
       if (L.h_leaves.empty()) continue;
       omgk::axpby_leaves(L.dev, IPHI, IRHS, f1, f2, h->stream); h->launches++;
     }
+  });
+}
+
+
+// ---- free-space front end (include/omg_gpu.h; src/m_free_space.f90:36-214) ---------------------------------------------
+int omg_free_space_kernel(omg_handle* h, int fft_lvl, const double r_min[3], int n_gauss, int n_range, const double* w,
+                          const double* kx, const double* ky, const double* kz) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    if (!h->have_tree) fail("no tree: call omg_set_tree first");
+    if (fft_lvl < h->lowest || fft_lvl > h->highest) fail("mg_poisson_free_3d: FFT level out of range");
+    if (n_gauss < 1 || n_range < 1 || !w || !kx || !ky || !kz) fail("mg_poisson_free_3d: bad kernel");
+    LevelHost& LF = h->L(fft_lvl);
+    const int nc = LF.nc;
+    int nbox[3] = {0, 0, 0};
+    for (int id : h->lvl_ids[fft_lvl - h->lowest]) for (int d = 0; d < 3; ++d) nbox[d] = std::max(nbox[d], h->ix[(size_t)(id - 1) * 3 + d]);
+    if ((size_t)nbox[0] * nbox[1] * nbox[2] != h->lvl_ids[fft_lvl - h->lowest].size()) fail("mg_poisson_free_3d: the FFT level is not fully refined");
+    const int nx[3] = {nbox[0] * nc + 2, nbox[1] * nc + 2, nbox[2] * nc + 2};
+    if (n_range < std::max(nx[0], std::max(nx[1], nx[2])) - 1) fail("mg_poisson_free_3d: kernel range smaller than the FFT grid");
+    if (h->fs_plan) { omgfs::destroy(h->fs_plan); h->fs_plan = nullptr; }
+    std::string err;
+    h->fs_plan = omgfs::create(nx, err);
+    if (!h->fs_plan) fail(err);
+    if (!omgfs::set_kernel(h->fs_plan, n_gauss, n_range, w, kx, ky, kz, h->stream, err)) fail(err);
+    h->fs_lvl = fft_lvl;
+    for (int d = 0; d < 3; ++d) { h->fs_geom.r_min[d] = r_min[d] - 0.5 * LF.dev.dr[d]; h->fs_geom.inv_dr[d] = 1 / LF.dev.dr[d]; }
+    std::vector<int> origin((size_t)LF.nb * 3);
+    for (int b = 0; b < LF.nb; ++b) for (int d = 0; d < 3; ++d) origin[(size_t)b * 3 + d] = (h->ix[(size_t)(LF.ids[b] - 1) * 3 + d] - 1) * nc;
+    h->fs_origin.upload(origin, h->stream);
+    // every physical-boundary face of every level gets a Dirichlet plane (mg%bc(:, mg_iphi)%boundary_cond =>
+    // ghost_cells_free_bc, :98-100, stored once by mg_phi_bc_store, :170)
+    h->fs_faces.resize(h->levels.size()); h->fs_nfaces.assign(h->levels.size(), 0);
+    for (size_t li = 0; li < h->levels.size(); ++li) {
+      LevelHost& L = h->levels[li];
+      const size_t n2 = (size_t)L.nc * L.nc;
+      std::vector<omgfs::Face> faces;
+      for (int b = 0; b < L.nb; ++b) for (int f = 0; f < 6; ++f) {
+        const size_t q = (size_t)b * 6 + f;
+        if (L.h_fkind[q] != FK_PHYS) continue;
+        if (L.h_farg[q] < 0) { L.h_farg[q] = L.n_bcpl++; L.h_farg_old[q] = L.h_farg[q]; L.h_bcpl.resize((size_t)L.n_bcpl * n2, 0.0); }
+        L.h_ftype[q] = -10;
+        const int d = f >> 1, ta = (d == 0) ? 1 : 0, tb = (d == 2) ? 1 : 2;
+        const int* ix = &h->ix[(size_t)(L.ids[b] - 1) * 3];
+        faces.push_back({L.h_farg[q], f, r_min[ta] + (ix[ta] - 1) * (L.nc * L.dev.dr[ta]), r_min[tb] + (ix[tb] - 1) * (L.nc * L.dev.dr[tb])});
+      }
+      L.meta_dirty = true;
+      h->fs_nfaces[li] = (int)faces.size();
+      h->fs_faces[li].upload(faces, h->stream);
+    }
+    CK(cudaStreamSynchronize(h->stream));
+  });
+}
+
+int omg_free_space_solve(omg_handle* h, double rhs_fac) {
+  OMG_TRY(h, {
+    CK(cudaSetDevice(h->device));
+    check_p2p(h);
+    if (!h->fs_plan) fail("mg_poisson_free_3d: no kernel (omg_free_space_kernel first)");
+    sync_meta(h);
+    LevelHost& LF = h->L(h->fs_lvl);
+    cudaStream_t s = h->stream;
+    int nx[3]; { int nbox[3] = {0, 0, 0}; for (int id : h->lvl_ids[h->fs_lvl - h->lowest]) for (int d = 0; d < 3; ++d) nbox[d] = std::max(nbox[d], h->ix[(size_t)(id - 1) * 3 + d]); for (int d = 0; d < 3; ++d) nx[d] = nbox[d] * LF.nc + 2; }
+    double* grid = omgfs::grid(h->fs_plan);
+    const size_t N = omgfs::grid_size(h->fs_plan);
+    CK(cudaMemsetAsync(grid, 0, N * sizeof(double), s));
+    omgfs::gather_rhs(LF.dev, h->fs_origin.p, rhs_fac, grid, nx, s); h->launches++;
+    if (h->n_cpu > 1) { need_comm(h); try { omg_comm_allreduce_sum_vec(h->comm, grid, N, s); } catch (const std::exception& e) { fail(e.what()); } }
+    std::string err;
+    if (!omgfs::convolve(h->fs_plan, LF.dev.dr[0] * LF.dev.dr[1] * LF.dev.dr[2], s, err)) fail(err);
+    h->launches += 5;
+    for (size_t li = 0; li < h->levels.size(); ++li) {
+      LevelHost& L = h->levels[li];
+      if (!h->fs_nfaces[li]) continue;
+      omgfs::bc_planes(L.dev, h->fs_faces[li].p, h->fs_nfaces[li], grid, nx, h->fs_geom, s); h->launches++;
+      // the host copy follows (sync_meta re-uploads it whenever the level's metadata change; omg_get_bc_plane reads it)
+      CK(cudaMemcpyAsync(L.h_bcpl.data(), L.d_bcpl.p, L.h_bcpl.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    omgfs::scatter_phi(LF.dev, h->fs_origin.p, grid, nx, s); h->launches++;
+    CK(cudaStreamSynchronize(s));
+    check_p2p(h);
+  });
+}
+
+int omg_get_bc_plane(omg_handle* h, int box_id, int nb, int* bc_type, double* plane) {
+  OMG_TRY(h, {
+    if (!h->have_tree) fail("no tree");
+    if (box_id < 1 || box_id > h->n_boxes || h->loc[box_id] < 0) fail("omg_get_bc_plane: box not owned by this rank");
+    if (nb < 1 || nb > 6) fail("omg_get_bc_plane: nb out of range");
+    LevelHost& L = h->L(h->blvl[box_id - 1]);
+    const size_t q = (size_t)h->loc[box_id] * 6 + (nb - 1);
+    if (L.h_fkind[q] != FK_PHYS || L.h_farg[q] < 0) fail("omg_get_bc_plane: no stored plane on this face");
+    const size_t n2 = (size_t)L.nc * L.nc;
+    std::memcpy(plane, &L.h_bcpl[(size_t)L.h_farg[q] * n2], n2 * sizeof(double));
+    if (bc_type) *bc_type = L.h_ftype[q];
   });
 }
 

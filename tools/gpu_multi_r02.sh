@@ -7,7 +7,7 @@ mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/gpus_${T}_n$N.txt
 nvidia-smi topo -m >> gpurun_out/gpus_${T}_n$N.txt 2>&1
 t0=$(date +%s)
-timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 \
+timeout ${BENCH_TIMEOUT:-300} python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 \
   bench.py --gpus $N --steps 10 --warmup 3 --trace gpurun_out/trace_${T}_n$N > gpurun_out/bench_${T}_n$N.json 2> gpurun_out/bench_${T}_n$N.err
 echo "N=$N rc=$? after $(( $(date +%s) - t0 )) s (124 = never exited)"
 python - <<PY
@@ -26,4 +26,4 @@ try:
 except Exception as e:
     print('  no trace', e)
 PY
-grep -v "OMP_NUM_THREADS\|^\*\*\*\|destroy_process_group" gpurun_out/bench_${T}_n$N.err | tail -8
+grep "bench rank\|bench.py\|rror\|File \"/root" gpurun_out/bench_${T}_n$N.err | tail -60
