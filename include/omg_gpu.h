@@ -138,6 +138,10 @@ int omg_diffusion_set_rhs(omg_handle* h, double f1, double f2);
 int omg_free_space_kernel(omg_handle* h, int fft_lvl, const double r_min[3], int n_gauss, int n_range, const double* w,
                           const double* kx, const double* ky, const double* kz);
 int omg_free_space_solve(omg_handle* h, double rhs_fac);
+/* host-side convenience: builds that separable kernel (order-8 interpolating scaling functions, 89-term Gaussian
+ * quadrature of 1/r: createKernel('F', n_kernel(1), n_kernel(2), n_kernel(3), dr(1), dr(2), dr(3), 8, ...),
+ * poisson_3d_fft/build_kernel.f90:55-199, 884-1050) and hands it to omg_free_space_kernel */
+int omg_free_space_setup(omg_handle* h, int fft_lvl, const double r_min[3], const int n_kernel[3], const double dr[3]);
 /* the stored boundary plane of a physical-boundary face (what mg_phi_bc_store keeps in the ghost cells of mg_irhs,
  * src/m_ghost_cells.f90:66-117): nc*nc values, first tangential index fastest; *bc_type receives its type */
 int omg_get_bc_plane(omg_handle* h, int box_id, int nb, int* bc_type, double* plane);

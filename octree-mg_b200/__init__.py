@@ -162,6 +162,8 @@ def _declare(G, H):
     H.omgh_fas_vcycle.argtypes = [vp, ci, ci, ci, C.POINTER(cd), ci]
     H.omgh_fas_fmg.argtypes = [vp, ci, ci, C.POINTER(cd)]
     H.omgh_diffusion_solve.argtypes = [vp, ci, cd, cd, ci, cd, C.POINTER(cd), C.POINTER(ci)]
+    H.omgh_poisson_free_3d.argtypes = [vp, ci, cd, ci, ci, C.POINTER(cd)]
+    H.omgh_free_space_fft_lvl.argtypes = [vp]
 
 
 def _arr(vals, ctype):
@@ -438,6 +440,16 @@ class Mg:
 
     def diffusion_set_rhs(self, f1, f2):
         self._gck(self.G.omg_diffusion_set_rhs(self.gpu, f1, f2))
+
+    def mg_poisson_free_3d(self, new_rhs, max_fft_frac, fmgcycle=True, want_res=True):
+        """src/m_free_space.f90:36-214; returns max_res (None if not requested)"""
+        r = C.c_double(0.0)
+        self._ck(self.H.omgh_poisson_free_3d(self.h, int(bool(new_rhs)), max_fft_frac, int(bool(fmgcycle)), int(bool(want_res)), C.byref(r)))
+        return r.value if want_res else None
+
+    @property
+    def free_space_fft_lvl(self):
+        return self.H.omgh_free_space_fft_lvl(self.h)
 
     # coupling_amrvac/mod_multigrid_coupling.t:133-267: application arrays <-> device tree, no host cc arrays in between
     def copy_size(self, leaves_only=True, with_ghosts=False, lvl_lo=-20, lvl_hi=20):

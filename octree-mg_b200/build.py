@@ -18,7 +18,7 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-ccbin", "/usr/bin/g++"]
-CU_SOURCES = ["omg_core.cu", "omg_kernels.cu", "omg_fast.cu", "omg_comm.cu", "omg_fs.cu", "omg_plan.cpp"]
+CU_SOURCES = ["omg_core.cu", "omg_kernels.cu", "omg_fast.cu", "omg_comm.cu", "omg_fs.cu", "omg_fs_kernel.cpp", "omg_plan.cpp"]
 LIB_CUDA = os.path.join(HERE, "libomg_b200.so")
 LIB_HOST = os.path.join(HERE, "libomg_host.so")
 

@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <chrono>
 #include <condition_variable>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -257,8 +258,14 @@ static bool teardown_rendezvous(omg_comm* c) {
 void omg_comm_destroy(omg_comm* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  const char* dbg_e = getenv("OMG_DEBUG_TEARDOWN");
+  const bool dbg = dbg_e && *dbg_e && atoi(dbg_e) != 0;
+  auto say = [&](const char* what) { if (dbg) { std::fprintf(stderr, "[omg teardown rank %d] %s\n", c->rank, what); std::fflush(stderr); } };
+  say("rendezvous");
   const bool met = teardown_rendezvous(c);
+  say(met ? "met; closing peer mappings" : "no rendezvous; closing peer mappings");
   for (void* p : c->ipc_opened) cudaIpcCloseMemHandle(p);
+  say("closed");
   if (met) {                                 // nobody frees before everybody has closed
     double* d = nullptr;
     if (cudaMalloc(&d, sizeof(double)) == cudaSuccess) {
@@ -271,7 +278,9 @@ void omg_comm_destroy(omg_comm* c) {
   if (c->ipc_scratch) cudaFree(c->ipc_scratch);
   if (c->h_err) cudaFreeHost((void*)c->h_err);
   if (c->d_peer_flags) cudaFree(c->d_peer_flags);
+  say("freed; destroying the NCCL communicator");
   if (c->nccl) nccl_api().CommDestroy(c->nccl);
+  say("done");
   if (c->g) {
     c->g->abort_group();                    // a group cannot continue without one of its ranks
     if (c->ev_ready) cudaEventDestroy(c->ev_ready);

@@ -87,8 +87,8 @@ struct LevelHost {
   // in-kernel exchange (PutDev): launch order = partition-face boxes, then the rest; per partition-face box the faces it
   // sends {receiver's face, receiver rank, plane in its pool}
   bool rb_remote_any = false;           // some rank receives interpolated coarse faces on this level (replicated-tree fact)
-  std::vector<int> h_order, h_put_ptr, h_put_item, h_launch;
-  DevBuf<int> d_order, d_put_ptr, d_put_item, d_launch;
+  std::vector<int> h_order, h_put_ptr, h_put_item, h_launch, h_launch_ring;   // h_launch_ring: interior boxes first (ring kernel)
+  DevBuf<int> d_order, d_put_ptr, d_put_item, d_launch, d_launch_ring;
   DevBuf<unsigned int> d_done;
   bool all_fast = false;                // every face of every box has a kind the fast kernels serve (FK_SAME, FK_PHYS, FK_PLANE)
 };
@@ -181,7 +181,7 @@ void free_levels(omg_handle* h) {
   for (LevelHost& L : h->levels) {
     L.d_fkind.free(); L.d_farg.free(); L.d_ftype.free(); L.d_fkind_old.free(); L.d_farg_old.free();
     L.d_parent.free(); L.d_coff.free(); L.d_parents.free(); L.d_leaves.free(); L.d_rb.free(); L.d_oldpl.free();
-    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free(); L.d_bnd.free(); L.d_int.free(); L.d_order.free(); L.d_launch.free(); L.d_put_ptr.free(); L.d_put_item.free(); L.d_done.free();
+    L.d_gpl.free(); L.d_gpl_old.free(); L.d_bcpl.free(); L.d_bnd.free(); L.d_int.free(); L.d_order.free(); L.d_launch.free(); L.d_launch_ring.free(); L.d_put_ptr.free(); L.d_put_item.free(); L.d_done.free();
     for (int v = 0; v < OMG_MAXV; ++v) { L.d_var[v].free(); L.d_faces[v].free(); }
     L.xg.free(); L.xr.free(); L.xp.free();
   }
@@ -377,6 +377,8 @@ void set_tree(omg_handle* h, const omg_tree_desc* t) {
     // (on big levels the extra indirection at every CTA start costs more than it hides, measured)
     L.h_launch = L.h_bnd;
     L.h_launch.insert(L.h_launch.end(), L.h_int.begin(), L.h_int.end());
+    L.h_launch_ring = L.h_int;
+    L.h_launch_ring.insert(L.h_launch_ring.end(), L.h_bnd.begin(), L.h_bnd.end());
     L.h_put_ptr.assign(1, 0);
     for (int b : L.h_bnd) {
       auto it = put_by_box.find(b);
@@ -473,7 +475,7 @@ void sync_meta(omg_handle* h) {
       L.d_parents.upload(L.h_parents, s); L.d_leaves.upload(L.h_leaves, s);
       L.d_rb.upload(L.h_rb, s); L.d_oldpl.upload(L.h_oldpl, s);
       L.d_bnd.upload(L.h_bnd, s); L.d_int.upload(L.h_int, s);
-      L.d_order.upload(L.h_order, s); L.d_launch.upload(L.h_launch, s); L.d_put_ptr.upload(L.h_put_ptr, s); L.d_put_item.upload(L.h_put_item, s);
+      L.d_order.upload(L.h_order, s); L.d_launch.upload(L.h_launch, s); L.d_launch_ring.upload(L.h_launch_ring, s); L.d_put_ptr.upload(L.h_put_ptr, s); L.d_put_item.upload(L.h_put_item, s);
       if (!L.d_done.p) { L.d_done.alloc(1); CK(cudaMemsetAsync(L.d_done.p, 0, sizeof(unsigned int), s)); }
       L.d_bcpl.upload(L.h_bcpl, s);
       for (PhasePlan* X : {&L.xg, &L.xr, &L.xp}) { X->d_sdesc.upload(X->h_sdesc, s); X->d_rdesc.upload(X->h_rdesc, s); X->d_dst.upload(X->h_dst, s); X->d_peer_stride.upload(X->h_peer_stride, s); }
@@ -769,7 +771,8 @@ void exec_steps(omg_handle* h, Program& P) {
         LevelHost& L = h->L(st.l);
         if (st.b == 3) {   // in-kernel exchange: whole level in one launch
           if (L.nb) {
-            if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, L.nb <= h->bnd_first_boxes ? L.d_launch.p : nullptr, L.nb, 1, s)) fail("fused smoother does not apply to this level");
+            const int* order = omgf::smooth_uses_ring(L.dev, PD, L.nb) ? L.d_launch_ring.p : (L.nb <= h->bnd_first_boxes ? L.d_launch.p : nullptr);
+            if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, order, L.nb, 1, s)) fail("fused smoother does not apply to this level");
             h->launches++; h->exchanges++; h->fused_smooths++; fast(L);
           }
           // emulated ranks share one GPU: a kernel must never wait for a kernel that may not be running, so the ranks
@@ -1200,6 +1203,11 @@ int omg_destroy(omg_handle* h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
+  // graph executables first: NCCL keeps a communicator alive (ncclCommDestroy does not return) while a captured graph
+  // that contains its send / recv / all-reduce nodes still exists -- which is what blocked every multi-rank teardown
+  // (gpurun_out r02n: both ranks inside omg_destroy for > 200 s)
+  invalidate_programs(h);
+  cudaStreamSynchronize(h->stream2);
   if (h->comm) omg_comm_destroy(h->comm);
   try { drain_totals(h, true); collect_profile(h); free_levels(h); } catch (...) {}
   for (auto& r : h->trace_events) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
@@ -1585,6 +1593,7 @@ void reset_epochs(omg_handle* h) {
 }
 int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks) {
   OMG_TRY(h, {
+    invalidate_programs(h);                  // graphs that captured the old communicator's operations go first
     if (h->comm) { omg_comm_destroy(h->comm); h->comm = nullptr; }
     try { h->comm = omg_comm_create_nccl(uid, rank, nranks, h->device); } catch (const std::exception& e) { fail(e.what()); }
     reset_epochs(h);

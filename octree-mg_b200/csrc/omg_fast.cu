@@ -1446,6 +1446,10 @@ bool smooth_applies(const LevelDev& L, const ParamsDev& P) {
   if (P.op == OP_AHELMH) return L.var[4] && L.faces[4] && L.var[5] && L.faces[5] && L.var[6] && L.faces[6];
   return P.op == OP_LPL || P.op == OP_HELMH;
 }
+// will smooth() run the persistent ring kernel on n boxes of this level?
+bool smooth_uses_ring(const LevelDev& L, const ParamsDev& P, int n) {
+  return L.nc == 16 && (P.op == OP_LPL || P.op == OP_HELMH) && g_ring && (n >= 4 * sm_count() || g_ring == 2);
+}
 bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, const int* list, int n, int fused, cudaStream_t s) {
   if (!all_fast || L.nb == 0) return false;
   if (list && n == 0) return true;
@@ -1462,7 +1466,7 @@ bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, co
     return false;
   }
   if (P.op != OP_LPL && P.op != OP_HELMH) return false;
-  if (L.nc == 16 && g_ring && ((list ? n : L.nb) >= 4 * sm_count() || g_ring == 2)) return dispatch_smooth_ring(L, P, colour, list, n, fused, s);
+  if (smooth_uses_ring(L, P, list ? n : L.nb)) return dispatch_smooth_ring(L, P, colour, list, n, fused, s);
   if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, fused, s);
   if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, fused, s);
   return false;

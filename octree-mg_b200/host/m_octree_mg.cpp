@@ -648,6 +648,8 @@ void mg_copy_from_tree(mg_t& mg, int iv, double* buf, int64_t n_doubles, bool le
 
 }  // namespace omg
 
+#include "m_free_space.inc"
+
 // =====================================================================================================
 // flat C wrapper for the Python harness (ctypes): one opaque pointer per mg_t
 // =====================================================================================================
@@ -773,6 +775,10 @@ int omgh_diffusion_solve(void* h, int kind, double dt, double coeff, int order, 
                                      : diffusion_solve_acoeff(w->mg, dt, order, max_res, res);
              if (n_vcycles) *n_vcycles = n; });
 }
+int omgh_poisson_free_3d(void* h, int new_rhs, double max_fft_frac, int fmgcycle, int want_res, double* max_res) {
+  Wrapped* w = (Wrapped*)h; H_TRY(w, mg_poisson_free_3d(w->mg, new_rhs != 0, max_fft_frac, fmgcycle != 0, want_res ? max_res : nullptr));
+}
+int omgh_free_space_fft_lvl(void* h) { Wrapped* w = (Wrapped*)h; return w->mg.free_bc_initialized ? w->mg.free_bc_fft_lvl : -999; }
 int omgh_fill_ghost_cells_lvl(void* h, int lvl, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_fill_ghost_cells_lvl(w->mg, lvl, iv)); }
 int omgh_fill_ghost_cells(void* h, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_fill_ghost_cells(w->mg, iv)); }
 int omgh_phi_bc_store(void* h) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_phi_bc_store(w->mg)); }

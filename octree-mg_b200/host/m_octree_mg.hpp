@@ -85,6 +85,9 @@ struct mg_t {
   bool bc_dirty = true, eps_dirty = true;
   int coarse_collapse_boxes = 0;   // > 0: coarse levels with fewer boxes per rank than this live on one GPU (see m_load_balance part)
   bool host_cc = true;   // false: device-resident runs that never touch host cc skip the host allocation
+  // type(mg_free_bc_t) of src/m_free_space.f90:9-22: what the host keeps of it (grids and planes live on the device)
+  bool free_bc_initialized = false;
+  int free_bc_fft_lvl = -1;
 
   mg_lvl_t& L(int lvl) { return lvls[lvl - mg_lvl_lo]; }
   const mg_lvl_t& L(int lvl) const { return lvls[lvl - mg_lvl_lo]; }
@@ -135,6 +138,11 @@ void mg_apply_op(mg_t& mg, int i_out);
 int diffusion_solve(mg_t& mg, double dt, double diffusion_coeff, int order, double max_res, double* res = nullptr);
 int diffusion_solve_vcoeff(mg_t& mg, double dt, int order, double max_res, double* res = nullptr);   // eps in mg_iveps
 int diffusion_solve_acoeff(mg_t& mg, double dt, int order, double max_res, double* res = nullptr);   // eps in mg_iveps1..3
+
+// ---- m_free_space (src/m_free_space.f90:36-214): free-space boundary conditions for 3-D Poisson problems.  Each call
+//      performs an additional FMG cycle (or V-cycle); max_fft_frac bounds the size of the level the FFT solve runs on ----
+void mg_poisson_free_3d(mg_t& mg, bool new_rhs, double max_fft_frac, bool fmgcycle, double* max_res = nullptr);
+int mg_highest_uniform_lvl(const mg_t& mg);
 
 // ---- m_ghost_cells / m_restrict / m_prolong level-wide entry points ---------------------------------
 void mg_fill_ghost_cells_lvl(mg_t& mg, int lvl, int iv);
