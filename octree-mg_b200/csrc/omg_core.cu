@@ -1561,6 +1561,9 @@ int omg_free_space_solve(omg_handle* h, double rhs_fac) {
       CK(cudaMemcpyAsync(L.h_bcpl.data(), L.d_bcpl.p, L.h_bcpl.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
     }
     omgfs::scatter_phi(LF.dev, h->fs_origin.p, grid, nx, s); h->launches++;
+    // the reference copies the ghost layer along with the solution (cc(0:nc+1, ...), :176-179); here ghost values are
+    // derived, except those of faces owned by other ranks, which need their exchange before the level is prolonged
+    if (LF.xg.any) exchange_ghost(h, h->fs_lvl, 0, s);
     CK(cudaStreamSynchronize(s));
     check_p2p(h);
   });
