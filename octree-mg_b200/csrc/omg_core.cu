@@ -125,7 +125,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1, ring_order = 0, ring_fused = 0;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -771,8 +771,18 @@ void exec_steps(omg_handle* h, Program& P) {
         LevelHost& L = h->L(st.l);
         if (st.b == 3) {   // in-kernel exchange: whole level in one launch
           if (L.nb) {
-            const int* order = omgf::smooth_uses_ring(L.dev, PD, L.nb) ? L.d_launch_ring.p : (L.nb <= h->bnd_first_boxes ? L.d_launch.p : nullptr);
-            if (!omgf::smooth(L.dev, PD, st.a, L.all_fast, order, L.nb, 1, s)) fail("fused smoother does not apply to this level");
+            // In-kernel exchange: the one-tile-per-CTA kernel, not the persistent ring (option "ring_fused" = 1 switches it on).
+            // A ring CTA that reaches a partition-face tile stalls its whole pipeline for the wait and the remote stores;
+            // measured at 2 GPUs, 512^3 each (profiles/r02p_*): ring with partition-face boxes first 4.899 ms per cycle,
+            // last 4.999, natural order 5.943 -- one tile per CTA 4.793, although its half-sweep alone is 0.279 vs 0.268 ms.
+            // Launch order: partition-face boxes first on small levels (their faces leave early), natural order on big ones.
+            const bool ring = h->ring_fused && omgf::smooth_uses_ring(L.dev, PD, L.nb);
+            omgf::set_ring(ring ? h->ring : 0);
+            const int* order = ring ? (h->ring_order == 1 ? L.d_launch_ring.p : h->ring_order == 2 ? nullptr : L.d_launch.p)
+                                    : (L.nb <= h->bnd_first_boxes ? L.d_launch.p : nullptr);
+            const bool ok_fused = omgf::smooth(L.dev, PD, st.a, L.all_fast, order, L.nb, 1, s);
+            omgf::set_ring(h->ring);
+            if (!ok_fused) fail("fused smoother does not apply to this level");
             h->launches++; h->exchanges++; h->fused_smooths++; fast(L);
           }
           // emulated ranks share one GPU: a kernel must never wait for a kernel that may not be running, so the ranks
@@ -1725,6 +1735,8 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "overlap") h->overlap = value;
     else if (k == "pdl") h->pdl = value;
     else if (k == "ring") h->ring = value;
+    else if (k == "ring_fused") h->ring_fused = value;
+    else if (k == "ring_order") h->ring_order = value;   // fused levels on the ring kernel: 0 partition-face boxes first, 1 last, 2 natural order
     else if (k == "store_fine_residual") h->store_fine_residual = value;
     else if (k == "trace") { h->trace = value; for (auto& r : h->trace_events) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); } h->trace_events.clear(); }
     else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
