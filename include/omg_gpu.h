@@ -71,6 +71,15 @@ typedef struct omg_params {
 /* ---- lifetime ------------------------------------------------------------ */
 int omg_create(int device, omg_handle** out);             /* one handle per mg_t, bound to one GPU */
 int omg_destroy(omg_handle* h);                           /* mg_deallocate_storage, src/m_allocate_storage.f90:14-47 */
+/* On-device regrid / re-partition.  The reference changes a tree with mg_add_children / mg_set_refinement_boundaries
+ * (src/m_build_tree.f90:296-367) and mg_load_balance (src/m_load_balance.f90:71-136); its application coupling then
+ * deallocates, rebuilds and copies every variable in again.  omg_update_tree takes the NEW description (same box size,
+ * variables and ranks) and keeps the device data of every box that exists in both trees on the same level: boxes that
+ * stay on this rank are copied device to device, boxes whose owner changed travel old owner -> new owner (NCCL send /
+ * recv), new boxes are zero-filled as mg_allocate_storage does (src/m_allocate_storage.f90:72-76).  Collective on several
+ * ranks.  Boundary planes, parameters and (for emulated ranks) the communicator's pool mappings are set again by the
+ * caller as after omg_set_tree. */
+int omg_update_tree(omg_handle* h, const omg_tree_desc* tree);
 const char* omg_last_error(const omg_handle* h);          /* message of the last failing call */
 const char* omg_version(void);
 

@@ -144,7 +144,7 @@ def _declare(G, H):
     H.omgh_set_bc_callback.argtypes = [vp, ci, ci, BC_CALLBACK, vp]
     H.omgh_comm_init.argtypes = [vp, ci, ci]
     H.omgh_build_rectangle.argtypes = [vp, C.POINTER(ci), ci, C.POINTER(cd), C.POINTER(cd), C.POINTER(ci), ci]
-    for n in ("omgh_set_methods", "omgh_allocate_storage", "omgh_deallocate_storage", "omgh_phi_bc_store",
+    for n in ("omgh_set_methods", "omgh_allocate_storage", "omgh_deallocate_storage", "omgh_gpu_update_tree", "omgh_phi_bc_store",
               "omgh_gpu_push_bc", "omgh_gpu_push_params"):
         getattr(H, n).argtypes = [vp]
     for n in ("omgh_add_children", "omgh_set_leaves_parents", "omgh_set_next_level_ids", "omgh_set_neighbors_lvl",
@@ -276,6 +276,11 @@ class Mg:
 
     def mg_deallocate_storage(self):
         self._ck(self.H.omgh_deallocate_storage(self.h))
+
+    def mg_gpu_update_tree(self):
+        """the host changed the tree of an allocated mg (mg_add_children ..., mg_load_balance): on-device regrid"""
+        self._ck(self.H.omgh_gpu_update_tree(self.h))
+        self._tree = None
 
     # -- introspection ------------------------------------------------------------------------------
     lowest_lvl = property(lambda self: self.get_int("lowest_lvl"))
@@ -603,6 +608,13 @@ class MgGroup:
             m.mg_allocate_storage()
         hs = (C.c_void_p * self.n)(*[m.gpu for m in self.ranks])
         if self.ranks[0].G.omg_comm_init_local(hs, self.n) != 0:
+            raise MgError(self.ranks[0].G.omg_last_error(self.ranks[0].gpu).decode())
+        self._owner = None
+
+    def mg_gpu_update_tree(self):
+        self._all(lambda m: m.mg_gpu_update_tree())
+        hs = (C.c_void_p * self.n)(*[m.gpu for m in self.ranks])
+        if self.ranks[0].G.omg_comm_init_local(hs, self.n) != 0:      # emulated ranks: the new plane pools are shared again
             raise MgError(self.ranks[0].G.omg_last_error(self.ranks[0].gpu).decode())
         self._owner = None
 

@@ -161,6 +161,7 @@ struct omg_comm {
   volatile int* h_err = nullptr;            // so the host reads it without touching the device
   unsigned long long timeout_ns = 0;
   std::vector<void*> ipc_opened;
+  size_t n_flag_maps = 0;                   // the first entries of ipc_opened: the peers' flag arrays (kept by omg_comm_unshare)
   void* ipc_scratch = nullptr;
 };
 
@@ -207,6 +208,7 @@ omg_comm* omg_comm_create_nccl(const char uid[128], int rank, int nranks, int de
       c->p2p = true;                                   // omg_comm_share clears it again (on every rank) if IPC is unavailable
       omg_comm_share(c, c->d_flags, pf.data());
       if (c->p2p) CCK(cudaMemcpy(c->d_peer_flags, pf.data(), nranks * sizeof(void*), cudaMemcpyHostToDevice));
+      c->n_flag_maps = c->ipc_opened.size();
     } catch (...) { c->p2p = false; }
   }
   return c;
@@ -449,6 +451,20 @@ void omg_comm_share(omg_comm* c, void* ptr, void** peer_ptrs) {
     return;
   }
   c->ipc_opened.insert(c->ipc_opened.end(), opened.begin(), opened.end());
+}
+
+void omg_comm_unshare(omg_comm* c) {
+  if (c->g) { c->g->barrier(); return; }       // emulated ranks share plain pointers: nothing to close, only the meeting point
+  if (!c->nccl) return;
+  CCK(cudaDeviceSynchronize());
+  for (size_t i = c->n_flag_maps; i < c->ipc_opened.size(); ++i) cudaIpcCloseMemHandle(c->ipc_opened[i]);
+  c->ipc_opened.resize(std::min(c->n_flag_maps, c->ipc_opened.size()));
+  double* d = nullptr;
+  CCK(cudaMalloc(&d, sizeof(double)));
+  CCK(cudaMemset(d, 0, sizeof(double)));
+  NCK(nccl_api().AllReduce(d, d, 1, ncclDouble, ncclSum, c->nccl, 0));
+  CCK(cudaDeviceSynchronize());
+  cudaFree(d);
 }
 
 void omg_comm_signal_wait(omg_comm* c, int channel, const int* peers, int npeers, unsigned long long* epoch, int signal, cudaStream_t s) {

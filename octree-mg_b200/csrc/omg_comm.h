@@ -39,6 +39,9 @@ bool omg_comm_p2p(const omg_comm* c);
 // collective: every rank contributes ONE device allocation (base pointer as returned by cudaMalloc); peer_ptrs[r]
 // becomes a pointer to rank r's allocation valid on this rank's device (peer_ptrs[me] = ptr)
 void omg_comm_share(omg_comm* c, void* ptr, void** peer_ptrs);
+// collective: close every mapping made by omg_comm_share since the communicator was created (the flag arrays stay), then
+// a barrier -- after it the owners may free the shared allocations (CUDA IPC: never free what a peer still has mapped)
+void omg_comm_unshare(omg_comm* c);
 // `epoch` (device, one counter per channel) is incremented when the wait completes: kernels launched after it see the
 // new value, which selects the plane buffer the peers have just filled
 // signal = 0: wait only (the puts of the current epoch were signalled from inside a kernel, see omg_fast.cu)

@@ -1604,30 +1604,147 @@ void reset_epochs(omg_handle* h) {
   CK(cudaMemset(h->d_epoch.p, 0, OMG_NLVL * sizeof(unsigned long long)));
   h->params_dirty = true;                    // LevelDev copies carry gpl_sel
 }
+// map every distributed level's plane pool of every rank (NCCL back end; collective, same level order on all ranks)
+void share_pools(omg_handle* h) {
+  const int nranks = h->n_cpu;
+  for (LevelHost& L : h->levels) L.xg.shared = false;
+  if (!h->comm || !h->have_tree || !omg_comm_p2p(h->comm) || !omg_comm_graph_safe(h->comm)) return;
+  std::vector<void*> ptrs(nranks, nullptr);
+  for (LevelHost& L : h->levels) {
+    if (!L.xg.any) continue;
+    try { omg_comm_share(h->comm, L.d_gpl.p, ptrs.data()); } catch (const std::exception& e) { fail(e.what()); }
+    if (!omg_comm_p2p(h->comm)) break;                       // IPC unavailable: every rank falls back to send/recv
+    std::vector<double*> pb(nranks);
+    for (int r = 0; r < nranks; ++r) pb[r] = static_cast<double*>(ptrs[r]);
+    L.xg.d_peer_base.upload(pb, h->stream);
+    CK(cudaStreamSynchronize(h->stream));
+    L.xg.shared = true;
+  }
+  if (!omg_comm_p2p(h->comm)) for (LevelHost& L : h->levels) L.xg.shared = false;
+}
 int omg_comm_init(omg_handle* h, const char uid[128], int rank, int nranks) {
   OMG_TRY(h, {
     invalidate_programs(h);                  // graphs that captured the old communicator's operations go first
     if (h->comm) { omg_comm_destroy(h->comm); h->comm = nullptr; }
     try { h->comm = omg_comm_create_nccl(uid, rank, nranks, h->device); } catch (const std::exception& e) { fail(e.what()); }
     reset_epochs(h);
-    for (LevelHost& L : h->levels) L.xg.shared = false;
-    if (h->have_tree && omg_comm_p2p(h->comm)) {
-      std::vector<void*> ptrs(nranks, nullptr);
-      for (LevelHost& L : h->levels) {
-        if (!L.xg.any) continue;
-        try { omg_comm_share(h->comm, L.d_gpl.p, ptrs.data()); } catch (const std::exception& e) { fail(e.what()); }
-        if (!omg_comm_p2p(h->comm)) break;                       // IPC unavailable: every rank falls back to send/recv
-        std::vector<double*> pb(nranks);
-        for (int r = 0; r < nranks; ++r) pb[r] = static_cast<double*>(ptrs[r]);
-        L.xg.d_peer_base.upload(pb, h->stream);
-        CK(cudaStreamSynchronize(h->stream));
-        L.xg.shared = true;
-      }
-      if (!omg_comm_p2p(h->comm)) for (LevelHost& L : h->levels) L.xg.shared = false;
-    }
+    share_pools(h);
     invalidate_programs(h);
   });
 }
+
+// ---- on-device regrid / re-partition (include/omg_gpu.h: omg_update_tree) ----------------------------------------------
+namespace {
+struct OldLevel { int lvl = 0, nc = 0; std::vector<int> ids; DevBuf<double> var[OMG_MAXV], faces[OMG_MAXV]; };
+
+void update_tree(omg_handle* h, const omg_tree_desc* t) {
+  if (!h->have_tree) { set_tree(h, t); return; }
+  CK(cudaSetDevice(h->device));
+  if (t->box_size != h->box_size || t->n_extra_vars != h->n_extra || t->n_cpu != h->n_cpu || t->my_rank != h->my_rank)
+    fail("omg_update_tree: box size, number of variables and ranks must stay the same");
+  if (h->n_cpu > 1) need_comm(h);
+  CK(cudaStreamSynchronize(h->stream));
+  check_p2p(h);
+  const int me = h->my_rank, nvar = h->nvar;
+  // the peers' mappings of the old plane pools must be closed before the pools are freed: everybody closes, then a barrier
+  if (h->comm && omg_comm_graph_safe(h->comm)) {
+    invalidate_programs(h);
+    try { omg_comm_unshare(h->comm); } catch (const std::exception& e) { fail(e.what()); }
+  }
+  // 1. keep the old variables out of free_levels' reach
+  std::vector<OldLevel> old(h->levels.size());
+  for (size_t li = 0; li < h->levels.size(); ++li) {
+    LevelHost& L = h->levels[li];
+    old[li].lvl = L.lvl; old[li].nc = L.nc; old[li].ids = L.ids;
+    for (int v = 0; v < OMG_MAXV; ++v) { std::swap(old[li].var[v], L.d_var[v]); std::swap(old[li].faces[v], L.d_faces[v]); }
+  }
+  const std::vector<int> old_rank = h->rank, old_lvl = h->blvl;
+  const int old_n = h->n_boxes, old_lowest = h->lowest;
+  auto free_old = [&]() { for (OldLevel& O : old) for (int v = 0; v < OMG_MAXV; ++v) { O.var[v].free(); O.faces[v].free(); } };
+  try {
+    // 2. the new tree: fresh, zero-filled storage (mg_allocate_storage, src/m_allocate_storage.f90:72-76)
+    set_tree(h, t);
+    cudaStream_t s = h->stream;
+    // 3. boxes that exist in both trees on the same level keep their data
+    for (LevelHost& L : h->levels) {
+      const int oi = L.lvl - old_lowest;
+      if (oi < 0 || oi >= (int)old.size() || old[oi].nc != L.nc) continue;
+      OldLevel& O = old[oi];
+      std::map<int, int> old_loc;
+      for (size_t b = 0; b < O.ids.size(); ++b) old_loc[O.ids[b]] = (int)b;
+      const size_t bs = (size_t)L.dev.bs, fs = (size_t)6 * L.nc * L.nc;
+      // (a) stayed on this rank: device-to-device
+      std::vector<int> pairs;
+      for (int b = 0; b < L.nb; ++b) { auto it = old_loc.find(L.ids[b]); if (it != old_loc.end()) { pairs.push_back(it->second); pairs.push_back(b); } }
+      if (!pairs.empty()) {
+        DevBuf<int> d_pairs; d_pairs.upload(pairs, s);
+        for (int v = 0; v < nvar; ++v) {
+          omgk::copy_boxes(L.d_var[v].p, O.var[v].p, d_pairs.p, (int)pairs.size() / 2, bs, s); h->launches++;
+          if (v >= 4 && O.faces[v].p && L.d_faces[v].p) { omgk::copy_boxes(L.d_faces[v].p, O.faces[v].p, d_pairs.p, (int)pairs.size() / 2, fs, s); h->launches++; }
+        }
+        CK(cudaStreamSynchronize(s));
+        d_pairs.free();
+      }
+      // (b) changed owner: old owner -> new owner, ids ascending on both sides (the tree is replicated)
+      if (h->n_cpu > 1) {
+        std::map<int, std::vector<int>> send_to, recv_from;       // peer -> box ids
+        for (int id : h->lvl_ids[L.lvl - h->lowest]) {
+          if (id > old_n || old_lvl[id - 1] != L.lvl) continue;
+          const int ro = old_rank[id - 1], rn = h->rank[id - 1];
+          if (ro == rn) continue;
+          if (ro == me) send_to[rn].push_back(id);
+          if (rn == me) recv_from[ro].push_back(id);
+        }
+        // every rank takes part in the exchange of a level on which ANY box moved (same decision everywhere)
+        bool any = false;
+        for (int id : h->lvl_ids[L.lvl - h->lowest]) if (id <= old_n && old_lvl[id - 1] == L.lvl && old_rank[id - 1] != h->rank[id - 1]) any = true;
+        if (any) {
+          const size_t item = (size_t)nvar * bs + (size_t)h->n_extra * fs;
+          std::vector<int> peers;
+          for (auto& kv : send_to) peers.push_back(kv.first);
+          for (auto& kv : recv_from) if (!send_to.count(kv.first)) peers.push_back(kv.first);
+          std::sort(peers.begin(), peers.end());
+          size_t ns = 0, nr = 0;
+          for (auto& kv : send_to) ns += kv.second.size();
+          for (auto& kv : recv_from) nr += kv.second.size();
+          DevBuf<double> d_send, d_recv; d_send.alloc(ns * item); d_recv.alloc(nr * item);
+          std::vector<OmgXfer> segs; std::vector<int> spairs, rpairs;     // (box index in its array, slot in the buffer)
+          size_t so = 0, ro = 0;
+          for (int p : peers) {
+            OmgXfer x{p, d_send.p + so * item, 0, d_recv.p + ro * item, 0};
+            if (send_to.count(p)) { for (int id : send_to[p]) { spairs.push_back(old_loc.at(id)); spairs.push_back((int)so++); } x.send_n = send_to[p].size() * item; }
+            if (recv_from.count(p)) { for (int id : recv_from[p]) { rpairs.push_back((int)ro++); rpairs.push_back(h->loc[id]); } x.recv_n = recv_from[p].size() * item; }
+            segs.push_back(x);
+          }
+          DevBuf<int> d_sp, d_rp; d_sp.upload(spairs, s); d_rp.upload(rpairs, s);
+          size_t off = 0;
+          for (int v = 0; v < nvar; ++v) {       // buffer layout per box: var 0 .. nvar-1, then the stored faces of the extra variables
+            if (ns) { omgk::copy_boxes_strided(d_send.p + off, item, O.var[v].p, bs, d_sp.p, (int)ns, bs, s); h->launches++; }
+            off += bs;
+          }
+          for (int v = 4; v < nvar; ++v) { if (ns && O.faces[v].p) { omgk::copy_boxes_strided(d_send.p + off, item, O.faces[v].p, fs, d_sp.p, (int)ns, fs, s); h->launches++; } off += fs; }
+          try { omg_comm_exchange(h->comm, segs.data(), (int)segs.size(), s); } catch (const std::exception& e) { fail(e.what()); }
+          off = 0;
+          for (int v = 0; v < nvar; ++v) {
+            if (nr) { omgk::copy_boxes_strided(L.d_var[v].p, bs, d_recv.p + off, item, d_rp.p, (int)nr, bs, s); h->launches++; }
+            off += bs;
+          }
+          for (int v = 4; v < nvar; ++v) { if (nr && L.d_faces[v].p) { omgk::copy_boxes_strided(L.d_faces[v].p, fs, d_recv.p + off, item, d_rp.p, (int)nr, fs, s); h->launches++; } off += fs; }
+          CK(cudaStreamSynchronize(s));
+          d_send.free(); d_recv.free(); d_sp.free(); d_rp.free();
+        }
+      }
+    }
+  } catch (...) { free_old(); throw; }
+  free_old();
+  // 4. the new plane pools are mapped again (NCCL back end; emulated ranks call omg_comm_init_local once more)
+  if (h->comm) { reset_epochs(h); share_pools(h); }
+  invalidate_programs(h);
+}
+}  // namespace
+
+int omg_update_tree(omg_handle* h, const omg_tree_desc* t) { OMG_TRY(h, update_tree(h, t)); }
+
 int omg_comm_init_local(omg_handle* const* handles, int nranks) {
   if (!handles || nranks < 1) return 1;
   omg_handle* h0 = handles[0];

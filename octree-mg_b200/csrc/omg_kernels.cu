@@ -149,6 +149,14 @@ __global__ void __launch_bounds__(kThreads) k_pack_prolong_var(const __grid_cons
   else do_pack_prolong_var<GM_STORED>(Lc, P, iv, desc[2 * blockIdx.x], desc[2 * blockIdx.x + 1], o, nc_f, threadIdx.x, blockDim.x);
 }
 
+// regrid: whole boxes from one array to another; pairs[2e] = source box, pairs[2e+1] = destination box, strides in doubles
+__global__ void __launch_bounds__(kThreads) k_copy_boxes(double* __restrict__ dst, size_t dstride, const double* __restrict__ src, size_t sstride,
+                                                         const int* __restrict__ pairs, size_t n) {
+  const double* sp = src + (size_t)pairs[2 * blockIdx.x] * sstride;
+  double* dp = dst + (size_t)pairs[2 * blockIdx.x + 1] * dstride;
+  for (size_t i = threadIdx.x; i < n; i += blockDim.x) dp[i] = sp[i];
+}
+
 // elementwise helpers over whole-level arrays
 __global__ void k_fill(double* p, size_t n, double v) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
@@ -347,6 +355,12 @@ void unpack_restrict(const LevelDev& Lc, const int* desc, int n, const double* i
 }
 void pack_prolong(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, cudaStream_t s) {
   if (n) k_pack_prolong<<<n, kThreads, 0, s>>>(Lc, P, desc, out, nc_f);
+}
+void copy_boxes(double* dst, const double* src, const int* pairs, int n_pairs, size_t box_doubles, cudaStream_t s) {
+  if (n_pairs) k_copy_boxes<<<n_pairs, kThreads, 0, s>>>(dst, box_doubles, src, box_doubles, pairs, box_doubles);
+}
+void copy_boxes_strided(double* dst, size_t dstride, const double* src, size_t sstride, const int* pairs, int n_pairs, size_t n, cudaStream_t s) {
+  if (n_pairs) k_copy_boxes<<<n_pairs, kThreads, 0, s>>>(dst, dstride, src, sstride, pairs, n);
 }
 void fill(double* p, size_t n, double v, cudaStream_t s) { if (n) k_fill<<<grid_for(n), 256, 0, s>>>(p, n, v); }
 void copy(double* dst, const double* src, size_t n, cudaStream_t s) { if (n) k_copy<<<grid_for(n), 256, 0, s>>>(dst, src, n); }

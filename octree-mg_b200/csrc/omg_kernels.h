@@ -37,6 +37,9 @@ void put_ghost(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, const 
 void pack_restrict(const LevelDev& Lf, const int* desc, int n, double* out, int iv0, int iv1, cudaStream_t s);
 void unpack_restrict(const LevelDev& Lc, const int* desc, int n, const double* in, int h, int iv0, int iv1, cudaStream_t s);
 void pack_prolong(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, cudaStream_t s);
+// regrid (omg_update_tree): whole boxes between arrays, pairs = {source box, destination box}*
+void copy_boxes(double* dst, const double* src, const int* pairs, int n_pairs, size_t box_doubles, cudaStream_t s);
+void copy_boxes_strided(double* dst, size_t dstride, const double* src, size_t sstride, const int* pairs, int n_pairs, size_t n, cudaStream_t s);
 void pack_prolong_var(const LevelDev& Lc, const ParamsDev& P, const int* desc, int n, double* out, int nc_f, int iv, cudaStream_t s);
 void fill(double* p, size_t n, double v, cudaStream_t s);
 void copy(double* dst, const double* src, size_t n, cudaStream_t s);

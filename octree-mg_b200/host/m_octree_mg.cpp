@@ -344,16 +344,9 @@ void mg_load_balance_parents(mg_t& mg) {                                        
 // ------------------------------------------------------------------------------------------------
 // m_allocate_storage: host cc arrays for owned boxes + the device mirror behind the C ABI
 // ------------------------------------------------------------------------------------------------
-void mg_allocate_storage(mg_t& mg) {                                              // :51-99
-  if (!mg.tree_created) stop("allocate_storage: tree is not yet created");
-  if (mg.is_allocated) stop("allocate_storage: tree is already allocated");
-  if (mg.my_rank < 0 || mg.n_cpu < 1) mg_comm_init(mg);
-  update_lvl_info(mg);
-  for (int lvl = mg.lowest_lvl; lvl <= mg.highest_lvl; ++lvl) {
-    const int nc = mg.box_size_lvl[lvl - mg_lvl_lo];
-    if (mg.host_cc) for (int id : mg.L(lvl).my_ids) mg.boxes[id].cc.assign((size_t)(nc + 2) * (nc + 2) * (nc + 2) * mg.nvar(), 0.0);
-  }
-  // flatten the tree for the C ABI
+static void push_params(mg_t& mg);
+// flatten type(mg_t) for the C ABI and hand it to omg_set_tree (update = false) or omg_update_tree (update = true)
+static void hand_over_tree(mg_t& mg, bool update, const char* where) {
   const int n = mg.n_boxes;
   std::vector<int32_t> rank(n), lvl(n), ix(3 * (size_t)n), parent(n), children(8 * (size_t)n), neighbors(6 * (size_t)n);
   for (int id = 1; id <= n; ++id) {
@@ -380,9 +373,64 @@ void mg_allocate_storage(mg_t& mg) {                                            
     const int rc = omg_create(mg.device, &mg.gpu);
     if (rc != 0 || !mg.gpu) { mg.gpu = nullptr; stop("mg_allocate_storage: no CUDA device available (there is no CPU fallback)"); }
   }
-  gpu_check(mg, omg_set_tree(mg.gpu, &t), "mg_allocate_storage");
+  gpu_check(mg, update ? omg_update_tree(mg.gpu, &t) : omg_set_tree(mg.gpu, &t), where);
+}
+
+void mg_allocate_storage(mg_t& mg) {                                              // :51-99
+  if (!mg.tree_created) stop("allocate_storage: tree is not yet created");
+  if (mg.is_allocated) stop("allocate_storage: tree is already allocated");
+  if (mg.my_rank < 0 || mg.n_cpu < 1) mg_comm_init(mg);
+  update_lvl_info(mg);
+  for (int lvl = mg.lowest_lvl; lvl <= mg.highest_lvl; ++lvl) {
+    const int nc = mg.box_size_lvl[lvl - mg_lvl_lo];
+    if (mg.host_cc) for (int id : mg.L(lvl).my_ids) mg.boxes[id].cc.assign((size_t)(nc + 2) * (nc + 2) * (nc + 2) * mg.nvar(), 0.0);
+  }
+  hand_over_tree(mg, false, "mg_allocate_storage");
   mg.bc_dirty = true; mg.eps_dirty = true;
   mg.is_allocated = true;
+}
+
+// On-device regrid: the host has changed the tree of an allocated mg_t (mg_add_children + mg_set_neighbors_lvl +
+// mg_set_refinement_boundaries, src/m_build_tree.f90:296-367; mg_load_balance*, src/m_load_balance.f90:22-235).  Boxes that
+// exist before and after keep their data on the device (omg_update_tree: local copy, or old owner -> new owner); new boxes
+// start from zero like freshly allocated storage.  The reference's own route is mg_deallocate_storage + a rebuild + copying
+// every variable in again (coupling_amrvac).  Host cc arrays follow: allocated for boxes this rank owns now, released for
+// the others, and in drop-in mode refreshed from the device (boxes that arrived from another rank exist only there).
+void mg_gpu_update_tree(mg_t& mg) {
+  if (!mg.is_allocated) stop("mg_gpu_update_tree: tree is not allocated");
+  need_gpu(mg);
+  const bool drop_in = !mg.gpu_resident && mg.host_cc;
+  if (drop_in) {
+    // drop-in mode: the host arrays are the truth.  Everything this rank held so far (= every box with a cc array) goes to
+    // the device first, so that boxes which change owner take ALL their variables along
+    std::vector<int32_t> ids;
+    for (int id = 1; id <= mg.n_boxes; ++id) if (!mg.boxes[id].cc.empty()) ids.push_back(id);
+    std::vector<const double*> ptrs(ids.size());
+    for (int iv = 1; iv <= mg.nvar(); ++iv) {
+      for (size_t q = 0; q < ids.size(); ++q) {
+        const int n2 = mg.box_size_lvl[mg.boxes[ids[q]].lvl - mg_lvl_lo] + 2;
+        ptrs[q] = mg.boxes[ids[q]].cc.data() + (size_t)(iv - 1) * n2 * n2 * n2;
+      }
+      gpu_check(mg, omg_push_var(mg.gpu, iv, (int)ids.size(), ids.data(), ptrs.data()), "mg_gpu_update_tree");
+    }
+  }
+  update_lvl_info(mg);
+  for (int lvl = mg.lowest_lvl; lvl <= mg.highest_lvl; ++lvl) {
+    const int nc = mg.box_size_lvl[lvl - mg_lvl_lo];
+    const size_t want = (size_t)(nc + 2) * (nc + 2) * (nc + 2) * mg.nvar();
+    for (int id : mg.L(lvl).ids) {
+      mg_box_t& box = mg.boxes[id];
+      if (box.rank == mg.my_rank) { if (mg.host_cc && box.cc.size() != want) box.cc.assign(want, 0.0); }
+      else if (!box.cc.empty()) std::vector<double>().swap(box.cc);
+    }
+  }
+  hand_over_tree(mg, true, "mg_gpu_update_tree");
+  mg.bc_dirty = true; mg.eps_dirty = true;
+  mg.free_bc_initialized = false;
+  if (drop_in) {
+    push_params(mg);
+    for (int iv = 1; iv <= mg.nvar(); ++iv) mg_gpu_pull(mg, iv, iv == mg_iphi || iv >= mg_iveps);
+  }
 }
 
 void mg_deallocate_storage(mg_t& mg) {                                            // :14-47
@@ -779,6 +827,7 @@ int omgh_poisson_free_3d(void* h, int new_rhs, double max_fft_frac, int fmgcycle
   Wrapped* w = (Wrapped*)h; H_TRY(w, mg_poisson_free_3d(w->mg, new_rhs != 0, max_fft_frac, fmgcycle != 0, want_res ? max_res : nullptr));
 }
 int omgh_free_space_fft_lvl(void* h) { Wrapped* w = (Wrapped*)h; return w->mg.free_bc_initialized ? w->mg.free_bc_fft_lvl : -999; }
+int omgh_gpu_update_tree(void* h) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_gpu_update_tree(w->mg)); }
 int omgh_fill_ghost_cells_lvl(void* h, int lvl, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_fill_ghost_cells_lvl(w->mg, lvl, iv)); }
 int omgh_fill_ghost_cells(void* h, int iv) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_fill_ghost_cells(w->mg, iv)); }
 int omgh_phi_bc_store(void* h) { Wrapped* w = (Wrapped*)h; H_TRY(w, mg_phi_bc_store(w->mg)); }

@@ -125,6 +125,8 @@ void mg_load_balance_parents(mg_t& mg);
 // ---- m_allocate_storage (host cc arrays + device mirrors) -----------------------------------------
 void mg_allocate_storage(mg_t& mg);
 void mg_deallocate_storage(mg_t& mg);
+// after the host changed the tree of an allocated mg_t (refinement, re-partition): keep the device data of surviving boxes
+void mg_gpu_update_tree(mg_t& mg);
 
 // ---- m_multigrid / operator modules ------------------------------------------------------------
 void mg_set_methods(mg_t& mg);
