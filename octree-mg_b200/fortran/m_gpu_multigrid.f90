@@ -101,6 +101,20 @@ module m_gpu_multigrid
      integer(c_int64_t) function omg_copy_size(h, lvl_lo, lvl_hi, leaves_only, with_ghosts) bind(C, name="omg_copy_size")
        import; type(c_ptr), value :: h; integer(c_int), value :: lvl_lo, lvl_hi, leaves_only, with_ghosts
      end function omg_copy_size
+     integer(c_int) function omg_update_tree(h, t) bind(C, name="omg_update_tree")
+       import; type(c_ptr), value :: h; type(omg_tree_desc), intent(in) :: t
+     end function omg_update_tree
+     integer(c_int) function omg_free_space_setup(h, fft_lvl, r_min, n_kernel, dr) bind(C, name="omg_free_space_setup")
+       import; type(c_ptr), value :: h; integer(c_int), value :: fft_lvl
+       real(c_double), intent(in) :: r_min(3), dr(3); integer(c_int), intent(in) :: n_kernel(3)
+     end function omg_free_space_setup
+     integer(c_int) function omg_free_space_solve(h, rhs_fac) bind(C, name="omg_free_space_solve")
+       import; type(c_ptr), value :: h; real(c_double), value :: rhs_fac
+     end function omg_free_space_solve
+     integer(c_int) function omg_get_bc_plane(h, id, nb, bc_type, plane) bind(C, name="omg_get_bc_plane")
+       import; type(c_ptr), value :: h; integer(c_int), value :: id, nb
+       integer(c_int), intent(out) :: bc_type; real(c_double), intent(out) :: plane(*)
+     end function omg_get_bc_plane
      integer(c_int) function omg_nccl_unique_id(uid) bind(C, name="omg_nccl_unique_id")
        import; character(kind=c_char) :: uid(128)
      end function omg_nccl_unique_id
@@ -118,6 +132,8 @@ module m_gpu_multigrid
      type(c_ptr) :: handle = c_null_ptr
      logical     :: resident = .false.   !< .true.: the host brackets its own cc accesses with mg_gpu_push/pull
      real(dp)    :: lambda = 0.0_dp      !< helmholtz / vhelmholtz / ahelmholtz lambda (module globals in the reference)
+     logical     :: free_initialized = .false.   !< type(mg_free_bc_t) of src/m_free_space.f90:9-22: what the host keeps of it
+     integer     :: free_fft_lvl = -1
   end type gpu_state_t
 
   type(gpu_state_t), save :: gpu   !< one tree per process, like the reference's module-level timers
@@ -128,6 +144,7 @@ module m_gpu_multigrid
   public :: diffusion_solve, diffusion_solve_vcoeff, diffusion_solve_acoeff
   public :: mg_gpu_copy_size, mg_gpu_copy_to_tree, mg_gpu_copy_from_tree
   public :: mg_fill_ghost_cells_lvl, mg_fill_ghost_cells, mg_restrict_lvl, mg_restrict, mg_prolong
+  public :: mg_gpu_update_tree, mg_poisson_free_3d
 
 contains
 
@@ -149,9 +166,35 @@ contains
   !> into omg_tree_desc, creates the device mirror on `device` and, with several ranks, the NCCL communicator
   !> (the unique id is broadcast over mg%comm -- the only MPI call the GPU path keeps).
   subroutine mg_gpu_attach(mg, device)
+    type(mg_t), intent(inout), target :: mg
+    integer, intent(in)               :: device
+    call hand_over_tree(mg, device, .false.)
+  end subroutine mg_gpu_attach
+
+  !> On-device regrid / re-partition: the host has changed the tree of an attached mg_t (mg_add_children +
+  !> mg_set_neighbors_lvl + mg_set_refinement_boundaries, src/m_build_tree.f90:296-367; mg_load_balance,
+  !> src/m_load_balance.f90:71-136; cc arrays of new boxes allocated by the caller).  Boxes that exist before and after
+  !> keep their device data (omg_update_tree); new boxes start from zero.  In drop-in mode the host arrays are pushed
+  !> before and pulled after, so that boxes which change owner take all their variables along.
+  subroutine mg_gpu_update_tree(mg)
+    type(mg_t), intent(inout), target :: mg
+    integer :: iv
+    if (.not. c_associated(gpu%handle)) error stop "mg_gpu_update_tree: call mg_gpu_attach first"
+    call hand_over_tree(mg, 0, .true.)
+    gpu%free_initialized = .false.
+    if (.not. gpu%resident) then
+       call push_params(mg)
+       do iv = 1, mg_num_vars + mg%n_extra_vars
+          call mg_gpu_pull(mg, iv, iv == mg_iphi .or. iv >= mg_iveps)
+       end do
+    end if
+  end subroutine mg_gpu_update_tree
+
+  subroutine hand_over_tree(mg, device, update)
     use mpi
     type(mg_t), intent(inout), target :: mg
     integer, intent(in)               :: device
+    logical, intent(in)               :: update
     type(omg_tree_desc)               :: t
     integer(c_int32_t), allocatable, target :: rank(:), lvl(:), ix(:, :), parent(:), children(:, :)
     integer(c_int32_t), allocatable, target :: neighbors(:, :), lvl_ptr(:), lvl_ids(:), bsl(:)
@@ -204,6 +247,10 @@ contains
        if (omg_create(int(device, c_int), gpu%handle) /= 0) &
             error stop "mg_gpu_attach: no CUDA device available (there is no CPU fallback)"
     end if
+    if (update) then
+       call check(omg_update_tree(gpu%handle, t), "omg_update_tree")   ! keeps the communicator, renews the pool mappings
+       return
+    end if
     call check(omg_set_tree(gpu%handle, t), "omg_set_tree")
 
     if (mg%n_cpu > 1) then
@@ -211,7 +258,7 @@ contains
        call mpi_bcast(uid, 128, MPI_CHARACTER, 0, mg%comm, ierr)
        call check(omg_comm_init(gpu%handle, uid, int(mg%my_rank, c_int), int(mg%n_cpu, c_int)), "omg_comm_init")
     end if
-  end subroutine mg_gpu_attach
+  end subroutine hand_over_tree
 
   !> Call from / instead of mg_deallocate_storage (src/m_allocate_storage.f90:14-47)
   subroutine mg_gpu_detach()
@@ -532,6 +579,111 @@ contains
     integer, intent(in)       :: order
     call diffusion_common(mg, mg_ahelmholtz, dt, order, max_res)
   end subroutine diffusion_solve_acoeff
+
+  !> Same interface as src/m_free_space.f90:36-50.  The FFT level is chosen as there (:75-86); the coarse free-space
+  !> solve, the Dirichlet planes of all levels and the initial guess are made on the device (omg_free_space_setup builds
+  !> the kernel createKernel would build, omg_free_space_solve replaces :140-180), the rest is the reference's sequence
+  !> of level-wide calls (:183-206).
+  subroutine mg_poisson_free_3d(mg, new_rhs, max_fft_frac, fmgcycle, max_res)
+    type(mg_t), intent(inout)       :: mg
+    logical, intent(in)             :: new_rhs, fmgcycle
+    real(dp), intent(in)            :: max_fft_frac
+    real(dp), intent(out), optional :: max_res
+    real(dp), parameter             :: rhs_fac = -1 / (4 * acos(-1.0_dp))
+    integer                         :: lvl, fft_lvl, n, nb, id, nc, bc_type
+    integer(c_int)                  :: nk(3)
+    integer(i8)                     :: n_lvl, n_total
+    logical                         :: new_fft_grid
+    real(c_double)                  :: res
+    real(dp), allocatable           :: plane(:, :)
+
+    if (.not. gpu%free_initialized .and. .not. new_rhs) &
+         error stop "mg_poisson_free_3d: first call requires new_rhs = .true."
+    if (mg%geometry_type /= mg_cartesian) error stop "mg_poisson_free_3d: Cartesian 3D geometry required"
+    if (mg%operator_type /= mg_laplacian) error stop "mg_poisson_free_3d: laplacian operator required"
+
+    n_total = mg_number_of_unknowns(mg)
+    do lvl = mg_highest_uniform_lvl(mg), mg%lowest_lvl+1, -1
+       n_lvl = size(mg%lvls(lvl)%ids) * int(mg%box_size**3, i8)
+       if (n_lvl <= max_fft_frac * n_total) exit
+    end do
+    fft_lvl      = lvl
+    new_fft_grid = (.not. gpu%free_initialized .or. gpu%free_fft_lvl /= fft_lvl)
+
+    ! the boundary planes live on the device from here on
+    do n = 1, mg_num_neighbors
+       nullify(mg%bc(n, mg_iphi)%boundary_cond)
+       mg%bc(n, mg_iphi)%bc_type = mg_bc_dirichlet
+    end do
+    call sync_in(mg)
+
+    if (new_fft_grid) then
+       gpu%free_initialized = .false.
+       gpu%free_fft_lvl     = fft_lvl
+       do lvl = mg%highest_lvl, fft_lvl+1, -1
+          call check(omg_restrict_lvl(gpu%handle, mg_irhs, lvl), "mg_poisson_free_3d")
+       end do
+       ! createKernel('F', nx(1), nx(3), nx(3), ...) of the reference (:119), nx = domain size + 2
+       nk = [mg%domain_size_lvl(1, fft_lvl), mg%domain_size_lvl(3, fft_lvl), mg%domain_size_lvl(3, fft_lvl)] + 2
+       call check(omg_free_space_setup(gpu%handle, fft_lvl, mg%r_min, nk, mg%dr(:, fft_lvl)), "mg_poisson_free_3d")
+    end if
+
+    if (new_rhs) then
+       call check(omg_free_space_solve(gpu%handle, rhs_fac), "mg_poisson_free_3d")
+       ! what mg_phi_bc_store (:170) leaves behind: the face types, and in drop-in mode the planes in the ghost cells of mg_irhs
+       do lvl = mg%lowest_lvl, mg%highest_lvl
+          nc = mg%box_size_lvl(lvl)
+          if (allocated(plane)) deallocate(plane)
+          allocate(plane(nc, nc))
+          do n = 1, size(mg%lvls(lvl)%ids)
+             id = mg%lvls(lvl)%ids(n)
+             do nb = 1, mg_num_neighbors
+                if (mg%boxes(id)%neighbors(nb) >= mg_no_box) cycle
+                mg%boxes(id)%neighbors(nb) = mg_bc_dirichlet
+                if (.not. gpu%resident .and. mg%boxes(id)%rank == mg%my_rank) then
+                   call check(omg_get_bc_plane(gpu%handle, id, nb, bc_type, plane), "mg_poisson_free_3d")
+                   call box_set_face(mg%boxes(id), nb, nc, mg_irhs, plane)
+                end if
+             end do
+          end do
+       end do
+       mg%phi_bc_data_stored = .true.
+       do lvl = fft_lvl, mg%lowest_lvl+1, -1
+          call check(omg_restrict_lvl(gpu%handle, mg_iphi, lvl), "mg_poisson_free_3d")
+       end do
+       do lvl = fft_lvl, mg%highest_lvl-1
+          call check(omg_prolong(gpu%handle, lvl, mg_iphi, mg_iphi, 0), "mg_poisson_free_3d")
+          call check(omg_fill_ghost_cells_lvl(gpu%handle, lvl+1, mg_iphi), "mg_poisson_free_3d")
+       end do
+       gpu%free_initialized = .true.
+    end if
+
+    if (fft_lvl < mg%highest_lvl) then
+       if (fmgcycle) then
+          call check(omg_fas_fmg(gpu%handle, 1, merge(1, 0, present(max_res)), res), "mg_poisson_free_3d")
+       else
+          call check(omg_fas_vcycle(gpu%handle, 0, 0, 1, merge(1, 0, present(max_res)), res), "mg_poisson_free_3d")
+       end if
+       if (present(max_res)) max_res = res
+    else if (present(max_res)) then
+       max_res = 0.0_dp
+    end if
+    call sync_out(mg)
+  end subroutine mg_poisson_free_3d
+
+  !> box_set_gc of src/m_ghost_cells.f90:622-663 for one face
+  subroutine box_set_face(box, nb, nc, iv, plane)
+    type(mg_box_t), intent(inout) :: box
+    integer, intent(in)           :: nb, nc, iv
+    real(dp), intent(in)          :: plane(nc, nc)
+    integer                       :: g
+    g = merge(0, nc + 1, mg_neighb_low(nb))
+    select case (mg_neighb_dim(nb))
+    case (1); box%cc(g, 1:nc, 1:nc, iv) = plane
+    case (2); box%cc(1:nc, g, 1:nc, iv) = plane
+    case (3); box%cc(1:nc, 1:nc, g, iv) = plane
+    end select
+  end subroutine box_set_face
 
   !> Doubles a buffer of the two routines below holds: owned leaves (or all owned boxes), nc**3 or (nc+2)**3 per box
   integer(c_int64_t) function mg_gpu_copy_size(leaves_only, with_ghosts)
