@@ -126,6 +126,8 @@ struct omg_handle {
   bool gz[OMG_NLVL];
   // options
   int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1, ring_order = 0, ring_fused = 0;
+  // cluster tail (k_tail_cluster): CTAs per cluster (0 = single-CTA tail only) and the level size it takes
+  int tail_cluster = 8, tail_cluster_cells = 262144, tail_cluster_always = 0;
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
@@ -198,6 +200,12 @@ inline bool has_children(const omg_handle* h, int id) { return h->children[(size
 
 // tail group: the coarsest levels, while they are small and live on one rank (the reference keeps
 // everything below first_normal_lvl on one rank, src/m_load_balance.f90:79-81)
+// the cluster tail serves GSRB on even box sizes (the other smoothers synchronise inside a CTA)
+bool cluster_tail_ok(const omg_handle* h) {
+  if (h->tail_cluster < 2 || h->params.smoother_type != 2) return false;
+  for (const LevelHost& L : h->levels) if (L.nc & 1) return false;
+  return true;
+}
 void compute_tail(omg_handle* h) {
   bool still = true; int owner = -1;
   for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
@@ -210,7 +218,7 @@ void compute_tail(omg_handle* h) {
       if (!one_rank) fail("Multiple CPUs for coarse grid (not implemented yet)");   // m_multigrid.f90:197-200
       L.tail = true;
     } else {
-      still = still && one_rank && cells <= h->tail_cells && lvl < h->highest;
+      still = still && one_rank && cells <= std::max(h->tail_cells, cluster_tail_ok(h) ? h->tail_cluster_cells : 0) && lvl < h->highest;
       L.tail = still;
     }
   }
@@ -466,6 +474,7 @@ void sync_meta(omg_handle* h) {
   for (LevelHost& L : h->levels) any = any || L.meta_dirty;
   if (!any) return;
   cudaStream_t s = h->stream;
+  if (h->params_dirty) compute_tail(h);      // the tail group depends on the smoother (cluster tail: GSRB only)
   for (LevelHost& L : h->levels) {
     LevelDev& D = L.dev;
     if (L.meta_dirty) {
@@ -837,7 +846,14 @@ void exec_steps(omg_handle* h, Program& P) {
         // stage the tail levels in shared memory when all four variables of all of them fit (option "tail_smem")
         int n_stage = 0; size_t bytes = 0;
         if (h->tail_smem) for (LevelHost& L : h->levels) { if (!L.tail) break; ++n_stage; bytes += (size_t)4 * L.nb * L.dev.bs * sizeof(double) + (size_t)32 * L.nb * sizeof(int); }   // variables + face / box tables (k_tail)
-        omgk::tail(h->d_levels.p, PD, P.d_ops.p + st.a, st.b, h->d_scal.p, n_stage, bytes, s); h->launches++;
+        // levels beyond the single-CTA limit in the tail group: only the cluster interpreter can take them
+        bool big = false;
+        for (LevelHost& L : h->levels) { if (!L.tail) break; if ((long)L.nb * L.nc * L.nc * L.nc > h->tail_cells) big = true; }
+        if (big || (h->tail_cluster >= 2 && h->tail_cluster_always && cluster_tail_ok(h))) {
+          if (!cluster_tail_ok(h) || !omgk::tail_cluster(h->d_levels.p, PD, P.d_ops.p + st.a, st.b, h->d_scal.p, h->tail_cluster, s))
+            fail("cluster tail: launch failed (option tail_cluster = 0 switches it off)");
+        } else omgk::tail(h->d_levels.p, PD, P.d_ops.p + st.a, st.b, h->d_scal.p, n_stage, bytes, s);
+        h->launches++;
       } break;
       case S_ZERO_PHI: {
         LevelHost& L = h->L(st.l);
@@ -1861,6 +1877,9 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "bnd_first_boxes") h->bnd_first_boxes = value;
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
     else if (k == "tail_cells") { h->tail_cells = value; if (h->have_tree) compute_tail(h); }
+    else if (k == "tail_cluster") { h->tail_cluster = value; if (h->have_tree) compute_tail(h); h->params_dirty = true; }
+    else if (k == "tail_cluster_cells") { h->tail_cluster_cells = value; if (h->have_tree) compute_tail(h); h->params_dirty = true; }
+    else if (k == "tail_cluster_always") h->tail_cluster_always = value;
     else fail("unknown option " + k);
     invalidate_programs(h);
   });

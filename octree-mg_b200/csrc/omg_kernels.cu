@@ -384,6 +384,17 @@ void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_o
   }
   k_tail<<<1, 1024, stage_bytes, s>>>(levels, P, ops, n_ops, scal, n_stage);
 }
+bool tail_cluster(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, int cluster, cudaStream_t s) {
+  if (!n_ops) return true;
+  if (cluster < 2 || cluster > 8) return false;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)cluster); cfg.blockDim = dim3(1024); cfg.dynamicSmemBytes = 0; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, k_tail_cluster, levels, P, ops, n_ops, scal) == cudaSuccess;
+}
 void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, int shell, cudaStream_t s) {
   if (n) k_unpack<<<n, kThreads, 0, s>>>(L, iv, boxes, stage, with_faces, shell);
 }

@@ -14,7 +14,8 @@ struct TailOp { int type, l, a, b; };   // l: index into the device level array 
 enum ScalSlot : int {
   SCAL_COARSE_REL = 0, SCAL_COARSE_ABS = 1, SCAL_COARSE_ITERS = 2, SCAL_MEAN = 3, SCAL_MAXRES = 4,
   SCAL_RESHIST = 8,            // SCAL_RESHIST + n: max_res of cycle n inside omg_fas_vcycles
-  SCAL_COUNT = 8 + 256
+  SCAL_TEAM = 8 + 256,         // SCAL_TEAM + r: scratch of CTA r of the cluster tail (cluster-wide max)
+  SCAL_COUNT = 8 + 256 + 16
 };
 
 namespace omgk {
@@ -51,6 +52,8 @@ void div_scalar(double* acc, double denom, cudaStream_t s);
 // n_stage > 0: the first n_stage levels are staged in shared memory for the launch (stage_bytes = 4 * 8 * their cells)
 void tail(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, int n_stage, size_t stage_bytes,
           cudaStream_t s);
+// the same op list run by a thread-block cluster of `cluster` CTAs (k_tail_cluster); false: launch failed (caller falls back)
+bool tail_cluster(const LevelDev* levels, const ParamsDev& P, const TailOp* ops, int n_ops, double* scal, int cluster, cudaStream_t s);
 // shell = 1: slabs of (nc+2)^3 with the ghost shell (the reference's cc arrays); 0: interior cells only, nc^3
 void unpack(const LevelDev& L, int iv, const int* boxes, int n, const double* stage, int with_faces, int shell, cudaStream_t s);
 void pack(const LevelDev& L, const ParamsDev& P, int iv, const int* boxes, int n, double* stage, int ghost_mode, int shell, cudaStream_t s);

@@ -20,28 +20,63 @@
 
 namespace {
 
+// Who runs the interpreter: one CTA (k_tail), or a thread-block cluster of CTAs that share the levels through L2 and meet
+// at the hardware cluster barrier (k_tail_cluster: the levels of up to tail_cluster_cells cells, i.e. also the 8- and
+// 64-box levels of a box-16 hierarchy, whose operations are launch-latency bound as separate kernels).
+struct CtaTeam {
+  __device__ static int tid() { return threadIdx.x; }
+  __device__ static int nthr() { return blockDim.x; }
+  __device__ static void sync() { __syncthreads(); }
+  __device__ static double max(double v, double* red, double*) { return block_max(v, red); }
+};
+#ifndef OMG_HOST_EMU
+struct ClusterTeam {
+  __device__ static unsigned rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+  __device__ static unsigned size() { unsigned r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
+  __device__ static int tid() { return (int)(rank() * blockDim.x + threadIdx.x); }
+  __device__ static int nthr() { return (int)(size() * blockDim.x); }
+  // release / acquire at cluster scope: global-memory writes of every CTA before the barrier are visible after it
+  __device__ static void sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  }
+  // cluster-wide max through a scratch array in global memory (one slot per CTA); the same value on every thread
+  __device__ static double max(double v, double* red, double* scratch) {
+    const double m = block_max(v, red);
+    if (threadIdx.x == 0) scratch[rank()] = m;
+    sync();
+    double r = 0.0;
+    const unsigned n = size();
+    for (unsigned q = 0; q < n; ++q) r = fmax(r, __ldcg(scratch + q));
+    sync();
+    return r;
+  }
+};
+#endif
+
 // ------------------------------------------------------------------ tail interpreter ---------
-template <int OP>
+template <int OP, class TEAM = CtaTeam>
 __device__ void tail_smooth(const LevelDev& L, const ParamsDev& P, int colour, int tid, int nthr) {
   if (L.simple && P.smoother == 2) {
     simple_smooth<OP>(L, P, colour, tid, nthr);
   } else if (P.smoother == 1) {   // mg_smoother_gs
     for (int b = 0; b < L.nb; ++b) do_gs_snapshot(L, P, b, tid, nthr);
-    __syncthreads();
-    for (int b = 0; b < L.nb; ++b) do_gs_sweep<OP>(L, P, b, tid, nthr);
+    TEAM::sync();
+    for (int b = 0; b < L.nb; ++b) do_gs_sweep<OP>(L, P, b, tid, nthr);     // (single CTA only: synchronises inside)
   } else if (L.nc & 1) {   // odd box size: Jacobi between boxes, see do_smooth_staged
     for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 0, tid, nthr);
-    __syncthreads();
+    TEAM::sync();
     for (int b = 0; b < L.nb; ++b) do_smooth_staged<OP>(L, P, b, colour, 1, tid, nthr);
   } else {
     for (int b = 0; b < L.nb; ++b) do_smooth<OP>(L, P, b, colour, tid, nthr);
   }
 }
 
-template <int OP>
+template <int OP, class TEAM = CtaTeam>
 __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailOp* __restrict__ ops, int n_ops,
                          double* scal, double* red) {
-  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int tid = TEAM::tid(), nthr = TEAM::nthr();
+  double* scratch = scal + SCAL_TEAM;
   for (int o = 0; o < n_ops; ++o) {
     const TailOp op = ops[o];
     const LevelDev& L = levels[op.l];
@@ -50,13 +85,13 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
     const bool fast = L.simple && P.smoother == 2;
     switch (op.type) {
       case TOP_SMOOTH:
-        tail_smooth<OP>(L, P, op.a, tid, nthr);
+        tail_smooth<OP, TEAM>(L, P, op.a, tid, nthr);
         break;
       case TOP_RESID: {
         double m = 0.0;
         if (fast) m = simple_resid<OP>(L, P, tid, nthr);
         else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
-        if (op.a >= 0) { m = block_max(m, red); if (tid == 0) atomic_max_nonneg(&scal[op.a], m); }
+        if (op.a >= 0) { m = block_max(m, red); if (threadIdx.x == 0) atomic_max_nonneg(&scal[op.a], m); }   // one atomic per CTA
       } break;
       case TOP_RESTRICT: {
         const LevelDev& Lc = levels[op.l - 1];
@@ -88,17 +123,17 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
         double m = 0.0;
         if (fast) m = simple_resid<OP>(L, P, tid, nthr);
         else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
-        const double init_res = block_max(m, red);
+        const double init_res = TEAM::max(m, red, scratch);
         int it = 0;
         for (int i = 1; i <= op.b; ++i) {
           for (int n = 1; n <= op.a; ++n) {
-            tail_smooth<OP>(L, P, (n - 1) & 1, tid, nthr);
-            __syncthreads();
+            tail_smooth<OP, TEAM>(L, P, (n - 1) & 1, tid, nthr);
+            TEAM::sync();
           }
           m = 0.0;
           if (fast) m = simple_resid<OP>(L, P, tid, nthr);
           else for (int b = 0; b < L.nb; ++b) m = fmax(m, do_resid<OP>(L, P, b, tid, nthr));
-          const double res = block_max(m, red);
+          const double res = TEAM::max(m, red, scratch);
           it = i;
           if (res < scal[SCAL_COARSE_REL] * init_res || res < scal[SCAL_COARSE_ABS]) break;
         }
@@ -106,7 +141,7 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
       } break;
       default: break;
     }
-    __syncthreads();
+    TEAM::sync();
   }
 }
 
@@ -181,5 +216,22 @@ __global__ void __launch_bounds__(1024) k_tail(const LevelDev* __restrict__ leve
     }
   }
 }
+
+#ifndef OMG_HOST_EMU
+// The same interpreter run by a thread-block cluster (up to 8 CTAs x 1024 threads): no staging -- the levels stay in global
+// memory, i.e. in L2 --, one hardware cluster barrier (~0.2 us) between operations.  GSRB and even box sizes only (the
+// lexicographic and the odd-size smoothers synchronise inside a CTA); the host falls back to k_tail otherwise.
+__global__ void __launch_bounds__(1024) k_tail_cluster(const LevelDev* __restrict__ levels, const __grid_constant__ ParamsDev P,
+                                                       const TailOp* __restrict__ ops, int n_ops, double* scal) {
+  __shared__ double red[32];
+  __shared__ TailOp sops[kMaxStageOps];
+  if (n_ops <= kMaxStageOps) {
+    for (int i = threadIdx.x; i < n_ops; i += blockDim.x) sops[i] = ops[i];
+    __syncthreads();
+    ops = sops;
+  }
+  OMG_SWITCH_OP(P.op, (tail_run<OP, ClusterTeam>(levels, P, ops, n_ops, scal, red)));
+}
+#endif
 
 }  // namespace
