@@ -315,6 +315,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-strong", action="store_true", help="skip the 1024^3 strong-scaling record")
     ap.add_argument("--no-parity", action="store_true", help="skip the bitwise parity check of the timed data plane")
+    ap.add_argument("--no-configs", action="store_true", help="skip the record of BASELINE configs[3] (vlaplacian / Helmholtz 512^3, Neumann BC)")
     ap.add_argument("--strong-cells", type=int, default=1024, help="total domain of the strong-scaling record (BASELINE configs[4])")
     ap.add_argument("--parity-cells", type=int, default=256, help="total domain of the parity check")
     ap.add_argument("--cpu-budget", type=float, default=150.0, help="seconds the CPU arm may take (it cuts its cycle count, then its domain, to fit)")
@@ -540,6 +541,28 @@ def main():
         parity = parity_check(om, P, args.parity_cells, args.box, rank, world, local, dist, collapse)
         phase("parity check done")
 
+    # --- BASELINE configs[3]: variable-coefficient Laplacian and Helmholtz, 512^3, Neumann BC: V(2,2) cycles and one FMG cycle
+    other = None
+    if world == 1 and not args.no_configs and args.op == "laplacian" and not args.no_strong:
+        other = {}
+        for name, oc in (("vlaplacian", P.mg_vlaplacian), ("helmholtz", P.mg_helmholtz)):
+            phase("configs[3]: %s" % name)
+            a2 = argparse.Namespace(**vars(args)); a2.op = name
+            omg2 = build_performance_mg(om, P, a2, dims, oc, rank, world, local, dist, collapse)
+            k3 = max(3, min(args.steps, 10))
+            _, ms3 = timed_cycles(omg2, a2, barrier, dist, k3, 3)
+            r3, _ = omg2.fas_vcycles(1, want_res=True)
+            omg2._gck(omg2.G.omg_set_var_const(omg2.gpu, P.mg_iphi, -20, 20, 0.0, 0))
+            omg2.mg_fas_fmg(False)                                   # builds the FMG program and its graph
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            rf = omg2.mg_fas_fmg(False)                              # FMG solve from phi = 0 (returns max_res: synchronises)
+            t_fmg = (time.perf_counter() - t0) * 1e3
+            other[name + "_%d" % dims[0]] = {"ms_per_vcycle": ms3 / k3, "value": dof * k3 / (ms3 * 1e-3) / 1e9, "unit": "GDOF/s", "steps": k3,
+                                           "max_res_after": r3[0], "fmg_ms": t_fmg, "fmg_max_res": rf,
+                                           "bc": "Neumann 0" + (" + Dirichlet on -x" if name == "vlaplacian" else ""), "eps": 1.0, "lambda": 1.0 if name == "helmholtz" else None}
+            omg2.mg_deallocate_storage()
+            del omg2
     if rank != 0:
         finish(world, dist)
         return
@@ -556,7 +579,7 @@ def main():
             "clocks": clocks, "residuals": res, "max_res_after": res_after,
             # tests/test_performance.f90:90-92: n_boxes * box_size^3 (all boxes on all levels) per microsecond
             "ref_style_unknowns_per_us": n_boxes_total * args.box ** 3 / (ms / args.steps * 1e3),
-            "timers_min_max_s": timers_minmax, "strong": strong, "parity_check": parity}
+            "timers_min_max_s": timers_minmax, "strong": strong, "parity_check": parity, "configs": other}
     print(json.dumps(line))
     finish(world, dist)
     if parity is not None and not parity.get("bitwise", False):

@@ -127,7 +127,7 @@ struct omg_handle {
   // options
   int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1, ring_order = 0, ring_fused = 0;
   // cluster tail (k_tail_cluster): CTAs per cluster (0 = single-CTA tail only) and the level size it takes
-  int tail_cluster = 8, tail_cluster_cells = 262144, tail_cluster_always = 0;
+  int tail_cluster = 0, tail_cluster_cells = 262144, tail_cluster_always = 0;   // off: measured slower (profiles/r02j_summary.txt)
   // staging
   double* h_stage[2] = {nullptr, nullptr};
   double* d_stage[2] = {nullptr, nullptr};
