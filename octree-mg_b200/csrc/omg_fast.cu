@@ -150,7 +150,7 @@ struct SmoothSmem : TileSmem<NC, KT> {
 };
 
 template <int NC, int KT, int NE>
-__global__ void __launch_bounds__(kThreads, NE == 3 ? 4 : NE ? 3 : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
+__global__ void __launch_bounds__(kThreads, NE == 3 ? (KT == NC && NC == 16 ? 2 : 4) : NE ? (KT < NC && NC == 16 ? 5 : 3) : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
                                                                           const __grid_constant__ ParamsDev P, int colour,
                                                                           const int* __restrict__ boxlist, int fused_put, int pdl) {
   constexpr int HX = NC / 2;
@@ -1210,7 +1210,8 @@ bool dispatch_stencil_h(const LevelDev& L, const LevelDev& Lc, const ParamsDev& 
 template <int MODE, bool HELM>
 bool dispatch_stencil_vc(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   if (!L.var[4] || !L.faces[4]) return false;
-  if (L.nc == 16) return launch_stencil<16, 16, MODE, HELM, 2, 1>(L, Lc, P, nboxes, maxslot, s);
+  static const int vc_kt = env_int("OMG_VC_STENCIL_KT", 16);   // tuning: half-box tiles (8): 46 KB of shared memory instead of 91
+  if (L.nc == 16) return vc_kt == 8 ? launch_stencil<16, 8, MODE, HELM, 3, 1>(L, Lc, P, nboxes, maxslot, s) : launch_stencil<16, 16, MODE, HELM, 2, 1>(L, Lc, P, nboxes, maxslot, s);
   if (L.nc == 32) return launch_stencil<32, 8, MODE, HELM, 1, 1>(L, Lc, P, nboxes, maxslot, s);
   return false;
 }
@@ -1218,6 +1219,8 @@ bool dispatch_stencil_vc(const LevelDev& L, const LevelDev& Lc, const ParamsDev&
 template <int MODE>
 bool dispatch_stencil_aniso(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P, int nboxes, double* maxslot, cudaStream_t s) {
   for (int e = 0; e < 3; ++e) if (!L.var[4 + e] || !L.faces[4 + e]) return false;
+  static const int ah_kt = env_int("OMG_AH_STENCIL_KT", 8);
+  if (L.nc == 16 && ah_kt == 16) return launch_stencil<16, 16, MODE, true, 1, 3>(L, Lc, P, nboxes, maxslot, s);
   if (L.nc == 16) return launch_stencil<16, 8, MODE, true, 2, 3>(L, Lc, P, nboxes, maxslot, s);
   if (L.nc == 32) return launch_stencil<32, 4, MODE, true, 1, 3>(L, Lc, P, nboxes, maxslot, s);
   return false;
@@ -1455,12 +1458,15 @@ bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, co
   if (list && n == 0) return true;
   if (P.op == OP_VLPL || P.op == OP_VHELMH) {
     if (!L.var[4] || !L.faces[4]) return false;
-    if (L.nc == 16) return launch_smooth<16, 16, 1>(L, P, colour, list, n, fused, s);
+    static const int vc_kt = env_int("OMG_VC_KT", 16);         // tuning: half-box tiles (8) give 5 CTAs per SM instead of 3
+    if (L.nc == 16) return vc_kt == 8 ? launch_smooth<16, 8, 1>(L, P, colour, list, n, fused, s) : launch_smooth<16, 16, 1>(L, P, colour, list, n, fused, s);
     if (L.nc == 32) return launch_smooth<32, 8, 1>(L, P, colour, list, n, fused, s);
     return false;
   }
   if (P.op == OP_AHELMH) {
     for (int e = 0; e < 3; ++e) if (!L.var[4 + e] || !L.faces[4 + e]) return false;
+    static const int ah_kt = env_int("OMG_AH_KT", 16);       // whole-box tiles: 1.06 vs 1.25 ms per half-sweep (profiles/r02s_summary.txt)
+    if (L.nc == 16 && ah_kt == 16) return launch_smooth<16, 16, 3>(L, P, colour, list, n, fused, s);
     if (L.nc == 16) return launch_smooth<16, 8, 3>(L, P, colour, list, n, fused, s);     // half-box tiles: 4 x 12 KB of shared memory
     if (L.nc == 32) return launch_smooth<32, 8, 3>(L, P, colour, list, n, fused, s);
     return false;
