@@ -5,9 +5,10 @@ With GSRB the reference's results do not depend on the box decomposition (SURVEY
 update reads only the other colour, ghost cells are refreshed after every half-sweep), so this
 numpy multigrid must agree BITWISE with oracle/omg_oracle.cpp for every box size and rank count.
 It shares no code and no data structure with the C++ oracle; agreement pins the oracle's box / ghost /
-tree bookkeeping.  Laplacian and Helmholtz, Dirichlet / Neumann / continuous constants or Dirichlet
-planes.  Follows src/m_multigrid.f90:84-243 (cycle), m_laplacian.f90:52-114,155-195 (smoother, operator),
-m_restrict.f90:165-214, m_prolong.f90:159-240, m_ghost_cells.f90:665-766 (bc_to_gc).
+tree bookkeeping.  Laplacian and Helmholtz, and (eps given) the variable-coefficient operators vlaplacian / vhelmholtz /
+ahelmholtz; Dirichlet / Neumann / continuous constants or Dirichlet planes.  Follows src/m_multigrid.f90:84-243 (cycle),
+m_laplacian.f90:52-114,155-195 (smoother, operator), m_vlaplacian.f90:51-189, m_vhelmholtz.f90:61-205,
+m_ahelmholtz.f90:69-237, m_restrict.f90:165-214, m_prolong.f90:159-240, m_ghost_cells.f90:665-766 (bc_to_gc).
 """
 import numpy as np
 
@@ -16,9 +17,11 @@ BC_DIRICHLET, BC_NEUMANN, BC_CONTINUOUS = -10, -11, -12
 
 class GlobalMG:
     def __init__(self, n, dr1, bc_fn, lam=0.0, helmholtz=False, n_down=2, n_up=2, coarsest=2,
-                 max_coarse_cycles=1000, res_abs=1e-8, res_rel=1e-8):
+                 max_coarse_cycles=1000, res_abs=1e-8, res_rel=1e-8, eps_fn=None):
         """n: cells per direction on the finest level (cube); dr1: its spacing;
-        bc_fn(lvl_index, nb, n_lvl, dr_lvl) -> (bc_type, plane[n_lvl, n_lvl] or scalar)."""
+        bc_fn(lvl_index, nb, n_lvl, dr_lvl) -> (bc_type, plane[n_lvl, n_lvl] or scalar);
+        eps_fn(lvl_index, n_lvl, dr_lvl) -> list of 1 (vlaplacian / vhelmholtz) or 3 (ahelmholtz) coefficient arrays of shape
+        (n_lvl + 2,) * 3 indexed [k, j, i], ghost layer included (host data in the reference)."""
         self.lam, self.helm = lam, helmholtz
         self.n_down, self.n_up = n_down, n_up
         self.max_coarse_cycles, self.res_abs, self.res_rel = max_coarse_cycles, res_abs, res_rel
@@ -33,6 +36,22 @@ class GlobalMG:
         self.old = [z(m) for m in self.ns]
         self.res = [z(m) for m in self.ns]
         self.bc = [[bc_fn(l, nb, self.ns[l], self.drs[l]) for nb in range(1, 7)] for l in range(self.nl)]
+        self.eps = None if eps_fn is None else [eps_fn(l, self.ns[l], self.drs[l]) for l in range(self.nl)]
+
+    # the six neighbours of the interior cells in the reference's face order (-x, +x, -y, +y, -z, +z)
+    @staticmethod
+    def _nb(a):
+        return [a[1:-1, 1:-1, :-2], a[1:-1, 1:-1, 2:], a[1:-1, :-2, 1:-1], a[1:-1, 2:, 1:-1], a[:-2, 1:-1, 1:-1], a[2:, 1:-1, 1:-1]]
+
+    def _coeff_pairs(self, l):
+        """a0[f], a[f]: the cell's own coefficient and the neighbour's, per face (aniso: array d serves direction d)"""
+        e = self.eps[l]
+        a0, a = [], []
+        for f in range(6):
+            arr = e[f // 2] if len(e) == 3 else e[0]
+            a0.append(arr[1:-1, 1:-1, 1:-1])
+            a.append(self._nb(arr)[f])
+        return a0, a
 
     # ghost fill = physical boundaries only (bc_to_gc)
     def fill(self, l, a=None):
@@ -57,6 +76,8 @@ class GlobalMG:
         return ((i + j + k) & 1) == colour
 
     def smooth(self, l, n_cycle):
+        if self.eps is not None:
+            return self._smooth_vc(l, n_cycle)
         n, p, r = self.ns[l], self.phi[l], self.rhs[l]
         idr2 = 1 / (self.drs[l] * self.drs[l])
         s3 = idr2 + idr2 + idr2
@@ -69,7 +90,40 @@ class GlobalMG:
             c[m] = new[m]
             self.fill(l)
 
+    def _smooth_vc(self, l, n_cycle):
+        """box_gs_vlpl / box_gs_vhelmh / box_gs_ahelmh: c_f = 2 a0 a / (a0 + a) idr2, phi = (sum c_f u_f - rhs) / (sum c_f [+ lambda])"""
+        n, p, r = self.ns[l], self.phi[l], self.rhs[l]
+        idr2 = 1 / (self.drs[l] * self.drs[l])
+        a0, a = self._coeff_pairs(l)
+        c = [2 * a0[f] * a[f] / (a0[f] + a[f]) * idr2 for f in range(6)]
+        sc = 0.0
+        for f in range(6):
+            sc = sc + c[f]
+        den = sc + self.lam if self.helm else sc
+        for cnt in range(1, 2 * n_cycle + 1):
+            m = self._colour_mask(n, (cnt - 1) & 1)
+            u = self._nb(p)
+            scu = 0.0
+            for f in range(6):
+                scu = scu + c[f] * u[f]
+            new = (scu - r[1:-1, 1:-1, 1:-1]) / den
+            ctr = p[1:-1, 1:-1, 1:-1]
+            ctr[m] = new[m]
+            self.fill(l)
+
+    def _op_vc(self, l):
+        p = self.phi[l]
+        idr2 = 1 / (self.drs[l] * self.drs[l])
+        a0, a = self._coeff_pairs(l)
+        u, u0 = self._nb(p), p[1:-1, 1:-1, 1:-1]
+        s = 0.0
+        for f in range(6):
+            s = s + 2 * idr2 * a0[f] * a[f] / (a0[f] + a[f]) * (u[f] - u0)
+        return s - self.lam * u0 if self.helm else s
+
     def op(self, l):
+        if self.eps is not None:
+            return self._op_vc(l)
         p = self.phi[l]
         idr2 = 1 / (self.drs[l] * self.drs[l])
         c = p[1:-1, 1:-1, 1:-1]

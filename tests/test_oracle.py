@@ -103,6 +103,37 @@ def test_global_array_restatement_agrees_bitwise(oracle, helm):
     assert np.array_equal(global_phi(mg), G.phi[0][1:-1, 1:-1, 1:-1])
 
 
+@pytest.mark.parametrize("op,lam,bc", [(P.mg_vlaplacian, 0.0, "callback"), (P.mg_vhelmholtz, 0.75, "mixed"), (P.mg_ahelmholtz, 1.25, "mixed")])
+def test_global_array_restatement_variable_coefficients(oracle, op, lam, bc):
+    """the same for vlaplacian / vhelmholtz / ahelmholtz: harmonic-mean face coefficients in the reference's expression
+    order on one global array per level (coefficient arrays, ghost layer included, from the same analytic fields), bit
+    for bit against the box-structured oracle (V-cycles and FMG)"""
+    from oracle.global_array_mg import GlobalMG
+    n, box = 32, 8
+    mg, _ = P.uniform_problem(oracle.OracleMg, n, box, operator_type=op, lam=lam, bc=bc)
+
+    def bc_fn(l, nb, n_l, dr_l):
+        if bc == "callback":
+            return P.mg_bc_dirichlet, P.face_plane(P.solution, np.zeros(3), np.full(3, dr_l), n_l, nb)
+        return (P.mg_bc_dirichlet, 0.25) if nb == 1 else (P.mg_bc_neumann, 0.5)
+
+    def eps_fn(l, n_l, dr_l):
+        x = (np.arange(n_l + 2) - 0.5) * dr_l           # ghost layer included; exact in binary for these sizes
+        Z, Y, X = np.meshgrid(x, x, x, indexing="ij")
+        return [P.eps_field(X, Y, Z, d) for d in range(P.n_eps(op))]
+    G = GlobalMG(n, 1.0 / n, bc_fn, lam=lam, helmholtz=(op != P.mg_vlaplacian), eps_fn=eps_fn)
+    # the oracle's coefficient arrays are these very fields (checked on the finest level, interior and ghost layer)
+    for id_ in mg.ids(mg.highest_lvl):
+        X, Y, Z = P.cell_coords(mg, id_, mg.highest_lvl)
+        for d in range(P.n_eps(op)):
+            assert np.array_equal(mg.cc(id_)[P.mg_iveps - 1 + d], P.eps_field(X, Y, Z, d))
+    G.rhs[0][1:-1, 1:-1, 1:-1] = global_phi(mg, iv=P.mg_irhs)
+    h_box = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False)
+    h_glob = [G.fmg(False), G.fmg(True), G.vcycle(), G.vcycle()]
+    assert h_box == h_glob
+    assert np.array_equal(global_phi(mg), G.phi[0][1:-1, 1:-1, 1:-1])
+
+
 def test_global_array_neumann_constants(oracle):
     from oracle.global_array_mg import GlobalMG
     n, box = 32, 16
