@@ -410,7 +410,8 @@ __global__ void __launch_bounds__(kThreads, NE == 3 ? (KT == NC && NC == 16 ? 2 
       a[3] = j < NC - 1 ? S.E[EY].B[kk][j + 1][m] : S.E[EY].yhi[kk][m];
       a[4] = kk > 0 ? S.E[EZ].B[kk - 1][j][m] : S.E[EZ].zlo[j][m];
       a[5] = kk < KT - 1 ? S.E[EZ].B[kk + 1][j][m] : S.E[EZ].zhi[j][m];
-      Ag[(size_t)k0 * NC * HX + idx] = gs_vlpl_value(L.idr2, u, a0, a, rhs[q], P.lambda, P.op != OP_VLPL);
+      Ag[(size_t)k0 * NC * HX + idx] = P.coeff_math ? gs_vlpl_value_tol(L.idr2, u, a0, a, rhs[q], P.lambda, P.op != OP_VLPL)
+                                                    : gs_vlpl_value(L.idr2, u, a0, a, rhs[q], P.lambda, P.op != OP_VLPL);
     } else {
       Ag[(size_t)k0 * NC * HX + idx] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - rhs[q]);
     }
@@ -1130,7 +1131,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_stencil_fast(const __grid_cons
 #pragma unroll
           for (int f = 0; f < 6; ++f) a0[f] = ue[0][e];
         }
-        lap = vlpl_value(L.idr2, u0, n, a0, an);
+        lap = P.coeff_math ? vlpl_value_tol(L.idr2, u0, n, a0, an) : vlpl_value(L.idr2, u0, n, a0, an);
       } else {
         lap = idx2 * (n[0] + n[1] - 2 * u0) + idy2 * (n[2] + n[3] - 2 * u0) + idz2 * (n[4] + n[5] - 2 * u0);
       }

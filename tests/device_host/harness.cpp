@@ -418,6 +418,17 @@ int dh_fused_proto(int nc, int nbx, int nby, int nbz, int tx, int ty, int S, con
   return bad;
 }
 // the batched division against the compiler's (host build: exact-reciprocal seed instead of MUFU.RCP64H)
+// tolerance mode of the coefficient kernels: the six reciprocals by batch inversion (omg_device.cuh recip6) and the two
+// per-cell functions built on it, against the exact ones; returns the number of groups that fell back to exact divisions
+int dh_recip6(const double* d, double* out, int n) {
+  int fallbacks = 0;
+  for (int i = 0; i + 6 <= n; i += 6) if (!recip6(d + i, out + i)) { ++fallbacks; for (int f = 0; f < 6; ++f) out[i + f] = 1.0 / d[i + f]; }
+  return fallbacks;
+}
+void dh_coeff_values(const double* idr2, const double* u, const double* a0, const double* a, double u0, double rhs, double lambda, double* out) {
+  out[0] = vlpl_value(idr2, u0, u, a0, a);          out[1] = vlpl_value_tol(idr2, u0, u, a0, a);
+  out[2] = gs_vlpl_value(idr2, u, a0, a, rhs, lambda, true); out[3] = gs_vlpl_value_tol(idr2, u, a0, a, rhs, lambda, true);
+}
 int dh_ddiv(const double* a, const double* b, double* out, int n) {
   for (int i = 0; i + 6 <= n; i += 6) ddiv_batch<6>(a + i, b + i, out + i);
   return 0;

@@ -29,6 +29,8 @@ def devhost():
     L.dh_compare_simple.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
     L.dh_compare_prolong.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_ulonglong]
     L.dh_ddiv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    L.dh_recip6.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    L.dh_coeff_values.argtypes = [C.c_void_p] * 4 + [C.c_double] * 3 + [C.c_void_p]
     return L
 
 
@@ -82,6 +84,28 @@ def test_batched_division_logic_on_host(devhost):
         ref = a / b
     same = (out.view(np.uint64) == ref.view(np.uint64)) | (np.isnan(out) & np.isnan(ref))
     assert same.all(), (a[~same][:5], b[~same][:5], out[~same][:5], ref[~same][:5])
+
+
+def test_tolerance_mode_batch_inversion_is_accurate_to_a_few_ulp(devhost):
+    """option coeff_math = 1 (NOT bitwise): six reciprocals from one division + 15 multiplications; each within a few ulp of
+    1 / d, the per-cell operator and smoother values within 1e-14 relative of the exact ones; products outside the normal
+    range fall back to exact divisions"""
+    rng = np.random.default_rng(5)
+    d = np.exp(rng.uniform(np.log(1e-6), np.log(1e6), 6 * 4000))
+    out = np.empty_like(d)
+    assert devhost.dh_recip6(d.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), d.size) == 0
+    rel = np.abs(out * d - 1.0)
+    assert rel.max() < 8 * np.finfo(float).eps, rel.max()
+    big = np.full(6, 1e60)
+    assert devhost.dh_recip6(big.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), 6) == 1 and np.array_equal(out[:6], 1.0 / big)
+    idr2 = np.array([1024.0, 1024.0, 4096.0])
+    for _ in range(200):
+        u = rng.normal(size=6); a0 = np.full(6, np.exp(rng.uniform(-2, 2))); a = np.exp(rng.uniform(-2, 2, 6))
+        res = np.zeros(4)
+        devhost.dh_coeff_values(*(x.ctypes.data_as(C.c_void_p) for x in (idr2, u, a0, a)), float(rng.normal()), float(rng.normal()), 1.5,
+                                res.ctypes.data_as(C.c_void_p))
+        scale = 2 * idr2.sum() * a.max() * (np.abs(u).max() + 1)
+        assert abs(res[0] - res[1]) <= 1e-14 * scale and abs(res[2] - res[3]) <= 1e-14 * (np.abs(u).max() + 1), res
 
 
 BC_OF = {"dirichlet0": ([-10] * 6, [0.0] * 6), "neumann0": ([-11] * 6, [0.0] * 6),

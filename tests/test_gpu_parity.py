@@ -279,6 +279,30 @@ def test_fast_kernels_variable_coefficient(oracle, product, op, bc, lam, n, box)
     assert_fast_path(mg, general_ok="small")
 
 
+@pytest.mark.parametrize("op,bc,lam,n,box", [
+    (P.mg_vlaplacian, "mixed", 0.0, 64, 16),
+    (P.mg_vhelmholtz, "neumann0", 1.0, (64, 32, 32), 16),
+    (P.mg_ahelmholtz, "mixed", 0.75, 64, 16),
+    (P.mg_vlaplacian, "callback", 0.0, 64, 32),
+])
+def test_tolerance_mode_of_the_coefficient_kernels(oracle, product, op, bc, lam, n, box):
+    """option coeff_math = 1: the TMA-staged coefficient kernels take their six face coefficients from one division by
+    batch inversion (omg_device.cuh recip6).  NOT bitwise: held to the north-star tolerances instead -- per-cycle residuals
+    within 1e-10 relative (plus the rounding floor of a converged residual), final solution within 1e-12 * |phi|"""
+    orc, _ = P.uniform_problem(oracle.OracleMg, n, box, operator_type=op, bc=bc, lam=lam)
+    mg, _ = P.uniform_problem(product.Mg, n, box, operator_type=op, bc=bc, lam=lam)
+    mg.set_option("coeff_math", 1)
+    h_o = P.run_cycles(orc, 2, True) + P.run_cycles(orc, 3, False)
+    h_g = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 3, False)
+    dr = np.asarray(mg.dr(mg.highest_lvl))
+    floor = 64 * np.finfo(float).eps * 2.0 * float(np.sum(1.0 / dr ** 2)) * 4.0       # eps up to ~2, |phi| ~ 1
+    for a, b in zip(h_o, h_g):
+        assert abs(a - b) <= 1e-10 * abs(a) + floor, (h_o, h_g, floor)
+    diff = state_diff(orc, mg, variables=(1,), ghosts_of=())
+    assert diff["phi"][0] <= 1e-12 * max(diff["phi"][1], 1e-300), diff
+    assert_fast_path(mg, general_ok="small")
+
+
 @pytest.mark.parametrize("ring", [0, 2])
 @pytest.mark.parametrize("case", ["uniform_callback", "helmholtz_mixed", "noncubic_dirichlet0", "amr"])
 def test_ring_smoother_options(oracle, product, case, ring):
