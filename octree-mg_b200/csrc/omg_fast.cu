@@ -15,6 +15,9 @@
 namespace {
 
 constexpr int kThreads = 256;
+#ifndef OMG_VC_MINB
+#define OMG_VC_MINB 3      // resident CTAs per SM the one-coefficient smoother is compiled for
+#endif
 
 #ifndef OMG_HOST_EMU   // tests/device_host/fast_emu.cpp supplies host stand-ins for this block and the three macros below
 // ---- mbarrier / TMA bulk-copy PTX ---------------------------------------------------------------
@@ -150,7 +153,7 @@ struct SmoothSmem : TileSmem<NC, KT> {
 };
 
 template <int NC, int KT, int NE>
-__global__ void __launch_bounds__(kThreads, NE == 3 ? (KT == NC && NC == 16 ? 2 : 4) : NE ? (KT < NC && NC == 16 ? 5 : 3) : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
+__global__ void __launch_bounds__(kThreads, NE == 3 ? (KT == NC && NC == 16 ? 2 : 4) : NE ? (KT < NC && NC == 16 ? 5 : OMG_VC_MINB) : (NC == 16 ? 5 : 4)) k_smooth_lpl_fast(const __grid_constant__ LevelDev L,
                                                                           const __grid_constant__ ParamsDev P, int colour,
                                                                           const int* __restrict__ boxlist, int fused_put, int pdl) {
   constexpr int HX = NC / 2;
