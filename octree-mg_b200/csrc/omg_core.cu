@@ -463,7 +463,7 @@ bool fused_level(const omg_handle* h, const LevelHost& L) {
   if (!h->comm || !h->p2p || !h->fused || !L.xg.any || !L.xg.shared || L.rb_remote_any || L.tail) return false;
   if (L.nc != 16 && L.nc != 32) return false;
   const int op = h->params.operator_type;
-  if (op < 1 || op > 4 || h->params.smoother_type != 2 || !h->fast_kernels) return false;
+  if (op < 1 || op > 5 || h->params.smoother_type != 2 || !h->fast_kernels) return false;
   return h->n_cpu <= 9;                       // PutDev holds up to 8 peers
 }
 

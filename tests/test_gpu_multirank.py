@@ -155,10 +155,12 @@ def test_gs_smoother_ranks(oracle, product, n_cpu):
     assert_state_equal(orc, mg)
 
 
-def test_fast_variable_coefficient_ranks(oracle, product):
-    """vlaplacian at box 16 on 4 ranks: fast kernels with phi faces from the plane pool and eps faces from the stored pool"""
-    orc, _ = P.uniform_problem(oracle.OracleMg, (64, 32, 32), 16, operator_type=P.mg_vlaplacian, bc="mixed", n_cpu=4)
-    mg, _ = P.uniform_problem(group_cls(product, 4), (64, 32, 32), 16, operator_type=P.mg_vlaplacian, bc="mixed")
+@pytest.mark.parametrize("op,lam", [(P.mg_vlaplacian, 0.0), (P.mg_ahelmholtz, 0.75)])
+def test_fast_variable_coefficient_ranks(oracle, product, op, lam):
+    """vlaplacian / ahelmholtz at box 16 on 4 ranks: fast kernels (with the in-kernel halo exchange) with phi faces from the
+    plane pool and eps faces from the stored pool"""
+    orc, _ = P.uniform_problem(oracle.OracleMg, (64, 32, 32), 16, operator_type=op, bc="mixed", lam=lam, n_cpu=4)
+    mg, _ = P.uniform_problem(group_cls(product, 4), (64, 32, 32), 16, operator_type=op, bc="mixed", lam=lam)
     check(P.run_cycles(orc, 2, True), P.run_cycles(mg, 2, True))
     check(P.run_cycles(orc, 2, False), P.run_cycles(mg, 2, False))
     assert_state_equal(orc, mg)
