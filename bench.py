@@ -243,7 +243,7 @@ def parity_check(om, P, n, box, rank, world, local, dist, collapse):
 
 def build_performance_mg(om, P, args, dims, op, rank, world, local, dist, collapse):
     """tests/test_performance.f90:51-66 without host cc arrays (the run is device-resident)"""
-    mg = om.Mg(op, P.mg_smoother_gsrb, n_extra_vars=P.n_eps(op), n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
+    mg = om.Mg(op, P.mg_smoother_gs if getattr(args, "smoother", "gsrb") == "gs" else P.mg_smoother_gsrb, n_extra_vars=P.n_eps(op), n_cpu=world, my_rank=rank, device=local, gpu_resident=True)
     mg.set_int("host_cc", 0)
     if op in (P.mg_helmholtz, P.mg_vhelmholtz, P.mg_ahelmholtz):
         mg.set_lambda(1.0)
@@ -325,6 +325,8 @@ def main():
     ap.add_argument("--no-fast", action="store_true", help="general-path kernels only")
     ap.add_argument("--store-res", action="store_true", help="write the residual of every level to mg_ires as the reference does "
                     "(default: resident mode without it -- nothing on the device reads it and this host never pulls it)")
+    ap.add_argument("--smoother", default="gsrb", choices=["gsrb", "gs"], help="mg_smoother_gsrb (test_performance.f90, the headline) or the "
+                    "reference's default mg_smoother_gs (lexicographic Gauss-Seidel inside each box); a side measurement, not the metric")
     ap.add_argument("--op", default="laplacian", choices=["laplacian", "vlaplacian", "helmholtz", "vhelmholtz", "ahelmholtz"],
                     help="operator (BASELINE.json configs[3]: vlaplacian / helmholtz with Neumann BC); default = the headline Laplacian")
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the TOTAL domain at n^3 instead of n^3 per GPU for the headline value")
@@ -338,7 +340,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dims = [args.n] * 3 if args.strong else domain_for(args.n, world)
     config = {"workload": workload_text(dims, args.box, args.max_res),
-              "n_cycle_down": 2, "n_cycle_up": 2, "smoother": "gsrb", "box_size": args.box, "domain": dims,
+              "n_cycle_down": 2, "n_cycle_up": 2, "smoother": args.smoother, "box_size": args.box, "domain": dims,
               "partition": "mg_load_balance (Morton-contiguous), %d rank(s)" % world,
               "l2": "inputs larger than L2 (4 x %.2f GB per GPU vs 126 MB)" % (dims[0] * dims[1] * dims[2] / world * 8 / 1e9)}
 

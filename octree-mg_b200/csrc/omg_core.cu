@@ -807,7 +807,11 @@ void exec_steps(omg_handle* h, Program& P) {
         const int* list = st.b == 1 ? L.d_bnd.p : st.b == 2 ? L.d_int.p : nullptr;
         const int nlist = st.b == 1 ? (int)L.h_bnd.size() : st.b == 2 ? (int)L.h_int.size() : 0;
         if (st.b && nlist == 0) break;
-        if (PD.smoother == 1) { omgk::smooth_gs(L.dev, PD, s); h->launches++; general(L); }
+        if (PD.smoother == 1) {   // mg_smoother_gs: ghost snapshot, then the in-box sweep (shared-memory staged where it applies)
+          omgk::gs_snapshot(L.dev, PD, s); h->launches++;
+          if (h->fast_kernels && L.nb && omgf::gs_sweep(L.dev, PD, s)) fast(L);
+          else { omgk::gs_sweep(L.dev, PD, s); general(L); }
+        }
         else if (h->fast_kernels && omgf::smooth(L.dev, PD, st.a, L.all_fast, st.b ? list : nullptr, nlist, 0, s)) fast(L);
         else { omgk::smooth(L.dev, PD, st.a, st.b ? list : nullptr, nlist, s); general(L); }
         h->launches++;

@@ -807,6 +807,89 @@ bool dispatch_smooth_ring(const LevelDev& L, const ParamsDev& P, int colour, con
   }
 }
 
+// =================================================================================================
+// mg_smoother_gs: lexicographic Gauss-Seidel inside one box (smooth_boxes / box_gs_lpl, src/m_laplacian.f90:64-84 and
+// m_helmholtz.f90:78-103 with the smoother type of m_multigrid.f90:380-410) against the ghost snapshot of
+// omgk::gs_snapshot.  One CTA per box: phi and rhs arrive by two bulk copies (the colour-split box is contiguous), the four
+// y / z ghost faces by a third, the two x ghosts of a column in registers.  Thread (j, k) owns the column of cells
+// (0..NC-1, j, k) and updates cell i = w - j - k of hyperplane w; the cells of a hyperplane have the colour w & 1, their six
+// neighbours the other one, and a lexicographic sweep only reads lower neighbours that are already new and upper ones that
+// are still old: the hyperplane order performs the same arithmetic on the same values (as do_gs_sweep, omg_ops.cuh).
+// Everything that depends on (j, k) alone -- which neighbour is a ghost, where it is stored -- is a per-thread constant
+// (base pointer + stride of the other colour + shift of i), so a step has no data-dependent branch besides "is my cell in
+// this hyperplane".  72 KB of shared memory: three boxes per SM.  Algorithmic traffic 24 B per cell + the snapshot.
+// =================================================================================================
+template <int NC>
+struct GsSmem {
+  static constexpr int HX = NC / 2;
+  double Ph[2][NC][NC][HX];
+  double R[2][NC][NC][HX];
+  double G[4][NC][NC];       // ghost faces y-, y+, z-, z+ as do_gs_snapshot stores them: [face][t2][t1]
+  uint64_t bar;
+};
+template <int NC>
+__global__ void __launch_bounds__(kThreads, NC == 16 ? 3 : 8) k_gs_sweep_fast(const __grid_constant__ LevelDev L) {
+  constexpr int HX = NC / 2, CS = NC * NC * HX, BOX = 2 * CS, PAIRS = NC * NC;
+  OMG_DYN_SMEM(smem_raw, 128);
+  GsSmem<NC>& S = *reinterpret_cast<GsSmem<NC>*>(smem_raw);
+  const int tid = threadIdx.x, b = blockIdx.x;
+  double* __restrict__ phi = L.var[0] + (size_t)b * L.bs;
+  const double* __restrict__ gh = L.faces[0] + (size_t)b * 6 * PAIRS;
+  if (tid == 0) {
+    mbar_init(&S.bar, 1);
+    mbar_arrive_expect_tx(&S.bar, (2 * BOX + 4 * PAIRS) * 8);
+    bulk_g2s(&S.Ph[0][0][0][0], phi, BOX * 8, &S.bar);
+    bulk_g2s(&S.R[0][0][0][0], L.var[1] + (size_t)b * L.bs, BOX * 8, &S.bar);
+    bulk_g2s(&S.G[0][0][0], gh + 2 * PAIRS, 4 * PAIRS * 8, &S.bar);
+  }
+  const double idx2 = L.idr2[0], idy2 = L.idr2[1], idz2 = L.idr2[2], fac = L.fac;
+  const bool act = tid < PAIRS;
+  const int j = act ? tid % NC : 0, k = act ? tid / NC : 0, s0 = j + k;
+  const double gx0 = act ? gh[k * NC + j] : 0.0, gx1 = act ? gh[PAIRS + k * NC + j] : 0.0;
+  // neighbour columns: value(i, colour oc) = base[oc * os + (i >> sh)]
+  double* const col = &S.Ph[0][k][j][0];
+  const double* const rcol = &S.R[0][k][j][0];
+  const double* const pyl = j > 0 ? col - HX : &S.G[0][k][0];
+  const double* const pyh = j < NC - 1 ? col + HX : &S.G[1][k][0];
+  const double* const pzl = k > 0 ? col - NC * HX : &S.G[2][j][0];
+  const double* const pzh = k < NC - 1 ? col + NC * HX : &S.G[3][j][0];
+  const int os_yl = j > 0 ? CS : 0, sh_yl = j > 0 ? 1 : 0;
+  const int os_yh = j < NC - 1 ? CS : 0, sh_yh = j < NC - 1 ? 1 : 0;
+  const int os_zl = k > 0 ? CS : 0, sh_zl = k > 0 ? 1 : 0;
+  const int os_zh = k < NC - 1 ? CS : 0, sh_zh = k < NC - 1 ? 1 : 0;
+  __syncthreads();
+  mbar_wait(&S.bar, 0);
+  for (int w = 0; w <= 3 * (NC - 1); ++w) {
+    const int i = w - s0;
+    if (act && i >= 0 && i < NC) {
+      const int c = w & 1, oc = c ^ 1, m = i >> 1;
+      const int il = (i > 0 ? i - 1 : 0) >> 1, ih = (i < NC - 1 ? i + 1 : NC - 1) >> 1;
+      const double a_xl = col[oc * CS + il], a_xh = col[oc * CS + ih];
+      const double ylo = pyl[oc * os_yl + (i >> sh_yl)], yhi = pyh[oc * os_yh + (i >> sh_yh)];
+      const double zlo = pzl[oc * os_zl + (i >> sh_zl)], zhi = pzh[oc * os_zh + (i >> sh_zh)];
+      const double r = rcol[c * CS + m];
+      const double xlo = i > 0 ? a_xl : gx0, xhi = i < NC - 1 ? a_xh : gx1;
+      col[c * CS + m] = fac * (idx2 * (xhi + xlo) + idy2 * (yhi + ylo) + idz2 * (zhi + zlo) - r);
+    }
+    __syncthreads();
+  }
+  fence_proxy_async();                // generic-proxy writes to Ph before the async proxy (TMA store) reads them
+  __syncthreads();
+  if (tid == 0) { bulk_s2g(phi, &S.Ph[0][0][0][0], BOX * 8); bulk_commit_wait_read(); }
+}
+template <int NC>
+bool launch_gs_sweep(const LevelDev& L, cudaStream_t s) {
+  static bool configured = false;
+  const size_t smem = sizeof(GsSmem<NC>);
+  auto kern = k_gs_sweep_fast<NC>;
+  if (!configured) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+    configured = true;
+  }
+  OMG_LAUNCH(kern, L.nb, smem, s, L);
+  return true;
+}
+
 // launch with the programmatic-stream-serialization attribute: the kernel may start before its predecessor in the stream
 // has finished and orders itself with pdl_sync()
 bool g_pdl = false;
@@ -1479,6 +1562,13 @@ bool smooth(const LevelDev& L, const ParamsDev& P, int colour, bool all_fast, co
   if (smooth_uses_ring(L, P, list ? n : L.nb)) return dispatch_smooth_ring(L, P, colour, list, n, fused, s);
   if (L.nc == 16) return launch_smooth<16, 16, false>(L, P, colour, list, n, fused, s);
   if (L.nc == 32) return launch_smooth<32, 8, false>(L, P, colour, list, n, fused, s);
+  return false;
+}
+bool gs_sweep(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
+  static const int on = env_int("OMG_GS_FAST", 1);          // 0: the general hyperplane sweep of omg_kernels.cu (A/B runs)
+  if (!on || L.nb == 0 || !L.faces[0] || (P.op != OP_LPL && P.op != OP_HELMH)) return false;
+  if (L.nc == 16) return launch_gs_sweep<16>(L, s);
+  if (L.nc == 8) return launch_gs_sweep<8>(L, s);
   return false;
 }
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s) {

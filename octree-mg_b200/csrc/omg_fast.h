@@ -26,6 +26,8 @@ bool smooth_applies(const LevelDev& L, const ParamsDev& P);   // would smooth() 
 // hold the partition-face boxes LAST: a persistent CTA that meets one waits for the peer's previous half-sweep to end, and
 // everything queued behind that tile waits with it (2 GPUs, r02n: 0.385 ms per half-sweep with the natural order)
 bool smooth_uses_ring(const LevelDev& L, const ParamsDev& P, int n);
+// mg_smoother_gs: the in-box lexicographic sweep after omgk::gs_snapshot (box 16 / 8, Laplacian / Helmholtz)
+bool gs_sweep(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s);
 bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s);
 bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s);

@@ -294,11 +294,15 @@ void smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, 
   if (nb == 0) return;
   OMG_SWITCH_OP(P.op, (k_smooth<OP><<<nb, kThreads, 0, s>>>(L, P, colour, list)));
 }
-void smooth_gs(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
+void gs_snapshot(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
   if (L.nb == 0) return;
   k_gs_snapshot<<<L.nb, kThreads, 0, s>>>(L, P);
+}
+void gs_sweep(const LevelDev& L, const ParamsDev& P, cudaStream_t s) {
+  if (L.nb == 0) return;
   OMG_SWITCH_OP(P.op, (k_smooth_gs<OP><<<L.nb, kThreads, 0, s>>>(L, P)));
 }
+void smooth_gs(const LevelDev& L, const ParamsDev& P, cudaStream_t s) { gs_snapshot(L, P, s); gs_sweep(L, P, s); }
 void resid(const LevelDev& L, const ParamsDev& P, double* maxslot, cudaStream_t s) {
   if (L.nb == 0) return;
   OMG_SWITCH_OP(P.op, (k_resid<OP><<<L.nb, kThreads, 0, s>>>(L, P, maxslot)));

@@ -22,6 +22,8 @@ namespace omgk {
 void smooth(const LevelDev& L, const ParamsDev& P, int colour, const int* list, int n, cudaStream_t s);   // list: subset of boxes or null
 // mg_smoother_gs: ghost snapshot into L.faces[0] + in-box lexicographic sweep (two launches)
 void smooth_gs(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
+void gs_snapshot(const LevelDev& L, const ParamsDev& P, cudaStream_t s);   // the two halves of smooth_gs
+void gs_sweep(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
 void resid(const LevelDev& L, const ParamsDev& P, double* maxslot, cudaStream_t s);
 void restrict2(const LevelDev& Lf, const LevelDev& Lc, int iv0, int iv1, cudaStream_t s);
 void crhs(const LevelDev& L, const ParamsDev& P, cudaStream_t s);

@@ -401,6 +401,34 @@ int ranks_case(int nc, int nbx, int nby, int nbz, int n_ranks, int bnd_first, co
   return bad;
 }
 
+
+// mg_smoother_gs: ghost snapshot + a plain lexicographic sweep (i fastest, the reference's loop order) against the
+// shared-memory staged hyperplane sweep k_gs_sweep_fast (one CTA per box), two sweeps
+template <int OP>
+int gs_level(int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda, uint64_t seed) {
+  HostLevel G, F;
+  build_level(G, nc, nbx, nby, nbz, bc_types, 0.01);
+  build_level(F, nc, nbx, nby, nbz, bc_types, 0.01);
+  ParamsDev P = params(OP, lambda, bc_types, bc_values);
+  P.smoother = 1;
+  set_fac(G, OP, lambda); set_fac(F, OP, lambda);
+  randomise(G, seed);
+  copy_data(F, G);
+  std::vector<double> snap_g((size_t)G.L.nb * 6 * nc * nc, -7.0), snap_f(snap_g);
+  G.L.faces[0] = snap_g.data(); F.L.faces[0] = snap_f.data();
+  int bad = 0;
+  for (int n = 0; n < 2; ++n) {
+    for (int b = 0; b < G.L.nb; ++b) do_gs_snapshot(G.L, P, b, 0, 1);
+    for (int b = 0; b < G.L.nb; ++b)
+      for (int k = 0; k < nc; ++k) for (int j = 0; j < nc; ++j) for (int i = 0; i < nc; ++i)
+        G.L.var[0][(size_t)b * G.L.bs + cidx(G.L, i, j, k)] = gs_at<OP, GM_STORED>(G.L, P, b, i, j, k);
+    for (int b = 0; b < F.L.nb; ++b) do_gs_snapshot(F.L, P, b, 0, 1);
+    if (!omgf::gs_sweep(F.L, P, nullptr)) return -1;
+    bad += differing(G, F) ? 1 : 0;
+  }
+  return bad;
+}
+
 }  // namespace
 
 extern "C" {
@@ -413,6 +441,10 @@ int fe_ranks(int op, int nc, int nbx, int nby, int nbz, int n_ranks, int bnd_fir
     case OP_HELMH: return ranks_case<OP_HELMH>(nc, nbx, nby, nbz, n_ranks, bnd_first, bc_types, bc_values, lambda, seed);
     default: return ranks_case<OP_VHELMH>(nc, nbx, nby, nbz, n_ranks, bnd_first, bc_types, bc_values, lambda, seed);
   }
+}
+int fe_gs_level(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda, unsigned long long seed) {
+  return op == OP_HELMH ? gs_level<OP_HELMH>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed)
+                        : gs_level<OP_LPL>(nc, nbx, nby, nbz, bc_types, bc_values, lambda, seed);
 }
 // mismatching comparisons between the fast kernels and the general path (0 = same bits); -1: a kernel did not apply
 int fe_one_level(int op, int nc, int nbx, int nby, int nbz, const int* bc_types, const double* bc_values, double lambda,

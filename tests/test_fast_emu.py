@@ -142,3 +142,20 @@ def test_tail_interpreter_runs_a_vcycle_like_the_general_path(emu, op, lam, plan
         assert emu.fe_violations() == 0
     finally:
         emu.dh_set_planes(0)
+
+
+@pytest.mark.parametrize("planes", [0, 1, 2])
+@pytest.mark.parametrize("op,lam", [(1, 0.0), (3, 2.5)])
+@pytest.mark.parametrize("nc", [16, 8])
+def test_gs_sweep_kernel_matches_general_path(emu, nc, op, lam, planes):
+    """mg_smoother_gs: k_gs_sweep_fast (box staged in shared memory, hyperplanes i + j + k = const, one thread per (j, k)
+    column) against a plain lexicographic sweep of gs_at over the same ghost snapshot: same bits after two sweeps."""
+    emu.fe_gs_level.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
+    emu.dh_set_planes(planes)
+    try:
+        for types, shape in zip(BC_SETS, [(2, 2, 1), (1, 2, 2), (2, 1, 2), (3, 1, 1)]):
+            bad = emu.fe_gs_level(op, nc, *shape, six(C.c_int, types), six(C.c_double, BC_VALUES), lam, 97 * nc + op)
+            assert bad == 0, (types, shape)
+        assert emu.fe_violations() == 0
+    finally:
+        emu.dh_set_planes(0)
