@@ -166,6 +166,16 @@ int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* ou
 /* Self-test of the branch-free fp64 division the variable-coefficient kernels use (omg_device.cuh: ddiv_batch):
  * out[i] = a[i] / b[i] on the device, batched = 1 through ddiv_batch<6>, 0 through the compiler's `/`; host arrays. */
 int omg_debug_ddiv(int device, const double* a, const double* b, double* out, int64_t n, int batched);
+/* omg_debug_ddiv without any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and result as omg_debug_ddiv (host arrays); the device staging that omg_debug_ddiv allocates lives in a
+ * file-scope __device__ array of 3 x OMG_DDIV_STATIC_MAX doubles (6 MiB per GPU that loads the library, held until exit).
+ * n > OMG_DDIV_STATIC_MAX is rejected (return 2, message in err); 1 = CUDA error, 3 = bad argument.  Calls no cudaMalloc,
+ * cudaFree or allocating library routine.  All calls share the array, which keeps the last call's contents (nothing in it
+ * has to start at zero): calls that overlap on one GPU race -- serialise them.  err (may be NULL) receives a message of at
+ * most err_cap bytes. */
+#define OMG_DDIV_STATIC_MAX 262144
+int omg_debug_ddiv_static(int device, const double* a, const double* b, double* out, int64_t n, int batched, char* err, int err_cap);
 
 /* ---- multi-GPU (replaces mg_comm_init + sort_and_transfer_buffers, src/m_communication.f90) */
 int omg_nccl_unique_id(char out[128]);

@@ -108,6 +108,7 @@ def _declare(G, H):
     G.omg_apply_op.argtypes = [vp, ci]
     G.omg_diffusion_set_rhs.argtypes = [vp, cd, cd]
     G.omg_debug_ddiv.argtypes = [ci, vp, vp, vp, C.c_int64, ci]
+    G.omg_debug_ddiv_static.argtypes = [ci, vp, vp, vp, C.c_int64, ci, C.c_char_p, ci]
     G.omg_nccl_unique_id.argtypes = [C.c_char_p]
     G.omg_comm_init.argtypes = [vp, C.c_char_p, ci, ci]
     G.omg_comm_init_local.argtypes = [C.POINTER(vp), ci]

@@ -434,3 +434,61 @@ extern "C" int omg_debug_ddiv(int device, const double* a, const double* b, doub
   cudaFree(da); cudaFree(db); cudaFree(dc);
   return rc;
 }
+
+// ---- omg_debug_ddiv_static: omg_debug_ddiv without any allocation -----------------------------------------------
+// No counterpart in the reference; added for callers that may not call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The device staging of a, b and the
+// quotients -- three cudaMalloc'ed arrays in omg_debug_ddiv -- lives in one file-scope array instead:
+// 3 x OMG_DDIV_STATIC_MAX doubles = 6 MiB, held by every GPU that loads the library until the process exits.
+// g_ddiv_scratch is a host-side stand-in in host code, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device with that device current.  Nothing in the array has to start at zero (every
+// element the kernel reads or the host copies back was written earlier in the same call; the rest keeps the last
+// call's contents).  All calls share the array: calls that overlap on one GPU race, the caller serialises them.
+#include <cstdio>
+#include <mutex>
+#ifndef OMG_DDIV_STATIC_MAX
+#define OMG_DDIV_STATIC_MAX 262144   /* = include/omg_gpu.h */
+#endif
+namespace {
+static __device__ __align__(256) double g_ddiv_scratch[3 * OMG_DDIV_STATIC_MAX];
+constexpr int kMaxDevices = 64;
+double* g_ddiv_ptr[kMaxDevices] = {};
+std::mutex g_ddiv_mutex;
+void put_error(char* err, int cap, const char* fmt, long long a = 0, long long b = 0) {
+  if (err && cap > 0) std::snprintf(err, (size_t)cap, fmt, a, b);
+}
+}  // namespace
+extern "C" int omg_debug_ddiv_static(int device, const double* a, const double* b, double* out, int64_t n, int batched,
+                                     char* err, int err_cap) {
+  if (err && err_cap > 0) err[0] = 0;
+  if (n <= 0) return 0;
+  if (n > OMG_DDIV_STATIC_MAX) {
+    put_error(err, err_cap, "omg_debug_ddiv_static: n = %lld exceeds the static scratch (at most %lld elements per call)", (long long)n, (long long)OMG_DDIV_STATIC_MAX);
+    return 2;
+  }
+  if (!a || !b || !out) { put_error(err, err_cap, "omg_debug_ddiv_static: null array"); return 3; }
+  if (device < 0 || device >= kMaxDevices) { put_error(err, err_cap, "omg_debug_ddiv_static: device %lld out of range", device); return 3; }
+  std::lock_guard<std::mutex> lock(g_ddiv_mutex);      // one call at a time from this process (other processes: see above)
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) { put_error(err, err_cap, "omg_debug_ddiv_static: cudaSetDevice failed (%lld)", (long long)e); return 1; }
+  if (!g_ddiv_ptr[device]) {                           // set-up, once per device, with that device current
+    double* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_ddiv_scratch);
+    if (e != cudaSuccess || !p) { put_error(err, err_cap, "omg_debug_ddiv_static: cudaGetSymbolAddress failed (%lld)", (long long)e); return 1; }
+    g_ddiv_ptr[device] = p;
+  }
+  double* const da = g_ddiv_ptr[device];
+  double* const db = da + OMG_DDIV_STATIC_MAX;
+  double* const dc = db + OMG_DDIV_STATIC_MAX;
+  if ((e = cudaMemcpy(da, a, n * 8, cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(db, b, n * 8, cudaMemcpyHostToDevice)) != cudaSuccess) {
+    put_error(err, err_cap, "omg_debug_ddiv_static: copy to the device failed (%lld)", (long long)e); return 1;
+  }
+  const long long thr = (n + 5) / 6;
+  k_debug_ddiv<<<(unsigned)((thr + 255) / 256), 256>>>(da, db, dc, n, batched);
+  if ((e = cudaGetLastError()) != cudaSuccess) { put_error(err, err_cap, "omg_debug_ddiv_static: launch failed (%lld)", (long long)e); return 1; }
+  if ((e = cudaMemcpy(out, dc, n * 8, cudaMemcpyDeviceToHost)) != cudaSuccess) {
+    put_error(err, err_cap, "omg_debug_ddiv_static: copy from the device failed (%lld)", (long long)e); return 1;
+  }
+  return 0;
+}
