@@ -316,6 +316,7 @@ def main():
     ap.add_argument("--no-strong", action="store_true", help="skip the 1024^3 strong-scaling record")
     ap.add_argument("--no-parity", action="store_true", help="skip the bitwise parity check of the timed data plane")
     ap.add_argument("--no-configs", action="store_true", help="skip the record of BASELINE configs[3] (vlaplacian / Helmholtz 512^3, Neumann BC)")
+    ap.add_argument("--no-amr", action="store_true", help="skip the record of BASELINE configs[2] (AMR grid of tests/test_refinement.f90, scaled up)")
     ap.add_argument("--strong-cells", type=int, default=1024, help="total domain of the strong-scaling record (BASELINE configs[4])")
     ap.add_argument("--parity-cells", type=int, default=256, help="total domain of the parity check")
     ap.add_argument("--cpu-budget", type=float, default=150.0, help="seconds the CPU arm may take (it cuts its cycle count, then its domain, to fit)")
@@ -565,6 +566,32 @@ def main():
                                            "bc": "Neumann 0" + (" + Dirichlet on -x" if name == "vlaplacian" else ""), "eps": 1.0, "lambda": 1.0 if name == "helmholtz" else None}
             omg2.mg_deallocate_storage()
             del omg2
+    # --- BASELINE configs[2]: tests/test_refinement.f90 scaled up: 256^3 base grid + 3 levels of centred refinement
+    # (4096 boxes of 16^3 on each of the 4 levels, refinement-boundary ghost interpolation on every fine level), Dirichlet 0
+    if other is not None and not args.no_amr:
+        phase("configs[2]: AMR")
+        mg3 = om.Mg(P.mg_laplacian, P.mg_smoother_gsrb, device=local, gpu_resident=True)
+        mg3.set_int("host_cc", 0)
+        for nb in range(1, 7):
+            mg3.set_bc(nb, P.mg_iphi, P.mg_bc_dirichlet, 0.0)
+        mg3.mg_set_methods()
+        P.build_amr_tree(mg3, 4, [256] * 3, args.box, [1.0 / 256] * 3)
+        mg3._gck(mg3.G.omg_set_var_const(mg3.gpu, P.mg_irhs, -20, 20, 1.0, 1))
+        mg3._gck(mg3.G.omg_set_var_const(mg3.gpu, P.mg_iphi, -20, 20, 0.0, 0))
+        mg3.set_option("store_fine_residual", 1 if args.store_res else 0)
+        unknowns = int(mg3.mg_number_of_unknowns())
+        cells_all = sum(len(mg3.ids(l)) for l in range(1, mg3.highest_lvl + 1)) * args.box ** 3
+        k2 = max(3, min(args.steps, 10))
+        l0, f0 = mg3.stat("launches"), mg3.stat("fast_launches")
+        _, ms2 = timed_cycles(mg3, args, barrier, dist, k2, 3)
+        r2, _ = mg3.fas_vcycles(1, want_res=True)
+        other["refinement_256_4lvl"] = {"ms_per_vcycle": ms2 / k2, "value": unknowns * k2 / (ms2 * 1e-3) / 1e9, "unit": "GDOF/s (leaf cells)",
+                                        "unknowns": unknowns, "cells_on_levels_1_to_4": cells_all,
+                                        "gcells_per_s_all_levels": cells_all * k2 / (ms2 * 1e-3) / 1e9, "steps": k2, "max_res_after": r2[0],
+                                        "boxes_per_level": [len(mg3.ids(l)) for l in range(mg3.lowest_lvl, mg3.highest_lvl + 1)],
+                                        "launches": mg3.stat("launches") - l0, "fast_launches": mg3.stat("fast_launches") - f0}
+        mg3.mg_deallocate_storage()
+        del mg3
     if rank != 0:
         finish(world, dist)
         return

@@ -134,6 +134,61 @@ def test_global_array_restatement_variable_coefficients(oracle, op, lam, bc):
     assert np.array_equal(global_phi(mg), G.phi[0][1:-1, 1:-1, 1:-1])
 
 
+
+@pytest.mark.parametrize("helm,box,bc", [(False, 8, "callback"), (True, 16, "mixed"), (False, 4, "mixed")])
+def test_global_array_restatement_gs_smoother(oracle, helm, box, bc):
+    """mg_smoother_gs, the reference's default: the result depends on the box size (a box reads its neighbours' values of
+    before the sweep), so the global-array restatement takes the box size and sweeps each box with plain nested loops:
+    bit for bit against the box-structured oracle, V-cycles and FMG"""
+    from oracle.global_array_mg import GlobalMG
+    n, lam = 32, (1.5 if helm else 0.0)
+    op = P.mg_helmholtz if helm else P.mg_laplacian
+    mg, _ = P.uniform_problem(oracle.OracleMg, n, box, operator_type=op, lam=lam, bc=bc, smoother=P.mg_smoother_gs)
+
+    def bc_fn(l, nb, n_l, dr_l):
+        if bc == "callback":
+            return P.mg_bc_dirichlet, P.face_plane(P.solution, np.zeros(3), np.full(3, dr_l), n_l, nb)
+        return (P.mg_bc_dirichlet, 0.25) if nb == 1 else (P.mg_bc_neumann, 0.5)
+    G = GlobalMG(n, 1.0 / n, bc_fn, lam=lam, helmholtz=helm, smoother="gs", box=box)
+    G.rhs[0][1:-1, 1:-1, 1:-1] = global_phi(mg, iv=P.mg_irhs)
+    h_box = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False)
+    h_glob = [G.fmg(False), G.fmg(True), G.vcycle(), G.vcycle()]
+    assert h_box == h_glob
+    assert np.array_equal(global_phi(mg), G.phi[0][1:-1, 1:-1, 1:-1])
+    # and it does depend on the box size: another decomposition gives other bits
+    G2 = GlobalMG(n, 1.0 / n, bc_fn, lam=lam, helmholtz=helm, smoother="gs", box=(8 if box != 8 else 16))
+    G2.rhs[0][...] = G.rhs[0]
+    assert G2.fmg(False) != h_glob[0]
+
+
+@pytest.mark.parametrize("smoother", ["gsrb", "gs"])
+def test_global_array_restatement_periodic_subtract_mean(oracle, smoother):
+    """fully periodic Laplacian with subtract_mean (src/m_multigrid.f90:245-294) on the global arrays.  The mean is a sum
+    whose association differs (box by box in the oracle, one numpy sum here): north-star tolerances instead of bits"""
+    from oracle.global_array_mg import GlobalMG
+    n, box = 32, 8
+    mg = oracle.OracleMg(P.mg_laplacian, P.mg_smoother_gs if smoother == "gs" else P.mg_smoother_gsrb)
+    mg.mg_set_methods()
+    mg.mg_build_rectangle([n] * 3, box, [1.0 / n] * 3, [0.0] * 3, [True] * 3)
+    mg.mg_load_balance()
+    mg.mg_allocate_storage()
+    assert mg.get_int("subtract_mean") == 1
+    for lvl, id_ in P.all_ids(mg):
+        X, Y, Z = P.cell_coords(mg, id_, lvl)
+        mg.cc(id_)[P.mg_irhs - 1] = np.sin(2 * np.pi * X) * np.cos(4 * np.pi * Y) + 0.3 * np.sin(2 * np.pi * Z) + 0.05
+    G = GlobalMG(n, 1.0 / n, None, smoother=smoother, box=box, periodic=True)
+    G.rhs[0][1:-1, 1:-1, 1:-1] = global_phi(mg, iv=P.mg_irhs)
+    rhs_norm = float(np.abs(G.rhs[0]).max())
+    h_box = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False)
+    h_glob = [G.fmg(False), G.fmg(True), G.vcycle(), G.vcycle()]
+    for a, b in zip(h_box, h_glob):
+        assert abs(a - b) <= max(1e-10 * abs(a), 1e-12 * rhs_norm), (h_box, h_glob)
+    assert h_box[-1] < 1e-3 * h_box[0]
+    a, b = global_phi(mg), G.phi[0][1:-1, 1:-1, 1:-1]
+    assert np.abs(a - b).max() <= 1e-12 * np.abs(a).max()
+    assert abs(a.mean()) < 1e-15 and abs(b.mean()) < 1e-15
+
+
 def test_global_array_neumann_constants(oracle):
     from oracle.global_array_mg import GlobalMG
     n, box = 32, 16
