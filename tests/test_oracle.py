@@ -257,3 +257,69 @@ def test_golden_fixtures(oracle):
         got = mk.run_case(oracle.OracleMg, case["name"])
         assert got["residuals"] == case["residuals"], case["name"]
         assert got["phi_checksum"] == case["phi_checksum"], case["name"]
+
+
+def _level_arrays(mg, lvl, iv):
+    """(array over the whole domain at the resolution of `lvl` filled where boxes exist, lo, hi of the boxes' bounding patch)"""
+    nc = mg.box_size_lvl(lvl)
+    ids = mg.ids(lvl)
+    ix = np.array([mg.box_info(i)["ix"] for i in ids])
+    n = int(round(1.0 / mg.dr(lvl)[0]))
+    out = np.zeros((n, n, n))
+    for id_, (bx, by, bz) in zip(ids, ix):
+        out[(bz - 1) * nc:bz * nc, (by - 1) * nc:by * nc, (bx - 1) * nc:bx * nc] = mg.cc(id_, nc)[iv - 1, 1:-1, 1:-1, 1:-1]
+    lo, hi = (ix.min(axis=0) - 1) * nc, ix.max(axis=0) * nc
+    assert len(ids) * nc ** 3 == int(np.prod(hi - lo)), "the level is not one rectangular patch"
+    return out, lo, hi
+
+
+AMR_CASES = {
+    # the reference's own rule (tests/test_refinement.f90:191-247): centred cubes, three levels
+    "centred": (3, 8, 32, None, [(P.mg_bc_dirichlet, 0.0)] * 6),
+    # a patch that touches the domain boundary on five sides (the coarse-side interpolation reads physical ghost cells),
+    # Neumann / non-zero Dirichlet constants, Helmholtz, and a second refinement inside it
+    "slab": (3, 4, 16, lambda lvl, c, L: bool(c[0] < (0.5 if lvl == 1 else 0.25) * L[0]),
+             [(P.mg_bc_dirichlet, 0.25), (P.mg_bc_neumann, 0.5), (P.mg_bc_neumann, -0.25), (P.mg_bc_dirichlet, -1.0),
+              (P.mg_bc_continuous, 0.0), (P.mg_bc_dirichlet, 0.0)]),
+}
+
+
+@pytest.mark.parametrize("case", sorted(AMR_CASES))
+@pytest.mark.parametrize("helm", [False, True])
+def test_global_array_restatement_refined_grid(oracle, case, helm):
+    """independent numpy multigrid with one global array per level and rectangular refined patches
+    (oracle/global_array_amr.py) == box-structured oracle on the same refined tree, bit for bit: FMG and V-cycle residual
+    histories and phi on every level.  Pins the refinement-boundary ghost cells (box_gc_for_fine_neighbor + sides_rb), the
+    partial restriction / coarse right-hand side / correction and the parent / leaf bookkeeping."""
+    from oracle.global_array_amr import GlobalAMR
+    n_levels, box, n, refine, bc = AMR_CASES[case]
+    lam = 1.5 if helm else 0.0
+    mg = oracle.OracleMg(P.mg_helmholtz if helm else P.mg_laplacian, P.mg_smoother_gsrb)
+    if helm:
+        mg.set_lambda(lam)
+    for nb in range(1, 7):
+        mg.set_bc(nb, P.mg_iphi, *bc[nb - 1])
+    mg.mg_set_methods()
+    P.build_amr_tree(mg, n_levels, [n] * 3, box, [1.0 / n] * 3, refine=refine)
+    rng = np.random.default_rng(7)
+    levels = list(range(mg.lowest_lvl, mg.highest_lvl + 1))
+    for lvl in levels:
+        for id_ in mg.ids(lvl):
+            mg.cc(id_)[P.mg_irhs - 1, 1:-1, 1:-1, 1:-1] = rng.standard_normal((mg.box_size_lvl(lvl),) * 3)
+    patches = []
+    for lvl in range(2, mg.highest_lvl + 1):
+        _, lo, hi = _level_arrays(mg, lvl, P.mg_irhs)
+        patches.append((lo, hi))
+    G = GlobalAMR(n, 1.0 / n, patches, bc, lam=lam, helmholtz=helm)
+    assert G.nl == len(levels)
+    for l, lvl in enumerate(levels):
+        a, lo, hi = _level_arrays(mg, lvl, P.mg_irhs)
+        assert np.array_equal(lo, G.lo[l]) and np.array_equal(hi, G.hi[l])
+        G.rhs[l][1:-1, 1:-1, 1:-1] = a
+    h_box = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False)
+    h_glob = [G.fmg(False), G.fmg(True), G.vcycle(), G.vcycle()]
+    assert h_box == h_glob
+    for l, lvl in enumerate(levels):
+        a, lo, hi = _level_arrays(mg, lvl, P.mg_iphi)
+        s = tuple(slice(lo[d], hi[d]) for d in (2, 1, 0))
+        assert np.array_equal(a[s], G.phi[l][1:-1, 1:-1, 1:-1][s]), lvl
