@@ -126,6 +126,7 @@ struct omg_handle {
   bool gz[OMG_NLVL];
   // options
   int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1, ring_order = 0, ring_fused = 0;
+  int warp_coarse = 1;    // option "warp_coarse": the coarse solve of a single 2^3 box by one warp in registers (0: interpreter operations)
   int coeff_math = 0;     // option "coeff_math": 1 = tolerance mode of the coefficient kernels (omg_device.cuh recip6), default bitwise
   // cluster tail (k_tail_cluster): CTAs per cluster (0 = single-CTA tail only) and the level size it takes
   int tail_cluster = 0, tail_cluster_cells = 262144, tail_cluster_always = 0;   // off: measured slower (profiles/r02j_summary.txt)
@@ -537,7 +538,7 @@ void sync_meta(omg_handle* h) {
   for (LevelHost& L : h->levels) devs.push_back(L.dev);
   h->d_levels.upload(devs, s);
   h->pdev.op = h->params.operator_type; h->pdev.smoother = h->params.smoother_type; h->pdev.lambda = h->params.lambda;
-  h->pdev.coeff_math = h->coeff_math;
+  h->pdev.coeff_math = h->coeff_math; h->pdev.warp_coarse = h->warp_coarse;
   for (int f = 0; f < 6; ++f) { h->pdev.bc_type[f] = h->bc_type[IPHI][f]; h->pdev.bc_value[f] = h->bc_value[IPHI][f]; }
   if (!h->d_scal.p) { h->d_scal.alloc(SCAL_COUNT); CK(cudaMemsetAsync(h->d_scal.p, 0, SCAL_COUNT * sizeof(double), s)); }
   const double ra[2] = {h->params.residual_coarse_rel, h->params.residual_coarse_abs};
@@ -1875,6 +1876,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "pdl") h->pdl = value;
     else if (k == "ring") h->ring = value;
     else if (k == "coeff_math") { h->coeff_math = value; h->params_dirty = true; }
+    else if (k == "warp_coarse") { h->warp_coarse = value; h->params_dirty = true; }
     else if (k == "ring_fused") h->ring_fused = value;
     else if (k == "ring_order") h->ring_order = value;   // fused levels on the ring kernel: 0 partition-face boxes first, 1 last, 2 natural order
     else if (k == "store_fine_residual") h->store_fine_residual = value;
