@@ -221,14 +221,14 @@ def parity_check(om, P, n, box, rank, world, local, dist, collapse):
     hist = [mg.mg_fas_fmg(False)] + [mg.mg_fas_vcycle() for _ in range(3)]
     fast, general = mg.stat("fast_launches") - f0, mg.stat("general_launches") - g0
     ck = phi_checksum(mg, P)
-    fused, puts = mg.stat("fused_smooths"), mg.stat("puts")
+    fused, puts, fusedp = mg.stat("fused_smooths"), mg.stat("puts"), mg.stat("fused_prolongs")
     if world > 1:
         t = torch.tensor([ck - (1 << 64) if ck >= (1 << 63) else ck], dtype=torch.int64, device="cuda")
         dist.all_reduce(t)            # two's-complement wrap-around = sum mod 2^64
         ck = int(t.item()) % (1 << 64)
     mg.mg_deallocate_storage()
     out = {"n_ranks": world, "problem": "test_uniform_grid %d^3 box %d, FMG + 3 V(2,2) GSRB cycles" % (n, box),
-           "fast_launches": fast, "general_launches": general, "fused_smooths": fused, "put_phases": puts}
+           "fast_launches": fast, "general_launches": general, "fused_smooths": fused, "fused_prolongs": fusedp, "put_phases": puts}
     if rank == 0:
         from oracle import oracle as O
         O.lib().orc_set_omp_threads(host_threads())

@@ -197,9 +197,10 @@ int64_t omg_stat(omg_handle* h, const char* key);                     /* "launch
 /* Tuning / diagnostic switches (defaults in brackets); none changes results:
  *   "use_graph" [1] CUDA graph per cycle program, "graph_multi" [1] also with several ranks, "fast_kernels" [1] TMA-staged
  *   kernels where they apply, "tail_cells" [4096] levels up to this many cells run in the single-CTA tail, "tail_smem" [1]
- *   tail levels staged in shared memory, "tail_simple" [1; 2 = also plane boundaries / variable coefficients, host-verified
- *   only so far], "overlap" [1] halo exchange overlapped with interior boxes, "p2p" / "fused" [1] peer-mapped puts / issued
- *   from inside the smoother, "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; measured: no gain),
+ *   tail levels staged in shared memory, "tail_simple" [2: per-cell fast path of the tail for all operators and boundary kinds; 1 = Laplacian /
+ *   Helmholtz between constant boundaries only; 0 = general functions], "warp_coarse" [1] coarse solve of a single 2^3 box by
+ *   one warp with the cells in registers, "overlap" [1] halo exchange overlapped with interior boxes, "p2p" / "fused" [1] peer-mapped puts / issued
+ *   from inside the smoother, "fused_prolong" [1] ... and from inside the prolongation kernel that precedes it, "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; measured: no gain),
  *   "ring" [1] persistent ring smoother on big levels (2 = every level it serves, 0 = one tile per CTA),
  *   "store_fine_residual" [1] (0: the level's own residual, mg_ires, is not written by the cycle -- the one switch that
  *   changes what the host can read back: only for device-resident hosts that never read mg_ires),

@@ -125,7 +125,7 @@ struct omg_handle {
   std::map<std::string, Program> programs;
   bool gz[OMG_NLVL];
   // options
-  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 1, pdl = 0, ring = 1, store_fine_residual = 1, ring_order = 0, ring_fused = 0;
+  int use_graph = 1, fast_kernels = 1, tail_cells = 4096, graph_multi = 1, tail_smem = 1, overlap = 1, tail_simple = 2, pdl = 0, ring = 1, store_fine_residual = 1, ring_order = 0, ring_fused = 0;
   int warp_coarse = 1;    // option "warp_coarse": the coarse solve of a single 2^3 box by one warp in registers (0: interpreter operations)
   int coeff_math = 0;     // option "coeff_math": 1 = tolerance mode of the coefficient kernels (omg_device.cuh recip6), default bitwise
   // cluster tail (k_tail_cluster): CTAs per cluster (0 = single-CTA tail only) and the level size it takes
@@ -138,7 +138,7 @@ struct omg_handle {
   size_t stage_doubles = 0; int stage_boxes = 0;
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
   // stats / timers
-  int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0, exchanges = 0, fused_smooths = 0, puts = 0;
+  int64_t launches = 0, bytes_h2d = 0, bytes_d2h = 0, graph_launches = 0, exchanges = 0, fused_smooths = 0, fused_prolongs = 0, puts = 0;
   // level kernels launched through the TMA-staged path (omg_fast.cu) / through the general one-CTA-per-box path
   // (omg_kernels.cu); the single-CTA tail and the pack / exchange kernels count in neither
   int64_t fast_launches = 0, general_launches = 0;
@@ -148,6 +148,7 @@ struct omg_handle {
   omg_comm* comm = nullptr;
   int bnd_first_boxes = 8192;               // levels up to this many boxes launch their partition-face boxes first
   int fused = 1;                            // in-kernel exchange in the smoother where fused_level() allows (option "fused")
+  int fused_prolong = 1;                    // ... and in the prolongation kernel that precedes such a smoother (option "fused_prolong")
   int p2p = 1;                              // ghost faces as peer-mapped puts where the plane pools are shared (option "p2p")
   DevBuf<unsigned long long> d_epoch;       // [OMG_NLVL] completed ghost exchanges per level (selects the plane-pool copy)
   // per-step CUDA-event profile of the finest level (option "profile"): kind -> (events, count)
@@ -515,9 +516,9 @@ void sync_meta(omg_handle* h) {
       U.epoch = h->d_epoch.p + (L.lvl - OMG_LVL_LO); U.done = L.d_done.p;
     }
     // tail fast path (omg_ops.cuh simple_*): every face a physical boundary or a local same-level neighbour
-    // Option "tail_simple": 1 (default) = Laplacian / Helmholtz between constant boundaries -- the part that has run on
-    // a B200 (bitwise, profiles/r01u_*); 2 = also boundary planes and the variable-coefficient operators, which so far
-    // are verified on the host build only (tests/test_device_host.py) and wait for a GPU pass.
+    // Option "tail_simple": 2 (default) = all five operators, constant boundary values and stored boundary planes (bitwise on
+    // a B200: tests/test_gpu_steps.py test_tail_fast_path_all_variants, the whole GPU suite since pass zb); 1 = Laplacian /
+    // Helmholtz between constant boundaries only; 0 = the general per-cell functions.
     D.simple = (h->tail_simple && L.nb >= 1 && D.sh_nc >= 0) ? 1 : 0;
     const bool all_variants = h->tail_simple >= 2;
     if (!all_variants && h->params.operator_type != 1 && h->params.operator_type != 3) D.simple = 0;
@@ -612,10 +613,18 @@ struct Builder {
     emit(lvl - 1, TOP_CRHS, S_CRHS);
     if (!h->L(lvl - 1).h_oldpl.empty()) emit(lvl - 1, TOP_OLDPL, S_OLDPL);
   }
-  // correct_children(lvl-1) :387-402, prolonging onto lvl
-  void correct_children_onto(int lvl) {
+  // correct_children(lvl-1) :387-402, prolonging onto lvl, and the ghost-cell fill that follows it (:219-222, :132-136).
+  // Where the next operation on the level is a GSRB half-sweep with in-kernel exchange (n_smooth > 0 of them follow), the
+  // partition-face boxes of the prolongation kernel put their corrected faces into the peers' plane pools themselves and the
+  // half-sweep's partition-face CTAs wait for the peers' signal: no stand-alone exchange (pack + put, signal + wait) in between.
+  // Every input of the decision is replicated, so all ranks emit the same steps.
+  void correct_children_onto(int lvl, int n_smooth) {
     if (h->L(lvl).xp.any) step(S_XPROLONG, lvl);
-    emit(lvl, TOP_CORR_PROLONG, S_CORR_PROLONG);
+    const LevelHost& L = h->L(lvl);
+    const bool put = h->fused_prolong && n_smooth > 0 && h->params.smoother_type == 2 && !h->profile && fused_level(h, L) &&
+                     lvl > h->lowest && h->L(lvl - 1).nc == L.nc;
+    if (put) { step(S_CORR_PROLONG, lvl, 3); gf_local(lvl); }
+    else { emit(lvl, TOP_CORR_PROLONG, S_CORR_PROLONG); gf(lvl); }
   }
   void subtract_mean(int iv, int with_ghosts) { step(S_SUBMEAN, 0, iv, with_ghosts); }
 
@@ -630,7 +639,7 @@ struct Builder {
       pend.push_back({TOP_COARSE_SOLVE, li(min_lvl), (h->params.n_cycle_up + h->params.n_cycle_down) * sub,
                       h->params.max_coarse_cycles});
     for (int lvl = min_lvl + 1; lvl <= max_lvl; ++lvl) {
-      correct_children_onto(lvl); gf(lvl); smooth_boxes(lvl, h->params.n_cycle_up);
+      correct_children_onto(lvl, h->params.n_cycle_up); smooth_boxes(lvl, h->params.n_cycle_up);
     }
     if (want_res) {
       step(S_CLEAR_SLOT, 0, SCAL_MAXRES);
@@ -651,7 +660,7 @@ struct Builder {
     for (int lvl = h->lowest; lvl <= h->highest; ++lvl) {
       emit(lvl, TOP_COPY_OLD, S_COPY_OLD);
       if (!h->L(lvl).h_oldpl.empty()) emit(lvl, TOP_OLDPL, S_OLDPL);
-      if (lvl > h->lowest) { correct_children_onto(lvl); gf(lvl); }
+      if (lvl > h->lowest) correct_children_onto(lvl, h->params.n_cycle_down);     // the V-cycle from lvl starts with its down-smoothing
       vcycle(true, lvl, false, want_res && lvl == h->highest, SCAL_MAXRES);
     }
   }
@@ -843,7 +852,18 @@ void exec_steps(omg_handle* h, Program& P) {
       case S_OLDPL: omgk::oldpl(h->L(st.l).dev, PD, s); h->launches++; break;
       case S_CORR_PROLONG: {
         LevelHost& L = h->L(st.l);
-        if (h->fast_kernels && omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, s)) fast(L);
+        if (st.a == 3) {   // in-kernel exchange of the corrected faces (see Builder::correct_children_onto)
+          if (L.nb) {
+            if (!omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, 1, s)) fail("fused prolongation does not apply to this level");
+            h->launches++; h->exchanges++; h->fused_prolongs++; fast(L);
+          }
+          if (!omg_comm_graph_safe(h->comm)) {      // emulated ranks: host rendezvous instead of in-kernel waits (see S_SMOOTH)
+            try { omg_comm_signal_wait(h->comm, st.l - OMG_LVL_LO, L.xg.peers.data(), (int)L.xg.peers.size(), h->d_epoch.p + (st.l - OMG_LVL_LO), 0, s); }
+            catch (const std::exception& e) { fail(e.what()); }
+          }
+          break;
+        }
+        if (h->fast_kernels && omgf::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, h->L(st.l - 1).all_fast, 0, s)) fast(L);
         else { omgk::corr_prolong(L.dev, h->L(st.l - 1).dev, PD, s); general(L); }
         h->launches++;
       } break;
@@ -1410,7 +1430,7 @@ int omg_debug_step(omg_handle* h, const char* what, int lvl, int arg, double* ou
     else if (w == "smooth_only") { for (int n = 1; n <= 2 * arg; ++n) B.emit(lvl, TOP_SMOOTH, S_SMOOTH, (n - 1) & 1); }   // timing probe: no ghost exchange
     else if (w == "halo_only") { for (int n = 1; n <= 2 * arg; ++n) B.gf(lvl); }                                          // timing probe
     else if (w == "update_coarse") { if (lvl <= h->lowest) fail("update_coarse: lvl <= lowest_lvl"); B.update_coarse(lvl); }
-    else if (w == "correct_children") { if (lvl >= h->highest) fail("correct_children: lvl >= highest_lvl"); B.correct_children_onto(lvl + 1); B.gf(lvl + 1); }
+    else if (w == "correct_children") { if (lvl >= h->highest) fail("correct_children: lvl >= highest_lvl"); B.correct_children_onto(lvl + 1, 0); }   // (0: the ghost fill as a stand-alone exchange)
     else if (w == "coarse_solve") {
       const int sub = (h->params.smoother_type == 2) ? 2 : 1;
       B.pend.push_back({TOP_COARSE_SOLVE, B.li(h->lowest), (h->params.n_cycle_up + h->params.n_cycle_down) * sub, h->params.max_coarse_cycles});
@@ -1853,6 +1873,7 @@ int64_t omg_stat(omg_handle* h, const char* key) {
   if (k == "bytes_d2h") return h->bytes_d2h;
   if (k == "exchanges") return h->exchanges;
   if (k == "fused_smooths") return h->fused_smooths;     // half-sweeps that exchanged their partition faces in-kernel
+  if (k == "fused_prolongs") return h->fused_prolongs;   // prolongations that did
   if (k == "puts") return h->puts;                       // ghost phases sent as peer-mapped puts
   if (k == "coarse_iters") {
     double v = 0; cudaSetDevice(h->device); cudaStreamSynchronize(h->stream);
@@ -1883,6 +1904,7 @@ int omg_set_option(omg_handle* h, const char* key, int value) {
     else if (k == "trace") { h->trace = value; for (auto& r : h->trace_events) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); } h->trace_events.clear(); }
     else if (k == "p2p") { h->p2p = value; h->params_dirty = true; }
     else if (k == "fused") { h->fused = value; h->params_dirty = true; }
+    else if (k == "fused_prolong") { h->fused_prolong = value; h->params_dirty = true; }
     else if (k == "bnd_first_boxes") h->bnd_first_boxes = value;
     else if (k == "profile") { collect_profile(h); h->profile = value; if (value) h->prof_acc.clear(); }
     else if (k == "tail_cells") { h->tail_cells = value; if (h->have_tree) compute_tail(h); }

@@ -121,6 +121,50 @@ __device__ __forceinline__ void bc_coeffs(int type, double dr, int f, double& c0
   else { c0 = 0; c1 = 2; c2 = -1; }
 }
 
+// In-kernel halo exchange, sending side (PutDev, omg_device.cuh): a CTA that has just written box `boxoff` (slab k0 .. k0 + KT of
+// it) stores the box's face layers into the neighbour ranks' plane pools -- the copy they are not reading, (epoch + 1) & 1 --
+// over NVLink; the last such CTA of the launch (n_bnd * tiles of them) signals the peers and bumps the epoch.  Used by the
+// GSRB half-sweep kernels and by the prolongation kernel (whose put replaces the stand-alone ghost exchange that would
+// follow it).  Called by every thread of the CTA.
+template <int NC, int KT>
+__device__ __forceinline__ void put_faces(const LevelDev& L, int slot, size_t boxoff, int k0, int tiles, int tid) {
+  constexpr int HX = NC / 2;
+  __syncthreads();
+  const unsigned long long e = *L.put.epoch;
+  const double* Abox = L.var[0] + boxoff;
+  for (int it = L.put.ptr[slot]; it < L.put.ptr[slot + 1]; ++it) {
+    const int f = L.put.item[3 * it], pr = L.put.item[3 * it + 1], pl = L.put.item[3 * it + 2];
+    double* o = L.put.peer_base[pr] + (size_t)((e + 1ull) & 1ull) * (size_t)L.put.peer_stride[pr] + (size_t)pl * NC * NC;
+    const int layer = (f & 1) ? 0 : NC - 1;          // f = the RECEIVER's face (buffer_for_nb, src/m_ghost_cells.f90:348-383)
+    if (f < 4) {
+      for (int r = tid; r < KT * NC; r += kThreads) {
+        const int k = k0 + r / NC, t1 = r % NC;
+        const int i = f < 2 ? layer : t1, j = f < 2 ? t1 : layer;
+        o[k * NC + t1] = __ldcg(Abox + ((i + j + k) & 1) * L.cs + (k * NC + j) * HX + (i >> 1));
+      }
+    } else if (layer >= k0 && layer < k0 + KT) {
+      for (int r = tid; r < NC * NC; r += kThreads) {
+        const int i = r % NC, j = r / NC;
+        o[r] = __ldcg(Abox + ((i + j + layer) & 1) * L.cs + (layer * NC + j) * HX + (i >> 1));
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int prev = atomicAdd(L.put.done, 1u);
+    if (prev == (unsigned int)(L.put.n_bnd * tiles) - 1u) {
+      *L.put.done = 0u;
+      __threadfence_system();
+      if (*(volatile int*)L.put.err == 0) {      // after a failed wait the exchange stops: no signal, epoch left alone
+        for (int q = 0; q < L.put.n_peers; ++q)
+          signal_flag(L.put.peer_flags[L.put.peers[q]] + L.put.channel * L.put.nranks + L.put.me, e + 1ull);
+        *L.put.epoch = e + 1ull;
+      }
+    }
+  }
+}
+
 // =================================================================================================
 // GSRB colour half-sweep, Laplacian / Helmholtz (box_gs_lpl src/m_laplacian.f90:52-114, box_gs_helmh
 // src/m_helmholtz.f90:49-108) over all boxes of a level.
@@ -421,45 +465,9 @@ __global__ void __launch_bounds__(kThreads, NE == 3 ? (KT == NC && NC == 16 ? 2 
   }
   }
 
-  // ---- partition-face box: store the fresh face layers into the neighbour ranks' plane pools (the copy they are not
-  // reading, (epoch + 1) & 1); the last such CTA of the launch signals the peers and bumps the epoch ----
-  if (bnd_put) {
-    __syncthreads();
-    const int slot = put_slot;
-    const unsigned long long e = *L.put.epoch;
-    const double* Abox = L.var[0] + boxoff;
-    for (int it = L.put.ptr[slot]; it < L.put.ptr[slot + 1]; ++it) {
-      const int f = L.put.item[3 * it], pr = L.put.item[3 * it + 1], pl = L.put.item[3 * it + 2];
-      double* o = L.put.peer_base[pr] + (size_t)((e + 1ull) & 1ull) * (size_t)L.put.peer_stride[pr] + (size_t)pl * NC * NC;
-      const int layer = (f & 1) ? 0 : NC - 1;          // f = the RECEIVER's face (buffer_for_nb, src/m_ghost_cells.f90:348-383)
-      if (f < 4) {
-        for (int r = tid; r < KT * NC; r += kThreads) {
-          const int k = k0 + r / NC, t1 = r % NC;
-          const int i = f < 2 ? layer : t1, j = f < 2 ? t1 : layer;
-          o[k * NC + t1] = __ldcg(Abox + ((i + j + k) & 1) * L.cs + (k * NC + j) * HX + (i >> 1));
-        }
-      } else if (layer >= k0 && layer < k0 + KT) {
-        for (int r = tid; r < NC * NC; r += kThreads) {
-          const int i = r % NC, j = r / NC;
-          o[r] = __ldcg(Abox + ((i + j + layer) & 1) * L.cs + (layer * NC + j) * HX + (i >> 1));
-        }
-      }
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (tid == 0) {
-      const unsigned int prev = atomicAdd(L.put.done, 1u);
-      if (prev == (unsigned int)(L.put.n_bnd * TILES) - 1u) {
-        *L.put.done = 0u;
-        __threadfence_system();
-        if (*(volatile int*)L.put.err == 0) {      // after a failed wait the exchange stops: no signal, epoch left alone
-          for (int q = 0; q < L.put.n_peers; ++q)
-            signal_flag(L.put.peer_flags[L.put.peers[q]] + L.put.channel * L.put.nranks + L.put.me, e + 1ull);
-          *L.put.epoch = e + 1ull;
-        }
-      }
-    }
-  }
+  // ---- partition-face box: store the fresh face layers into the neighbour ranks' plane pools; the last such CTA of the
+  // launch signals the peers and bumps the epoch (put_faces) ----
+  if (bnd_put) put_faces<NC, KT>(L, put_slot, boxoff, k0, TILES, tid);
 }
 
 // =================================================================================================
@@ -1331,7 +1339,7 @@ bool dispatch_stencil(const LevelDev& L, const LevelDev& Lc, const ParamsDev& P,
 // =================================================================================================
 template <int NC, int MB>
 __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid_constant__ LevelDev Lf, const __grid_constant__ LevelDev Lc,
-                                                                const __grid_constant__ ParamsDev P, int pdl) {
+                                                                const __grid_constant__ ParamsDev P, int pdl, int fused_put) {
   constexpr int HC = NC / 2, HX = NC / 2, PW = HC + 2, NIT = HC * HC * HC / kThreads;
   static_assert((HC * HC * HC) % kThreads == 0, "coarse cells must tile the CTA");
   OMG_DYN_SMEM(smem_raw, 16);
@@ -1339,8 +1347,15 @@ __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid
   const int tid = threadIdx.x, b = blockIdx.x;
   const int p = Lf.parent[b];
   const int off = Lf.coff[b];
+  // in-kernel halo exchange (fused_put, as in k_smooth_lpl_fast): a box on a partition face stores its corrected face layers
+  // into the neighbour ranks' plane pools; the GSRB half-sweep that follows waits for the peers' signal in its own
+  // partition-face CTAs, so that no stand-alone ghost exchange (pack + put + signal + wait) runs between the two
+  const int put_slot = fused_put ? Lf.put.slot_of[b] : -1;
   pdl_sync(pdl);
-  if (p == -1) return;
+  if (p == -1) {                      // (uniform across the CTA)
+    if (put_slot >= 0) put_faces<NC, NC>(Lf, put_slot, (size_t)b * Lf.bs, 0, 1, tid);
+    return;
+  }
   const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
   double* __restrict__ phi = Lf.var[0] + (size_t)b * Lf.bs;
   const int fcs = Lf.cs;
@@ -1408,6 +1423,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid
       phi[goff(q, e)] = cur[e] + fine;
     }
   }
+  if (put_slot >= 0) put_faces<NC, NC>(Lf, put_slot, (size_t)b * Lf.bs, 0, 1, tid);
 }
 
 // Box 16, TMA version: the child's 32 KiB of phi (both colours, contiguous) arrive by ONE bulk copy that is in flight
@@ -1509,16 +1525,16 @@ bool launch_corr_prolong_tma(const LevelDev& Lf, const LevelDev& Lc, const Param
 }
 
 template <int NC, int MB>
-bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, cudaStream_t s) {
+bool launch_corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, int fused, cudaStream_t s) {
   static bool configured = false;
   const size_t smem = sizeof(double) * (NC / 2 + 2) * (NC / 2 + 2) * (NC / 2 + 2);
   if (!configured) {
     if (cudaFuncSetAttribute(k_corr_prolong_fast<NC, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
     configured = true;
   }
-  if (g_pdl) return launch_pdl(k_corr_prolong_fast<NC, MB>, Lf.nb, smem, s, Lf, Lc, P, 1);
+  if (g_pdl && !fused) return launch_pdl(k_corr_prolong_fast<NC, MB>, Lf.nb, smem, s, Lf, Lc, P, 1, 0);
   auto kern = k_corr_prolong_fast<NC, MB>;
-  OMG_LAUNCH(kern, Lf.nb, smem, s, Lf, Lc, P, 0);
+  OMG_LAUNCH(kern, Lf.nb, smem, s, Lf, Lc, P, 0, fused);
   return true;
 }
 
@@ -1583,14 +1599,15 @@ bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s) 
   if (!all_fast || L.n_parents == 0) return false;
   return dispatch_stencil<MODE_CRHS>(L, L, P, L.n_parents, nullptr, s);
 }
-bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool, cudaStream_t s) {
+bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool, int fused, cudaStream_t s) {
   if (Lf.nb == 0 || Lc.nc != Lf.nc) return false;
   static const int mb = env_int("OMG_PROLONG_MB", 4);
   static const int tma = env_int("OMG_PROLONG_TMA", 0);        // CTAs per SM of the TMA version; 0 (default): register-prefetch version --
                                                                // measured equal within 1 % (0.488 / 0.492 / 0.492 / 0.516 ms for 0 / 3 / 4 / 5, profiles/r02f_*)
-  if (Lf.nc == 16 && tma && !g_pdl) return tma == 4 ? launch_corr_prolong_tma<16, 4>(Lf, Lc, P, s) : tma == 3 ? launch_corr_prolong_tma<16, 3>(Lf, Lc, P, s) : launch_corr_prolong_tma<16, 5>(Lf, Lc, P, s);
-  if (Lf.nc == 16) return mb == 4 ? launch_corr_prolong<16, 4>(Lf, Lc, P, s) : mb == 2 ? launch_corr_prolong<16, 2>(Lf, Lc, P, s) : launch_corr_prolong<16, 3>(Lf, Lc, P, s);
-  if (Lf.nc == 32) return launch_corr_prolong<32, 3>(Lf, Lc, P, s);
+  // fused = 1: partition-face boxes put their corrected faces into the peers' plane pools (register-prefetch version only)
+  if (Lf.nc == 16 && tma && !g_pdl && !fused) return tma == 4 ? launch_corr_prolong_tma<16, 4>(Lf, Lc, P, s) : tma == 3 ? launch_corr_prolong_tma<16, 3>(Lf, Lc, P, s) : launch_corr_prolong_tma<16, 5>(Lf, Lc, P, s);
+  if (Lf.nc == 16) return mb == 4 ? launch_corr_prolong<16, 4>(Lf, Lc, P, fused, s) : mb == 2 ? launch_corr_prolong<16, 2>(Lf, Lc, P, fused, s) : launch_corr_prolong<16, 3>(Lf, Lc, P, fused, s);
+  if (Lf.nc == 32) return launch_corr_prolong<32, 3>(Lf, Lc, P, fused, s);
   return false;
 }
 

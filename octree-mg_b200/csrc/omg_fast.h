@@ -31,5 +31,5 @@ bool gs_sweep(const LevelDev& L, const ParamsDev& P, cudaStream_t s);
 bool resid_restrict(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool all_fast, cudaStream_t s);
 bool resid_max(const LevelDev& L, const ParamsDev& P, bool all_fast, double* maxslot, cudaStream_t s);
 bool crhs(const LevelDev& L, const ParamsDev& P, bool all_fast, cudaStream_t s);
-bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool coarse_all_fast, cudaStream_t s);
+bool corr_prolong(const LevelDev& Lf, const LevelDev& Lc, const ParamsDev& P, bool coarse_all_fast, int fused, cudaStream_t s);   // fused = 1: in-kernel halo put of the corrected faces
 }  // namespace omgf

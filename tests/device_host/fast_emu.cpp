@@ -280,7 +280,7 @@ int two_levels(int nc, int nbx, int nby, int nbz, const int* bc_types, const dou
   // correct_children
   randomise(Gc, seed + 31); copy_data(Fc, Gc);
   for (int b = 0; b < Gf.L.nb; ++b) do_corr_prolong(Gf.L, Gc.L, P, b, 0, 1);
-  if (!omgf::corr_prolong(Ff.L, Fc.L, P, true, nullptr)) return -1;
+  if (!omgf::corr_prolong(Ff.L, Fc.L, P, true, 0, nullptr)) return -1;
   bad += (differing(Gf, Ff) ? 1 : 0) + (differing(Gc, Fc) ? 1 : 0);
   return bad;
 }

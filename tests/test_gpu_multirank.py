@@ -42,6 +42,8 @@ def test_fast_kernels_with_remote_faces(oracle, product, lb):
     # the halo exchange of the smoother ran inside the smoother kernels (peer-mapped puts + flags), the other ghost
     # fills as put kernels
     assert mg.stat("fused_smooths") > 0 and mg.stat("puts") > 0
+    # ... and the prolongation kernels that precede such half-sweeps put their corrected faces themselves
+    assert mg.stat("fused_prolongs") > 0
     # ... and every level kernel of the box-16 levels was a TMA-staged one (omg_fast.cu), on every rank
     assert mg.stat("fast_launches") > 0 and mg.stat("general_cells") <= 0.2 * mg.stat("fast_cells")
 
@@ -59,6 +61,24 @@ def test_exchange_transports(oracle, product, opts):
     assert_state_equal(orc, mg)
     assert mg.stat("fused_smooths") == 0
     assert (mg.stat("puts") > 0) == (opts.get("p2p", 1) == 1)
+
+
+@pytest.mark.parametrize("n_cpu,dims", [(2, (64, 32, 32)), (8, (64, 64, 64))])
+def test_fused_prolongation_put_on_and_off(oracle, product, n_cpu, dims):
+    """the ghost exchange after correct_children (src/m_multigrid.f90:219-222) issued from inside the prolongation kernel
+    (option fused_prolong, default) against the stand-alone put kernels: same bits, and the stand-alone exchange phases it
+    replaces are gone"""
+    orc, _ = P.uniform_problem(oracle.OracleMg, dims, 16, n_cpu=n_cpu)
+    h_o = P.run_cycles(orc, 2, True) + P.run_cycles(orc, 2, False)
+    puts = {}
+    for on in (1, 0):
+        mg, _ = P.uniform_problem(group_cls(product, n_cpu), dims, 16)
+        mg.set_option("fused_prolong", on)
+        check(h_o, P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False))
+        assert_state_equal(orc, mg)
+        assert (mg.stat("fused_prolongs") > 0) == (on == 1)
+        puts[on] = mg.stat("puts")
+    assert puts[1] < puts[0]
 
 
 @pytest.mark.parametrize("op,bc,lam", [(P.mg_helmholtz, "neumann0", 1.0), (P.mg_vlaplacian, "mixed", 0.0)])

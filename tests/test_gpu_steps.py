@@ -198,3 +198,23 @@ def test_pdl_launches_change_nothing(oracle, product, op, lam, graph):
     assert P.run_cycles(orc, 3, True) == P.run_cycles(mg, 3, True)
     assert P.run_cycles(orc, 3, False) == P.run_cycles(mg, 3, False)
     assert_state_equal(orc, mg)
+
+
+@pytest.mark.parametrize("warp", [1, 0])
+@pytest.mark.parametrize("op,bc,lam", [(P.mg_laplacian, "callback", 0.0), (P.mg_laplacian, "neumann0", 0.0), (P.mg_helmholtz, "neumann0", 1.0),
+                                       (P.mg_vlaplacian, "mixed", 0.0), (P.mg_vhelmholtz, "neumann0", 1.0),
+                                       (P.mg_ahelmholtz, "mixed", 0.5)])
+def test_warp_coarse_solve(oracle, product, op, bc, lam, warp):
+    """cubic grids end in ONE 2^3 box: its coarse solve (src/m_multigrid.f90:202-208) runs in one warp with the eight cells in
+    registers (omg_tail.cuh warp_coarse_solve; option warp_coarse = 0: as interpreter operations) -- residual histories, the
+    full state and the iteration count of the coarse loop as the oracle's, for problems whose coarse loop is short (Dirichlet)
+    and long (the constant mode of a Neumann problem: tens of iterations, or the limit max_coarse_cycles)"""
+    orc, _ = P.uniform_problem(oracle.OracleMg, 32, 16, operator_type=op, bc=bc, lam=lam)
+    mg, _ = P.uniform_problem(product.Mg, 32, 16, operator_type=op, bc=bc, lam=lam)
+    mg.set_option("warp_coarse", warp)
+    for m in (orc, mg):
+        m.set_int("max_coarse_cycles", 30)      # the Neumann problems reach the limit (the oracle's coarse loop is slow per iteration)
+    assert P.run_cycles(orc, 2, True) == P.run_cycles(mg, 2, True)
+    assert P.run_cycles(orc, 1, False) == P.run_cycles(mg, 1, False)
+    assert_state_equal(orc, mg)
+    assert 1 <= mg.stat("coarse_iters") <= 30
