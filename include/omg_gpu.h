@@ -200,7 +200,8 @@ int64_t omg_stat(omg_handle* h, const char* key);                     /* "launch
  *   tail levels staged in shared memory, "tail_simple" [2: per-cell fast path of the tail for all operators and boundary kinds; 1 = Laplacian /
  *   Helmholtz between constant boundaries only; 0 = general functions], "warp_coarse" [1] coarse solve of a single 2^3 box by
  *   one warp with the cells in registers, "overlap" [1] halo exchange overlapped with interior boxes, "p2p" / "fused" [1] peer-mapped puts / issued
- *   from inside the smoother, "fused_prolong" [1] ... and from inside the prolongation kernel that precedes it, "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; measured: no gain),
+ *   from inside the smoother, "fused_prolong" [1] ... and from inside the prolongation kernel that precedes it, "put_fence" [2] one system-scope fence per
+ *   CTA before its puts are signalled (1 = one per thread), "bnd_first_boxes", "pdl" [0] programmatic dependent launch (single rank; measured: no gain),
  *   "ring" [1] persistent ring smoother on big levels (2 = every level it serves, 0 = one tile per CTA),
  *   "store_fine_residual" [1] (0: the level's own residual, mg_ires, is not written by the cycle -- the one switch that
  *   changes what the host can read back: only for device-resident hosts that never read mg_ires),

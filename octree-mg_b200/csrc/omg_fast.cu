@@ -127,7 +127,7 @@ __device__ __forceinline__ void bc_coeffs(int type, double dr, int f, double& c0
 // GSRB half-sweep kernels and by the prolongation kernel (whose put replaces the stand-alone ghost exchange that would
 // follow it).  Called by every thread of the CTA.
 template <int NC, int KT>
-__device__ __forceinline__ void put_faces(const LevelDev& L, int slot, size_t boxoff, int k0, int tiles, int tid) {
+__device__ __forceinline__ void put_faces(const LevelDev& L, int slot, size_t boxoff, int k0, int tiles, int tid, int mode) {
   constexpr int HX = NC / 2;
   __syncthreads();
   const unsigned long long e = *L.put.epoch;
@@ -149,9 +149,12 @@ __device__ __forceinline__ void put_faces(const LevelDev& L, int slot, size_t bo
       }
     }
   }
-  __threadfence_system();
+  // mode 1: every thread fences its own remote stores before the CTA barrier; mode 2 (option "put_fence" = 2): the barrier
+  // orders the CTA's stores before thread 0, whose system-scope fence + atomic is the (cumulative) release -- one fence per CTA
+  if (mode != 2) __threadfence_system();
   __syncthreads();
   if (tid == 0) {
+    if (mode == 2) __threadfence_system();
     const unsigned int prev = atomicAdd(L.put.done, 1u);
     if (prev == (unsigned int)(L.put.n_bnd * tiles) - 1u) {
       *L.put.done = 0u;
@@ -467,7 +470,7 @@ __global__ void __launch_bounds__(kThreads, NE == 3 ? (KT == NC && NC == 16 ? 2 
 
   // ---- partition-face box: store the fresh face layers into the neighbour ranks' plane pools; the last such CTA of the
   // launch signals the peers and bumps the epoch (put_faces) ----
-  if (bnd_put) put_faces<NC, KT>(L, put_slot, boxoff, k0, TILES, tid);
+  if (bnd_put) put_faces<NC, KT>(L, put_slot, boxoff, k0, TILES, tid, fused_put);
 }
 
 // =================================================================================================
@@ -1353,7 +1356,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid
   const int put_slot = fused_put ? Lf.put.slot_of[b] : -1;
   pdl_sync(pdl);
   if (p == -1) {                      // (uniform across the CTA)
-    if (put_slot >= 0) put_faces<NC, NC>(Lf, put_slot, (size_t)b * Lf.bs, 0, 1, tid);
+    if (put_slot >= 0) put_faces<NC, NC>(Lf, put_slot, (size_t)b * Lf.bs, 0, 1, tid, fused_put);
     return;
   }
   const int ox = off & 1023, oy = (off >> 10) & 1023, oz = (off >> 20) & 1023;
@@ -1423,7 +1426,7 @@ __global__ void __launch_bounds__(kThreads, MB) k_corr_prolong_fast(const __grid
       phi[goff(q, e)] = cur[e] + fine;
     }
   }
-  if (put_slot >= 0) put_faces<NC, NC>(Lf, put_slot, (size_t)b * Lf.bs, 0, 1, tid);
+  if (put_slot >= 0) put_faces<NC, NC>(Lf, put_slot, (size_t)b * Lf.bs, 0, 1, tid, fused_put);
 }
 
 // Box 16, TMA version: the child's 32 KiB of phi (both colours, contiguous) arrive by ONE bulk copy that is in flight
