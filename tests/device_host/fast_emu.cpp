@@ -398,6 +398,54 @@ int ranks_case(int nc, int nbx, int nby, int nbz, int n_ranks, int bnd_first, co
       for (size_t lb = 0; lb < R[me].gid.size(); ++lb)
         bad += std::memcmp(&R[me].H.var[0][lb * G.L.bs], &G.var[0][(size_t)R[me].gid[lb] * G.L.bs], sizeof(double) * G.L.bs) != 0;
   }
+  // correct_children with the in-kernel put of the corrected faces (k_corr_prolong_fast, fused = 2: one fence per CTA), then
+  // two more fused half-sweeps, which read the planes that kernel sent.  Box b's parent is coarse box b (an isolated box
+  // between physical boundaries, so that a rank's coarse level is a plain copy of its share), its octant varies with b.
+  if ((nc == 16 || nc == 32) && (OP == OP_LPL || OP == OP_HELMH)) {
+    const int hc = nc / 2;
+    auto make_coarse = [&](HostLevel& C, int n, const std::vector<int>* gid) {
+      const int save = g_planes; g_planes = 0;
+      build_level(C, nc, n, 1, 1, bc_types, 0.02);
+      g_planes = save;
+      set_fac(C, OP, lambda);
+      for (int q = 0; q < n * 6; ++q) { C.fkind[q] = FK_PHYS; C.farg[q] = -1; C.ftype[q] = bc_types[q % 6]; }
+      C.fkind_old = C.fkind; C.farg_old = C.farg;
+      C.L.fkind_old = C.fkind_old.data(); C.L.farg_old = C.farg_old.data();
+      (void)gid;
+    };
+    HostLevel Gc;
+    make_coarse(Gc, nb, nullptr);
+    randomise(Gc, seed + 91);
+    for (int b = 0; b < nb; ++b) { G.parent[b] = b; G.coff[b] = ((b & 1) * hc) | ((((b >> 1) & 1) * hc) << 10) | ((((b >> 2) & 1) * hc) << 20); }
+    std::vector<HostLevel> Rc(n_ranks);
+    for (int me = 0; me < n_ranks; ++me) {
+      RankLevel& r = R[me];
+      const int nl = (int)r.gid.size();
+      make_coarse(Rc[me], nl, &r.gid);
+      for (int lb = 0; lb < nl; ++lb) {
+        const int g = r.gid[lb];
+        for (int v = 0; v < 4; ++v)
+          std::copy(Gc.var[v].begin() + (size_t)g * Gc.L.bs, Gc.var[v].begin() + (size_t)(g + 1) * Gc.L.bs, Rc[me].var[v].begin() + (size_t)lb * Gc.L.bs);
+        r.H.parent[lb] = lb; r.H.coff[lb] = G.coff[g];
+      }
+    }
+    for (int b = 0; b < nb; ++b) do_corr_prolong(G.L, Gc.L, P, b, 0, 1);
+    for (int me = 0; me < n_ranks; ++me) {
+      RankLevel& r = R[me];
+      const unsigned long long e0 = r.epoch;
+      if (!omgf::corr_prolong(r.H.L, Rc[me].L, P, true, 2, nullptr)) return -1;
+      if (r.epoch != e0 + 1 && r.H.L.put.n_bnd > 0) ++bad;
+      if (r.err) ++bad;
+    }
+    for (int n = 0; n < 2; ++n) {
+      for (int b = 0; b < nb; ++b) do_smooth<OP>(G.L, P, b, n & 1, 0, 1);
+      for (int me = 0; me < n_ranks; ++me)
+        if (!omgf::smooth(R[me].H.L, P, n & 1, true, nullptr, R[me].H.L.nb, 2, nullptr)) return -1;
+      for (int me = 0; me < n_ranks; ++me)
+        for (size_t lb = 0; lb < R[me].gid.size(); ++lb)
+          bad += std::memcmp(&R[me].H.var[0][lb * G.L.bs], &G.var[0][(size_t)R[me].gid[lb] * G.L.bs], sizeof(double) * G.L.bs) != 0;
+    }
+  }
   return bad;
 }
 
