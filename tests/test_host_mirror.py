@@ -224,3 +224,91 @@ def test_host_side_error_stops_keep_the_reference_wording(product):
     mg.set_int("smoother_type", 3)                      # mg_smoother_jacobi is declared but not implemented by the reference either
     with pytest.raises(product.MgError, match="unsupported smoother type"):
         mg.mg_set_methods()
+
+
+def check_tree_against_geometry(mg, n3, periodic):
+    """Pins the tree to plain geometry, without the libraries' index bookkeeping (ix, child offsets, id arithmetic): every
+    box is a cube [r_min, r_min + nc * dr); its neighbour through a face is whichever box of the level contains the point
+    one box size beyond its centre (the periodic image of that point; outside the domain: a physical boundary, id < 0;
+    inside but not covered: a refinement boundary, id 0 = mg_no_box, src/m_data_structures.f90:60-66); its parent is the box
+    of the level below that contains its centre, its children those of the level above whose centres it contains, x fastest
+    (src/m_build_tree.f90:330-393, mg_child_dix src/m_data_structures.f90:150-170)."""
+    L = np.array(n3, dtype=float) * mg.dr(1)                      # domain size (r_min = 0)
+    boxes = {}
+    for lvl in range(mg.lowest_lvl, mg.highest_lvl + 1):
+        size = mg.box_size_lvl(lvl) * mg.dr(lvl)
+        assert len(set(mg.ids(lvl))) == len(mg.ids(lvl))
+        for id_ in mg.ids(lvl):
+            info = mg.box_info(id_)
+            assert info["lvl"] == lvl
+            key = tuple(np.rint(info["r_min"] / size).astype(int))
+            assert np.array_equal(np.array(key) * size, info["r_min"]), "boxes are aligned to their own size"
+            assert (lvl, key) not in boxes, "two boxes of a level overlap"
+            boxes[(lvl, key)] = (id_, info, size)
+    per_level = {}
+    for (lvl, key), v in boxes.items():
+        per_level.setdefault(lvl, {})[key] = v
+
+    def find(lvl, point):
+        if lvl not in per_level:
+            return None
+        size = next(iter(per_level[lvl].values()))[2]
+        key = tuple(np.floor(point / size).astype(int))
+        hit = per_level[lvl].get(key)
+        return hit[0] if hit else None
+
+    n_checked = 0
+    for (lvl, key), (id_, info, size) in boxes.items():
+        centre = info["r_min"] + 0.5 * size
+        for nb in range(6):
+            d, sign = nb // 2, (1 if nb % 2 else -1)
+            p = centre.copy()
+            p[d] += sign * size[d]
+            got = info["neighbors"][nb]
+            if p[d] < 0 or p[d] > L[d]:
+                if periodic[d]:
+                    p[d] = p[d] % L[d]
+                    assert got == find(lvl, p), (lvl, key, nb)
+                else:
+                    assert got < 0, (lvl, key, nb, got)
+            else:
+                want = find(lvl, p)
+                assert got == (want if want is not None else 0), (lvl, key, nb, got, want)
+            n_checked += 1
+        want_parent = find(lvl - 1, centre)
+        if lvl > mg.lowest_lvl:
+            assert info["parent"] == want_parent, (lvl, key)
+        kids = [c for c in info["children"] if c > 0]
+        if lvl < mg.highest_lvl and lvl + 1 in per_level:
+            fsize = next(iter(per_level[lvl + 1].values()))[2]
+            if np.allclose(fsize, size):          # below first_normal_lvl: one child, the same cube at twice the resolution
+                want_kids = [find(lvl + 1, centre)]
+            else:
+                want_kids = [find(lvl + 1, info["r_min"] + (np.array([cx, cy, cz]) + 0.5) * fsize)
+                             for cz in (0, 1) for cy in (0, 1) for cx in (0, 1)]
+            want_kids = [k for k in want_kids if k is not None]
+            assert kids == want_kids, (lvl, key, kids, want_kids)
+        else:
+            assert kids == []
+    return n_checked
+
+
+@pytest.mark.parametrize("n,box,periodic", [(64, 16, (False,) * 3), ((64, 32, 32), 8, (False,) * 3), ((32, 64, 96), 16, (False, True, False)),
+                                            (32, 8, (True,) * 3), ((48, 48, 48), 8, (False,) * 3)])
+def test_uniform_tree_matches_plain_geometry(oracle, product, n, box, periodic):
+    for cls in (oracle.OracleMg, product.Mg):
+        mg = build_uniform(cls, n, box, periodic=periodic)
+        n3 = [n] * 3 if np.isscalar(n) else list(n)
+        assert check_tree_against_geometry(mg, n3, periodic) >= 6 * len(mg.ids(1))
+
+
+def test_refined_tree_matches_plain_geometry(oracle, product):
+    for cls in (oracle.OracleMg, product.Mg):
+        mg = cls(P.mg_laplacian, P.mg_smoother_gsrb)
+        mg.mg_set_methods()
+        mg.mg_allocate_storage = lambda: None         # tree only
+        P.build_amr_tree(mg, 3, [64] * 3, 16, [1.0 / 64] * 3)
+        check_tree_against_geometry(mg, [64] * 3, (False,) * 3)
+        # refinement boundaries: exactly the faces of the refined cubes that do not touch another fine box
+        n_rb = sum(1 for lvl in (2, 3) for id_ in mg.ids(lvl) for nbr in mg.box_info(id_)["neighbors"] if nbr == 0)
+        assert n_rb == 2 * 6 * 16                     # two refined cubes of 4^3 boxes: 6 faces x 4 x 4 box faces each
