@@ -56,17 +56,22 @@ struct ClusterTeam {
 };
 #endif
 
-// ---- coarse solve of ONE 2^3 box between physical boundaries (the coarsest level of every cubic hierarchy) by ONE warp:
-// the coarse loop of mg_fas_vcycle (src/m_multigrid.f90:202-208) runs 5-6 times per cycle for the Poisson problem and
-// 40-90 times for a Helmholtz / Neumann problem whose constant mode converges slowly; as interpreter operations each
-// colour half-sweep and each residual of these EIGHT cells costs a 1024-thread barrier and a pass through shared memory.
-// Here lane l < 8 keeps cell l = colour * 4 + k * 2 + j (hx = 1: i = colour ^ ((j + k) & 1)) in a register; the in-box
-// neighbours in x / y / z are lanes l ^ 4 / l ^ 5 / l ^ 6, the out-of-box one is the ghost value of simple_gather's
-// `outside` (same expression, same operand order); lanes 8-31 compute replicas.  No barrier, no memory traffic inside the
-// loop; the results (phi, res, iteration count) are those of the interpreter's loop bit for bit.
+// ---- coarse solve of a coarsest level of up to FOUR 2^3 boxes (one box: every cubic hierarchy; two or four: domains with
+// extents 2 : 1 : 1 or 2 : 2 : 1) by ONE warp: the coarse loop of mg_fas_vcycle (src/m_multigrid.f90:202-208) runs 5-6 times
+// per cycle for the Poisson problem and 40-90 times for a Helmholtz / Neumann problem whose constant mode converges slowly;
+// as interpreter operations each colour half-sweep and each residual of these few cells costs a 1024-thread barrier and a
+// pass through shared memory.  Here lane l keeps cell l & 7 = colour * 4 + k * 2 + j (hx = 1: i = colour ^ ((j + k) & 1)) of
+// box l >> 3 in a register; the in-box neighbours in x / y / z are lanes l ^ 4 / l ^ 5 / l ^ 6, the out-of-box one is the
+// face cell of the neighbouring box (another lane) or the ghost value of simple_gather's `outside` (same expression, same
+// operand order); lanes beyond the last box compute replicas of box 0 that are never stored.  No barrier, no memory
+// traffic inside the loop; the results (phi, res, iteration count) are those of the interpreter's loop bit for bit.
 __device__ __forceinline__ bool warp_coarse_ok(const LevelDev& L) {
-  if (L.nb != 1 || L.nc != 2) return false;
-  for (int f = 0; f < 6; ++f) if (L.fkind[f] != FK_PHYS) return false;
+  if (L.nc != 2 || L.nb < 1 || L.nb > 4) return false;
+  for (int q = 0; q < 6 * L.nb; ++q) {
+    const int kd = L.fkind[q];
+    if (kd == FK_SAME) { if (L.farg[q] < 0 || L.farg[q] >= L.nb) return false; }
+    else if (kd != FK_PHYS) return false;
+  }
   return true;
 }
 template <int OP>
@@ -74,31 +79,41 @@ __device__ void warp_coarse_solve(const LevelDev& L, const ParamsDev& P, int n_s
   constexpr bool VC = (OP != OP_LPL && OP != OP_HELMH);
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
+  const bool act = lane < 8 * L.nb;
+  const int bx = act ? lane >> 3 : 0;
   const int colour = (lane >> 2) & 1, idx = lane & 3, j = idx & 1, k = idx >> 1, i = colour ^ ((j + k) & 1);
-  const int g = colour * 4 + idx;
-  SimpleBc B; simple_bc(L, P, 0, B);
-  // the face through which this cell looks out of the box, per direction, and its boundary value (constant or stored plane)
+  const int g = bx * 8 + colour * 4 + idx;
+  SimpleBc B; simple_bc(L, P, bx, B);
+  // the face through which this cell looks out of its box, per direction: a neighbouring box (the lane that holds the cell
+  // across the face: same j, k for x; row nc - 1 - j for y; plane nc - 1 - k for z; always of the other colour) or a
+  // physical boundary with its boundary value (constant or stored plane)
   const int fx = i, fy = 2 + j, fz = 4 + k;
   double c0[3], c1[3], c2[3], bv[3];
+  int src[3];
+  bool same[3];
 #pragma unroll
   for (int f = 0; f < 6; ++f) {
     const int d = f >> 1;
     if (f == (d == 0 ? fx : d == 1 ? fy : fz)) {
-      const int a = L.farg[f];
+      const int q = bx * 6 + f, a = L.farg[q];
       const int t1 = d == 0 ? j : i, t2 = d == 2 ? j : k;
+      same[d] = L.fkind[q] == FK_SAME;
+      const int pos = d == 0 ? idx : d == 1 ? (k * 2 + (1 - j)) : ((1 - k) * 2 + j);
+      src[d] = same[d] ? a * 8 + (colour ^ 1) * 4 + pos : lane;
       c0[d] = B.c0[f]; c1[d] = B.c1[f]; c2[d] = B.c2[f];
-      bv[d] = a >= 0 ? L.bcpl[(size_t)a * 4 + t2 * 2 + t1] : B.bv[f];
+      bv[d] = (!same[d] && a >= 0) ? L.bcpl[(size_t)a * 4 + t2 * 2 + t1] : B.bv[f];
     }
   }
   double a0[6], a[6];
-  if (VC) simple_eps<OP>(L, 0, colour, idx, a0, a);
+  if (VC) simple_eps<OP>(L, bx, colour, idx, a0, a);
   double phi = L.var[0][g];
   const double rhs = L.var[1][g];
   auto gather = [&](double* u) {
     const double x = __shfl_xor_sync(full, phi, 4), y = __shfl_xor_sync(full, phi, 5), z = __shfl_xor_sync(full, phi, 6);
-    const double gx = c0[0] * bv[0] + c1[0] * phi + c2[0] * x;
-    const double gy = c0[1] * bv[1] + c1[1] * phi + c2[1] * y;
-    const double gz = c0[2] * bv[2] + c1[2] * phi + c2[2] * z;
+    const double ox = __shfl_sync(full, phi, src[0]), oy = __shfl_sync(full, phi, src[1]), oz = __shfl_sync(full, phi, src[2]);
+    const double gx = same[0] ? ox : c0[0] * bv[0] + c1[0] * phi + c2[0] * x;
+    const double gy = same[1] ? oy : c0[1] * bv[1] + c1[1] * phi + c2[1] * y;
+    const double gz = same[2] ? oz : c0[2] * bv[2] + c1[2] * phi + c2[2] * z;
     u[0] = i ? x : gx; u[1] = i ? gx : x;
     u[2] = j ? y : gy; u[3] = j ? gy : y;
     u[4] = k ? z : gz; u[5] = k ? gz : z;
@@ -112,7 +127,7 @@ __device__ void warp_coarse_solve(const LevelDev& L, const ParamsDev& P, int n_s
     else if (OP == OP_HELMH) v = lpl_value(L.idr2, phi, u) - P.lambda * phi;
     else { v = vlpl_value(L.idr2, phi, u, a0, a); if (OP != OP_VLPL) v = v - P.lambda * phi; }
     r = rhs - v;
-    double m = fabs(r);
+    double m = act ? fabs(r) : 0.0;
     for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(full, m, o));
     return m;
   };
@@ -131,7 +146,7 @@ __device__ void warp_coarse_solve(const LevelDev& L, const ParamsDev& P, int n_s
     it = n_it;
     if (res < scal[SCAL_COARSE_REL] * init_res || res < scal[SCAL_COARSE_ABS]) break;
   }
-  if (lane < 8) { L.var[0][g] = phi; L.var[3][g] = r; }
+  if (act) { L.var[0][g] = phi; L.var[3][g] = r; }
   if (lane == 0) scal[SCAL_COARSE_ITERS] = (double)it;
 }
 
@@ -201,7 +216,7 @@ __device__ void tail_run(const LevelDev* levels, const ParamsDev& P, const TailO
         break;
       case TOP_COARSE_SOLVE: {
         // coarse loop of mg_fas_vcycle, src/m_multigrid.f90:202-208
-        if (TEAM::warp_solve && fast && P.warp_coarse && warp_coarse_ok(L)) {      // one 2^3 box: one warp, cells in registers
+        if (TEAM::warp_solve && fast && P.warp_coarse && warp_coarse_ok(L)) {      // up to four 2^3 boxes: one warp, cells in registers
           if (threadIdx.x < 32) warp_coarse_solve<OP>(L, P, op.a, op.b, scal);
           break;
         }

@@ -61,6 +61,14 @@ static inline double __shfl_xor_sync(unsigned, double v, int o) {
   pthread_barrier_wait(&emu::g_warp_bar[t >> 5]);
   return r;
 }
+static inline double __shfl_sync(unsigned, double v, int src) {
+  const int t = (int)threadIdx.x;
+  emu::g_shfl[t] = v;
+  pthread_barrier_wait(&emu::g_warp_bar[t >> 5]);
+  const double r = emu::g_shfl[(t & ~31) | (src & 31)];
+  pthread_barrier_wait(&emu::g_warp_bar[t >> 5]);
+  return r;
+}
 static inline unsigned long long atomicMax(unsigned long long* a, unsigned long long v) {
   unsigned long long o = __atomic_load_n(a, __ATOMIC_RELAXED);
   while (o < v && !__atomic_compare_exchange_n(a, &o, v, false, __ATOMIC_SEQ_CST, __ATOMIC_RELAXED)) {}

@@ -129,7 +129,9 @@ def test_tail_interpreter_runs_a_vcycle_like_the_general_path(emu, op, lam, plan
     emu.fe_tail.argtypes = [C.c_int] * 8 + [C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_ulonglong]
     emu.dh_set_planes(planes)
     try:
-        cases = list(zip(BC_SETS, [(4, (1, 1, 1)), (4, (2, 1, 1)), (3, (1, 2, 1)), (3, (1, 1, 2))]))
+        # (four- and three-box coarsest levels: the warp-level coarse solve takes up to four 2^3 boxes, three is the odd case
+        # whose last eight lanes idle)
+        cases = list(zip(BC_SETS + BC_SETS[2:], [(4, (1, 1, 1)), (4, (2, 1, 1)), (3, (1, 2, 1)), (3, (1, 1, 2)), (3, (2, 2, 1)), (3, (3, 1, 1))]))
         for types, (n_levels, shape) in (cases[2:] if planes else cases):
             for simple in (0, 1):
                 for staged in (0, 1):
