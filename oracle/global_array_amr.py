@@ -22,7 +22,10 @@ BC_DIRICHLET, BC_NEUMANN, BC_CONTINUOUS = -10, -11, -12
 class GlobalAMR:
     def __init__(self, n_base, dr_base, patches, bc, lam=0.0, helmholtz=False, n_down=2, n_up=2, coarsest=2,
                  max_coarse_cycles=1000, res_abs=1e-8, res_rel=1e-8):
-        """n_base: cells per direction of the base level (the reference's level 1, a cube); dr_base: its spacing;
+        """n_base: cells per direction of the base level (the reference's level 1): one number (a cube) or (nx, ny, nz) -- the
+        levels below it halve every direction while all are even and none has reached `coarsest` (mg_build_rectangle,
+        src/m_build_tree.f90:51-72, in cells: whether boxes or the box size are halved makes no difference here);
+        dr_base: its spacing;
         patches: for each finer level in turn ((x0, y0, z0), (x1, y1, z1)), the patch [lo, hi) in cells of THAT level
         (even numbers; properly nested: a patch's coarse footprint lies inside the coarser patch with at least one
         coarse cell to spare wherever it does not touch the domain boundary);
@@ -31,13 +34,14 @@ class GlobalAMR:
         self.n_down, self.n_up = n_down, n_up
         self.max_coarse_cycles, self.res_abs, self.res_rel = max_coarse_cycles, res_abs, res_rel
         self.bc = list(bc)
+        n_base = np.array([n_base] * 3 if np.isscalar(n_base) else list(n_base), dtype=int)
         ns, drs = [n_base], [dr_base]
-        while ns[0] % 2 == 0 and ns[0] != coarsest:
+        while np.all(ns[0] % 2 == 0) and not np.any(ns[0] == coarsest):
             ns.insert(0, ns[0] // 2)
             drs.insert(0, drs[0] * 2)
         self.base = len(ns) - 1
         self.lo = [np.zeros(3, dtype=int) for _ in ns]
-        self.hi = [np.full(3, m, dtype=int) for m in ns]
+        self.hi = [m.copy() for m in ns]
         for lo, hi in patches:
             ns.append(ns[-1] * 2)
             drs.append(drs[-1] / 2)
@@ -48,7 +52,7 @@ class GlobalAMR:
             self.lo.append(lo)
             self.hi.append(hi)
         self.ns, self.drs, self.nl = ns, drs, len(ns)
-        z = lambda m: np.zeros((m + 2, m + 2, m + 2))
+        z = lambda m: np.zeros((m[2] + 2, m[1] + 2, m[0] + 2))
         self.phi = [z(m) for m in ns]
         self.rhs = [z(m) for m in ns]
         self.old = [z(m) for m in ns]
@@ -83,7 +87,7 @@ class GlobalAMR:
             s1, s2 = slice(lo[t1] + 1, hi[t1] + 1), slice(lo[t2] + 1, hi[t2] + 1)
             g, i1, i2 = (lo[d], lo[d] + 1, lo[d] + 2) if low else (hi[d] + 1, hi[d], hi[d] - 1)
             P = lambda q: self._plane(d, q, s1, s2)
-            if (low and lo[d] == 0) or (not low and hi[d] == n):
+            if (low and lo[d] == 0) or (not low and hi[d] == n[d]):
                 t, b = self.bc[nb - 1]
                 if t == BC_DIRICHLET:
                     c0, c1, c2 = 2.0, -1.0, 0.0

@@ -264,8 +264,8 @@ def _level_arrays(mg, lvl, iv):
     nc = mg.box_size_lvl(lvl)
     ids = mg.ids(lvl)
     ix = np.array([mg.box_info(i)["ix"] for i in ids])
-    n = int(round(1.0 / mg.dr(lvl)[0]))
-    out = np.zeros((n, n, n))
+    n = [int(round(e / mg.dr(lvl)[0])) for e in getattr(mg, "_domain_extent", (1.0, 1.0, 1.0))]
+    out = np.zeros((n[2], n[1], n[0]))
     for id_, (bx, by, bz) in zip(ids, ix):
         out[(bz - 1) * nc:bz * nc, (by - 1) * nc:by * nc, (bx - 1) * nc:bx * nc] = mg.cc(id_, nc)[iv - 1, 1:-1, 1:-1, 1:-1]
     lo, hi = (ix.min(axis=0) - 1) * nc, ix.max(axis=0) * nc
@@ -323,3 +323,30 @@ def test_global_array_restatement_refined_grid(oracle, case, helm):
         a, lo, hi = _level_arrays(mg, lvl, P.mg_iphi)
         s = tuple(slice(lo[d], hi[d]) for d in (2, 1, 0))
         assert np.array_equal(a[s], G.phi[l][1:-1, 1:-1, 1:-1][s]), lvl
+
+
+@pytest.mark.parametrize("dims,box,bc_name,helm", [((32, 16, 16), 8, "mixed", False), ((32, 16, 16), 8, "mixed", True),
+                                                   ((16, 32, 16), 4, "neumann0", True),      # (all-Neumann Laplacian: singular)
+                                                   ((32, 32, 16), 8, "dirichlet0", False), ((32, 32, 16), 8, "dirichlet0", True)])
+def test_global_array_restatement_non_cubic_grid(oracle, dims, box, bc_name, helm):
+    """non-cubic domains: the coarsening stops when one direction reaches two cells, so the coarsest level -- the one the
+    coarse solve iterates on (src/m_multigrid.f90:202-208) -- has 2 x 1 x 1 or 2 x 2 x 1 boxes.  The global-array multigrid
+    (its base level a brick) against the box-structured oracle, bit for bit: residual histories of FMG and V-cycles, phi
+    on every level"""
+    from oracle.global_array_amr import GlobalAMR
+    lam = 1.5 if helm else 0.0
+    mg, _ = P.uniform_problem(oracle.OracleMg, dims, box, operator_type=P.mg_helmholtz if helm else P.mg_laplacian, bc=bc_name, lam=lam)
+    mg._domain_extent = tuple(d / dims[0] for d in dims)
+    bc = {"mixed": [(P.mg_bc_dirichlet, 0.25)] + [(P.mg_bc_neumann, 0.5)] * 5, "neumann0": [(P.mg_bc_neumann, 0.0)] * 6,
+          "dirichlet0": [(P.mg_bc_dirichlet, 0.0)] * 6}[bc_name]
+    G = GlobalAMR(dims, 1.0 / dims[0], [], bc, lam=lam, helmholtz=helm)
+    levels = list(range(mg.lowest_lvl, mg.highest_lvl + 1))
+    assert G.nl == len(levels) and min(G.ns[0]) == 2 and max(G.ns[0]) > 2
+    a, lo, hi = _level_arrays(mg, mg.highest_lvl, P.mg_irhs)
+    G.rhs[-1][1:-1, 1:-1, 1:-1] = a
+    h_box = P.run_cycles(mg, 2, True) + P.run_cycles(mg, 2, False)
+    h_glob = [G.fmg(False), G.fmg(True), G.vcycle(), G.vcycle()]
+    assert h_box == h_glob
+    for l, lvl in enumerate(levels):
+        a, lo, hi = _level_arrays(mg, lvl, P.mg_iphi)
+        assert np.array_equal(a, G.phi[l][1:-1, 1:-1, 1:-1]), lvl
