@@ -9,7 +9,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import octree_mg_b200 as om
 import problems as P
 
-CASES = [("laplacian dirichlet0 rhs=1 128^3", 0, lambda: P.performance_problem(om.Mg, 128, 16, gpu_resident=True)),
+D = (256, 128, 128)      # non-cubic: the coarsest level has two 2^3 boxes
+CASES = [("laplacian dirichlet0 rhs=1 256x128x128", 0, lambda: P.performance_problem(om.Mg, D, 16, gpu_resident=True)),
+         ("helmholtz neumann0 256x128x128", 0, lambda: P.uniform_problem(om.Mg, D, 16, operator_type=P.mg_helmholtz, bc="neumann0", lam=1.0, gpu_resident=True)[0]),
+         ("laplacian dirichlet0 rhs=1 128^3", 0, lambda: P.performance_problem(om.Mg, 128, 16, gpu_resident=True)),
          ("helmholtz neumann0 128^3", 0, lambda: P.uniform_problem(om.Mg, 128, 16, operator_type=P.mg_helmholtz, bc="neumann0", lam=1.0, gpu_resident=True)[0]),
          ("vlaplacian mixed 128^3", 1, lambda: P.uniform_problem(om.Mg, 128, 16, operator_type=P.mg_vlaplacian, bc="mixed", gpu_resident=True)[0])]
 for name, ne, make in CASES:
